@@ -1,0 +1,535 @@
+// Fused exchange kernels over NVLink peer memory (sm_100a).
+//
+// Every GPU is a worker *and* the owner of one shard of the centre variable; the reference's
+// parameter-server round trips collapse into one-sided accesses issued from inside the kernel
+// that also does the math:
+//
+//   pull   (pclient.lua:74-84  <-> pserver.lua:65-79)   -> ld.relaxed.sys on the owner's shard
+//   push   (pclient.lua:49-59  <-> pserver.lua:83-98)   -> red.relaxed.sys.add (p += g on owner)
+//   seed   (pclient.lua:62-72  <-> pserver.lua:101-111) -> st.relaxed.sys
+//   elastic step (optim-eamsgd.lua:58-70 + :26-47)      -> one pass: pull, d = a(x - c), push d,
+//                                                          Nesterov apply/lookahead, operand pack
+//   allreduce (test/testreduceall.lua:28)               -> one-shot / two-shot over peer loads or
+//                                                          NVLS multimem.ld_reduce / multimem.st
+//
+// (paths relative to /root/reference/asyncsgd unless noted).  No NCCL or MPI call is made here.
+#include "mpit_b200.h"
+#include "comm.cuh"
+#include "optim_math.cuh"
+
+namespace mpit {
+
+// Walks the flat vector in units of 4 consecutive elements that never straddle a shard.
+struct QuadWalk {
+  Partition part;
+  long long qps;    // quads per regular shard
+  long long total;  // total quads
+  __host__ __device__ static QuadWalk make(long long n, int S) {
+    QuadWalk w;
+    w.part.n = n; w.part.S = S; w.part.base = n / S;
+    w.qps = (w.part.base + 3) / 4;
+    long long last = w.part.size(S - 1);
+    w.total = w.qps * (S - 1) + (last + 3) / 4;
+    return w;
+  }
+  __device__ __forceinline__ void at(long long q, int& s, long long& j0, long long& i0, int& cnt) const {
+    s = (qps > 0) ? (int)(q / qps) : part.S - 1;
+    if (s > part.S - 1) s = part.S - 1;
+    j0 = (q - qps * s) * 4;
+    i0 = part.begin(s) + j0;
+    long long rem = part.size(s) - j0;
+    cnt = rem >= 4 ? 4 : (int)rem;
+  }
+};
+
+__device__ __forceinline__ void load4(const float* p, long long i0, int cnt, float (&r)[4]) {
+  if (cnt == 4 && ((i0 & 3) == 0)) {
+    float4 t = ld4(p + i0);
+    r[0] = t.x; r[1] = t.y; r[2] = t.z; r[3] = t.w;
+  } else {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) r[k] = k < cnt ? p[i0 + k] : 0.f;
+  }
+}
+__device__ __forceinline__ void store4(float* p, long long i0, int cnt, const float (&r)[4]) {
+  if (cnt == 4 && ((i0 & 3) == 0)) {
+    st4(p + i0, make_float4(r[0], r[1], r[2], r[3]));
+  } else {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) if (k < cnt) p[i0 + k] = r[k];
+  }
+}
+// Owner-side accesses: j0 is always a multiple of 4 and shard buffers are 16-byte aligned and
+// padded to a multiple of 4 floats, so full quads are always vector accesses over NVLink.
+__device__ __forceinline__ void peer_load4(const float* p, int cnt, float (&r)[4]) {
+  if (cnt == 4) {
+    float4 t = ld_sys4(p);
+    r[0] = t.x; r[1] = t.y; r[2] = t.z; r[3] = t.w;
+  } else {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) r[k] = k < cnt ? ld_sys(p + k) : 0.f;
+  }
+}
+__device__ __forceinline__ void peer_store4(float* p, int cnt, const float (&r)[4]) {
+  if (cnt == 4) st_sys4(p, make_float4(r[0], r[1], r[2], r[3]));
+  else {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) if (k < cnt) st_sys(p + k, r[k]);
+  }
+}
+__device__ __forceinline__ void peer_red4(float* p, int cnt, const float (&r)[4]) {
+  if (cnt == 4) red_add_sys4(p, make_float4(r[0], r[1], r[2], r[3]));
+  else {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) if (k < cnt) red_add_sys(p + k, r[k]);
+  }
+}
+
+enum ExchMode : int { EX_PULL = 0, EX_PUT = 1, EX_PUSH = 2, EX_ELASTIC = 3, EX_FUSED = 4 };
+
+struct ExchArgs {
+  PeerTable tab;
+  QuadWalk walk;
+  float* x;            // local parameters (flat)
+  float* v;            // momentum
+  const float* g;      // gradient source (flat, or packed with gmap)
+  const int* gmap;
+  float* d;            // elastic difference buffer (read by apply, written by sync)
+  float* src;          // push source / pull destination when not x
+  float* wpk;
+  const int* wmap;
+  float alpha, clr, l2wd, mom_next, scale, l1, l2, clip;
+  int do_apply, use_mom, do_lookahead, do_sync, has_d_in, zero_src;
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(256) exchange_kernel(ExchArgs a) {
+  long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < a.walk.total; q += stride) {
+    int s, cnt;
+    long long j0, i0;
+    a.walk.at(q, s, j0, i0, cnt);
+    float* cptr = a.tab.peer[s] + j0;
+    if (MODE == EX_PULL) {
+      // x <- centre (MPI_Get).  Issue the remote load first; everything else hides under it.
+      float c[4];
+      peer_load4(cptr, cnt, c);
+      store4(a.src, i0, cnt, c);
+      if (a.wpk) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) if (k < cnt) a.wpk[a.wmap ? a.wmap[i0 + k] : i0 + k] = c[k];
+      }
+    } else if (MODE == EX_PUT) {
+      float r[4];
+      load4(a.src, i0, cnt, r);
+      peer_store4(cptr, cnt, r);
+    } else if (MODE == EX_PUSH) {
+      // centre += scale * clip(reg(g))   (MPI_Accumulate); optionally clears the accumulator.
+      float r[4];
+      load4(a.src, i0, cnt, r);
+      if (a.l1 != 0.f || a.l2 != 0.f || a.clip > 0.f) {
+        float p[4];
+        load4(a.x, i0, cnt, p);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) r[k] = grad_reg_clip(r[k], p[k], a.l1, a.l2, a.clip);
+      }
+      if (a.scale != 1.f) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) r[k] = mul_rn(r[k], a.scale);
+      }
+      peer_red4(cptr, cnt, r);
+      if (a.zero_src) {
+        float z[4] = {0.f, 0.f, 0.f, 0.f};
+        store4(a.src, i0, cnt, z);
+      }
+    } else {
+      // EX_ELASTIC / EX_FUSED
+      float c[4] = {0.f, 0.f, 0.f, 0.f};
+      if (a.do_sync) peer_load4(cptr, cnt, c);  // remote load in flight while we do the local step
+      float x[4], v[4] = {0.f, 0.f, 0.f, 0.f};
+      load4(a.x, i0, cnt, x);
+      if (a.use_mom) load4(a.v, i0, cnt, v);
+      if (MODE == EX_FUSED && a.do_apply) {
+        float g[4], din[4] = {0.f, 0.f, 0.f, 0.f};
+        if (a.gmap) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) g[k] = k < cnt ? a.g[a.gmap[i0 + k]] : 0.f;
+        } else {
+          load4(a.g, i0, cnt, g);
+        }
+        if (a.has_d_in) load4(a.d, i0, cnt, din);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          msgd_apply_elem(x[k], v[k], g[k], din[k], a.clr, a.l2wd, a.use_mom != 0, a.has_d_in != 0);
+      }
+      if (a.do_sync) {
+        float dd[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) dd[k] = mul_rn(a.alpha, sub_rn(x[k], c[k]));
+        peer_red4(cptr, cnt, dd);   // centre += d, fire-and-forget: completes under fwd/bwd
+        store4(a.d, i0, cnt, dd);
+      }
+      if (MODE == EX_FUSED) {
+        if (a.do_lookahead && a.use_mom) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) nesterov_lookahead_elem(x[k], v[k], a.mom_next);
+        }
+        store4(a.x, i0, cnt, x);
+        if (a.use_mom) store4(a.v, i0, cnt, v);
+        if (a.wpk) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) if (k < cnt) a.wpk[a.wmap ? a.wmap[i0 + k] : i0 + k] = x[k];
+        }
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// All-reduce family.  Buffers are symmetric: tab.peer[r] is rank r's input.
+// ---------------------------------------------------------------------------------------
+struct ArArgs {
+  PeerTable in;       // symmetric input buffers
+  PeerTable out;      // symmetric output buffers (two-shot gathers into every rank's out)
+  SignalTable sig;
+  float* local_out;   // one-shot: private output
+  float* x;           // elastic variant: local params to pull toward the mean
+  long long n;        // elements (multiple of 4 for the vector path; tail handled scalar)
+  float scale;        // 1 for SUM, 1/nranks for AVG
+  float alpha;        // elastic moving rate
+};
+
+// One-shot: every rank reads all inputs and keeps the whole sum (latency path, small messages).
+__global__ void __launch_bounds__(512) allreduce_oneshot_kernel(ArArgs a) {
+  block_barrier_sys(a.sig, blockIdx.x);  // inputs of every rank are in place
+  long long n4 = a.n >> 2;
+  long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    float4 acc;
+    if (a.in.mc) {
+      acc = multimem_ld_reduce_add4(a.in.mc + 4 * i);   // reduction happens inside the NVSwitch
+    } else {
+      float4 r[MPIT_MAX_RANKS];
+#pragma unroll
+      for (int p = 0; p < MPIT_MAX_RANKS; ++p)
+        if (p < a.in.nranks) r[p] = ld_sys4(a.in.peer[p] + 4 * i);   // all loads in flight first
+      acc = r[0];
+#pragma unroll
+      for (int p = 1; p < MPIT_MAX_RANKS; ++p)
+        if (p < a.in.nranks) { acc.x += r[p].x; acc.y += r[p].y; acc.z += r[p].z; acc.w += r[p].w; }
+    }
+    if (a.scale != 1.f) { acc.x *= a.scale; acc.y *= a.scale; acc.z *= a.scale; acc.w *= a.scale; }
+    if (a.x) {
+      // fused elastic pull toward the average: x -= alpha * (x - mean)
+      float4 x = ld4(a.x + 4 * i);
+      x.x = sub_rn(x.x, mul_rn(a.alpha, sub_rn(x.x, acc.x)));
+      x.y = sub_rn(x.y, mul_rn(a.alpha, sub_rn(x.y, acc.y)));
+      x.z = sub_rn(x.z, mul_rn(a.alpha, sub_rn(x.z, acc.z)));
+      x.w = sub_rn(x.w, mul_rn(a.alpha, sub_rn(x.w, acc.w)));
+      st4(a.x + 4 * i, x);
+    }
+    if (a.local_out) st4(a.local_out + 4 * i, acc);
+  }
+  if (blockIdx.x == 0) {
+    for (long long i = (n4 << 2) + threadIdx.x; i < a.n; i += blockDim.x) {
+      float acc = 0.f;
+      for (int p = 0; p < a.in.nranks; ++p) acc += ld_sys(a.in.peer[p] + i);
+      acc *= a.scale;
+      if (a.x) a.x[i] = sub_rn(a.x[i], mul_rn(a.alpha, sub_rn(a.x[i], acc)));
+      if (a.local_out) a.local_out[i] = acc;
+    }
+  }
+  block_barrier_sys(a.sig, blockIdx.x);  // nobody overwrites an input that is still being read
+}
+
+// Two-shot: rank r reduces slice r (reduce-scatter) and writes it into every rank's output
+// (all-gather) -- each byte crosses NVLink once in, once out (bandwidth path, large messages).
+__global__ void __launch_bounds__(512) allreduce_twoshot_kernel(ArArgs a) {
+  block_barrier_sys(a.sig, blockIdx.x);
+  int R = a.in.nranks, me = a.in.rank;
+  long long n4 = a.n >> 2;
+  long long per = (n4 + R - 1) / R;
+  long long lo = per * me, hi = lo + per < n4 ? lo + per : n4;
+  long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
+    float4 acc;
+    if (a.in.mc) {
+      acc = multimem_ld_reduce_add4(a.in.mc + 4 * i);
+    } else {
+      float4 r[MPIT_MAX_RANKS];
+#pragma unroll
+      for (int p = 0; p < MPIT_MAX_RANKS; ++p)
+        if (p < R) r[p] = ld_sys4(a.in.peer[(me + p) % R] + 4 * i);   // stagger peers across ranks
+      acc = r[0];
+#pragma unroll
+      for (int p = 1; p < MPIT_MAX_RANKS; ++p)
+        if (p < R) { acc.x += r[p].x; acc.y += r[p].y; acc.z += r[p].z; acc.w += r[p].w; }
+    }
+    if (a.scale != 1.f) { acc.x *= a.scale; acc.y *= a.scale; acc.z *= a.scale; acc.w *= a.scale; }
+    if (a.out.mc) {
+      multimem_st4(a.out.mc + 4 * i, acc);   // one store, the switch replicates it
+    } else {
+#pragma unroll
+      for (int p = 0; p < MPIT_MAX_RANKS; ++p)
+        if (p < R) st_sys4(a.out.peer[(me + p) % R] + 4 * i, acc);
+    }
+  }
+  if (me == R - 1 && blockIdx.x == 0) {
+    for (long long i = (n4 << 2) + threadIdx.x; i < a.n; i += blockDim.x) {
+      float acc = 0.f;
+      for (int p = 0; p < R; ++p) acc += ld_sys(a.in.peer[p] + i);
+      acc *= a.scale;
+      for (int p = 0; p < R; ++p) st_sys(a.out.peer[p] + i, acc);
+    }
+  }
+  block_barrier_sys(a.sig, blockIdx.x);  // every slice has landed everywhere
+  if (a.x) {
+    // elastic pull toward the mean, reading the gathered result locally
+    const float* mean = a.out.peer[me];
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += stride)
+      a.x[i] = sub_rn(a.x[i], mul_rn(a.alpha, sub_rn(a.x[i], mean[i])));
+  }
+}
+
+// Broadcast (MPI_Bcast, wrapped at /root/reference/mpifuncs.c:145): the root pushes.
+__global__ void __launch_bounds__(512) bcast_kernel(ArArgs a, int root) {
+  int R = a.out.nranks, me = a.out.rank;
+  long long stride = (long long)gridDim.x * blockDim.x;
+  if (me == root) {
+    const float* src = a.out.peer[me];
+    long long n4 = a.n >> 2;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+      float4 v = ld4(src + 4 * i);
+      if (a.out.mc) multimem_st4(a.out.mc + 4 * i, v);
+      else {
+#pragma unroll
+        for (int p = 0; p < MPIT_MAX_RANKS; ++p)
+          if (p < R && p != me) st_sys4(a.out.peer[p] + 4 * i, v);
+      }
+    }
+    if (blockIdx.x == 0)
+      for (long long i = (n4 << 2) + threadIdx.x; i < a.n; i += blockDim.x)
+        for (int p = 0; p < R; ++p) if (p != me) st_sys(a.out.peer[p] + i, src[i]);
+  }
+  block_barrier_sys(a.sig, blockIdx.x);
+}
+
+__global__ void barrier_kernel(SignalTable sig) { block_barrier_sys(sig, blockIdx.x); }
+
+// ---------------------------------------------------------------------------------------
+// Device mailbox: two-sided tagged messages as put + flag (MPI_Send/Recv latency path,
+// /root/reference/test.lua:32-38).  One slot per (src -> dst) pair in the receiver's memory:
+//   header {seq, tag, count, state} then payload.
+// ---------------------------------------------------------------------------------------
+struct MailboxSlot {
+  uint32_t seq;      // written last with release: message number, 0 = empty
+  uint32_t tag;
+  uint32_t count;    // floats
+  uint32_t ack;      // consumer writes seq here when it has copied the payload out
+};
+
+__global__ void __launch_bounds__(256)
+mailbox_put_kernel(float* slot_base, const float* payload, uint32_t count, uint32_t tag, uint32_t seq) {
+  MailboxSlot* hdr = reinterpret_cast<MailboxSlot*>(slot_base);
+  float* body = slot_base + 8;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
+    st_sys(body + i, payload[i]);
+  __threadfence_system();
+  __syncthreads();
+  // single-CTA launches only (latency path): the last thread publishes
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    st_sys(reinterpret_cast<float*>(&hdr->tag), __uint_as_float(tag));
+    st_sys(reinterpret_cast<float*>(&hdr->count), __uint_as_float(count));
+    st_release_sys_u32(&hdr->seq, seq);
+  }
+}
+
+// Copies the payload out if message `seq` with a matching tag has arrived; result[0] = 1 if so,
+// 0 if not yet (MPI_Iprobe + MPI_Recv in one); result[1] = count, result[2] = tag.
+__global__ void __launch_bounds__(256)
+mailbox_recv_kernel(float* slot_base, float* dst, uint32_t max_count, int tag, uint32_t seq, int* result) {
+  MailboxSlot* hdr = reinterpret_cast<MailboxSlot*>(slot_base);
+  __shared__ uint32_t s_ok, s_count;
+  if (threadIdx.x == 0) {
+    uint32_t got = ld_acquire_sys_u32(&hdr->seq);
+    uint32_t t = hdr->tag;
+    bool ok = (got == seq) && (tag < 0 || t == (uint32_t)tag);
+    s_ok = ok ? 1u : 0u;
+    s_count = ok ? (hdr->count < max_count ? hdr->count : max_count) : 0u;
+    result[0] = ok ? 1 : 0;
+    result[1] = (int)hdr->count;
+    result[2] = (int)t;
+  }
+  __syncthreads();
+  if (!s_ok) return;
+  const float* body = slot_base + 8;
+  for (uint32_t i = threadIdx.x; i < s_count; i += blockDim.x) dst[i] = body[i];
+  __syncthreads();
+  if (threadIdx.x == 0) st_release_sys_u32(&hdr->ack, seq);
+}
+
+static PeerTable make_table(const unsigned long long* ptrs, unsigned long long mc, int nranks, int rank) {
+  PeerTable t{};
+  for (int i = 0; i < MPIT_MAX_RANKS; ++i) t.peer[i] = i < nranks ? reinterpret_cast<float*>(ptrs[i]) : nullptr;
+  t.mc = reinterpret_cast<float*>(mc);
+  t.nranks = nranks;
+  t.rank = rank;
+  return t;
+}
+static SignalTable make_sig(const unsigned long long* ptrs, int nranks, int rank) {
+  SignalTable t{};
+  for (int i = 0; i < MPIT_MAX_RANKS; ++i) t.pad[i] = i < nranks ? reinterpret_cast<uint32_t*>(ptrs[i]) : nullptr;
+  t.nranks = nranks;
+  t.rank = rank;
+  return t;
+}
+
+static int exch_grid(const QuadWalk& w) { return ew_grid(w.total, 256, 2, 8); }
+
+}  // namespace mpit
+
+using namespace mpit;
+
+extern "C" {
+
+int mpit_signal_words(void) { return MPIT_SIGNAL_WORDS; }
+int mpit_max_ranks(void) { return MPIT_MAX_RANKS; }
+
+int mpit_param_pull(const unsigned long long* shard_ptrs, int nranks, int rank, float* dst, long long n,
+                    float* wpk, const int* wmap, void* stream) {
+  if (n <= 0) return 0;
+  if (nranks < 1 || nranks > MPIT_MAX_RANKS) return MPIT_E_ARG;
+  ExchArgs a{};
+  a.tab = make_table(shard_ptrs, 0, nranks, rank);
+  a.walk = QuadWalk::make(n, nranks);
+  a.src = dst; a.wpk = wpk; a.wmap = wmap;
+  exchange_kernel<EX_PULL><<<exch_grid(a.walk), 256, 0, (cudaStream_t)stream>>>(a);
+  MPIT_LAUNCH_CHECK();
+  return 0;
+}
+
+int mpit_param_put(const unsigned long long* shard_ptrs, int nranks, int rank, const float* src, long long n,
+                   void* stream) {
+  if (n <= 0) return 0;
+  if (nranks < 1 || nranks > MPIT_MAX_RANKS) return MPIT_E_ARG;
+  ExchArgs a{};
+  a.tab = make_table(shard_ptrs, 0, nranks, rank);
+  a.walk = QuadWalk::make(n, nranks);
+  a.src = const_cast<float*>(src);
+  exchange_kernel<EX_PUT><<<exch_grid(a.walk), 256, 0, (cudaStream_t)stream>>>(a);
+  MPIT_LAUNCH_CHECK();
+  return 0;
+}
+
+int mpit_push_add(const unsigned long long* shard_ptrs, int nranks, int rank, float* src, const float* params,
+                  long long n, float scale, float l1, float l2, float clip, int zero_src, void* stream) {
+  if (n <= 0) return 0;
+  if (nranks < 1 || nranks > MPIT_MAX_RANKS) return MPIT_E_ARG;
+  ExchArgs a{};
+  a.tab = make_table(shard_ptrs, 0, nranks, rank);
+  a.walk = QuadWalk::make(n, nranks);
+  a.src = src; a.x = const_cast<float*>(params);
+  a.scale = scale; a.l1 = l1; a.l2 = l2; a.clip = clip; a.zero_src = zero_src;
+  if ((l1 != 0.f || l2 != 0.f) && !params) return MPIT_E_ARG;
+  exchange_kernel<EX_PUSH><<<exch_grid(a.walk), 256, 0, (cudaStream_t)stream>>>(a);
+  MPIT_LAUNCH_CHECK();
+  return 0;
+}
+
+int mpit_elastic_exchange(const unsigned long long* shard_ptrs, int nranks, int rank, const float* x, float* d,
+                          long long n, float alpha, void* stream) {
+  if (n <= 0) return 0;
+  if (nranks < 1 || nranks > MPIT_MAX_RANKS) return MPIT_E_ARG;
+  ExchArgs a{};
+  a.tab = make_table(shard_ptrs, 0, nranks, rank);
+  a.walk = QuadWalk::make(n, nranks);
+  a.x = const_cast<float*>(x); a.d = d; a.alpha = alpha; a.do_sync = 1;
+  exchange_kernel<EX_ELASTIC><<<exch_grid(a.walk), 256, 0, (cudaStream_t)stream>>>(a);
+  MPIT_LAUNCH_CHECK();
+  return 0;
+}
+
+int mpit_eamsgd_fused_step(const unsigned long long* shard_ptrs, int nranks, int rank, float* x, float* v,
+                           const float* g, const int* gmap, float* d, float* wpk, const int* wmap,
+                           long long n, float alpha, float clr, float l2wd, float mom_next, int do_apply,
+                           int use_mom, int do_lookahead, int do_sync, int has_d_in, void* stream) {
+  if (n <= 0) return 0;
+  if (nranks < 1 || nranks > MPIT_MAX_RANKS) return MPIT_E_ARG;
+  ExchArgs a{};
+  a.tab = make_table(shard_ptrs, 0, nranks, rank);
+  a.walk = QuadWalk::make(n, nranks);
+  a.x = x; a.v = v; a.g = g; a.gmap = gmap; a.d = d; a.wpk = wpk; a.wmap = wmap;
+  a.alpha = alpha; a.clr = clr; a.l2wd = l2wd; a.mom_next = mom_next;
+  a.do_apply = do_apply; a.use_mom = use_mom; a.do_lookahead = do_lookahead; a.do_sync = do_sync;
+  a.has_d_in = has_d_in;
+  exchange_kernel<EX_FUSED><<<exch_grid(a.walk), 256, 0, (cudaStream_t)stream>>>(a);
+  MPIT_LAUNCH_CHECK();
+  return 0;
+}
+
+static int ar_grid(long long n, int max_blocks) {
+  long long need = ((n >> 2) + 511) / 512;
+  if (need < 1) need = 1;
+  if (need > max_blocks) need = max_blocks;
+  return (int)need;
+}
+
+int mpit_allreduce(const unsigned long long* in_ptrs, unsigned long long in_mc,
+                   const unsigned long long* out_ptrs, unsigned long long out_mc,
+                   const unsigned long long* sig_ptrs, int nranks, int rank, float* local_out, float* x_elastic,
+                   long long n, float scale, float alpha, int algo, int max_blocks, void* stream) {
+  if (n <= 0) return 0;
+  if (nranks < 1 || nranks > MPIT_MAX_RANKS) return MPIT_E_ARG;
+  if (max_blocks <= 0 || max_blocks > MPIT_BARRIER_BLOCKS) max_blocks = MPIT_BARRIER_BLOCKS;
+  ArArgs a{};
+  a.in = make_table(in_ptrs, in_mc, nranks, rank);
+  a.sig = make_sig(sig_ptrs, nranks, rank);
+  a.local_out = local_out; a.x = x_elastic; a.n = n; a.scale = scale; a.alpha = alpha;
+  int grid = ar_grid(n, max_blocks);
+  if (algo == 0) {
+    allreduce_oneshot_kernel<<<grid, 512, 0, (cudaStream_t)stream>>>(a);
+  } else {
+    if (!out_ptrs) return MPIT_E_ARG;
+    a.out = make_table(out_ptrs, out_mc, nranks, rank);
+    allreduce_twoshot_kernel<<<grid, 512, 0, (cudaStream_t)stream>>>(a);
+  }
+  MPIT_LAUNCH_CHECK();
+  return 0;
+}
+
+int mpit_bcast(const unsigned long long* buf_ptrs, unsigned long long buf_mc, const unsigned long long* sig_ptrs,
+               int nranks, int rank, int root, long long n, int max_blocks, void* stream) {
+  if (n <= 0) return 0;
+  if (nranks < 1 || nranks > MPIT_MAX_RANKS || root < 0 || root >= nranks) return MPIT_E_ARG;
+  if (max_blocks <= 0 || max_blocks > MPIT_BARRIER_BLOCKS) max_blocks = MPIT_BARRIER_BLOCKS;
+  ArArgs a{};
+  a.out = make_table(buf_ptrs, buf_mc, nranks, rank);
+  a.sig = make_sig(sig_ptrs, nranks, rank);
+  a.n = n;
+  bcast_kernel<<<ar_grid(n, max_blocks), 512, 0, (cudaStream_t)stream>>>(a, root);
+  MPIT_LAUNCH_CHECK();
+  return 0;
+}
+
+int mpit_device_barrier(const unsigned long long* sig_ptrs, int nranks, int rank, void* stream) {
+  if (nranks < 1 || nranks > MPIT_MAX_RANKS) return MPIT_E_ARG;
+  barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(make_sig(sig_ptrs, nranks, rank));
+  MPIT_LAUNCH_CHECK();
+  return 0;
+}
+
+int mpit_mailbox_put(float* slot_base, const float* payload, unsigned count, unsigned tag, unsigned seq,
+                     void* stream) {
+  mailbox_put_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(slot_base, payload, count, tag, seq);
+  MPIT_LAUNCH_CHECK();
+  return 0;
+}
+
+int mpit_mailbox_recv(float* slot_base, float* dst, unsigned max_count, int tag, unsigned seq, int* result3,
+                      void* stream) {
+  mailbox_recv_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(slot_base, dst, max_count, tag, seq, result3);
+  MPIT_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,82 @@
+// Shared device/host helpers for the mpit_b200 sm_100a kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define MPIT_NUM_SMS 148  // B200: 2 dies x 74 SMs
+
+#define MPIT_LAUNCH_CHECK()                         \
+  do {                                              \
+    cudaError_t e__ = cudaGetLastError();           \
+    if (e__ != cudaSuccess) return (int)e__;        \
+  } while (0)
+
+#define MPIT_CUDA_TRY(expr)                         \
+  do {                                              \
+    cudaError_t e__ = (expr);                       \
+    if (e__ != cudaSuccess) return (int)e__;        \
+  } while (0)
+
+namespace mpit {
+
+// Grid sizing for streaming elementwise kernels: enough CTAs for >= 2 waves on
+// 148 SMs but never more than the work needs.
+static inline int ew_grid(long long n_items, int threads, int items_per_thread = 4, int max_ctas_per_sm = 8) {
+  long long per_cta = (long long)threads * items_per_thread;
+  long long need = (n_items + per_cta - 1) / per_cta;
+  long long cap = (long long)MPIT_NUM_SMS * max_ctas_per_sm;
+  if (need < 1) need = 1;
+  return (int)(need < cap ? need : cap);
+}
+
+__device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ void st4(float* p, const float4& v) { *reinterpret_cast<float4*>(p) = v; }
+
+// Streaming (read-once) 128-bit load that does not allocate in L1.
+__device__ __forceinline__ float4 ld4_stream(const float* p) {
+  float4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+  return r;
+}
+
+// Non-fused fp32 arithmetic: the optimizer kernels promise the same rounding as a
+// plain CPU fp32 restatement (one rounding per op, no FMA contraction), so that a
+// single-worker trajectory is bit-reproducible against the NumPy/torch oracle.
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float sub_rn(float a, float b) { return __fsub_rn(a, b); }
+
+// Philox4x32-10 counter RNG (stateless; used for dropout masks and sampling).
+struct Philox {
+  __device__ __forceinline__ static uint4 round(uint4 c, uint2 k) {
+    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
+    uint32_t hi0 = __umulhi(M0, c.x), lo0 = M0 * c.x;
+    uint32_t hi1 = __umulhi(M1, c.z), lo1 = M1 * c.z;
+    return make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+  }
+  __device__ __forceinline__ static uint4 gen(uint64_t seed, uint64_t ctr, uint32_t stream) {
+    uint2 k = make_uint2((uint32_t)seed, (uint32_t)(seed >> 32));
+    uint4 c = make_uint4((uint32_t)ctr, (uint32_t)(ctr >> 32), stream, 0u);
+#pragma unroll
+    for (int i = 0; i < 10; ++i) {
+      c = round(c, k);
+      k.x += 0x9E3779B9u;
+      k.y += 0xBB67AE85u;
+    }
+    return c;
+  }
+};
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+}  // namespace mpit

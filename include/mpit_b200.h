@@ -1,0 +1,147 @@
+/* mpit_b200 -- C ABI of the sm_100a kernel library (libmpit_kernels.so).
+ *
+ * Conventions
+ *   - every entry point returns 0 on success or a cudaError_t value (negative values are
+ *     library-level errors, see MPIT_E_*);
+ *   - pointers are device pointers unless the name says host; `stream` is a cudaStream_t
+ *     passed as void*; nothing here synchronises the stream;
+ *   - "flat" tensors are in the reference's getParameters() order
+ *     (/root/reference/asyncsgd/goot.lua:41), "packed" tensors are in the tensor-core
+ *     operand layouts described in DESIGN.md; `*map` arrays translate flat index -> packed
+ *     offset.
+ *
+ * The reference's native layer is a Lua binding of MPI (/root/reference/lua-mpi.h,
+ * /root/reference/mpifuncs.c); it has no device code.  The host message layer that takes
+ * its place is declared in mpit_msg.h; this header is the device side.
+ */
+#ifndef MPIT_B200_H_
+#define MPIT_B200_H_
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MPIT_E_UNSUPPORTED (-2)
+#define MPIT_E_TIMEOUT (-3)
+#define MPIT_E_ARG (-4)
+
+/* ---- optimizer rules (csrc/kernels/optim.cu) ------------------------------------------ */
+
+/* Rule ids for mpit_rule_step (server rules of /root/reference/BiCNN/pserver.lua:123-198 and
+ * the single-worker rules of /root/reference/BiCNN/optim-*-single.lua). */
+enum { MPIT_RULE_ADD = 0, MPIT_RULE_RMSPROP = 1, MPIT_RULE_ADAM = 2, MPIT_RULE_ADAMAX = 3,
+       MPIT_RULE_ADAGRAD = 4, MPIT_RULE_ADADELTA = 5 };
+
+/* Nesterov SGD halves fused into one pass (/root/reference/asyncsgd/optim-msgd.lua:20-39,
+ * /root/reference/asyncsgd/optim-eamsgd.lua:26-47,70):
+ *   do_apply:     g' = g[gmap] + l2wd*x ; x -= clr*g' ; v -= clr*g' ; x -= d
+ *   do_lookahead: v *= mom_next ; x += v
+ *   wpk != NULL:  wpk[wmap[i]] = x[i]   (refresh tensor-core operand copy) */
+int mpit_local_step(float* x, float* v, const float* g, const int* gmap, const float* d, float* wpk,
+                    const int* wmap, long long n, float clr, float l2wd, float mom_next, int do_apply,
+                    int use_mom, int do_lookahead, void* stream);
+
+/* One fused pass of a server/single rule. hyper6 is a HOST array {a,b,c,d,eps,step}
+ * (see csrc/kernels/optim_math.cuh). Optional gradient prologue: gscale, L1, L2, clamp
+ * (/root/reference/BiCNN/bicnn.lua:398-409). */
+int mpit_rule_step(int rule, float* p, const float* g, const int* gmap, float* s0, float* s1, float* s2,
+                   float* wpk, const int* wmap, long long n, const float* hyper6, float l1, float l2,
+                   float clip, float gscale, void* stream);
+
+/* Downpour client accumulate (/root/reference/asyncsgd/optim-downpour.lua:26-45). */
+int mpit_downpour_accum(float* x, float* acc, const float* g, const int* gmap, float* wpk, const int* wmap,
+                        long long n, float neg_lr, float l2wd, int move_local, void* stream);
+
+int mpit_grad_reg_clip(float* g, const float* p, long long n, float l1, float l2, float clip, void* stream);
+
+/* dst[i] = src[map[i]] (scatter=0) or dst[map[i]] = src[i] (scatter=1). */
+int mpit_map_copy(float* dst, const float* src, const int* map, long long n, int scatter, void* stream);
+
+/* ---- fp32 CUDA-core reference layers (csrc/kernels/nn_ref.cu) -------------------------- */
+/* geom12 is a HOST array {B,SH,SW,H,W,C,KH,KW,KWP,OH,OW,CO}.  `rng` is a DEVICE array
+ * {seed, step} keying the Philox dropout stream; mpit_nll_fwd_bwd increments rng_inc[1]. */
+int mpit_conv_fwd_ref(const int* geom12, const float* x, const float* w, const float* bias, const int* crop,
+                      float* out, unsigned char* pool_idx, int relu, int pool, int dropout,
+                      const unsigned long long* rng, void* stream);
+int mpit_conv_dgrad_ref(const int* geom12, const float* dz, const float* w, float* dx, void* stream);
+int mpit_conv_wgrad_ref(const int* geom12, const float* dz, const float* x, const int* crop, float* dw,
+                        void* stream);
+int mpit_act_bwd(const float* dout, const float* out, const unsigned char* pool_idx, float* dz, int B, int OH,
+                 int OW, int C, int pool, float scale, void* stream);
+int mpit_colsum(const float* dz, float* db, long long rows, int C, void* stream);
+int mpit_prep_u8(const unsigned char* src, float* dst, int B, int SH, int SW, void* stream);
+int mpit_nll_fwd_bwd(const float* logits, const int* labels, float* dlogits, float* loss_sum, int* confusion,
+                     int B, int ncls, int ld, float gscale, unsigned long long* rng_inc, void* stream);
+
+/* ---- NVLink exchange kernels (csrc/kernels/comm.cu) -------------------------------------- */
+/* `shard_ptrs` is a HOST array of nranks device addresses: entry s is rank s's shard of the
+ * centre variable mapped into this process (symmetric heap).  The flat vector of n floats is
+ * partitioned as in /root/reference/asyncsgd/pclient.lua:118-128 (floor(n/S) each, last takes
+ * the remainder); shard buffers must be 16-byte aligned and padded to a multiple of 4 floats. */
+int mpit_signal_words(void);
+int mpit_max_ranks(void);
+
+/* Get: dst[i] = centre[i]  (pclient.lua:74-84); optionally also refreshes the packed operand copy. */
+int mpit_param_pull(const unsigned long long* shard_ptrs, int nranks, int rank, float* dst, long long n,
+                    float* wpk, const int* wmap, void* stream);
+/* Put: centre[i] = src[i]  (seed, pclient.lua:62-72,131-133; single-mode push). */
+int mpit_param_put(const unsigned long long* shard_ptrs, int nranks, int rank, const float* src, long long n,
+                   void* stream);
+/* Accumulate: centre[i] += scale * clip(reg(src[i]))  (pserver.lua:91), optionally zeroing src
+ * (optim-downpour.lua:42). `params` is only read when l1/l2 != 0. */
+int mpit_push_add(const unsigned long long* shard_ptrs, int nranks, int rank, float* src, const float* params,
+                  long long n, float scale, float l1, float l2, float clip, int zero_src, void* stream);
+/* d = alpha*(x - centre); centre += d  (optim-eamsgd.lua:58-65). */
+int mpit_elastic_exchange(const unsigned long long* shard_ptrs, int nranks, int rank, const float* x, float* d,
+                          long long n, float alpha, void* stream);
+/* The whole EAMSGD step boundary in one pass: apply(t-1) [x -= clr g; v -= clr g; x -= d_in],
+ * elastic(t) when do_sync [d = alpha (x - centre); centre += d], lookahead(t) [v *= mom; x += v],
+ * and refresh of the packed operand copy (optim-eamsgd.lua:26-47,58-70). */
+int mpit_eamsgd_fused_step(const unsigned long long* shard_ptrs, int nranks, int rank, float* x, float* v,
+                           const float* g, const int* gmap, float* d, float* wpk, const int* wmap,
+                           long long n, float alpha, float clr, float l2wd, float mom_next, int do_apply,
+                           int use_mom, int do_lookahead, int do_sync, int has_d_in, void* stream);
+/* SUM/AVG all-reduce over symmetric buffers (test/testreduceall.lua:28). algo 0 = one-shot,
+ * 1 = two-shot. `in_mc`/`out_mc` are NVLS multicast addresses (0 = use peer loads/stores).
+ * x_elastic != NULL fuses x -= alpha*(x - mean). All ranks must call with identical n/max_blocks. */
+int mpit_allreduce(const unsigned long long* in_ptrs, unsigned long long in_mc,
+                   const unsigned long long* out_ptrs, unsigned long long out_mc,
+                   const unsigned long long* sig_ptrs, int nranks, int rank, float* local_out, float* x_elastic,
+                   long long n, float scale, float alpha, int algo, int max_blocks, void* stream);
+int mpit_bcast(const unsigned long long* buf_ptrs, unsigned long long buf_mc, const unsigned long long* sig_ptrs,
+               int nranks, int rank, int root, long long n, int max_blocks, void* stream);
+int mpit_device_barrier(const unsigned long long* sig_ptrs, int nranks, int rank, void* stream);
+/* Device mailbox (MPI_Send/Recv latency path, /root/reference/test.lua:32-38). A slot is 8 header
+ * floats + payload in the receiver's symmetric memory. result3 = {arrived, count, tag}. */
+int mpit_mailbox_put(float* slot_base, const float* payload, unsigned count, unsigned tag, unsigned seq,
+                     void* stream);
+int mpit_mailbox_recv(float* slot_base, float* dst, unsigned max_count, int tag, unsigned seq, int* result3,
+                      void* stream);
+
+/* ---- symmetric heap (csrc/symm/symm_heap.cu) --------------------------------------------- */
+/* Takes the place of the reference's CUDA-aware-MPI pointer bridge (/root/reference/lua-mpi.h:70-78).
+ * All sizes in bytes; pointers are returned as integers. VMM calls return 1000+CUresult on a
+ * driver error. */
+int mpit_symm_malloc(unsigned long long bytes, unsigned long long* out_ptr);
+int mpit_symm_free(unsigned long long ptr);
+int mpit_symm_ipc_export(unsigned long long ptr, void* handle64);
+int mpit_symm_ipc_import(const void* handle64, unsigned long long* out_ptr);
+int mpit_symm_ipc_close(unsigned long long ptr);
+int mpit_enable_peer_access(int dev, int peer);
+long long mpit_vmm_granularity(int dev, int nranks, int with_multicast);
+int mpit_vmm_multicast_supported(int dev);
+int mpit_vmm_alloc(int dev, unsigned long long bytes, unsigned long long* out_ptr, int* out_fd);
+int mpit_fd_from_pid(int pid, int remote_fd);
+int mpit_vmm_import(int dev, int fd, unsigned long long bytes, unsigned long long* out_ptr);
+int mpit_mc_create(int nranks, unsigned long long bytes, unsigned long long* out_handle, int* out_fd);
+int mpit_mc_import(int fd, unsigned long long* out_handle);
+int mpit_mc_add_device(unsigned long long mc_handle, int dev);
+int mpit_mc_bind(unsigned long long mc_handle, unsigned long long local_ptr, unsigned long long bytes);
+int mpit_mc_map(unsigned long long mc_handle, int dev, unsigned long long bytes, unsigned long long* out_ptr);
+int mpit_vmm_free(unsigned long long ptr);
+int mpit_close_fd(int fd);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MPIT_B200_H_ */

@@ -1,0 +1,236 @@
+"""Device-side optimizers: fused kernel schedules around an engine's forward/backward.
+
+An *engine* (e.g. ``models.cifar_cnn.CifarEngine``) exposes ``wpk`` (packed operand copy of the
+parameters), ``gpk`` (packed gradients), ``wmap`` (flat -> packed index map) and ``fwd_bwd()``.
+Each optimizer below owns the flat fp32 state in the reference's parameter order and drives one
+training step as ``boundary kernel -> fwd_bwd``; the boundary kernel finishes step t-1 (apply),
+does step t's exchange with the sharded centre over NVLink and prepares step t (Nesterov
+look-ahead + operand refresh) in ONE pass over the parameters.  Steps are captured into CUDA
+graphs after their first eager run.
+
+Semantics mirror asyncsgd/optim-msgd.lua, optim-downpour.lua, optim-eamsgd.lua and the BiCNN
+``*-single`` rules; see ``optim/reference.py`` for the line-by-line restatements they are tested
+against.
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, Optional
+
+import torch
+
+from .. import ops
+from .._native import launches
+from ..parallel.center import ShardedCenter
+
+
+class _GraphCache:
+    """Eager on first sight of a step variant, capture on the second, replay afterwards."""
+
+    def __init__(self, enabled: bool):
+        self.enabled = enabled
+        self.seen: Dict[tuple, int] = {}
+        self.graphs: Dict[tuple, tuple] = {}
+
+    def run(self, key: tuple, fn) -> None:
+        if not self.enabled:
+            fn()
+            return
+        if key in self.graphs:
+            g, n = self.graphs[key]
+            g.replay()
+            launches.count += n
+            return
+        n_seen = self.seen.get(key, 0)
+        self.seen[key] = n_seen + 1
+        if n_seen == 0:
+            fn()
+            return
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        before = launches.count
+        with torch.cuda.graph(g):
+            fn()
+        n = launches.count - before
+        launches.count = before
+        self.graphs[key] = (g, n)
+        g.replay()
+        launches.count += n
+
+
+class _DeviceOptBase:
+    def __init__(self, engine, theta0: torch.Tensor, use_graphs: bool = True):
+        self.engine = engine
+        self.dev = engine.wpk.device
+        self.x = theta0.detach().to(self.dev, torch.float32).clone().contiguous()
+        self.n = self.x.numel()
+        self.t = 0                      # pversion: number of completed local steps
+        self.graphs = _GraphCache(use_graphs)
+        self.pending_apply = False      # a gradient is sitting in engine.gpk, not yet applied
+
+    def params(self) -> torch.Tensor:
+        """Flat parameters with every computed gradient applied."""
+        self.finalize()
+        return self.x
+
+    def finalize(self) -> None:  # overridden
+        pass
+
+
+class DeviceMSGD(_DeviceOptBase):
+    """Nesterov momentum SGD on one GPU (asyncsgd/optim-msgd.lua:6-42)."""
+
+    def __init__(self, engine, theta0, *, lr, mom=0.0, l2wd=0.0, lrd=0.0, lrp=0.0, mommax=1.0, momdecay=0.0,
+                 use_graphs=True):
+        super().__init__(engine, theta0, use_graphs and lrd == 0 and momdecay == 0)
+        self.lr, self.mom, self.l2wd, self.lrd, self.lrp = lr, mom, l2wd, lrd, lrp
+        self.mommax, self.momdecay = mommax, momdecay
+        self.v = torch.zeros_like(self.x) if mom > 0 else None
+        self.engine.load_flat(self.x)
+
+    def _clr(self, t):
+        if self.lrd > 0 and self.lrp > 0:
+            return self.lr / math.pow(1 + t * self.lrd, self.lrp)
+        return self.lr
+
+    def _mom(self, t):
+        if self.mom > 0 and self.momdecay > 0:
+            return min(self.mommax, 1 - 0.5 / (1 + t / self.momdecay))
+        return self.mom
+
+    def _boundary(self, do_apply: bool, do_lookahead: bool):
+        e = self.engine
+        ops.local_step(self.x, self.v, e.gpk, e.wmap, None, e.wpk, e.wmap, clr=self._clr(self.t - 1),
+                       l2wd=self.l2wd, mom_next=self._mom(self.t), do_apply=do_apply, use_mom=self.mom > 0,
+                       do_lookahead=do_lookahead)
+
+    def step(self) -> None:
+        do_apply = self.pending_apply
+
+        def body():
+            self._boundary(do_apply, True)
+            self.engine.fwd_bwd()
+
+        self.graphs.run(("step", do_apply), body)
+        self.pending_apply = True
+        self.t += 1
+
+    def finalize(self) -> None:
+        if self.pending_apply:
+            self._boundary(True, False)
+            self.pending_apply = False
+
+
+class DeviceEAMSGD(_DeviceOptBase):
+    """Asynchronous EASGD/EAMSGD against an NVLink-sharded centre (asyncsgd/optim-eamsgd.lua:7-79).
+
+    Per step ONE fused kernel touches the parameters: it applies the previous gradient
+    (``x -= clr g; v -= clr g; x -= d``), on sync steps reads the centre shards from their owners,
+    forms ``d = mva (x - centre)`` and accumulates it into the owners with ``red.add`` (fire and
+    forget: it completes under the following forward/backward), then does the Nesterov look-ahead
+    and refreshes the tensor-core operand copy.
+    """
+
+    def __init__(self, engine, theta0, center: ShardedCenter, *, lr, mva, su=1, mom=0.0, l2wd=0.0, lrd=0.0,
+                 lrp=0.0, seed_center: Optional[bool] = None, use_graphs=True):
+        super().__init__(engine, theta0, use_graphs and not (lrd != 0 and lrp > 0))
+        assert su > 0 and mva > 0, "eamsgd needs su > 0 and mva > 0 (optim-eamsgd.lua:50)"
+        self.center = center
+        self.lr, self.mva, self.su, self.mom, self.l2wd, self.lrd, self.lrp = lr, mva, su, mom, l2wd, lrd, lrp
+        self.v = torch.zeros_like(self.x) if mom > 0 else None
+        self.d = torch.zeros_like(self.x)
+        self.prev_sync = False
+        # the first client seeds the servers (pclient.lua:131-133)
+        if seed_center if seed_center is not None else center.rank == 0:
+            center.put(self.x)
+        self.engine.load_flat(self.x)
+
+    def _clr(self, t):
+        if self.lrd != 0 and self.lrp > 0:
+            return self.lr / math.pow(1 + t * self.lrd, self.lrp)
+        return self.lr
+
+    def _boundary(self, do_apply, do_lookahead, do_sync, has_d_in):
+        e = self.engine
+        self.center.eamsgd_step(self.x, self.v, e.gpk, e.wmap, self.d, e.wpk, e.wmap, alpha=self.mva,
+                                clr=self._clr(self.t - 1), l2wd=self.l2wd, mom_next=self.mom,
+                                do_apply=do_apply, use_mom=self.mom > 0, do_lookahead=do_lookahead,
+                                do_sync=do_sync, has_d_in=has_d_in)
+
+    def step(self) -> None:
+        do_apply = self.pending_apply
+        do_sync = self.t % self.su == 0
+        has_d_in = do_apply and self.prev_sync
+
+        def body():
+            self._boundary(do_apply, True, do_sync, has_d_in)
+            self.engine.fwd_bwd()
+
+        self.graphs.run(("step", do_apply, do_sync, has_d_in), body)
+        self.pending_apply = True
+        self.prev_sync = do_sync
+        self.t += 1
+
+    def finalize(self) -> None:
+        if self.pending_apply:
+            self._boundary(True, False, False, self.prev_sync)
+            self.pending_apply = False
+            self.prev_sync = False
+
+
+class DeviceDownpour(_DeviceOptBase):
+    """Downpour / hogwild SGD against the sharded centre (asyncsgd/optim-downpour.lua:6-60)."""
+
+    def __init__(self, engine, theta0, center: ShardedCenter, *, lr, su=1, l2wd=0.0, lrd=0.0,
+                 seed_center: Optional[bool] = None, use_graphs=True):
+        super().__init__(engine, theta0, use_graphs and lrd == 0)
+        assert su >= 1
+        self.center = center
+        self.lr, self.su, self.l2wd, self.lrd = lr, su, l2wd, lrd
+        self.acc = torch.zeros_like(self.x)
+        if seed_center if seed_center is not None else center.rank == 0:
+            center.put(self.x)
+        self.engine.load_flat(self.x)
+
+    def step(self) -> None:
+        e = self.engine
+        lr = self.lr / (1 + self.t * self.lrd) if self.lrd != 0 else self.lr
+        do_sync = self.t % self.su == 0
+
+        def body():
+            e.fwd_bwd()
+            # acc += -lr (g + l2wd x); between syncs also move locally
+            ops.downpour_accum(self.x, self.acc, e.gpk, e.wmap, e.wpk, e.wmap, lr=lr, l2wd=self.l2wd,
+                               move_local=not do_sync)
+            if do_sync:
+                self.center.push_add(self.acc, zero_src=True)   # centre += acc ; acc = 0
+                self.center.pull(self.x, e.wpk, e.wmap)          # x = centre (overwrites), refresh operands
+
+        self.graphs.run(("step", do_sync), body)
+        self.t += 1
+
+
+class DeviceRule(_DeviceOptBase):
+    """Single-worker adaptive rules (BiCNN/optim-*-single.lua) fused into one pass, optionally
+    pushing the parameters to the centre afterwards (``async_send_param``)."""
+
+    def __init__(self, engine, theta0, rule: str, hyper: dict, center: Optional[ShardedCenter] = None, *,
+                 l1=0.0, l2=0.0, clip=0.0, use_graphs=False):
+        super().__init__(engine, theta0, False)
+        self.rule, self.hyper, self.center = rule, dict(hyper), center
+        self.l1, self.l2, self.clip = l1, l2, clip
+        z = lambda: torch.zeros_like(self.x)
+        self.s0 = z() if rule != "add" else None
+        self.s1 = z() if rule in ("rmsprop", "adam", "adamax", "adadelta") else None
+        self.s2 = z() if rule == "rmsprop" else None
+        self.engine.load_flat(self.x)
+
+    def step(self) -> None:
+        e = self.engine
+        e.fwd_bwd()
+        self.t += 1
+        h = ops.rule_hyper(self.rule, self.t, **self.hyper)
+        ops.rule_step(self.rule, self.x, e.gpk, h, self.s0, self.s1, self.s2, gmap=e.wmap, wpk=e.wpk,
+                      wmap=e.wmap, l1=self.l1, l2=self.l2, clip=self.clip)
+        if self.center is not None:
+            self.center.put(self.x)

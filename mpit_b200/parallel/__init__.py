@@ -1,0 +1,3 @@
+"""Multi-GPU plumbing: symmetric heap, sharded centre variable, device collectives."""
+from .symm import SymmetricHeap, SymmBuffer, LocalPeerHeap
+from .center import ShardedCenter, partition

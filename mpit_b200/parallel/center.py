@@ -1,0 +1,90 @@
+"""Centre variable sharded over the GPUs of one box (device path of the parameter server).
+
+Reference: a set of CPU server processes each owning a contiguous slice of the flat parameter
+vector (asyncsgd/pserver.lua:38-62, partition in asyncsgd/pclient.lua:116-129).  Here every GPU is
+a worker *and* the owner of shard ``rank``; clients reach every shard with one-sided NVLink
+accesses issued by the fused kernels in ``csrc/kernels/comm.cu``.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Tuple
+
+import torch
+
+from .._native import kernels, check, ptr, cur_stream
+from .symm import SymmBuffer
+
+
+def partition(n: int, nshards: int) -> List[Tuple[int, int]]:
+    """Reference partition, 0-based ``(offset, size)`` per shard (pclient.lua:118-128: equal
+    ``floor(n/S)`` pieces, the last one extended to ``n``; the wire format there is 1-based)."""
+    base = n // nshards
+    out = []
+    for s in range(nshards):
+        off = s * base
+        size = base if s < nshards - 1 else n - off
+        out.append((off, size))
+    return out
+
+
+def shard_capacity(n: int, nshards: int) -> int:
+    """Floats to allocate per shard: the largest shard, padded to 4 floats (16-byte quads)."""
+    cap = max(sz for _, sz in partition(n, nshards))
+    return (cap + 3) // 4 * 4 + 4
+
+
+class ShardedCenter:
+    """Handle on the sharded centre: thin launcher of the exchange kernels."""
+
+    def __init__(self, buf: SymmBuffer, n: int):
+        self.buf = buf
+        self.n = n
+        self.nranks = buf.nranks
+        self.rank = buf.rank
+        self.parts = partition(n, self.nranks)
+        self._ptrs = buf.ptr_array()
+        self.k = kernels()
+
+    @classmethod
+    def create(cls, heap, n: int) -> "ShardedCenter":
+        return cls(heap.alloc(shard_capacity(n, heap.nranks)), n)
+
+    @property
+    def local_shard(self) -> torch.Tensor:
+        off, size = self.parts[self.rank]
+        return self.buf.local[:size]
+
+    # -- one-sided operations ------------------------------------------------------------------
+    def put(self, src: torch.Tensor) -> None:
+        """centre := src (seeding by the first worker, pclient.lua:131-133)."""
+        check(self.k.mpit_param_put(self._ptrs, self.nranks, self.rank, ptr(src), self.n, cur_stream()),
+              "mpit_param_put")
+
+    def pull(self, dst: torch.Tensor, wpk=None, wmap=None) -> None:
+        """dst := centre (pclient.lua:74-84), optionally refreshing the packed operand copy."""
+        check(self.k.mpit_param_pull(self._ptrs, self.nranks, self.rank, ptr(dst), self.n, ptr(wpk), ptr(wmap),
+                                     cur_stream()), "mpit_param_pull")
+
+    def push_add(self, src: torch.Tensor, params: Optional[torch.Tensor] = None, *, scale=1.0, l1=0.0, l2=0.0,
+                 clip=0.0, zero_src=False) -> None:
+        """centre += scale * clip(reg(src)) (pserver.lua:91)."""
+        check(self.k.mpit_push_add(self._ptrs, self.nranks, self.rank, ptr(src), ptr(params), self.n, scale, l1,
+                                   l2, clip, int(zero_src), cur_stream()), "mpit_push_add")
+
+    def elastic(self, x: torch.Tensor, d: torch.Tensor, alpha: float) -> None:
+        """d = alpha (x - centre); centre += d (optim-eamsgd.lua:58-65)."""
+        check(self.k.mpit_elastic_exchange(self._ptrs, self.nranks, self.rank, ptr(x), ptr(d), self.n, alpha,
+                                           cur_stream()), "mpit_elastic_exchange")
+
+    def eamsgd_step(self, x, v, g, gmap, d, wpk, wmap, *, alpha, clr, l2wd, mom_next, do_apply, use_mom,
+                    do_lookahead, do_sync, has_d_in) -> None:
+        check(self.k.mpit_eamsgd_fused_step(self._ptrs, self.nranks, self.rank, ptr(x), ptr(v), ptr(g), ptr(gmap),
+                                            ptr(d), ptr(wpk), ptr(wmap), self.n, alpha, clr, l2wd, mom_next,
+                                            int(do_apply), int(use_mom), int(do_lookahead), int(do_sync),
+                                            int(has_d_in), cur_stream()), "mpit_eamsgd_fused_step")
+
+    def gather_full(self) -> torch.Tensor:
+        """Materialise the whole centre on this rank (tester role, BiCNN/bicnn.lua:580-596)."""
+        out = torch.empty(self.n, dtype=torch.float32, device=self.buf.local.device)
+        self.pull(out)
+        return out

@@ -1,0 +1,153 @@
+"""CIFAR-10 training/testing loop on B200s (reference: asyncsgd/goot.lua).
+
+``CifarTrainer`` is the public entry point a user (and ``bench.py``) drives: it owns the kernel
+engine, the device optimizer and -- for the distributed optimizers -- this rank's handle on the
+NVLink-sharded centre variable.  ``train_step`` takes one mini-batch in pinned host memory, exactly
+what a data loader hands over, and returns the (one step delayed) loss.
+
+Differences from goot.lua that are deliberate: the mini-batch is one batched kernel schedule instead
+of 128 sequential single-sample passes (goot.lua:198-210); random crops are applied by the first
+convolution's TMA box coordinates instead of ``image.crop`` on the CPU (goot.lua:177-178); the
+confusion matrix is accumulated on the device (goot.lua:209).
+"""
+from __future__ import annotations
+
+import os
+import time
+from dataclasses import dataclass, field
+from typing import Optional
+
+import torch
+
+from ..models.cifar_cnn import (CifarEngine, TorchCifarCNN, flat_from_torch, random_crop_offsets,
+                                center_crop_offsets, NUM_CLASSES, IMG)
+from ..optim.device import DeviceMSGD, DeviceEAMSGD, DeviceDownpour, DeviceRule
+from ..parallel.center import ShardedCenter
+from ..parallel.symm import SymmetricHeap
+
+
+@dataclass
+class CifarOpts:
+    """Mirror of the ``opt`` table of goot.lua:6-21 plus launcher settings (mlaunch.lua:48-67)."""
+    name: str = "eamsgd"          # sgd | downpour | eamsgd | easgd | adam/adamax/adagrad/adadelta/rmsprop-single
+    lr: float = 1e-2
+    mom: float = 0.99
+    mb: int = 128
+    mva: float = 0.0              # moving rate alpha; default 0.9/p as in mlaunch.lua:57-58
+    su: int = 1                   # communication period tau
+    l2wd: float = 0.0
+    lrd: float = 0.0
+    lrp: float = 0.0
+    maxepoch: int = 1
+    saveep: int = 10
+    seed: int = 1
+    impl: str = "umma"            # kernel path: umma (tcgen05) | ref (fp32 CUDA cores)
+    use_graphs: bool = True
+    save: str = "results"
+    rule_hyper: dict = field(default_factory=dict)
+
+
+def synthetic_cifar(n: int, seed: int = 0, pinned: bool = True):
+    """Synthetic data of the CIFAR-10 shape: uint8 [n,3,32,32] images, labels in [0,10)."""
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randint(0, 256, (n, 3, IMG, IMG), dtype=torch.uint8, generator=g)
+    y = torch.randint(0, NUM_CLASSES, (n,), dtype=torch.int32, generator=g)
+    if pinned and torch.cuda.is_available():
+        x, y = x.pin_memory(), y.pin_memory()
+    return x, y
+
+
+class CifarTrainer:
+    def __init__(self, opts: CifarOpts, device: Optional[torch.device] = None, heap: Optional[SymmetricHeap] = None,
+                 theta0: Optional[torch.Tensor] = None):
+        self.opts = opts
+        self.dev = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        torch.cuda.set_device(self.dev)
+        self.engine = CifarEngine(opts.mb, device=self.dev, impl=opts.impl, seed=opts.seed)
+        if theta0 is None:
+            g = torch.Generator().manual_seed(opts.seed)
+            m = TorchCifarCNN()
+            from ..models.cifar_cnn import torch7_reset
+            torch7_reset(m, g)
+            theta0 = flat_from_torch(m)
+        self.heap = heap
+        self.center: Optional[ShardedCenter] = None
+        name = opts.name
+        n = theta0.numel()
+        if name in ("eamsgd", "easgd", "downpour"):
+            if heap is None:
+                self.heap = heap = SymmetricHeap(self.dev)
+            self.center = ShardedCenter.create(heap, n)
+        p = heap.nranks if heap is not None else 1
+        if name in ("eamsgd", "easgd"):
+            mva = opts.mva if opts.mva > 0 else 0.9 / p
+            self.opt = DeviceEAMSGD(self.engine, theta0, self.center, lr=opts.lr, mva=mva, su=opts.su,
+                                    mom=0.0 if name == "easgd" else opts.mom, l2wd=opts.l2wd, lrd=opts.lrd,
+                                    lrp=opts.lrp, use_graphs=opts.use_graphs)
+        elif name == "downpour":
+            self.opt = DeviceDownpour(self.engine, theta0, self.center, lr=opts.lr, su=opts.su, l2wd=opts.l2wd,
+                                      lrd=opts.lrd, use_graphs=opts.use_graphs)
+        elif name in ("sgd", "msgd"):
+            self.opt = DeviceMSGD(self.engine, theta0, lr=opts.lr, mom=opts.mom, l2wd=opts.l2wd, lrd=opts.lrd,
+                                  lrp=opts.lrp, use_graphs=opts.use_graphs)
+        elif name.endswith("single"):
+            self.opt = DeviceRule(self.engine, theta0, name[:-6], opts.rule_hyper, self.center)
+        else:
+            raise ValueError(f"unknown optimizer {name}")
+        if self.heap is not None and self.heap.nranks > 1:
+            import torch.distributed as dist
+            torch.cuda.synchronize()
+            dist.barrier()   # centre seeded before anyone syncs against it
+        # pinned landing zone for the per-step loss read-back
+        self._loss_host = torch.zeros(2, dtype=torch.float32).pin_memory()
+        self._loss_dev = torch.zeros(2, dtype=torch.float32, device=self.dev)
+        self._loss_evt = torch.cuda.Event()
+        self._have_loss = False
+        self.tm = {"feval": 0.0, "sync": 0.0}
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+
+    # -- one training step ---------------------------------------------------------------------
+    def train_step(self, images_u8: torch.Tensor, labels: torch.Tensor, crop: torch.Tensor) -> Optional[float]:
+        """Stage a mini-batch (pinned host tensors), run one optimizer step, and return the mean loss
+        of the *previous* step (its device->host copy has landed by now, so nothing stalls)."""
+        prev = None
+        if self._have_loss:
+            self._loss_evt.synchronize()
+            prev = float(self._loss_host[0]) / self.opts.mb
+        self.engine.set_batch(images_u8, labels, crop)
+        self.h2d_bytes = images_u8.numel() + labels.numel() * 4 + crop.numel() * 4
+        self.opt.step()
+        self._loss_dev[:1].copy_(self.engine.loss_sum)     # snapshot: the next step zeroes loss_sum
+        self._loss_host.copy_(self._loss_dev, non_blocking=True)
+        self._loss_evt.record()
+        self.d2h_bytes = self._loss_host.numel() * 4
+        self._have_loss = True
+        return prev
+
+    def device_step(self) -> None:
+        """One optimizer step on whatever batch is already staged on the device (kernel-only timing)."""
+        self.opt.step()
+
+    def last_loss(self) -> float:
+        self._loss_evt.synchronize()
+        return float(self._loss_host[0]) / self.opts.mb
+
+    def params(self) -> torch.Tensor:
+        return self.opt.params()
+
+    # -- evaluation (goot.lua:265-322) ---------------------------------------------------------
+    @torch.no_grad()
+    def test(self, images_u8: torch.Tensor, labels: torch.Tensor) -> dict:
+        eng, B = self.engine, self.opts.mb
+        eng.load_flat(self.params())
+        eng.confusion.zero_()
+        total, n = 0.0, (images_u8.shape[0] // B) * B
+        crop = center_crop_offsets(B)
+        for i in range(0, n, B):
+            eng.set_batch(images_u8[i:i + B], labels[i:i + B], crop)
+            eng.evaluate()
+            total += float(eng.loss_sum.item())
+        conf = eng.confusion.cpu()
+        return {"loss": total / max(n, 1), "acc": float(conf.diag().sum()) / max(int(conf.sum()), 1),
+                "confusion": conf, "n": n}

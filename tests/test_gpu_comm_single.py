@@ -1,0 +1,123 @@
+"""GPU numerics of the exchange kernels with every 'rank' aliased onto one device (shard arithmetic,
+put/pull/push/elastic and the fused EAMSGD boundary kernel vs the Lua restatement)."""
+import pytest
+import torch
+
+from mpit_b200.optim import reference as R
+from mpit_b200.parallel.center import ShardedCenter, partition, shard_capacity
+from mpit_b200.parallel.symm import LocalPeerHeap
+
+pytestmark = pytest.mark.gpu
+
+
+def _centers(n, S):
+    heap = LocalPeerHeap(S, devices=[0] * S)
+    bufs = heap.alloc(shard_capacity(n, S))
+    return [ShardedCenter(b, n) for b in bufs]
+
+
+def _center_as_flat(cs, n):
+    parts = partition(n, len(cs))
+    return torch.cat([cs[s].buf.local[:sz] for s, (off, sz) in enumerate(parts)])
+
+
+@pytest.mark.parametrize("n,S", [(351946, 8), (1003, 3), (5, 8), (4096, 1), (43993 * 8 + 5, 8)])
+def test_put_pull_push_roundtrip(n, S):
+    cs = _centers(n, S)
+    x = torch.randn(n, device="cuda")
+    cs[0].put(x)
+    torch.cuda.synchronize()
+    assert torch.equal(_center_as_flat(cs, n), x)
+    y = torch.empty_like(x)
+    cs[S - 1].pull(y)
+    assert torch.equal(y, x)
+    g = torch.randn(n, device="cuda")
+    g0 = g.clone()
+    cs[min(1, S - 1)].push_add(g, zero_src=True)
+    torch.cuda.synchronize()
+    assert torch.equal(_center_as_flat(cs, n), x + g0)
+    assert float(g.abs().sum()) == 0.0
+
+
+def test_push_with_clip_and_scale():
+    n, S = 1003, 3
+    cs = _centers(n, S)
+    p = torch.randn(n, device="cuda")
+    g = torch.randn(n, device="cuda") * 5
+    cs[0].push_add(g, p, scale=0.5, l2=0.1, clip=1.0)
+    ref = (g + p * 0.1).clamp(-1, 1) * 0.5
+    assert torch.allclose(_center_as_flat(cs, n), ref, atol=1e-6)
+
+
+def test_elastic_exchange_conserves():
+    n, S = 1003, 4
+    cs = _centers(n, S)
+    c0 = torch.randn(n, device="cuda")
+    cs[0].put(c0)
+    x = torch.randn(n, device="cuda")
+    d = torch.empty_like(x)
+    cs[2].elastic(x, d, 0.25)
+    torch.cuda.synchronize()
+    ref_d = (x - c0) * 0.25
+    assert torch.equal(d, ref_d)
+    assert torch.equal(_center_as_flat(cs, n), c0 + ref_d)
+
+
+class _LocalPS:
+    """In-process stand-in for pclient/pserver: one worker, plain-add server."""
+
+    def __init__(self, center):
+        self.center = center
+        self.p = self.g = None
+
+    def reset(self, p, g):
+        self.p, self.g = p, g
+
+    def async_recv_param(self):
+        self.p.copy_(self.center)
+
+    def async_send_grad(self):
+        self.center.add_(self.g)
+
+    def ping(self):
+        pass
+
+    def wait(self):
+        pass
+
+
+@pytest.mark.parametrize("su,mom", [(1, 0.9), (3, 0.99), (2, 0.0)])
+def test_fused_eamsgd_step_matches_reference_bitwise(su, mom):
+    n, S, K = 10007, 8, 9
+    gen = torch.Generator().manual_seed(5)
+    grads = [torch.randn(n, generator=gen) * 0.1 for _ in range(K)]
+    w0 = torch.randn(n, generator=gen)
+    # --- oracle: asyncsgd/optim-eamsgd.lua restated, single worker
+    w = w0.clone()
+    ps = _LocalPS(w0.clone())
+    cfg = {"lr": 0.05, "mom": mom, "mva": 0.3, "su": su, "pclient": ps}
+    it = iter(grads)
+    for _ in range(K):
+        R.eamsgd(lambda w_: (0.0, next(it).clone()), w, cfg)
+    # --- device: fused boundary kernel
+    cs = _centers(n, S)
+    c = cs[3]
+    x = w0.cuda()
+    c.put(x)
+    v = torch.zeros_like(x) if mom > 0 else None
+    d = torch.zeros_like(x)
+    g_prev = None
+    prev_sync = False
+    for t in range(K + 1):
+        do_apply = t > 0
+        last = t == K
+        do_sync = (not last) and t % su == 0
+        c.eamsgd_step(x, v, g_prev, None, d, None, None, alpha=0.3, clr=0.05, l2wd=0.0, mom_next=mom,
+                      do_apply=do_apply, use_mom=mom > 0, do_lookahead=not last, do_sync=do_sync,
+                      has_d_in=do_apply and prev_sync)
+        if not last:
+            g_prev = grads[t].cuda()
+        prev_sync = do_sync
+    torch.cuda.synchronize()
+    assert torch.equal(x.cpu(), w)
+    assert torch.equal(_center_as_flat(cs, n).cpu(), ps.center)
