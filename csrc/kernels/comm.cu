@@ -98,6 +98,8 @@ struct ExchArgs {
   float* src;          // push source / pull destination when not x
   float* wpk;
   const int* wmap;
+  int nmaps;
+  long long n;
   float alpha, clr, l2wd, mom_next, scale, l1, l2, clip;
   int do_apply, use_mom, do_lookahead, do_sync, has_d_in, zero_src;
 };
@@ -117,7 +119,7 @@ __global__ void __launch_bounds__(256) exchange_kernel(ExchArgs a) {
       store4(a.src, i0, cnt, c);
       if (a.wpk) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) if (k < cnt) a.wpk[a.wmap ? a.wmap[i0 + k] : i0 + k] = c[k];
+        for (int k = 0; k < 4; ++k) if (k < cnt) pack_store(a.wpk, a.wmap, a.nmaps, a.n, i0 + k, c[k]);
       }
     } else if (MODE == EX_PUT) {
       float r[4];
@@ -178,7 +180,7 @@ __global__ void __launch_bounds__(256) exchange_kernel(ExchArgs a) {
         if (a.use_mom) store4(a.v, i0, cnt, v);
         if (a.wpk) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) if (k < cnt) a.wpk[a.wmap ? a.wmap[i0 + k] : i0 + k] = x[k];
+          for (int k = 0; k < 4; ++k) if (k < cnt) pack_store(a.wpk, a.wmap, a.nmaps, a.n, i0 + k, x[k]);
         }
       }
     }
@@ -396,13 +398,13 @@ int mpit_signal_words(void) { return MPIT_SIGNAL_WORDS; }
 int mpit_max_ranks(void) { return MPIT_MAX_RANKS; }
 
 int mpit_param_pull(const unsigned long long* shard_ptrs, int nranks, int rank, float* dst, long long n,
-                    float* wpk, const int* wmap, void* stream) {
+                    float* wpk, const int* wmap, int nmaps, void* stream) {
   if (n <= 0) return 0;
   if (nranks < 1 || nranks > MPIT_MAX_RANKS) return MPIT_E_ARG;
   ExchArgs a{};
   a.tab = make_table(shard_ptrs, 0, nranks, rank);
   a.walk = QuadWalk::make(n, nranks);
-  a.src = dst; a.wpk = wpk; a.wmap = wmap;
+  a.src = dst; a.wpk = wpk; a.wmap = wmap; a.nmaps = nmaps; a.n = n;
   exchange_kernel<EX_PULL><<<exch_grid(a.walk), 256, 0, (cudaStream_t)stream>>>(a);
   MPIT_LAUNCH_CHECK();
   return 0;
@@ -451,14 +453,14 @@ int mpit_elastic_exchange(const unsigned long long* shard_ptrs, int nranks, int 
 
 int mpit_eamsgd_fused_step(const unsigned long long* shard_ptrs, int nranks, int rank, float* x, float* v,
                            const float* g, const int* gmap, float* d, float* wpk, const int* wmap,
-                           long long n, float alpha, float clr, float l2wd, float mom_next, int do_apply,
+                           int nmaps, long long n, float alpha, float clr, float l2wd, float mom_next, int do_apply,
                            int use_mom, int do_lookahead, int do_sync, int has_d_in, void* stream) {
   if (n <= 0) return 0;
   if (nranks < 1 || nranks > MPIT_MAX_RANKS) return MPIT_E_ARG;
   ExchArgs a{};
   a.tab = make_table(shard_ptrs, 0, nranks, rank);
   a.walk = QuadWalk::make(n, nranks);
-  a.x = x; a.v = v; a.g = g; a.gmap = gmap; a.d = d; a.wpk = wpk; a.wmap = wmap;
+  a.x = x; a.v = v; a.g = g; a.gmap = gmap; a.d = d; a.wpk = wpk; a.wmap = wmap; a.nmaps = nmaps; a.n = n;
   a.alpha = alpha; a.clr = clr; a.l2wd = l2wd; a.mom_next = mom_next;
   a.do_apply = do_apply; a.use_mom = use_mom; a.do_lookahead = do_lookahead; a.do_sync = do_sync;
   a.has_d_in = has_d_in;

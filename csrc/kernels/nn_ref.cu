@@ -182,8 +182,11 @@ colsum_kernel(const float* __restrict__ dz, float* __restrict__ db, long long ro
   }
 }
 
-// uint8 CHW [B,3,SH,SW] -> fp32 NHWC4 [B,SH,SW,4], scaled by 1/255 (asyncsgd/goot.lua:87-88),
-// channel 3 = 0.
+// uint8 CHW [B,3,SH,SW] -> fp32 "pair-expanded" NHWC8 [B,SH,SW,8], scaled by 1/255
+// (asyncsgd/goot.lua:87-88): pixel x holds (r,g,b,0) of pixel x followed by (r,g,b,0) of pixel x+1.
+// 32 consecutive floats starting at pixel x are then pixels x,x+1 | x+1,x+2 | x+2,x+3 | x+3,x+4, i.e.
+// one 128-byte TMA row carries all five kernel columns of the first 5x5 convolution, and every row
+// starts on a 32-byte boundary (needed by the 32-byte-atom swizzle of the weight-gradient kernel).
 __global__ void __launch_bounds__(256)
 prep_u8_kernel(const unsigned char* __restrict__ src, float* __restrict__ dst, int B, int SH, int SW) {
   long long total = (long long)B * SH * SW;
@@ -191,13 +194,24 @@ prep_u8_kernel(const unsigned char* __restrict__ src, float* __restrict__ dst, i
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
     long long n = i / (SH * SW);
     int p = (int)(i % (SH * SW));
+    int x = p % SW;
     const unsigned char* s = src + (size_t)n * 3 * SH * SW + p;
-    float4 v;
-    v.x = (float)s[0] / 255.f;
-    v.y = (float)s[(size_t)SH * SW] / 255.f;
-    v.z = (float)s[(size_t)2 * SH * SW] / 255.f;
-    v.w = 0.f;
-    st4(dst + 4 * i, v);
+    size_t plane = (size_t)SH * SW;
+    float4 a, b;
+    a.x = (float)s[0] / 255.f;
+    a.y = (float)s[plane] / 255.f;
+    a.z = (float)s[2 * plane] / 255.f;
+    a.w = 0.f;
+    if (x + 1 < SW) {
+      b.x = (float)s[1] / 255.f;
+      b.y = (float)s[plane + 1] / 255.f;
+      b.z = (float)s[2 * plane + 1] / 255.f;
+    } else {
+      b.x = b.y = b.z = 0.f;
+    }
+    b.w = 0.f;
+    st4(dst + 8 * i, a);
+    st4(dst + 8 * i + 4, b);
   }
 }
 

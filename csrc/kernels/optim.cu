@@ -16,7 +16,8 @@ struct LocalStepArgs {
   const int* gmap;     // flat index -> offset in g (null: identity)
   const float* d;      // elastic difference to subtract after the step (null: none)
   float* wpk;          // packed weights to refresh (null: none)
-  const int* wmap;     // flat index -> offset in wpk
+  const int* wmap;     // flat index -> offset in wpk; nmaps tables of n entries, -1 = skip
+  int nmaps;
   long long n;
   float clr, l2wd, mom_next;
   int do_apply, use_mom, do_lookahead;
@@ -35,7 +36,7 @@ __global__ void __launch_bounds__(256) local_step_kernel(LocalStepArgs a) {
     if (a.do_lookahead && a.use_mom) nesterov_lookahead_elem(x, v, a.mom_next);
     a.x[i] = x;
     if (a.use_mom) a.v[i] = v;
-    if (a.wpk) a.wpk[a.wmap ? a.wmap[i] : i] = x;
+    if (a.wpk) pack_store(a.wpk, a.wmap, a.nmaps, a.n, i, x);
   }
 }
 
@@ -92,6 +93,7 @@ struct RuleArgs {
   float* s2;
   float* wpk;
   const int* wmap;
+  int nmaps;
   long long n;
   RuleHyper h;
   float l1, l2, clip;  // optional gradient prologue (bicnn.lua:398-409)
@@ -115,7 +117,7 @@ __global__ void __launch_bounds__(256) rule_kernel(RuleArgs a) {
     if (RULE != RULE_ADD) a.s0[i] = s0;
     if (RULE == RULE_RMSPROP || RULE == RULE_ADAM || RULE == RULE_ADAMAX || RULE == RULE_ADADELTA) a.s1[i] = s1;
     if (RULE == RULE_RMSPROP) a.s2[i] = s2;
-    if (a.wpk) a.wpk[a.wmap ? a.wmap[i] : i] = p;
+    if (a.wpk) pack_store(a.wpk, a.wmap, a.nmaps, a.n, i, p);
   }
 }
 
@@ -130,6 +132,7 @@ struct DownpourArgs {
   const int* gmap;
   float* wpk;
   const int* wmap;
+  int nmaps;
   long long n;
   float neg_lr, l2wd;
   int move_local;
@@ -146,7 +149,7 @@ __global__ void __launch_bounds__(256) downpour_accum_kernel(DownpourArgs a) {
     if (a.move_local) {
       x = add_rn(x, g);
       a.x[i] = x;
-      if (a.wpk) a.wpk[a.wmap ? a.wmap[i] : i] = x;
+      if (a.wpk) pack_store(a.wpk, a.wmap, a.nmaps, a.n, i, x);
     }
   }
 }
@@ -174,10 +177,10 @@ using namespace mpit;
 extern "C" {
 
 int mpit_local_step(float* x, float* v, const float* g, const int* gmap, const float* d, float* wpk,
-                    const int* wmap, long long n, float clr, float l2wd, float mom_next, int do_apply,
+                    const int* wmap, int nmaps, long long n, float clr, float l2wd, float mom_next, int do_apply,
                     int use_mom, int do_lookahead, void* stream) {
   if (n <= 0) return 0;
-  LocalStepArgs a{x, v, g, gmap, d, wpk, wmap, n, clr, l2wd, mom_next, do_apply, use_mom, do_lookahead};
+  LocalStepArgs a{x, v, g, gmap, d, wpk, wmap, nmaps, n, clr, l2wd, mom_next, do_apply, use_mom, do_lookahead};
   cudaStream_t st = (cudaStream_t)stream;
   bool vec = !gmap && !wmap && aligned16(x) && (!v || aligned16(v)) && (!g || aligned16(g)) &&
              (!d || aligned16(d)) && (!wpk || aligned16(wpk));
@@ -193,11 +196,11 @@ int mpit_local_step(float* x, float* v, const float* g, const int* gmap, const f
 }
 
 int mpit_rule_step(int rule, float* p, const float* g, const int* gmap, float* s0, float* s1, float* s2,
-                   float* wpk, const int* wmap, long long n, const float* hyper6, float l1, float l2,
-                   float clip, float gscale, void* stream) {
+                   float* wpk, const int* wmap, int nmaps, long long n, const float* hyper6, float l1,
+                   float l2, float clip, float gscale, void* stream) {
   if (n <= 0) return 0;
   RuleArgs a{};
-  a.p = p; a.g = g; a.gmap = gmap; a.s0 = s0; a.s1 = s1; a.s2 = s2; a.wpk = wpk; a.wmap = wmap; a.n = n;
+  a.p = p; a.g = g; a.gmap = gmap; a.s0 = s0; a.s1 = s1; a.s2 = s2; a.wpk = wpk; a.wmap = wmap; a.nmaps = nmaps; a.n = n;
   a.h = RuleHyper{hyper6[0], hyper6[1], hyper6[2], hyper6[3], hyper6[4], hyper6[5]};
   a.l1 = l1; a.l2 = l2; a.clip = clip; a.gscale = gscale;
   cudaStream_t st = (cudaStream_t)stream;
@@ -216,9 +219,9 @@ int mpit_rule_step(int rule, float* p, const float* g, const int* gmap, float* s
 }
 
 int mpit_downpour_accum(float* x, float* acc, const float* g, const int* gmap, float* wpk, const int* wmap,
-                        long long n, float neg_lr, float l2wd, int move_local, void* stream) {
+                        int nmaps, long long n, float neg_lr, float l2wd, int move_local, void* stream) {
   if (n <= 0) return 0;
-  DownpourArgs a{x, acc, g, gmap, wpk, wmap, n, neg_lr, l2wd, move_local};
+  DownpourArgs a{x, acc, g, gmap, wpk, wmap, nmaps, n, neg_lr, l2wd, move_local};
   downpour_accum_kernel<<<ew_grid(n, 256, 4), 256, 0, (cudaStream_t)stream>>>(a);
   MPIT_LAUNCH_CHECK();
   return 0;

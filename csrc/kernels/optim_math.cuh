@@ -65,6 +65,17 @@ __device__ __forceinline__ void rule_apply(float& p, float g, float& s0, float& 
   }
 }
 
+// Refresh the tensor-core operand copies of one parameter: `nmaps` index tables of n entries each
+// (forward layout, data-gradient layout, ...); -1 means "this parameter has no slot in that copy".
+__device__ __forceinline__ void pack_store(float* wpk, const int* wmap, int nmaps, long long n, long long i,
+                                           float x) {
+  if (!wmap) { wpk[i] = x; return; }
+  for (int m = 0; m < nmaps; ++m) {
+    int o = wmap[(long long)m * n + i];
+    if (o >= 0) wpk[o] = x;
+  }
+}
+
 // Gradient post-processing of BiCNN/bicnn.lua:398-409 (L1, L2, clamp), applied while
 // the gradient is in registers on its way into a push or a local rule.
 __device__ __forceinline__ float grad_reg_clip(float g, float p, float l1, float l2, float clip) {

@@ -1,0 +1,363 @@
+// Implicit-GEMM convolution / linear layers on the 5th-gen tensor cores (sm_100a):
+//
+//   D[128 x BLOCK_N] (TMEM, fp32) = sum_kb  A_kb[128 x 32] (smem, tf32)  *  B_kb[BLOCK_N x 32]^T
+//
+// * A rows are output pixels (n, oh, ow) of an NHWC activation tensor.  One k-block is one
+//   (kernel-row, kernel-col, 32-channel) slice, fetched by TMA as a 4-D box whose (w, h) coordinates
+//   are shifted by the kernel offset -- im2col never exists in memory.  Forward uses +offsets,
+//   the data-gradient uses -offsets on the output gradient with TMA zero fill standing in for the
+//   "full" padding.  The random/centre crop of the first layer is just another coordinate offset
+//   (asyncsgd/goot.lua:177-178,283-285).  A Linear layer is the 1x1 case.
+// * B rows are output channels of the packed weight matrix, fetched as a 2-D TMA box.
+// * Both operands land in 128-byte-swizzled shared memory and are consumed by tcgen05.mma
+//   (kind::tf32, M=128, N=BLOCK_N, K=8 per instruction) issued by one elected thread.
+// * Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (+TMEM allocator), warps 2..5 =
+//   epilogue (tcgen05.ld -> bias/ReLU/2x2-maxpool/dropout or gradient masking -> 128-byte stores).
+//
+// Layers: asyncsgd/models/7-layers-cnn.lua:8-24 (SpatialConvolution+ReLU+SpatialMaxPooling,
+// Linear+ReLU+Dropout, Linear).
+#include "mpit_b200.h"
+#include "common.cuh"
+#include "umma.cuh"
+#include <string.h>
+
+namespace mpit {
+using namespace umma;
+
+enum EpiMode : int { EPI_STORE = 0, EPI_POOL = 1, EPI_MASK = 2, EPI_EXPAND = 3 };
+
+struct IgemmParams {
+  int nsub, tw, th, tn;      // sub-box: tw*th*tn rows, nsub sub-boxes per 128-row tile
+  int tiles_w, tiles_h;      // sub-tiles per image
+  int kw_it, cb;             // k-block -> (kh, kw, channel block)
+  int num_kb;
+  int sgn;                   // +1 forward, -1 data gradient
+  int B, OH, OW;             // extent of the GEMM M side: rows are (n, oh, ow)
+  int N;                     // total output columns
+  int mode, relu, dropout;
+  float scale;
+  const float* bias;
+  float* out;
+  unsigned char* idx;
+  const float* aux;
+  const unsigned char* aux_idx;
+  const int* crop;
+  const unsigned long long* rng;
+  int* err;                  // set to 1 when a bounded pipeline wait expires
+};
+
+constexpr int kStages = 4;
+constexpr int kABytes = 128 * 128;  // 128 rows x 32 tf32
+
+template <int BLOCK_N>
+struct SmemLayout {
+  static constexpr int kBBytes = BLOCK_N * 128;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kBarOff = kStages * kStageBytes;
+  static constexpr int kTotal = kBarOff + 256 + 1024;  // barriers + alignment slack
+};
+
+__device__ __forceinline__ void subtile_origin(const IgemmParams& p, int s, int& n0, int& oh0, int& ow0) {
+  int per_img = p.tiles_w * p.tiles_h;
+  int grp = s / per_img, r = s - grp * per_img;
+  int th_i = r / p.tiles_w, tw_i = r - th_i * p.tiles_w;
+  n0 = grp * p.tn;
+  oh0 = th_i * p.th;
+  ow0 = tw_i * p.tw;
+}
+
+template <int BLOCK_N>
+__global__ void __launch_bounds__(192)
+umma_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                  const IgemmParams p) {
+  using L = SmemLayout<BLOCK_N>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tmem_full = empty_bar + kStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tile = blockIdx.x;
+  const int n_tile0 = blockIdx.y * BLOCK_N;
+  const int rows_per_sub = 128 / p.nsub;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmap_a);
+    prefetch_tmap(&tmap_b);
+    for (int i = 0; i < kStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    mbar_init(tmem_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, BLOCK_N);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (elect_one()) {
+      int n0[2], oh0[2], ow0[2];
+      for (int j = 0; j < p.nsub; ++j) {
+        subtile_origin(p, tile * p.nsub + j, n0[j], oh0[j], ow0[j]);
+        if (p.crop && n0[j] < p.B) { oh0[j] += p.crop[2 * n0[j]]; ow0[j] += p.crop[2 * n0[j] + 1]; }
+      }
+      int stage = 0, phase = 0;
+      const int per_kh = p.kw_it * p.cb;
+      for (int kb = 0; kb < p.num_kb; ++kb) {
+        if (!mbar_wait(&empty_bar[stage], phase ^ 1)) { if (p.err) *p.err = 1; break; }
+        uint8_t* a_dst = smem + stage * L::kStageBytes;
+        uint8_t* b_dst = a_dst + kABytes;
+        mbar_expect_tx(&full_bar[stage], L::kStageBytes);
+        int kh = kb / per_kh, r = kb - kh * per_kh;
+        int kw = r / p.cb, cblk = r - kw * p.cb;
+        for (int j = 0; j < p.nsub; ++j)
+          tma_load_4d(a_dst + j * rows_per_sub * 128, &tmap_a, &full_bar[stage], cblk * 32,
+                      ow0[j] + p.sgn * kw, oh0[j] + p.sgn * kh, n0[j]);
+        tma_load_2d(b_dst, &tmap_b, &full_bar[stage], kb * 32, n_tile0);
+        if (++stage == kStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (elect_one()) {
+      constexpr uint32_t idesc = make_idesc_tf32(128, BLOCK_N, 0, 0);
+      int stage = 0, phase = 0;
+      for (int kb = 0; kb < p.num_kb; ++kb) {
+        if (!mbar_wait(&full_bar[stage], phase)) { if (p.err) *p.err = 2; break; }
+        tc_fence_after();
+        uint32_t a_addr = smem_u32(smem + stage * L::kStageBytes);
+        uint32_t b_addr = a_addr + kABytes;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          uint64_t ad = make_smem_desc(a_addr + k * 32, 16, 1024);
+          uint64_t bd = make_smem_desc(b_addr + k * 32, 16, 1024);
+          mma_tf32(tmem_base, ad, bd, idesc, (kb | k) ? 1u : 0u);
+        }
+        mma_commit(&empty_bar[stage]);   // frees the smem slot once these MMAs have read it
+        if (++stage == kStages) { stage = 0; phase ^= 1; }
+      }
+      mma_commit(tmem_full);             // accumulator complete
+    }
+  } else {
+    // ===== epilogue: warps 2..5, TMEM lane quadrant = warp % 4 =====
+    const int quad = warp & 3;
+    const int row = quad * 32 + lane;
+    const int j = row / rows_per_sub, rr = row - j * rows_per_sub;
+    int n0, oh0, ow0;
+    subtile_origin(p, tile * p.nsub + j, n0, oh0, ow0);
+    const int w_ = rr % p.tw, h_ = (rr / p.tw) % p.th, nn = rr / (p.tw * p.th);
+    const int n = n0 + nn, oh = oh0 + h_, ow = ow0 + w_;
+    const bool valid = n < p.B && oh < p.OH && ow < p.OW;
+    if (!mbar_wait(tmem_full, 0)) { if (p.err) *p.err = 3; }
+    tc_fence_after();
+    unsigned long long seed = 0, step = 0;
+    if (p.dropout) { seed = p.rng[0]; step = p.rng[1]; }
+#pragma unroll 1
+    for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+      float v[32];
+      tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
+      const int col0 = n_tile0 + c0;
+      if (p.mode == EPI_STORE) {
+        size_t orow = ((size_t)n * p.OH + oh) * p.OW + ow;
+        size_t obase = orow * p.N + col0;
+#pragma unroll
+        for (int c = 0; c < 32; ++c) {
+          float x = v[c] + (p.bias ? p.bias[col0 + c] : 0.f);
+          if (p.relu) x = fmaxf(x, 0.f);
+          v[c] = x;
+        }
+        if (p.dropout) {
+#pragma unroll
+          for (int c4 = 0; c4 < 8; ++c4) {
+            uint4 rnd = Philox::gen(seed, (unsigned long long)((obase + 4 * c4) >> 2), (uint32_t)step);
+            v[4 * c4 + 0] = (rnd.x & 1u) ? v[4 * c4 + 0] * 2.f : 0.f;
+            v[4 * c4 + 1] = (rnd.y & 1u) ? v[4 * c4 + 1] * 2.f : 0.f;
+            v[4 * c4 + 2] = (rnd.z & 1u) ? v[4 * c4 + 2] * 2.f : 0.f;
+            v[4 * c4 + 3] = (rnd.w & 1u) ? v[4 * c4 + 3] * 2.f : 0.f;
+          }
+        }
+        if (valid) {
+#pragma unroll
+          for (int c4 = 0; c4 < 8; ++c4)
+            st4(p.out + obase + 4 * c4, make_float4(v[4 * c4], v[4 * c4 + 1], v[4 * c4 + 2], v[4 * c4 + 3]));
+        }
+      } else if (p.mode == EPI_POOL) {
+        // 2x2 max over (oh^1, ow^1): partners are lane+1, lane+tw, lane+tw+1 of the even/even lane
+        const bool writer = ((h_ | w_) & 1) == 0;
+        const int PH = p.OH >> 1, PW = p.OW >> 1;
+        size_t obase = ((((size_t)n * PH + (oh >> 1)) * PW + (ow >> 1)) * p.N) + col0;
+        unsigned char bi[32];
+#pragma unroll
+        for (int c = 0; c < 32; ++c) {
+          float x = v[c] + (p.bias ? p.bias[col0 + c] : 0.f);
+          float x01 = __shfl_down_sync(0xffffffffu, x, 1);
+          float x10 = __shfl_down_sync(0xffffffffu, x, p.tw);
+          float x11 = __shfl_down_sync(0xffffffffu, x, p.tw + 1);
+          float best = x;
+          int b = 0;
+          if (x01 > best) { best = x01; b = 1; }
+          if (x10 > best) { best = x10; b = 2; }
+          if (x11 > best) { best = x11; b = 3; }
+          if (p.relu) best = fmaxf(best, 0.f);
+          v[c] = best;
+          bi[c] = (unsigned char)b;
+        }
+        if (valid && writer) {
+#pragma unroll
+          for (int c4 = 0; c4 < 8; ++c4)
+            st4(p.out + obase + 4 * c4, make_float4(v[4 * c4], v[4 * c4 + 1], v[4 * c4 + 2], v[4 * c4 + 3]));
+          uint4* ip = reinterpret_cast<uint4*>(p.idx + obase);
+          const uint4* bp = reinterpret_cast<const uint4*>(bi);
+          ip[0] = bp[0];
+          ip[1] = bp[1];
+        }
+      } else if (p.mode == EPI_MASK) {
+        size_t orow = ((size_t)n * p.OH + oh) * p.OW + ow;
+        size_t obase = orow * p.N + col0;
+        if (valid) {
+#pragma unroll
+          for (int c4 = 0; c4 < 8; ++c4) {
+            float4 a = ld4(p.aux + obase + 4 * c4);
+            float4 o;
+            o.x = a.x > 0.f ? v[4 * c4 + 0] * p.scale : 0.f;
+            o.y = a.y > 0.f ? v[4 * c4 + 1] * p.scale : 0.f;
+            o.z = a.z > 0.f ? v[4 * c4 + 2] * p.scale : 0.f;
+            o.w = a.w > 0.f ? v[4 * c4 + 3] * p.scale : 0.f;
+            st4(p.out + obase + 4 * c4, o);
+          }
+        }
+      } else {  // EPI_EXPAND: un-pool + ReLU mask; rows are pooled positions
+        if (valid) {
+          size_t pbase = ((((size_t)n * p.OH + oh) * p.OW + ow) * p.N) + col0;
+          unsigned char bi[32];
+          const uint4* ip = reinterpret_cast<const uint4*>(p.aux_idx + pbase);
+          uint4* bp = reinterpret_cast<uint4*>(bi);
+          bp[0] = ip[0];
+          bp[1] = ip[1];
+          float a[32];
+#pragma unroll
+          for (int c4 = 0; c4 < 8; ++c4) {
+            float4 t = ld4(p.aux + pbase + 4 * c4);
+            a[4 * c4] = t.x; a[4 * c4 + 1] = t.y; a[4 * c4 + 2] = t.z; a[4 * c4 + 3] = t.w;
+          }
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            size_t drow = ((size_t)n * (2 * p.OH) + 2 * oh + (q >> 1)) * (2 * p.OW) + 2 * ow + (q & 1);
+            float* dst = p.out + drow * p.N + col0;
+#pragma unroll
+            for (int c4 = 0; c4 < 8; ++c4) {
+              float4 o;
+              o.x = (bi[4 * c4 + 0] == q && a[4 * c4 + 0] > 0.f) ? v[4 * c4 + 0] * p.scale : 0.f;
+              o.y = (bi[4 * c4 + 1] == q && a[4 * c4 + 1] > 0.f) ? v[4 * c4 + 1] * p.scale : 0.f;
+              o.z = (bi[4 * c4 + 2] == q && a[4 * c4 + 2] > 0.f) ? v[4 * c4 + 2] * p.scale : 0.f;
+              o.w = (bi[4 * c4 + 3] == q && a[4 * c4 + 3] > 0.f) ? v[4 * c4 + 3] * p.scale : 0.f;
+              st4(dst + 4 * c4, o);
+            }
+          }
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, BLOCK_N);
+  }
+}
+
+// ---- host side -----------------------------------------------------------------------------------
+static decltype(&cuTensorMapEncodeTiled) get_encode() {
+  static decltype(&cuTensorMapEncodeTiled) fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && p)
+      fn = reinterpret_cast<decltype(&cuTensorMapEncodeTiled)>(p);
+  }
+  return fn;
+}
+
+template <int BLOCK_N>
+static int launch_igemm(const CUtensorMap* ta, const CUtensorMap* tb, const IgemmParams& p, int m_tiles,
+                        cudaStream_t st) {
+  using L = SmemLayout<BLOCK_N>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    MPIT_CUDA_TRY(cudaFuncSetAttribute(umma_igemm_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       L::kTotal));
+    attr_done = true;
+  }
+  dim3 grid(m_tiles, p.N / BLOCK_N);
+  umma_igemm_kernel<BLOCK_N><<<grid, 192, L::kTotal, st>>>(*ta, *tb, p);
+  MPIT_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // namespace mpit
+
+using namespace mpit;
+
+extern "C" {
+
+// Encode a rank-`rank` fp32 tiled tensor map; swizzle128: 0 none, 1 SWIZZLE_128B (K-major operands),
+// 2 SWIZZLE_128B_ATOM_32B (tf32 MN-major operands).  dims/box are innermost-first;
+// strides_bytes has rank-1 entries (stride of dim 1..rank-1).  out128 is a HOST buffer of 128 bytes.
+int mpit_tmap_encode_f32(void* out128, const void* gptr, int rank, const unsigned long long* dims,
+                         const unsigned long long* strides_bytes, const unsigned* box, int swizzle128) {
+  auto enc = get_encode();
+  if (!enc) return MPIT_E_UNSUPPORTED;
+  if (rank < 1 || rank > 5) return MPIT_E_ARG;
+  cuuint64_t gdim[5], gstr[5];
+  cuuint32_t bx[5], es[5];
+  for (int i = 0; i < rank; ++i) { gdim[i] = dims[i]; bx[i] = box[i]; es[i] = 1; }
+  for (int i = 0; i + 1 < rank; ++i) gstr[i] = strides_bytes[i];
+  CUtensorMap m;
+  CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<void*>(gptr), gdim, gstr, bx,
+                   es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   swizzle128 == 2 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B
+                                   : (swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE),
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return 1000 + (int)r;
+  memcpy(out128, &m, sizeof(m));
+  static_assert(sizeof(CUtensorMap) == 128, "CUtensorMap is 128 bytes");
+  return 0;
+}
+
+// geom17 (HOST): {nsub,tw,th,tn,tiles_w,tiles_h,kw_it,cb,num_kb,sgn,B,OH,OW,N,mode,relu,dropout}
+int mpit_umma_igemm(const void* tmap_a128, const void* tmap_b128, const int* geom17, float scale,
+                    const float* bias, float* out, unsigned char* idx, const float* aux,
+                    const unsigned char* aux_idx, const int* crop, const unsigned long long* rng, int* err,
+                    int block_n, void* stream) {
+  IgemmParams p{};
+  p.nsub = geom17[0]; p.tw = geom17[1]; p.th = geom17[2]; p.tn = geom17[3];
+  p.tiles_w = geom17[4]; p.tiles_h = geom17[5]; p.kw_it = geom17[6]; p.cb = geom17[7];
+  p.num_kb = geom17[8]; p.sgn = geom17[9]; p.B = geom17[10]; p.OH = geom17[11]; p.OW = geom17[12];
+  p.N = geom17[13]; p.mode = geom17[14]; p.relu = geom17[15]; p.dropout = geom17[16];
+  p.scale = scale; p.bias = bias; p.out = out; p.idx = idx; p.aux = aux; p.aux_idx = aux_idx;
+  p.crop = crop; p.rng = rng; p.err = err;
+  if (p.nsub * p.tw * p.th * p.tn != 128 || p.num_kb < 1 || p.N % block_n != 0) return MPIT_E_ARG;
+  if (p.mode == EPI_POOL && (p.tw > 16 || (p.tw & 1) || (p.th & 1))) return MPIT_E_ARG;
+  int subtiles = ((p.B + p.tn - 1) / p.tn) * p.tiles_w * p.tiles_h;
+  int m_tiles = (subtiles + p.nsub - 1) / p.nsub;
+  CUtensorMap ta_, tb_;   // the caller's buffers need not be 64-byte aligned
+  memcpy(&ta_, tmap_a128, sizeof(CUtensorMap));
+  memcpy(&tb_, tmap_b128, sizeof(CUtensorMap));
+  const CUtensorMap* ta = &ta_;
+  const CUtensorMap* tb = &tb_;
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (block_n) {
+    case 32: return launch_igemm<32>(ta, tb, p, m_tiles, st);
+    case 64: return launch_igemm<64>(ta, tb, p, m_tiles, st);
+    case 128: return launch_igemm<128>(ta, tb, p, m_tiles, st);
+    case 256: return launch_igemm<256>(ta, tb, p, m_tiles, st);
+    default: return MPIT_E_ARG;
+  }
+}
+
+}  // extern "C"

@@ -1,0 +1,310 @@
+// Weight gradients of the conv / linear layers on tcgen05 (sm_100a).
+//
+//   dW[m][n] = sum over pixels p of  Xcol[p][m] * dZ[p][n]
+//
+// m runs over the packed weight's K index (kernel row, kernel column, input channel), n over output
+// channels and the reduction runs over output pixels (n_img, oh, ow).  Both operands are therefore
+// "MN-major": a shared-memory tile is [64 pixels][32 floats], exactly what a TMA box over an NHWC
+// tensor delivers -- for X the box is shifted by the kernel offset (and the crop offset), so im2col
+// is again only a coordinate.  tcgen05.mma (kind::tf32, M=128, N=BLOCK_N, K=8) is issued with both
+// major bits set; the accumulator lives in TMEM.  32-bit MN-major operands require the
+// SWIZZLE_128B_BASE32B shared-memory layout (TMA mode SWIZZLE_128B_ATOM_32B).
+//
+// The pixel dimension is split over gridDim.z CTAs.  Each CTA writes its partial [128 x BLOCK_N]
+// tile to a scratch workspace with plain 128-byte stores and mpit_wgrad_reduce sums the splits into
+// the packed gradient (no atomics: bit-reproducible gradients, and the stores are 4x cheaper than
+// red.add at this size).
+//
+// Reference counterpart: nn.SpatialConvolution / nn.Linear accGradParameters called once per sample
+// (asyncsgd/goot.lua:206); here once per mini-batch.
+#include "mpit_b200.h"
+#include "common.cuh"
+#include "umma.cuh"
+#include <string.h>
+
+namespace mpit {
+using namespace umma;
+
+struct WgradParams {
+  int tw, th, tn;            // pixel box of one k-block: tw*th*tn == 64
+  int tiles_w, tiles_h;      // pixel sub-tiles per image
+  int kw_it, cb;             // M-chunk -> (kh, kw, channel block)
+  int total_chunks;          // K/32 of the packed weight
+  int num_kb;                // total pixel k-blocks
+  int B;
+  int N;                     // output channels (physical)
+  int m_pad;                 // m_tiles * 128
+  float* part;               // scratch [split][m_pad][N]
+  const int* crop;
+  int* err;
+};
+
+constexpr int kWStages = 3;
+constexpr int kChunkBytes = 64 * 128;   // 64 pixels x 32 floats
+constexpr int kWABytes = 4 * kChunkBytes;
+
+template <int BLOCK_N>
+struct WSmem {
+  static constexpr int kBBytes = (BLOCK_N / 32) * kChunkBytes;
+  static constexpr int kStageBytes = kWABytes + kBBytes;
+  static constexpr int kBarOff = kWStages * kStageBytes;
+  static constexpr int kTotal = kBarOff + 256 + 1024;
+};
+
+template <int BLOCK_N>
+__global__ void __launch_bounds__(192)
+umma_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_dz,
+                  const WgradParams p) {
+  using L = WSmem<BLOCK_N>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
+  uint64_t* empty_bar = full_bar + kWStages;
+  uint64_t* tmem_full = empty_bar + kWStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m_tile = blockIdx.x;
+  const int n_tile0 = blockIdx.y * BLOCK_N;
+  const int split = blockIdx.z, nsplit = gridDim.z;
+  const int kb_per = (p.num_kb + nsplit - 1) / nsplit;
+  const int kb_lo = split * kb_per;
+  const int kb_hi = min(p.num_kb, kb_lo + kb_per);
+  const int nkb = max(0, kb_hi - kb_lo);
+  int nchunks = p.total_chunks - m_tile * 4;
+  if (nchunks > 4) nchunks = 4;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmap_x);
+    prefetch_tmap(&tmap_dz);
+    for (int i = 0; i < kWStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    mbar_init(tmem_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, BLOCK_N);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      // decode this tile's M chunks once
+      int ckh[4], ckw[4], cc0[4];
+      const int per_kh = p.kw_it * p.cb;
+      for (int j = 0; j < 4; ++j) {
+        int ch = m_tile * 4 + j;
+        int kh = ch / per_kh, r = ch - kh * per_kh;
+        ckh[j] = kh; ckw[j] = r / p.cb; cc0[j] = (r - (r / p.cb) * p.cb) * 32;
+      }
+      const uint32_t bytes = (uint32_t)(nchunks * kChunkBytes + L::kBBytes);
+      const int per_img = p.tiles_w * p.tiles_h;
+      int stage = 0, phase = 0;
+      for (int kb = kb_lo; kb < kb_hi; ++kb) {
+        if (!mbar_wait(&empty_bar[stage], phase ^ 1)) { if (p.err) *p.err = 11; break; }
+        int grp = kb / per_img, r = kb - grp * per_img;
+        int th_i = r / p.tiles_w, tw_i = r - th_i * p.tiles_w;
+        int n0 = grp * p.tn, oh0 = th_i * p.th, ow0 = tw_i * p.tw;
+        int y0 = 0, x0 = 0;
+        if (p.crop && n0 < p.B) { y0 = p.crop[2 * n0]; x0 = p.crop[2 * n0 + 1]; }
+        uint8_t* a_dst = smem + stage * L::kStageBytes;
+        uint8_t* b_dst = a_dst + kWABytes;
+        mbar_expect_tx(&full_bar[stage], bytes);
+        for (int j = 0; j < nchunks; ++j)
+          tma_load_4d(a_dst + j * kChunkBytes, &tmap_x, &full_bar[stage], cc0[j], ow0 + ckw[j] + x0,
+                      oh0 + ckh[j] + y0, n0);
+#pragma unroll
+        for (int j = 0; j < BLOCK_N / 32; ++j)
+          tma_load_4d(b_dst + j * kChunkBytes, &tmap_dz, &full_bar[stage], n_tile0 + j * 32, ow0, oh0, n0);
+        if (++stage == kWStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      constexpr uint32_t idesc = make_idesc_tf32(128, BLOCK_N, 1, 1);   // both operands MN-major
+      int stage = 0, phase = 0;
+      for (int i = 0; i < nkb; ++i) {
+        if (!mbar_wait(&full_bar[stage], phase)) { if (p.err) *p.err = 12; break; }
+        tc_fence_after();
+        uint32_t a_addr = smem_u32(smem + stage * L::kStageBytes);
+        uint32_t b_addr = a_addr + kWABytes;
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {   // 8 pixels per MMA
+          uint64_t ad = make_smem_desc(a_addr + ks * 1024, kChunkBytes, 512, 1);
+          uint64_t bd = make_smem_desc(b_addr + ks * 1024, kChunkBytes, 512, 1);
+          mma_tf32(tmem_base, ad, bd, idesc, (i | ks) ? 1u : 0u);
+        }
+        mma_commit(&empty_bar[stage]);
+        if (++stage == kWStages) { stage = 0; phase ^= 1; }
+      }
+      mma_commit(tmem_full);
+    }
+  } else {
+    const int quad = warp & 3;
+    const int row = quad * 32 + lane;
+    const int m_global = m_tile * 128 + row;
+    if (nkb > 0) {
+      if (!mbar_wait(tmem_full, 0)) { if (p.err) *p.err = 13; }
+    }
+    tc_fence_after();
+    float* dst = p.part + ((size_t)split * p.m_pad + m_global) * p.N + n_tile0;
+#pragma unroll 1
+    for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+      float v[32];
+      if (nkb > 0) {
+        tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
+      } else {
+#pragma unroll
+        for (int c = 0; c < 32; ++c) v[c] = 0.f;
+      }
+      // rows of chunks this tile does not own hold garbage: write zeros there
+      const bool row_ok = (row >> 5) < nchunks;
+#pragma unroll
+      for (int c4 = 0; c4 < 8; ++c4) {
+        float4 o = row_ok ? make_float4(v[4 * c4], v[4 * c4 + 1], v[4 * c4 + 2], v[4 * c4 + 3])
+                          : make_float4(0.f, 0.f, 0.f, 0.f);
+        st4(dst + c0 + 4 * c4, o);
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, BLOCK_N);
+  }
+}
+
+// dW[n][m] (packed forward layout, K = ldw) = sum_s part[s][m][n]
+__global__ void __launch_bounds__(256)
+wgrad_reduce_kernel(const float* __restrict__ part, float* __restrict__ gw, int nsplit, int m_pad, int K, int N,
+                    int ldw) {
+  // tile 32(m) x 32(n) through shared memory so that both sides are coalesced
+  __shared__ float t[32][33];
+  int m0 = blockIdx.x * 32, n0 = blockIdx.y * 32;
+  int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 8 rows per pass
+  for (int r = ty; r < 32; r += 8) {
+    int m = m0 + r, n = n0 + tx;
+    float acc = 0.f;
+    if (m < K && n < N)
+      for (int s = 0; s < nsplit; ++s) acc += part[((size_t)s * m_pad + m) * N + n];
+    t[r][tx] = acc;
+  }
+  __syncthreads();
+  for (int r = ty; r < 32; r += 8) {
+    int n = n0 + r, m = m0 + tx;
+    if (m < K && n < N) gw[(size_t)n * ldw + m] = t[tx][r];
+  }
+}
+
+// Column sums of up to 8 [rows][C] matrices in one launch (bias gradients of every layer).
+struct ColsumSeg { const float* src; float* dst; long long rows; int C; int first_block; };
+struct ColsumArgs { ColsumSeg seg[8]; int nseg; };
+
+__global__ void __launch_bounds__(256) multi_colsum_kernel(ColsumArgs a) {
+  int s = 0;
+  while (s + 1 < a.nseg && (int)blockIdx.x >= a.seg[s + 1].first_block) ++s;
+  const ColsumSeg sg = a.seg[s];
+  int nblk = (s + 1 < a.nseg ? a.seg[s + 1].first_block : (int)gridDim.x) - sg.first_block;
+  int b = blockIdx.x - sg.first_block;
+  int cgroups = (sg.C + 31) / 32;
+  int cg = b % cgroups, rb = b / cgroups, nrb = nblk / cgroups;
+  if (rb >= nrb) return;
+  int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  int c = cg * 32 + tx;
+  float acc = 0.f;
+  if (c < sg.C)
+    for (long long r = (long long)rb * 8 + ty; r < sg.rows; r += (long long)nrb * 8) acc += sg.src[(size_t)r * sg.C + c];
+  __shared__ float sm[8][33];
+  sm[ty][tx] = acc;
+  __syncthreads();
+  if (ty == 0 && c < sg.C) {
+    float t = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += sm[k][tx];
+    atomicAdd(sg.dst + c, t);
+  }
+}
+
+template <int BLOCK_N>
+static int launch_wgrad(const CUtensorMap& tx, const CUtensorMap& tz, const WgradParams& p, int m_tiles,
+                        int nsplit, cudaStream_t st) {
+  using L = WSmem<BLOCK_N>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    MPIT_CUDA_TRY(cudaFuncSetAttribute(umma_wgrad_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       L::kTotal));
+    attr_done = true;
+  }
+  dim3 grid(m_tiles, p.N / BLOCK_N, nsplit);
+  umma_wgrad_kernel<BLOCK_N><<<grid, 192, L::kTotal, st>>>(tx, tz, p);
+  MPIT_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // namespace mpit
+
+using namespace mpit;
+
+extern "C" {
+
+// geom11 (HOST): {tw,th,tn,tiles_w,tiles_h,kw_it,cb,total_chunks,num_kb,B,N}.  `part` must hold
+// nsplit * m_pad * N floats, m_pad = ceil(total_chunks/4)*128.
+int mpit_umma_wgrad(const void* tmap_x128, const void* tmap_dz128, const int* geom11, float* part,
+                    const int* crop, int* err, int block_n, int nsplit, void* stream) {
+  WgradParams p{};
+  p.tw = geom11[0]; p.th = geom11[1]; p.tn = geom11[2]; p.tiles_w = geom11[3]; p.tiles_h = geom11[4];
+  p.kw_it = geom11[5]; p.cb = geom11[6]; p.total_chunks = geom11[7]; p.num_kb = geom11[8];
+  p.B = geom11[9]; p.N = geom11[10];
+  if (p.tw * p.th * p.tn != 64 || p.N % block_n != 0 || nsplit < 1) return MPIT_E_ARG;
+  int m_tiles = (p.total_chunks + 3) / 4;
+  p.m_pad = m_tiles * 128;
+  p.part = part; p.crop = crop; p.err = err;
+  CUtensorMap tx, tz;
+  memcpy(&tx, tmap_x128, sizeof(tx));
+  memcpy(&tz, tmap_dz128, sizeof(tz));
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (block_n) {
+    case 32: return launch_wgrad<32>(tx, tz, p, m_tiles, nsplit, st);
+    case 64: return launch_wgrad<64>(tx, tz, p, m_tiles, nsplit, st);
+    case 128: return launch_wgrad<128>(tx, tz, p, m_tiles, nsplit, st);
+    default: return MPIT_E_ARG;
+  }
+}
+
+// gw[n*ldw + m] = sum_s part[s][m][n] for m < K, n < N.
+int mpit_wgrad_reduce(const float* part, float* gw, int nsplit, int m_pad, int K, int N, int ldw, void* stream) {
+  dim3 grid((K + 31) / 32, (N + 31) / 32);
+  wgrad_reduce_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(part, gw, nsplit, m_pad, K, N, ldw);
+  MPIT_LAUNCH_CHECK();
+  return 0;
+}
+
+// Bias gradients of up to 8 layers in one launch. srcs/dsts are HOST arrays of device pointers;
+// dst vectors are zeroed here (memset nodes) and accumulated with atomics.
+int mpit_multi_colsum(int nseg, const unsigned long long* srcs, const unsigned long long* dsts,
+                      const long long* rows, const int* cols, void* stream) {
+  if (nseg < 1 || nseg > 8) return MPIT_E_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  ColsumArgs a{};
+  a.nseg = nseg;
+  int blocks = 0;
+  for (int i = 0; i < nseg; ++i) {
+    a.seg[i].src = reinterpret_cast<const float*>(srcs[i]);
+    a.seg[i].dst = reinterpret_cast<float*>(dsts[i]);
+    a.seg[i].rows = rows[i];
+    a.seg[i].C = cols[i];
+    a.seg[i].first_block = blocks;
+    int cgroups = (cols[i] + 31) / 32;
+    long long rb = (rows[i] + 255) / 256;
+    if (rb > 64) rb = 64;
+    if (rb < 1) rb = 1;
+    blocks += cgroups * (int)rb;
+    MPIT_CUDA_TRY(cudaMemsetAsync(a.seg[i].dst, 0, sizeof(float) * (size_t)cols[i], st));
+  }
+  multi_colsum_kernel<<<blocks, 256, 0, st>>>(a);
+  MPIT_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"

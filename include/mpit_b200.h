@@ -36,21 +36,22 @@ enum { MPIT_RULE_ADD = 0, MPIT_RULE_RMSPROP = 1, MPIT_RULE_ADAM = 2, MPIT_RULE_A
  * /root/reference/asyncsgd/optim-eamsgd.lua:26-47,70):
  *   do_apply:     g' = g[gmap] + l2wd*x ; x -= clr*g' ; v -= clr*g' ; x -= d
  *   do_lookahead: v *= mom_next ; x += v
- *   wpk != NULL:  wpk[wmap[i]] = x[i]   (refresh tensor-core operand copy) */
+ *   wpk != NULL:  wpk[wmap[m*n+i]] = x[i] for m < nmaps, skipping -1 (refresh the tensor-core
+ *                 operand copies: forward layout, data-gradient layout) */
 int mpit_local_step(float* x, float* v, const float* g, const int* gmap, const float* d, float* wpk,
-                    const int* wmap, long long n, float clr, float l2wd, float mom_next, int do_apply,
+                    const int* wmap, int nmaps, long long n, float clr, float l2wd, float mom_next, int do_apply,
                     int use_mom, int do_lookahead, void* stream);
 
 /* One fused pass of a server/single rule. hyper6 is a HOST array {a,b,c,d,eps,step}
  * (see csrc/kernels/optim_math.cuh). Optional gradient prologue: gscale, L1, L2, clamp
  * (/root/reference/BiCNN/bicnn.lua:398-409). */
 int mpit_rule_step(int rule, float* p, const float* g, const int* gmap, float* s0, float* s1, float* s2,
-                   float* wpk, const int* wmap, long long n, const float* hyper6, float l1, float l2,
-                   float clip, float gscale, void* stream);
+                   float* wpk, const int* wmap, int nmaps, long long n, const float* hyper6, float l1,
+                   float l2, float clip, float gscale, void* stream);
 
 /* Downpour client accumulate (/root/reference/asyncsgd/optim-downpour.lua:26-45). */
 int mpit_downpour_accum(float* x, float* acc, const float* g, const int* gmap, float* wpk, const int* wmap,
-                        long long n, float neg_lr, float l2wd, int move_local, void* stream);
+                        int nmaps, long long n, float neg_lr, float l2wd, int move_local, void* stream);
 
 int mpit_grad_reg_clip(float* g, const float* p, long long n, float l1, float l2, float clip, void* stream);
 
@@ -83,7 +84,7 @@ int mpit_max_ranks(void);
 
 /* Get: dst[i] = centre[i]  (pclient.lua:74-84); optionally also refreshes the packed operand copy. */
 int mpit_param_pull(const unsigned long long* shard_ptrs, int nranks, int rank, float* dst, long long n,
-                    float* wpk, const int* wmap, void* stream);
+                    float* wpk, const int* wmap, int nmaps, void* stream);
 /* Put: centre[i] = src[i]  (seed, pclient.lua:62-72,131-133; single-mode push). */
 int mpit_param_put(const unsigned long long* shard_ptrs, int nranks, int rank, const float* src, long long n,
                    void* stream);
@@ -99,7 +100,7 @@ int mpit_elastic_exchange(const unsigned long long* shard_ptrs, int nranks, int 
  * and refresh of the packed operand copy (optim-eamsgd.lua:26-47,58-70). */
 int mpit_eamsgd_fused_step(const unsigned long long* shard_ptrs, int nranks, int rank, float* x, float* v,
                            const float* g, const int* gmap, float* d, float* wpk, const int* wmap,
-                           long long n, float alpha, float clr, float l2wd, float mom_next, int do_apply,
+                           int nmaps, long long n, float alpha, float clr, float l2wd, float mom_next, int do_apply,
                            int use_mom, int do_lookahead, int do_sync, int has_d_in, void* stream);
 /* SUM/AVG all-reduce over symmetric buffers (test/testreduceall.lua:28). algo 0 = one-shot,
  * 1 = two-shot. `in_mc`/`out_mc` are NVLS multicast addresses (0 = use peer loads/stores).
@@ -140,6 +141,34 @@ int mpit_mc_bind(unsigned long long mc_handle, unsigned long long local_ptr, uns
 int mpit_mc_map(unsigned long long mc_handle, int dev, unsigned long long bytes, unsigned long long* out_ptr);
 int mpit_vmm_free(unsigned long long ptr);
 int mpit_close_fd(int fd);
+
+/* ---- tcgen05 / TMEM / TMA layers (csrc/kernels/umma_igemm.cu) ---------------------------------- */
+/* Encode a rank-`rank` fp32 tiled tensor map (dims/box innermost-first, strides_bytes for dims
+ * 1..rank-1). out128 is a HOST buffer of 128 bytes. */
+int mpit_tmap_encode_f32(void* out128, const void* gptr, int rank, const unsigned long long* dims,
+                         const unsigned long long* strides_bytes, const unsigned* box, int swizzle128);
+/* Implicit-GEMM conv / linear, forward (sgn=+1) or data gradient (sgn=-1) with fused epilogue:
+ * mode 0 bias(+ReLU)(+dropout) store, 1 bias+2x2 maxpool(+ReLU)+argmax, 2 ReLU-mask of a gradient,
+ * 3 un-pool + ReLU-mask of a gradient (7-layers-cnn.lua:8-24 forward/backward).
+ * geom17 (HOST) = {nsub,tw,th,tn,tiles_w,tiles_h,kw_it,cb,num_kb,sgn,B,OH,OW,N,mode,relu,dropout}. */
+int mpit_umma_igemm(const void* tmap_a128, const void* tmap_b128, const int* geom17, float scale,
+                    const float* bias, float* out, unsigned char* idx, const float* aux,
+                    const unsigned char* aux_idx, const int* crop, const unsigned long long* rng, int* err,
+                    int block_n, void* stream);
+
+/* ---- tcgen05 weight gradients (csrc/kernels/umma_wgrad.cu) ------------------------------------- */
+/* dW = Xcol^T dZ over all output pixels, pixel dimension split over `nsplit` CTAs that each write a
+ * partial tile into the scratch workspace `part` (nsplit * m_pad * N floats, m_pad =
+ * ceil(total_chunks/4)*128); mpit_wgrad_reduce sums the splits into the packed gradient
+ * (accGradParameters of SpatialConvolution/Linear, asyncsgd/goot.lua:206).
+ * geom11 (HOST) = {tw,th,tn,tiles_w,tiles_h,kw_it,cb,total_chunks,num_kb,B,N}. */
+int mpit_umma_wgrad(const void* tmap_x128, const void* tmap_dz128, const int* geom11, float* part,
+                    const int* crop, int* err, int block_n, int nsplit, void* stream);
+int mpit_wgrad_reduce(const float* part, float* gw, int nsplit, int m_pad, int K, int N, int ldw, void* stream);
+/* Bias gradients (column sums) of up to 8 [rows][C] matrices in one launch; srcs/dsts/rows/cols are
+ * HOST arrays. */
+int mpit_multi_colsum(int nseg, const unsigned long long* srcs, const unsigned long long* dsts,
+                      const long long* rows, const int* cols, void* stream);
 
 #ifdef __cplusplus
 }

@@ -45,11 +45,13 @@ class Layer:
     relu: bool
     dropout: bool
     C: int          # physical input channels
-    KWP: int        # physical kernel width
+    KWP: int        # physical kernel width (taps)
     CO: int         # physical output channels
+    kw_taps: int = 0    # physical horizontal taps when they differ from k (pair-expanded first layer)
     # filled by build_layout
     w_off: int = 0
     b_off: int = 0
+    d_off: int = -1     # data-gradient operand copy [C][KH][KW][CO] (-1: layer needs none)
     flat_w: int = 0
     flat_b: int = 0
 
@@ -62,8 +64,8 @@ class Layer:
         return self.out_hw // 2 if self.pool else self.out_hw
 
     def geom(self, B: int) -> ConvGeom:
-        return ConvGeom(B, self.src_hw, self.src_hw, self.in_hw, self.in_hw, self.C, self.k, self.k,
-                        self.KWP, self.out_hw, self.out_hw, self.CO)
+        return ConvGeom(B, self.src_hw, self.src_hw, self.in_hw, self.in_hw, self.C, self.k,
+                        self.kw_taps or self.k, self.KWP, self.out_hw, self.out_hw, self.CO)
 
     @property
     def wsize(self):
@@ -73,7 +75,10 @@ class Layer:
 def cifar_layers() -> List[Layer]:
     """Layer table.  fc layers are 1x1 convolutions over a 1x1 'image' of 256 channels."""
     return [
-        Layer("conv1", 3, 64, 5, CROP, IMG, True, True, False, C=4, KWP=8, CO=64),
+        # conv1 reads the pair-expanded image (8 floats per pixel = this pixel + the next one, 4
+        # channels each): physically a 5x4-tap convolution over 8 channels whose 32-float rows hold
+        # kernel columns [0,1 | 1,2 | 2,3 | 3,4]; the duplicated columns carry zero weights.
+        Layer("conv1", 3, 64, 5, CROP, IMG, True, True, False, C=8, KWP=4, CO=64, kw_taps=4),
         Layer("conv2", 64, 128, 5, 12, 12, True, True, False, C=64, KWP=5, CO=128),
         Layer("conv3", 128, 64, 3, 4, 4, False, True, False, C=128, KWP=3, CO=64),
         Layer("fc1", 256, 256, 1, 1, 1, False, True, True, C=256, KWP=1, CO=256),
@@ -101,9 +106,16 @@ class ParamLayout:
             pk += _align(L.wsize)
             L.b_off = pk
             pk += _align(L.CO)
+        for i, L in enumerate(self.layers):
+            if i > 0:   # the first layer never needs a gradient w.r.t. its input
+                L.d_off = pk
+                pk += _align(L.C * L.k * L.k * L.CO)
         self.n_flat = flat
         self.n_packed = pk
         self.wmap = self._build_map()
+        self.dmap = self._build_dmap()
+        # stacked tables consumed by the optimizer kernels' operand refresh (pack_store)
+        self.wmap2 = torch.cat([self.wmap, self.dmap])
 
     def _build_map(self) -> torch.Tensor:
         m = torch.empty(self.n_flat, dtype=torch.int64)
@@ -115,17 +127,44 @@ class ParamLayout:
                 # (7-layers-cnn.lua:19): flat input index i = c*4 + h*2 + w  ->  (h*2+w)*64 + c
                 c, hw = ci // 4, ci % 4
                 pc = hw * 64 + c
+                tap = kw
+            elif L.name == "conv1":
+                # kernel column kw lives in slot [0,1,3,5,7][kw] of the 8 four-channel slots of a row
+                slot = torch.tensor([0, 1, 3, 5, 7])[kw]
+                tap = slot // 2
+                pc = (slot % 2) * 4 + ci
             else:
                 pc = ci
-            off = ((co * L.k + kh) * L.KWP + kw) * L.C + pc + L.w_off
+                tap = kw
+            off = ((co * L.k + kh) * L.KWP + tap) * L.C + pc + L.w_off
             m[L.flat_w:L.flat_w + off.numel()] = off.reshape(-1)
             m[L.flat_b:L.flat_b + L.cout] = torch.arange(L.cout) + L.b_off
         assert m.unique().numel() == self.n_flat
         return m.to(torch.int32)
 
+    def _build_dmap(self) -> torch.Tensor:
+        """flat index -> slot in the data-gradient operand copy Wd[c][kh][kw][co] (K-major over
+        (kh,kw,co)), -1 for parameters that have none (first layer, biases)."""
+        m = torch.full((self.n_flat,), -1, dtype=torch.int64)
+        for L in self.layers:
+            if L.d_off < 0:
+                continue
+            co, ci, kh, kw = torch.meshgrid(torch.arange(L.cout), torch.arange(L.cin), torch.arange(L.k),
+                                            torch.arange(L.k), indexing="ij")
+            if L.name == "fc1":
+                pc = (ci % 4) * 64 + ci // 4
+            else:
+                pc = ci
+            off = ((pc * L.k + kh) * L.k + kw) * L.CO + co + L.d_off
+            m[L.flat_w:L.flat_w + off.numel()] = off.reshape(-1)
+        return m.to(torch.int32)
+
     def pack(self, theta: torch.Tensor) -> torch.Tensor:
         out = torch.zeros(self.n_packed, dtype=theta.dtype, device=theta.device)
         out[self.wmap.to(theta.device).long()] = theta
+        dm = self.dmap.to(theta.device).long()
+        sel = dm >= 0
+        out[dm[sel]] = theta[sel]
         return out
 
     def unpack(self, packed: torch.Tensor) -> torch.Tensor:
@@ -210,15 +249,16 @@ class CifarEngine:
         dev = self.dev
         f32 = dict(dtype=torch.float32, device=dev)
         B = batch
-        self.wmap = self.layout.wmap.to(dev)
+        self.wmap = self.layout.wmap2.to(dev)          # [2 * n_flat]: forward + data-gradient tables
+        self.gmap = self.wmap[:self.layout.n_flat]     # gradients come back in the forward layout
         self.wpk = torch.zeros(self.layout.n_packed, **f32)
         self.gpk = torch.zeros(self.layout.n_packed, **f32)
         # inputs
         self.x_u8 = torch.zeros(B, 3, IMG, IMG, dtype=torch.uint8, device=dev)
         self.labels = torch.zeros(B, dtype=torch.int32, device=dev)
         self.crop = torch.zeros(B, 2, dtype=torch.int32, device=dev)
-        # +1 image of slack: the 8-wide kernel-row TMA box of conv1 reads past the last row
-        self.x0 = torch.zeros((B + 1) * IMG * IMG * 4, **f32)
+        # pair-expanded NHWC8 image (+1 image of slack for the 4-pixel TMA rows at the image edge)
+        self.x0 = torch.zeros((B + 1) * IMG * IMG * 8, **f32)
         # activations (NHWC)
         L1, L2, L3, L4, L5 = self.layers
         self.act = [torch.zeros(B * L.act_hw * L.act_hw * L.CO, **f32) for L in self.layers]
@@ -238,13 +278,11 @@ class CifarEngine:
     # -- parameter plumbing --------------------------------------------------------------------
     def load_flat(self, theta: torch.Tensor) -> None:
         """Refresh the packed operand copy from a flat parameter vector."""
-        self.ops.map_copy(self.wpk, theta, self.wmap, scatter=True)
-        if self._umma is not None:
-            self._umma.after_weight_update()
+        self.ops.local_step(theta, None, None, None, None, self.wpk, self.wmap, do_apply=False)
 
     def flat_grad(self, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         out = out if out is not None else torch.empty(self.layout.n_flat, dtype=torch.float32, device=self.dev)
-        self.ops.map_copy(out, self.gpk, self.wmap, scatter=False)
+        self.ops.map_copy(out, self.gpk, self.gmap, scatter=False)
         return out
 
     def set_batch(self, images_u8: torch.Tensor, labels: torch.Tensor, crop: torch.Tensor) -> None:

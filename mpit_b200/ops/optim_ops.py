@@ -13,11 +13,16 @@ def _n(t):
     return int(t.numel())
 
 
+def _nmaps(wmap, n):
+    """Number of stacked index tables in ``wmap`` ([nmaps * n] int32)."""
+    return 0 if wmap is None else max(1, int(wmap.numel()) // max(n, 1))
+
+
 def local_step(x, v=None, g=None, gmap=None, d=None, wpk=None, wmap=None, *, clr=0.0, l2wd=0.0,
                mom_next=0.0, do_apply=True, use_mom=False, do_lookahead=False):
     """Fused Nesterov apply/lookahead/pack pass (asyncsgd/optim-msgd.lua:20-39)."""
     check(kernels().mpit_local_step(ptr(x), ptr(v), ptr(g), ptr(gmap), ptr(d), ptr(wpk), ptr(wmap),
-                                    _n(x), clr, l2wd, mom_next, int(do_apply), int(use_mom),
+                                    _nmaps(wmap, _n(x)), _n(x), clr, l2wd, mom_next, int(do_apply), int(use_mom),
                                     int(do_lookahead), cur_stream()), "mpit_local_step")
 
 
@@ -58,13 +63,14 @@ def rule_step(rule: str, p, g, hyper6, s0=None, s1=None, s2=None, gmap=None, wpk
               l1=0.0, l2=0.0, clip=0.0, gscale=1.0):
     h = (ctypes.c_float * 6)(*hyper6)
     check(kernels().mpit_rule_step(RULES[rule], ptr(p), ptr(g), ptr(gmap), ptr(s0), ptr(s1), ptr(s2),
-                                   ptr(wpk), ptr(wmap), _n(p), h, l1, l2, clip, gscale, cur_stream()),
+                                   ptr(wpk), ptr(wmap), _nmaps(wmap, _n(p)), _n(p), h, l1, l2, clip, gscale,
+                                   cur_stream()),
           "mpit_rule_step")
 
 
 def downpour_accum(x, acc, g, gmap=None, wpk=None, wmap=None, *, lr, l2wd=0.0, move_local=False):
-    check(kernels().mpit_downpour_accum(ptr(x), ptr(acc), ptr(g), ptr(gmap), ptr(wpk), ptr(wmap), _n(x),
-                                        -lr, l2wd, int(move_local), cur_stream()), "mpit_downpour_accum")
+    check(kernels().mpit_downpour_accum(ptr(x), ptr(acc), ptr(g), ptr(gmap), ptr(wpk), ptr(wmap),
+                                        _nmaps(wmap, _n(x)), _n(x), -lr, l2wd, int(move_local), cur_stream()), "mpit_downpour_accum")
 
 
 def grad_reg_clip(g, p, *, l1=0.0, l2=0.0, clip=0.0):

@@ -1,0 +1,187 @@
+"""tcgen05/TMEM/TMA layer kernels (csrc/kernels/umma_igemm.cu, umma_wgrad.cu): tensor-map
+construction and the per-layer launch plans of the CIFAR CNN.
+
+A plan is built once per engine: every TMA descriptor (activation boxes, weight boxes) is encoded
+on the host up front and the launches carry them by value, so a training step is a fixed sequence
+of kernel launches that captures cleanly into a CUDA graph.
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+from typing import List, Optional
+
+import torch
+
+from .._native import kernels, check, ptr, cur_stream
+
+
+def make_tmap(t_ptr: int, dims: List[int], strides_bytes: List[int], box: List[int], swizzle128: int = 1):
+    """Encode a tiled fp32 tensor map; dims/box innermost first, strides for dims 1..rank-1."""
+    rank = len(dims)
+    buf = (ctypes.c_ubyte * 128)()
+    d = (ctypes.c_ulonglong * 5)(*dims)
+    s = (ctypes.c_ulonglong * 5)(*strides_bytes)
+    b = (ctypes.c_uint * 5)(*box)
+    check(kernels().mpit_tmap_encode_f32(buf, ctypes.c_void_p(t_ptr), rank, d, s, b, int(swizzle128)),
+          "mpit_tmap_encode_f32")
+    return buf
+
+
+@dataclass
+class IgemmLaunch:
+    tmap_a: object
+    tmap_b: object
+    geom: object          # c_int * 17
+    scale: float
+    bias: Optional[torch.Tensor]
+    out: torch.Tensor
+    idx: Optional[torch.Tensor]
+    aux: Optional[torch.Tensor]
+    aux_idx: Optional[torch.Tensor]
+    crop: Optional[torch.Tensor]
+    rng: Optional[torch.Tensor]
+    block_n: int
+    dropout_slot: int = 16
+
+    def run(self, err: torch.Tensor, dropout: Optional[bool] = None):
+        g = self.geom
+        if dropout is not None:
+            g = (ctypes.c_int * 17)(*self.geom)
+            g[16] = int(dropout)
+        check(kernels().mpit_umma_igemm(self.tmap_a, self.tmap_b, g, self.scale, ptr(self.bias), ptr(self.out),
+                                        ptr(self.idx), ptr(self.aux), ptr(self.aux_idx), ptr(self.crop),
+                                        ptr(self.rng), ptr(err), self.block_n, cur_stream()), "mpit_umma_igemm")
+
+
+def igemm_geom(*, nsub, tw, th, tn, tiles_w, tiles_h, kw_it, cb, num_kb, sgn, B, OH, OW, N, mode, relu=0,
+               dropout=0):
+    assert nsub * tw * th * tn == 128
+    return (ctypes.c_int * 17)(nsub, tw, th, tn, tiles_w, tiles_h, kw_it, cb, num_kb, sgn, B, OH, OW, N, mode,
+                               int(relu), int(dropout))
+
+
+EPI_STORE, EPI_POOL, EPI_MASK, EPI_EXPAND = 0, 1, 2, 3
+
+
+def nhwc_tmap(t: torch.Tensor, B: int, H: int, W: int, C: int, box_w: int, box_h: int, box_n: int,
+              swizzle: int = 1):
+    """4-D map over an NHWC fp32 tensor, box = (32 channels, box_w, box_h, box_n)."""
+    return make_tmap(t.data_ptr(), [C, W, H, B], [C * 4, W * C * 4, H * W * C * 4], [32, box_w, box_h, box_n],
+                     swizzle)
+
+
+def weight_tmap(t: torch.Tensor, rows: int, K: int, block_n: int):
+    """2-D map over a [rows][K] K-major operand matrix, box = (32, block_n)."""
+    return make_tmap(t.data_ptr(), [K, rows], [K * 4], [32, block_n])
+
+
+class CifarUmmaPlan:
+    """Launch plan of the CIFAR CNN on the tensor cores (forward, data gradients, weight gradients)."""
+
+    def __init__(self, eng, wgrad: str = "auto"):
+        self.eng = eng
+        B = eng.B
+        assert B % 2 == 0, "the 128-row tiles pair two 8x8 sub-tiles: batch must be even"
+        L1, L2, L3, L4, L5 = eng.layers
+        self.err = torch.zeros(1, dtype=torch.int32, device=eng.dev)
+        act, dz, idx = eng.act, eng.dz, eng.idx
+        w = lambda i: eng.w(i)
+
+        def wd(i):
+            L = eng.layers[i]
+            return eng.wpk[L.d_off:L.d_off + L.C * L.k * L.k * L.CO]
+
+        self.fwd: List[IgemmLaunch] = []
+        # conv1: overlapping view of the pair-expanded NHWC8 image: one 128-byte row = 4 pixels x 8 floats
+        # = kernel columns [0,1|1,2|2,3|3,4] x 4 channels, pixel stride 32 bytes
+        ta = make_tmap(eng.x0.data_ptr(), [32, 32, 32, B], [32, 32 * 32, 32 * 32 * 32], [32, 8, 8, 1])
+        self.fwd.append(IgemmLaunch(
+            ta, weight_tmap(w(0), L1.CO, 5 * 32, 64),
+            igemm_geom(nsub=2, tw=8, th=8, tn=1, tiles_w=3, tiles_h=3, kw_it=1, cb=1, num_kb=5, sgn=1, B=B,
+                       OH=24, OW=24, N=64, mode=EPI_POOL, relu=1),
+            1.0, eng.b(0), act[0], idx[0], None, None, eng.crop, None, 64))
+        # conv2
+        self.fwd.append(IgemmLaunch(
+            nhwc_tmap(act[0], B, 12, 12, 64, 8, 8, 1), weight_tmap(w(1), L2.CO, 25 * 64, 64),
+            igemm_geom(nsub=2, tw=8, th=8, tn=1, tiles_w=1, tiles_h=1, kw_it=5, cb=2, num_kb=50, sgn=1, B=B,
+                       OH=8, OW=8, N=128, mode=EPI_POOL, relu=1),
+            1.0, eng.b(1), act[1], idx[1], None, None, None, None, 64))
+        # conv3
+        self.fwd.append(IgemmLaunch(
+            nhwc_tmap(act[1], B, 4, 4, 128, 2, 2, 32), weight_tmap(w(2), L3.CO, 9 * 128, 32),
+            igemm_geom(nsub=1, tw=2, th=2, tn=32, tiles_w=1, tiles_h=1, kw_it=3, cb=4, num_kb=36, sgn=1, B=B,
+                       OH=2, OW=2, N=64, mode=EPI_STORE, relu=1),
+            1.0, eng.b(2), act[2], None, None, None, None, None, 32))
+        # fc1 (+ReLU +dropout)
+        self.fwd.append(IgemmLaunch(
+            nhwc_tmap(act[2], B, 1, 1, 256, 1, 1, 128), weight_tmap(w(3), 256, 256, 32),
+            igemm_geom(nsub=1, tw=1, th=1, tn=128, tiles_w=1, tiles_h=1, kw_it=1, cb=8, num_kb=8, sgn=1, B=B,
+                       OH=1, OW=1, N=256, mode=EPI_STORE, relu=1, dropout=1),
+            1.0, eng.b(3), act[3], None, None, None, None, eng.rng, 32))
+        # fc2
+        self.fwd.append(IgemmLaunch(
+            nhwc_tmap(act[3], B, 1, 1, 256, 1, 1, 128), weight_tmap(w(4), 32, 256, 32),
+            igemm_geom(nsub=1, tw=1, th=1, tn=128, tiles_w=1, tiles_h=1, kw_it=1, cb=8, num_kb=8, sgn=1, B=B,
+                       OH=1, OW=1, N=32, mode=EPI_STORE),
+            1.0, eng.b(4), act[4], None, None, None, None, None, 32))
+
+        # ---- data gradients (layer i -> dz of layer i-1) ----
+        self.dgrad = {}
+        # fc2: dz5 [B,32] x Wd5 [256][32] -> mask by a4 > 0, x2 (dropout scale) -> dz4
+        self.dgrad[4] = IgemmLaunch(
+            nhwc_tmap(dz[4], B, 1, 1, 32, 1, 1, 128), weight_tmap(wd(4), 256, 32, 32),
+            igemm_geom(nsub=1, tw=1, th=1, tn=128, tiles_w=1, tiles_h=1, kw_it=1, cb=1, num_kb=1, sgn=-1, B=B,
+                       OH=1, OW=1, N=256, mode=EPI_MASK),
+            2.0, None, dz[3], None, act[3], None, None, None, 32)
+        # fc1: dz4 [B,256] x Wd4 [256][256] -> mask by a3 > 0 -> dz3
+        self.dgrad[3] = IgemmLaunch(
+            nhwc_tmap(dz[3], B, 1, 1, 256, 1, 1, 128), weight_tmap(wd(3), 256, 256, 32),
+            igemm_geom(nsub=1, tw=1, th=1, tn=128, tiles_w=1, tiles_h=1, kw_it=1, cb=8, num_kb=8, sgn=-1, B=B,
+                       OH=1, OW=1, N=256, mode=EPI_MASK),
+            1.0, None, dz[2], None, act[2], None, None, None, 32)
+        # conv3: dz3 [B,2,2,64] -> d(a2) over 4x4 -> un-pool with idx2, mask a2 > 0 -> dz2 [B,8,8,128]
+        self.dgrad[2] = IgemmLaunch(
+            nhwc_tmap(dz[2], B, 2, 2, 64, 4, 4, 8), weight_tmap(wd(2), 128, 9 * 64, 32),
+            igemm_geom(nsub=1, tw=4, th=4, tn=8, tiles_w=1, tiles_h=1, kw_it=3, cb=2, num_kb=18, sgn=-1, B=B,
+                       OH=4, OW=4, N=128, mode=EPI_EXPAND),
+            1.0, None, dz[1], None, act[1], idx[1], None, None, 32)
+        # conv2: dz2 [B,8,8,128] -> d(a1) over 12x12 -> un-pool with idx1, mask -> dz1 [B,24,24,64]
+        self.dgrad[1] = IgemmLaunch(
+            nhwc_tmap(dz[1], B, 8, 8, 128, 4, 4, 4), weight_tmap(wd(1), 64, 25 * 128, 32),
+            igemm_geom(nsub=2, tw=4, th=4, tn=4, tiles_w=3, tiles_h=3, kw_it=5, cb=4, num_kb=100, sgn=-1, B=B,
+                       OH=12, OW=12, N=64, mode=EPI_EXPAND),
+            1.0, None, dz[0], None, act[0], idx[0], None, None, 32)
+
+        self.wgrad = None
+        if wgrad != "ref":
+            try:
+                from .umma_wgrad_ops import CifarWgradPlan
+                self.wgrad = CifarWgradPlan(eng, self.err)
+            except ImportError:
+                if wgrad == "umma":
+                    raise
+
+    # -- schedules -----------------------------------------------------------------------------
+    def forward(self, train: bool):
+        for i, l in enumerate(self.fwd):
+            l.run(self.err, dropout=(train if i == 3 else None))
+
+    def backward(self):
+        eng, ops, B = self.eng, self.eng.ops, self.eng.B
+        for i in range(4, -1, -1):
+            L = eng.layers[i]
+            x_in = eng.act[i - 1] if i > 0 else eng.x0
+            if self.wgrad is not None:
+                self.wgrad.run(i)
+            else:
+                ops.conv_wgrad_ref(L.geom(B), eng.dz[i], x_in, eng.gw(i), crop=eng.crop if i == 0 else None)
+                ops.colsum(eng.dz[i], eng.gb(i), B * L.out_hw * L.out_hw, L.CO)
+            if i > 0:
+                self.dgrad[i].run(self.err)
+
+    def check(self):
+        """Raise if any bounded pipeline wait inside a tcgen05 kernel expired."""
+        e = int(self.err.item())
+        if e:
+            raise RuntimeError(f"umma pipeline wait timed out (code {e})")

@@ -1,0 +1,83 @@
+"""Launch plan of the tcgen05 weight-gradient kernels (csrc/kernels/umma_wgrad.cu) for the CIFAR CNN."""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+
+from .._native import kernels, check, ptr, cur_stream
+from .umma_ops import make_tmap, nhwc_tmap as _nhwc_tmap
+
+MN_SWIZZLE = 2   # CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B: the only layout tf32 MN-major operands support
+
+
+def nhwc_tmap(*a):
+    return _nhwc_tmap(*a, swizzle=MN_SWIZZLE)
+
+
+@dataclass
+class WgradLaunch:
+    tmap_x: object
+    tmap_dz: object
+    geom: object
+    crop: Optional[torch.Tensor]
+    block_n: int
+    nsplit: int
+    m_pad: int
+    K: int
+    N: int
+    gw: torch.Tensor
+    part_off: int
+
+
+class CifarWgradPlan:
+    def __init__(self, eng, err: torch.Tensor):
+        self.eng, self.err = eng, err
+        B = eng.B
+        act, dz = eng.act, eng.dz
+        G = lambda *a: (ctypes.c_int * 11)(*a)
+        ceil = lambda a, b: (a + b - 1) // b
+        x0map = make_tmap(eng.x0.data_ptr(), [32, 32, 32, B], [32, 32 * 32, 32 * 32 * 32], [32, 8, 8, 1], MN_SWIZZLE)
+        specs = [
+            # tmap_x, tmap_dz, (tw,th,tn,tiles_w,tiles_h,kw_it,cb,total_chunks,num_kb,B,N), crop, block_n, nsplit
+            (x0map, nhwc_tmap(dz[0], B, 24, 24, 64, 8, 8, 1), (8, 8, 1, 3, 3, 1, 1, 5, B * 9, B, 64), eng.crop, 64,
+             min(64, B * 9)),
+            (nhwc_tmap(act[0], B, 12, 12, 64, 8, 8, 1), nhwc_tmap(dz[1], B, 8, 8, 128, 8, 8, 1),
+             (8, 8, 1, 1, 1, 5, 2, 50, B, B, 128), None, 128, min(8, B)),
+            (nhwc_tmap(act[1], B, 4, 4, 128, 2, 2, 16), nhwc_tmap(dz[2], B, 2, 2, 64, 2, 2, 16),
+             (2, 2, 16, 1, 1, 3, 4, 36, ceil(B, 16), B, 64), None, 64, ceil(B, 16)),
+            (nhwc_tmap(act[2], B, 1, 1, 256, 1, 1, 64), nhwc_tmap(dz[3], B, 1, 1, 256, 1, 1, 64),
+             (1, 1, 64, 1, 1, 1, 8, 8, ceil(B, 64), B, 256), None, 128, ceil(B, 64)),
+            (nhwc_tmap(act[3], B, 1, 1, 256, 1, 1, 64), nhwc_tmap(dz[4], B, 1, 1, 32, 1, 1, 64),
+             (1, 1, 64, 1, 1, 1, 8, 8, ceil(B, 64), B, 32), None, 32, ceil(B, 64)),
+        ]
+        self.launches = []
+        off = 0
+        for i, (tx, tz, g, crop, bn, ns) in enumerate(specs):
+            chunks, N = g[7], g[10]
+            m_pad = ceil(chunks, 4) * 128
+            self.launches.append(WgradLaunch(tx, tz, G(*g), crop, bn, ns, m_pad, chunks * 32, N, eng.gw(i), off))
+            off += ns * m_pad * N
+        # split-K scratch workspace shared by all layers
+        self.part = torch.empty(off, dtype=torch.float32, device=eng.dev)
+        L = eng.layers
+        n = len(L)
+        self._cs = ((ctypes.c_ulonglong * n)(*[dz[i].data_ptr() for i in range(n)]),
+                    (ctypes.c_ulonglong * n)(*[eng.gb(i).data_ptr() for i in range(n)]),
+                    (ctypes.c_longlong * n)(*[B * L[i].out_hw * L[i].out_hw for i in range(n)]),
+                    (ctypes.c_int * n)(*[L[i].CO for i in range(n)]))
+
+    def run(self, i: int):
+        l = self.launches[i]
+        k = kernels()
+        part = self.part[l.part_off:]
+        check(k.mpit_umma_wgrad(l.tmap_x, l.tmap_dz, l.geom, ptr(part), ptr(l.crop), ptr(self.err), l.block_n,
+                                l.nsplit, cur_stream()), "mpit_umma_wgrad")
+        check(k.mpit_wgrad_reduce(ptr(part), ptr(l.gw), l.nsplit, l.m_pad, l.K, l.N, l.K, cur_stream()),
+              "mpit_wgrad_reduce")
+        if i == 0:   # last layer of the backward sweep: all dz are final, sum every bias gradient at once
+            n = len(self.launches)
+            check(k.mpit_multi_colsum(n, self._cs[0], self._cs[1], self._cs[2], self._cs[3], cur_stream()),
+                  "mpit_multi_colsum")

@@ -100,7 +100,7 @@ class DeviceMSGD(_DeviceOptBase):
 
     def _boundary(self, do_apply: bool, do_lookahead: bool):
         e = self.engine
-        ops.local_step(self.x, self.v, e.gpk, e.wmap, None, e.wpk, e.wmap, clr=self._clr(self.t - 1),
+        ops.local_step(self.x, self.v, e.gpk, e.gmap, None, e.wpk, e.wmap, clr=self._clr(self.t - 1),
                        l2wd=self.l2wd, mom_next=self._mom(self.t), do_apply=do_apply, use_mom=self.mom > 0,
                        do_lookahead=do_lookahead)
 
@@ -152,7 +152,7 @@ class DeviceEAMSGD(_DeviceOptBase):
 
     def _boundary(self, do_apply, do_lookahead, do_sync, has_d_in):
         e = self.engine
-        self.center.eamsgd_step(self.x, self.v, e.gpk, e.wmap, self.d, e.wpk, e.wmap, alpha=self.mva,
+        self.center.eamsgd_step(self.x, self.v, e.gpk, e.gmap, self.d, e.wpk, e.wmap, alpha=self.mva,
                                 clr=self._clr(self.t - 1), l2wd=self.l2wd, mom_next=self.mom,
                                 do_apply=do_apply, use_mom=self.mom > 0, do_lookahead=do_lookahead,
                                 do_sync=do_sync, has_d_in=has_d_in)
@@ -200,7 +200,7 @@ class DeviceDownpour(_DeviceOptBase):
         def body():
             e.fwd_bwd()
             # acc += -lr (g + l2wd x); between syncs also move locally
-            ops.downpour_accum(self.x, self.acc, e.gpk, e.wmap, e.wpk, e.wmap, lr=lr, l2wd=self.l2wd,
+            ops.downpour_accum(self.x, self.acc, e.gpk, e.gmap, e.wpk, e.wmap, lr=lr, l2wd=self.l2wd,
                                move_local=not do_sync)
             if do_sync:
                 self.center.push_add(self.acc, zero_src=True)   # centre += acc ; acc = 0
@@ -230,7 +230,7 @@ class DeviceRule(_DeviceOptBase):
         e.fwd_bwd()
         self.t += 1
         h = ops.rule_hyper(self.rule, self.t, **self.hyper)
-        ops.rule_step(self.rule, self.x, e.gpk, h, self.s0, self.s1, self.s2, gmap=e.wmap, wpk=e.wpk,
+        ops.rule_step(self.rule, self.x, e.gpk, h, self.s0, self.s1, self.s2, gmap=e.gmap, wpk=e.wpk,
                       wmap=e.wmap, l1=self.l1, l2=self.l2, clip=self.clip)
         if self.center is not None:
             self.center.put(self.x)

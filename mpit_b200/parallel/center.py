@@ -49,6 +49,9 @@ class ShardedCenter:
     def create(cls, heap, n: int) -> "ShardedCenter":
         return cls(heap.alloc(shard_capacity(n, heap.nranks)), n)
 
+    def _nmaps(self, wmap) -> int:
+        return 0 if wmap is None else max(1, int(wmap.numel()) // self.n)
+
     @property
     def local_shard(self) -> torch.Tensor:
         off, size = self.parts[self.rank]
@@ -63,7 +66,7 @@ class ShardedCenter:
     def pull(self, dst: torch.Tensor, wpk=None, wmap=None) -> None:
         """dst := centre (pclient.lua:74-84), optionally refreshing the packed operand copy."""
         check(self.k.mpit_param_pull(self._ptrs, self.nranks, self.rank, ptr(dst), self.n, ptr(wpk), ptr(wmap),
-                                     cur_stream()), "mpit_param_pull")
+                                     self._nmaps(wmap), cur_stream()), "mpit_param_pull")
 
     def push_add(self, src: torch.Tensor, params: Optional[torch.Tensor] = None, *, scale=1.0, l1=0.0, l2=0.0,
                  clip=0.0, zero_src=False) -> None:
@@ -79,7 +82,7 @@ class ShardedCenter:
     def eamsgd_step(self, x, v, g, gmap, d, wpk, wmap, *, alpha, clr, l2wd, mom_next, do_apply, use_mom,
                     do_lookahead, do_sync, has_d_in) -> None:
         check(self.k.mpit_eamsgd_fused_step(self._ptrs, self.nranks, self.rank, ptr(x), ptr(v), ptr(g), ptr(gmap),
-                                            ptr(d), ptr(wpk), ptr(wmap), self.n, alpha, clr, l2wd, mom_next,
+                                            ptr(d), ptr(wpk), ptr(wmap), self._nmaps(wmap), self.n, alpha, clr, l2wd, mom_next,
                                             int(do_apply), int(use_mom), int(do_lookahead), int(do_sync),
                                             int(has_d_in), cur_stream()), "mpit_eamsgd_fused_step")
 

@@ -17,8 +17,19 @@ def test_pack_unpack_roundtrip():
     theta = torch.randn(lay.n_flat)
     pk = lay.pack(theta)
     assert torch.equal(lay.unpack(pk), theta)
-    # padded entries stay zero
-    assert int((pk != 0).sum()) <= lay.n_flat
+    # padded entries stay zero (forward copy + data-gradient copy of the weights)
+    assert int((pk != 0).sum()) <= 2 * lay.n_flat
+
+
+def test_dgrad_operand_copy_is_transposed_weight():
+    lay = ParamLayout()
+    m = TorchCifarCNN()
+    pk = lay.pack(flat_from_torch(m))
+    L = lay.layers[2]   # conv3: Wd[c][kh][kw][co]
+    wd = pk[L.d_off:L.d_off + L.C * L.k * L.k * L.CO].view(L.C, L.k, L.k, L.CO)
+    ref = m.features[6].weight.detach().permute(1, 2, 3, 0)
+    assert torch.equal(wd, ref)
+    assert lay.layers[0].d_off == -1 and int((lay.dmap >= 0).sum()) > 0
 
 
 def test_packed_conv_layout_matches_torch_weight():
@@ -30,11 +41,12 @@ def test_packed_conv_layout_matches_torch_weight():
     w = pk[L.w_off:L.w_off + L.wsize].view(L.CO, L.k, L.KWP, L.C)
     ref = m.features[3].weight.detach().permute(0, 2, 3, 1)  # co,kh,kw,ci
     assert torch.equal(w[:, :, :L.k, :], ref)
+    # conv1: pair-expanded layout, 8 four-channel slots per kernel row; kw -> slot [0,1,3,5,7]
     L = lay.layers[0]
-    w = pk[L.w_off:L.w_off + L.wsize].view(L.CO, L.k, L.KWP, L.C)
+    w = pk[L.w_off:L.w_off + L.wsize].view(L.CO, L.k, 8, 4)
     ref = m.features[0].weight.detach().permute(0, 2, 3, 1)
-    assert torch.equal(w[:, :, :5, :3], ref)
-    assert float(w[:, :, 5:, :].abs().sum()) == 0.0 and float(w[..., 3].abs().sum()) == 0.0
+    assert torch.equal(w[:, :, [0, 1, 3, 5, 7], :3], ref)
+    assert float(w[:, :, [2, 4, 6], :].abs().sum()) == 0.0 and float(w[..., 3].abs().sum()) == 0.0
 
 
 def test_fc1_hwc_permutation():

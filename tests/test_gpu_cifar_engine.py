@@ -46,6 +46,10 @@ def _run(impl, B=16, train=True, tol=2e-4):
         got_g = eng.flat_grad().cpu()
         denom = ref_g.abs().max().item()
         assert (got_g - ref_g).abs().max().item() <= tol * max(1.0, denom) + tol
+        # TF32 forward flips a few ReLU / max-pool decisions, which moves the gradient by a few
+        # per cent in L2 although every kernel is within 1e-3 of fp32 on identical inputs (see the
+        # layer-wise tests); the exact-fp32 path has to match tightly.
+        assert float((got_g - ref_g).norm() / ref_g.norm()) < (10 * tol if impl == "ref" else 0.15)
         # about half of the active units are dropped
         frac = float((a4 > 0).float().mean())
         assert 0.05 < frac < 0.6
@@ -64,3 +68,109 @@ def test_engine_ref_eval_matches_torch_cpu():
 def test_dropout_counter_advances():
     eng = _run("ref", train=True)
     assert int(eng.rng[1].item()) == 1
+
+
+def _rel_l2(a, b):
+    return float((a - b).norm() / (b.norm() + 1e-12))
+
+
+def test_engine_umma_forward_matches_ref_kernels():
+    """tcgen05 forward (TF32 inputs) vs the exact-fp32 CUDA-core kernels, layer by layer."""
+    torch.manual_seed(1)
+    B = 16
+    model = TorchCifarCNN()
+    theta = flat_from_torch(model).cuda()
+    images = torch.randint(0, 256, (B, 3, 32, 32), dtype=torch.uint8)
+    labels = torch.randint(0, NUM_CLASSES, (B,), dtype=torch.int32)
+    crop = random_crop_offsets(B)
+    engs = {}
+    for impl in ("ref", "umma"):
+        e = CifarEngine(B, impl=impl, seed=3)
+        e.load_flat(theta.clone())
+        e.set_batch(images, labels, crop)
+        e.forward(True)
+        torch.cuda.synchronize()
+        engs[impl] = e
+    engs["umma"]._umma.check()
+    for i in range(5):
+        a, b = engs["umma"].act[i], engs["ref"].act[i]
+        if i == 3:   # dropout: same Philox stream, so the same units are dropped
+            assert float(((a > 0) != (b > 0)).float().mean()) < 2e-3
+        assert _rel_l2(a, b) < 3e-3, (i, _rel_l2(a, b))
+    for i in (0, 1):
+        same = float((engs["umma"].idx[i] == engs["ref"].idx[i]).float().mean())
+        assert same > 0.995, (i, same)
+
+
+def test_engine_umma_train_matches_torch_cpu():
+    eng = _run("umma", train=True, tol=4e-3)
+    eng._umma.check()
+
+
+def test_engine_umma_eval_matches_torch_cpu():
+    eng = _run("umma", train=False, tol=4e-3)
+    eng._umma.check()
+
+
+def test_engine_umma_dgrad_matches_ref_layerwise():
+    """Each tcgen05 data-gradient kernel fed with the exact-fp32 path's inputs."""
+    torch.manual_seed(2)
+    B = 16
+    model = TorchCifarCNN()
+    theta = flat_from_torch(model).cuda()
+    images = torch.randint(0, 256, (B, 3, 32, 32), dtype=torch.uint8)
+    labels = torch.randint(0, NUM_CLASSES, (B,), dtype=torch.int32)
+    crop = random_crop_offsets(B)
+    ref = CifarEngine(B, impl="ref", seed=3)
+    um = CifarEngine(B, impl="umma", seed=3)
+    for e in (ref, um):
+        e.load_flat(theta.clone())
+        e.set_batch(images, labels, crop)
+    ref.fwd_bwd()
+    torch.cuda.synchronize()
+    for i in range(5):
+        um.act[i].copy_(ref.act[i])
+        if ref.idx[i] is not None:
+            um.idx[i].copy_(ref.idx[i])
+    for i in range(4, 0, -1):
+        um.dz[i].copy_(ref.dz[i])
+        um.dz[i - 1].fill_(123.0)
+        um._umma.dgrad[i].run(um._umma.err)
+        torch.cuda.synchronize()
+        um._umma.check()
+        err = _rel_l2(um.dz[i - 1], ref.dz[i - 1])
+        assert err < 3e-3, (i, err)
+
+
+@pytest.mark.parametrize("B", [16, 128])
+def test_engine_umma_wgrad_matches_ref_layerwise(B):
+    """tcgen05 weight/bias gradients fed with the exact-fp32 path's activations and dz."""
+    torch.manual_seed(4)
+    model = TorchCifarCNN()
+    theta = flat_from_torch(model).cuda()
+    images = torch.randint(0, 256, (B, 3, 32, 32), dtype=torch.uint8)
+    labels = torch.randint(0, NUM_CLASSES, (B,), dtype=torch.int32)
+    crop = random_crop_offsets(B)
+    ref = CifarEngine(B, impl="ref", seed=3)
+    um = CifarEngine(B, impl="umma", seed=3)
+    assert um._umma.wgrad is not None
+    for e in (ref, um):
+        e.load_flat(theta.clone())
+        e.set_batch(images, labels, crop)
+    ref.fwd_bwd()
+    um.ops.prep_u8(um.x_u8, um.x0, B, 32, 32)
+    torch.cuda.synchronize()
+    for i in range(5):
+        um.act[i].copy_(ref.act[i])
+        um.dz[i].copy_(ref.dz[i])
+    um.gpk.fill_(7.0)
+    for i in range(4, -1, -1):
+        um._umma.wgrad.run(i)
+    torch.cuda.synchronize()
+    um._umma.check()
+    for i in range(5):
+        L = um.layers[i]
+        gw_u = um.gw(i).view(L.CO, L.k, L.KWP, L.C)[:, :, :L.k]
+        gw_r = ref.gw(i).view(L.CO, L.k, L.KWP, L.C)[:, :, :L.k]
+        assert _rel_l2(gw_u, gw_r) < 3e-3, (i, _rel_l2(gw_u, gw_r))
+        assert _rel_l2(um.gb(i), ref.gb(i)) < 1e-4, (i, "bias")
