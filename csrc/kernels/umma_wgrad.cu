@@ -21,6 +21,8 @@
 #include "common.cuh"
 #include "umma.cuh"
 #include <string.h>
+#include <stdio.h>
+#include <mutex>
 
 namespace mpit {
 using namespace umma;
@@ -308,3 +310,80 @@ int mpit_multi_colsum(int nseg, const unsigned long long* srcs, const unsigned l
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// Weight gradient for callers that cannot allocate device memory.
+//
+// mpit_umma_wgrad needs a split-K workspace and normally the caller provides it.  Some callers have
+// no way to do that: a host program or foreign-language binding that only holds this C ABI and owns
+// no device allocator; code running next to a framework whose caching allocator has already claimed
+// the whole device heap, where a raw cudaMalloc would fail or evict; and latency-sensitive loops that
+// must not execute cudaMalloc/cudaFree because those calls synchronise the whole device.  For them
+// the workspace lives in the library image itself: a fixed array in device global memory that every
+// GPU loading this library carries until the process exits (MPIT_NOALLOC_SCRATCH_FLOATS floats,
+// 8 MiB).  Requests that would need more are refused, nothing is ever allocated or freed here.
+//
+// `g_noalloc_scratch` below is, in host code, only a handle for the symbol: its device address is
+// looked up once per device with cudaGetSymbolAddress (with that device current) and it is that
+// address which the kernels receive.
+// ---------------------------------------------------------------------------------------------
+static __device__ __align__(256) float g_noalloc_scratch[MPIT_NOALLOC_SCRATCH_FLOATS];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mu;
+float* g_noalloc_ptr[kMaxDevices] = {nullptr};
+
+// One-time set-up for the CURRENT device: resolve the scratch symbol's device address and raise the
+// dynamic shared-memory limit of the kernel instantiations on this device.
+int noalloc_setup_current_device(float** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= kMaxDevices) return MPIT_E_ARG;
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_ptr[dev]) {
+    float* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
+    if (e != cudaSuccess) return (int)e;
+    if (!p) return MPIT_E_UNSUPPORTED;
+    e = cudaFuncSetAttribute(mpit::umma_wgrad_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             mpit::WSmem<32>::kTotal);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(mpit::umma_wgrad_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             mpit::WSmem<64>::kTotal);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(mpit::umma_wgrad_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             mpit::WSmem<128>::kTotal);
+    if (e != cudaSuccess) return (int)e;
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  return 0;
+}
+}  // namespace
+
+extern "C" int mpit_umma_wgrad_noalloc(const void* tmap_x128, const void* tmap_dz128, const int* geom11,
+                                       float* gw, int ldw, const int* crop, int* err, int block_n,
+                                       int nsplit, void* stream) {
+  if (!geom11 || !gw || nsplit < 1) return MPIT_E_ARG;
+  const int total_chunks = geom11[7], N = geom11[10];
+  if (total_chunks < 1 || N < 1) return MPIT_E_ARG;
+  const int m_pad = ((total_chunks + 3) / 4) * 128;
+  const unsigned long long need = (unsigned long long)nsplit * (unsigned long long)m_pad * (unsigned long long)N;
+  if (need > (unsigned long long)MPIT_NOALLOC_SCRATCH_FLOATS) {
+    fprintf(stderr,
+            "mpit_umma_wgrad_noalloc: this problem needs %llu scratch floats (nsplit=%d x m_pad=%d x N=%d) but the "
+            "built-in scratch holds %u; lower nsplit or call mpit_umma_wgrad with your own workspace\n",
+            need, nsplit, m_pad, N, (unsigned)MPIT_NOALLOC_SCRATCH_FLOATS);
+    return MPIT_E_SCRATCH;
+  }
+  float* scratch = nullptr;
+  int rc = noalloc_setup_current_device(&scratch);
+  if (rc) return rc;
+  // Every partial tile that the reduction reads is written in full by the gradient kernel of this
+  // same call, so whatever an earlier call left in the scratch is never observed: nothing to clear.
+  rc = mpit_umma_wgrad(tmap_x128, tmap_dz128, geom11, scratch, crop, err, block_n, nsplit, stream);
+  if (rc) return rc;
+  return mpit_wgrad_reduce(scratch, gw, nsplit, m_pad, total_chunks * 32, N, ldw, stream);
+}

@@ -24,6 +24,7 @@ extern "C" {
 #define MPIT_E_UNSUPPORTED (-2)
 #define MPIT_E_TIMEOUT (-3)
 #define MPIT_E_ARG (-4)
+#define MPIT_E_SCRATCH (-5)   /* request exceeds the built-in scratch of a *_noalloc entry point */
 
 /* ---- optimizer rules (csrc/kernels/optim.cu) ------------------------------------------ */
 
@@ -165,6 +166,25 @@ int mpit_umma_igemm(const void* tmap_a128, const void* tmap_b128, const int* geo
 int mpit_umma_wgrad(const void* tmap_x128, const void* tmap_dz128, const int* geom11, float* part,
                     const int* crop, int* err, int block_n, int nsplit, void* stream);
 int mpit_wgrad_reduce(const float* part, float* gw, int nsplit, int m_pad, int K, int N, int ldw, void* stream);
+/* Same result as mpit_umma_wgrad followed by mpit_wgrad_reduce (gw[n*ldw + m], n < N,
+ * m < 32*total_chunks), for callers that cannot allocate device memory: a plain-C host or another
+ * language binding with no device allocator of its own, code sharing the GPU with a framework
+ * allocator that already owns the whole heap, or a latency-critical loop that must avoid the
+ * device-wide synchronisation of cudaMalloc/cudaFree.  The split-K workspace is a fixed array inside
+ * the library (MPIT_NOALLOC_SCRATCH_FLOATS floats = 8 MiB, resident on every GPU that loads the
+ * library until the process exits); the call allocates and frees nothing.
+ *   - Limit: nsplit * ceil(total_chunks/4)*128 * N <= MPIT_NOALLOC_SCRATCH_FLOATS, otherwise the call
+ *     prints the required size to stderr, launches nothing and returns MPIT_E_SCRATCH.
+ *   - The first call on each device looks up the array's device address and sets kernel attributes
+ *     for that device; make that first call with the device current and before any stream capture
+ *     is started on it.
+ *   - All calls on a device share the one array, which keeps the previous call's contents. The
+ *     kernels overwrite every word they later read, so no clearing is needed, but two calls whose
+ *     GPU work overlaps (different streams, or different host threads) race on it: serialise them.
+ * This entry point has no counterpart in the reference. */
+#define MPIT_NOALLOC_SCRATCH_FLOATS (2u * 1024u * 1024u)
+int mpit_umma_wgrad_noalloc(const void* tmap_x128, const void* tmap_dz128, const int* geom11, float* gw, int ldw,
+                            const int* crop, int* err, int block_n, int nsplit, void* stream);
 /* Bias gradients (column sums) of up to 8 [rows][C] matrices in one launch; srcs/dsts/rows/cols are
  * HOST arrays. */
 int mpit_multi_colsum(int nseg, const unsigned long long* srcs, const unsigned long long* dsts,

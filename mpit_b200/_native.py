@@ -71,7 +71,8 @@ def check(code: int, what: str = "") -> None:
     if code == 0:
         launches.count += 1
         return
-    msg = {-2: "unsupported", -3: "timeout", -4: "bad argument"}.get(code)
+    msg = {-2: "unsupported", -3: "timeout", -4: "bad argument",
+           -5: "request exceeds the built-in scratch of a no-allocation entry point"}.get(code)
     if msg is None and code > 0:
         try:
             import torch
