@@ -199,32 +199,65 @@ wgrad_reduce_kernel(const float* __restrict__ part, float* __restrict__ gw, int 
   }
 }
 
+// Sum the split-K partials of up to 8 layers in one launch: one thread per output element,
+// consecutive threads along n (coalesced reads of part[s][m][n]), splits unrolled for ILP.
+struct ReduceSeg { const float* part; float* gw; int nsplit, m_pad, K, N, ldw, first_block; };
+struct ReduceArgs { ReduceSeg seg[8]; int nseg; };
+
+__global__ void __launch_bounds__(256) multi_wgrad_reduce_kernel(ReduceArgs a) {
+  int s = 0;
+  while (s + 1 < a.nseg && (int)blockIdx.x >= a.seg[s + 1].first_block) ++s;
+  const ReduceSeg sg = a.seg[s];
+  long long e = (long long)(blockIdx.x - sg.first_block) * 256 + threadIdx.x;
+  if (e >= (long long)sg.K * sg.N) return;
+  int m = (int)(e / sg.N), n = (int)(e % sg.N);
+  const float* p = sg.part + (size_t)m * sg.N + n;
+  const size_t stride = (size_t)sg.m_pad * sg.N;
+  float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
+  int sp = 0;
+  for (; sp + 4 <= sg.nsplit; sp += 4) {
+    acc0 += p[(size_t)sp * stride];
+    acc1 += p[(size_t)(sp + 1) * stride];
+    acc2 += p[(size_t)(sp + 2) * stride];
+    acc3 += p[(size_t)(sp + 3) * stride];
+  }
+  for (; sp < sg.nsplit; ++sp) acc0 += p[(size_t)sp * stride];
+  sg.gw[(size_t)n * sg.ldw + m] = (acc0 + acc1) + (acc2 + acc3);
+}
+
 // Column sums of up to 8 [rows][C] matrices in one launch (bias gradients of every layer).
-struct ColsumSeg { const float* src; float* dst; long long rows; int C; int first_block; };
+// A warp covers 128 consecutive floats with float4 loads; C must be a multiple of 4 and <= 256.
+struct ColsumSeg { const float* src; float* dst; long long rows; int C; int first_block; int nblk; };
 struct ColsumArgs { ColsumSeg seg[8]; int nseg; };
 
 __global__ void __launch_bounds__(256) multi_colsum_kernel(ColsumArgs a) {
   int s = 0;
   while (s + 1 < a.nseg && (int)blockIdx.x >= a.seg[s + 1].first_block) ++s;
   const ColsumSeg sg = a.seg[s];
-  int nblk = (s + 1 < a.nseg ? a.seg[s + 1].first_block : (int)gridDim.x) - sg.first_block;
-  int b = blockIdx.x - sg.first_block;
-  int cgroups = (sg.C + 31) / 32;
-  int cg = b % cgroups, rb = b / cgroups, nrb = nblk / cgroups;
-  if (rb >= nrb) return;
-  int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  int c = cg * 32 + tx;
-  float acc = 0.f;
-  if (c < sg.C)
-    for (long long r = (long long)rb * 8 + ty; r < sg.rows; r += (long long)nrb * 8) acc += sg.src[(size_t)r * sg.C + c];
-  __shared__ float sm[8][33];
-  sm[ty][tx] = acc;
+  const int b = blockIdx.x - sg.first_block;
+  const int c4 = sg.C >> 2;                 // float4 columns per row
+  const long long total4 = sg.rows * c4;    // float4 elements
+  // thread t always visits the same column group: stride is a multiple of c4
+  long long stride = (long long)sg.nblk * 256;
+  stride = (stride + c4 - 1) / c4 * c4;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  long long i0 = (long long)b * 256 + threadIdx.x;
+  for (long long i = i0; i < total4; i += stride) {
+    float4 v = ld4(sg.src + 4 * i);
+    acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+  }
+  // combine threads of the block that share a column group through shared memory
+  __shared__ float4 sm[256];
+  sm[threadIdx.x] = acc;
   __syncthreads();
-  if (ty == 0 && c < sg.C) {
-    float t = 0.f;
-#pragma unroll
-    for (int k = 0; k < 8; ++k) t += sm[k][tx];
-    atomicAdd(sg.dst + c, t);
+  if ((int)threadIdx.x < c4) {
+    float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int k = threadIdx.x; k < 256; k += c4) { t.x += sm[k].x; t.y += sm[k].y; t.z += sm[k].z; t.w += sm[k].w; }
+    const int col = threadIdx.x;   // (b*256 + t) % c4 == t because 256 % c4 == 0
+    atomicAdd(sg.dst + 4 * col + 0, t.x);
+    atomicAdd(sg.dst + 4 * col + 1, t.y);
+    atomicAdd(sg.dst + 4 * col + 2, t.z);
+    atomicAdd(sg.dst + 4 * col + 3, t.w);
   }
 }
 
@@ -292,19 +325,41 @@ int mpit_multi_colsum(int nseg, const unsigned long long* srcs, const unsigned l
   a.nseg = nseg;
   int blocks = 0;
   for (int i = 0; i < nseg; ++i) {
+    if (cols[i] % 4 != 0 || 256 % (cols[i] / 4) != 0) return MPIT_E_ARG;
     a.seg[i].src = reinterpret_cast<const float*>(srcs[i]);
     a.seg[i].dst = reinterpret_cast<float*>(dsts[i]);
     a.seg[i].rows = rows[i];
     a.seg[i].C = cols[i];
     a.seg[i].first_block = blocks;
-    int cgroups = (cols[i] + 31) / 32;
-    long long rb = (rows[i] + 255) / 256;
-    if (rb > 64) rb = 64;
-    if (rb < 1) rb = 1;
-    blocks += cgroups * (int)rb;
+    long long total4 = rows[i] * (cols[i] / 4);
+    long long nb = (total4 + 256 * 8 - 1) / (256 * 8);   // ~8 float4 per thread
+    if (nb > 296) nb = 296;
+    if (nb < 1) nb = 1;
+    a.seg[i].nblk = (int)nb;
+    blocks += (int)nb;
     MPIT_CUDA_TRY(cudaMemsetAsync(a.seg[i].dst, 0, sizeof(float) * (size_t)cols[i], st));
   }
   multi_colsum_kernel<<<blocks, 256, 0, st>>>(a);
+  MPIT_LAUNCH_CHECK();
+  return 0;
+}
+
+// Split-K reduction of up to 8 layers in one launch; every array is a HOST array of nseg entries.
+int mpit_multi_wgrad_reduce(int nseg, const unsigned long long* parts, const unsigned long long* gws,
+                            const int* nsplit, const int* m_pad, const int* K, const int* N, void* stream) {
+  if (nseg < 1 || nseg > 8) return MPIT_E_ARG;
+  ReduceArgs a{};
+  a.nseg = nseg;
+  int blocks = 0;
+  for (int i = 0; i < nseg; ++i) {
+    a.seg[i].part = reinterpret_cast<const float*>(parts[i]);
+    a.seg[i].gw = reinterpret_cast<float*>(gws[i]);
+    a.seg[i].nsplit = nsplit[i]; a.seg[i].m_pad = m_pad[i]; a.seg[i].K = K[i]; a.seg[i].N = N[i];
+    a.seg[i].ldw = K[i];
+    a.seg[i].first_block = blocks;
+    blocks += (int)(((long long)K[i] * N[i] + 255) / 256);
+  }
+  multi_wgrad_reduce_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(a);
   MPIT_LAUNCH_CHECK();
   return 0;
 }

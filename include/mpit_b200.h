@@ -185,8 +185,11 @@ int mpit_wgrad_reduce(const float* part, float* gw, int nsplit, int m_pad, int K
 #define MPIT_NOALLOC_SCRATCH_FLOATS (2u * 1024u * 1024u)
 int mpit_umma_wgrad_noalloc(const void* tmap_x128, const void* tmap_dz128, const int* geom11, float* gw, int ldw,
                             const int* crop, int* err, int block_n, int nsplit, void* stream);
-/* Bias gradients (column sums) of up to 8 [rows][C] matrices in one launch; srcs/dsts/rows/cols are
- * HOST arrays. */
+/* mpit_multi_wgrad_reduce: the split-K reduction of up to 8 layers in ONE launch (HOST arrays of
+ * nseg entries).  mpit_multi_colsum: bias gradients (column sums) of up to 8 [rows][C] matrices in
+ * one launch; srcs/dsts/rows/cols are HOST arrays; C % 4 == 0 and 256 % (C/4) == 0. */
+int mpit_multi_wgrad_reduce(int nseg, const unsigned long long* parts, const unsigned long long* gws,
+                            const int* nsplit, const int* m_pad, const int* K, const int* N, void* stream);
 int mpit_multi_colsum(int nseg, const unsigned long long* srcs, const unsigned long long* dsts,
                       const long long* rows, const int* cols, void* stream);
 

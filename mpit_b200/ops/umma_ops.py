@@ -103,10 +103,10 @@ class CifarUmmaPlan:
             1.0, eng.b(0), act[0], idx[0], None, None, eng.crop, None, 64))
         # conv2
         self.fwd.append(IgemmLaunch(
-            nhwc_tmap(act[0], B, 12, 12, 64, 8, 8, 1), weight_tmap(w(1), L2.CO, 25 * 64, 64),
+            nhwc_tmap(act[0], B, 12, 12, 64, 8, 8, 1), weight_tmap(w(1), L2.CO, 25 * 64, 128),
             igemm_geom(nsub=2, tw=8, th=8, tn=1, tiles_w=1, tiles_h=1, kw_it=5, cb=2, num_kb=50, sgn=1, B=B,
                        OH=8, OW=8, N=128, mode=EPI_POOL, relu=1),
-            1.0, eng.b(1), act[1], idx[1], None, None, None, None, 64))
+            1.0, eng.b(1), act[1], idx[1], None, None, None, None, 128))
         # conv3
         self.fwd.append(IgemmLaunch(
             nhwc_tmap(act[1], B, 4, 4, 128, 2, 2, 32), weight_tmap(w(2), L3.CO, 9 * 128, 32),
@@ -142,16 +142,16 @@ class CifarUmmaPlan:
             1.0, None, dz[2], None, act[2], None, None, None, 32)
         # conv3: dz3 [B,2,2,64] -> d(a2) over 4x4 -> un-pool with idx2, mask a2 > 0 -> dz2 [B,8,8,128]
         self.dgrad[2] = IgemmLaunch(
-            nhwc_tmap(dz[2], B, 2, 2, 64, 4, 4, 8), weight_tmap(wd(2), 128, 9 * 64, 32),
+            nhwc_tmap(dz[2], B, 2, 2, 64, 4, 4, 8), weight_tmap(wd(2), 128, 9 * 64, 64),
             igemm_geom(nsub=1, tw=4, th=4, tn=8, tiles_w=1, tiles_h=1, kw_it=3, cb=2, num_kb=18, sgn=-1, B=B,
                        OH=4, OW=4, N=128, mode=EPI_EXPAND),
-            1.0, None, dz[1], None, act[1], idx[1], None, None, 32)
+            1.0, None, dz[1], None, act[1], idx[1], None, None, 64)
         # conv2: dz2 [B,8,8,128] -> d(a1) over 12x12 -> un-pool with idx1, mask -> dz1 [B,24,24,64]
         self.dgrad[1] = IgemmLaunch(
-            nhwc_tmap(dz[1], B, 8, 8, 128, 4, 4, 4), weight_tmap(wd(1), 64, 25 * 128, 32),
+            nhwc_tmap(dz[1], B, 8, 8, 128, 4, 4, 4), weight_tmap(wd(1), 64, 25 * 128, 64),
             igemm_geom(nsub=2, tw=4, th=4, tn=4, tiles_w=3, tiles_h=3, kw_it=5, cb=4, num_kb=100, sgn=-1, B=B,
                        OH=12, OW=12, N=64, mode=EPI_EXPAND),
-            1.0, None, dz[0], None, act[0], idx[0], None, None, 32)
+            1.0, None, dz[0], None, act[0], idx[0], None, None, 64)
 
         self.wgrad = None
         if wgrad != "ref":

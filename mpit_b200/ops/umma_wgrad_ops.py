@@ -62,8 +62,13 @@ class CifarWgradPlan:
             off += ns * m_pad * N
         # split-K scratch workspace shared by all layers
         self.part = torch.empty(off, dtype=torch.float32, device=eng.dev)
+        n = len(self.launches)
+        ls = self.launches
+        self._red = ((ctypes.c_ulonglong * n)(*[self.part.data_ptr() + 4 * l.part_off for l in ls]),
+                     (ctypes.c_ulonglong * n)(*[l.gw.data_ptr() for l in ls]),
+                     (ctypes.c_int * n)(*[l.nsplit for l in ls]), (ctypes.c_int * n)(*[l.m_pad for l in ls]),
+                     (ctypes.c_int * n)(*[l.K for l in ls]), (ctypes.c_int * n)(*[l.N for l in ls]))
         L = eng.layers
-        n = len(L)
         self._cs = ((ctypes.c_ulonglong * n)(*[dz[i].data_ptr() for i in range(n)]),
                     (ctypes.c_ulonglong * n)(*[eng.gb(i).data_ptr() for i in range(n)]),
                     (ctypes.c_longlong * n)(*[B * L[i].out_hw * L[i].out_hw for i in range(n)]),
@@ -75,9 +80,12 @@ class CifarWgradPlan:
         part = self.part[l.part_off:]
         check(k.mpit_umma_wgrad(l.tmap_x, l.tmap_dz, l.geom, ptr(part), ptr(l.crop), ptr(self.err), l.block_n,
                                 l.nsplit, cur_stream()), "mpit_umma_wgrad")
-        check(k.mpit_wgrad_reduce(ptr(part), ptr(l.gw), l.nsplit, l.m_pad, l.K, l.N, l.K, cur_stream()),
-              "mpit_wgrad_reduce")
-        if i == 0:   # last layer of the backward sweep: all dz are final, sum every bias gradient at once
+        if i == 0:
+            # last layer of the backward sweep: every partial and every dz is final -> one launch sums
+            # the split-K partials of all layers, one more sums every bias gradient
             n = len(self.launches)
+            r = self._red
+            check(k.mpit_multi_wgrad_reduce(n, r[0], r[1], r[2], r[3], r[4], r[5], cur_stream()),
+                  "mpit_multi_wgrad_reduce")
             check(k.mpit_multi_colsum(n, self._cs[0], self._cs[1], self._cs[2], self._cs[3], cur_stream()),
                   "mpit_multi_colsum")
