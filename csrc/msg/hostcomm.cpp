@@ -1,0 +1,1242 @@
+// Host message layer: tagged point-to-point messages, communicators and collectives over TCP, with
+// a progress thread.  Written from scratch for mpit_b200; the API shape (error-code returns,
+// caller-owned buffers, integer handles) follows what the reference exposes to Lua from MPI
+// (/root/reference/lua-mpi.h:80-121,235-297; /root/reference/mpifuncs.c), so that the coroutine IO
+// layer (aio_send / aio_recv: /root/reference/init.lua:41-108) can be re-built on top of it with the
+// same Isend / Iprobe / Irecv / Test / Cancel state machine.
+//
+// Design
+//  * One TCP connection per rank pair (full mesh), established at init through a rendezvous on
+//    rank 0.  A single progress thread per process owns all socket IO (poll + non-blocking
+//    read/write); user threads only touch queues under one mutex and sleep on one condition
+//    variable.  Unlike the reference, where progress only happens while Lua polls MPI_Test
+//    (/root/reference/init.lua:185-192), transfers advance in the background.
+//  * Matching is MPI's: per (source, communicator) non-overtaking, posted-receive list searched in
+//    post order, unexpected-message list searched in arrival order, wildcards for source and tag.
+//    A message whose header has arrived is visible to Iprobe even if its payload is still in flight.
+//  * Cancel has real semantics (the reference leaks a posted receive at shutdown,
+//    /root/reference/init.lua:88-90): a receive that is still unmatched or a send that has not begun
+//    to hit the wire is withdrawn and reports cancelled; anything further along completes.
+//  * Collectives are built on the same transport with a reserved communicator id bit, binomial
+//    trees for bcast/reduce, and a helper thread for the non-blocking all-reduce.
+#include "mpit_msg.h"
+
+#include <arpa/inet.h>
+#include <errno.h>
+#include <fcntl.h>
+#include <netdb.h>
+#include <netinet/in.h>
+#include <netinet/tcp.h>
+#include <poll.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <sys/eventfd.h>
+#include <sys/socket.h>
+#include <time.h>
+#include <unistd.h>
+
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <condition_variable>
+#include <deque>
+#include <list>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <thread>
+#include <vector>
+
+namespace {
+
+constexpr int kCollBit = 0x40000000;   // communicator id bit reserved for collective traffic
+constexpr int kNbcBit = 0x20000000;    // ... and for non-blocking collectives
+
+struct Frame {
+  int32_t tag;
+  int32_t comm;
+  int64_t nbytes;
+};
+
+enum ReqKind { REQ_SEND, REQ_RECV, REQ_COLL };
+
+struct Req {
+  int id = -1;
+  ReqKind kind = REQ_SEND;
+  bool done = false;
+  bool cancelled = false;
+  bool started = false;       // send: first byte handed to the socket
+  int peer = -1;              // world rank (send: destination, recv: source or ANY)
+  int tag = 0;
+  int comm = 0;               // wire communicator id
+  void* buf = nullptr;
+  size_t cap = 0;             // bytes
+  // completion info
+  int src_world = -1;
+  int src_tag = 0;
+  size_t got = 0;
+  int error = MPIT_SUCCESS;
+  std::thread worker;         // REQ_COLL
+};
+
+struct Unexpected {
+  int src;                    // world rank
+  int tag;
+  int comm;
+  std::vector<char> data;
+  size_t got = 0;
+  bool complete = false;
+  Req* claimed = nullptr;     // receive that matched while the payload was still arriving
+};
+
+struct SendItem {
+  Req* req;                   // may be null for internal fire-and-forget (not used)
+  Frame hdr;
+  const char* payload;
+  size_t off = 0;             // bytes of (hdr + payload) already written
+};
+
+struct Peer {
+  int fd = -1;
+  std::deque<SendItem> sendq;
+  // receive state machine
+  Frame hdr{};
+  size_t hdr_got = 0;
+  bool in_body = false;
+  Req* rreq = nullptr;        // direct delivery target
+  Unexpected* runx = nullptr; // or unexpected buffer
+  size_t body_got = 0;
+  size_t body_len = 0;
+  size_t deliver_cap = 0;
+};
+
+struct Comm {
+  int id;                     // wire id (unique among live communicators on its members)
+  std::vector<int> ranks;     // world ranks of members, index = rank in comm
+  int my = -1;                // my rank in this comm
+  int split_seq = 0;
+  unsigned nbc_seq = 0;
+};
+
+struct State {
+  bool inited = false;
+  int rank = 0, size = 1;
+  std::vector<Peer> peers;
+  std::mutex mu;
+  std::condition_variable cv;
+  std::thread progress;
+  std::atomic<bool> stop{false};
+  int wake_fd = -1;
+  std::map<int, std::unique_ptr<Req>> reqs;
+  int next_req = 1;
+  std::list<Req*> posted;
+  std::list<std::unique_ptr<Unexpected>> unexpected;
+  std::map<int, Comm> comms;   // handle -> comm
+  int next_comm = 2;
+  long long stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+};
+
+State g;
+
+size_t dtype_size(int dt) {
+  switch (dt) {
+    case MPIT_BYTE: case MPIT_CHAR: case MPIT_UNSIGNED_CHAR: return 1;
+    case MPIT_SHORT: return 2;
+    case MPIT_INT: case MPIT_FLOAT: case MPIT_UNSIGNED: return 4;
+    case MPIT_LONG: case MPIT_DOUBLE: case MPIT_LONG_LONG: return 8;
+    default: return 0;
+  }
+}
+
+void set_nonblock(int fd) {
+  int fl = fcntl(fd, F_GETFL, 0);
+  fcntl(fd, F_SETFL, fl | O_NONBLOCK);
+}
+void set_nodelay(int fd) {
+  int one = 1;
+  setsockopt(fd, IPPROTO_TCP, TCP_NODELAY, &one, sizeof(one));
+  int sz = 4 << 20;
+  setsockopt(fd, SOL_SOCKET, SO_SNDBUF, &sz, sizeof(sz));
+  setsockopt(fd, SOL_SOCKET, SO_RCVBUF, &sz, sizeof(sz));
+}
+
+bool write_all(int fd, const void* p, size_t n) {
+  const char* c = static_cast<const char*>(p);
+  while (n) {
+    ssize_t k = ::write(fd, c, n);
+    if (k < 0) { if (errno == EINTR) continue; return false; }
+    c += k; n -= (size_t)k;
+  }
+  return true;
+}
+bool read_all(int fd, void* p, size_t n) {
+  char* c = static_cast<char*>(p);
+  while (n) {
+    ssize_t k = ::read(fd, c, n);
+    if (k < 0) { if (errno == EINTR) continue; return false; }
+    if (k == 0) return false;
+    c += k; n -= (size_t)k;
+  }
+  return true;
+}
+
+void wake() {
+  uint64_t one = 1;
+  if (g.wake_fd >= 0) { ssize_t r = ::write(g.wake_fd, &one, sizeof(one)); (void)r; }
+}
+
+bool match(int want_src, int want_tag, int want_comm, int src, int tag, int comm) {
+  return want_comm == comm && (want_src == MPIT_ANY_SOURCE || want_src == src) &&
+         (want_tag == MPIT_ANY_TAG || want_tag == tag);
+}
+
+void complete_recv(Req* r, int src, int tag, size_t nbytes) {
+  r->src_world = src;
+  r->src_tag = tag;
+  r->got = std::min(nbytes, r->cap);
+  if (nbytes > r->cap) r->error = MPIT_ERR_TRUNCATE;
+  r->done = true;
+  g.stats[2]++;
+  g.stats[3] += (long long)nbytes;
+}
+
+// A header from `src` has been read: choose where the payload goes.  Caller holds g.mu.
+void route_incoming(Peer& p, int src) {
+  p.in_body = true;
+  p.body_got = 0;
+  p.body_len = (size_t)p.hdr.nbytes;
+  p.rreq = nullptr;
+  p.runx = nullptr;
+  for (auto it = g.posted.begin(); it != g.posted.end(); ++it) {
+    Req* r = *it;
+    if (match(r->peer, r->tag, r->comm, src, p.hdr.tag, p.hdr.comm)) {
+      g.posted.erase(it);
+      p.rreq = r;
+      p.deliver_cap = r->cap;
+      return;
+    }
+  }
+  auto u = std::make_unique<Unexpected>();
+  u->src = src; u->tag = p.hdr.tag; u->comm = p.hdr.comm;
+  u->data.resize(p.body_len);
+  p.runx = u.get();
+  g.unexpected.push_back(std::move(u));
+}
+
+void finish_incoming(Peer& p, int src) {
+  if (p.rreq) {
+    complete_recv(p.rreq, src, p.hdr.tag, p.body_len);
+  } else if (p.runx) {
+    Unexpected* u = p.runx;
+    u->complete = true;
+    u->got = p.body_len;
+    if (u->claimed) {
+      Req* r = u->claimed;
+      memcpy(r->buf, u->data.data(), std::min(r->cap, u->data.size()));
+      complete_recv(r, u->src, u->tag, u->data.size());
+      for (auto it = g.unexpected.begin(); it != g.unexpected.end(); ++it)
+        if (it->get() == u) { g.unexpected.erase(it); break; }
+    }
+  }
+  p.in_body = false;
+  p.hdr_got = 0;
+  p.rreq = nullptr;
+  p.runx = nullptr;
+}
+
+// Non-blocking drain of one peer socket.  Caller holds g.mu.  Returns false on a dead connection.
+bool pump_recv(int src) {
+  Peer& p = g.peers[src];
+  for (;;) {
+    if (!p.in_body) {
+      ssize_t k = ::read(p.fd, reinterpret_cast<char*>(&p.hdr) + p.hdr_got, sizeof(Frame) - p.hdr_got);
+      if (k < 0) return errno == EAGAIN || errno == EWOULDBLOCK || errno == EINTR;
+      if (k == 0) return false;
+      p.hdr_got += (size_t)k;
+      if (p.hdr_got < sizeof(Frame)) return true;
+      route_incoming(p, src);
+      if (p.body_len == 0) { finish_incoming(p, src); g.cv.notify_all(); continue; }
+      g.cv.notify_all();   // header visible to probes
+    }
+    char* dst;
+    size_t want = p.body_len - p.body_got;
+    static thread_local std::vector<char> sink;
+    if (p.rreq) {
+      if (p.body_got < p.deliver_cap) {
+        dst = static_cast<char*>(p.rreq->buf) + p.body_got;
+        want = std::min(want, p.deliver_cap - p.body_got);
+      } else {   // truncated message: discard the tail
+        sink.resize(1 << 16);
+        dst = sink.data();
+        want = std::min(want, sink.size());
+      }
+    } else {
+      dst = p.runx->data.data() + p.body_got;
+    }
+    ssize_t k = ::read(p.fd, dst, want);
+    if (k < 0) return errno == EAGAIN || errno == EWOULDBLOCK || errno == EINTR;
+    if (k == 0) return false;
+    p.body_got += (size_t)k;
+    if (p.body_got == p.body_len) { finish_incoming(p, src); g.cv.notify_all(); }
+  }
+}
+
+bool pump_send(int dst) {
+  Peer& p = g.peers[dst];
+  while (!p.sendq.empty()) {
+    SendItem& it = p.sendq.front();
+    size_t total = sizeof(Frame) + (size_t)it.hdr.nbytes;
+    while (it.off < total) {
+      const char* src;
+      size_t n;
+      if (it.off < sizeof(Frame)) {
+        src = reinterpret_cast<const char*>(&it.hdr) + it.off;
+        n = sizeof(Frame) - it.off;
+      } else {
+        src = it.payload + (it.off - sizeof(Frame));
+        n = total - it.off;
+      }
+      ssize_t k = ::send(p.fd, src, n, MSG_NOSIGNAL);
+      if (k < 0) {
+        if (errno == EAGAIN || errno == EWOULDBLOCK || errno == EINTR) return true;
+        return false;
+      }
+      if (it.req) it.req->started = true;
+      it.off += (size_t)k;
+    }
+    if (it.req) { it.req->done = true; }
+    g.stats[0]++;
+    g.stats[1] += it.hdr.nbytes;
+    p.sendq.pop_front();
+    g.cv.notify_all();
+  }
+  return true;
+}
+
+void progress_loop() {
+  std::vector<pollfd> pfds;
+  while (!g.stop.load()) {
+    pfds.clear();
+    {
+      std::lock_guard<std::mutex> lk(g.mu);
+      for (int r = 0; r < g.size; ++r) {
+        if (r == g.rank || g.peers[r].fd < 0) continue;
+        pollfd pf{};
+        pf.fd = g.peers[r].fd;
+        pf.events = POLLIN | (g.peers[r].sendq.empty() ? 0 : POLLOUT);
+        pfds.push_back(pf);
+      }
+    }
+    pollfd w{};
+    w.fd = g.wake_fd;
+    w.events = POLLIN;
+    pfds.push_back(w);
+    int n = ::poll(pfds.data(), pfds.size(), 100);
+    if (n <= 0) continue;
+    if (pfds.back().revents & POLLIN) {
+      uint64_t v;
+      ssize_t r = ::read(g.wake_fd, &v, sizeof(v));
+      (void)r;
+    }
+    std::lock_guard<std::mutex> lk(g.mu);
+    size_t i = 0;
+    for (int r = 0; r < g.size; ++r) {
+      if (r == g.rank || g.peers[r].fd < 0) continue;
+      short ev = pfds[i++].revents;
+      if (ev & (POLLIN | POLLHUP | POLLERR)) {
+        if (!pump_recv(r)) { ::close(g.peers[r].fd); g.peers[r].fd = -1; g.cv.notify_all(); continue; }
+      }
+      if (!g.peers[r].sendq.empty()) {
+        if (!pump_send(r)) { ::close(g.peers[r].fd); g.peers[r].fd = -1; g.cv.notify_all(); }
+      }
+    }
+  }
+}
+
+Req* new_req(ReqKind kind) {
+  auto r = std::make_unique<Req>();
+  r->id = g.next_req++;
+  r->kind = kind;
+  Req* raw = r.get();
+  g.reqs[raw->id] = std::move(r);
+  return raw;
+}
+
+Comm* find_comm(int h) {
+  auto it = g.comms.find(h);
+  return it == g.comms.end() ? nullptr : &it->second;
+}
+
+void fill_status(mpit_status* st, const Req* r, const Comm* c) {
+  if (!st) return;
+  int src = r->src_world;
+  if (c && src >= 0) {
+    auto it = std::find(c->ranks.begin(), c->ranks.end(), src);
+    src = it == c->ranks.end() ? src : (int)(it - c->ranks.begin());
+  }
+  st->source = src;
+  st->tag = r->src_tag;
+  st->error = r->error;
+  st->count_bytes = (long long)r->got;
+  st->cancelled = r->cancelled ? 1 : 0;
+}
+
+// ---- core p2p on wire ids (caller holds no lock) ------------------------------------------------
+int isend_wire(const void* buf, size_t nbytes, int dst_world, int tag, int wire_comm, Req** out) {
+  std::unique_lock<std::mutex> lk(g.mu);
+  Req* r = new_req(REQ_SEND);
+  r->peer = dst_world; r->tag = tag; r->comm = wire_comm;
+  r->buf = const_cast<void*>(buf); r->cap = nbytes;
+  if (dst_world == g.rank) {
+    // loop-back: deliver straight into a posted receive or the unexpected list
+    bool delivered = false;
+    for (auto it = g.posted.begin(); it != g.posted.end(); ++it) {
+      Req* q = *it;
+      if (match(q->peer, q->tag, q->comm, g.rank, tag, wire_comm)) {
+        g.posted.erase(it);
+        memcpy(q->buf, buf, std::min(nbytes, q->cap));
+        complete_recv(q, g.rank, tag, nbytes);
+        delivered = true;
+        break;
+      }
+    }
+    if (!delivered) {
+      auto u = std::make_unique<Unexpected>();
+      u->src = g.rank; u->tag = tag; u->comm = wire_comm;
+      u->data.assign(static_cast<const char*>(buf), static_cast<const char*>(buf) + nbytes);
+      u->complete = true; u->got = nbytes;
+      g.unexpected.push_back(std::move(u));
+    }
+    r->started = true;
+    r->done = true;
+    g.stats[0]++; g.stats[1] += (long long)nbytes;
+    g.cv.notify_all();
+  } else {
+    if (g.peers[dst_world].fd < 0) { r->error = MPIT_ERR_OTHER; r->done = true; *out = r; return MPIT_ERR_OTHER; }
+    SendItem it{};
+    it.req = r;
+    it.hdr.tag = tag; it.hdr.comm = wire_comm; it.hdr.nbytes = (int64_t)nbytes;
+    it.payload = static_cast<const char*>(buf);
+    g.peers[dst_world].sendq.push_back(it);
+    lk.unlock();
+    wake();
+  }
+  *out = r;
+  return MPIT_SUCCESS;
+}
+
+int irecv_wire(void* buf, size_t cap, int src_world, int tag, int wire_comm, Req** out) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  Req* r = new_req(REQ_RECV);
+  r->peer = src_world; r->tag = tag; r->comm = wire_comm; r->buf = buf; r->cap = cap;
+  for (auto it = g.unexpected.begin(); it != g.unexpected.end(); ++it) {
+    Unexpected* u = it->get();
+    if (u->claimed || !match(src_world, tag, wire_comm, u->src, u->tag, u->comm)) continue;
+    if (u->complete) {
+      memcpy(buf, u->data.data(), std::min(cap, u->data.size()));
+      complete_recv(r, u->src, u->tag, u->data.size());
+      g.unexpected.erase(it);
+      g.cv.notify_all();
+    } else {
+      u->claimed = r;   // payload still arriving: deliver on completion
+    }
+    *out = r;
+    return MPIT_SUCCESS;
+  }
+  g.posted.push_back(r);
+  *out = r;
+  return MPIT_SUCCESS;
+}
+
+int wait_req(Req* r) {
+  std::unique_lock<std::mutex> lk(g.mu);
+  g.cv.wait(lk, [&] { return r->done; });
+  return r->error;
+}
+
+void free_req_locked(int id) {
+  auto it = g.reqs.find(id);
+  if (it == g.reqs.end()) return;
+  if (it->second->worker.joinable()) it->second->worker.detach();
+  g.reqs.erase(it);
+}
+
+int send_wire_blocking(const void* buf, size_t n, int dst_world, int tag, int wire_comm) {
+  Req* r;
+  int rc = isend_wire(buf, n, dst_world, tag, wire_comm, &r);
+  if (rc) return rc;
+  rc = wait_req(r);
+  std::lock_guard<std::mutex> lk(g.mu);
+  free_req_locked(r->id);
+  return rc;
+}
+int recv_wire_blocking(void* buf, size_t cap, int src_world, int tag, int wire_comm, size_t* got = nullptr) {
+  Req* r;
+  int rc = irecv_wire(buf, cap, src_world, tag, wire_comm, &r);
+  if (rc) return rc;
+  rc = wait_req(r);
+  if (got) *got = r->got;
+  std::lock_guard<std::mutex> lk(g.mu);
+  free_req_locked(r->id);
+  return rc;
+}
+
+// ---- reductions -------------------------------------------------------------------------------------
+template <typename T>
+void reduce_typed(T* acc, const T* in, size_t n, int op) {
+  switch (op) {
+    case MPIT_SUM: for (size_t i = 0; i < n; ++i) acc[i] = acc[i] + in[i]; break;
+    case MPIT_PROD: for (size_t i = 0; i < n; ++i) acc[i] = acc[i] * in[i]; break;
+    case MPIT_MAX: for (size_t i = 0; i < n; ++i) acc[i] = std::max(acc[i], in[i]); break;
+    case MPIT_MIN: for (size_t i = 0; i < n; ++i) acc[i] = std::min(acc[i], in[i]); break;
+    case MPIT_LAND: for (size_t i = 0; i < n; ++i) acc[i] = (T)((acc[i] != 0) && (in[i] != 0)); break;
+    case MPIT_LOR: for (size_t i = 0; i < n; ++i) acc[i] = (T)((acc[i] != 0) || (in[i] != 0)); break;
+    default: break;
+  }
+}
+template <typename T>
+void reduce_bits(T* acc, const T* in, size_t n, int op) {
+  if (op == MPIT_BAND) for (size_t i = 0; i < n; ++i) acc[i] = acc[i] & in[i];
+  else if (op == MPIT_BOR) for (size_t i = 0; i < n; ++i) acc[i] = acc[i] | in[i];
+  else reduce_typed(acc, in, n, op);
+}
+int reduce_into(void* acc, const void* in, size_t n, int dt, int op) {
+  if ((op == MPIT_BAND || op == MPIT_BOR) && (dt == MPIT_FLOAT || dt == MPIT_DOUBLE)) return MPIT_ERR_OP;
+  switch (dt) {
+    case MPIT_BYTE: case MPIT_UNSIGNED_CHAR: reduce_bits((uint8_t*)acc, (const uint8_t*)in, n, op); break;
+    case MPIT_CHAR: reduce_bits((int8_t*)acc, (const int8_t*)in, n, op); break;
+    case MPIT_SHORT: reduce_bits((int16_t*)acc, (const int16_t*)in, n, op); break;
+    case MPIT_INT: reduce_bits((int32_t*)acc, (const int32_t*)in, n, op); break;
+    case MPIT_UNSIGNED: reduce_bits((uint32_t*)acc, (const uint32_t*)in, n, op); break;
+    case MPIT_LONG: case MPIT_LONG_LONG: reduce_bits((int64_t*)acc, (const int64_t*)in, n, op); break;
+    case MPIT_FLOAT: reduce_typed((float*)acc, (const float*)in, n, op); break;
+    case MPIT_DOUBLE: reduce_typed((double*)acc, (const double*)in, n, op); break;
+    default: return MPIT_ERR_TYPE;
+  }
+  return MPIT_SUCCESS;
+}
+
+// ---- collectives on (ranks, me, wire id) ------------------------------------------------------------
+struct Group { std::vector<int> ranks; int me; int wire; };
+
+bool group_of(int comm, int extra_bit, Group* out) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  Comm* c = find_comm(comm);
+  if (!c) return false;
+  out->ranks = c->ranks; out->me = c->my; out->wire = c->id | extra_bit;
+  return true;
+}
+
+int coll_bcast(const Group& G, void* buf, size_t nbytes, int root, int tag) {
+  int n = (int)G.ranks.size();
+  if (n == 1) return MPIT_SUCCESS;
+  int rel = (G.me - root + n) % n;
+  int mask = 1;
+  while (mask < n) {
+    if (rel & mask) {
+      int src = (rel - mask + root) % n;
+      int rc = recv_wire_blocking(buf, nbytes, G.ranks[src], tag, G.wire);
+      if (rc) return rc;
+      break;
+    }
+    mask <<= 1;
+  }
+  mask >>= 1;
+  while (mask > 0) {
+    if (rel + mask < n) {
+      int dst = (rel + mask + root) % n;
+      int rc = send_wire_blocking(buf, nbytes, G.ranks[dst], tag, G.wire);
+      if (rc) return rc;
+    }
+    mask >>= 1;
+  }
+  return MPIT_SUCCESS;
+}
+
+// Binomial-tree reduction to `root`; `acc` must hold this rank's contribution on entry.
+int coll_reduce(const Group& G, void* acc, size_t count, int dt, int op, int root, int tag) {
+  int n = (int)G.ranks.size();
+  if (n == 1) return MPIT_SUCCESS;
+  size_t nbytes = count * dtype_size(dt);
+  std::vector<char> tmp(nbytes);
+  int rel = (G.me - root + n) % n;
+  int mask = 1;
+  while (mask < n) {
+    if (rel & mask) {
+      int dst = (rel - mask + root) % n;
+      return send_wire_blocking(acc, nbytes, G.ranks[dst], tag, G.wire);
+    }
+    int partner = rel + mask;
+    if (partner < n) {
+      int src = (partner + root) % n;
+      int rc = recv_wire_blocking(tmp.data(), nbytes, G.ranks[src], tag, G.wire);
+      if (rc) return rc;
+      rc = reduce_into(acc, tmp.data(), count, dt, op);
+      if (rc) return rc;
+    }
+    mask <<= 1;
+  }
+  return MPIT_SUCCESS;
+}
+
+int coll_allreduce(const Group& G, const void* sbuf, void* rbuf, size_t count, int dt, int op, int tag) {
+  size_t nbytes = count * dtype_size(dt);
+  if (sbuf != rbuf && sbuf) memcpy(rbuf, sbuf, nbytes);
+  int rc = coll_reduce(G, rbuf, count, dt, op, 0, tag);
+  if (rc) return rc;
+  return coll_bcast(G, rbuf, nbytes, 0, tag + 1);
+}
+
+int coll_barrier(const Group& G, int tag) {
+  char z = 0;
+  return coll_allreduce(G, &z, &z, 1, MPIT_BYTE, MPIT_BOR, tag);
+}
+
+bool valid_p2p(const Comm* c, int peer, bool allow_any) {
+  if (!c) return false;
+  if (allow_any && peer == MPIT_ANY_SOURCE) return true;
+  return peer >= 0 && peer < (int)c->ranks.size();
+}
+
+}  // namespace
+
+extern "C" {
+
+// ---- environment ------------------------------------------------------------------------------------
+int mpit_msg_init(int rank, int size, const char* master_addr, int master_port, int thread_level,
+                  int* provided) {
+  std::unique_lock<std::mutex> lk(g.mu);
+  if (g.inited) return MPIT_ERR_OTHER;
+  if (size < 1 || rank < 0 || rank >= size) return MPIT_ERR_ARG;
+  (void)thread_level;
+  if (provided) *provided = 3;
+  g.rank = rank; g.size = size;
+  g.peers.assign(size, Peer{});
+  g.stop = false;
+  g.wake_fd = eventfd(0, EFD_NONBLOCK);
+  g.comms.clear();
+  Comm world; world.id = MPIT_COMM_WORLD; world.my = rank;
+  for (int i = 0; i < size; ++i) world.ranks.push_back(i);
+  g.comms[MPIT_COMM_WORLD] = world;
+  Comm self; self.id = MPIT_COMM_SELF; self.my = 0; self.ranks = {rank};
+  g.comms[MPIT_COMM_SELF] = self;
+  g.next_comm = 2;
+
+  if (size > 1) {
+    // my listening socket (ephemeral port)
+    int lfd = ::socket(AF_INET, SOCK_STREAM, 0);
+    int one = 1;
+    setsockopt(lfd, SOL_SOCKET, SO_REUSEADDR, &one, sizeof(one));
+    sockaddr_in la{};
+    la.sin_family = AF_INET;
+    la.sin_addr.s_addr = htonl(INADDR_ANY);
+    la.sin_port = htons(rank == 0 ? (uint16_t)master_port : 0);
+    if (::bind(lfd, (sockaddr*)&la, sizeof(la)) != 0) { ::close(lfd); return MPIT_ERR_OTHER; }
+    ::listen(lfd, size + 8);
+    socklen_t sl = sizeof(la);
+    getsockname(lfd, (sockaddr*)&la, &sl);
+    int my_port = ntohs(la.sin_port);
+
+    std::vector<uint32_t> addrs(size, 0);
+    std::vector<int32_t> ports(size, 0);
+    sockaddr_in ma{};
+    ma.sin_family = AF_INET;
+    ma.sin_port = htons((uint16_t)master_port);
+    if (inet_pton(AF_INET, master_addr ? master_addr : "127.0.0.1", &ma.sin_addr) != 1) {
+      hostent* he = gethostbyname(master_addr);
+      if (!he) { ::close(lfd); return MPIT_ERR_OTHER; }
+      memcpy(&ma.sin_addr, he->h_addr_list[0], sizeof(in_addr));
+    }
+    if (rank == 0) {
+      // gather (rank, port, addr) from everyone, then broadcast the table
+      std::vector<int> cfds(size, -1);
+      ports[0] = my_port;
+      addrs[0] = ma.sin_addr.s_addr;
+      for (int i = 1; i < size; ++i) {
+        sockaddr_in pa{};
+        socklen_t pl = sizeof(pa);
+        int fd = ::accept(lfd, (sockaddr*)&pa, &pl);
+        if (fd < 0) { ::close(lfd); return MPIT_ERR_OTHER; }
+        int32_t hello[2];
+        if (!read_all(fd, hello, sizeof(hello)) || hello[0] <= 0 || hello[0] >= size) { ::close(lfd); return MPIT_ERR_OTHER; }
+        cfds[hello[0]] = fd;
+        ports[hello[0]] = hello[1];
+        addrs[hello[0]] = pa.sin_addr.s_addr;
+      }
+      for (int i = 1; i < size; ++i) {
+        write_all(cfds[i], ports.data(), sizeof(int32_t) * size);
+        write_all(cfds[i], addrs.data(), sizeof(uint32_t) * size);
+        g.peers[i].fd = cfds[i];   // the rendezvous connection becomes the data connection 0 <-> i
+      }
+    } else {
+      int fd = -1;
+      for (int attempt = 0; attempt < 600; ++attempt) {   // rank 0 may not be listening yet
+        fd = ::socket(AF_INET, SOCK_STREAM, 0);
+        if (::connect(fd, (sockaddr*)&ma, sizeof(ma)) == 0) break;
+        ::close(fd);
+        fd = -1;
+        usleep(100 * 1000);
+      }
+      if (fd < 0) { ::close(lfd); return MPIT_ERR_OTHER; }
+      int32_t hello[2] = {rank, my_port};
+      write_all(fd, hello, sizeof(hello));
+      if (!read_all(fd, ports.data(), sizeof(int32_t) * size) || !read_all(fd, addrs.data(), sizeof(uint32_t) * size)) {
+        ::close(lfd);
+        return MPIT_ERR_OTHER;
+      }
+      g.peers[0].fd = fd;
+      // mesh among ranks >= 1: connect to lower ranks, accept from higher ranks
+      for (int j = 1; j < rank; ++j) {
+        sockaddr_in pa{};
+        pa.sin_family = AF_INET;
+        pa.sin_port = htons((uint16_t)ports[j]);
+        pa.sin_addr.s_addr = addrs[j];
+        int cfd = ::socket(AF_INET, SOCK_STREAM, 0);
+        if (::connect(cfd, (sockaddr*)&pa, sizeof(pa)) != 0) { ::close(lfd); return MPIT_ERR_OTHER; }
+        int32_t me = rank;
+        write_all(cfd, &me, sizeof(me));
+        g.peers[j].fd = cfd;
+      }
+    }
+    if (rank >= 1) {
+      for (int k = rank + 1; k < size; ++k) {
+        int fd = ::accept(lfd, nullptr, nullptr);
+        if (fd < 0) { ::close(lfd); return MPIT_ERR_OTHER; }
+        int32_t who = -1;
+        if (!read_all(fd, &who, sizeof(who)) || who <= rank || who >= size) { ::close(lfd); return MPIT_ERR_OTHER; }
+        g.peers[who].fd = fd;
+      }
+    }
+    ::close(lfd);
+    for (int i = 0; i < size; ++i)
+      if (g.peers[i].fd >= 0) { set_nodelay(g.peers[i].fd); set_nonblock(g.peers[i].fd); }
+  }
+  g.inited = true;
+  g.progress = std::thread(progress_loop);
+  return MPIT_SUCCESS;
+}
+
+int mpit_msg_initialized(int* flag) { *flag = g.inited ? 1 : 0; return MPIT_SUCCESS; }
+
+int mpit_msg_finalize(void) {
+  if (!g.inited) return MPIT_ERR_OTHER;
+  {
+    // flush outstanding sends
+    std::unique_lock<std::mutex> lk(g.mu);
+    g.cv.wait_for(lk, std::chrono::seconds(10), [&] {
+      for (auto& p : g.peers) if (p.fd >= 0 && !p.sendq.empty()) return false;
+      return true;
+    });
+  }
+  g.stop = true;
+  wake();
+  if (g.progress.joinable()) g.progress.join();
+  std::lock_guard<std::mutex> lk(g.mu);
+  for (auto& p : g.peers) if (p.fd >= 0) { ::shutdown(p.fd, SHUT_RDWR); ::close(p.fd); p.fd = -1; }
+  if (g.wake_fd >= 0) { ::close(g.wake_fd); g.wake_fd = -1; }
+  for (auto& kv : g.reqs) if (kv.second->worker.joinable()) kv.second->worker.detach();
+  g.reqs.clear();
+  g.posted.clear();
+  g.unexpected.clear();
+  g.comms.clear();
+  g.inited = false;
+  return MPIT_SUCCESS;
+}
+
+int mpit_msg_abort(int comm, int errorcode) {
+  (void)comm;
+  fprintf(stderr, "mpit_msg_abort: rank %d aborting with code %d\n", g.rank, errorcode);
+  _exit(errorcode ? errorcode : 1);
+}
+
+double mpit_msg_wtime(void) {
+  timespec ts;
+  clock_gettime(CLOCK_MONOTONIC, &ts);
+  return (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec;
+}
+double mpit_msg_wtick(void) {
+  timespec ts;
+  clock_getres(CLOCK_MONOTONIC, &ts);
+  return (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec;
+}
+int mpit_msg_get_processor_name(char* name64, int* resultlen) {
+  if (gethostname(name64, 63) != 0) strcpy(name64, "localhost");
+  name64[63] = 0;
+  if (resultlen) *resultlen = (int)strlen(name64);
+  return MPIT_SUCCESS;
+}
+int mpit_msg_type_size(int dtype, int* size) {
+  size_t s = dtype_size(dtype);
+  if (!s) return MPIT_ERR_TYPE;
+  *size = (int)s;
+  return MPIT_SUCCESS;
+}
+
+// ---- communicators ------------------------------------------------------------------------------------
+int mpit_msg_comm_rank(int comm, int* rank) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  Comm* c = find_comm(comm);
+  if (!c) return MPIT_ERR_COMM;
+  *rank = c->my;
+  return MPIT_SUCCESS;
+}
+int mpit_msg_comm_size(int comm, int* size) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  Comm* c = find_comm(comm);
+  if (!c) return MPIT_ERR_COMM;
+  *size = (int)c->ranks.size();
+  return MPIT_SUCCESS;
+}
+
+int mpit_msg_comm_split(int comm, int color, int key, int* newcomm) {
+  Group G;
+  if (!group_of(comm, kCollBit, &G)) return MPIT_ERR_COMM;
+  int n = (int)G.ranks.size();
+  int seq;
+  int parent_id;
+  {
+    std::lock_guard<std::mutex> lk(g.mu);
+    Comm* c = find_comm(comm);
+    seq = c->split_seq++;
+    parent_id = c->id;
+  }
+  // allgather (color, key) by reduce-with-placement
+  std::vector<int32_t> mine(2 * n, 0), all(2 * n, 0);
+  mine[2 * G.me] = color;
+  mine[2 * G.me + 1] = key;
+  int rc = coll_allreduce(G, mine.data(), all.data(), 2 * n, MPIT_INT, MPIT_SUM, 100);
+  if (rc) return rc;
+  if (color == MPIT_UNDEFINED) { *newcomm = MPIT_COMM_NULL; return MPIT_SUCCESS; }
+  std::vector<int> colors;
+  for (int i = 0; i < n; ++i) if (all[2 * i] != MPIT_UNDEFINED) colors.push_back(all[2 * i]);
+  std::sort(colors.begin(), colors.end());
+  colors.erase(std::unique(colors.begin(), colors.end()), colors.end());
+  int cidx = (int)(std::find(colors.begin(), colors.end(), color) - colors.begin());
+  std::vector<std::pair<std::pair<int, int>, int>> members;   // ((key, old rank), world rank)
+  for (int i = 0; i < n; ++i)
+    if (all[2 * i] == color) members.push_back({{all[2 * i + 1], i}, G.ranks[i]});
+  std::sort(members.begin(), members.end());
+  Comm nc;
+  // wire id agreed without communication: every member derives it from the parent and the split
+  nc.id = ((((parent_id & 0xFFFF) * 131 + seq + 1) * 67 + cidx) & 0x0FFFFFFF) | 0x10000000;
+  for (auto& m : members) nc.ranks.push_back(m.second);
+  nc.my = (int)(std::find(nc.ranks.begin(), nc.ranks.end(), g.rank) - nc.ranks.begin());
+  std::lock_guard<std::mutex> lk(g.mu);
+  int h = g.next_comm++;
+  g.comms[h] = nc;
+  *newcomm = h;
+  return MPIT_SUCCESS;
+}
+
+int mpit_msg_comm_dup(int comm, int* newcomm) { return mpit_msg_comm_split(comm, 0, 0, newcomm); }
+
+int mpit_msg_comm_free(int* comm) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  if (*comm == MPIT_COMM_WORLD || *comm == MPIT_COMM_SELF) return MPIT_ERR_COMM;
+  g.comms.erase(*comm);
+  *comm = MPIT_COMM_NULL;
+  return MPIT_SUCCESS;
+}
+
+// ---- point to point ------------------------------------------------------------------------------------
+int mpit_msg_isend(const void* buf, long long count, int dtype, int dest, int tag, int comm, int* request) {
+  size_t es = dtype_size(dtype);
+  if (!es) return MPIT_ERR_TYPE;
+  if (count < 0) return MPIT_ERR_COUNT;
+  if (tag < 0) return MPIT_ERR_TAG;
+  int world, wire;
+  {
+    std::lock_guard<std::mutex> lk(g.mu);
+    Comm* c = find_comm(comm);
+    if (!c) return MPIT_ERR_COMM;
+    if (!valid_p2p(c, dest, false)) return MPIT_ERR_RANK;
+    world = c->ranks[dest];
+    wire = c->id;
+  }
+  Req* r;
+  int rc = isend_wire(buf, (size_t)count * es, world, tag, wire, &r);
+  *request = r->id;
+  return rc;
+}
+
+int mpit_msg_irecv(void* buf, long long count, int dtype, int source, int tag, int comm, int* request) {
+  size_t es = dtype_size(dtype);
+  if (!es) return MPIT_ERR_TYPE;
+  if (count < 0) return MPIT_ERR_COUNT;
+  if (tag < 0 && tag != MPIT_ANY_TAG) return MPIT_ERR_TAG;
+  int world, wire;
+  {
+    std::lock_guard<std::mutex> lk(g.mu);
+    Comm* c = find_comm(comm);
+    if (!c) return MPIT_ERR_COMM;
+    if (!valid_p2p(c, source, true)) return MPIT_ERR_RANK;
+    world = source == MPIT_ANY_SOURCE ? MPIT_ANY_SOURCE : c->ranks[source];
+    wire = c->id;
+  }
+  Req* r;
+  int rc = irecv_wire(buf, (size_t)count * es, world, tag, wire, &r);
+  *request = r->id;
+  return rc;
+}
+
+int mpit_msg_test(int* request, int* flag, mpit_status* status) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  if (*request == MPIT_REQUEST_NULL) { *flag = 1; return MPIT_SUCCESS; }
+  auto it = g.reqs.find(*request);
+  if (it == g.reqs.end()) return MPIT_ERR_REQUEST;
+  Req* r = it->second.get();
+  *flag = r->done ? 1 : 0;
+  if (r->done) {
+    Comm* c = nullptr;
+    for (auto& kv : g.comms) if (kv.second.id == (r->comm & ~(kCollBit | kNbcBit))) { c = &kv.second; break; }
+    fill_status(status, r, c);
+    int err = r->error;
+    free_req_locked(r->id);
+    *request = MPIT_REQUEST_NULL;
+    return err;
+  }
+  return MPIT_SUCCESS;
+}
+
+int mpit_msg_wait(int* request, mpit_status* status) {
+  if (*request == MPIT_REQUEST_NULL) return MPIT_SUCCESS;
+  Req* r;
+  {
+    std::lock_guard<std::mutex> lk(g.mu);
+    auto it = g.reqs.find(*request);
+    if (it == g.reqs.end()) return MPIT_ERR_REQUEST;
+    r = it->second.get();
+  }
+  wait_req(r);
+  int flag = 0;
+  return mpit_msg_test(request, &flag, status);
+}
+
+int mpit_msg_waitall(int n, int* requests, mpit_status* statuses) {
+  int rc = MPIT_SUCCESS;
+  for (int i = 0; i < n; ++i) {
+    int e = mpit_msg_wait(&requests[i], statuses ? &statuses[i] : nullptr);
+    if (e) rc = e;
+  }
+  return rc;
+}
+
+int mpit_msg_testall(int n, int* requests, int* flag, mpit_status* statuses) {
+  {
+    std::lock_guard<std::mutex> lk(g.mu);
+    for (int i = 0; i < n; ++i) {
+      if (requests[i] == MPIT_REQUEST_NULL) continue;
+      auto it = g.reqs.find(requests[i]);
+      if (it == g.reqs.end()) return MPIT_ERR_REQUEST;
+      if (!it->second->done) { *flag = 0; return MPIT_SUCCESS; }
+    }
+  }
+  *flag = 1;
+  return mpit_msg_waitall(n, requests, statuses);
+}
+
+int mpit_msg_waitany(int n, int* requests, int* index, mpit_status* status) {
+  for (;;) {
+    bool any = false;
+    for (int i = 0; i < n; ++i) {
+      if (requests[i] == MPIT_REQUEST_NULL) continue;
+      any = true;
+      int flag = 0;
+      int rc = mpit_msg_test(&requests[i], &flag, status);
+      if (flag) { *index = i; return rc; }
+    }
+    if (!any) { *index = MPIT_UNDEFINED; return MPIT_SUCCESS; }
+    std::unique_lock<std::mutex> lk(g.mu);
+    g.cv.wait_for(lk, std::chrono::milliseconds(1));
+  }
+}
+
+int mpit_msg_send(const void* buf, long long count, int dtype, int dest, int tag, int comm) {
+  int req;
+  int rc = mpit_msg_isend(buf, count, dtype, dest, tag, comm, &req);
+  if (rc) return rc;
+  return mpit_msg_wait(&req, nullptr);
+}
+
+int mpit_msg_recv(void* buf, long long count, int dtype, int source, int tag, int comm, mpit_status* status) {
+  int req;
+  int rc = mpit_msg_irecv(buf, count, dtype, source, tag, comm, &req);
+  if (rc) return rc;
+  return mpit_msg_wait(&req, status);
+}
+
+int mpit_msg_sendrecv(const void* sbuf, long long scount, int sdtype, int dest, int stag, void* rbuf,
+                      long long rcount, int rdtype, int source, int rtag, int comm, mpit_status* status) {
+  int rr, sr;
+  int rc = mpit_msg_irecv(rbuf, rcount, rdtype, source, rtag, comm, &rr);
+  if (rc) return rc;
+  rc = mpit_msg_isend(sbuf, scount, sdtype, dest, stag, comm, &sr);
+  if (rc) return rc;
+  rc = mpit_msg_wait(&sr, nullptr);
+  int rc2 = mpit_msg_wait(&rr, status);
+  return rc ? rc : rc2;
+}
+
+int mpit_msg_iprobe(int source, int tag, int comm, int* flag, mpit_status* status) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  Comm* c = find_comm(comm);
+  if (!c) return MPIT_ERR_COMM;
+  if (!valid_p2p(c, source, true)) return MPIT_ERR_RANK;
+  int world = source == MPIT_ANY_SOURCE ? MPIT_ANY_SOURCE : c->ranks[source];
+  *flag = 0;
+  for (auto& up : g.unexpected) {
+    Unexpected* u = up.get();
+    if (u->claimed || !match(world, tag, c->id, u->src, u->tag, u->comm)) continue;
+    *flag = 1;
+    if (status) {
+      auto it = std::find(c->ranks.begin(), c->ranks.end(), u->src);
+      status->source = it == c->ranks.end() ? u->src : (int)(it - c->ranks.begin());
+      status->tag = u->tag;
+      status->error = MPIT_SUCCESS;
+      status->count_bytes = (long long)u->data.size();
+      status->cancelled = 0;
+    }
+    break;
+  }
+  return MPIT_SUCCESS;
+}
+
+int mpit_msg_probe(int source, int tag, int comm, mpit_status* status) {
+  for (;;) {
+    int flag = 0;
+    int rc = mpit_msg_iprobe(source, tag, comm, &flag, status);
+    if (rc || flag) return rc;
+    std::unique_lock<std::mutex> lk(g.mu);
+    g.cv.wait_for(lk, std::chrono::milliseconds(2));
+  }
+}
+
+int mpit_msg_cancel(int* request) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  auto it = g.reqs.find(*request);
+  if (it == g.reqs.end()) return MPIT_ERR_REQUEST;
+  Req* r = it->second.get();
+  if (r->done) return MPIT_SUCCESS;
+  if (r->kind == REQ_RECV) {
+    for (auto pit = g.posted.begin(); pit != g.posted.end(); ++pit)
+      if (*pit == r) {
+        g.posted.erase(pit);
+        r->cancelled = true;
+        r->done = true;
+        g.cv.notify_all();
+        break;
+      }
+    // matched-but-arriving receives are past the point of no return and complete normally
+  } else if (r->kind == REQ_SEND && !r->started && r->peer != g.rank) {
+    auto& q = g.peers[r->peer].sendq;
+    for (auto sit = q.begin(); sit != q.end(); ++sit)
+      if (sit->req == r && sit->off == 0) {
+        q.erase(sit);
+        r->cancelled = true;
+        r->done = true;
+        g.cv.notify_all();
+        break;
+      }
+  }
+  return MPIT_SUCCESS;
+}
+
+int mpit_msg_test_cancelled(const mpit_status* status, int* flag) {
+  *flag = status && status->cancelled ? 1 : 0;
+  return MPIT_SUCCESS;
+}
+
+int mpit_msg_request_free(int* request) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  auto it = g.reqs.find(*request);
+  if (it == g.reqs.end()) return MPIT_ERR_REQUEST;
+  if (!it->second->done) return MPIT_ERR_REQUEST;   // only completed requests may be freed here
+  free_req_locked(*request);
+  *request = MPIT_REQUEST_NULL;
+  return MPIT_SUCCESS;
+}
+
+int mpit_msg_get_count(const mpit_status* status, int dtype, long long* count) {
+  size_t es = dtype_size(dtype);
+  if (!es) return MPIT_ERR_TYPE;
+  *count = status->count_bytes % (long long)es ? MPIT_UNDEFINED : status->count_bytes / (long long)es;
+  return MPIT_SUCCESS;
+}
+
+// ---- collectives ------------------------------------------------------------------------------------------
+int mpit_msg_barrier(int comm) {
+  Group G;
+  if (!group_of(comm, kCollBit, &G)) return MPIT_ERR_COMM;
+  return coll_barrier(G, 10);
+}
+
+int mpit_msg_bcast(void* buf, long long count, int dtype, int root, int comm) {
+  Group G;
+  if (!group_of(comm, kCollBit, &G)) return MPIT_ERR_COMM;
+  size_t es = dtype_size(dtype);
+  if (!es) return MPIT_ERR_TYPE;
+  if (root < 0 || root >= (int)G.ranks.size()) return MPIT_ERR_ROOT;
+  return coll_bcast(G, buf, (size_t)count * es, root, 20);
+}
+
+int mpit_msg_reduce(const void* sbuf, void* rbuf, long long count, int dtype, int op, int root, int comm) {
+  Group G;
+  if (!group_of(comm, kCollBit, &G)) return MPIT_ERR_COMM;
+  size_t es = dtype_size(dtype);
+  if (!es) return MPIT_ERR_TYPE;
+  if (root < 0 || root >= (int)G.ranks.size()) return MPIT_ERR_ROOT;
+  std::vector<char> acc((size_t)count * es);
+  memcpy(acc.data(), sbuf, acc.size());
+  int rc = coll_reduce(G, acc.data(), (size_t)count, dtype, op, root, 30);
+  if (rc) return rc;
+  if (G.me == root) memcpy(rbuf, acc.data(), acc.size());
+  return MPIT_SUCCESS;
+}
+
+int mpit_msg_allreduce(const void* sbuf, void* rbuf, long long count, int dtype, int op, int comm) {
+  Group G;
+  if (!group_of(comm, kCollBit, &G)) return MPIT_ERR_COMM;
+  if (!dtype_size(dtype)) return MPIT_ERR_TYPE;
+  return coll_allreduce(G, sbuf, rbuf, (size_t)count, dtype, op, 40);
+}
+
+int mpit_msg_iallreduce(const void* sbuf, void* rbuf, long long count, int dtype, int op, int comm,
+                        int* request) {
+  Group G;
+  if (!group_of(comm, kNbcBit, &G)) return MPIT_ERR_COMM;
+  if (!dtype_size(dtype)) return MPIT_ERR_TYPE;
+  int tag;
+  Req* r;
+  {
+    std::lock_guard<std::mutex> lk(g.mu);
+    Comm* c = find_comm(comm);
+    tag = 1000 + 2 * (int)(c->nbc_seq++ % 100000);   // operations of one communicator stay apart
+    r = new_req(REQ_COLL);
+    r->comm = G.wire;
+  }
+  *request = r->id;
+  r->worker = std::thread([=]() {
+    int rc = coll_allreduce(G, sbuf, rbuf, (size_t)count, dtype, op, tag);
+    std::lock_guard<std::mutex> lk(g.mu);
+    r->error = rc;
+    r->src_world = -1;
+    r->done = true;
+    g.cv.notify_all();
+  });
+  return MPIT_SUCCESS;
+}
+
+int mpit_msg_gather(const void* sbuf, long long scount, int dtype, void* rbuf, int root, int comm) {
+  Group G;
+  if (!group_of(comm, kCollBit, &G)) return MPIT_ERR_COMM;
+  size_t nb = (size_t)scount * dtype_size(dtype);
+  int n = (int)G.ranks.size();
+  if (G.me == root) {
+    for (int i = 0; i < n; ++i) {
+      char* dst = static_cast<char*>(rbuf) + (size_t)i * nb;
+      if (i == root) memcpy(dst, sbuf, nb);
+      else { int rc = recv_wire_blocking(dst, nb, G.ranks[i], 50, G.wire); if (rc) return rc; }
+    }
+    return MPIT_SUCCESS;
+  }
+  return send_wire_blocking(sbuf, nb, G.ranks[root], 50, G.wire);
+}
+
+int mpit_msg_allgather(const void* sbuf, long long scount, int dtype, void* rbuf, int comm) {
+  int rc = mpit_msg_gather(sbuf, scount, dtype, rbuf, 0, comm);
+  if (rc) return rc;
+  int n;
+  mpit_msg_comm_size(comm, &n);
+  return mpit_msg_bcast(rbuf, scount * n, dtype, 0, comm);
+}
+
+int mpit_msg_scatter(const void* sbuf, long long count, int dtype, void* rbuf, int root, int comm) {
+  Group G;
+  if (!group_of(comm, kCollBit, &G)) return MPIT_ERR_COMM;
+  size_t nb = (size_t)count * dtype_size(dtype);
+  int n = (int)G.ranks.size();
+  if (G.me == root) {
+    for (int i = 0; i < n; ++i) {
+      const char* src = static_cast<const char*>(sbuf) + (size_t)i * nb;
+      if (i == root) memcpy(rbuf, src, nb);
+      else { int rc = send_wire_blocking(src, nb, G.ranks[i], 60, G.wire); if (rc) return rc; }
+    }
+    return MPIT_SUCCESS;
+  }
+  return recv_wire_blocking(rbuf, nb, G.ranks[root], 60, G.wire);
+}
+
+int mpit_msg_alltoall(const void* sbuf, long long count, int dtype, void* rbuf, int comm) {
+  Group G;
+  if (!group_of(comm, kCollBit, &G)) return MPIT_ERR_COMM;
+  size_t nb = (size_t)count * dtype_size(dtype);
+  int n = (int)G.ranks.size();
+  std::vector<Req*> rs, ss;
+  for (int i = 0; i < n; ++i) {
+    if (i == G.me) { memcpy(static_cast<char*>(rbuf) + (size_t)i * nb, static_cast<const char*>(sbuf) + (size_t)i * nb, nb); continue; }
+    Req* r;
+    irecv_wire(static_cast<char*>(rbuf) + (size_t)i * nb, nb, G.ranks[i], 70, G.wire, &r);
+    rs.push_back(r);
+  }
+  for (int i = 0; i < n; ++i) {
+    if (i == G.me) continue;
+    Req* r;
+    isend_wire(static_cast<const char*>(sbuf) + (size_t)i * nb, nb, G.ranks[i], 70, G.wire, &r);
+    ss.push_back(r);
+  }
+  int rc = MPIT_SUCCESS;
+  for (Req* r : ss) { int e = wait_req(r); if (e) rc = e; }
+  for (Req* r : rs) { int e = wait_req(r); if (e) rc = e; }
+  std::lock_guard<std::mutex> lk(g.mu);
+  for (Req* r : ss) free_req_locked(r->id);
+  for (Req* r : rs) free_req_locked(r->id);
+  return rc;
+}
+
+int mpit_msg_reduce_scatter_block(const void* sbuf, void* rbuf, long long count, int dtype, int op, int comm) {
+  int n, me;
+  if (mpit_msg_comm_size(comm, &n) || mpit_msg_comm_rank(comm, &me)) return MPIT_ERR_COMM;
+  size_t es = dtype_size(dtype);
+  if (!es) return MPIT_ERR_TYPE;
+  std::vector<char> full((size_t)count * n * es);
+  int rc = mpit_msg_allreduce(sbuf, full.data(), count * n, dtype, op, comm);
+  if (rc) return rc;
+  memcpy(rbuf, full.data() + (size_t)me * count * es, (size_t)count * es);
+  return MPIT_SUCCESS;
+}
+
+int mpit_msg_scan(const void* sbuf, void* rbuf, long long count, int dtype, int op, int comm) {
+  Group G;
+  if (!group_of(comm, kCollBit, &G)) return MPIT_ERR_COMM;
+  size_t es = dtype_size(dtype);
+  if (!es) return MPIT_ERR_TYPE;
+  size_t nb = (size_t)count * es;
+  if (sbuf != rbuf) memcpy(rbuf, sbuf, nb);
+  if (G.me > 0) {
+    std::vector<char> prev(nb);
+    int rc = recv_wire_blocking(prev.data(), nb, G.ranks[G.me - 1], 80, G.wire);
+    if (rc) return rc;
+    // inclusive prefix: result = prefix(me-1) op mine  (order matters only for non-commutative ops)
+    std::vector<char> mine(nb);
+    memcpy(mine.data(), rbuf, nb);
+    memcpy(rbuf, prev.data(), nb);
+    rc = reduce_into(rbuf, mine.data(), (size_t)count, dtype, op);
+    if (rc) return rc;
+  }
+  if (G.me + 1 < (int)G.ranks.size()) return send_wire_blocking(rbuf, nb, G.ranks[G.me + 1], 80, G.wire);
+  return MPIT_SUCCESS;
+}
+
+int mpit_msg_stats(long long* stats8) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  for (int i = 0; i < 4; ++i) stats8[i] = g.stats[i];
+  stats8[4] = (long long)g.unexpected.size();
+  stats8[5] = (long long)g.posted.size();
+  stats8[6] = (long long)g.reqs.size();
+  stats8[7] = 0;
+  return MPIT_SUCCESS;
+}
+
+}  // extern "C"

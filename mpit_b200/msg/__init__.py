@@ -1,0 +1,487 @@
+"""Tensor message layer: the ``mpiT`` table of the reference, backed by ``libmpit_host.so``.
+
+Reference surface: /root/reference/lua-mpi.h:235-297 registers 262 MPI wrappers plus handle
+constructors and constants as the Lua table ``mpiT``; the tree only ever uses ``Init, Finalize,
+Comm_rank, Comm_size, Send, Recv, Isend, Irecv, Iprobe, Test, Wait, Cancel, Test_cancelled,
+Allreduce, Iallreduce, Request, Status`` and ``FLOAT, LONG, BYTE, SUM, COMM_WORLD``.
+This module provides those, plus ``Bcast, Barrier, Probe, Sendrecv, Reduce, Gather, Allgather,
+Scatter, Alltoall, Scan, Reduce_scatter_block, Waitall, Testall, Waitany, Wtime, Wtick, Comm_dup,
+Comm_split, Comm_free, Get_count, Get_processor_name, Abort, Init_MTF/MTS/MTM``.  MPI-IO, topology
+and derived datatypes (wrapped but never called in the reference) are out of scope.
+
+Buffers are torch tensors or numpy arrays.  Where the reference passes a Torch *Storage* and reads
+``storage->data`` with no type or bounds check (/root/reference/lua-mpi.h:70-76), this layer checks
+dtype size and element count.  CUDA tensors are staged through pinned host memory (the reference
+hands device pointers to a CUDA-aware MPI, lua-mpi.h:78); the device-to-device fast path of this
+framework is the symmetric-heap transport in ``mpit_b200.parallel``, not this layer.
+
+Functions return what MPI writes through out-parameters (``Comm_rank -> int``, ``Test -> bool``...)
+and raise :class:`MPIError` on a non-zero error code, instead of returning the code as a number
+(/root/reference/mpifuncs.c: every wrapper ends in ``lua_pushnumber(L, res)``).
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import List, Optional
+
+import numpy as np
+import torch
+
+from .._native import host
+
+# ---- constants (/root/reference/lua-mpi.h:125-231) -------------------------------------------------
+BYTE, CHAR, SHORT, INT, LONG, FLOAT, DOUBLE, UNSIGNED_CHAR, UNSIGNED, LONG_LONG = range(10)
+SUM, PROD, MAX, MIN, LAND, LOR, BAND, BOR = range(8)
+COMM_WORLD, COMM_SELF, COMM_NULL = 0, 1, -1
+ANY_SOURCE, ANY_TAG, REQUEST_NULL, UNDEFINED = -1, -1, -1, -32766
+SUCCESS = 0
+ERR_TRUNCATE = 15
+THREAD_SINGLE, THREAD_FUNNELED, THREAD_SERIALIZED, THREAD_MULTIPLE = 0, 1, 2, 3
+
+_DTYPE_SIZE = {BYTE: 1, CHAR: 1, SHORT: 2, INT: 4, LONG: 8, FLOAT: 4, DOUBLE: 8, UNSIGNED_CHAR: 1, UNSIGNED: 4,
+               LONG_LONG: 8}
+_TORCH_TO_MPI = {torch.float32: FLOAT, torch.float64: DOUBLE, torch.int64: LONG, torch.int32: INT,
+                 torch.int16: SHORT, torch.uint8: BYTE, torch.int8: CHAR}
+
+# signal constants live with the coroutine layer but the reference hangs them on the same table
+# (/root/reference/init.lua:21-25)
+signal_INIT, signal_EXEC, signal_OK, signal_ERR, signal_DONE = 1, 2, 3, 4, 5
+
+
+class MPIError(RuntimeError):
+    def __init__(self, code: int, what: str):
+        super().__init__(f"{what} failed with error class {code}")
+        self.code = code
+
+
+class _CStatus(ctypes.Structure):
+    _fields_ = [("source", ctypes.c_int), ("tag", ctypes.c_int), ("error", ctypes.c_int),
+                ("count_bytes", ctypes.c_longlong), ("cancelled", ctypes.c_int)]
+
+
+class Status:
+    """``mpiT.Status(n)`` (/root/reference/lua-mpi.h:7-21): an array of n status records."""
+
+    def __init__(self, n: int = 1):
+        self._arr = (_CStatus * n)()
+
+    def __len__(self):
+        return len(self._arr)
+
+    def __getitem__(self, i):
+        return self._arr[i]
+
+    source = property(lambda s: s._arr[0].source)
+    tag = property(lambda s: s._arr[0].tag)
+    error = property(lambda s: s._arr[0].error)
+    count_bytes = property(lambda s: s._arr[0].count_bytes)
+    cancelled = property(lambda s: bool(s._arr[0].cancelled))
+
+    def _ptr(self, i=0):
+        return ctypes.byref(self._arr[i])
+
+
+class Request:
+    """``mpiT.Request(n)``: n request handles, initialised to REQUEST_NULL."""
+
+    def __init__(self, n: int = 1):
+        self._arr = (ctypes.c_int * n)(*([REQUEST_NULL] * n))
+        self._after: List[Optional[callable]] = [None] * n   # completion hooks (device staging)
+        self._keep: List[object] = [None] * n                # buffers that must outlive the transfer
+
+    def __len__(self):
+        return len(self._arr)
+
+    def is_null(self, i=0):
+        return self._arr[i] == REQUEST_NULL
+
+    def _ptr(self, i=0):
+        return ctypes.byref(self._arr, i * ctypes.sizeof(ctypes.c_int))
+
+    def _finish(self, i=0):
+        fn, self._after[i], self._keep[i] = self._after[i], None, None
+        if fn is not None:
+            fn()
+
+
+def _chk(code: int, what: str):
+    if code != SUCCESS:
+        raise MPIError(code, what)
+
+
+class _Buf:
+    """Resolve a user buffer to (host pointer, keep-alive, completion hook)."""
+
+    def __init__(self, obj, count: int, dtype: int, writable: bool):
+        self.after = None
+        es = _DTYPE_SIZE[dtype]
+        nbytes = count * es
+        if obj is None:
+            if count != 0:
+                raise ValueError("a null buffer can only carry zero elements")
+            self.ptr, self.keep = ctypes.c_void_p(0), None
+            return
+        if isinstance(obj, torch.Tensor):
+            if not obj.is_contiguous():
+                raise ValueError("message buffers must be contiguous")
+            if dtype not in (BYTE, CHAR, UNSIGNED_CHAR) and obj.element_size() != es:
+                raise TypeError(f"tensor element size {obj.element_size()} does not match the MPI datatype ({es} bytes)")
+            if obj.numel() * obj.element_size() < nbytes:
+                raise ValueError(f"buffer holds {obj.numel()} elements, {count} requested")
+            if obj.is_cuda:
+                flat = obj.view(-1)
+                n_el = (nbytes + obj.element_size() - 1) // obj.element_size()
+                stage = torch.empty(n_el, dtype=obj.dtype, pin_memory=True)
+                if writable:
+                    self.after = lambda: flat[:n_el].copy_(stage)
+                else:
+                    stage.copy_(flat[:n_el])
+                    torch.cuda.current_stream(obj.device).synchronize()
+                self.ptr, self.keep = ctypes.c_void_p(stage.data_ptr()), (obj, stage)
+            else:
+                self.ptr, self.keep = ctypes.c_void_p(obj.data_ptr()), obj
+            return
+        if isinstance(obj, np.ndarray):
+            if not obj.flags["C_CONTIGUOUS"]:
+                raise ValueError("message buffers must be contiguous")
+            if obj.nbytes < nbytes:
+                raise ValueError("buffer too small")
+            self.ptr, self.keep = ctypes.c_void_p(obj.ctypes.data), obj
+            return
+        if isinstance(obj, (bytearray, memoryview)):
+            arr = (ctypes.c_char * len(obj)).from_buffer(obj)
+            if len(obj) < nbytes:
+                raise ValueError("buffer too small")
+            self.ptr, self.keep = ctypes.cast(arr, ctypes.c_void_p), (obj, arr)
+            return
+        if isinstance(obj, bytes) and not writable:
+            self.ptr, self.keep = ctypes.cast(ctypes.c_char_p(obj), ctypes.c_void_p), obj
+            return
+        raise TypeError(f"unsupported buffer type {type(obj)}")
+
+
+def mpi_dtype_of(t: torch.Tensor) -> int:
+    """The reference's stubbed ``mpiT.type(s)`` (/root/reference/init.lua:121-123), implemented."""
+    return _TORCH_TO_MPI[t.dtype]
+
+
+# ---- environment ---------------------------------------------------------------------------------------
+_state = {"rank": 0, "size": 1}
+
+
+def Init(rank: Optional[int] = None, size: Optional[int] = None, master_addr: Optional[str] = None,
+         master_port: Optional[int] = None, thread_level: int = THREAD_SINGLE) -> int:
+    """MPI_Init (/root/reference/lua-mpi.h:80-85).  Rank/size/rendezvous come from the environment
+    (``MPIT_RANK``/``RANK``, ``MPIT_WORLD_SIZE``/``WORLD_SIZE``, ``MASTER_ADDR``, ``MPIT_PORT`` or
+    ``MASTER_PORT``+17) as set by ``python -m mpit_b200.launch.run`` or torchrun."""
+    env = os.environ
+    rank = int(env.get("MPIT_RANK", env.get("RANK", "0"))) if rank is None else rank
+    size = int(env.get("MPIT_WORLD_SIZE", env.get("WORLD_SIZE", "1"))) if size is None else size
+    master_addr = master_addr or env.get("MPIT_ADDR", env.get("MASTER_ADDR", "127.0.0.1"))
+    if master_port is None:
+        master_port = int(env["MPIT_PORT"]) if "MPIT_PORT" in env else int(env.get("MASTER_PORT", "29400")) + 17
+    provided = ctypes.c_int(0)
+    _chk(host().mpit_msg_init(rank, size, master_addr.encode(), master_port, thread_level, ctypes.byref(provided)),
+         "Init")
+    if provided.value < thread_level:
+        Abort(COMM_WORLD, 1)
+    _state["rank"], _state["size"] = rank, size
+    return provided.value
+
+
+def Init_MTF():
+    """MPI_Init_thread(FUNNELED) (/root/reference/lua-mpi.h:87-97)."""
+    return Init(thread_level=THREAD_FUNNELED)
+
+
+def Init_MTS():
+    """MPI_Init_thread(SERIALIZED) (/root/reference/lua-mpi.h:99-109)."""
+    return Init(thread_level=THREAD_SERIALIZED)
+
+
+def Init_MTM():
+    """MPI_Init_thread(MULTIPLE) (/root/reference/lua-mpi.h:111-121)."""
+    return Init(thread_level=THREAD_MULTIPLE)
+
+
+def Initialized() -> bool:
+    f = ctypes.c_int(0)
+    host().mpit_msg_initialized(ctypes.byref(f))
+    return bool(f.value)
+
+
+def Finalize():
+    _chk(host().mpit_msg_finalize(), "Finalize")
+
+
+def Abort(comm: int = COMM_WORLD, errorcode: int = 1):
+    host().mpit_msg_abort(comm, errorcode)
+
+
+def Wtime() -> float:
+    return host().mpit_msg_wtime()
+
+
+def Wtick() -> float:
+    return host().mpit_msg_wtick()
+
+
+def Get_processor_name() -> str:
+    buf = ctypes.create_string_buffer(64)
+    n = ctypes.c_int(0)
+    _chk(host().mpit_msg_get_processor_name(buf, ctypes.byref(n)), "Get_processor_name")
+    return buf.value.decode()
+
+
+def Comm_rank(comm: int = COMM_WORLD) -> int:
+    r = ctypes.c_int(0)
+    _chk(host().mpit_msg_comm_rank(comm, ctypes.byref(r)), "Comm_rank")
+    return r.value
+
+
+def Comm_size(comm: int = COMM_WORLD) -> int:
+    r = ctypes.c_int(0)
+    _chk(host().mpit_msg_comm_size(comm, ctypes.byref(r)), "Comm_size")
+    return r.value
+
+
+# helpers of /root/reference/init.lua:28-38
+get_rank = Comm_rank
+get_size = Comm_size
+
+
+def Comm_dup(comm: int) -> int:
+    r = ctypes.c_int(0)
+    _chk(host().mpit_msg_comm_dup(comm, ctypes.byref(r)), "Comm_dup")
+    return r.value
+
+
+def Comm_split(comm: int, color: int, key: int) -> int:
+    r = ctypes.c_int(0)
+    _chk(host().mpit_msg_comm_split(comm, color, key, ctypes.byref(r)), "Comm_split")
+    return r.value
+
+
+def Comm_free(comm: int) -> None:
+    c = ctypes.c_int(comm)
+    _chk(host().mpit_msg_comm_free(ctypes.byref(c)), "Comm_free")
+
+
+# ---- point to point ---------------------------------------------------------------------------------------
+def Send(buf, count: int, dtype: int, dest: int, tag: int, comm: int = COMM_WORLD) -> None:
+    b = _Buf(buf, count, dtype, False)
+    _chk(host().mpit_msg_send(b.ptr, count, dtype, dest, tag, comm), "Send")
+
+
+def Recv(buf, count: int, dtype: int, source: int, tag: int, comm: int = COMM_WORLD,
+         status: Optional[Status] = None) -> None:
+    b = _Buf(buf, count, dtype, True)
+    _chk(host().mpit_msg_recv(b.ptr, count, dtype, source, tag, comm, status._ptr() if status else None), "Recv")
+    if b.after:
+        b.after()
+
+
+def Isend(buf, count: int, dtype: int, dest: int, tag: int, comm: int, request: Request, i: int = 0) -> None:
+    b = _Buf(buf, count, dtype, False)
+    request._keep[i] = b.keep
+    _chk(host().mpit_msg_isend(b.ptr, count, dtype, dest, tag, comm, request._ptr(i)), "Isend")
+
+
+def Irecv(buf, count: int, dtype: int, source: int, tag: int, comm: int, request: Request, i: int = 0) -> None:
+    b = _Buf(buf, count, dtype, True)
+    request._keep[i], request._after[i] = b.keep, b.after
+    _chk(host().mpit_msg_irecv(b.ptr, count, dtype, source, tag, comm, request._ptr(i)), "Irecv")
+
+
+def Sendrecv(sbuf, scount, sdtype, dest, stag, rbuf, rcount, rdtype, source, rtag, comm=COMM_WORLD,
+             status: Optional[Status] = None) -> None:
+    s, r = _Buf(sbuf, scount, sdtype, False), _Buf(rbuf, rcount, rdtype, True)
+    _chk(host().mpit_msg_sendrecv(s.ptr, scount, sdtype, dest, stag, r.ptr, rcount, rdtype, source, rtag, comm,
+                                  status._ptr() if status else None), "Sendrecv")
+    if r.after:
+        r.after()
+
+
+def Iprobe(source: int, tag: int, comm: int = COMM_WORLD, status: Optional[Status] = None) -> bool:
+    f = ctypes.c_int(0)
+    _chk(host().mpit_msg_iprobe(source, tag, comm, ctypes.byref(f), status._ptr() if status else None), "Iprobe")
+    return bool(f.value)
+
+
+def Probe(source: int, tag: int, comm: int = COMM_WORLD, status: Optional[Status] = None) -> None:
+    _chk(host().mpit_msg_probe(source, tag, comm, status._ptr() if status else None), "Probe")
+
+
+def Test(request: Request, status: Optional[Status] = None, i: int = 0) -> bool:
+    """MPI_Test: True when complete (the handle becomes REQUEST_NULL).  A truncated receive raises."""
+    st = status or Status()
+    f = ctypes.c_int(0)
+    code = host().mpit_msg_test(request._ptr(i), ctypes.byref(f), st._ptr())
+    if f.value and not st.cancelled:
+        request._finish(i)
+    elif f.value:
+        request._after[i] = request._keep[i] = None
+    _chk(code, "Test")
+    return bool(f.value)
+
+
+def Wait(request: Request, status: Optional[Status] = None, i: int = 0) -> None:
+    st = status or Status()
+    code = host().mpit_msg_wait(request._ptr(i), st._ptr())
+    if not st.cancelled:
+        request._finish(i)
+    else:
+        request._after[i] = request._keep[i] = None
+    _chk(code, "Wait")
+
+
+def Waitall(request: Request, statuses: Optional[Status] = None) -> None:
+    for i in range(len(request)):
+        if not request.is_null(i):
+            st = Status()
+            Wait(request, st, i)
+            if statuses is not None:
+                ctypes.memmove(statuses._ptr(i), st._ptr(), ctypes.sizeof(_CStatus))
+
+
+def Testall(request: Request) -> bool:
+    return all(request.is_null(i) or Test(request, None, i) for i in range(len(request)))
+
+
+def Waitany(request: Request, status: Optional[Status] = None) -> int:
+    import time
+    while True:
+        live = False
+        for i in range(len(request)):
+            if request.is_null(i):
+                continue
+            live = True
+            if Test(request, status, i):
+                return i
+        if not live:
+            return UNDEFINED
+        time.sleep(0)
+
+
+def Cancel(request: Request, i: int = 0) -> None:
+    _chk(host().mpit_msg_cancel(request._ptr(i)), "Cancel")
+
+
+def Test_cancelled(status: Status) -> bool:
+    f = ctypes.c_int(0)
+    _chk(host().mpit_msg_test_cancelled(status._ptr(), ctypes.byref(f)), "Test_cancelled")
+    return bool(f.value)
+
+
+def Get_count(status: Status, dtype: int) -> int:
+    c = ctypes.c_longlong(0)
+    _chk(host().mpit_msg_get_count(status._ptr(), dtype, ctypes.byref(c)), "Get_count")
+    return c.value
+
+
+# ---- collectives ----------------------------------------------------------------------------------------------
+def Barrier(comm: int = COMM_WORLD) -> None:
+    _chk(host().mpit_msg_barrier(comm), "Barrier")
+
+
+def Bcast(buf, count: int, dtype: int, root: int, comm: int = COMM_WORLD) -> None:
+    b = _Buf(buf, count, dtype, True)
+    if b.after and Comm_rank(comm) == root:   # root's device data must be staged out first
+        b.keep[1].copy_(b.keep[0].view(-1)[:b.keep[1].numel()])
+    _chk(host().mpit_msg_bcast(b.ptr, count, dtype, root, comm), "Bcast")
+    if b.after:
+        b.after()
+
+
+def Reduce(sbuf, rbuf, count: int, dtype: int, op: int, root: int, comm: int = COMM_WORLD) -> None:
+    s, r = _Buf(sbuf, count, dtype, False), _Buf(rbuf, count, dtype, True)
+    _chk(host().mpit_msg_reduce(s.ptr, r.ptr, count, dtype, op, root, comm), "Reduce")
+    if r.after and Comm_rank(comm) == root:
+        r.after()
+
+
+def Allreduce(sbuf, rbuf, count: int, dtype: int, op: int, comm: int = COMM_WORLD) -> None:
+    """MPI_Allreduce (/root/reference/test/testreduceall.lua:28)."""
+    s, r = _Buf(sbuf, count, dtype, False), _Buf(rbuf, count, dtype, True)
+    _chk(host().mpit_msg_allreduce(s.ptr, r.ptr, count, dtype, op, comm), "Allreduce")
+    if r.after:
+        r.after()
+
+
+def Iallreduce(sbuf, rbuf, count: int, dtype: int, op: int, comm: int, request: Request, i: int = 0) -> None:
+    """MPI_Iallreduce (/root/reference/test/testireduceall.lua:32); complete it with Test/Wait."""
+    s, r = _Buf(sbuf, count, dtype, False), _Buf(rbuf, count, dtype, True)
+    request._keep[i], request._after[i] = (s.keep, r.keep), r.after
+    _chk(host().mpit_msg_iallreduce(s.ptr, r.ptr, count, dtype, op, comm, request._ptr(i)), "Iallreduce")
+
+
+def Gather(sbuf, scount: int, dtype: int, rbuf, root: int, comm: int = COMM_WORLD) -> None:
+    n = Comm_size(comm)
+    s = _Buf(sbuf, scount, dtype, False)
+    r = _Buf(rbuf, scount * n, dtype, True) if Comm_rank(comm) == root else _Buf(None, 0, dtype, True)
+    _chk(host().mpit_msg_gather(s.ptr, scount, dtype, r.ptr, root, comm), "Gather")
+    if r.after:
+        r.after()
+
+
+def Allgather(sbuf, scount: int, dtype: int, rbuf, comm: int = COMM_WORLD) -> None:
+    s, r = _Buf(sbuf, scount, dtype, False), _Buf(rbuf, scount * Comm_size(comm), dtype, True)
+    _chk(host().mpit_msg_allgather(s.ptr, scount, dtype, r.ptr, comm), "Allgather")
+    if r.after:
+        r.after()
+
+
+def Scatter(sbuf, count: int, dtype: int, rbuf, root: int, comm: int = COMM_WORLD) -> None:
+    n = Comm_size(comm)
+    s = _Buf(sbuf, count * n, dtype, False) if Comm_rank(comm) == root else _Buf(None, 0, dtype, False)
+    r = _Buf(rbuf, count, dtype, True)
+    _chk(host().mpit_msg_scatter(s.ptr, count, dtype, r.ptr, root, comm), "Scatter")
+    if r.after:
+        r.after()
+
+
+def Alltoall(sbuf, count: int, dtype: int, rbuf, comm: int = COMM_WORLD) -> None:
+    n = Comm_size(comm)
+    s, r = _Buf(sbuf, count * n, dtype, False), _Buf(rbuf, count * n, dtype, True)
+    _chk(host().mpit_msg_alltoall(s.ptr, count, dtype, r.ptr, comm), "Alltoall")
+    if r.after:
+        r.after()
+
+
+def Reduce_scatter_block(sbuf, rbuf, count: int, dtype: int, op: int, comm: int = COMM_WORLD) -> None:
+    s, r = _Buf(sbuf, count * Comm_size(comm), dtype, False), _Buf(rbuf, count, dtype, True)
+    _chk(host().mpit_msg_reduce_scatter_block(s.ptr, r.ptr, count, dtype, op, comm), "Reduce_scatter_block")
+    if r.after:
+        r.after()
+
+
+def Scan(sbuf, rbuf, count: int, dtype: int, op: int, comm: int = COMM_WORLD) -> None:
+    s, r = _Buf(sbuf, count, dtype, False), _Buf(rbuf, count, dtype, True)
+    _chk(host().mpit_msg_scan(s.ptr, r.ptr, count, dtype, op, comm), "Scan")
+    if r.after:
+        r.after()
+
+
+def stats() -> dict:
+    a = (ctypes.c_longlong * 8)()
+    host().mpit_msg_stats(a)
+    keys = ("msgs_sent", "bytes_sent", "msgs_recv", "bytes_recv", "unexpected_now", "posted_now", "requests_live")
+    return dict(zip(keys, list(a)))
+
+
+# ---- serialize / deserialize (/root/reference/init.lua:111-132) -----------------------------------------------
+def serialize(obj) -> torch.Tensor:
+    """Any Torch7-representable object -> uint8 tensor (the reference's CharStorage), using the Torch7
+    binary format so that the bytes are interchangeable with ``torch.MemoryFile`` output."""
+    from ..t7 import dumps
+    return torch.frombuffer(bytearray(dumps(obj)), dtype=torch.uint8)
+
+
+def deserialize(buf: torch.Tensor):
+    from ..t7 import loads
+    return loads(bytes(buf.cpu().numpy().tobytes()))
+
+
+# coroutine IO lives in mpit_b200.aio; re-exported here because the reference hangs everything on mpiT
+from ..aio import (aio_send, aio_recv, co_execute, co_ping, co_wait, Queue)  # noqa: E402,F401
