@@ -188,28 +188,28 @@ colsum_kernel(const float* __restrict__ dz, float* __restrict__ db, long long ro
 // one 128-byte TMA row carries all five kernel columns of the first 5x5 convolution, and every row
 // starts on a 32-byte boundary (needed by the 32-byte-atom swizzle of the weight-gradient kernel).
 __global__ void __launch_bounds__(256)
-prep_u8_kernel(const unsigned char* __restrict__ src, float* __restrict__ dst, int B, int SH, int SW) {
+prep_u8_kernel(const unsigned char* __restrict__ src, float* __restrict__ dst, int B, int SH, int SW, int cin) {
   long long total = (long long)B * SH * SW;
   long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
     long long n = i / (SH * SW);
     int p = (int)(i % (SH * SW));
     int x = p % SW;
-    const unsigned char* s = src + (size_t)n * 3 * SH * SW + p;
+    const unsigned char* s = src + (size_t)n * cin * SH * SW + p;
     size_t plane = (size_t)SH * SW;
     float4 a, b;
     a.x = (float)s[0] / 255.f;
-    a.y = (float)s[plane] / 255.f;
-    a.z = (float)s[2 * plane] / 255.f;
-    a.w = 0.f;
+    a.y = cin > 1 ? (float)s[plane] / 255.f : 0.f;
+    a.z = cin > 2 ? (float)s[2 * plane] / 255.f : 0.f;
+    a.w = cin > 3 ? (float)s[3 * plane] / 255.f : 0.f;
     if (x + 1 < SW) {
       b.x = (float)s[1] / 255.f;
-      b.y = (float)s[plane + 1] / 255.f;
-      b.z = (float)s[2 * plane + 1] / 255.f;
+      b.y = cin > 1 ? (float)s[plane + 1] / 255.f : 0.f;
+      b.z = cin > 2 ? (float)s[2 * plane + 1] / 255.f : 0.f;
+      b.w = cin > 3 ? (float)s[3 * plane + 1] / 255.f : 0.f;
     } else {
-      b.x = b.y = b.z = 0.f;
+      b.x = b.y = b.z = b.w = 0.f;
     }
-    b.w = 0.f;
     st4(dst + 8 * i, a);
     st4(dst + 8 * i + 4, b);
   }
@@ -316,9 +316,10 @@ int mpit_colsum(const float* dz, float* db, long long rows, int C, void* stream)
   return 0;
 }
 
-int mpit_prep_u8(const unsigned char* src, float* dst, int B, int SH, int SW, void* stream) {
+int mpit_prep_u8(const unsigned char* src, float* dst, int B, int SH, int SW, int cin, void* stream) {
+  if (cin < 1 || cin > 4) return MPIT_E_ARG;
   long long total = (long long)B * SH * SW;
-  prep_u8_kernel<<<ew_grid(total, 256, 1), 256, 0, (cudaStream_t)stream>>>(src, dst, B, SH, SW);
+  prep_u8_kernel<<<ew_grid(total, 256, 1), 256, 0, (cudaStream_t)stream>>>(src, dst, B, SH, SW, cin);
   MPIT_LAUNCH_CHECK();
   return 0;
 }

@@ -71,7 +71,7 @@ int mpit_conv_wgrad_ref(const int* geom12, const float* dz, const float* x, cons
 int mpit_act_bwd(const float* dout, const float* out, const unsigned char* pool_idx, float* dz, int B, int OH,
                  int OW, int C, int pool, float scale, void* stream);
 int mpit_colsum(const float* dz, float* db, long long rows, int C, void* stream);
-int mpit_prep_u8(const unsigned char* src, float* dst, int B, int SH, int SW, void* stream);
+int mpit_prep_u8(const unsigned char* src, float* dst, int B, int SH, int SW, int cin, void* stream);
 int mpit_nll_fwd_bwd(const float* logits, const int* labels, float* dlogits, float* loss_sum, int* confusion,
                      int B, int ncls, int ld, float gscale, unsigned long long* rng_inc, void* stream);
 

@@ -1,0 +1,107 @@
+"""mlaunch: distributed EAMSGD / EASGD / Downpour training (reference /root/reference/asyncsgd/mlaunch.lua:
+even ranks = servers, odd ranks = clients, ``eamsgd, su=2, mva=0.9/p, lr=1e-2, mom=0.99``).
+
+Two paths:
+
+* ``--device cuda`` (default when GPUs are present): one process per B200, every GPU is a worker and the
+  owner of one shard of the centre (no server processes); start with torchrun::
+
+      python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 -m mpit_b200.launch.mlaunch
+
+* ``--device cpu``: the reference's process layout over the host message layer::
+
+      python -m mpit_b200.launch.run -np 4 -m mpit_b200.launch.mlaunch --device cpu
+
+``--model mnist`` runs the MNIST-shaped CNN (BASELINE.json config 2), ``--optim downpour`` its Downpour arm.
+"""
+from __future__ import annotations
+
+import argparse
+import os
+import sys
+
+import torch
+
+
+def main(argv=None) -> int:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--device", default="cuda" if torch.cuda.is_available() else "cpu")
+    ap.add_argument("--optim", default="eamsgd", choices=["eamsgd", "easgd", "downpour"])
+    ap.add_argument("--model", default="cifar", choices=["cifar", "mnist"])
+    ap.add_argument("--su", type=int, default=2)
+    ap.add_argument("--lr", type=float, default=None)
+    ap.add_argument("--mom", type=float, default=0.99)
+    ap.add_argument("--epochs", type=int, default=1)
+    ap.add_argument("--trsize", type=int, default=2048)
+    ap.add_argument("--tesize", type=int, default=512)
+    ap.add_argument("--mb", type=int, default=128)
+    ap.add_argument("--save", default="results/mlaunch")
+    a = ap.parse_args(argv)
+    lr = a.lr if a.lr is not None else (1e-4 if a.optim == "downpour" else 1e-2)   # mlaunch.lua:50-60
+    if a.device == "cuda":
+        return _gpu(a, lr)
+    return _cpu(a, lr)
+
+
+def _gpu(a, lr) -> int:
+    import torch.distributed as dist
+    from ..parallel.symm import SymmetricHeap
+    from ..workloads.cifar import CifarTrainer, CifarOpts, synthetic_cifar, train_epochs
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    heap = SymmetricHeap(dev)
+    opts = CifarOpts(name=a.optim, lr=lr, mom=a.mom, mb=a.mb, su=a.su, mva=0.9 / world, maxepoch=a.epochs,
+                     save=a.save, seed=1 + rank, model=a.model)
+    print(f"[client] rank {rank} use gpu {local}")
+    tr = CifarTrainer(opts, dev, heap)
+    ch = 1 if a.model == "mnist" else 3
+    hist = train_epochs(tr, synthetic_cifar(a.trsize, seed=10 + rank, channels=ch),
+                        synthetic_cifar(a.tesize, seed=2, channels=ch), rank=rank, quiet=rank != 0)
+    print(f"[rank {rank}] train loss {hist['train_loss'][-1]:.4f} test acc {hist['test_acc'][-1]:.4f} "
+          f"{hist['samples_per_s']:.0f} samples/s")
+    heap.check_timeout()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def _cpu(a, lr) -> int:
+    from .. import msg as mpiT, ps
+    from ..models.cifar_cnn import TorchCifarCNN
+    from ..models.mnist import MnistMLP, synthetic_mnist
+    from ..workloads import goot
+    from ..workloads.cifar import synthetic_cifar
+    torch.set_num_threads(1)
+    mpiT.Init()
+    rank, size = mpiT.get_rank(), mpiT.get_size()
+    conf = ps.make_conf(rank, size, "parity")
+    if rank % 2 == 0:
+        print("[server] rank", rank, "use cpu")
+        ps.pServer(conf).start()
+    else:
+        print(f"[client] rank {rank} use cpu")
+        p = size // 2
+        torch.manual_seed(rank)
+        if a.model == "mnist":
+            model, crop = MnistMLP(), 0
+            tr, te = synthetic_mnist(a.trsize, 10 + rank), synthetic_mnist(a.tesize, 2)
+        else:
+            model, crop = TorchCifarCNN(), 28
+            (x, y), (tx, ty) = synthetic_cifar(a.trsize, 10 + rank, pinned=False), synthetic_cifar(a.tesize, 2, pinned=False)
+            tr, te = (x.float() / 255, y), (tx.float() / 255, ty)
+        opt = dict(name=a.optim, lr=lr, su=a.su, mva=0.9 / p, mom=a.mom, maxepoch=a.epochs, mb=a.mb, trsize=a.trsize,
+                   tesize=a.tesize, save=a.save, seed=rank, crop=crop, quiet=rank != 1)
+        hist = goot.run(opt, model, tr, te, pclient=ps.pClient(conf), rank=rank)
+        print(f"[client {rank}] train loss {hist['train_loss'][-1]:.4f} test acc {hist['test_acc'][-1]:.4f}")
+    mpiT.Finalize()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -72,18 +72,32 @@ class Layer:
         return self.CO * self.k * self.KWP * self.C
 
 
-def cifar_layers() -> List[Layer]:
-    """Layer table.  fc layers are 1x1 convolutions over a 1x1 'image' of 256 channels."""
+def convnet_layers(cin: int = 3, c1: int = 64, c2: int = 128, c3: int = 64, f1: int = 256,
+                   ncls: int = NUM_CLASSES) -> List[Layer]:
+    """Layer table of the Conv5-pool / Conv5-pool / Conv3 / FC / FC topology of 7-layers-cnn.lua with
+    free channel counts.  fc layers are 1x1 convolutions over a 1x1 'image'.  Constraints of the
+    tensor-core tiles: cin <= 4 (pair-expanded 4-channel pixels), c1/c2/c3/f1 multiples of 32."""
+    assert 1 <= cin <= 4 and all(c % 32 == 0 for c in (c1, c2, c3, f1)) and ncls <= 32
     return [
         # conv1 reads the pair-expanded image (8 floats per pixel = this pixel + the next one, 4
         # channels each): physically a 5x4-tap convolution over 8 channels whose 32-float rows hold
         # kernel columns [0,1 | 1,2 | 2,3 | 3,4]; the duplicated columns carry zero weights.
-        Layer("conv1", 3, 64, 5, CROP, IMG, True, True, False, C=8, KWP=4, CO=64, kw_taps=4),
-        Layer("conv2", 64, 128, 5, 12, 12, True, True, False, C=64, KWP=5, CO=128),
-        Layer("conv3", 128, 64, 3, 4, 4, False, True, False, C=128, KWP=3, CO=64),
-        Layer("fc1", 256, 256, 1, 1, 1, False, True, True, C=256, KWP=1, CO=256),
-        Layer("fc2", 256, NUM_CLASSES, 1, 1, 1, False, False, False, C=256, KWP=1, CO=32),
+        Layer("conv1", cin, c1, 5, CROP, IMG, True, True, False, C=8, KWP=4, CO=c1, kw_taps=4),
+        Layer("conv2", c1, c2, 5, 12, 12, True, True, False, C=c1, KWP=5, CO=c2),
+        Layer("conv3", c2, c3, 3, 4, 4, False, True, False, C=c2, KWP=3, CO=c3),
+        Layer("fc1", 4 * c3, f1, 1, 1, 1, False, True, True, C=4 * c3, KWP=1, CO=f1),
+        Layer("fc2", f1, ncls, 1, 1, 1, False, False, False, C=f1, KWP=1, CO=32),
     ]
+
+
+def cifar_layers() -> List[Layer]:
+    """asyncsgd/models/7-layers-cnn.lua:8-24."""
+    return convnet_layers(3, 64, 128, 64, 256, NUM_CLASSES)
+
+
+def mnist_cnn_layers() -> List[Layer]:
+    """MNIST-shaped CNN (1 input channel) for BASELINE.json config 2; see models/mnist.py."""
+    return convnet_layers(1, 32, 64, 64, 256, NUM_CLASSES)
 
 
 def _align(n: int, a: int = 32) -> int:
@@ -126,7 +140,7 @@ class ParamLayout:
                 # Torch's View(64*2*2) flattens CHW; our activations are HWC
                 # (7-layers-cnn.lua:19): flat input index i = c*4 + h*2 + w  ->  (h*2+w)*64 + c
                 c, hw = ci // 4, ci % 4
-                pc = hw * 64 + c
+                pc = hw * (L.cin // 4) + c
                 tap = kw
             elif L.name == "conv1":
                 # kernel column kw lives in slot [0,1,3,5,7][kw] of the 8 four-channel slots of a row
@@ -152,7 +166,7 @@ class ParamLayout:
             co, ci, kh, kw = torch.meshgrid(torch.arange(L.cout), torch.arange(L.cin), torch.arange(L.k),
                                             torch.arange(L.k), indexing="ij")
             if L.name == "fc1":
-                pc = (ci % 4) * 64 + ci // 4
+                pc = (ci % 4) * (L.cin // 4) + ci // 4
             else:
                 pc = ci
             off = ((pc * L.k + kh) * L.k + kw) * L.CO + co + L.d_off
@@ -175,16 +189,17 @@ class ParamLayout:
 # Plain PyTorch restatement (CPU oracle, CPU workers, and the library-call GPU baseline)
 # ---------------------------------------------------------------------------------------------
 class TorchCifarCNN(torch.nn.Module):
-    def __init__(self):
+    def __init__(self, cin: int = 3, c1: int = 64, c2: int = 128, c3: int = 64, f1: int = 256,
+                 ncls: int = NUM_CLASSES):
         super().__init__()
         nn = torch.nn
         self.features = nn.Sequential(
-            nn.Conv2d(3, 64, 5), nn.ReLU(), nn.MaxPool2d(2, 2),
-            nn.Conv2d(64, 128, 5), nn.ReLU(), nn.MaxPool2d(2, 2),
-            nn.Conv2d(128, 64, 3), nn.ReLU())
-        self.fc1 = nn.Linear(256, 256)
+            nn.Conv2d(cin, c1, 5), nn.ReLU(), nn.MaxPool2d(2, 2),
+            nn.Conv2d(c1, c2, 5), nn.ReLU(), nn.MaxPool2d(2, 2),
+            nn.Conv2d(c2, c3, 3), nn.ReLU())
+        self.fc1 = nn.Linear(4 * c3, f1)
         self.drop = nn.Dropout(0.5)
-        self.fc2 = nn.Linear(256, NUM_CLASSES)
+        self.fc2 = nn.Linear(f1, ncls)
         torch7_reset(self)
 
     def forward(self, x, drop_mask=None):
@@ -238,13 +253,16 @@ class CifarEngine:
     implicit-GEMM kernels (TF32 inputs, fp32 accumulate).  Both read ``wpk`` and write ``gpk``.
     """
 
-    def __init__(self, batch: int, device="cuda", impl: str = "umma", seed: int = 1):
+    def __init__(self, batch: int, device="cuda", impl: str = "umma", seed: int = 1,
+                 layers: Optional[List[Layer]] = None):
         from .. import ops
         self.ops = ops
         self.B = batch
         self.dev = torch.device(device)
         self.impl = impl
-        self.layout = ParamLayout()
+        self.layout = ParamLayout(layers)
+        self.cin = self.layout.layers[0].cin
+        self.ncls = self.layout.layers[-1].cout
         self.layers = self.layout.layers
         dev = self.dev
         f32 = dict(dtype=torch.float32, device=dev)
@@ -254,7 +272,7 @@ class CifarEngine:
         self.wpk = torch.zeros(self.layout.n_packed, **f32)
         self.gpk = torch.zeros(self.layout.n_packed, **f32)
         # inputs
-        self.x_u8 = torch.zeros(B, 3, IMG, IMG, dtype=torch.uint8, device=dev)
+        self.x_u8 = torch.zeros(B, self.cin, IMG, IMG, dtype=torch.uint8, device=dev)
         self.labels = torch.zeros(B, dtype=torch.int32, device=dev)
         self.crop = torch.zeros(B, 2, dtype=torch.int32, device=dev)
         # pair-expanded NHWC8 image (+1 image of slack for the 4-pixel TMA rows at the image edge)
@@ -268,7 +286,7 @@ class CifarEngine:
         self.dact = [torch.zeros_like(a) for a in self.act]
         self.dz = [torch.zeros(B * L.out_hw * L.out_hw * L.CO, **f32) for L in self.layers]
         self.loss_sum = torch.zeros(1, **f32)
-        self.confusion = torch.zeros(NUM_CLASSES, NUM_CLASSES, dtype=torch.int32, device=dev)
+        self.confusion = torch.zeros(self.ncls, self.ncls, dtype=torch.int32, device=dev)
         self.rng = torch.tensor([seed, 0], dtype=torch.int64, device=dev)
         self._umma = None
         if impl == "umma":
@@ -310,7 +328,7 @@ class CifarEngine:
     # -- schedules -----------------------------------------------------------------------------
     def forward(self, train: bool = True) -> None:
         ops, B = self.ops, self.B
-        ops.prep_u8(self.x_u8, self.x0, B, IMG, IMG)
+        ops.prep_u8(self.x_u8, self.x0, B, IMG, IMG, self.cin)
         if self._umma is not None:
             self._umma.forward(train)
         else:
@@ -325,7 +343,7 @@ class CifarEngine:
         L5 = self.layers[-1]
         self.loss_sum.zero_()
         self.ops.nll_fwd_bwd(self.act[-1], self.labels, self.dz[-1] if train else None, self.loss_sum,
-                             self.B, NUM_CLASSES, L5.CO, gscale=1.0 / self.B, confusion=self.confusion,
+                             self.B, self.ncls, L5.CO, gscale=1.0 / self.B, confusion=self.confusion,
                              rng_inc=self.rng if train else None)
 
     def backward(self) -> None:
@@ -359,7 +377,7 @@ class CifarEngine:
         self.loss_and_grad(False)
 
     def logits(self) -> torch.Tensor:
-        return self.act[-1].view(self.B, self.layers[-1].CO)[:, :NUM_CLASSES]
+        return self.act[-1].view(self.B, self.layers[-1].CO)[:, :self.ncls]
 
 
 def center_crop_offsets(B: int) -> torch.Tensor:

@@ -64,8 +64,8 @@ def colsum(dz, db, rows, C):
     check(kernels().mpit_colsum(ptr(dz), ptr(db), rows, C, cur_stream()), "mpit_colsum")
 
 
-def prep_u8(src, dst, B, SH, SW):
-    check(kernels().mpit_prep_u8(ptr(src), ptr(dst), B, SH, SW, cur_stream()), "mpit_prep_u8")
+def prep_u8(src, dst, B, SH, SW, cin=3):
+    check(kernels().mpit_prep_u8(ptr(src), ptr(dst), B, SH, SW, cin, cur_stream()), "mpit_prep_u8")
 
 
 def nll_fwd_bwd(logits, labels, dlogits, loss_sum, B, ncls, ld, *, gscale, confusion=None, rng_inc=None):

@@ -76,14 +76,23 @@ def weight_tmap(t: torch.Tensor, rows: int, K: int, block_n: int):
     return make_tmap(t.data_ptr(), [K, rows], [K * 4], [32, block_n])
 
 
+def _pick_block(n: int, prefer=(128, 64, 32)) -> int:
+    for b in prefer:
+        if n % b == 0:
+            return b
+    raise ValueError(f"N={n} is not a multiple of 32")
+
+
 class CifarUmmaPlan:
-    """Launch plan of the CIFAR CNN on the tensor cores (forward, data gradients, weight gradients)."""
+    """Launch plan of the Conv5-pool / Conv5-pool / Conv3 / FC / FC network on the tensor cores
+    (forward, data gradients, weight gradients) for any channel counts the layer table allows."""
 
     def __init__(self, eng, wgrad: str = "auto"):
         self.eng = eng
         B = eng.B
         assert B % 2 == 0, "the 128-row tiles pair two 8x8 sub-tiles: batch must be even"
         L1, L2, L3, L4, L5 = eng.layers
+        c1, c2, c3, f_in, f1 = L1.CO, L2.CO, L3.CO, L4.C, L4.CO
         self.err = torch.zeros(1, dtype=torch.int32, device=eng.dev)
         act, dz, idx = eng.act, eng.dz, eng.idx
         w = lambda i: eng.w(i)
@@ -96,62 +105,66 @@ class CifarUmmaPlan:
         # conv1: overlapping view of the pair-expanded NHWC8 image: one 128-byte row = 4 pixels x 8 floats
         # = kernel columns [0,1|1,2|2,3|3,4] x 4 channels, pixel stride 32 bytes
         ta = make_tmap(eng.x0.data_ptr(), [32, 32, 32, B], [32, 32 * 32, 32 * 32 * 32], [32, 8, 8, 1])
+        bn = _pick_block(c1, (64, 32))
         self.fwd.append(IgemmLaunch(
-            ta, weight_tmap(w(0), L1.CO, 5 * 32, 64),
+            ta, weight_tmap(w(0), c1, 5 * 32, bn),
             igemm_geom(nsub=2, tw=8, th=8, tn=1, tiles_w=3, tiles_h=3, kw_it=1, cb=1, num_kb=5, sgn=1, B=B,
-                       OH=24, OW=24, N=64, mode=EPI_POOL, relu=1),
-            1.0, eng.b(0), act[0], idx[0], None, None, eng.crop, None, 64))
+                       OH=24, OW=24, N=c1, mode=EPI_POOL, relu=1),
+            1.0, eng.b(0), act[0], idx[0], None, None, eng.crop, None, bn))
         # conv2
+        bn = _pick_block(c2)
         self.fwd.append(IgemmLaunch(
-            nhwc_tmap(act[0], B, 12, 12, 64, 8, 8, 1), weight_tmap(w(1), L2.CO, 25 * 64, 128),
-            igemm_geom(nsub=2, tw=8, th=8, tn=1, tiles_w=1, tiles_h=1, kw_it=5, cb=2, num_kb=50, sgn=1, B=B,
-                       OH=8, OW=8, N=128, mode=EPI_POOL, relu=1),
-            1.0, eng.b(1), act[1], idx[1], None, None, None, None, 128))
+            nhwc_tmap(act[0], B, 12, 12, c1, 8, 8, 1), weight_tmap(w(1), c2, 25 * c1, bn),
+            igemm_geom(nsub=2, tw=8, th=8, tn=1, tiles_w=1, tiles_h=1, kw_it=5, cb=c1 // 32, num_kb=25 * c1 // 32,
+                       sgn=1, B=B, OH=8, OW=8, N=c2, mode=EPI_POOL, relu=1),
+            1.0, eng.b(1), act[1], idx[1], None, None, None, None, bn))
         # conv3
         self.fwd.append(IgemmLaunch(
-            nhwc_tmap(act[1], B, 4, 4, 128, 2, 2, 32), weight_tmap(w(2), L3.CO, 9 * 128, 32),
-            igemm_geom(nsub=1, tw=2, th=2, tn=32, tiles_w=1, tiles_h=1, kw_it=3, cb=4, num_kb=36, sgn=1, B=B,
-                       OH=2, OW=2, N=64, mode=EPI_STORE, relu=1),
+            nhwc_tmap(act[1], B, 4, 4, c2, 2, 2, 32), weight_tmap(w(2), c3, 9 * c2, 32),
+            igemm_geom(nsub=1, tw=2, th=2, tn=32, tiles_w=1, tiles_h=1, kw_it=3, cb=c2 // 32, num_kb=9 * c2 // 32,
+                       sgn=1, B=B, OH=2, OW=2, N=c3, mode=EPI_STORE, relu=1),
             1.0, eng.b(2), act[2], None, None, None, None, None, 32))
         # fc1 (+ReLU +dropout)
         self.fwd.append(IgemmLaunch(
-            nhwc_tmap(act[2], B, 1, 1, 256, 1, 1, 128), weight_tmap(w(3), 256, 256, 32),
-            igemm_geom(nsub=1, tw=1, th=1, tn=128, tiles_w=1, tiles_h=1, kw_it=1, cb=8, num_kb=8, sgn=1, B=B,
-                       OH=1, OW=1, N=256, mode=EPI_STORE, relu=1, dropout=1),
+            nhwc_tmap(act[2], B, 1, 1, f_in, 1, 1, 128), weight_tmap(w(3), f1, f_in, 32),
+            igemm_geom(nsub=1, tw=1, th=1, tn=128, tiles_w=1, tiles_h=1, kw_it=1, cb=f_in // 32, num_kb=f_in // 32,
+                       sgn=1, B=B, OH=1, OW=1, N=f1, mode=EPI_STORE, relu=1, dropout=1),
             1.0, eng.b(3), act[3], None, None, None, None, eng.rng, 32))
         # fc2
         self.fwd.append(IgemmLaunch(
-            nhwc_tmap(act[3], B, 1, 1, 256, 1, 1, 128), weight_tmap(w(4), 32, 256, 32),
-            igemm_geom(nsub=1, tw=1, th=1, tn=128, tiles_w=1, tiles_h=1, kw_it=1, cb=8, num_kb=8, sgn=1, B=B,
-                       OH=1, OW=1, N=32, mode=EPI_STORE),
+            nhwc_tmap(act[3], B, 1, 1, f1, 1, 1, 128), weight_tmap(w(4), 32, f1, 32),
+            igemm_geom(nsub=1, tw=1, th=1, tn=128, tiles_w=1, tiles_h=1, kw_it=1, cb=f1 // 32, num_kb=f1 // 32,
+                       sgn=1, B=B, OH=1, OW=1, N=32, mode=EPI_STORE),
             1.0, eng.b(4), act[4], None, None, None, None, None, 32))
 
         # ---- data gradients (layer i -> dz of layer i-1) ----
         self.dgrad = {}
-        # fc2: dz5 [B,32] x Wd5 [256][32] -> mask by a4 > 0, x2 (dropout scale) -> dz4
+        # fc2: dz5 [B,32] x Wd5 [f1][32] -> mask by a4 > 0, x2 (dropout scale) -> dz4
         self.dgrad[4] = IgemmLaunch(
-            nhwc_tmap(dz[4], B, 1, 1, 32, 1, 1, 128), weight_tmap(wd(4), 256, 32, 32),
+            nhwc_tmap(dz[4], B, 1, 1, 32, 1, 1, 128), weight_tmap(wd(4), f1, 32, 32),
             igemm_geom(nsub=1, tw=1, th=1, tn=128, tiles_w=1, tiles_h=1, kw_it=1, cb=1, num_kb=1, sgn=-1, B=B,
-                       OH=1, OW=1, N=256, mode=EPI_MASK),
+                       OH=1, OW=1, N=f1, mode=EPI_MASK),
             2.0, None, dz[3], None, act[3], None, None, None, 32)
-        # fc1: dz4 [B,256] x Wd4 [256][256] -> mask by a3 > 0 -> dz3
+        # fc1: dz4 [B,f1] x Wd4 [f_in][f1] -> mask by a3 > 0 -> dz3
         self.dgrad[3] = IgemmLaunch(
-            nhwc_tmap(dz[3], B, 1, 1, 256, 1, 1, 128), weight_tmap(wd(3), 256, 256, 32),
-            igemm_geom(nsub=1, tw=1, th=1, tn=128, tiles_w=1, tiles_h=1, kw_it=1, cb=8, num_kb=8, sgn=-1, B=B,
-                       OH=1, OW=1, N=256, mode=EPI_MASK),
+            nhwc_tmap(dz[3], B, 1, 1, f1, 1, 1, 128), weight_tmap(wd(3), f_in, f1, 32),
+            igemm_geom(nsub=1, tw=1, th=1, tn=128, tiles_w=1, tiles_h=1, kw_it=1, cb=f1 // 32, num_kb=f1 // 32,
+                       sgn=-1, B=B, OH=1, OW=1, N=f_in, mode=EPI_MASK),
             1.0, None, dz[2], None, act[2], None, None, None, 32)
-        # conv3: dz3 [B,2,2,64] -> d(a2) over 4x4 -> un-pool with idx2, mask a2 > 0 -> dz2 [B,8,8,128]
+        # conv3: dz3 [B,2,2,c3] -> d(a2) over 4x4 -> un-pool with idx2, mask a2 > 0 -> dz2 [B,8,8,c2]
+        bn = _pick_block(c2, (64, 32))
         self.dgrad[2] = IgemmLaunch(
-            nhwc_tmap(dz[2], B, 2, 2, 64, 4, 4, 8), weight_tmap(wd(2), 128, 9 * 64, 64),
-            igemm_geom(nsub=1, tw=4, th=4, tn=8, tiles_w=1, tiles_h=1, kw_it=3, cb=2, num_kb=18, sgn=-1, B=B,
-                       OH=4, OW=4, N=128, mode=EPI_EXPAND),
-            1.0, None, dz[1], None, act[1], idx[1], None, None, 64)
-        # conv2: dz2 [B,8,8,128] -> d(a1) over 12x12 -> un-pool with idx1, mask -> dz1 [B,24,24,64]
+            nhwc_tmap(dz[2], B, 2, 2, c3, 4, 4, 8), weight_tmap(wd(2), c2, 9 * c3, bn),
+            igemm_geom(nsub=1, tw=4, th=4, tn=8, tiles_w=1, tiles_h=1, kw_it=3, cb=c3 // 32, num_kb=9 * c3 // 32,
+                       sgn=-1, B=B, OH=4, OW=4, N=c2, mode=EPI_EXPAND),
+            1.0, None, dz[1], None, act[1], idx[1], None, None, bn)
+        # conv2: dz2 [B,8,8,c2] -> d(a1) over 12x12 -> un-pool with idx1, mask -> dz1 [B,24,24,c1]
+        bn = _pick_block(c1, (64, 32))
         self.dgrad[1] = IgemmLaunch(
-            nhwc_tmap(dz[1], B, 8, 8, 128, 4, 4, 4), weight_tmap(wd(1), 64, 25 * 128, 64),
-            igemm_geom(nsub=2, tw=4, th=4, tn=4, tiles_w=3, tiles_h=3, kw_it=5, cb=4, num_kb=100, sgn=-1, B=B,
-                       OH=12, OW=12, N=64, mode=EPI_EXPAND),
-            1.0, None, dz[0], None, act[0], idx[0], None, None, 64)
+            nhwc_tmap(dz[1], B, 8, 8, c2, 4, 4, 4), weight_tmap(wd(1), c1, 25 * c2, bn),
+            igemm_geom(nsub=2, tw=4, th=4, tn=4, tiles_w=3, tiles_h=3, kw_it=5, cb=c2 // 32, num_kb=25 * c2 // 32,
+                       sgn=-1, B=B, OH=12, OW=12, N=c1, mode=EPI_EXPAND),
+            1.0, None, dz[0], None, act[0], idx[0], None, None, bn)
 
         self.wgrad = None
         if wgrad != "ref":

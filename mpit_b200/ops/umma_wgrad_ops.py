@@ -40,18 +40,21 @@ class CifarWgradPlan:
         G = lambda *a: (ctypes.c_int * 11)(*a)
         ceil = lambda a, b: (a + b - 1) // b
         x0map = make_tmap(eng.x0.data_ptr(), [32, 32, 32, B], [32, 32 * 32, 32 * 32 * 32], [32, 8, 8, 1], MN_SWIZZLE)
+        L1, L2, L3, L4, L5 = eng.layers
+        c1, c2, c3, f_in, f1 = L1.CO, L2.CO, L3.CO, L4.C, L4.CO
+        pick = lambda n: 128 if n % 128 == 0 else (64 if n % 64 == 0 else 32)
         specs = [
             # tmap_x, tmap_dz, (tw,th,tn,tiles_w,tiles_h,kw_it,cb,total_chunks,num_kb,B,N), crop, block_n, nsplit
-            (x0map, nhwc_tmap(dz[0], B, 24, 24, 64, 8, 8, 1), (8, 8, 1, 3, 3, 1, 1, 5, B * 9, B, 64), eng.crop, 64,
-             min(64, B * 9)),
-            (nhwc_tmap(act[0], B, 12, 12, 64, 8, 8, 1), nhwc_tmap(dz[1], B, 8, 8, 128, 8, 8, 1),
-             (8, 8, 1, 1, 1, 5, 2, 50, B, B, 128), None, 128, min(8, B)),
-            (nhwc_tmap(act[1], B, 4, 4, 128, 2, 2, 16), nhwc_tmap(dz[2], B, 2, 2, 64, 2, 2, 16),
-             (2, 2, 16, 1, 1, 3, 4, 36, ceil(B, 16), B, 64), None, 64, ceil(B, 16)),
-            (nhwc_tmap(act[2], B, 1, 1, 256, 1, 1, 64), nhwc_tmap(dz[3], B, 1, 1, 256, 1, 1, 64),
-             (1, 1, 64, 1, 1, 1, 8, 8, ceil(B, 64), B, 256), None, 128, ceil(B, 64)),
-            (nhwc_tmap(act[3], B, 1, 1, 256, 1, 1, 64), nhwc_tmap(dz[4], B, 1, 1, 32, 1, 1, 64),
-             (1, 1, 64, 1, 1, 1, 8, 8, ceil(B, 64), B, 32), None, 32, ceil(B, 64)),
+            (x0map, nhwc_tmap(dz[0], B, 24, 24, c1, 8, 8, 1), (8, 8, 1, 3, 3, 1, 1, 5, B * 9, B, c1), eng.crop,
+             min(64, pick(c1)), min(64, B * 9)),
+            (nhwc_tmap(act[0], B, 12, 12, c1, 8, 8, 1), nhwc_tmap(dz[1], B, 8, 8, c2, 8, 8, 1),
+             (8, 8, 1, 1, 1, 5, c1 // 32, 25 * c1 // 32, B, B, c2), None, pick(c2), min(8, B)),
+            (nhwc_tmap(act[1], B, 4, 4, c2, 2, 2, 16), nhwc_tmap(dz[2], B, 2, 2, c3, 2, 2, 16),
+             (2, 2, 16, 1, 1, 3, c2 // 32, 9 * c2 // 32, ceil(B, 16), B, c3), None, min(64, pick(c3)), ceil(B, 16)),
+            (nhwc_tmap(act[2], B, 1, 1, f_in, 1, 1, 64), nhwc_tmap(dz[3], B, 1, 1, f1, 1, 1, 64),
+             (1, 1, 64, 1, 1, 1, f_in // 32, f_in // 32, ceil(B, 64), B, f1), None, pick(f1), ceil(B, 64)),
+            (nhwc_tmap(act[3], B, 1, 1, f1, 1, 1, 64), nhwc_tmap(dz[4], B, 1, 1, 32, 1, 1, 64),
+             (1, 1, 64, 1, 1, 1, f1 // 32, f1 // 32, ceil(B, 64), B, 32), None, 32, ceil(B, 64)),
         ]
         self.launches = []
         off = 0

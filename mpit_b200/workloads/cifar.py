@@ -45,12 +45,14 @@ class CifarOpts:
     use_graphs: bool = True
     save: str = "results"
     rule_hyper: dict = field(default_factory=dict)
+    model: str = "cifar"          # cifar (3x32x32, 64/128/64 channels) | mnist (1x32x32, 32/64/64 channels)
 
 
-def synthetic_cifar(n: int, seed: int = 0, pinned: bool = True):
-    """Synthetic data of the CIFAR-10 shape: uint8 [n,3,32,32] images, labels in [0,10)."""
+def synthetic_cifar(n: int, seed: int = 0, pinned: bool = True, channels: int = 3):
+    """Synthetic data of the CIFAR-10 shape: uint8 [n,3,32,32] images, labels in [0,10)
+    (``channels=1`` gives the MNIST-shaped variant)."""
     g = torch.Generator().manual_seed(seed)
-    x = torch.randint(0, 256, (n, 3, IMG, IMG), dtype=torch.uint8, generator=g)
+    x = torch.randint(0, 256, (n, channels, IMG, IMG), dtype=torch.uint8, generator=g)
     y = torch.randint(0, NUM_CLASSES, (n,), dtype=torch.int32, generator=g)
     if pinned and torch.cuda.is_available():
         x, y = x.pin_memory(), y.pin_memory()
@@ -63,10 +65,12 @@ class CifarTrainer:
         self.opts = opts
         self.dev = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         torch.cuda.set_device(self.dev)
-        self.engine = CifarEngine(opts.mb, device=self.dev, impl=opts.impl, seed=opts.seed)
+        from ..models.cifar_cnn import mnist_cnn_layers, cifar_layers
+        layers = mnist_cnn_layers() if opts.model == "mnist" else cifar_layers()
+        self.engine = CifarEngine(opts.mb, device=self.dev, impl=opts.impl, seed=opts.seed, layers=layers)
         if theta0 is None:
             g = torch.Generator().manual_seed(opts.seed)
-            m = TorchCifarCNN()
+            m = TorchCifarCNN(1, 32, 64, 64, 256) if opts.model == "mnist" else TorchCifarCNN()
             from ..models.cifar_cnn import torch7_reset
             torch7_reset(m, g)
             theta0 = flat_from_torch(m)
@@ -151,3 +155,64 @@ class CifarTrainer:
         conf = eng.confusion.cpu()
         return {"loss": total / max(n, 1), "acc": float(conf.diag().sum()) / max(int(conf.sum()), 1),
                 "confusion": conf, "n": n}
+
+
+def train_epochs(tr: CifarTrainer, train_xy, test_xy, rank: int = -1, quiet: bool = False) -> dict:
+    """Epoch loop of goot.lua:154-261 around a :class:`CifarTrainer`: per-epoch shuffle, random crops,
+    ``train.log``/``test.log`` rows, a Torch7 ``model-epoch-N.net`` every ``saveep`` epochs (a loadable
+    ``nn.Sequential``, goot.lua:246-254), test after every epoch, timing summary (goot.lua:330-337)."""
+    from .. import t7
+    from ..utils import Logger, ConfusionMatrix
+    opts = tr.opts
+    B = opts.mb
+    (trx, try_), (tex, tey) = train_xy, test_xy
+    trsize = (trx.shape[0] // B) * B
+    os.makedirs(opts.save, exist_ok=True)
+    sfx = "" if rank < 0 else str(rank)
+    train_log = Logger(os.path.join(opts.save, f"train{sfx}.log"))
+    test_log = Logger(os.path.join(opts.save, f"test{sfx}.log"))
+    gen = torch.Generator().manual_seed(opts.seed)
+    stage_x = torch.empty(B, tr.engine.cin, IMG, IMG, dtype=torch.uint8).pin_memory()
+    stage_y = torch.empty(B, dtype=torch.int32).pin_memory()
+    stage_c = torch.empty(B, 2, dtype=torch.int32).pin_memory()
+    hist = {"train_loss": [], "train_acc": [], "test_acc": [], "test_loss": []}
+    t0 = time.perf_counter()
+    n_steps = 0
+    for epoch in range(1, opts.maxepoch + 1):
+        shuffle = torch.randperm(trsize, generator=gen)
+        tr.engine.confusion.zero_()
+        losses = []
+        for t in range(0, trsize, B):
+            idx = shuffle[t:t + B]
+            torch.index_select(trx, 0, idx, out=stage_x)
+            torch.index_select(try_, 0, idx, out=stage_y)
+            stage_c.copy_(random_crop_offsets(B, gen))
+            prev = tr.train_step(stage_x, stage_y, stage_c)
+            if prev is not None:
+                losses.append(prev)
+            n_steps += 1
+        losses.append(tr.last_loss())
+        conf = tr.engine.confusion.cpu()
+        acc = float(conf.diag().sum()) / max(int(conf.sum()), 1)
+        elapsed = (time.perf_counter() - t0) / 60
+        train_log.add({"% train accuracy": f"{acc:0.4f}", "% wall-clock elapsed time(min)": f"{elapsed:0.2f}",
+                       "% train loss": f"{sum(losses) / len(losses):0.4f}"})
+        hist["train_loss"].append(sum(losses) / len(losses))
+        hist["train_acc"].append(acc)
+        if epoch % opts.saveep == 0:
+            t7.save(os.path.join(opts.save, f"model-epoch-{epoch}.net"), t7.cifar_model_to_t7(tr.params()))
+        res = tr.test(tex, tey)
+        test_log.add({"% test accuracy": f"{res['acc']:0.4f}",
+                      "% wall-clock elapsed time(min)": f"{(time.perf_counter() - t0) / 60:0.2f}",
+                      "% test error": f"{res['loss']:0.2f}"})
+        hist["test_acc"].append(res["acc"])
+        hist["test_loss"].append(res["loss"])
+    total = time.perf_counter() - t0
+    hist["total"] = total
+    hist["samples_per_s"] = n_steps * B / total
+    if not quiet:
+        print(rank, "total training time is", total)
+        print(f"\n===> time to learn 1 sample = {total / max(n_steps * B, 1) * 1000:.5f}ms")
+    train_log.close()
+    test_log.close()
+    return hist

@@ -174,3 +174,28 @@ def test_engine_umma_wgrad_matches_ref_layerwise(B):
         gw_r = ref.gw(i).view(L.CO, L.k, L.KWP, L.C)[:, :, :L.k]
         assert _rel_l2(gw_u, gw_r) < 3e-3, (i, _rel_l2(gw_u, gw_r))
         assert _rel_l2(um.gb(i), ref.gb(i)) < 1e-4, (i, "bias")
+
+
+def test_mnist_cnn_engine_matches_torch_cpu():
+    """The same engine with the MNIST-shaped layer table (1 input channel, 32/64/64 channels)."""
+    from mpit_b200.models.cifar_cnn import mnist_cnn_layers
+    torch.manual_seed(5)
+    B = 8
+    model = TorchCifarCNN(1, 32, 64, 64, 256)
+    theta = flat_from_torch(model)
+    images = torch.randint(0, 256, (B, 1, 32, 32), dtype=torch.uint8)
+    labels = torch.randint(0, NUM_CLASSES, (B,), dtype=torch.int32)
+    crop = random_crop_offsets(B)
+    for impl, tol in (("ref", 2e-4), ("umma", 4e-3)):
+        eng = CifarEngine(B, impl=impl, seed=7, layers=mnist_cnn_layers())
+        eng.load_flat(theta.cuda())
+        eng.set_batch(images, labels, crop)
+        eng.fwd_bwd()
+        torch.cuda.synchronize()
+        a4 = eng.act[3].view(B, 256).cpu()
+        logp, loss = _oracle(model, images, labels, crop, (a4 > 0).float() * 2.0)
+        assert torch.allclose(torch.log_softmax(eng.logits().cpu(), 1), logp.detach(), atol=tol, rtol=tol)
+        loss.backward()
+        ref_g = flat_from_torch(model, grads=True)
+        rel = float((eng.flat_grad().cpu() - ref_g).norm() / ref_g.norm())
+        assert rel < (1e-3 if impl == "ref" else 0.15), (impl, rel)
