@@ -1,3 +1,4 @@
 """Multi-GPU plumbing: symmetric heap, sharded centre variable, device collectives."""
 from .symm import SymmetricHeap, SymmBuffer, LocalPeerHeap
 from .center import ShardedCenter, partition
+from .collectives import DeviceCollectives, DeviceMailbox, DeviceRequest

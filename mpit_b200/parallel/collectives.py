@@ -1,0 +1,138 @@
+"""Device collectives over the symmetric heap: all-reduce (one-shot / two-shot, NVLS multimem when the
+heap has a multicast mapping), broadcast, barrier, the all-reduce fused with the elastic pull, and the
+device mailbox (two-sided Send/Recv as put + flag).  Kernels: csrc/kernels/comm.cu.
+
+Reference call sites: MPI_Allreduce / MPI_Iallreduce (test/testreduceall.lua:28, test/testireduceall.lua:32,
+asyncsgd/testreduceall.lua:76), MPI_Bcast (wrapped only, mpifuncs.c:145), MPI_Send/Recv (test.lua:32-38).
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional
+
+import torch
+
+from .._native import kernels, check, ptr, cur_stream
+from .symm import SymmBuffer
+
+
+class DeviceRequest:
+    """Handle of a non-blocking device collective (MPI_Request for Iallreduce): a CUDA event recorded on
+    the side stream that runs the kernel; ``test()`` polls it, ``wait()`` makes the current stream (and
+    optionally the host) wait for it."""
+
+    def __init__(self, stream: torch.cuda.Stream):
+        self.event = torch.cuda.Event()
+        self.event.record(stream)
+        self.stream = stream
+
+    def test(self) -> bool:
+        return self.event.query()
+
+    def wait(self, host: bool = False) -> None:
+        torch.cuda.current_stream().wait_event(self.event)
+        if host:
+            self.event.synchronize()
+
+
+class DeviceCollectives:
+    """Collectives of one rank over buffers allocated from one symmetric heap.
+
+    ``inp``/``out`` are symmetric buffers of ``capacity`` floats; the caller writes its contribution
+    into ``inp.local`` (or passes a tensor to copy in) and reads the result from ``out.local``."""
+
+    ONE_SHOT_MAX = 256 * 1024   # floats (1 MiB): below this the latency path wins
+
+    def __init__(self, heap, capacity: int, multicast: bool = True):
+        self.heap = heap
+        self.k = kernels()
+        self.capacity = capacity
+        self.inp: SymmBuffer = heap.alloc(capacity, multicast=multicast)
+        self.out: SymmBuffer = heap.alloc(capacity, multicast=multicast)
+        self.sig: SymmBuffer = heap.signal_pad()
+        self.nranks, self.rank = self.inp.nranks, self.inp.rank
+        self._in_ptrs, self._out_ptrs, self._sig_ptrs = self.inp.ptr_array(), self.out.ptr_array(), self.sig.ptr_array()
+        self._side = torch.cuda.Stream()
+
+    def allreduce(self, x: Optional[torch.Tensor] = None, n: Optional[int] = None, *, average: bool = False,
+                  algo: Optional[str] = None, elastic_x: Optional[torch.Tensor] = None, alpha: float = 0.0,
+                  max_blocks: int = 0) -> torch.Tensor:
+        """Sum (or mean) over ranks.  ``elastic_x`` fuses ``x -= alpha (x - mean)`` into the same kernel
+        (synchronous EASGD: the all-reduce/average path of testreduceall fused with the elastic update).
+        Returns a view of the result."""
+        if x is not None:
+            n = x.numel()
+            self.inp.local[:n].copy_(x.reshape(-1))
+        assert n is not None and n <= self.capacity
+        if algo is None:
+            algo = "oneshot" if n <= self.ONE_SHOT_MAX else "twoshot"
+        scale = 1.0 / self.nranks if average else 1.0
+        two = algo == "twoshot"
+        local_out = None if two else self.out.local
+        check(self.k.mpit_allreduce(self._in_ptrs, self.inp.mc_ptr, self._out_ptrs if two else None,
+                                    self.out.mc_ptr if two else 0, self._sig_ptrs, self.nranks, self.rank,
+                                    ptr(local_out), ptr(elastic_x), n, scale, alpha, 1 if two else 0, max_blocks,
+                                    cur_stream()), "mpit_allreduce")
+        return self.out.local[:n]
+
+    def iallreduce(self, x: torch.Tensor, **kw) -> DeviceRequest:
+        """MPI_Iallreduce: the same kernel on a side stream; Request = CUDA event."""
+        self._side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(self._side):
+            self.allreduce(x, **kw)
+        return DeviceRequest(self._side)
+
+    def bcast(self, n: int, root: int, max_blocks: int = 0) -> torch.Tensor:
+        """Broadcast ``out.local[:n]`` of ``root`` into every rank's ``out.local``."""
+        check(self.k.mpit_bcast(self._out_ptrs, self.out.mc_ptr, self._sig_ptrs, self.nranks, self.rank, root, n,
+                                max_blocks, cur_stream()), "mpit_bcast")
+        return self.out.local[:n]
+
+    def barrier(self) -> None:
+        check(self.k.mpit_device_barrier(self._sig_ptrs, self.nranks, self.rank, cur_stream()), "mpit_device_barrier")
+
+
+class DeviceMailbox:
+    """Two-sided tagged messages between GPUs: one slot per (source -> destination) pair in the
+    receiver's symmetric memory, payload stores followed by a release-flag; probe = acquire-load."""
+
+    HEADER = 8   # floats
+
+    def __init__(self, heap, max_count: int):
+        self.k = kernels()
+        self.max_count = max_count
+        self.slot = self.HEADER + (max_count + 3) // 4 * 4
+        self.buf: SymmBuffer = heap.alloc(self.slot * heap.nranks)
+        self.nranks, self.rank = self.buf.nranks, self.buf.rank
+        self.send_seq = [0] * self.nranks
+        self.recv_seq = [0] * self.nranks
+        self._res = torch.zeros(3, dtype=torch.int32, device=self.buf.local.device)
+
+    def send(self, x: torch.Tensor, dest: int, tag: int) -> None:
+        n = x.numel()
+        assert n <= self.max_count
+        self.send_seq[dest] += 1
+        slot_ptr = self.buf.ptrs[dest] + 4 * self.slot * self.rank      # my slot inside dest's buffer
+        check(self.k.mpit_mailbox_put(ctypes.c_void_p(slot_ptr), ptr(x), n, tag, self.send_seq[dest], cur_stream()),
+              "mpit_mailbox_put")
+
+    def try_recv(self, out: torch.Tensor, source: int, tag: int = -1):
+        """Iprobe+Recv: returns (arrived, count, tag) after a stream sync."""
+        seq = self.recv_seq[source] + 1
+        slot_ptr = self.buf.ptrs[self.rank] + 4 * self.slot * source
+        check(self.k.mpit_mailbox_recv(ctypes.c_void_p(slot_ptr), ptr(out), out.numel(), tag, seq, ptr(self._res),
+                                       cur_stream()), "mpit_mailbox_recv")
+        arrived, count, got_tag = self._res.tolist()
+        if arrived:
+            self.recv_seq[source] = seq
+        return bool(arrived), count, got_tag
+
+    def recv(self, out: torch.Tensor, source: int, tag: int = -1, timeout_s: float = 10.0):
+        import time
+        t0 = time.time()
+        while True:
+            ok, count, got_tag = self.try_recv(out, source, tag)
+            if ok:
+                return count, got_tag
+            if time.time() - t0 > timeout_s:
+                raise TimeoutError("device mailbox receive timed out")

@@ -1,0 +1,159 @@
+"""Multi-GPU test bodies: run with ``python -m torch.distributed.run --nproc-per-node N tests/mp_gpu_cases.py <case>``."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import torch.distributed as dist
+
+from mpit_b200.parallel import SymmetricHeap, ShardedCenter, DeviceCollectives, DeviceMailbox
+from mpit_b200.parallel.center import partition
+
+
+def setup():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    return rank, world, dev
+
+
+def sync(dev):
+    torch.cuda.synchronize(dev)
+    dist.barrier()
+    torch.cuda.synchronize(dev)
+
+
+def case_center(rank, world, dev, heap):
+    n = 351946
+    c = ShardedCenter.create(heap, n)
+    x0 = torch.arange(n, dtype=torch.float32, device=dev) * 1e-3
+    if rank == 0:
+        c.put(x0)
+    sync(dev)
+    y = torch.empty(n, device=dev)
+    c.pull(y)
+    torch.cuda.synchronize()
+    assert torch.equal(y, x0), "pull after seed"
+    off, sz = partition(n, world)[rank]
+    assert torch.equal(c.local_shard, x0[off:off + sz]), "my shard holds the reference partition"
+    sync(dev)
+    # conservation of pushes: every rank accumulates (rank+1) everywhere
+    g = torch.full((n,), float(rank + 1), device=dev)
+    c.push_add(g)
+    sync(dev)
+    c.pull(y)
+    torch.cuda.synchronize()
+    tot = world * (world + 1) / 2
+    assert torch.allclose(y, x0 + tot), float((y - x0 - tot).abs().max())
+    sync(dev)
+    # elastic: d_i = alpha (x_i - centre_seen_by_i); centre += d_i.  Ranks race by design
+    # ("no lock ... expect inconsistent read", asyncsgd/pserver.lua:81), so each d_i depends on the
+    # interleaving -- what must hold exactly is conservation: centre_after = centre_before + sum_i d_i.
+    before = y.clone()
+    xi = x0 + tot + (rank + 1)
+    d = torch.empty(n, device=dev)
+    c.elastic(xi, d, 0.1)
+    sync(dev)
+    lo, hi = 0.1 * ((rank + 1) - 0.1 * tot) - 1e-3, 0.1 * (rank + 1) + 1e-3
+    assert float(d.min()) >= lo and float(d.max()) <= hi, (float(d.min()), float(d.max()), lo, hi)
+    dsum = d.clone()
+    dist.all_reduce(dsum)
+    c.pull(y)
+    torch.cuda.synchronize()
+    assert torch.allclose(y, before + dsum, atol=2e-3), float((y - before - dsum).abs().max())
+
+
+def case_collectives(rank, world, dev, heap):
+    for n, algo in ((6, "oneshot"), (1000, "oneshot"), (1 << 20, "twoshot"), ((1 << 20) + 3, "twoshot"), (4096, "twoshot")):
+        coll = DeviceCollectives(heap, n)
+        x = torch.full((n,), float(rank + 1), device=dev) + torch.arange(n, device=dev) % 7
+        out = coll.allreduce(x, algo=algo)
+        torch.cuda.synchronize()
+        want = world * (world + 1) / 2 + world * (torch.arange(n, device=dev) % 7)
+        assert torch.allclose(out, want), (n, algo, float((out - want).abs().max()))
+        sync(dev)
+        out = coll.allreduce(x, algo=algo, average=True)
+        torch.cuda.synchronize()
+        assert torch.allclose(out, want / world, atol=1e-5)
+        sync(dev)
+        # fused elastic pull toward the mean
+        xe = x.clone()
+        coll.allreduce(x, algo=algo, average=True, elastic_x=xe, alpha=0.25)
+        torch.cuda.synchronize()
+        mean = want / world
+        assert torch.allclose(xe, x - 0.25 * (x - mean), atol=1e-5), (n, algo)
+        sync(dev)
+        # non-blocking: Test / Wait state machine (test/testireduceall.lua:27-39)
+        req = coll.iallreduce(x, algo=algo)
+        req.wait(host=True)
+        assert req.test()
+        assert torch.allclose(coll.out.local[:n], want)
+        sync(dev)
+        # broadcast from the last rank
+        root = world - 1
+        coll.out.local[:n].fill_(float(rank))
+        sync(dev)
+        coll.bcast(n, root)
+        torch.cuda.synchronize()
+        assert float(coll.out.local[:n].min()) == root and float(coll.out.local[:n].max()) == root
+        sync(dev)
+    coll.barrier()
+    torch.cuda.synchronize()
+    heap.check_timeout()
+
+
+def case_mailbox(rank, world, dev, heap):
+    """Ring of one float (test.lua:19-38) through the device mailbox, twice to exercise sequencing."""
+    mb = DeviceMailbox(heap, 64)
+    sync(dev)
+    src, dest = (rank - 1) % world, (rank + 1) % world
+    for rnd in range(2):
+        s = torch.full((4,), float(rank * 10 + rnd), device=dev)
+        r = torch.zeros(4, device=dev)
+        if rank == 0:
+            mb.send(s, dest, tag=3)
+            cnt, tag = mb.recv(r, src, tag=3)
+        else:
+            cnt, tag = mb.recv(r, src, tag=3)
+            mb.send(s, dest, tag=3)
+        assert cnt == 4 and tag == 3 and float(r[0]) == src * 10 + rnd, (rank, rnd, r)
+        sync(dev)
+
+
+def case_eamsgd_train(rank, world, dev, heap):
+    """Asynchronous EAMSGD over the sharded centre: workers and centre stay finite and close."""
+    from mpit_b200.workloads.cifar import CifarTrainer, CifarOpts, synthetic_cifar
+    from mpit_b200.models.cifar_cnn import random_crop_offsets
+    B = 32
+    opts = CifarOpts(name="eamsgd", lr=1e-2, mom=0.9, mb=B, su=2, mva=0.9 / world, seed=1 + rank, use_graphs=True)
+    tr = CifarTrainer(opts, dev, heap)
+    x, y = synthetic_cifar(8 * B, seed=rank)
+    for i in range(24):
+        j = (i % 8) * B
+        tr.train_step(x[j:j + B], y[j:j + B], random_crop_offsets(B))
+    theta = tr.params()
+    sync(dev)
+    centre = tr.center.gather_full()
+    torch.cuda.synchronize()
+    assert torch.isfinite(theta).all() and torch.isfinite(centre).all()
+    rel = float((theta - centre).norm() / centre.norm())
+    assert rel < 0.5, rel
+    assert 0.5 < tr.last_loss() < 5.0
+    heap.check_timeout()
+
+
+CASES = {k[5:]: v for k, v in globals().items() if k.startswith("case_")}
+
+if __name__ == "__main__":
+    rank, world, dev = setup()
+    mode = os.environ.get("MPIT_SYMM_MODE", "auto")
+    heap = SymmetricHeap(dev, mode=mode)
+    names = sys.argv[1:] or list(CASES)
+    for name in names:
+        CASES[name](rank, world, dev, heap)
+        sync(dev)
+        if rank == 0:
+            print(f"case {name}: ok (heap mode {heap.mode}, multicast {heap.multicast_ok})", flush=True)
+    dist.barrier()
+    dist.destroy_process_group()

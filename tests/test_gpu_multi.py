@@ -1,0 +1,34 @@
+"""Multi-GPU tests: one process per GPU under torchrun, exercising the symmetric heap (IPC and VMM /
+multicast), the sharded centre, device collectives, the mailbox and asynchronous EAMSGD."""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _torchrun(cases, nproc, env=None, timeout=600):
+    e = dict(os.environ)
+    e.update(env or {})
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+           "--master-addr", "127.0.0.1", "--master-port", "29533", os.path.join(HERE, "mp_gpu_cases.py"), *cases]
+    r = subprocess.run(cmd, env=e, capture_output=True, text=True, timeout=timeout)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    return r.stdout
+
+
+@pytest.mark.parametrize("mode", ["ipc", "vmm"])
+def test_center_collectives_mailbox(mode):
+    n = min(torch.cuda.device_count(), 8)
+    out = _torchrun(["center", "collectives", "mailbox"], n, {"MPIT_SYMM_MODE": mode})
+    assert "case mailbox: ok" in out
+
+
+def test_async_eamsgd_training():
+    n = min(torch.cuda.device_count(), 8)
+    out = _torchrun(["eamsgd_train"], n)
+    assert "case eamsgd_train: ok" in out
