@@ -27,3 +27,18 @@ def test_failing_rank_aborts_job():
     rc = launch(2, ["-c", "import os,sys,time; sys.exit(3) if os.environ['MPIT_RANK']=='1' else time.sleep(30)"],
                 timeout=20)
     assert rc == 3
+
+
+def test_ptest_cpu_bandwidth():
+    assert launch(4, ["mpit_b200.launch.ptest", "--device", "cpu", "--ssize", "65536", "--rounds", "3"], module=True,
+                  timeout=120) == 0
+
+
+def test_testreduceall_cpu():
+    assert launch(4, ["mpit_b200.launch.testreduceall", "--ssize", "65536", "--megs", "0.25"], module=True,
+                  timeout=120) == 0
+
+
+def test_ptest2_stragglers():
+    assert launch(4, ["mpit_b200.launch.ptest2", "--ssize", "4096", "--rounds", "2", "--skew-size", "16"], module=True,
+                  timeout=120) == 0
