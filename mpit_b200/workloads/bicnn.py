@@ -1,0 +1,335 @@
+"""BiCNN training / evaluation workload (reference: /root/reference/BiCNN/bicnn.lua:279-651,
+prepareData.lua, plaunch.lua).
+
+``feval`` (bicnn.lua:279-420) does, per training sample: forward Q and A+, draw up to ``maxnegsample``
+random wrong answers and stop at the first one that violates the margin, skip the sample if none does,
+back-propagate the hinge loss, add L1/L2 regularisation and clamp the gradient to ``+-gradClip``.  The
+reference evaluates the candidates one nngraph forward at a time; here all candidates of all samples of
+the mini-batch are encoded in ONE batched pass and the first violator is picked on the device, with the
+same random draws in the same order, so the selected triples are the ones the reference would select.
+(With ``batchSize > 1`` regularisation and clamping are applied once per mini-batch rather than after
+every sample; for the reference's default ``batchSize=1`` the two coincide.)
+
+Corpus files (insuranceQA "ibmprep" layout, prepareData.lua:40-250) are parsed when present; otherwise a
+synthetic corpus of the same structure is generated (questions share vocabulary with their answers so
+that the task is learnable).
+"""
+from __future__ import annotations
+
+import os
+import random
+import time
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Tuple
+
+import torch
+
+from .. import t7
+from ..models.bicnn import BiCNN, gesd, margin_ranking, pad_sentences
+from ..utils import Timers
+
+SENTBEGIN, SENTEND = "SENTBEGIN", "SENTEND"
+
+
+@dataclass
+class Corpus:
+    word2idx: Dict[str, int]
+    idx2word: List[str]
+    vectors: torch.Tensor                    # [V, E] initial embeddings (pretrained or random for OOV)
+    answers: List[torch.Tensor]              # label -> token ids (mapLabel2AnswerIdx)
+    train: List[Tuple[List[int], torch.Tensor, torch.Tensor]]      # (labels, question, answer)
+    valid: List[Tuple[List[int], torch.Tensor, List[int]]]         # (targets, question, pool)
+    test1: List[Tuple[List[int], torch.Tensor, List[int]]] = field(default_factory=list)
+    test2: List[Tuple[List[int], torch.Tensor, List[int]]] = field(default_factory=list)
+
+
+def _wrap(ids: List[int], begin: int, end: int, kw: int) -> torch.Tensor:
+    """prepareData.lua:90,102: ``contConvWidth`` SENTBEGIN tokens, the words, ``contConvWidth-1`` SENTEND."""
+    return torch.tensor([begin] * kw + ids + [end] * (kw - 1), dtype=torch.long)
+
+
+def synthetic_corpus(vocab: int = 2000, n_answers: int = 200, n_train: int = 400, n_eval: int = 60, pool: int = 20,
+                     emb_dim: int = 100, kw: int = 2, seed: int = 0) -> Corpus:
+    rng = random.Random(seed)
+    words = [SENTBEGIN, SENTEND] + [f"w{i}" for i in range(vocab - 2)]
+    w2i = {w: i for i, w in enumerate(words)}
+    g = torch.Generator().manual_seed(seed)
+    vectors = torch.rand(vocab, emb_dim, generator=g)     # math.random() OOV embeddings (prepareData.lua:95-97)
+    topic_words = [[rng.randrange(2, vocab) for _ in range(12)] for _ in range(n_answers)]
+    answers = [_wrap([rng.choice(tw) for _ in range(rng.randint(6, 14))], 0, 1, kw) for tw in topic_words]
+
+    def question(label):
+        return _wrap([rng.choice(topic_words[label]) for _ in range(rng.randint(4, 9))], 0, 1, kw)
+
+    train = []
+    for _ in range(n_train):
+        lab = rng.randrange(n_answers)
+        train.append(([lab], question(lab), answers[lab]))
+
+    def evalset(n):
+        out = []
+        for _ in range(n):
+            lab = rng.randrange(n_answers)
+            cand = rng.sample(range(n_answers), pool - 1)
+            if lab not in cand:
+                cand.append(lab)
+            out.append(([lab], question(lab), cand))
+        return out
+
+    return Corpus(w2i, words, vectors, answers, train, evalset(n_eval), evalset(n_eval), evalset(n_eval))
+
+
+def parse_corpus(opt: dict) -> Corpus:
+    """prepareData.lua restated: embeddings file, label2answers, train/valid/test files."""
+    kw, E = opt["contConvWidth"], opt["embeddingDim"]
+    w2i: Dict[str, int] = {}
+    i2w: List[str] = []
+    vecs: List[List[float]] = []
+
+    def add(word, vec=None):
+        if word not in w2i:
+            w2i[word] = len(i2w)
+            i2w.append(word)
+            vecs.append(vec if vec is not None else [random.random() for _ in range(E)])
+        return w2i[word]
+
+    with open(opt["embeddingFile"]) as f:
+        for line in f:
+            parts = line.split()
+            if len(parts) == E + 1:
+                add(parts[0], [float(x) for x in parts[1:]])
+    add(SENTBEGIN)
+    add(SENTEND)
+    ids = lambda text: _wrap([add(w) for w in text.split()], w2i[SENTBEGIN], w2i[SENTEND], kw)
+    answers: Dict[int, torch.Tensor] = {}
+    with open(opt["label2answFile"]) as f:
+        for line in f:
+            lab, text = line.rstrip("\n").split("\t", 1)
+            answers[int(lab)] = ids(text)
+    n_lab = max(answers) if answers else 0
+    ans_list = [answers.get(i + 1, torch.zeros(kw * 2 - 1, dtype=torch.long)) for i in range(n_lab)]   # 1-based labels
+
+    train = []
+    with open(opt["trainFile"]) as f:
+        for line in f:
+            p = line.rstrip("\n").split("\t")
+            if len(p) >= 4:
+                train.append(([int(x) - 1 for x in p[0].split()], ids(p[2]), ids(p[3])))
+
+    def evalfile(path):
+        out = []
+        if not path or not os.path.exists(path):
+            return out
+        with open(path) as f:
+            for line in f:
+                p = line.rstrip("\n").split("\t")
+                if len(p) >= 3:
+                    out.append(([int(x) - 1 for x in p[0].split()], ids(p[1]), [int(x) - 1 for x in p[2].split()]))
+        return out
+
+    return Corpus(w2i, i2w, torch.tensor(vecs, dtype=torch.float32), ans_list, train, evalfile(opt["validFile"]),
+                  evalfile(opt.get("testFile1")), evalfile(opt.get("testFile2")))
+
+
+def save_binary(corpus: Corpus, prefix: str = "binary_") -> None:
+    """The ``-preloadBinary`` cache (plaunch.lua:218-229) in Torch7 format (1-based ids, like the reference)."""
+    t7.save(prefix + "mapWordStr2WordIdx", {w: i + 1 for w, i in corpus.word2idx.items()})
+    t7.save(prefix + "mapWordIdx2WordStr", {i + 1: w for i, w in enumerate(corpus.idx2word)})
+    t7.save(prefix + "mapWordIdx2Vector", {i + 1: v.tolist() for i, v in enumerate(corpus.vectors)})
+    t7.save(prefix + "mapLabel2AnswerIdx", {i + 1: (a + 1).float() for i, a in enumerate(corpus.answers)})
+
+
+class BiCNNTrainer:
+    """feval / test / driver around a :class:`BiCNN` with flat parameters (bicnn.lua:245-262)."""
+
+    def __init__(self, corpus: Corpus, opt: dict, device="cpu", rank: int = 0):
+        self.c, self.opt, self.rank = corpus, opt, rank
+        self.dev = torch.device(device)
+        self.model = BiCNN(len(corpus.idx2word), opt["embeddingDim"], opt["wordHiddenDim"], opt["numFilters"],
+                           opt["contConvWidth"], corpus.vectors).to(self.dev)
+        ps = self.model.param_list()
+        n = sum(p.numel() for p in ps)
+        self.parameters = torch.zeros(n, device=self.dev)
+        self.gradParameters = torch.zeros(n, device=self.dev)
+        o = 0
+        for p in ps:                      # model:getParameters(): one flat storage the tensors alias
+            k = p.numel()
+            self.parameters[o:o + k].copy_(p.detach().reshape(-1))
+            p.data = self.parameters[o:o + k].view_as(p)
+            p.grad = self.gradParameters[o:o + k].view_as(p)
+            o += k
+        if opt.get("loadmodel", "none") != "none":
+            self.parameters.copy_(t7.load(opt["loadmodel"]).to(self.dev))     # bicnn.lua:259-261
+        self.rng = random.Random(rank)    # math.randomseed(rank) (plaunch.lua:114-115)
+        self.tm = Timers()
+        self.loss, self.loss_times = 0.0, 0
+        self.best = {}
+        self.t_start = time.perf_counter()
+        self.batch: List[int] = []
+        self._ans_tokens, self._ans_lens = pad_sentences(corpus.answers, self.dev)
+
+    # -- feval (bicnn.lua:279-420) ----------------------------------------------------------------
+    def _draw_negatives(self, targets: List[int]) -> List[int]:
+        """The reference's rejection sampling (bicnn.lua:327-334), all ``maxnegsample`` draws up front."""
+        tset, A = set(targets), len(self.c.answers)
+        out = []
+        for _ in range(self.opt["maxnegsample"]):
+            while True:
+                j = self.rng.randrange(A)
+                if j not in tset:
+                    break
+            out.append(j)
+        return out
+
+    def feval(self, x: torch.Tensor):
+        opt, m, dev = self.opt, self.model, self.dev
+        if x is not self.parameters:
+            self.parameters.copy_(x)
+        self.gradParameters.zero_()
+        samples = [self.c.train[i] for i in self.batch]
+        K = opt["maxnegsample"]
+        with self.tm("fprop"), torch.no_grad():
+            qt, ql = pad_sentences([s[1] for s in samples], dev)
+            at, al = pad_sentences([s[2] for s in samples], dev)
+            negs = [self._draw_negatives(s[0]) for s in samples]
+            q = m.encode(qt, ql)
+            s_pos = gesd(q, m.encode(at, al))
+            neg_idx = torch.tensor(negs, device=dev)                           # [B, K]
+            cand = m.encode(self._ans_tokens[neg_idx.view(-1)], self._ans_lens[neg_idx.view(-1)])
+            s_neg = gesd(q.repeat_interleave(K, 0), cand).view(len(samples), K)
+            viol = (s_pos[:, None] - s_neg) < opt["margin"]                    # bicnn.lua:351-358
+            first = torch.where(viol.any(1), viol.float().argmax(1), torch.full((len(samples),), -1, device=dev))
+        keep = (first >= 0).nonzero().flatten().tolist()
+        f = 0.0
+        if keep:
+            with self.tm("bprop"):
+                sel = [negs[i][int(first[i])] for i in keep]
+                qt2, ql2 = qt[keep], ql[keep]
+                nt, nl = self._ans_tokens[sel], self._ans_lens[sel]
+                qv = m.encode(qt2, ql2)
+                loss = margin_ranking(gesd(qv, m.encode(at[keep], al[keep])), gesd(qv, m.encode(nt, nl)),
+                                      opt["margin"]).sum()
+                loss.backward()
+                f = float(loss)
+            g, p = self.gradParameters, self.parameters
+            if opt["L1reg"] != 0:                                              # bicnn.lua:398-402
+                f += opt["L1reg"] * float(p.abs().sum())
+                g.add_(torch.sign(p) * opt["L1reg"])
+            if opt["L2reg"] != 0:                                              # bicnn.lua:403-408
+                f += opt["L2reg"] * float((p * p).sum()) / 2
+                g.add_(p * opt["L2reg"])
+            g.clamp_(-opt["gradClip"], opt["gradClip"])                        # bicnn.lua:409
+        self.loss += f
+        self.loss_times += 1
+        if self.loss_times % 2000 == 0:
+            print(f"Client {self.rank}: curr time: {time.perf_counter() - self.t_start + opt['prevtime']:.2f}, "
+                  f"training loss avg. : {self.loss / self.loss_times:.5f} ")
+            self.loss, self.loss_times = 0.0, 0
+        return f, self.gradParameters
+
+    # -- evaluation (bicnn.lua:422-571) --------------------------------------------------------------
+    @torch.no_grad()
+    def test(self, dataset, name="valid") -> float:
+        if not dataset:
+            return 0.0
+        with self.tm("test"):
+            m = self.model
+            emb = torch.cat([m.encode(self._ans_tokens[i:i + 256], self._ans_lens[i:i + 256])
+                             for i in range(0, len(self.c.answers), 256)])
+            qt, ql = pad_sentences([d[1] for d in dataset], self.dev)
+            qv = torch.cat([m.encode(qt[i:i + 256], ql[i:i + 256]) for i in range(0, len(dataset), 256)])
+            correct = 0
+            for i, (targets, _, pool) in enumerate(dataset):
+                sims = gesd(qv[i:i + 1].expand(len(pool), -1), emb[pool])
+                # ``simi >= most_simi`` keeps the LAST maximum (bicnn.lua:443-446)
+                best = len(pool) - 1 - int(torch.flip(sims, [0]).argmax())
+                correct += int(pool[best] in targets)
+        acc = correct / len(dataset)
+        self.best[name] = max(self.best.get(name, 0.0), acc)
+        print(f"Client {self.rank}: curr time: {time.perf_counter() - self.t_start + self.opt['prevtime']:.2f}, "
+              f"Accuracy: {acc:.4f}, best Accuracy: {self.best[name]:.4f} on {name} ")
+        return acc
+
+    def test3(self):
+        return [self.test(self.c.valid, "file1"), self.test(self.c.test1, "file2"), self.test(self.c.test2, "file3")]
+
+    def save(self, prefix: str) -> str:
+        """bicnn.lua:590-594: the flat parameter tensor as ``<prefix>_<elapsed>_model`` (Torch7)."""
+        path = f"{prefix}_{time.perf_counter() - self.t_start + self.opt['prevtime']:010.2f}_model"
+        t7.save(path, self.parameters.detach().cpu())
+        return path
+
+
+def optimizer_for(opt: dict, pc):
+    """bicnn.lua:126-245: option table -> (optimizer function, config)."""
+    from ..optim import reference as R
+    name = opt["optimization"]
+    if name == "sgd":
+        return R.msgdsingle, {"lr": opt["learningRate"], "lrd": opt["weightDecay"], "mom": opt["momentum"], "pclient": pc}
+    if name == "downpour":
+        return R.downpour, {"lr": opt["learningRate"], "lrd": opt["weightDecay"], "pclient": pc, "su": opt["commperiod"]}
+    if name == "eamsgd":
+        return R.eamsgd, {"lr": opt["learningRate"], "lrd": opt["weightDecay"], "pclient": pc, "su": opt["commperiod"],
+                          "mva": opt["movingrate"], "mom": opt["momentum"]}
+    rules = {
+        "rmsprop": dict(mode=opt["modeRMSProp"], decay=opt["decayRMSProp"], lr=opt["lrRMSProp"],
+                        momentum=opt["momentumRMSProp"], epsilon=opt["epsilonRMSProp"]),
+        "adam": dict(mode=opt["modeAdam"], lr=opt["lrAdam"], beta1=opt["beta1Adam"], beta2=opt["beta2Adam"],
+                     epsilon=opt["epsilonAdam"]),
+        "adagrad": dict(mode=opt["modeAdagrad"], lr=opt["lrAdagrad"], lrd=opt["lrDecayAdagrad"],
+                        epsilon=opt["epsilonAdagrad"]),
+        "adadelta": dict(mode=opt["modeAdadelta"], rho=opt["rhoAdadelta"], lr=opt["lrAdadelta"],
+                         epsilon=opt["epsilonAdadelta"]),
+    }
+    rules["adamax"] = dict(rules["adam"])
+    base = name[:-6] if name.endswith("single") else name
+    if base not in rules:
+        raise ValueError("unknown optimization method")
+    cfg = dict(rules[base])
+    cfg["pclient"] = pc
+    if not name.endswith("single"):
+        cfg["su"] = opt["commperiod"]
+    return R.OPTIMIZERS[name], cfg
+
+
+def run_trainer(tr: BiCNNTrainer, pc, is_tester: bool, also_test: bool) -> dict:
+    """bicnn.lua:575-651: the tester role loops pull -> test3 -> save -> sleep (bounded by ``maxEvals``; the
+    reference never exits, TODO at :581); trainers run epochs of mini-batches through the optimizer."""
+    opt = tr.opt
+    if pc is not None:
+        pc.start(tr.parameters, tr.gradParameters)
+    out = {"acc": [], "loss": []}
+    if is_tester:
+        for _ in range(opt.get("maxEvals", 3)):
+            t0 = time.perf_counter()
+            pc.async_recv_param()
+            pc.wait()
+            print(f"Client {tr.rank}: communication time: {time.perf_counter() - t0:.2f} ")
+            out["acc"].append(tr.test3())
+            if opt["outputprefix"] != "none":
+                tr.save(opt["outputprefix"])
+            time.sleep(opt["validSleepTime"])
+    else:
+        opti, cfg = optimizer_for(opt, pc)
+        n = len(tr.c.train)
+        pversion = 0
+        for epoch in range(1, opt["epoch"] + 1):
+            t0 = time.perf_counter()
+            shuffle = torch.randperm(n).tolist()
+            for t in range(0, n, opt["batchSize"]):
+                tr.batch = shuffle[t:t + opt["batchSize"]]
+                _, fx = opti(tr.feval, tr.parameters, cfg)
+                out["loss"].append(fx[0])
+                if also_test and pversion % opt["commperiod"] == 0 and pversion % opt.get("testEvery", 50) == 0:
+                    out["acc"].append(tr.test3())
+                    if opt["outputprefix"] != "none":
+                        tr.save(opt["outputprefix"])
+                pversion += 1
+            print(f"client {tr.rank}: epoch {epoch} done,  for {time.perf_counter() - t0} seconds ")
+        tr.tm["sync"] = cfg.get("dusync", 0.0)
+    print("Before Stop !!!!!!!!!!!!!!!!!!!!!!!!!!!!!!!!!!!!!!!")
+    if pc is not None:
+        pc.stop()
+    print(tr.rank, "total training time", time.perf_counter() - tr.t_start)
+    print(tr.rank, "factor time", dict(tr.tm))
+    return out
