@@ -1,0 +1,207 @@
+"""Library-call GPU baseline for bench.py (``--impl torch``): the same model, data path and EAMSGD
+algorithm expressed with PyTorch library kernels only -- cuDNN convolutions / cuBLAS GEMMs through
+autograd (TF32 allowed, the same precision class as the tcgen05 path), torch elementwise ops for the
+Nesterov / elastic math, and NCCL collectives for the exchange (pull = all_gather of the centre shards,
+push = reduce_scatter of the elastic differences).  This is "the path that only calls NCCL" that
+BASELINE.json names as the baseline; nothing from mpit_b200's kernels or engine is on it.
+
+The reference's own build (Lua/Torch7 + MPI) cannot be installed on this image.
+"""
+from __future__ import annotations
+
+import json
+import os
+import sys
+import time
+
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F
+
+from mpit_b200.models.cifar_cnn import TorchCifarCNN, flat_from_torch, torch7_reset
+from mpit_b200.parallel.center import partition
+
+
+class TorchEAMSGD:
+    def __init__(self, dev, world, rank, B, lr=1e-2, mom=0.99, su=10, mva=0.9, graphs=True):
+        torch.backends.cudnn.allow_tf32 = True
+        torch.backends.cuda.matmul.allow_tf32 = True
+        torch.backends.cudnn.benchmark = True
+        self.dev, self.world, self.rank, self.B = dev, world, rank, B
+        self.lr, self.mom, self.su, self.mva = lr, mom, su, mva
+        g = torch.Generator().manual_seed(1 + rank)
+        m = TorchCifarCNN()
+        torch7_reset(m, g)
+        self.model = m.to(dev).to(memory_format=torch.channels_last)
+        self.params = [p for p in self.model.parameters()]
+        self.n = sum(p.numel() for p in self.params)
+        self.v = [torch.zeros_like(p) for p in self.params]
+        self.d = [torch.zeros_like(p) for p in self.params]
+        parts = partition(self.n, world)
+        self.shard_cap = max(s for _, s in parts)
+        self.parts = parts
+        self.center_shard = torch.zeros(self.shard_cap, device=dev)
+        flat = flat_from_torch(self.model)
+        if world > 1:
+            dist.broadcast(flat, 0)       # seed: centre := first worker's theta (pclient.lua:131-133)
+        off, sz = parts[rank]
+        self.center_shard[:sz].copy_(flat[off:off + sz])
+        self.t = 0
+        self.x_u8 = torch.zeros(B, 3, 32, 32, dtype=torch.uint8, device=dev)
+        self.labels = torch.zeros(B, dtype=torch.int64, device=dev)
+        self.crop = torch.zeros(B, 2, dtype=torch.int64, device=dev)
+        self.loss = torch.zeros((), device=dev)
+        self.ar = torch.arange(28, device=dev)
+        self.bi = torch.arange(B, device=dev)
+        self.graphs = graphs
+        self.graph = None
+        self.have_d = False
+
+    def set_batch(self, x, y, c):
+        self.x_u8.copy_(x, non_blocking=True)
+        self.labels.copy_(y, non_blocking=True)
+        self.crop.copy_(c, non_blocking=True)
+
+    def _local(self):
+        """Nesterov look-ahead, forward/backward, apply (asyncsgd/optim-eamsgd.lua:26-47)."""
+        with torch.no_grad():
+            torch._foreach_mul_(self.v, self.mom)
+            torch._foreach_add_(self.params, self.v)
+        rows = self.crop[:, 0:1] + self.ar[None, :]
+        cols = self.crop[:, 1:2] + self.ar[None, :]
+        x = self.x_u8[self.bi[:, None, None], :, rows[:, :, None], cols[:, None, :]]      # [B,28,28,3]
+        x = x.permute(0, 3, 1, 2).float().div_(255.0).contiguous(memory_format=torch.channels_last)
+        for p in self.params:
+            p.grad = None
+        loss = F.nll_loss(self.model(x), self.labels)
+        loss.backward()
+        self.loss.copy_(loss.detach())
+        with torch.no_grad():
+            grads = [p.grad for p in self.params]
+            torch._foreach_add_(self.params, grads, alpha=-self.lr)
+            torch._foreach_add_(self.v, grads, alpha=-self.lr)
+
+    def _sync(self):
+        """Elastic exchange with NCCL collectives: pull (all_gather), d = mva (x - centre), push (reduce_scatter)."""
+        with torch.no_grad():
+            if self.world > 1:
+                full = torch.empty(self.shard_cap * self.world, device=self.dev)
+                dist.all_gather_into_tensor(full, self.center_shard)
+                center = torch.cat([full[r * self.shard_cap: r * self.shard_cap + sz] for r, (_, sz) in enumerate(self.parts)])
+            else:
+                center = self.center_shard[:self.n]
+            x = torch.cat([p.reshape(-1) for p in self.params])
+            dflat = (x - center) * self.mva
+            if self.world > 1:
+                pad = torch.zeros(self.shard_cap * self.world, device=self.dev)
+                for r, (off, sz) in enumerate(self.parts):
+                    pad[r * self.shard_cap: r * self.shard_cap + sz] = dflat[off:off + sz]
+                out = torch.empty(self.shard_cap, device=self.dev)
+                dist.reduce_scatter_tensor(out, pad)
+                self.center_shard.add_(out)
+            else:
+                self.center_shard[:self.n].add_(dflat)
+            o = 0
+            for dd in self.d:
+                k = dd.numel()
+                dd.copy_(dflat[o:o + k].view_as(dd))
+                o += k
+
+    def step(self):
+        do_sync = self.t % self.su == 0
+        if do_sync:
+            self._sync()
+        if self.graphs and self.t >= 3:
+            if self.graph is None:
+                torch.cuda.synchronize()
+                self.graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(self.graph):
+                    self._local()
+            self.graph.replay()
+        else:
+            self._local()
+        if do_sync:
+            with torch.no_grad():
+                torch._foreach_sub_(self.params, self.d)     # w -= sug (optim-eamsgd.lua:70)
+        self.t += 1
+
+
+def run(args, rank, world, dev):
+    B = args.batch
+    from mpit_b200.workloads.cifar import synthetic_cifar
+    from mpit_b200.models.cifar_cnn import random_crop_offsets
+    tr = TorchEAMSGD(dev, world, rank, B, su=args.tau, mva=0.9 / world, graphs=not args.no_graphs)
+    n_host = 64 * B
+    hx, hy = synthetic_cifar(n_host, seed=100 + rank)
+    hy = hy.long().pin_memory()
+    n_dev = 352
+    dx = torch.randint(0, 256, (n_dev, B, 3, 32, 32), dtype=torch.uint8, device=dev)
+    dy = torch.randint(0, 10, (n_dev, B), dtype=torch.int64, device=dev)
+    dc = torch.randint(0, 5, (n_dev, B, 2), dtype=torch.int64, device=dev)
+    gen = torch.Generator().manual_seed(7 + rank)
+    sx = torch.empty(B, 3, 32, 32, dtype=torch.uint8).pin_memory()
+    sy = torch.empty(B, dtype=torch.int64).pin_memory()
+    sc = torch.empty(B, 2, dtype=torch.int64).pin_memory()
+    loss_host = torch.zeros(1).pin_memory()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def dev_step(i):
+        j = i % n_dev
+        tr.set_batch(dx[j], dy[j], dc[j])
+        tr.step()
+
+    def e2e_step(i):
+        lo = (i * B) % n_host
+        sx.copy_(hx[lo:lo + B])
+        sy.copy_(hy[lo:lo + B])
+        sc.copy_(random_crop_offsets(B, gen).long())
+        tr.set_batch(sx, sy, sc)
+        tr.step()
+        loss_host.copy_(tr.loss.view(1), non_blocking=False)     # device -> host read of the step's loss
+        return float(loss_host)
+
+    for i in range(max(args.warmup, 3 * args.tau + 3)):
+        dev_step(i)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        dev_step(i)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    for i in range(5):
+        e2e_step(i)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        last = e2e_step(i)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    gb = B * world
+    if rank == 0:
+        print(json.dumps({
+            "metric": "samples/sec (device-timed, max over ranks) CIFAR-10 CNN EAMSGD tau=10",
+            "value": round(gb * args.steps / (float(t[0]) / 1e3), 1), "unit": "samples/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(float(t[0]) / args.steps, 5),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "tf32 (cuDNN/cuBLAS allow_tf32)",
+            "data": "synthetic CIFAR-10-shaped uint8 images, random-init weights", "impl": "torch",
+            "config": {"model": "CIFAR-10 7-layer CNN", "global_batch": gb, "per_gpu_batch": B, "optimizer": "eamsgd",
+                       "tau": args.tau, "parallelism": f"sync-elastic dp{world} via NCCL all_gather/reduce_scatter",
+                       "cuda_graphs": not args.no_graphs},
+            "e2e": {"value": round(gb * args.steps / (float(t[1]) / 1e3), 1), "unit": "samples/s",
+                    "ms_per_step": round(float(t[1]) / args.steps, 5), "h2d_bytes_per_step": int(sx.numel() + 8 * B + 16 * B),
+                    "d2h_bytes_per_step": 4},
+            "gpu_launches": 0, "loss": round(last, 4)}))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0

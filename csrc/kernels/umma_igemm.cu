@@ -20,6 +20,7 @@
 #include "common.cuh"
 #include "umma.cuh"
 #include <string.h>
+#include <stdlib.h>
 
 namespace mpit {
 using namespace umma;
@@ -44,17 +45,20 @@ struct IgemmParams {
   const int* crop;
   const unsigned long long* rng;
   int* err;                  // set to 1 when a bounded pipeline wait expires
+  int stages;                // smem pipeline depth (2..kMaxStages), chosen per launch
+  long long* dbg;            // optional per-CTA timeline (8 clock64 stamps per CTA), null in production
 };
 
-constexpr int kStages = 4;
+constexpr int kMaxStages = 12;
 constexpr int kABytes = 128 * 128;  // 128 rows x 32 tf32
+constexpr int kSmemBudget = 200 * 1024;
 
 template <int BLOCK_N>
 struct SmemLayout {
   static constexpr int kBBytes = BLOCK_N * 128;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kBarOff = kStages * kStageBytes;
-  static constexpr int kTotal = kBarOff + 256 + 1024;  // barriers + alignment slack
+  static constexpr int kMaxFit = (kSmemBudget / kStageBytes) < kMaxStages ? (kSmemBudget / kStageBytes) : kMaxStages;
+  static constexpr int total(int stages) { return stages * kStageBytes + 256 + 1024; }   // + barriers + align slack
 };
 
 __device__ __forceinline__ void subtile_origin(const IgemmParams& p, int s, int& n0, int& oh0, int& ow0) {
@@ -73,9 +77,10 @@ umma_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   using L = SmemLayout<BLOCK_N>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
-  uint64_t* empty_bar = full_bar + kStages;
-  uint64_t* tmem_full = empty_bar + kStages;
+  const int kStages = p.stages;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * L::kStageBytes);
+  uint64_t* empty_bar = full_bar + kMaxStages;
+  uint64_t* tmem_full = empty_bar + kMaxStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -83,6 +88,8 @@ umma_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   const int n_tile0 = blockIdx.y * BLOCK_N;
   const int rows_per_sub = 128 / p.nsub;
 
+  long long* dbg = p.dbg ? p.dbg + 8 * (blockIdx.y * gridDim.x + blockIdx.x) : nullptr;
+  if (dbg && threadIdx.x == 0) dbg[0] = clock64();
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmap_a);
     prefetch_tmap(&tmap_b);
@@ -95,6 +102,7 @@ umma_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (dbg && threadIdx.x == 0) dbg[1] = clock64();   // prologue done
 
   if (warp == 0) {
     // ===== TMA producer =====
@@ -119,6 +127,7 @@ umma_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         tma_load_2d(b_dst, &tmap_b, &full_bar[stage], kb * 32, n_tile0);
         if (++stage == kStages) { stage = 0; phase ^= 1; }
       }
+      if (dbg) dbg[2] = clock64();   // last TMA issued
     }
   } else if (warp == 1) {
     // ===== MMA issuer =====
@@ -127,6 +136,7 @@ umma_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       int stage = 0, phase = 0;
       for (int kb = 0; kb < p.num_kb; ++kb) {
         if (!mbar_wait(&full_bar[stage], phase)) { if (p.err) *p.err = 2; break; }
+        if (dbg && kb == 0) dbg[3] = clock64();   // first operands landed
         tc_fence_after();
         uint32_t a_addr = smem_u32(smem + stage * L::kStageBytes);
         uint32_t b_addr = a_addr + kABytes;
@@ -140,6 +150,7 @@ umma_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         if (++stage == kStages) { stage = 0; phase ^= 1; }
       }
       mma_commit(tmem_full);             // accumulator complete
+      if (dbg) dbg[4] = clock64();       // last MMA issued
     }
   } else {
     // ===== epilogue: warps 2..5, TMEM lane quadrant = warp % 4 =====
@@ -152,6 +163,7 @@ umma_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     const int n = n0 + nn, oh = oh0 + h_, ow = ow0 + w_;
     const bool valid = n < p.B && oh < p.OH && ow < p.OW;
     if (!mbar_wait(tmem_full, 0)) { if (p.err) *p.err = 3; }
+    if (dbg && threadIdx.x == 64) dbg[5] = clock64();   // accumulator ready
     tc_fence_after();
     unsigned long long seed = 0, step = 0;
     if (p.dropout) { seed = p.rng[0]; step = p.rng[1]; }
@@ -261,12 +273,14 @@ umma_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       }
     }
     tc_fence_before();
+    if (dbg && threadIdx.x == 64) dbg[6] = clock64();   // epilogue done
   }
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, BLOCK_N);
   }
+  if (dbg && threadIdx.x == 0) dbg[7] = clock64();
 }
 
 // ---- host side -----------------------------------------------------------------------------------
@@ -284,17 +298,24 @@ static decltype(&cuTensorMapEncodeTiled) get_encode() {
 }
 
 template <int BLOCK_N>
-static int launch_igemm(const CUtensorMap* ta, const CUtensorMap* tb, const IgemmParams& p, int m_tiles,
+static int launch_igemm(const CUtensorMap* ta, const CUtensorMap* tb, IgemmParams p, int m_tiles,
                         cudaStream_t st) {
   using L = SmemLayout<BLOCK_N>;
   static bool attr_done = false;
   if (!attr_done) {
     MPIT_CUDA_TRY(cudaFuncSetAttribute(umma_igemm_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       L::kTotal));
+                                       L::total(L::kMaxFit)));
     attr_done = true;
   }
   dim3 grid(m_tiles, p.N / BLOCK_N);
-  umma_igemm_kernel<BLOCK_N><<<grid, 192, L::kTotal, st>>>(*ta, *tb, p);
+  // Pipeline depth: deep (latency hiding) when the grid leaves SMs to spare or k-loops are long;
+  // 4 stages when many short CTAs should co-reside two per SM.
+  int ctas = m_tiles * (p.N / BLOCK_N);
+  int stages = (ctas > 2 * MPIT_NUM_SMS && p.num_kb <= 8) ? 4 : L::kMaxFit;
+  if (stages > p.num_kb) stages = p.num_kb < 2 ? 2 : p.num_kb;
+  if (stages > L::kMaxFit) stages = L::kMaxFit;
+  p.stages = stages;
+  umma_igemm_kernel<BLOCK_N><<<grid, 192, L::total(stages), st>>>(*ta, *tb, p);
   MPIT_LAUNCH_CHECK();
   return 0;
 }
@@ -335,6 +356,14 @@ int mpit_umma_igemm(const void* tmap_a128, const void* tmap_b128, const int* geo
                     const unsigned char* aux_idx, const int* crop, const unsigned long long* rng, int* err,
                     int block_n, void* stream) {
   IgemmParams p{};
+  {
+    // MPIT_IGEMM_DBG=<device address of a long long[8 * ctas] buffer>: per-CTA timeline for tuning
+    static long long* dbg_buf = []() -> long long* {
+      const char* e = getenv("MPIT_IGEMM_DBG");
+      return e ? reinterpret_cast<long long*>(strtoull(e, nullptr, 0)) : nullptr;
+    }();
+    p.dbg = dbg_buf;
+  }
   p.nsub = geom17[0]; p.tw = geom17[1]; p.th = geom17[2]; p.tn = geom17[3];
   p.tiles_w = geom17[4]; p.tiles_h = geom17[5]; p.kw_it = geom17[6]; p.cb = geom17[7];
   p.num_kb = geom17[8]; p.sgn = geom17[9]; p.B = geom17[10]; p.OH = geom17[11]; p.OW = geom17[12];
