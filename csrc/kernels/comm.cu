@@ -19,26 +19,36 @@
 
 namespace mpit {
 
-// Walks the flat vector in units of 4 consecutive elements that never straddle a shard.
+// Walks the flat vector in units of 4 consecutive elements ("quads") that never straddle a shard.
+// The walk is organised in chunks of kChunkQuads quads that are dealt round-robin over the shards,
+// starting at the shard after the caller's own: concurrently running CTAs therefore talk to all
+// owners at once and the ranks never gang up on one owner (every rank walking shard 0, then shard 1,
+// ... in lockstep would serialise the whole exchange on one GPU's links at a time).
+constexpr long long kChunkQuads = 1024;   // 16 KiB per chunk
 struct QuadWalk {
   Partition part;
-  long long qps;    // quads per regular shard
-  long long total;  // total quads
-  __host__ __device__ static QuadWalk make(long long n, int S) {
+  long long cps;    // chunks per shard (enough for the largest shard)
+  long long total;  // virtual quads to visit: S * cps * kChunkQuads (some fall outside a shard: cnt = 0)
+  int rank;
+  __host__ __device__ static QuadWalk make(long long n, int S, int rank = 0) {
     QuadWalk w;
     w.part.n = n; w.part.S = S; w.part.base = n / S;
-    w.qps = (w.part.base + 3) / 4;
-    long long last = w.part.size(S - 1);
-    w.total = w.qps * (S - 1) + (last + 3) / 4;
+    long long max_quads = (w.part.size(S - 1) + 3) / 4;
+    w.cps = (max_quads + kChunkQuads - 1) / kChunkQuads;
+    if (w.cps < 1) w.cps = 1;
+    w.total = w.cps * S * kChunkQuads;
+    w.rank = rank;
     return w;
   }
-  __device__ __forceinline__ void at(long long q, int& s, long long& j0, long long& i0, int& cnt) const {
-    s = (qps > 0) ? (int)(q / qps) : part.S - 1;
-    if (s > part.S - 1) s = part.S - 1;
-    j0 = (q - qps * s) * 4;
+  __device__ __forceinline__ void at(long long v, int& s, long long& j0, long long& i0, int& cnt) const {
+    long long c = v / kChunkQuads, within = v - c * kChunkQuads;
+    int lane_shard = (int)(c % part.S);
+    long long k = c / part.S;
+    s = (lane_shard + rank + 1) % part.S;
+    j0 = (k * kChunkQuads + within) * 4;
     i0 = part.begin(s) + j0;
     long long rem = part.size(s) - j0;
-    cnt = rem >= 4 ? 4 : (int)rem;
+    cnt = rem >= 4 ? 4 : (rem > 0 ? (int)rem : 0);
   }
 };
 
@@ -111,6 +121,7 @@ __global__ void __launch_bounds__(256) exchange_kernel(ExchArgs a) {
     int s, cnt;
     long long j0, i0;
     a.walk.at(q, s, j0, i0, cnt);
+    if (cnt == 0) continue;
     float* cptr = a.tab.peer[s] + j0;
     if (MODE == EX_PULL) {
       // x <- centre (MPI_Get).  Issue the remote load first; everything else hides under it.
@@ -386,7 +397,7 @@ static SignalTable make_sig(const unsigned long long* ptrs, int nranks, int rank
   return t;
 }
 
-static int exch_grid(const QuadWalk& w) { return ew_grid(w.total, 256, 2, 8); }
+static int exch_grid(const QuadWalk& w) { return ew_grid(w.total, 256, 4, 8); }
 
 }  // namespace mpit
 
@@ -403,7 +414,7 @@ int mpit_param_pull(const unsigned long long* shard_ptrs, int nranks, int rank, 
   if (nranks < 1 || nranks > MPIT_MAX_RANKS) return MPIT_E_ARG;
   ExchArgs a{};
   a.tab = make_table(shard_ptrs, 0, nranks, rank);
-  a.walk = QuadWalk::make(n, nranks);
+  a.walk = QuadWalk::make(n, nranks, rank);
   a.src = dst; a.wpk = wpk; a.wmap = wmap; a.nmaps = nmaps; a.n = n;
   exchange_kernel<EX_PULL><<<exch_grid(a.walk), 256, 0, (cudaStream_t)stream>>>(a);
   MPIT_LAUNCH_CHECK();
@@ -416,7 +427,7 @@ int mpit_param_put(const unsigned long long* shard_ptrs, int nranks, int rank, c
   if (nranks < 1 || nranks > MPIT_MAX_RANKS) return MPIT_E_ARG;
   ExchArgs a{};
   a.tab = make_table(shard_ptrs, 0, nranks, rank);
-  a.walk = QuadWalk::make(n, nranks);
+  a.walk = QuadWalk::make(n, nranks, rank);
   a.src = const_cast<float*>(src);
   exchange_kernel<EX_PUT><<<exch_grid(a.walk), 256, 0, (cudaStream_t)stream>>>(a);
   MPIT_LAUNCH_CHECK();
@@ -429,7 +440,7 @@ int mpit_push_add(const unsigned long long* shard_ptrs, int nranks, int rank, fl
   if (nranks < 1 || nranks > MPIT_MAX_RANKS) return MPIT_E_ARG;
   ExchArgs a{};
   a.tab = make_table(shard_ptrs, 0, nranks, rank);
-  a.walk = QuadWalk::make(n, nranks);
+  a.walk = QuadWalk::make(n, nranks, rank);
   a.src = src; a.x = const_cast<float*>(params);
   a.scale = scale; a.l1 = l1; a.l2 = l2; a.clip = clip; a.zero_src = zero_src;
   if ((l1 != 0.f || l2 != 0.f) && !params) return MPIT_E_ARG;
@@ -444,7 +455,7 @@ int mpit_elastic_exchange(const unsigned long long* shard_ptrs, int nranks, int 
   if (nranks < 1 || nranks > MPIT_MAX_RANKS) return MPIT_E_ARG;
   ExchArgs a{};
   a.tab = make_table(shard_ptrs, 0, nranks, rank);
-  a.walk = QuadWalk::make(n, nranks);
+  a.walk = QuadWalk::make(n, nranks, rank);
   a.x = const_cast<float*>(x); a.d = d; a.alpha = alpha; a.do_sync = 1;
   exchange_kernel<EX_ELASTIC><<<exch_grid(a.walk), 256, 0, (cudaStream_t)stream>>>(a);
   MPIT_LAUNCH_CHECK();
@@ -459,7 +470,7 @@ int mpit_eamsgd_fused_step(const unsigned long long* shard_ptrs, int nranks, int
   if (nranks < 1 || nranks > MPIT_MAX_RANKS) return MPIT_E_ARG;
   ExchArgs a{};
   a.tab = make_table(shard_ptrs, 0, nranks, rank);
-  a.walk = QuadWalk::make(n, nranks);
+  a.walk = QuadWalk::make(n, nranks, rank);
   a.x = x; a.v = v; a.g = g; a.gmap = gmap; a.d = d; a.wpk = wpk; a.wmap = wmap; a.nmaps = nmaps; a.n = n;
   a.alpha = alpha; a.clr = clr; a.l2wd = l2wd; a.mom_next = mom_next;
   a.do_apply = do_apply; a.use_mom = use_mom; a.do_lookahead = do_lookahead; a.do_sync = do_sync;
