@@ -25,7 +25,9 @@
 namespace mpit {
 using namespace umma;
 
-enum EpiMode : int { EPI_STORE = 0, EPI_POOL = 1, EPI_MASK = 2, EPI_EXPAND = 3 };
+enum EpiMode : int { EPI_STORE = 0, EPI_POOL = 1, EPI_MASK = 2, EPI_EXPAND = 3, EPI_MAXTIME = 4 };
+// `relu` doubles as the activation selector: 0 none, 1 ReLU, 2 Tanh (forward: tanh(x); EPI_MASK: the
+// gradient is multiplied by 1 - aux^2, aux being the stored tanh output).
 
 struct IgemmParams {
   int nsub, tw, th, tn;      // sub-box: tw*th*tn rows, nsub sub-boxes per 128-row tile
@@ -110,7 +112,8 @@ umma_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       int n0[2], oh0[2], ow0[2];
       for (int j = 0; j < p.nsub; ++j) {
         subtile_origin(p, tile * p.nsub + j, n0[j], oh0[j], ow0[j]);
-        if (p.crop && n0[j] < p.B) { oh0[j] += p.crop[2 * n0[j]]; ow0[j] += p.crop[2 * n0[j] + 1]; }
+        // (in MAXTIME mode `crop` carries per-sentence frame counts for the epilogue, not offsets)
+        if (p.crop && p.mode != EPI_MAXTIME && n0[j] < p.B) { oh0[j] += p.crop[2 * n0[j]]; ow0[j] += p.crop[2 * n0[j] + 1]; }
       }
       int stage = 0, phase = 0;
       const int per_kh = p.kw_it * p.cb;
@@ -178,7 +181,8 @@ umma_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 #pragma unroll
         for (int c = 0; c < 32; ++c) {
           float x = v[c] + (p.bias ? p.bias[col0 + c] : 0.f);
-          if (p.relu) x = fmaxf(x, 0.f);
+          if (p.relu == 1) x = fmaxf(x, 0.f);
+          else if (p.relu == 2) x = tanhf(x);
           v[c] = x;
         }
         if (p.dropout) {
@@ -234,13 +238,43 @@ umma_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           for (int c4 = 0; c4 < 8; ++c4) {
             float4 a = ld4(p.aux + obase + 4 * c4);
             float4 o;
-            o.x = a.x > 0.f ? v[4 * c4 + 0] * p.scale : 0.f;
-            o.y = a.y > 0.f ? v[4 * c4 + 1] * p.scale : 0.f;
-            o.z = a.z > 0.f ? v[4 * c4 + 2] * p.scale : 0.f;
-            o.w = a.w > 0.f ? v[4 * c4 + 3] * p.scale : 0.f;
+            if (p.relu == 2) {   // d tanh: g * (1 - h^2)
+              o.x = v[4 * c4 + 0] * (1.f - a.x * a.x) * p.scale;
+              o.y = v[4 * c4 + 1] * (1.f - a.y * a.y) * p.scale;
+              o.z = v[4 * c4 + 2] * (1.f - a.z * a.z) * p.scale;
+              o.w = v[4 * c4 + 3] * (1.f - a.w * a.w) * p.scale;
+            } else {
+              o.x = a.x > 0.f ? v[4 * c4 + 0] * p.scale : 0.f;
+              o.y = a.y > 0.f ? v[4 * c4 + 1] * p.scale : 0.f;
+              o.z = a.z > 0.f ? v[4 * c4 + 2] * p.scale : 0.f;
+              o.w = a.w > 0.f ? v[4 * c4 + 3] * p.scale : 0.f;
+            }
             st4(p.out + obase + 4 * c4, o);
           }
         }
+      } else if (p.mode == EPI_MAXTIME) {
+        // Temporal convolution -> Max over time -> ReLU (BiCNN/bicnn.lua:59,76-84).  A warp holds the
+        // 32 time steps of one sentence (tile = tn sentences x 32 frames): bias, mask frames past the
+        // sentence end, butterfly max with the arg-max, then lane c publishes column c with one
+        // 64-bit atomicMax of (bits(max(v,0)) << 32 | t): relu(max) = max over t of max(v,0), and
+        // non-negative floats order like their bit patterns, so several w-tiles of a long sentence
+        // combine correctly.  `crop` carries the per-sentence frame counts here.
+        const int frames = (n < p.B) ? p.crop[n] : 0;
+        const bool live = valid && ow < frames;
+        unsigned long long mine = 0ull;
+#pragma unroll
+        for (int c = 0; c < 32; ++c) {
+          float x = live ? fmaxf(v[c] + (p.bias ? p.bias[col0 + c] : 0.f), 0.f) : 0.f;
+          unsigned long long key = ((unsigned long long)__float_as_uint(x) << 32) | (unsigned)(live ? ow : 0);
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+            unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
+            key = other > key ? other : key;
+          }
+          if (lane == c) mine = key;
+        }
+        if (n < p.B && (col0 + lane) < p.N)
+          atomicMax(reinterpret_cast<unsigned long long*>(p.out) + (size_t)n * p.N + col0 + lane, mine);
       } else {  // EPI_EXPAND: un-pool + ReLU mask; rows are pooled positions
         if (valid) {
           size_t pbase = ((((size_t)n * p.OH + oh) * p.OW + ow) * p.N) + col0;

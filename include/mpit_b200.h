@@ -193,6 +193,26 @@ int mpit_multi_wgrad_reduce(int nseg, const unsigned long long* parts, const uns
 int mpit_multi_colsum(int nseg, const unsigned long long* srcs, const unsigned long long* dsts,
                       const long long* rows, const int* cols, void* stream);
 
+/* ---- BiCNN sentence-CNN kernels (csrc/kernels/bicnn.cu) ---------------------------------------- */
+/* LookupTable forward / tied backward (/root/reference/BiCNN/bicnn.lua:30-40). dims multiples of 4. */
+int mpit_embedding_gather(const float* E, const int* tokens, float* out, long long rows, int dim, int ldE, int ld,
+                          void* stream);
+int mpit_embedding_scatter_add(float* dE, const int* tokens, const float* g, const int* row_valid, long long rows,
+                               int dim, int ldE, int ld, void* stream);
+/* Finish of TemporalConvolution -> Max -> ReLU -> Normalize(2) (bicnn.lua:59,76-84; Normalize.lua:11-38):
+ * unpack the (value, argmax) keys written by the max-over-time epilogue of mpit_umma_igemm (mode 4). */
+int mpit_encoder_finish(const unsigned long long* mx, float* r, unsigned char* arg, float* y, float* normp, int S,
+                        int F, int ld, float eps, void* stream);
+/* GESD similarity of P index pairs (bicnn.lua:98-105); stats = {dot, l2} per pair. */
+int mpit_gesd_pairs(const float* y, const int* qi, const int* ai, float* sim, float* stats, int P, int F, int ld,
+                    void* stream);
+/* MarginRankingCriterion (bicnn.lua:121) over triples (pairs 2t, 2t+1) fused with the GESD gradient. */
+int mpit_gesd_margin_bwd(const float* y, const int* qi, const int* ai, const float* sim, const float* stats, float* dy,
+                         float* loss_sum, int triples, int F, int ld, float margin, void* stream);
+/* Backward of Normalize (closed form, cf. Normalize.lua:53-69) -> ReLU -> Max: scatter into dense dC[S][T][ld]. */
+int mpit_encoder_bwd(const float* dy, const float* r, const unsigned char* arg, const float* normp, float* dC, int S,
+                     int F, int ld, int T, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -148,7 +148,11 @@ def main(argv=None) -> int:
             corpus = W.synthetic_corpus(opt["synthVocab"], opt["synthAnswers"], opt["synthTrain"], 20, 10,
                                         opt["embeddingDim"], opt["contConvWidth"], seed=0)
         dev = "cuda" if opt["type"] == "cuda" and torch.cuda.is_available() else "cpu"
-        tr = W.BiCNNTrainer(corpus, opt, dev, rank)
+        if dev == "cuda":     # B200 path: tcgen05 encoder + fused GESD/margin kernels
+            torch.cuda.set_device(rank % torch.cuda.device_count())
+            tr = W.BiCNNKernelTrainer(corpus, opt, f"cuda:{rank % torch.cuda.device_count()}", rank)
+        else:
+            tr = W.BiCNNTrainer(corpus, opt, dev, rank)
         pc = ps.pClient(conf)
         is_tester = opt["validMode"] == "additionalTester" and rank in tranks
         also_test = opt["validMode"] == "lastClient" and rank in tranks

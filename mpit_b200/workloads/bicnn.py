@@ -333,3 +333,107 @@ def run_trainer(tr: BiCNNTrainer, pc, is_tester: bool, also_test: bool) -> dict:
     print(tr.rank, "total training time", time.perf_counter() - tr.t_start)
     print(tr.rank, "factor time", dict(tr.tm))
     return out
+
+
+class BiCNNKernelTrainer(BiCNNTrainer):
+    """``-type cuda``: the same feval / test semantics on one B200 through the kernel engine
+    (models/bicnn_engine.py).  One encoder pass covers the question, the positive answer and all
+    ``maxnegsample`` candidate negatives of every sample of the mini-batch; the first margin violator is
+    picked on the device from that pass and the SAME pass is back-propagated for the selected triples
+    (unselected sentences simply receive a zero gradient), so no second forward is needed."""
+
+    def __init__(self, corpus: Corpus, opt: dict, device="cuda", rank: int = 0):
+        super().__init__(corpus, opt, device, rank)
+        from ..models.bicnn_engine import BiCnnEngine
+        from ..ops import grad_reg_clip
+        self._reg_clip = grad_reg_clip
+        K, B = opt["maxnegsample"], opt["batchSize"]
+        lmax = max(int(a.numel()) for a in corpus.answers)
+        lmax = max([lmax] + [int(s[1].numel()) for s in corpus.train] + [int(s[1].numel()) for s in corpus.valid])
+        self.Lk = (lmax + 31) // 32 * 32
+        self.S_train = (B * (2 + K) + 3) // 4 * 4
+        mk = lambda S: BiCnnEngine(len(corpus.idx2word), S, self.Lk, opt["embeddingDim"], opt["wordHiddenDim"],
+                                   opt["numFilters"], opt["contConvWidth"], self.dev, opt["margin"])
+        self.eng = mk(self.S_train)
+        self.eng_eval = mk(256)
+        self._ans_tok32 = self._fit(self._ans_tokens)
+
+    def _fit(self, tok: torch.Tensor) -> torch.Tensor:
+        out = torch.zeros(tok.shape[0], self.Lk, dtype=torch.int32, device=self.dev)
+        out[:, :tok.shape[1]] = tok.int()
+        return out
+
+    def feval(self, x: torch.Tensor):
+        opt, eng, dev = self.opt, self.eng, self.dev
+        if x is not self.parameters:
+            self.parameters.copy_(x)
+        self.gradParameters.zero_()
+        samples = [self.c.train[i] for i in self.batch]
+        B, K = len(samples), opt["maxnegsample"]
+        with self.tm("fprop"):
+            qt, ql = pad_sentences([s[1] for s in samples], dev)
+            at, al = pad_sentences([s[2] for s in samples], dev)
+            negs = torch.tensor([self._draw_negatives(s[0]) for s in samples], device=dev)       # [B, K]
+            tok = torch.cat([self._fit(qt), self._fit(at), self._ans_tok32[negs.view(-1)]])
+            lens = torch.cat([ql, al, self._ans_lens[negs.view(-1)]]).int()
+            eng.load_flat(self.parameters)
+            eng.set_sentences(tok, lens)
+            eng.encode()
+            ar = torch.arange(B, device=dev, dtype=torch.int32)
+            s_pos = eng.gesd(ar, ar + B)
+            qi_all = ar.repeat_interleave(K)
+            ai_all = (2 * B + torch.arange(B * K, device=dev)).int()
+            s_neg = eng.gesd(qi_all, ai_all).view(B, K)
+            viol = (s_pos[:, None] - s_neg) < opt["margin"]
+            has = viol.any(1)
+            first = viol.float().argmax(1)
+        keep = has.nonzero().flatten()
+        f = 0.0
+        if keep.numel():
+            with self.tm("bprop"):
+                k32 = keep.int()
+                neg_sent = (2 * B + keep * K + first[keep]).int()
+                qi = torch.stack([k32, k32], 1).view(-1).contiguous()
+                ai = torch.stack([k32 + B, neg_sent], 1).view(-1).contiguous()
+                loss = eng.loss_backward(qi, ai, self.gradParameters)
+                eng.flat_grad(self.gradParameters)
+                f = float(loss.item())
+            p = self.parameters
+            if opt["L1reg"] != 0:
+                f += opt["L1reg"] * float(p.abs().sum())
+            if opt["L2reg"] != 0:
+                f += opt["L2reg"] * float((p * p).sum()) / 2
+            # L1 / L2 / clamp in one fused pass over the flat gradient (bicnn.lua:398-409)
+            self._reg_clip(self.gradParameters, p, l1=opt["L1reg"], l2=opt["L2reg"], clip=opt["gradClip"])
+        self.loss += f
+        self.loss_times += 1
+        return f, self.gradParameters
+
+    @torch.no_grad()
+    def _encode_all(self, tok: torch.Tensor, lens: torch.Tensor) -> torch.Tensor:
+        eng = self.eng_eval
+        eng.load_flat(self.parameters)
+        out = []
+        for i in range(0, tok.shape[0], eng.S):
+            eng.set_sentences(tok[i:i + eng.S], lens[i:i + eng.S].int())
+            out.append(eng.encode()[:min(eng.S, tok.shape[0] - i)].clone())
+        return torch.cat(out)
+
+    @torch.no_grad()
+    def test(self, dataset, name="valid") -> float:
+        if not dataset:
+            return 0.0
+        with self.tm("test"):
+            emb = self._encode_all(self._ans_tok32, self._ans_lens)
+            qt, ql = pad_sentences([d[1] for d in dataset], self.dev)
+            qv = self._encode_all(self._fit(qt), ql)
+            correct = 0
+            for i, (targets, _, pool) in enumerate(dataset):
+                sims = gesd(qv[i:i + 1].expand(len(pool), -1), emb[pool])
+                best = len(pool) - 1 - int(torch.flip(sims, [0]).argmax())
+                correct += int(pool[best] in targets)
+        acc = correct / len(dataset)
+        self.best[name] = max(self.best.get(name, 0.0), acc)
+        print(f"Client {self.rank}: curr time: {time.perf_counter() - self.t_start + self.opt['prevtime']:.2f}, "
+              f"Accuracy: {acc:.4f}, best Accuracy: {self.best[name]:.4f} on {name} ")
+        return acc
