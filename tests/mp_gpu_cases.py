@@ -142,6 +142,54 @@ def case_eamsgd_train(rank, world, dev, heap):
     assert 0.5 < tr.last_loss() < 5.0
     heap.check_timeout()
 
+def case_server_rules(rank, world, dev, heap):
+    """Server-side Adam on the device path: owners drain per-client staging slots in rank order; the
+    result must equal the CPU restatement of BiCNN/pserver.lua applied client by client."""
+    from mpit_b200.optim import reference as R
+    from mpit_b200.optim.device import DeviceRuleParallel
+
+    class FakeEngine:     # gradient source with the engine interface, deterministic per (rank, step)
+        def __init__(self, n):
+            self.n, self.t = n, 0
+            self.wpk = torch.zeros(n, device=dev)
+            self.wmap = None
+            self.g = torch.zeros(n, device=dev)
+
+        def grad_for(self, r, t):
+            gen = torch.Generator().manual_seed(1000 * r + t)
+            return torch.randn(self.n, generator=gen) * 0.1
+
+        def load_flat(self, x):
+            pass
+
+        def fwd_bwd(self):
+            self.g.copy_(self.grad_for(rank, self.t))
+            self.t += 1
+
+        def flat_grad(self, out):
+            out.copy_(self.g)
+
+    n = 10007
+    hyper = dict(lr=0.01, beta1=0.9, beta2=0.999, epsilon=1e-8, step_div=3)
+    theta0 = torch.linspace(-1, 1, n)
+    eng = FakeEngine(n)
+    center = ShardedCenter.create(heap, n)
+    opt = DeviceRuleParallel(eng, theta0, "adam", hyper, center, heap)
+    sync(dev)
+    steps = 4
+    for _ in range(steps):
+        opt.step()
+    sync(dev)
+    heap.check_timeout()
+    # oracle: one server holding everything, gradients applied client by client each round
+    p = theta0.clone()
+    st = R.rule_state("adam", p)
+    for t in range(steps):
+        for c in range(world):
+            R.apply_rule("adam", p, eng.grad_for(c, t), st, hyper)
+    got = opt.x.cpu()
+    assert torch.allclose(got, p, rtol=1e-5, atol=1e-6), float((got - p).abs().max())
+
 
 CASES = {k[5:]: v for k, v in globals().items() if k.startswith("case_")}
 

@@ -32,3 +32,9 @@ def test_async_eamsgd_training():
     n = min(torch.cuda.device_count(), 8)
     out = _torchrun(["eamsgd_train"], n)
     assert "case eamsgd_train: ok" in out
+
+
+def test_server_side_rules_on_device_path():
+    n = min(torch.cuda.device_count(), 8)
+    out = _torchrun(["server_rules"], n)
+    assert "case server_rules: ok" in out
