@@ -397,7 +397,7 @@ static SignalTable make_sig(const unsigned long long* ptrs, int nranks, int rank
   return t;
 }
 
-static int exch_grid(const QuadWalk& w) { return ew_grid(w.total, 256, 4, 8); }
+static int exch_grid(const QuadWalk& w) { return ew_grid(w.total, 256, 2, 8); }
 
 }  // namespace mpit
 
