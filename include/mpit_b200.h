@@ -213,6 +213,18 @@ int mpit_gesd_margin_bwd(const float* y, const int* qi, const int* ai, const flo
 int mpit_encoder_bwd(const float* dy, const float* r, const unsigned char* arg, const float* normp, float* dC, int S,
                      int F, int ld, int T, void* stream);
 
+/* ---- bandwidth-path exchange through the bulk-copy engine (csrc/kernels/comm_bulk.cu) ----------- */
+/* Same semantics as mpit_param_pull / mpit_push_add / mpit_elastic_exchange, moved in 16 KiB
+ * cp.async.bulk / cp.reduce.async.bulk transactions. Require n >= 4096*nranks, n % (4*nranks) == 0 and
+ * 16-byte aligned buffers; return MPIT_E_UNSUPPORTED otherwise (callers then use the per-thread kernels). */
+int mpit_bulk_supported(long long n, int nranks);
+int mpit_param_pull_bulk(const unsigned long long* shard_ptrs, int nranks, int rank, float* dst, long long n,
+                         void* stream);
+int mpit_push_add_bulk(const unsigned long long* shard_ptrs, int nranks, int rank, float* src, long long n,
+                       float scale, int zero_src, void* stream);
+int mpit_elastic_exchange_bulk(const unsigned long long* shard_ptrs, int nranks, int rank, const float* x, float* d,
+                               long long n, float alpha, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -103,7 +103,9 @@ def device_sweep(sizes, iters, warmup, ops, nccl, out_path=None, straggler=0):
             "pull": (lambda: center.pull(x), 4 * n * frac),
             "push": (lambda: center.push_add(g), 4 * n * frac),
             "put": (lambda: center.put(x), 4 * n * frac),
-            "elastic": (lambda: center.elastic(x, d, 0.1), 4 * n * frac),          # per direction
+            # every rank pulls its remote shards (inbound) AND receives the other ranks' d for the shard it
+            # owns (inbound too), and symmetrically outbound: 2 x 4n x frac bytes per direction per GPU
+            "elastic": (lambda: center.elastic(x, d, 0.1), 2 * 4 * n * frac),
             "allreduce_oneshot": (lambda: coll.allreduce(n=n, algo="oneshot"), 4 * n * frac),
             "allreduce_twoshot": (lambda: coll.allreduce(n=n, algo="twoshot"), 4 * n * frac),
             "allreduce_elastic": (lambda: coll.allreduce(n=n, average=True, elastic_x=x, alpha=0.1), 4 * n * frac),

@@ -44,6 +44,8 @@ class ShardedCenter:
         self.parts = partition(n, self.nranks)
         self._ptrs = buf.ptr_array()
         self.k = kernels()
+        # large, 16-byte-aligned problems go through the bulk-copy engine (comm_bulk.cu)
+        self.bulk = bool(self.k.mpit_bulk_supported(n, self.nranks)) and n >= (1 << 20)
 
     @classmethod
     def create(cls, heap, n: int) -> "ShardedCenter":
@@ -65,17 +67,29 @@ class ShardedCenter:
 
     def pull(self, dst: torch.Tensor, wpk=None, wmap=None) -> None:
         """dst := centre (pclient.lua:74-84), optionally refreshing the packed operand copy."""
+        if self.bulk and wpk is None and dst.data_ptr() % 16 == 0:
+            check(self.k.mpit_param_pull_bulk(self._ptrs, self.nranks, self.rank, ptr(dst), self.n, cur_stream()),
+                  "mpit_param_pull_bulk")
+            return
         check(self.k.mpit_param_pull(self._ptrs, self.nranks, self.rank, ptr(dst), self.n, ptr(wpk), ptr(wmap),
                                      self._nmaps(wmap), cur_stream()), "mpit_param_pull")
 
     def push_add(self, src: torch.Tensor, params: Optional[torch.Tensor] = None, *, scale=1.0, l1=0.0, l2=0.0,
                  clip=0.0, zero_src=False) -> None:
         """centre += scale * clip(reg(src)) (pserver.lua:91)."""
+        if self.bulk and l1 == 0 and l2 == 0 and clip == 0 and src.data_ptr() % 16 == 0:
+            check(self.k.mpit_push_add_bulk(self._ptrs, self.nranks, self.rank, ptr(src), self.n, scale,
+                                            int(zero_src), cur_stream()), "mpit_push_add_bulk")
+            return
         check(self.k.mpit_push_add(self._ptrs, self.nranks, self.rank, ptr(src), ptr(params), self.n, scale, l1,
                                    l2, clip, int(zero_src), cur_stream()), "mpit_push_add")
 
     def elastic(self, x: torch.Tensor, d: torch.Tensor, alpha: float) -> None:
         """d = alpha (x - centre); centre += d (optim-eamsgd.lua:58-65)."""
+        if self.bulk and x.data_ptr() % 16 == 0 and d.data_ptr() % 16 == 0:
+            check(self.k.mpit_elastic_exchange_bulk(self._ptrs, self.nranks, self.rank, ptr(x), ptr(d), self.n, alpha,
+                                                    cur_stream()), "mpit_elastic_exchange_bulk")
+            return
         check(self.k.mpit_elastic_exchange(self._ptrs, self.nranks, self.rank, ptr(x), ptr(d), self.n, alpha,
                                            cur_stream()), "mpit_elastic_exchange")
 

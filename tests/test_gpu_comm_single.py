@@ -21,7 +21,8 @@ def _center_as_flat(cs, n):
     return torch.cat([cs[s].buf.local[:sz] for s, (off, sz) in enumerate(parts)])
 
 
-@pytest.mark.parametrize("n,S", [(351946, 8), (1003, 3), (5, 8), (4096, 1), (43993 * 8 + 5, 8)])
+@pytest.mark.parametrize("n,S", [(351946, 8), (1003, 3), (5, 8), (4096, 1), (43993 * 8 + 5, 8),
+                                 (1 << 20, 8), ((1 << 20) + 4096 * 3, 3), (3 << 20, 2)])   # last three: bulk-engine path
 def test_put_pull_push_roundtrip(n, S):
     cs = _centers(n, S)
     x = torch.randn(n, device="cuda")
@@ -121,3 +122,24 @@ def test_fused_eamsgd_step_matches_reference_bitwise(su, mom):
     torch.cuda.synchronize()
     assert torch.equal(x.cpu(), w)
     assert torch.equal(_center_as_flat(cs, n).cpu(), ps.center)
+
+
+@pytest.mark.parametrize("n,S", [(1 << 20, 8), (3 * 4096 * 100, 3)])
+def test_bulk_elastic_and_scaled_push(n, S):
+    cs = _centers(n, S)
+    assert cs[0].bulk
+    c0 = torch.randn(n, device="cuda")
+    cs[0].put(c0)
+    x = torch.randn(n, device="cuda")
+    d = torch.empty_like(x)
+    cs[1].elastic(x, d, 0.25)
+    torch.cuda.synchronize()
+    ref_d = (x - c0) * 0.25
+    assert torch.equal(d, ref_d)
+    assert torch.equal(_center_as_flat(cs, n), c0 + ref_d)
+    g = torch.randn(n, device="cuda")
+    g0 = g.clone()
+    cs[S - 1].push_add(g, scale=0.5, zero_src=True)
+    torch.cuda.synchronize()
+    assert torch.allclose(_center_as_flat(cs, n), c0 + ref_d + g0 * 0.5, atol=1e-6)
+    assert float(g.abs().sum()) == 0.0
