@@ -72,10 +72,14 @@ __device__ __forceinline__ void subtile_origin(const IgemmParams& p, int s, int&
   ow0 = tw_i * p.tw;
 }
 
+// Body shared by the plain kernel and the pull-fused kernel.  `tmap_a_p`/`tmap_b_p` point into
+// kernel-parameter space; `b_row0` is the row coordinate of this CTA's B tile inside *its* tensor map
+// (equal to the output column offset unless B lives in a peer's shard).
 template <int BLOCK_N>
-__global__ void __launch_bounds__(192)
-umma_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                  const IgemmParams p) {
+__device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CUtensorMap* tmap_b_p, const int b_row0,
+                                           const IgemmParams& p) {
+  const CUtensorMap& tmap_a = *tmap_a_p;
+  const CUtensorMap& tmap_b = *tmap_b_p;
   using L = SmemLayout<BLOCK_N>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -127,7 +131,7 @@ umma_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         for (int j = 0; j < p.nsub; ++j)
           tma_load_4d(a_dst + j * rows_per_sub * 128, &tmap_a, &full_bar[stage], cblk * 32,
                       ow0[j] + p.sgn * kw, oh0[j] + p.sgn * kh, n0[j]);
-        tma_load_2d(b_dst, &tmap_b, &full_bar[stage], kb * 32, n_tile0);
+        tma_load_2d(b_dst, &tmap_b, &full_bar[stage], kb * 32, b_row0);
         if (++stage == kStages) { stage = 0; phase ^= 1; }
       }
       if (dbg) dbg[2] = clock64();   // last TMA issued
@@ -317,6 +321,32 @@ umma_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   if (dbg && threadIdx.x == 0) dbg[7] = clock64();
 }
 
+template <int BLOCK_N>
+__global__ void __launch_bounds__(192)
+umma_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                  const IgemmParams p) {
+  igemm_body<BLOCK_N>(&tmap_a, &tmap_b, blockIdx.y * BLOCK_N, p);
+}
+
+// Parameter pull fused with the GEMM that consumes the weights: the B operand (rows of a Linear /
+// convolution weight) is NOT first copied out of the sharded centre; each CTA's TMA loads fetch its
+// weight tile straight from the owner's shard over NVLink (a tensor map per owner over the peer-mapped
+// shard) while the MMAs of earlier tiles run.  Reference: pclient.lua:74-84 (pull) followed by the
+// first nn.Linear forward of the model.
+struct PeerMaps {
+  CUtensorMap map[8];
+  int rows_per_owner;
+};
+
+template <int BLOCK_N>
+__global__ void __launch_bounds__(192)
+umma_igemm_pull_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ PeerMaps pm,
+                       const IgemmParams p) {
+  const int n_tile0 = blockIdx.y * BLOCK_N;
+  const int owner = n_tile0 / pm.rows_per_owner;
+  igemm_body<BLOCK_N>(&tmap_a, &pm.map[owner], n_tile0 - owner * pm.rows_per_owner, p);
+}
+
 // ---- host side -----------------------------------------------------------------------------------
 static decltype(&cuTensorMapEncodeTiled) get_encode() {
   static decltype(&cuTensorMapEncodeTiled) fn = nullptr;
@@ -421,6 +451,50 @@ int mpit_umma_igemm(const void* tmap_a128, const void* tmap_b128, const int* geo
     case 256: return launch_igemm<256>(ta, tb, p, m_tiles, st);
     default: return MPIT_E_ARG;
   }
+}
+
+// Linear layer whose weight rows live in the NVLink-sharded centre: y = act(x W^T + b), W fetched by
+// the GEMM's own TMA loads from each owner's shard (tmaps_b: HOST array of nranks x 128 bytes, one map
+// per owner over its [rows_per_owner][K] block).  N = nranks * rows_per_owner; BLOCK_N 32 or 64 must
+// divide rows_per_owner.
+int mpit_umma_linear_pull(const void* tmap_a128, const void* tmaps_b, int nranks, int rows_per_owner,
+                          const int* geom17, const float* bias, float* out, int* err, int block_n, void* stream) {
+  if (nranks < 1 || nranks > 8 || rows_per_owner % block_n != 0) return MPIT_E_ARG;
+  IgemmParams p{};
+  p.nsub = geom17[0]; p.tw = geom17[1]; p.th = geom17[2]; p.tn = geom17[3];
+  p.tiles_w = geom17[4]; p.tiles_h = geom17[5]; p.kw_it = geom17[6]; p.cb = geom17[7];
+  p.num_kb = geom17[8]; p.sgn = geom17[9]; p.B = geom17[10]; p.OH = geom17[11]; p.OW = geom17[12];
+  p.N = geom17[13]; p.mode = geom17[14]; p.relu = geom17[15]; p.dropout = 0;
+  p.scale = 1.f; p.bias = bias; p.out = out; p.err = err;
+  if (p.nsub * p.tw * p.th * p.tn != 128 || p.num_kb < 1 || p.N != nranks * rows_per_owner || p.mode != EPI_STORE)
+    return MPIT_E_ARG;
+  int subtiles = ((p.B + p.tn - 1) / p.tn) * p.tiles_w * p.tiles_h;
+  int m_tiles = (subtiles + p.nsub - 1) / p.nsub;
+  CUtensorMap ta;
+  PeerMaps pm;
+  memset(&pm, 0, sizeof(pm));
+  memcpy(&ta, tmap_a128, sizeof(CUtensorMap));
+  for (int i = 0; i < nranks; ++i) memcpy(&pm.map[i], static_cast<const char*>(tmaps_b) + 128 * i, sizeof(CUtensorMap));
+  pm.rows_per_owner = rows_per_owner;
+  cudaStream_t st = (cudaStream_t)stream;
+  dim3 grid(m_tiles, p.N / block_n);
+  if (block_n == 32) {
+    using L = SmemLayout<32>;
+    p.stages = p.num_kb < 4 ? (p.num_kb < 2 ? 2 : p.num_kb) : 4;
+    MPIT_CUDA_TRY(cudaFuncSetAttribute(umma_igemm_pull_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       L::total(4)));
+    umma_igemm_pull_kernel<32><<<grid, 192, L::total(p.stages), st>>>(ta, pm, p);
+  } else if (block_n == 64) {
+    using L = SmemLayout<64>;
+    p.stages = p.num_kb < 4 ? (p.num_kb < 2 ? 2 : p.num_kb) : 4;
+    MPIT_CUDA_TRY(cudaFuncSetAttribute(umma_igemm_pull_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       L::total(4)));
+    umma_igemm_pull_kernel<64><<<grid, 192, L::total(p.stages), st>>>(ta, pm, p);
+  } else {
+    return MPIT_E_ARG;
+  }
+  MPIT_LAUNCH_CHECK();
+  return 0;
 }
 
 }  // extern "C"

@@ -156,6 +156,11 @@ int mpit_umma_igemm(const void* tmap_a128, const void* tmap_b128, const int* geo
                     const float* bias, float* out, unsigned char* idx, const float* aux,
                     const unsigned char* aux_idx, const int* crop, const unsigned long long* rng, int* err,
                     int block_n, void* stream);
+/* Parameter pull fused with the GEMM that consumes the weights (/root/reference/asyncsgd/pclient.lua:74-84
+ * followed by the model's first Linear): the weight rows stay in the NVLink-sharded centre and the
+ * kernel's TMA loads read each tile from its owner's shard. tmaps_b: HOST array of nranks x 128 bytes. */
+int mpit_umma_linear_pull(const void* tmap_a128, const void* tmaps_b, int nranks, int rows_per_owner,
+                          const int* geom17, const float* bias, float* out, int* err, int block_n, void* stream);
 
 /* ---- tcgen05 weight gradients (csrc/kernels/umma_wgrad.cu) ------------------------------------- */
 /* dW = Xcol^T dZ over all output pixels, pixel dimension split over `nsplit` CTAs that each write a

@@ -191,6 +191,34 @@ def case_server_rules(rank, world, dev, heap):
     assert torch.allclose(got, p, rtol=1e-5, atol=1e-6), float((got - p).abs().max())
 
 
+def case_pulled_linear(rank, world, dev, heap):
+    """Pull fused with the consuming GEMM: weights stay sharded; every rank's GEMM reads them over NVLink."""
+    from mpit_b200.ops.pulled_linear import PulledLinear
+    K, N, M = 256, 64 * world * 2, 200
+    lin = PulledLinear(heap, K, N, M, act=1)
+    gen = torch.Generator().manual_seed(42)
+    W = torch.randn(N, K, generator=gen) * 0.05
+    b = torch.randn(N, generator=gen) * 0.1
+    rpo = N // world
+    lin.weight_rows().copy_(W[rank * rpo:(rank + 1) * rpo])
+    sync(dev)
+    x = torch.randn(M, K, generator=torch.Generator().manual_seed(rank))
+    y = lin.forward(x.to(dev), b.to(dev))
+    torch.cuda.synchronize()
+    assert int(lin.err.item()) == 0
+    ref = torch.relu(x @ W.t() + b)
+    rel = float((y.cpu() - ref).norm() / ref.norm())
+    assert rel < 3e-3, rel
+    sync(dev)
+    # an owner updates its rows; the next forward of every rank sees the new weights without any pull call
+    lin.weight_rows().mul_(2.0)
+    sync(dev)
+    y2 = lin.forward(x.to(dev), None)
+    torch.cuda.synchronize()
+    ref2 = torch.relu(x @ (2 * W).t())
+    assert float((y2.cpu() - ref2).norm() / ref2.norm()) < 3e-3
+
+
 CASES = {k[5:]: v for k, v in globals().items() if k.startswith("case_")}
 
 if __name__ == "__main__":

@@ -38,3 +38,9 @@ def test_server_side_rules_on_device_path():
     n = min(torch.cuda.device_count(), 8)
     out = _torchrun(["server_rules"], n)
     assert "case server_rules: ok" in out
+
+
+def test_pull_fused_with_consumer_gemm():
+    n = min(torch.cuda.device_count(), 8)
+    out = _torchrun(["pulled_linear"], n)
+    assert "case pulled_linear: ok" in out
