@@ -116,6 +116,7 @@ struct ExchArgs {
 
 template <int MODE>
 __global__ void __launch_bounds__(256) exchange_kernel(ExchArgs a) {
+  pdl_trigger();   // the step kernel that follows may start its set-up; it waits for this grid's completion
   long long stride = (long long)gridDim.x * blockDim.x;
   for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < a.walk.total; q += stride) {
     int s, cnt;

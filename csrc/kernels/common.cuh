@@ -29,6 +29,35 @@ static inline int ew_grid(long long n_items, int threads, int items_per_thread =
   return (int)(need < cap ? need : cap);
 }
 
+// ---- programmatic dependent launch (PDL) -------------------------------------------------------
+// A training step is ~20 short kernels; each spends its first 1.5-2 us on set-up (barrier init, TMEM
+// allocation, descriptor fetch) before it touches data.  Launched with the programmatic-serialization
+// attribute a kernel may start while its predecessor is still running: it does its set-up, then
+// `pdl_wait()` blocks until the predecessor grid has completed and its writes are visible.
+// `pdl_trigger()` (first statement of every participating kernel) lets the *next* kernel start early.
+// Rule: a kernel launched through launch_k() must execute pdl_wait() in every thread before its first
+// global-memory access that could alias anything an earlier kernel reads or writes.
+extern int g_pdl_enabled;   // defined in optim.cu; mpit_set_pdl()
+
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                   Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = g_pdl_enabled ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 __device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
 __device__ __forceinline__ void st4(float* p, const float4& v) { *reinterpret_cast<float4*>(p) = v; }
 

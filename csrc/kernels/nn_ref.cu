@@ -189,6 +189,8 @@ colsum_kernel(const float* __restrict__ dz, float* __restrict__ db, long long ro
 // starts on a 32-byte boundary (needed by the 32-byte-atom swizzle of the weight-gradient kernel).
 __global__ void __launch_bounds__(256)
 prep_u8_kernel(const unsigned char* __restrict__ src, float* __restrict__ dst, int B, int SH, int SW, int cin) {
+  pdl_trigger();
+  pdl_wait();
   long long total = (long long)B * SH * SW;
   long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
@@ -219,33 +221,50 @@ prep_u8_kernel(const unsigned char* __restrict__ src, float* __restrict__ dst, i
 // asyncsgd/goot.lua:40,200-206), one warp per sample.  logits are [B][ld] with ncls valid
 // columns.  dlogits = (softmax - onehot) * gscale.  Also accumulates the confusion matrix
 // that the reference updates per sample (goot.lua:209).
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 nll_fwd_bwd_kernel(const float* __restrict__ logits, const int* __restrict__ labels,
                    float* __restrict__ dlogits, float* __restrict__ loss_sum, int* __restrict__ confusion,
-                   int B, int ncls, int ld, float gscale, unsigned long long* __restrict__ rng_inc) {
+                   int B, int ncls, int ld, float gscale, unsigned long long* __restrict__ rng_inc, int accumulate) {
+  __shared__ float part[32];
+  pdl_trigger();
+  pdl_wait();
   // The step counter that keys the dropout Philox stream lives on the device so that a
   // captured CUDA graph advances it on every replay.
   if (rng_inc && blockIdx.x == 0 && threadIdx.x == 0) rng_inc[1] += 1ull;
-  int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (warp >= B) return;
-  const float* row = logits + (size_t)warp * ld;
-  float z = lane < ncls ? row[lane] : -INFINITY;
-  float m = warp_max(z);
-  float e = lane < ncls ? __expf(z - m) : 0.f;
-  float s = warp_sum(e);
-  float lse = m + __logf(s);
-  int y = labels[warp];
-  if (dlogits) {
-    float gz = 0.f;
-    if (lane < ncls) gz = (e / s - (lane == y ? 1.f : 0.f)) * gscale;
-    if (lane < ld) dlogits[(size_t)warp * ld + lane] = gz;
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  float mine = 0.f;
+  for (int r = blockIdx.x * nw + wib; r < B; r += gridDim.x * nw) {
+    const float* row = logits + (size_t)r * ld;
+    float z = lane < ncls ? row[lane] : -INFINITY;
+    float m = warp_max(z);
+    float e = lane < ncls ? __expf(z - m) : 0.f;
+    float s = warp_sum(e);
+    float lse = m + __logf(s);
+    int y = labels[r];
+    if (dlogits) {
+      float gz = 0.f;
+      if (lane < ncls) gz = (e / s - (lane == y ? 1.f : 0.f)) * gscale;
+      if (lane < ld) dlogits[(size_t)r * ld + lane] = gz;
+    }
+    // argmax (first max wins, like torch.max)
+    unsigned ball = __ballot_sync(0xffffffffu, lane < ncls && z == m);
+    int pred = __ffs(ball) - 1;
+    if (lane == 0) {
+      mine += lse - row[y];
+      if (confusion) atomicAdd(confusion + y * ncls + pred, 1);
+    }
   }
-  // argmax (first max wins, like torch.max)
-  unsigned ball = __ballot_sync(0xffffffffu, lane < ncls && z == m);
-  int pred = __ffs(ball) - 1;
-  if (lane == 0) {
-    atomicAdd(loss_sum, lse - row[y]);
-    if (confusion) atomicAdd(confusion + y * ncls + pred, 1);
+  // fixed-order block reduction: with one CTA (the training configuration) the loss is a plain store,
+  // bit-reproducible and with no zeroing launch in front of it
+  if (lane == 0) part[wib] = mine;
+  __syncthreads();
+  if (wib == 0) {
+    float t = lane < nw ? part[lane] : 0.f;
+    t = warp_sum(t);
+    if (lane == 0) {
+      if (gridDim.x == 1 && !accumulate) *loss_sum = t;
+      else atomicAdd(loss_sum, t);
+    }
   }
 }
 
@@ -319,18 +338,26 @@ int mpit_colsum(const float* dz, float* db, long long rows, int C, void* stream)
 int mpit_prep_u8(const unsigned char* src, float* dst, int B, int SH, int SW, int cin, void* stream) {
   if (cin < 1 || cin > 4) return MPIT_E_ARG;
   long long total = (long long)B * SH * SW;
-  prep_u8_kernel<<<ew_grid(total, 256, 1), 256, 0, (cudaStream_t)stream>>>(src, dst, B, SH, SW, cin);
-  MPIT_LAUNCH_CHECK();
+  MPIT_CUDA_TRY(launch_k(prep_u8_kernel, dim3(ew_grid(total, 256, 1)), dim3(256), 0, (cudaStream_t)stream, src, dst,
+                         B, SH, SW, cin));
   return 0;
 }
 
 int mpit_nll_fwd_bwd(const float* logits, const int* labels, float* dlogits, float* loss_sum, int* confusion,
-                     int B, int ncls, int ld, float gscale, unsigned long long* rng_inc, void* stream) {
+                     int B, int ncls, int ld, float gscale, unsigned long long* rng_inc, int accumulate,
+                     void* stream) {
   if (ncls > 32 || ld > 32) return (int)cudaErrorInvalidValue;
-  int threads = 256, warps_per_block = threads / 32;
-  nll_fwd_bwd_kernel<<<(B + warps_per_block - 1) / warps_per_block, threads, 0, (cudaStream_t)stream>>>(
-      logits, labels, dlogits, loss_sum, confusion, B, ncls, ld, gscale, rng_inc);
-  MPIT_LAUNCH_CHECK();
+  cudaStream_t st = (cudaStream_t)stream;
+  // up to 4096 rows: one 1024-thread CTA (32 warps x <=128 rows each) stores the sum directly
+  int grid = 1;
+  if (B > 4096) {
+    grid = (B + 1023) / 1024;
+    if (grid > 4 * MPIT_NUM_SMS) grid = 4 * MPIT_NUM_SMS;
+    if (!accumulate) MPIT_CUDA_TRY(cudaMemsetAsync(loss_sum, 0, sizeof(float), st));
+    accumulate = 1;
+  }
+  MPIT_CUDA_TRY(launch_k(nll_fwd_bwd_kernel, dim3(grid), dim3(1024), 0, st, logits, labels, dlogits, loss_sum,
+                         confusion, B, ncls, ld, gscale, rng_inc, accumulate));
   return 0;
 }
 

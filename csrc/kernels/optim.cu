@@ -6,6 +6,8 @@
 
 namespace mpit {
 
+int g_pdl_enabled = 1;
+
 // ---------------------------------------------------------------------------------------
 // local_step: [apply(t)] -> [lookahead(t+1)] -> [pack] in one pass.
 // ---------------------------------------------------------------------------------------
@@ -24,6 +26,8 @@ struct LocalStepArgs {
 };
 
 __global__ void __launch_bounds__(256) local_step_kernel(LocalStepArgs a) {
+  pdl_trigger();
+  pdl_wait();
   long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += stride) {
     float x = a.x[i];
@@ -42,6 +46,8 @@ __global__ void __launch_bounds__(256) local_step_kernel(LocalStepArgs a) {
 
 // Vectorised variant for the map-free case (bandwidth sweeps, big flat tensors).
 __global__ void __launch_bounds__(256) local_step_vec_kernel(LocalStepArgs a) {
+  pdl_trigger();
+  pdl_wait();
   long long n4 = a.n >> 2;
   long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
@@ -176,6 +182,12 @@ using namespace mpit;
 
 extern "C" {
 
+int mpit_set_pdl(int enabled) {
+  int old = g_pdl_enabled;
+  if (enabled >= 0) g_pdl_enabled = enabled ? 1 : 0;
+  return old;
+}
+
 int mpit_local_step(float* x, float* v, const float* g, const int* gmap, const float* d, float* wpk,
                     const int* wmap, int nmaps, long long n, float clr, float l2wd, float mom_next, int do_apply,
                     int use_mom, int do_lookahead, void* stream) {
@@ -186,12 +198,11 @@ int mpit_local_step(float* x, float* v, const float* g, const int* gmap, const f
              (!d || aligned16(d)) && (!wpk || aligned16(wpk));
   if (vec) {
     int grid = ew_grid(n, 256, 8);
-    local_step_vec_kernel<<<grid, 256, 0, st>>>(a);
+    MPIT_CUDA_TRY(launch_k(local_step_vec_kernel, dim3(grid), dim3(256), 0, st, a));
   } else {
     int grid = ew_grid(n, 256, 4);
-    local_step_kernel<<<grid, 256, 0, st>>>(a);
+    MPIT_CUDA_TRY(launch_k(local_step_kernel, dim3(grid), dim3(256), 0, st, a));
   }
-  MPIT_LAUNCH_CHECK();
   return 0;
 }
 

@@ -95,6 +95,7 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
   const int rows_per_sub = 128 / p.nsub;
 
   long long* dbg = p.dbg ? p.dbg + 8 * (blockIdx.y * gridDim.x + blockIdx.x) : nullptr;
+  pdl_trigger();   // let the next kernel of the step begin its own set-up now
   if (dbg && threadIdx.x == 0) dbg[0] = clock64();
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmap_a);
@@ -108,53 +109,70 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();      // everything above overlapped the previous kernel; its results are visible from here on
   if (dbg && threadIdx.x == 0) dbg[1] = clock64();   // prologue done
 
-  if (warp == 0) {
-    // ===== TMA producer =====
-    if (elect_one()) {
-      int n0[2], oh0[2], ow0[2];
-      for (int j = 0; j < p.nsub; ++j) {
-        subtile_origin(p, tile * p.nsub + j, n0[j], oh0[j], ow0[j]);
-        // (in MAXTIME mode `crop` carries per-sentence frame counts for the epilogue, not offsets)
-        if (p.crop && p.mode != EPI_MAXTIME && n0[j] < p.B) { oh0[j] += p.crop[2 * n0[j]]; ow0[j] += p.crop[2 * n0[j] + 1]; }
-      }
-      int stage = 0, phase = 0;
-      const int per_kh = p.kw_it * p.cb;
-      for (int kb = 0; kb < p.num_kb; ++kb) {
-        if (!mbar_wait(&empty_bar[stage], phase ^ 1)) { if (p.err) *p.err = 1; break; }
-        uint8_t* a_dst = smem + stage * L::kStageBytes;
-        uint8_t* b_dst = a_dst + kABytes;
-        mbar_expect_tx(&full_bar[stage], L::kStageBytes);
-        int kh = kb / per_kh, r = kb - kh * per_kh;
-        int kw = r / p.cb, cblk = r - kw * p.cb;
-        for (int j = 0; j < p.nsub; ++j)
-          tma_load_4d(a_dst + j * rows_per_sub * 128, &tmap_a, &full_bar[stage], cblk * 32,
-                      ow0[j] + p.sgn * kw, oh0[j] + p.sgn * kh, n0[j]);
-        tma_load_2d(b_dst, &tmap_b, &full_bar[stage], kb * 32, b_row0);
-        if (++stage == kStages) { stage = 0; phase ^= 1; }
-      }
-      if (dbg) dbg[2] = clock64();   // last TMA issued
+  // ===== TMA producers =====
+  // Issuing a k-block (wait for the slot, expect_tx, 2-3 tensor loads with their coordinate arithmetic) is a
+  // ~400-clock dependent chain in ONE thread -- measured (tools/dev/tma_feed_probe.cu) to be what bounded the
+  // operand feed at ~35 B/clk/SM while the TMA unit itself sustains > 120 B/clk/SM.  So k-blocks are dealt
+  // round-robin to kProducers issuing threads: the elected lane of warp 0 and of the four epilogue warps,
+  // which have nothing else to do until the accumulator is complete.  No integer division on the issue path.
+  // Never more producers than stages: a producer that has passed its wait for k-block kb knows k-block
+  // kb - kStages is consumed; its next one (kb + NP) needs kb + NP - 2*kStages consumed for the parity test
+  // to be unambiguous, which in-order consumption guarantees iff NP <= kStages.
+  const int kProducers = kStages < 5 ? kStages : 5;
+  const int pi = warp == 0 ? 0 : warp - 1;          // warps 0,2,3,4,5 -> 0,1,2,3,4 (warp 1 issues the MMAs)
+  if (warp != 1 && pi < kProducers && elect_one()) {
+    int n0[2], oh0[2], ow0[2];
+    for (int j = 0; j < p.nsub; ++j) {
+      subtile_origin(p, tile * p.nsub + j, n0[j], oh0[j], ow0[j]);
+      // (in MAXTIME mode `crop` carries per-sentence frame counts for the epilogue, not offsets)
+      if (p.crop && p.mode != EPI_MAXTIME && n0[j] < p.B) { oh0[j] += p.crop[2 * n0[j]]; ow0[j] += p.crop[2 * n0[j] + 1]; }
     }
+    const int sub_bytes = rows_per_sub * 128;
+    int stage = 0, phase = 0, kh = 0, kw = 0, cblk = 0;
+    auto advance = [&](int by) {
+      stage += by;
+      while (stage >= kStages) { stage -= kStages; phase ^= 1; }
+      cblk += by;
+      while (cblk >= p.cb) { cblk -= p.cb; if (++kw == p.kw_it) { kw = 0; ++kh; } }
+    };
+    advance(pi);
+    for (int kb = pi; kb < p.num_kb; kb += kProducers) {
+      if (!mbar_wait(&empty_bar[stage], phase ^ 1)) { if (p.err) *p.err = 1; break; }
+      uint8_t* a_dst = smem + stage * L::kStageBytes;
+      mbar_expect_tx(&full_bar[stage], L::kStageBytes);
+      tma_load_4d(a_dst, &tmap_a, &full_bar[stage], cblk * 32, ow0[0] + p.sgn * kw, oh0[0] + p.sgn * kh, n0[0]);
+      if (p.nsub == 2)
+        tma_load_4d(a_dst + sub_bytes, &tmap_a, &full_bar[stage], cblk * 32, ow0[1] + p.sgn * kw, oh0[1] + p.sgn * kh,
+                    n0[1]);
+      tma_load_2d(a_dst + kABytes, &tmap_b, &full_bar[stage], kb * 32, b_row0);
+      advance(kProducers);
+    }
+    if (dbg && warp == 0) dbg[2] = clock64();   // warp 0's last TMA issued
+  }
+  __syncwarp();
+  if (warp == 0) {
+    // nothing further: warp 0 only issues loads
   } else if (warp == 1) {
     // ===== MMA issuer =====
     if (elect_one()) {
       constexpr uint32_t idesc = make_idesc_tf32(128, BLOCK_N, 0, 0);
+      // descriptor of stage 0; later stages / k-steps only add to the 14-bit address field (smem < 256 KB)
+      const uint64_t desc0 = make_smem_desc(smem_u32(smem), 16, 1024);
+      uint64_t ad = desc0;
       int stage = 0, phase = 0;
       for (int kb = 0; kb < p.num_kb; ++kb) {
         if (!mbar_wait(&full_bar[stage], phase)) { if (p.err) *p.err = 2; break; }
         if (dbg && kb == 0) dbg[3] = clock64();   // first operands landed
         tc_fence_after();
-        uint32_t a_addr = smem_u32(smem + stage * L::kStageBytes);
-        uint32_t b_addr = a_addr + kABytes;
+        const uint64_t bd = ad + (kABytes >> 4);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          uint64_t ad = make_smem_desc(a_addr + k * 32, 16, 1024);
-          uint64_t bd = make_smem_desc(b_addr + k * 32, 16, 1024);
-          mma_tf32(tmem_base, ad, bd, idesc, (kb | k) ? 1u : 0u);
-        }
+        for (int k = 0; k < 4; ++k) mma_tf32(tmem_base, ad + 2 * k, bd + 2 * k, idesc, (kb | k) ? 1u : 0u);
         mma_commit(&empty_bar[stage]);   // frees the smem slot once these MMAs have read it
-        if (++stage == kStages) { stage = 0; phase ^= 1; }
+        ad += (L::kStageBytes >> 4);
+        if (++stage == kStages) { stage = 0; phase ^= 1; ad = desc0; }
       }
       mma_commit(tmem_full);             // accumulator complete
       if (dbg) dbg[4] = clock64();       // last MMA issued
@@ -379,8 +397,7 @@ static int launch_igemm(const CUtensorMap* ta, const CUtensorMap* tb, IgemmParam
   if (stages > p.num_kb) stages = p.num_kb < 2 ? 2 : p.num_kb;
   if (stages > L::kMaxFit) stages = L::kMaxFit;
   p.stages = stages;
-  umma_igemm_kernel<BLOCK_N><<<grid, 192, L::total(stages), st>>>(*ta, *tb, p);
-  MPIT_LAUNCH_CHECK();
+  MPIT_CUDA_TRY(launch_k(umma_igemm_kernel<BLOCK_N>, grid, dim3(192), (size_t)L::total(stages), st, *ta, *tb, p));
   return 0;
 }
 
@@ -434,7 +451,8 @@ int mpit_umma_igemm(const void* tmap_a128, const void* tmap_b128, const int* geo
   p.N = geom17[13]; p.mode = geom17[14]; p.relu = geom17[15]; p.dropout = geom17[16];
   p.scale = scale; p.bias = bias; p.out = out; p.idx = idx; p.aux = aux; p.aux_idx = aux_idx;
   p.crop = crop; p.rng = rng; p.err = err;
-  if (p.nsub * p.tw * p.th * p.tn != 128 || p.num_kb < 1 || p.N % block_n != 0) return MPIT_E_ARG;
+  if (p.nsub < 1 || p.nsub > 2 || p.nsub * p.tw * p.th * p.tn != 128 || p.num_kb < 1 || p.N % block_n != 0)
+    return MPIT_E_ARG;
   if (p.mode == EPI_POOL && (p.tw > 16 || (p.tw & 1) || (p.th & 1))) return MPIT_E_ARG;
   int subtiles = ((p.B + p.tn - 1) / p.tn) * p.tiles_w * p.tiles_h;
   int m_tiles = (subtiles + p.nsub - 1) / p.nsub;
@@ -466,7 +484,8 @@ int mpit_umma_linear_pull(const void* tmap_a128, const void* tmaps_b, int nranks
   p.num_kb = geom17[8]; p.sgn = geom17[9]; p.B = geom17[10]; p.OH = geom17[11]; p.OW = geom17[12];
   p.N = geom17[13]; p.mode = geom17[14]; p.relu = geom17[15]; p.dropout = 0;
   p.scale = 1.f; p.bias = bias; p.out = out; p.err = err;
-  if (p.nsub * p.tw * p.th * p.tn != 128 || p.num_kb < 1 || p.N != nranks * rows_per_owner || p.mode != EPI_STORE)
+  if (p.nsub < 1 || p.nsub > 2 || p.nsub * p.tw * p.th * p.tn != 128 || p.num_kb < 1 ||
+      p.N != nranks * rows_per_owner || p.mode != EPI_STORE)
     return MPIT_E_ARG;
   int subtiles = ((p.B + p.tn - 1) / p.tn) * p.tiles_w * p.tiles_h;
   int m_tiles = (subtiles + p.nsub - 1) / p.nsub;

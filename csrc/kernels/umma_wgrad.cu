@@ -76,6 +76,7 @@ umma_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
   int nchunks = p.total_chunks - m_tile * 4;
   if (nchunks > 4) nchunks = 4;
 
+  pdl_trigger();
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmap_x);
     prefetch_tmap(&tmap_dz);
@@ -88,56 +89,70 @@ umma_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
 
-  if (warp == 0) {
-    if (elect_one()) {
-      // decode this tile's M chunks once
-      int ckh[4], ckw[4], cc0[4];
-      const int per_kh = p.kw_it * p.cb;
-      for (int j = 0; j < 4; ++j) {
-        int ch = m_tile * 4 + j;
-        int kh = ch / per_kh, r = ch - kh * per_kh;
-        ckh[j] = kh; ckw[j] = r / p.cb; cc0[j] = (r - (r / p.cb) * p.cb) * 32;
+  // ===== TMA producers =====
+  // A k-block is up to 4 A-chunk loads + BLOCK_N/32 B-chunk loads; issued by one thread that is a > 1000-clock
+  // dependent chain per k-block (the feed was issue-bound, not bandwidth-bound: tools/dev/tma_feed_probe.cu).
+  // The loads are dealt to four issuing threads -- the elected lanes of warp 0 and of epilogue warps 2,3,4:
+  // producer j issues A chunk j and B chunk j of EVERY k-block, producer 0 also posts the expect_tx.  Each
+  // producer walks the k-blocks in order, so the empty-barrier parity test stays unambiguous.
+  const int pj = warp == 0 ? 0 : warp - 1;     // warps 0,2,3,4 -> 0,1,2,3
+  const bool has_a = pj < nchunks, has_b = pj < BLOCK_N / 32;
+  if (warp != 1 && pj < 4 && (has_a || has_b || pj == 0) && elect_one()) {
+    // decode this producer's M chunk once
+    const int per_kh = p.kw_it * p.cb;
+    const int ch = m_tile * 4 + pj;
+    const int ckh = ch / per_kh, rch = ch - ckh * per_kh;
+    const int ckw = rch / p.cb, cc0 = (rch - ckw * p.cb) * 32;
+    const uint32_t bytes = (uint32_t)(nchunks * kChunkBytes + L::kBBytes);
+    const int per_img = p.tiles_w * p.tiles_h;
+    // k-block -> (image group, tile row, tile column), kept incrementally
+    int grp = kb_lo / per_img, r = kb_lo - grp * per_img;
+    int th_i = r / p.tiles_w, tw_i = r - th_i * p.tiles_w;
+    int y0 = 0, x0 = 0;
+    if (p.crop && has_a && grp * p.tn < p.B) { y0 = p.crop[2 * grp * p.tn]; x0 = p.crop[2 * grp * p.tn + 1]; }
+    int stage = 0, phase = 0;
+    for (int kb = kb_lo; kb < kb_hi; ++kb) {
+      const int n0 = grp * p.tn, oh0 = th_i * p.th, ow0 = tw_i * p.tw;
+      // next k-block's position (and its crop offsets, fetched before the wait so the load latency hides)
+      int ngrp = grp, nth = th_i, ntw = tw_i + 1;
+      if (ntw == p.tiles_w) { ntw = 0; if (++nth == p.tiles_h) { nth = 0; ++ngrp; } }
+      int ny0 = y0, nx0 = x0;
+      if (p.crop && has_a && ngrp != grp && kb + 1 < kb_hi && ngrp * p.tn < p.B) {
+        ny0 = p.crop[2 * ngrp * p.tn]; nx0 = p.crop[2 * ngrp * p.tn + 1];
       }
-      const uint32_t bytes = (uint32_t)(nchunks * kChunkBytes + L::kBBytes);
-      const int per_img = p.tiles_w * p.tiles_h;
-      int stage = 0, phase = 0;
-      for (int kb = kb_lo; kb < kb_hi; ++kb) {
-        if (!mbar_wait(&empty_bar[stage], phase ^ 1)) { if (p.err) *p.err = 11; break; }
-        int grp = kb / per_img, r = kb - grp * per_img;
-        int th_i = r / p.tiles_w, tw_i = r - th_i * p.tiles_w;
-        int n0 = grp * p.tn, oh0 = th_i * p.th, ow0 = tw_i * p.tw;
-        int y0 = 0, x0 = 0;
-        if (p.crop && n0 < p.B) { y0 = p.crop[2 * n0]; x0 = p.crop[2 * n0 + 1]; }
-        uint8_t* a_dst = smem + stage * L::kStageBytes;
-        uint8_t* b_dst = a_dst + kWABytes;
-        mbar_expect_tx(&full_bar[stage], bytes);
-        for (int j = 0; j < nchunks; ++j)
-          tma_load_4d(a_dst + j * kChunkBytes, &tmap_x, &full_bar[stage], cc0[j], ow0 + ckw[j] + x0,
-                      oh0 + ckh[j] + y0, n0);
-#pragma unroll
-        for (int j = 0; j < BLOCK_N / 32; ++j)
-          tma_load_4d(b_dst + j * kChunkBytes, &tmap_dz, &full_bar[stage], n_tile0 + j * 32, ow0, oh0, n0);
-        if (++stage == kWStages) { stage = 0; phase ^= 1; }
-      }
+      if (!mbar_wait(&empty_bar[stage], phase ^ 1)) { if (p.err) *p.err = 11; break; }
+      uint8_t* a_dst = smem + stage * L::kStageBytes;
+      if (pj == 0) mbar_expect_tx(&full_bar[stage], bytes);
+      if (has_a)
+        tma_load_4d(a_dst + pj * kChunkBytes, &tmap_x, &full_bar[stage], cc0, ow0 + ckw + x0, oh0 + ckh + y0, n0);
+      if (has_b)
+        tma_load_4d(a_dst + kWABytes + pj * kChunkBytes, &tmap_dz, &full_bar[stage], n_tile0 + pj * 32, ow0, oh0, n0);
+      if (++stage == kWStages) { stage = 0; phase ^= 1; }
+      grp = ngrp; th_i = nth; tw_i = ntw; y0 = ny0; x0 = nx0;
     }
+  }
+  __syncwarp();
+  if (warp == 0) {
+    // warp 0 only issues loads
   } else if (warp == 1) {
     if (elect_one()) {
       constexpr uint32_t idesc = make_idesc_tf32(128, BLOCK_N, 1, 1);   // both operands MN-major
+      // descriptor of stage 0; stages / k-steps only add to the 14-bit address field
+      const uint64_t desc0 = make_smem_desc(smem_u32(smem), kChunkBytes, 512, 1);
+      uint64_t ad = desc0;
       int stage = 0, phase = 0;
       for (int i = 0; i < nkb; ++i) {
         if (!mbar_wait(&full_bar[stage], phase)) { if (p.err) *p.err = 12; break; }
         tc_fence_after();
-        uint32_t a_addr = smem_u32(smem + stage * L::kStageBytes);
-        uint32_t b_addr = a_addr + kWABytes;
+        const uint64_t bd = ad + (kWABytes >> 4);
 #pragma unroll
-        for (int ks = 0; ks < 8; ++ks) {   // 8 pixels per MMA
-          uint64_t ad = make_smem_desc(a_addr + ks * 1024, kChunkBytes, 512, 1);
-          uint64_t bd = make_smem_desc(b_addr + ks * 1024, kChunkBytes, 512, 1);
-          mma_tf32(tmem_base, ad, bd, idesc, (i | ks) ? 1u : 0u);
-        }
+        for (int ks = 0; ks < 8; ++ks)     // 8 pixels per MMA
+          mma_tf32(tmem_base, ad + ks * (1024 >> 4), bd + ks * (1024 >> 4), idesc, (i | ks) ? 1u : 0u);
         mma_commit(&empty_bar[stage]);
-        if (++stage == kWStages) { stage = 0; phase ^= 1; }
+        ad += (L::kStageBytes >> 4);
+        if (++stage == kWStages) { stage = 0; phase ^= 1; ad = desc0; }
       }
       mma_commit(tmem_full);
     }
@@ -205,6 +220,8 @@ struct ReduceSeg { const float* part; float* gw; int nsplit, m_pad, K, N, ldw, f
 struct ReduceArgs { ReduceSeg seg[8]; int nseg; };
 
 __global__ void __launch_bounds__(256) multi_wgrad_reduce_kernel(ReduceArgs a) {
+  pdl_trigger();
+  pdl_wait();
   int s = 0;
   while (s + 1 < a.nseg && (int)blockIdx.x >= a.seg[s + 1].first_block) ++s;
   const ReduceSeg sg = a.seg[s];
@@ -272,8 +289,7 @@ static int launch_wgrad(const CUtensorMap& tx, const CUtensorMap& tz, const Wgra
     attr_done = true;
   }
   dim3 grid(m_tiles, p.N / BLOCK_N, nsplit);
-  umma_wgrad_kernel<BLOCK_N><<<grid, 192, L::kTotal, st>>>(tx, tz, p);
-  MPIT_LAUNCH_CHECK();
+  MPIT_CUDA_TRY(launch_k(umma_wgrad_kernel<BLOCK_N>, grid, dim3(192), (size_t)L::kTotal, st, tx, tz, p));
   return 0;
 }
 
@@ -359,8 +375,7 @@ int mpit_multi_wgrad_reduce(int nseg, const unsigned long long* parts, const uns
     a.seg[i].first_block = blocks;
     blocks += (int)(((long long)K[i] * N[i] + 255) / 256);
   }
-  multi_wgrad_reduce_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(a);
-  MPIT_LAUNCH_CHECK();
+  MPIT_CUDA_TRY(launch_k(multi_wgrad_reduce_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, a));
   return 0;
 }
 

@@ -26,6 +26,13 @@ extern "C" {
 #define MPIT_E_ARG (-4)
 #define MPIT_E_SCRATCH (-5)   /* request exceeds the built-in scratch of a *_noalloc entry point */
 
+/* Programmatic dependent launch for the training-step kernels (boundary, prep, igemm, wgrad, loss,
+ * reduces): when on (default) each of them may begin its set-up while the previous kernel on the
+ * stream is still running and blocks in `griddepcontrol.wait` before touching data.
+ * enabled: 1 on, 0 off, <0 query only.  Returns the previous setting.  Takes effect for launches
+ * (and graph captures) made after the call.  No reference counterpart. */
+int mpit_set_pdl(int enabled);
+
 /* ---- optimizer rules (csrc/kernels/optim.cu) ------------------------------------------ */
 
 /* Rule ids for mpit_rule_step (server rules of /root/reference/BiCNN/pserver.lua:123-198 and
@@ -72,8 +79,10 @@ int mpit_act_bwd(const float* dout, const float* out, const unsigned char* pool_
                  int OW, int C, int pool, float scale, void* stream);
 int mpit_colsum(const float* dz, float* db, long long rows, int C, void* stream);
 int mpit_prep_u8(const unsigned char* src, float* dst, int B, int SH, int SW, int cin, void* stream);
+/* loss_sum = (accumulate ? loss_sum : 0) + sum of per-sample NLL; dlogits (may be NULL) = gscale * dNLL. */
 int mpit_nll_fwd_bwd(const float* logits, const int* labels, float* dlogits, float* loss_sum, int* confusion,
-                     int B, int ncls, int ld, float gscale, unsigned long long* rng_inc, void* stream);
+                     int B, int ncls, int ld, float gscale, unsigned long long* rng_inc, int accumulate,
+                     void* stream);
 
 /* ---- NVLink exchange kernels (csrc/kernels/comm.cu) -------------------------------------- */
 /* `shard_ptrs` is a HOST array of nranks device addresses: entry s is rank s's shard of the

@@ -43,6 +43,8 @@ def kernels() -> ctypes.CDLL:
     from ._cabi import bind
     lib = _load("libmpit_kernels.so")
     bind(lib, "mpit_b200.h")
+    if os.environ.get("MPIT_PDL", "1") == "0":     # programmatic dependent launch off (A/B runs, debugging)
+        lib.mpit_set_pdl(0)
     return lib
 
 

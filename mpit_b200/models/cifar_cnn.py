@@ -341,7 +341,6 @@ class CifarEngine:
 
     def loss_and_grad(self, train: bool = True) -> None:
         L5 = self.layers[-1]
-        self.loss_sum.zero_()
         self.ops.nll_fwd_bwd(self.act[-1], self.labels, self.dz[-1] if train else None, self.loss_sum,
                              self.B, self.ncls, L5.CO, gscale=1.0 / self.B, confusion=self.confusion,
                              rng_inc=self.rng if train else None)

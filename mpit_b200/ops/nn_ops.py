@@ -68,6 +68,9 @@ def prep_u8(src, dst, B, SH, SW, cin=3):
     check(kernels().mpit_prep_u8(ptr(src), ptr(dst), B, SH, SW, cin, cur_stream()), "mpit_prep_u8")
 
 
-def nll_fwd_bwd(logits, labels, dlogits, loss_sum, B, ncls, ld, *, gscale, confusion=None, rng_inc=None):
+def nll_fwd_bwd(logits, labels, dlogits, loss_sum, B, ncls, ld, *, gscale, confusion=None, rng_inc=None,
+                accumulate=False):
+    """``loss_sum`` is overwritten with the batch's summed NLL (added to when ``accumulate``)."""
     check(kernels().mpit_nll_fwd_bwd(ptr(logits), ptr(labels), ptr(dlogits), ptr(loss_sum), ptr(confusion),
-                                     B, ncls, ld, gscale, ptr(rng_inc), cur_stream()), "mpit_nll_fwd_bwd")
+                                     B, ncls, ld, gscale, ptr(rng_inc), int(accumulate), cur_stream()),
+          "mpit_nll_fwd_bwd")
