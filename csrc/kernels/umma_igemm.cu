@@ -48,7 +48,7 @@ struct IgemmParams {
   const unsigned long long* rng;
   int* err;                  // set to 1 when a bounded pipeline wait expires
   int stages;                // smem pipeline depth (2..kMaxStages), chosen per launch
-  long long* dbg;            // optional per-CTA timeline (8 clock64 stamps per CTA), null in production
+  long long* dbg;            // optional per-CTA timeline (16 clock64 stamps per CTA), null in production
 };
 
 constexpr int kMaxStages = 12;
@@ -63,10 +63,28 @@ struct SmemLayout {
   static constexpr int total(int stages) { return stages * kStageBytes + 256 + 1024; }   // + barriers + align slack
 };
 
+// Out of line on purpose.  An epilogue runs once per CTA, so its code is fetched cold; with tanh and Philox
+// inlined into each of the 8 unrolled store steps the taken path hopped over ~16 KB of skipped code per
+// step and the instruction misses cost > 1 us per tile.  As functions their lines are fetched once.
+__device__ __noinline__ float4 tanh4_ool(float4 x) { return make_float4(tanhf(x.x), tanhf(x.y), tanhf(x.z), tanhf(x.w)); }
+// Keep-bits of four float4 groups at once: four independent Philox chains interleave, so the call costs
+// about one chain's latency.  Nibble j of the result belongs to idx_j (bit k = element k of the group).
+__device__ __noinline__ uint32_t keep4_ool(unsigned long long seed, uint32_t step, unsigned long long i0,
+                                           unsigned long long i1, unsigned long long i2, unsigned long long i3) {
+  const uint4 r0 = Philox::gen(seed, i0, step), r1 = Philox::gen(seed, i1, step);
+  const uint4 r2 = Philox::gen(seed, i2, step), r3 = Philox::gen(seed, i3, step);
+  auto nib = [](const uint4& r) { return (r.x & 1u) | ((r.y & 1u) << 1) | ((r.z & 1u) << 2) | ((r.w & 1u) << 3); };
+  return nib(r0) | (nib(r1) << 4) | (nib(r2) << 8) | (nib(r3) << 12);
+}
+
 __device__ __forceinline__ void subtile_origin(const IgemmParams& p, int s, int& n0, int& oh0, int& ow0) {
-  int per_img = p.tiles_w * p.tiles_h;
-  int grp = s / per_img, r = s - grp * per_img;
-  int th_i = r / p.tiles_w, tw_i = r - th_i * p.tiles_w;
+  // integer division is ~100 clocks of dependent latency on the issue path: skip it in the common cases
+  // (one sub-tile per image group, or a single column of sub-tiles)
+  const int per_img = p.tiles_w * p.tiles_h;
+  int grp = s, r = 0;
+  if (per_img != 1) { grp = s / per_img; r = s - grp * per_img; }
+  int th_i = r, tw_i = 0;
+  if (p.tiles_w != 1) { th_i = r / p.tiles_w; tw_i = r - th_i * p.tiles_w; }
   n0 = grp * p.tn;
   oh0 = th_i * p.th;
   ow0 = tw_i * p.tw;
@@ -75,7 +93,10 @@ __device__ __forceinline__ void subtile_origin(const IgemmParams& p, int s, int&
 // Body shared by the plain kernel and the pull-fused kernel.  `tmap_a_p`/`tmap_b_p` point into
 // kernel-parameter space; `b_row0` is the row coordinate of this CTA's B tile inside *its* tensor map
 // (equal to the output column offset unless B lives in a peer's shard).
-template <int BLOCK_N>
+// MODE (the epilogue) is a template parameter: with all five epilogues, 32-column unrolling, tanh and Philox
+// inlined in one body the kernel was ~100 KB of straight-line code that every CTA walks once, and the cold
+// instruction fetches cost more than the math (the "math" phase of a 32-column epilogue measured 1.2 us).
+template <int BLOCK_N, int MODE>
 __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CUtensorMap* tmap_b_p, const int b_row0,
                                            const IgemmParams& p) {
   const CUtensorMap& tmap_a = *tmap_a_p;
@@ -94,7 +115,7 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
   const int n_tile0 = blockIdx.y * BLOCK_N;
   const int rows_per_sub = 128 / p.nsub;
 
-  long long* dbg = p.dbg ? p.dbg + 8 * (blockIdx.y * gridDim.x + blockIdx.x) : nullptr;
+  long long* dbg = p.dbg ? p.dbg + 16 * (blockIdx.y * gridDim.x + blockIdx.x) : nullptr;
   pdl_trigger();   // let the next kernel of the step begin its own set-up now
   if (dbg && threadIdx.x == 0) dbg[0] = clock64();
   if (warp == 0 && lane == 0) {
@@ -111,6 +132,11 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();      // everything above overlapped the previous kernel; its results are visible from here on
   if (dbg && threadIdx.x == 0) dbg[1] = clock64();   // prologue done
+  // The epilogue's bias row goes to shared memory now, so its global-load latency hides under the main loop
+  // (fetched after the accumulator was ready, 32 scalar loads cost the fc layers > 2 us each).
+  __shared__ __align__(16) float bias_s[256];
+  if (warp >= 2)
+    for (int c = threadIdx.x - 64; c < BLOCK_N; c += 128) bias_s[c] = p.bias ? p.bias[n_tile0 + c] : 0.f;
 
   // ===== TMA producers =====
   // Issuing a k-block (wait for the slot, expect_tx, 2-3 tensor loads with their coordinate arithmetic) is a
@@ -128,7 +154,7 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
     for (int j = 0; j < p.nsub; ++j) {
       subtile_origin(p, tile * p.nsub + j, n0[j], oh0[j], ow0[j]);
       // (in MAXTIME mode `crop` carries per-sentence frame counts for the epilogue, not offsets)
-      if (p.crop && p.mode != EPI_MAXTIME && n0[j] < p.B) { oh0[j] += p.crop[2 * n0[j]]; ow0[j] += p.crop[2 * n0[j] + 1]; }
+      if (p.crop && MODE != EPI_MAXTIME && n0[j] < p.B) { oh0[j] += p.crop[2 * n0[j]]; ow0[j] += p.crop[2 * n0[j] + 1]; }
     }
     const int sub_bytes = rows_per_sub * 128;
     int stage = 0, phase = 0, kh = 0, kw = 0, cblk = 0;
@@ -139,8 +165,10 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
       while (cblk >= p.cb) { cblk -= p.cb; if (++kw == p.kw_it) { kw = 0; ++kh; } }
     };
     advance(pi);
+    if (dbg && warp == 0) dbg[8] = clock64();   // producer set-up done
     for (int kb = pi; kb < p.num_kb; kb += kProducers) {
       if (!mbar_wait(&empty_bar[stage], phase ^ 1)) { if (p.err) *p.err = 1; break; }
+      if (dbg && kb == 0) dbg[9] = clock64();   // first slot free
       uint8_t* a_dst = smem + stage * L::kStageBytes;
       mbar_expect_tx(&full_bar[stage], L::kStageBytes);
       tma_load_4d(a_dst, &tmap_a, &full_bar[stage], cblk * 32, ow0[0] + p.sgn * kw, oh0[0] + p.sgn * kh, n0[0]);
@@ -148,6 +176,7 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
         tma_load_4d(a_dst + sub_bytes, &tmap_a, &full_bar[stage], cblk * 32, ow0[1] + p.sgn * kw, oh0[1] + p.sgn * kh,
                     n0[1]);
       tma_load_2d(a_dst + kABytes, &tmap_b, &full_bar[stage], kb * 32, b_row0);
+      if (dbg && kb == 0) dbg[10] = clock64();  // first k-block's loads issued
       advance(kProducers);
     }
     if (dbg && warp == 0) dbg[2] = clock64();   // warp 0's last TMA issued
@@ -187,50 +216,29 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
     const int w_ = rr % p.tw, h_ = (rr / p.tw) % p.th, nn = rr / (p.tw * p.th);
     const int n = n0 + nn, oh = oh0 + h_, ow = ow0 + w_;
     const bool valid = n < p.B && oh < p.OH && ow < p.OW;
-    if (!mbar_wait(tmem_full, 0)) { if (p.err) *p.err = 3; }
-    if (dbg && threadIdx.x == 64) dbg[5] = clock64();   // accumulator ready
-    tc_fence_after();
     unsigned long long seed = 0, step = 0;
     if (p.dropout) { seed = p.rng[0]; step = p.rng[1]; }
+    if constexpr (MODE == EPI_POOL || MODE == EPI_MAXTIME) {
+      // ---- lane == output row (the reductions run across rows with warp shuffles) ----
+      if (!mbar_wait(tmem_full, 0)) { if (p.err) *p.err = 3; }
+      if (dbg && threadIdx.x == 64) dbg[5] = clock64();   // accumulator ready
+      tc_fence_after();
+      asm volatile("bar.sync 1, 128;" ::: "memory");      // bias_s written by all four epilogue warps
+      __align__(16) unsigned char bi[32];
 #pragma unroll 1
-    for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
-      float v[32];
-      tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
-      const int col0 = n_tile0 + c0;
-      if (p.mode == EPI_STORE) {
-        size_t orow = ((size_t)n * p.OH + oh) * p.OW + ow;
-        size_t obase = orow * p.N + col0;
-#pragma unroll
-        for (int c = 0; c < 32; ++c) {
-          float x = v[c] + (p.bias ? p.bias[col0 + c] : 0.f);
-          if (p.relu == 1) x = fmaxf(x, 0.f);
-          else if (p.relu == 2) x = tanhf(x);
-          v[c] = x;
-        }
-        if (p.dropout) {
-#pragma unroll
-          for (int c4 = 0; c4 < 8; ++c4) {
-            uint4 rnd = Philox::gen(seed, (unsigned long long)((obase + 4 * c4) >> 2), (uint32_t)step);
-            v[4 * c4 + 0] = (rnd.x & 1u) ? v[4 * c4 + 0] * 2.f : 0.f;
-            v[4 * c4 + 1] = (rnd.y & 1u) ? v[4 * c4 + 1] * 2.f : 0.f;
-            v[4 * c4 + 2] = (rnd.z & 1u) ? v[4 * c4 + 2] * 2.f : 0.f;
-            v[4 * c4 + 3] = (rnd.w & 1u) ? v[4 * c4 + 3] * 2.f : 0.f;
-          }
-        }
-        if (valid) {
-#pragma unroll
-          for (int c4 = 0; c4 < 8; ++c4)
-            st4(p.out + obase + 4 * c4, make_float4(v[4 * c4], v[4 * c4 + 1], v[4 * c4 + 2], v[4 * c4 + 3]));
-        }
-      } else if (p.mode == EPI_POOL) {
+      for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+        float v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
+        if (dbg && threadIdx.x == 64 && c0 == 0) dbg[11] = clock64();   // first TMEM read done
+        const int col0 = n_tile0 + c0;
+        if (MODE == EPI_POOL) {
         // 2x2 max over (oh^1, ow^1): partners are lane+1, lane+tw, lane+tw+1 of the even/even lane
         const bool writer = ((h_ | w_) & 1) == 0;
         const int PH = p.OH >> 1, PW = p.OW >> 1;
         size_t obase = ((((size_t)n * PH + (oh >> 1)) * PW + (ow >> 1)) * p.N) + col0;
-        unsigned char bi[32];
 #pragma unroll
         for (int c = 0; c < 32; ++c) {
-          float x = v[c] + (p.bias ? p.bias[col0 + c] : 0.f);
+          float x = v[c] + bias_s[c0 + c];
           float x01 = __shfl_down_sync(0xffffffffu, x, 1);
           float x10 = __shfl_down_sync(0xffffffffu, x, p.tw);
           float x11 = __shfl_down_sync(0xffffffffu, x, p.tw + 1);
@@ -252,29 +260,7 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
           ip[0] = bp[0];
           ip[1] = bp[1];
         }
-      } else if (p.mode == EPI_MASK) {
-        size_t orow = ((size_t)n * p.OH + oh) * p.OW + ow;
-        size_t obase = orow * p.N + col0;
-        if (valid) {
-#pragma unroll
-          for (int c4 = 0; c4 < 8; ++c4) {
-            float4 a = ld4(p.aux + obase + 4 * c4);
-            float4 o;
-            if (p.relu == 2) {   // d tanh: g * (1 - h^2)
-              o.x = v[4 * c4 + 0] * (1.f - a.x * a.x) * p.scale;
-              o.y = v[4 * c4 + 1] * (1.f - a.y * a.y) * p.scale;
-              o.z = v[4 * c4 + 2] * (1.f - a.z * a.z) * p.scale;
-              o.w = v[4 * c4 + 3] * (1.f - a.w * a.w) * p.scale;
-            } else {
-              o.x = a.x > 0.f ? v[4 * c4 + 0] * p.scale : 0.f;
-              o.y = a.y > 0.f ? v[4 * c4 + 1] * p.scale : 0.f;
-              o.z = a.z > 0.f ? v[4 * c4 + 2] * p.scale : 0.f;
-              o.w = a.w > 0.f ? v[4 * c4 + 3] * p.scale : 0.f;
-            }
-            st4(p.out + obase + 4 * c4, o);
-          }
-        }
-      } else if (p.mode == EPI_MAXTIME) {
+        } else {
         // Temporal convolution -> Max over time -> ReLU (BiCNN/bicnn.lua:59,76-84).  A warp holds the
         // 32 time steps of one sentence (tile = tn sentences x 32 frames): bias, mask frames past the
         // sentence end, butterfly max with the arg-max, then lane c publishes column c with one
@@ -286,7 +272,7 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
         unsigned long long mine = 0ull;
 #pragma unroll
         for (int c = 0; c < 32; ++c) {
-          float x = live ? fmaxf(v[c] + (p.bias ? p.bias[col0 + c] : 0.f), 0.f) : 0.f;
+          float x = live ? fmaxf(v[c] + bias_s[c0 + c], 0.f) : 0.f;
           unsigned long long key = ((unsigned long long)__float_as_uint(x) << 32) | (unsigned)(live ? ow : 0);
 #pragma unroll
           for (int o = 16; o > 0; o >>= 1) {
@@ -297,35 +283,130 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
         }
         if (n < p.B && (col0 + lane) < p.N)
           atomicMax(reinterpret_cast<unsigned long long*>(p.out) + (size_t)n * p.N + col0 + lane, mine);
-      } else {  // EPI_EXPAND: un-pool + ReLU mask; rows are pooled positions
-        if (valid) {
-          size_t pbase = ((((size_t)n * p.OH + oh) * p.OW + ow) * p.N) + col0;
-          unsigned char bi[32];
-          const uint4* ip = reinterpret_cast<const uint4*>(p.aux_idx + pbase);
-          uint4* bp = reinterpret_cast<uint4*>(bi);
-          bp[0] = ip[0];
-          bp[1] = ip[1];
-          float a[32];
+        }
+      }
+    } else {
+      // ---- coalesced epilogue (STORE / MASK / EXPAND) ----
+      // TMEM hands every lane one output ROW (32 columns = 128 B).  Storing (or loading the side inputs) in
+      // that arrangement touches 32 different 128-byte lines per warp instruction -- measured 5.4 us for the
+      // un-pooling epilogue of one 128x64 tile.  So each 32x32 block is transposed through a warp-private,
+      // XOR-swizzled 4 KB tile in (by now idle) pipeline memory: afterwards 8 adjacent lanes cover one
+      // 128-byte row segment and a warp instruction touches 4 full lines.
+      __shared__ long long rowoff_s[128];   // element offset of each tile row's output row, -1 = out of range
+      __shared__ long long rowdst_s[128];   // EXPAND: offset of the 2x2 window's top-left pixel
+      const size_t row_base = (((size_t)n * p.OH + oh) * p.OW + ow) * p.N + n_tile0;
+      rowoff_s[row] = valid ? (long long)row_base : -1;
+      if (MODE == EPI_EXPAND)
+        rowdst_s[row] = (long long)((((size_t)n * (2 * p.OH) + 2 * oh) * (2 * p.OW) + 2 * ow) * p.N + n_tile0);
+      __syncwarp();
+      const int sub = lane >> 3, ch = lane & 7;   // row within a group of 4, 16-byte chunk within the row
+      long long off[8], dst[8];
 #pragma unroll
-          for (int c4 = 0; c4 < 8; ++c4) {
-            float4 t = ld4(p.aux + pbase + 4 * c4);
-            a[4 * c4] = t.x; a[4 * c4 + 1] = t.y; a[4 * c4 + 2] = t.z; a[4 * c4 + 3] = t.w;
-          }
+      for (int i = 0; i < 8; ++i) {
+        off[i] = rowoff_s[quad * 32 + i * 4 + sub];
+        dst[i] = MODE == EPI_EXPAND ? rowdst_s[quad * 32 + i * 4 + sub] : 0;
+      }
+      // side inputs (stored activation, pool index) are fetched BEFORE the accumulator is waited for
+      float4 ax[8];
+      uint32_t ai[8];
+      auto fetch_side = [&](int c0) {
+        if (MODE == EPI_STORE) return;
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            size_t drow = ((size_t)n * (2 * p.OH) + 2 * oh + (q >> 1)) * (2 * p.OW) + 2 * ow + (q & 1);
-            float* dst = p.out + drow * p.N + col0;
+        for (int i = 0; i < 8; ++i) {
+          if (off[i] < 0) continue;
+          ax[i] = ld4(p.aux + off[i] + c0 + 4 * ch);
+          if (MODE == EPI_EXPAND) ai[i] = *reinterpret_cast<const uint32_t*>(p.aux_idx + off[i] + c0 + 4 * ch);
+        }
+      };
+      fetch_side(0);
+      // touch the output rows now: the first access of an SM to a page costs ~1 us (translation miss), which
+      // otherwise lands on the critical path between "accumulator ready" and the first store
+      if (off[0] >= 0) {
+        const float* o0 = MODE == EPI_EXPAND ? p.out + (size_t)dst[0] : p.out + (size_t)off[0];
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(o0 + 4 * ch));
+      }
+      if (!mbar_wait(tmem_full, 0)) { if (p.err) *p.err = 3; }
+      if (dbg && threadIdx.x == 64) dbg[5] = clock64();   // accumulator ready
+      tc_fence_after();
+      asm volatile("bar.sync 1, 128;" ::: "memory");      // bias_s written by all four epilogue warps
+      const uint32_t tile = smem_u32(smem) + quad * 4096;   // stage 0 is idle: every MMA has completed
+      const size_t up = (size_t)2 * p.OW * p.N;                      // EXPAND: one image row down
+#pragma unroll 1
+      for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+        float v[32];
+        if (c0) fetch_side(c0);
+        tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
+        if (dbg && threadIdx.x == 64 && c0 == 0) dbg[11] = clock64();   // first TMEM read done
 #pragma unroll
-            for (int c4 = 0; c4 < 8; ++c4) {
+        for (int c4 = 0; c4 < 8; ++c4)
+          sts4(tile + (lane * 8 + (c4 ^ (lane & 7))) * 16, v[4 * c4], v[4 * c4 + 1], v[4 * c4 + 2], v[4 * c4 + 3]);
+        __syncwarp();
+        float4 xs[8];     // all eight reads first: explicit shared-space loads, nothing for them to alias with
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int r = i * 4 + sub;
+          xs[i] = lds4(tile + (r * 8 + (ch ^ (r & 7))) * 16);
+        }
+        if (dbg && threadIdx.x == 64 && c0 == 0) dbg[12] = clock64();   // first block transposed
+        const float4 b4 = *reinterpret_cast<const float4*>(&bias_s[c0 + 4 * ch]);
+        uint32_t keep = 0;
+        if (MODE == EPI_STORE && p.dropout) {
+          auto gi = [&](int i) { return (unsigned long long)(((size_t)off[i] + c0 + 4 * ch) >> 2); };
+          keep = keep4_ool(seed, (uint32_t)step, gi(0), gi(1), gi(2), gi(3)) |
+                 (keep4_ool(seed, (uint32_t)step, gi(4), gi(5), gi(6), gi(7)) << 16);
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float4 x = xs[i];
+          if (off[i] < 0) continue;
+          const size_t e0 = (size_t)off[i] + c0 + 4 * ch;
+          if (MODE == EPI_STORE) {
+            x.x += b4.x; x.y += b4.y; x.z += b4.z; x.w += b4.w;
+            if (p.relu == 1) {
+              x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
+            } else if (p.relu == 2) {
+              x = tanh4_ool(x);
+            }
+            if (p.dropout) {
+              const uint32_t kb = keep >> (4 * i);
+              x.x = (kb & 1u) ? x.x * 2.f : 0.f;
+              x.y = (kb & 2u) ? x.y * 2.f : 0.f;
+              x.z = (kb & 4u) ? x.z * 2.f : 0.f;
+              x.w = (kb & 8u) ? x.w * 2.f : 0.f;
+            }
+            st4(p.out + e0, x);
+          } else if (MODE == EPI_MASK) {
+            const float4 h = ax[i];
+            float4 o;
+            if (p.relu == 2) {   // d tanh: g * (1 - h^2)
+              o.x = x.x * (1.f - h.x * h.x) * p.scale;
+              o.y = x.y * (1.f - h.y * h.y) * p.scale;
+              o.z = x.z * (1.f - h.z * h.z) * p.scale;
+              o.w = x.w * (1.f - h.w * h.w) * p.scale;
+            } else {
+              o.x = h.x > 0.f ? x.x * p.scale : 0.f;
+              o.y = h.y > 0.f ? x.y * p.scale : 0.f;
+              o.z = h.z > 0.f ? x.z * p.scale : 0.f;
+              o.w = h.w > 0.f ? x.w * p.scale : 0.f;
+            }
+            st4(p.out + e0, o);
+          } else {  // EPI_EXPAND: un-pool + ReLU mask; tile rows are pooled positions
+            const float4 h = ax[i];
+            const uint32_t bsel = ai[i];   // four arg-max codes (0..3), one byte per column
+            float* d0 = p.out + (size_t)dst[i] + c0 + 4 * ch;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
               float4 o;
-              o.x = (bi[4 * c4 + 0] == q && a[4 * c4 + 0] > 0.f) ? v[4 * c4 + 0] * p.scale : 0.f;
-              o.y = (bi[4 * c4 + 1] == q && a[4 * c4 + 1] > 0.f) ? v[4 * c4 + 1] * p.scale : 0.f;
-              o.z = (bi[4 * c4 + 2] == q && a[4 * c4 + 2] > 0.f) ? v[4 * c4 + 2] * p.scale : 0.f;
-              o.w = (bi[4 * c4 + 3] == q && a[4 * c4 + 3] > 0.f) ? v[4 * c4 + 3] * p.scale : 0.f;
-              st4(dst + 4 * c4, o);
+              o.x = ((bsel & 0xffu) == (uint32_t)q && h.x > 0.f) ? x.x * p.scale : 0.f;
+              o.y = (((bsel >> 8) & 0xffu) == (uint32_t)q && h.y > 0.f) ? x.y * p.scale : 0.f;
+              o.z = (((bsel >> 16) & 0xffu) == (uint32_t)q && h.z > 0.f) ? x.z * p.scale : 0.f;
+              o.w = ((bsel >> 24) == (uint32_t)q && h.w > 0.f) ? x.w * p.scale : 0.f;
+              st4(d0 + (q >> 1) * up + (q & 1) * p.N, o);
             }
           }
         }
+        if (dbg && threadIdx.x == 64 && c0 == 0) dbg[13] = clock64();   // first iteration's stores issued
+        __syncwarp();
       }
     }
     tc_fence_before();
@@ -339,11 +420,11 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
   if (dbg && threadIdx.x == 0) dbg[7] = clock64();
 }
 
-template <int BLOCK_N>
+template <int BLOCK_N, int MODE>
 __global__ void __launch_bounds__(192)
 umma_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                   const IgemmParams p) {
-  igemm_body<BLOCK_N>(&tmap_a, &tmap_b, blockIdx.y * BLOCK_N, p);
+  igemm_body<BLOCK_N, MODE>(&tmap_a, &tmap_b, blockIdx.y * BLOCK_N, p);
 }
 
 // Parameter pull fused with the GEMM that consumes the weights: the B operand (rows of a Linear /
@@ -362,7 +443,7 @@ umma_igemm_pull_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
                        const IgemmParams p) {
   const int n_tile0 = blockIdx.y * BLOCK_N;
   const int owner = n_tile0 / pm.rows_per_owner;
-  igemm_body<BLOCK_N>(&tmap_a, &pm.map[owner], n_tile0 - owner * pm.rows_per_owner, p);
+  igemm_body<BLOCK_N, EPI_STORE>(&tmap_a, &pm.map[owner], n_tile0 - owner * pm.rows_per_owner, p);
 }
 
 // ---- host side -----------------------------------------------------------------------------------
@@ -379,13 +460,13 @@ static decltype(&cuTensorMapEncodeTiled) get_encode() {
   return fn;
 }
 
-template <int BLOCK_N>
+template <int BLOCK_N, int MODE>
 static int launch_igemm(const CUtensorMap* ta, const CUtensorMap* tb, IgemmParams p, int m_tiles,
                         cudaStream_t st) {
   using L = SmemLayout<BLOCK_N>;
   static bool attr_done = false;
   if (!attr_done) {
-    MPIT_CUDA_TRY(cudaFuncSetAttribute(umma_igemm_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    MPIT_CUDA_TRY(cudaFuncSetAttribute(umma_igemm_kernel<BLOCK_N, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        L::total(L::kMaxFit)));
     attr_done = true;
   }
@@ -397,7 +478,7 @@ static int launch_igemm(const CUtensorMap* ta, const CUtensorMap* tb, IgemmParam
   if (stages > p.num_kb) stages = p.num_kb < 2 ? 2 : p.num_kb;
   if (stages > L::kMaxFit) stages = L::kMaxFit;
   p.stages = stages;
-  MPIT_CUDA_TRY(launch_k(umma_igemm_kernel<BLOCK_N>, grid, dim3(192), (size_t)L::total(stages), st, *ta, *tb, p));
+  MPIT_CUDA_TRY(launch_k(umma_igemm_kernel<BLOCK_N, MODE>, grid, dim3(192), (size_t)L::total(stages), st, *ta, *tb, p));
   return 0;
 }
 
@@ -438,7 +519,7 @@ int mpit_umma_igemm(const void* tmap_a128, const void* tmap_b128, const int* geo
                     int block_n, void* stream) {
   IgemmParams p{};
   {
-    // MPIT_IGEMM_DBG=<device address of a long long[8 * ctas] buffer>: per-CTA timeline for tuning
+    // MPIT_IGEMM_DBG=<device address of a long long[16 * ctas] buffer>: per-CTA timeline for tuning
     static long long* dbg_buf = []() -> long long* {
       const char* e = getenv("MPIT_IGEMM_DBG");
       return e ? reinterpret_cast<long long*>(strtoull(e, nullptr, 0)) : nullptr;
@@ -463,10 +544,20 @@ int mpit_umma_igemm(const void* tmap_a128, const void* tmap_b128, const int* geo
   const CUtensorMap* tb = &tb_;
   cudaStream_t st = (cudaStream_t)stream;
   switch (block_n) {
-    case 32: return launch_igemm<32>(ta, tb, p, m_tiles, st);
-    case 64: return launch_igemm<64>(ta, tb, p, m_tiles, st);
-    case 128: return launch_igemm<128>(ta, tb, p, m_tiles, st);
-    case 256: return launch_igemm<256>(ta, tb, p, m_tiles, st);
+#define MPIT_IGEMM_MODES(BN)                                                         \
+  switch (p.mode) {                                                                 \
+    case EPI_STORE: return launch_igemm<BN, EPI_STORE>(ta, tb, p, m_tiles, st);     \
+    case EPI_POOL: return launch_igemm<BN, EPI_POOL>(ta, tb, p, m_tiles, st);       \
+    case EPI_MASK: return launch_igemm<BN, EPI_MASK>(ta, tb, p, m_tiles, st);       \
+    case EPI_EXPAND: return launch_igemm<BN, EPI_EXPAND>(ta, tb, p, m_tiles, st);   \
+    case EPI_MAXTIME: return launch_igemm<BN, EPI_MAXTIME>(ta, tb, p, m_tiles, st); \
+    default: return MPIT_E_ARG;                                                     \
+  }
+    case 32: MPIT_IGEMM_MODES(32)
+    case 64: MPIT_IGEMM_MODES(64)
+    case 128: MPIT_IGEMM_MODES(128)
+    case 256: MPIT_IGEMM_MODES(256)
+#undef MPIT_IGEMM_MODES
     default: return MPIT_E_ARG;
   }
 }

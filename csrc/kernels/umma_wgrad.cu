@@ -158,30 +158,40 @@ umma_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
     }
   } else {
     const int quad = warp & 3;
-    const int row = quad * 32 + lane;
-    const int m_global = m_tile * 128 + row;
     if (nkb > 0) {
       if (!mbar_wait(tmem_full, 0)) { if (p.err) *p.err = 13; }
     }
     tc_fence_after();
-    float* dst = p.part + ((size_t)split * p.m_pad + m_global) * p.N + n_tile0;
+    // TMEM gives each lane one row (128 B per 32 columns); storing that way touches 32 lines per warp
+    // instruction.  Transpose each 32x32 block through a swizzled warp-private tile in the (now idle)
+    // pipeline memory so that 8 adjacent lanes write one full 128-byte line.
+    const uint32_t tile = smem_u32(smem) + quad * 4096;
+    const int sub = lane >> 3, ch = lane & 7;
+    // rows of chunks this tile does not own hold garbage: write zeros there (one chunk = one warp's 32 rows)
+    const bool rows_ok = nkb > 0 && quad < nchunks;
+    float* dst = p.part + ((size_t)split * p.m_pad + m_tile * 128 + quad * 32) * p.N + n_tile0 + 4 * ch;
 #pragma unroll 1
     for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
-      float v[32];
-      if (nkb > 0) {
+      float4 xs[8];
+      if (rows_ok) {
+        float v[32];
         tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
+#pragma unroll
+        for (int c4 = 0; c4 < 8; ++c4)
+          sts4(tile + (lane * 8 + (c4 ^ (lane & 7))) * 16, v[4 * c4], v[4 * c4 + 1], v[4 * c4 + 2], v[4 * c4 + 3]);
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int r = i * 4 + sub;
+          xs[i] = lds4(tile + (r * 8 + (ch ^ (r & 7))) * 16);
+        }
+        __syncwarp();
       } else {
 #pragma unroll
-        for (int c = 0; c < 32; ++c) v[c] = 0.f;
+        for (int i = 0; i < 8; ++i) xs[i] = make_float4(0.f, 0.f, 0.f, 0.f);
       }
-      // rows of chunks this tile does not own hold garbage: write zeros there
-      const bool row_ok = (row >> 5) < nchunks;
 #pragma unroll
-      for (int c4 = 0; c4 < 8; ++c4) {
-        float4 o = row_ok ? make_float4(v[4 * c4], v[4 * c4 + 1], v[4 * c4 + 2], v[4 * c4 + 3])
-                          : make_float4(0.f, 0.f, 0.f, 0.f);
-        st4(dst + c0 + 4 * c4, o);
-      }
+      for (int i = 0; i < 8; ++i) st4(dst + (size_t)(i * 4 + sub) * p.N + c0, xs[i]);
     }
     tc_fence_before();
   }

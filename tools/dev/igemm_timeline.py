@@ -2,7 +2,7 @@ import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch
 torch.cuda.init()
-dbg = torch.zeros(8 * 2048, dtype=torch.int64, device="cuda")
+dbg = torch.zeros(16 * 2048, dtype=torch.int64, device="cuda")
 os.environ["MPIT_IGEMM_DBG"] = str(dbg.data_ptr())
 from mpit_b200.models.cifar_cnn import *
 B = 128
@@ -15,13 +15,14 @@ torch.cuda.synchronize()
 names = ["conv1 fwd", "conv2 fwd", "conv3 fwd", "fc1 fwd", "fc2 fwd"]
 def show(name, launch, nct):
     dbg.zero_()
+    torch.cuda.synchronize()
     launch.run(eng._umma.err)
     torch.cuda.synchronize()
-    d = dbg.view(-1, 8)[:nct].cpu().double()
+    d = dbg.view(-1, 16)[:nct].cpu().double()
     t0 = d[:, 0].min()
     rel = (d - d[:, 0:1])
     f = lambda i: f"{rel[:, i].mean() / 1.9:8.0f}"
-    print(f"{name:12s} ctas {nct:4d} | ns since CTA start: prologue {f(1)} lastTMA {f(2)} firstFull {f(3)} lastMMAissue {f(4)} accReady {f(5)} epiDone {f(6)} end {f(7)} | span {(d[:,7].max()-t0)/1.9:8.0f}")
+    print(f"{name:12s} ctas {nct:4d} | ns since CTA start: prologue {f(1)} prodSetup {f(8)} slotFree {f(9)} firstIssued {f(10)} lastTMA {f(2)} firstFull {f(3)} lastMMAissue {f(4)} accReady {f(5)} tmemLd {f(11)} math {f(12)} stores {f(13)} epiDone {f(6)} end {f(7)} | span {(d[:,7].max()-t0)/1.9:8.0f}", flush=True)
 cts = [576, 64, 8, 8, 1]
 for i in range(5):
     show(names[i], eng._umma.fwd[i], cts[i])

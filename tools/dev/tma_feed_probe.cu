@@ -62,6 +62,40 @@ __global__ void __launch_bounds__(128) probe_kernel(const __grid_constant__ CUte
   }
 }
 
+// First-load latency: where does the ~1.5 us between "prologue done" and "first operands landed" in the real
+// kernels go?  Variant 0: tensor map passed by value (__grid_constant__, lives in the launch's parameter
+// buffer); variant 1: tensor map in ordinary global memory that stays put across launches.
+__global__ void __launch_bounds__(128) first_load_kernel(const __grid_constant__ CUtensorMap tm_param,
+                                                         const CUtensorMap* tm_global, int use_global, int do_prefetch,
+                                                         long long* out) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ uint64_t bar[2];
+  const CUtensorMap* tm = use_global ? tm_global : &tm_param;
+  long long t0 = clock64();
+  if (threadIdx.x == 0) {
+    if (do_prefetch) prefetch_tmap(tm);
+    mbar_init(&bar[0], 1);
+    mbar_init(&bar[1], 1);
+    fence_barrier_init();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    long long t1 = clock64();
+    mbar_expect_tx(&bar[0], 16384);
+    tma_load_2d(smem, tm, &bar[0], 0, (blockIdx.x & 7) * 128);
+    while (!mbar_try_wait(&bar[0], 0)) {}
+    long long t2 = clock64();
+    mbar_expect_tx(&bar[1], 16384);
+    tma_load_2d(smem + 16384, tm, &bar[1], 32, (blockIdx.x & 7) * 128);
+    while (!mbar_try_wait(&bar[1], 0)) {}
+    long long t3 = clock64();
+    out[blockIdx.x * 4 + 0] = t1 - t0;
+    out[blockIdx.x * 4 + 1] = t2 - t1;
+    out[blockIdx.x * 4 + 2] = t3 - t2;
+  }
+}
+
 static decltype(&cuTensorMapEncodeTiled) get_encode() {
   void* p = nullptr;
   cudaDriverEntryPointQueryResult q;
@@ -83,6 +117,31 @@ int main() {
   cudaMalloc(&out, sizeof(long long) * 1024);
   long long hout[1024];
 
+  {
+    CUtensorMap tm;
+    cuuint64_t dims[2] = {1600, 1024};
+    cuuint64_t strides[1] = {1600 * 4};
+    cuuint32_t box[2] = {32, 128};
+    cuuint32_t es[2] = {1, 1};
+    enc(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, x2, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    CUtensorMap* dtm;
+    cudaMalloc(&dtm, sizeof(tm));
+    cudaMemcpy(dtm, &tm, sizeof(tm), cudaMemcpyHostToDevice);
+    cudaFuncSetAttribute(first_load_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    for (int use_global = 0; use_global < 2; ++use_global)
+      for (int pf = 0; pf < 2; ++pf)
+        for (int g : {1, 148})
+          for (int rep = 0; rep < 3; ++rep) {
+            first_load_kernel<<<g, 128, 40 * 1024>>>(tm, dtm, use_global, pf, out);
+            cudaDeviceSynchronize();
+            cudaMemcpy(hout, out, sizeof(long long) * 4 * g, cudaMemcpyDeviceToHost);
+            double a = 0, b = 0, c = 0;
+            for (int i = 0; i < g; ++i) { a += hout[4 * i]; b += hout[4 * i + 1]; c += hout[4 * i + 2]; }
+            printf("first-load tmap=%s prefetch=%d ctas %3d rep %d : setup %6.0f  first %6.0f  second %6.0f clk\n",
+                   use_global ? "global" : "param ", pf, g, rep, a / g, b / g, c / g);
+          }
+  }
   struct Case { const char* name; int kind, rows, w, h, n; };
   Case cases[] = {
       {"2D 32x128 (16KB)", 0, 128, 0, 0, 0},
