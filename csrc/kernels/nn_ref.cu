@@ -224,8 +224,10 @@ prep_u8_kernel(const unsigned char* __restrict__ src, float* __restrict__ dst, i
 __global__ void __launch_bounds__(1024)
 nll_fwd_bwd_kernel(const float* __restrict__ logits, const int* __restrict__ labels,
                    float* __restrict__ dlogits, float* __restrict__ loss_sum, int* __restrict__ confusion,
-                   int B, int ncls, int ld, float gscale, unsigned long long* __restrict__ rng_inc, int accumulate) {
+                   int B, int ncls, int ld, float gscale, unsigned long long* __restrict__ rng_inc, int accumulate,
+                   float* __restrict__ dbias) {
   __shared__ float part[32];
+  __shared__ float bpart[32][33];
   pdl_trigger();
   pdl_wait();
   // The step counter that keys the dropout Philox stream lives on the device so that a
@@ -233,31 +235,53 @@ nll_fwd_bwd_kernel(const float* __restrict__ logits, const int* __restrict__ lab
   if (rng_inc && blockIdx.x == 0 && threadIdx.x == 0) rng_inc[1] += 1ull;
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, nw = blockDim.x >> 5;
   float mine = 0.f;
-  for (int r = blockIdx.x * nw + wib; r < B; r += gridDim.x * nw) {
-    const float* row = logits + (size_t)r * ld;
-    float z = lane < ncls ? row[lane] : -INFINITY;
-    float m = warp_max(z);
-    float e = lane < ncls ? __expf(z - m) : 0.f;
-    float s = warp_sum(e);
-    float lse = m + __logf(s);
-    int y = labels[r];
-    if (dlogits) {
-      float gz = 0.f;
-      if (lane < ncls) gz = (e / s - (lane == y ? 1.f : 0.f)) * gscale;
-      if (lane < ld) dlogits[(size_t)r * ld + lane] = gz;
+  float bsum = 0.f;     // this lane's class: gradient summed over the rows of this warp
+  const int rstride = gridDim.x * nw;
+  // four rows per warp in flight: their loads are issued together (one CTA serves a whole 128-sample batch,
+  // so per-row load latency would otherwise be paid four times in sequence)
+  for (int r0 = blockIdx.x * nw + wib; r0 < B; r0 += 4 * rstride) {
+    float z[4];
+    int y[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int r = r0 + k * rstride;
+      z[k] = (r < B && lane < ncls) ? logits[(size_t)r * ld + lane] : -INFINITY;
+      y[k] = r < B ? labels[r] : 0;
     }
-    // argmax (first max wins, like torch.max)
-    unsigned ball = __ballot_sync(0xffffffffu, lane < ncls && z == m);
-    int pred = __ffs(ball) - 1;
-    if (lane == 0) {
-      mine += lse - row[y];
-      if (confusion) atomicAdd(confusion + y * ncls + pred, 1);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int r = r0 + k * rstride;
+      if (r >= B) break;
+      float m = warp_max(z[k]);
+      float e = lane < ncls ? __expf(z[k] - m) : 0.f;
+      float s = warp_sum(e);
+      float lse = m + __logf(s);
+      if (dlogits) {
+        float gz = 0.f;
+        if (lane < ncls) gz = (e / s - (lane == y[k] ? 1.f : 0.f)) * gscale;
+        if (lane < ld) dlogits[(size_t)r * ld + lane] = gz;
+        bsum += gz;
+      }
+      // argmax (first max wins, like torch.max)
+      unsigned ball = __ballot_sync(0xffffffffu, lane < ncls && z[k] == m);
+      int pred = __ffs(ball) - 1;
+      float zy = __shfl_sync(0xffffffffu, z[k], y[k] & 31);
+      if (lane == 0) {
+        mine += lse - zy;
+        if (confusion) atomicAdd(confusion + y[k] * ncls + pred, 1);
+      }
     }
   }
   // fixed-order block reduction: with one CTA (the training configuration) the loss is a plain store,
   // bit-reproducible and with no zeroing launch in front of it
   if (lane == 0) part[wib] = mine;
+  if (dbias) bpart[wib][lane] = bsum;
   __syncthreads();
+  if (dbias && wib == 1 && lane < ld) {   // single-CTA launches only (host checks): fixed-order sum over warps
+    float t = 0.f;
+    for (int w = 0; w < nw; ++w) t += bpart[w][lane];
+    dbias[lane] = t;
+  }
   if (wib == 0) {
     float t = lane < nw ? part[lane] : 0.f;
     t = warp_sum(t);
@@ -345,8 +369,9 @@ int mpit_prep_u8(const unsigned char* src, float* dst, int B, int SH, int SW, in
 
 int mpit_nll_fwd_bwd(const float* logits, const int* labels, float* dlogits, float* loss_sum, int* confusion,
                      int B, int ncls, int ld, float gscale, unsigned long long* rng_inc, int accumulate,
-                     void* stream) {
+                     float* dbias, void* stream) {
   if (ncls > 32 || ld > 32) return (int)cudaErrorInvalidValue;
+  if (dbias && (!dlogits || B > 4096)) return MPIT_E_ARG;
   cudaStream_t st = (cudaStream_t)stream;
   // up to 4096 rows: one 1024-thread CTA (32 warps x <=128 rows each) stores the sum directly
   int grid = 1;
@@ -357,7 +382,7 @@ int mpit_nll_fwd_bwd(const float* logits, const int* labels, float* dlogits, flo
     accumulate = 1;
   }
   MPIT_CUDA_TRY(launch_k(nll_fwd_bwd_kernel, dim3(grid), dim3(1024), 0, st, logits, labels, dlogits, loss_sum,
-                         confusion, B, ncls, ld, gscale, rng_inc, accumulate));
+                         confusion, B, ncls, ld, gscale, rng_inc, accumulate, dbias));
   return 0;
 }
 

@@ -16,6 +16,7 @@
 //
 // Layers: asyncsgd/models/7-layers-cnn.lua:8-24 (SpatialConvolution+ReLU+SpatialMaxPooling,
 // Linear+ReLU+Dropout, Linear).
+#include <stdio.h>
 #include "mpit_b200.h"
 #include "common.cuh"
 #include "umma.cuh"
@@ -47,6 +48,7 @@ struct IgemmParams {
   const int* crop;
   const unsigned long long* rng;
   int* err;                  // set to 1 when a bounded pipeline wait expires
+  float* colpart;            // optional [m_tiles][N]: per-tile column sums of the values written (MASK / EXPAND)
   int stages;                // smem pipeline depth (2..kMaxStages), chosen per launch
   long long* dbg;            // optional per-CTA timeline (16 clock64 stamps per CTA), null in production
 };
@@ -294,6 +296,7 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
       // 128-byte row segment and a warp instruction touches 4 full lines.
       __shared__ long long rowoff_s[128];   // element offset of each tile row's output row, -1 = out of range
       __shared__ long long rowdst_s[128];   // EXPAND: offset of the 2x2 window's top-left pixel
+      __shared__ __align__(16) float colsum_s[2 * 128];
       const size_t row_base = (((size_t)n * p.OH + oh) * p.OW + ow) * p.N + n_tile0;
       rowoff_s[row] = valid ? (long long)row_base : -1;
       if (MODE == EPI_EXPAND)
@@ -329,7 +332,7 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
       if (dbg && threadIdx.x == 64) dbg[5] = clock64();   // accumulator ready
       tc_fence_after();
       asm volatile("bar.sync 1, 128;" ::: "memory");      // bias_s written by all four epilogue warps
-      const uint32_t tile = smem_u32(smem) + quad * 4096;   // stage 0 is idle: every MMA has completed
+      const uint32_t xpose = smem_u32(smem) + quad * 4096;   // stage 0 is idle: every MMA has completed
       const size_t up = (size_t)2 * p.OW * p.N;                      // EXPAND: one image row down
 #pragma unroll 1
       for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
@@ -339,16 +342,17 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
         if (dbg && threadIdx.x == 64 && c0 == 0) dbg[11] = clock64();   // first TMEM read done
 #pragma unroll
         for (int c4 = 0; c4 < 8; ++c4)
-          sts4(tile + (lane * 8 + (c4 ^ (lane & 7))) * 16, v[4 * c4], v[4 * c4 + 1], v[4 * c4 + 2], v[4 * c4 + 3]);
+          sts4(xpose + (lane * 8 + (c4 ^ (lane & 7))) * 16, v[4 * c4], v[4 * c4 + 1], v[4 * c4 + 2], v[4 * c4 + 3]);
         __syncwarp();
         float4 xs[8];     // all eight reads first: explicit shared-space loads, nothing for them to alias with
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           const int r = i * 4 + sub;
-          xs[i] = lds4(tile + (r * 8 + (ch ^ (r & 7))) * 16);
+          xs[i] = lds4(xpose + (r * 8 + (ch ^ (r & 7))) * 16);
         }
         if (dbg && threadIdx.x == 64 && c0 == 0) dbg[12] = clock64();   // first block transposed
         const float4 b4 = *reinterpret_cast<const float4*>(&bias_s[c0 + 4 * ch]);
+        float4 csum = make_float4(0.f, 0.f, 0.f, 0.f);   // this lane's 4 columns, summed over its 8 rows
         uint32_t keep = 0;
         if (MODE == EPI_STORE && p.dropout) {
           auto gi = [&](int i) { return (unsigned long long)(((size_t)off[i] + c0 + 4 * ch) >> 2); };
@@ -390,6 +394,7 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
               o.w = h.w > 0.f ? x.w * p.scale : 0.f;
             }
             st4(p.out + e0, o);
+            csum.x += o.x; csum.y += o.y; csum.z += o.z; csum.w += o.w;
           } else {  // EPI_EXPAND: un-pool + ReLU mask; tile rows are pooled positions
             const float4 h = ax[i];
             const uint32_t bsel = ai[i];   // four arg-max codes (0..3), one byte per column
@@ -403,7 +408,27 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
               o.w = ((bsel >> 24) == (uint32_t)q && h.w > 0.f) ? x.w * p.scale : 0.f;
               st4(d0 + (q >> 1) * up + (q & 1) * p.N, o);
             }
+            // exactly one of the four window positions receives the gradient (when the unit was active)
+            csum.x += h.x > 0.f ? x.x * p.scale : 0.f;
+            csum.y += h.y > 0.f ? x.y * p.scale : 0.f;
+            csum.z += h.z > 0.f ? x.z * p.scale : 0.f;
+            csum.w += h.w > 0.f ? x.w * p.scale : 0.f;
           }
+        }
+        if ((MODE == EPI_MASK || MODE == EPI_EXPAND) && p.colpart) {
+          // Bias gradient of the layer below = column sums of what was just written.  Fixed-order reduction:
+          // 8 rows in registers, 4 row groups by shuffle, 4 warps through shared memory -> one partial row per
+          // tile, summed over tiles by the split-K reduce kernel.  No atomics, no zeroing, and the 19 MB
+          // gradient tensor is not read again by a separate column-sum kernel.
+          csum.x += __shfl_xor_sync(0xffffffffu, csum.x, 8);  csum.y += __shfl_xor_sync(0xffffffffu, csum.y, 8);
+          csum.z += __shfl_xor_sync(0xffffffffu, csum.z, 8);  csum.w += __shfl_xor_sync(0xffffffffu, csum.w, 8);
+          csum.x += __shfl_xor_sync(0xffffffffu, csum.x, 16); csum.y += __shfl_xor_sync(0xffffffffu, csum.y, 16);
+          csum.z += __shfl_xor_sync(0xffffffffu, csum.z, 16); csum.w += __shfl_xor_sync(0xffffffffu, csum.w, 16);
+          float* cs = colsum_s + ((c0 >> 5) & 1) * 128;      // double-buffered by iteration parity
+          if (sub == 0) *reinterpret_cast<float4*>(cs + quad * 32 + 4 * ch) = csum;
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (quad == 0)
+            p.colpart[(size_t)tile * p.N + n_tile0 + c0 + lane] = (cs[lane] + cs[32 + lane]) + (cs[64 + lane] + cs[96 + lane]);
         }
         if (dbg && threadIdx.x == 64 && c0 == 0) dbg[13] = clock64();   // first iteration's stores issued
         __syncwarp();
@@ -516,7 +541,7 @@ int mpit_tmap_encode_f32(void* out128, const void* gptr, int rank, const unsigne
 int mpit_umma_igemm(const void* tmap_a128, const void* tmap_b128, const int* geom17, float scale,
                     const float* bias, float* out, unsigned char* idx, const float* aux,
                     const unsigned char* aux_idx, const int* crop, const unsigned long long* rng, int* err,
-                    int block_n, void* stream) {
+                    float* colpart, int block_n, void* stream) {
   IgemmParams p{};
   {
     // MPIT_IGEMM_DBG=<device address of a long long[16 * ctas] buffer>: per-CTA timeline for tuning
@@ -531,7 +556,7 @@ int mpit_umma_igemm(const void* tmap_a128, const void* tmap_b128, const int* geo
   p.num_kb = geom17[8]; p.sgn = geom17[9]; p.B = geom17[10]; p.OH = geom17[11]; p.OW = geom17[12];
   p.N = geom17[13]; p.mode = geom17[14]; p.relu = geom17[15]; p.dropout = geom17[16];
   p.scale = scale; p.bias = bias; p.out = out; p.idx = idx; p.aux = aux; p.aux_idx = aux_idx;
-  p.crop = crop; p.rng = rng; p.err = err;
+  p.crop = crop; p.rng = rng; p.err = err; p.colpart = colpart;
   if (p.nsub < 1 || p.nsub > 2 || p.nsub * p.tw * p.th * p.tn != 128 || p.num_kb < 1 || p.N % block_n != 0)
     return MPIT_E_ARG;
   if (p.mode == EPI_POOL && (p.tw > 16 || (p.tw & 1) || (p.th & 1))) return MPIT_E_ARG;

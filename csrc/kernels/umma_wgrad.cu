@@ -224,32 +224,49 @@ wgrad_reduce_kernel(const float* __restrict__ part, float* __restrict__ gw, int 
   }
 }
 
-// Sum the split-K partials of up to 8 layers in one launch: one thread per output element,
-// consecutive threads along n (coalesced reads of part[s][m][n]), splits unrolled for ILP.
-struct ReduceSeg { const float* part; float* gw; int nsplit, m_pad, K, N, ldw, first_block; };
-struct ReduceArgs { ReduceSeg seg[8]; int nseg; };
+// Sum the split-K partials of up to 16 segments (layers' weight gradients, and bias-gradient partial rows
+// written by the data-gradient epilogues) in one launch.  An output element is owned by SL = 1..8 threads
+// ("split lanes", chosen per segment from its split count) that each add every SL-th partial with four loads
+// in flight, then combine through shared memory in a fixed order -- a single thread walking 64-144 partials
+// with dependent L2 latencies made this kernel 10 us.  Consecutive threads run along n (coalesced reads of
+// part[s][m][n]).
+struct ReduceSeg { const float* part; float* gw; int nsplit, m_pad, K, N, ldw, first_block, sl; };
+struct ReduceArgs { ReduceSeg seg[16]; int nseg; };
 
 __global__ void __launch_bounds__(256) multi_wgrad_reduce_kernel(ReduceArgs a) {
+  __shared__ float red[256];
   pdl_trigger();
   pdl_wait();
   int s = 0;
   while (s + 1 < a.nseg && (int)blockIdx.x >= a.seg[s + 1].first_block) ++s;
   const ReduceSeg sg = a.seg[s];
-  long long e = (long long)(blockIdx.x - sg.first_block) * 256 + threadIdx.x;
-  if (e >= (long long)sg.K * sg.N) return;
-  int m = (int)(e / sg.N), n = (int)(e % sg.N);
-  const float* p = sg.part + (size_t)m * sg.N + n;
-  const size_t stride = (size_t)sg.m_pad * sg.N;
+  const int opb = 256 / sg.sl;                         // outputs per block
+  const int o = threadIdx.x % opb, sl = threadIdx.x / opb;
+  const long long e = (long long)(blockIdx.x - sg.first_block) * opb + o;
+  const bool live = e < (long long)sg.K * sg.N;
   float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
-  int sp = 0;
-  for (; sp + 4 <= sg.nsplit; sp += 4) {
-    acc0 += p[(size_t)sp * stride];
-    acc1 += p[(size_t)(sp + 1) * stride];
-    acc2 += p[(size_t)(sp + 2) * stride];
-    acc3 += p[(size_t)(sp + 3) * stride];
+  int m = 0, n = 0;
+  if (live) {
+    m = (int)(e / sg.N); n = (int)(e % sg.N);
+    const float* p = sg.part + (size_t)m * sg.N + n;
+    const size_t stride = (size_t)sg.m_pad * sg.N;
+    int sp = sl;
+    for (; sp + 3 * sg.sl < sg.nsplit; sp += 4 * sg.sl) {
+      acc0 += p[(size_t)sp * stride];
+      acc1 += p[(size_t)(sp + sg.sl) * stride];
+      acc2 += p[(size_t)(sp + 2 * sg.sl) * stride];
+      acc3 += p[(size_t)(sp + 3 * sg.sl) * stride];
+    }
+    for (; sp < sg.nsplit; sp += sg.sl) acc0 += p[(size_t)sp * stride];
   }
-  for (; sp < sg.nsplit; ++sp) acc0 += p[(size_t)sp * stride];
-  sg.gw[(size_t)n * sg.ldw + m] = (acc0 + acc1) + (acc2 + acc3);
+  float t = (acc0 + acc1) + (acc2 + acc3);
+  if (sg.sl > 1) {
+    red[threadIdx.x] = t;
+    __syncthreads();
+    if (sl == 0)
+      for (int k = 1; k < sg.sl; ++k) t += red[k * opb + o];
+  }
+  if (live && sl == 0) sg.gw[(size_t)n * sg.ldw + m] = t;
 }
 
 // Column sums of up to 8 [rows][C] matrices in one launch (bias gradients of every layer).
@@ -370,10 +387,12 @@ int mpit_multi_colsum(int nseg, const unsigned long long* srcs, const unsigned l
   return 0;
 }
 
-// Split-K reduction of up to 8 layers in one launch; every array is a HOST array of nseg entries.
+// Split-K reduction of up to 16 segments in one launch; every array is a HOST array of nseg entries.
+// Segment i: gw_i[n*K_i + m] = sum_{s < nsplit_i} part_i[(s*m_pad_i + m)*N_i + n], m < K_i, n < N_i.
+// (A bias gradient summed from T tile rows of width G*C is the segment {nsplit=T*G, m_pad=1, K=1, N=C}.)
 int mpit_multi_wgrad_reduce(int nseg, const unsigned long long* parts, const unsigned long long* gws,
                             const int* nsplit, const int* m_pad, const int* K, const int* N, void* stream) {
-  if (nseg < 1 || nseg > 8) return MPIT_E_ARG;
+  if (nseg < 1 || nseg > 16) return MPIT_E_ARG;
   ReduceArgs a{};
   a.nseg = nseg;
   int blocks = 0;
@@ -383,7 +402,11 @@ int mpit_multi_wgrad_reduce(int nseg, const unsigned long long* parts, const uns
     a.seg[i].nsplit = nsplit[i]; a.seg[i].m_pad = m_pad[i]; a.seg[i].K = K[i]; a.seg[i].N = N[i];
     a.seg[i].ldw = K[i];
     a.seg[i].first_block = blocks;
-    blocks += (int)(((long long)K[i] * N[i] + 255) / 256);
+    int sl = 1;
+    while (sl < 8 && sl * 4 < nsplit[i]) sl *= 2;      // ~4+ partials per split lane
+    a.seg[i].sl = sl;
+    const long long opb = 256 / sl;
+    blocks += (int)(((long long)K[i] * N[i] + opb - 1) / opb);
   }
   MPIT_CUDA_TRY(launch_k(multi_wgrad_reduce_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, a));
   return 0;

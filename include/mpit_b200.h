@@ -79,10 +79,12 @@ int mpit_act_bwd(const float* dout, const float* out, const unsigned char* pool_
                  int OW, int C, int pool, float scale, void* stream);
 int mpit_colsum(const float* dz, float* db, long long rows, int C, void* stream);
 int mpit_prep_u8(const unsigned char* src, float* dst, int B, int SH, int SW, int cin, void* stream);
-/* loss_sum = (accumulate ? loss_sum : 0) + sum of per-sample NLL; dlogits (may be NULL) = gscale * dNLL. */
+/* loss_sum = (accumulate ? loss_sum : 0) + sum of per-sample NLL; dlogits (may be NULL) = gscale * dNLL.
+ * dbias (optional, needs dlogits and B <= 4096): dbias[c] = sum over samples of dlogits[.][c], c < ld --
+ * the bias gradient of the classifier layer, in a fixed summation order. */
 int mpit_nll_fwd_bwd(const float* logits, const int* labels, float* dlogits, float* loss_sum, int* confusion,
                      int B, int ncls, int ld, float gscale, unsigned long long* rng_inc, int accumulate,
-                     void* stream);
+                     float* dbias, void* stream);
 
 /* ---- NVLink exchange kernels (csrc/kernels/comm.cu) -------------------------------------- */
 /* `shard_ptrs` is a HOST array of nranks device addresses: entry s is rank s's shard of the
@@ -160,11 +162,14 @@ int mpit_tmap_encode_f32(void* out128, const void* gptr, int rank, const unsigne
 /* Implicit-GEMM conv / linear, forward (sgn=+1) or data gradient (sgn=-1) with fused epilogue:
  * mode 0 bias(+ReLU)(+dropout) store, 1 bias+2x2 maxpool(+ReLU)+argmax, 2 ReLU-mask of a gradient,
  * 3 un-pool + ReLU-mask of a gradient (7-layers-cnn.lua:8-24 forward/backward).
- * geom17 (HOST) = {nsub,tw,th,tn,tiles_w,tiles_h,kw_it,cb,num_kb,sgn,B,OH,OW,N,mode,relu,dropout}. */
+ * geom17 (HOST) = {nsub,tw,th,tn,tiles_w,tiles_h,kw_it,cb,num_kb,sgn,B,OH,OW,N,mode,relu,dropout}.
+ * colpart (optional, modes 2 and 3): [m_tiles][N] floats, row t = column sums of the values tile t wrote
+ * (m_tiles = ceil(ceil(B/tn)*tiles_w*tiles_h / nsub)); summing the rows gives the bias gradient of the
+ * layer whose pre-activation gradient this call produces. */
 int mpit_umma_igemm(const void* tmap_a128, const void* tmap_b128, const int* geom17, float scale,
                     const float* bias, float* out, unsigned char* idx, const float* aux,
                     const unsigned char* aux_idx, const int* crop, const unsigned long long* rng, int* err,
-                    int block_n, void* stream);
+                    float* colpart, int block_n, void* stream);
 /* Parameter pull fused with the GEMM that consumes the weights (/root/reference/asyncsgd/pclient.lua:74-84
  * followed by the model's first Linear): the weight rows stay in the NVLink-sharded centre and the
  * kernel's TMA loads read each tile from its owner's shard. tmaps_b: HOST array of nranks x 128 bytes. */

@@ -341,9 +341,12 @@ class CifarEngine:
 
     def loss_and_grad(self, train: bool = True) -> None:
         L5 = self.layers[-1]
+        # with the tensor-core plan the classifier's bias gradient is produced here (the other layers' come from
+        # the data-gradient epilogues); the reference path column-sums every dz in backward()
+        fused_bias = train and self._umma is not None and self._umma.wgrad is not None
         self.ops.nll_fwd_bwd(self.act[-1], self.labels, self.dz[-1] if train else None, self.loss_sum,
                              self.B, self.ncls, L5.CO, gscale=1.0 / self.B, confusion=self.confusion,
-                             rng_inc=self.rng if train else None)
+                             rng_inc=self.rng if train else None, dbias=self.gb(len(self.layers) - 1) if fused_bias else None)
 
     def backward(self) -> None:
         ops, B = self.ops, self.B

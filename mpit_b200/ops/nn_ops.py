@@ -69,8 +69,9 @@ def prep_u8(src, dst, B, SH, SW, cin=3):
 
 
 def nll_fwd_bwd(logits, labels, dlogits, loss_sum, B, ncls, ld, *, gscale, confusion=None, rng_inc=None,
-                accumulate=False):
-    """``loss_sum`` is overwritten with the batch's summed NLL (added to when ``accumulate``)."""
+                accumulate=False, dbias=None):
+    """``loss_sum`` is overwritten with the batch's summed NLL (added to when ``accumulate``); ``dbias``
+    (optional) receives the column sums of ``dlogits``: the classifier's bias gradient."""
     check(kernels().mpit_nll_fwd_bwd(ptr(logits), ptr(labels), ptr(dlogits), ptr(loss_sum), ptr(confusion),
-                                     B, ncls, ld, gscale, ptr(rng_inc), int(accumulate), cur_stream()),
+                                     B, ncls, ld, gscale, ptr(rng_inc), int(accumulate), ptr(dbias), cur_stream()),
           "mpit_nll_fwd_bwd")

@@ -43,6 +43,7 @@ class IgemmLaunch:
     rng: Optional[torch.Tensor]
     block_n: int
     dropout_slot: int = 16
+    colpart: Optional[torch.Tensor] = None    # [m_tiles][N] per-tile column sums (modes MASK / EXPAND)
 
     def run(self, err: torch.Tensor, dropout: Optional[bool] = None):
         g = self.geom
@@ -51,7 +52,8 @@ class IgemmLaunch:
             g[16] = int(dropout)
         check(kernels().mpit_umma_igemm(self.tmap_a, self.tmap_b, g, self.scale, ptr(self.bias), ptr(self.out),
                                         ptr(self.idx), ptr(self.aux), ptr(self.aux_idx), ptr(self.crop),
-                                        ptr(self.rng), ptr(err), self.block_n, cur_stream()), "mpit_umma_igemm")
+                                        ptr(self.rng), ptr(err), ptr(self.colpart), self.block_n, cur_stream()),
+              "mpit_umma_igemm")
 
 
 def igemm_geom(*, nsub, tw, th, tn, tiles_w, tiles_h, kw_it, cb, num_kb, sgn, B, OH, OW, N, mode, relu=0,
@@ -166,11 +168,23 @@ class CifarUmmaPlan:
                        sgn=-1, B=B, OH=12, OW=12, N=c1, mode=EPI_EXPAND),
             1.0, None, dz[0], None, act[0], idx[0], None, None, bn)
 
+        # Bias gradients ride on the data-gradient epilogues: dgrad[i] writes dz[i-1], and its per-tile column
+        # sums (summed over tiles by the split-K reduce launch) are the bias gradient of layer i-1.  The
+        # classifier's bias gradient comes from the loss kernel.  (tiles, columns seen by the kernel, channels)
+        self.bias_parts = {}
+        for i in (4, 3, 2, 1):
+            g = self.dgrad[i].geom            # {nsub,tw,th,tn,tiles_w,tiles_h,...,B at [10],...,N at [13]}
+            tiles = -(-(-(-g[10] // g[3]) * g[4] * g[5]) // g[0])
+            ncols = g[13]
+            cp = torch.zeros(tiles * ncols, dtype=torch.float32, device=eng.dev)
+            self.dgrad[i].colpart = cp
+            self.bias_parts[i - 1] = (cp, tiles, ncols, eng.layers[i - 1].CO)
+
         self.wgrad = None
         if wgrad != "ref":
             try:
                 from .umma_wgrad_ops import CifarWgradPlan
-                self.wgrad = CifarWgradPlan(eng, self.err)
+                self.wgrad = CifarWgradPlan(eng, self.err, self.bias_parts)
             except ImportError:
                 if wgrad == "umma":
                     raise

@@ -33,7 +33,7 @@ class WgradLaunch:
 
 
 class CifarWgradPlan:
-    def __init__(self, eng, err: torch.Tensor):
+    def __init__(self, eng, err: torch.Tensor, bias_parts=None):
         self.eng, self.err = eng, err
         B = eng.B
         act, dz = eng.act, eng.dz
@@ -65,13 +65,23 @@ class CifarWgradPlan:
             off += ns * m_pad * N
         # split-K scratch workspace shared by all layers
         self.part = torch.empty(off, dtype=torch.float32, device=eng.dev)
-        n = len(self.launches)
         ls = self.launches
-        self._red = ((ctypes.c_ulonglong * n)(*[self.part.data_ptr() + 4 * l.part_off for l in ls]),
-                     (ctypes.c_ulonglong * n)(*[l.gw.data_ptr() for l in ls]),
-                     (ctypes.c_int * n)(*[l.nsplit for l in ls]), (ctypes.c_int * n)(*[l.m_pad for l in ls]),
-                     (ctypes.c_int * n)(*[l.K for l in ls]), (ctypes.c_int * n)(*[l.N for l in ls]))
+        # segments of the one reduce launch: split-K partials of every layer's weight gradient ...
+        segs = [(self.part.data_ptr() + 4 * l.part_off, l.gw.data_ptr(), l.nsplit, l.m_pad, l.K, l.N) for l in ls]
+        # ... and the bias-gradient partial rows written by the data-gradient epilogues: T tile rows of
+        # G*C columns -> {nsplit = T*G, m_pad = 1, K = 1, N = C}
+        self.bias_from_epilogue = bias_parts is not None
+        if bias_parts:
+            for li, (cp, tiles, ncols, C) in sorted(bias_parts.items()):
+                assert ncols % C == 0
+                segs.append((cp.data_ptr(), eng.gb(li).data_ptr(), tiles * (ncols // C), 1, 1, C))
+        n = len(segs)
+        self._nred = n
+        self._red = ((ctypes.c_ulonglong * n)(*[g[0] for g in segs]), (ctypes.c_ulonglong * n)(*[g[1] for g in segs]),
+                     (ctypes.c_int * n)(*[g[2] for g in segs]), (ctypes.c_int * n)(*[g[3] for g in segs]),
+                     (ctypes.c_int * n)(*[g[4] for g in segs]), (ctypes.c_int * n)(*[g[5] for g in segs]))
         L = eng.layers
+        n = len(ls)
         self._cs = ((ctypes.c_ulonglong * n)(*[dz[i].data_ptr() for i in range(n)]),
                     (ctypes.c_ulonglong * n)(*[eng.gb(i).data_ptr() for i in range(n)]),
                     (ctypes.c_longlong * n)(*[B * L[i].out_hw * L[i].out_hw for i in range(n)]),
@@ -86,9 +96,10 @@ class CifarWgradPlan:
         if i == 0:
             # last layer of the backward sweep: every partial and every dz is final -> one launch sums
             # the split-K partials of all layers, one more sums every bias gradient
-            n = len(self.launches)
             r = self._red
-            check(k.mpit_multi_wgrad_reduce(n, r[0], r[1], r[2], r[3], r[4], r[5], cur_stream()),
+            check(k.mpit_multi_wgrad_reduce(self._nred, r[0], r[1], r[2], r[3], r[4], r[5], cur_stream()),
                   "mpit_multi_wgrad_reduce")
-            check(k.mpit_multi_colsum(n, self._cs[0], self._cs[1], self._cs[2], self._cs[3], cur_stream()),
-                  "mpit_multi_colsum")
+            if not self.bias_from_epilogue:
+                n = len(self.launches)
+                check(k.mpit_multi_colsum(n, self._cs[0], self._cs[1], self._cs[2], self._cs[3], cur_stream()),
+                      "mpit_multi_colsum")

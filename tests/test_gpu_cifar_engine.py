@@ -163,6 +163,8 @@ def test_engine_umma_wgrad_matches_ref_layerwise(B):
     for i in range(5):
         um.act[i].copy_(ref.act[i])
         um.dz[i].copy_(ref.dz[i])
+        if ref.idx[i] is not None:
+            um.idx[i].copy_(ref.idx[i])
     um.gpk.fill_(7.0)
     for i in range(4, -1, -1):
         um._umma.wgrad.run(i)
@@ -173,7 +175,16 @@ def test_engine_umma_wgrad_matches_ref_layerwise(B):
         gw_u = um.gw(i).view(L.CO, L.k, L.KWP, L.C)[:, :, :L.k]
         gw_r = ref.gw(i).view(L.CO, L.k, L.KWP, L.C)[:, :, :L.k]
         assert _rel_l2(gw_u, gw_r) < 3e-3, (i, _rel_l2(gw_u, gw_r))
-        assert _rel_l2(um.gb(i), ref.gb(i)) < 1e-4, (i, "bias")
+    # Bias gradients are by-products of the loss kernel (classifier) and of the data-gradient epilogues
+    # (per-tile column sums, summed by the split-K reduce launch): run the whole backward sweep on the same
+    # activations.  dz below the classifier is then the TF32 data gradient, hence the TF32-level tolerance.
+    um.gpk.fill_(7.0)
+    um.loss_and_grad(True)
+    um._umma.backward()
+    torch.cuda.synchronize()
+    um._umma.check()
+    for i in range(5):
+        assert _rel_l2(um.gb(i), ref.gb(i)) < 3e-3, (i, "bias", _rel_l2(um.gb(i), ref.gb(i)))
 
 
 def test_mnist_cnn_engine_matches_torch_cpu():
