@@ -41,11 +41,16 @@ struct QuadWalk {
     return w;
   }
   __device__ __forceinline__ void at(long long v, int& s, long long& j0, long long& i0, int& cnt) const {
-    long long c = v / kChunkQuads, within = v - c * kChunkQuads;
-    int lane_shard = (int)(c % part.S);
-    long long k = c / part.S;
-    s = (lane_shard + rank + 1) % part.S;
-    j0 = (k * kChunkQuads + within) * 4;
+    // chunk index fits 32 bits for any n < 2^40; 64-bit division by a run-time value is ~200 instructions,
+    // which on the 350k-parameter step boundary cost more than the memory traffic
+    const long long c = v / kChunkQuads, within = v - c * kChunkQuads;
+    const unsigned c32 = (unsigned)c, S32 = (unsigned)part.S;
+    const unsigned k = S32 == 1 ? c32 : c32 / S32;
+    const int lane_shard = (int)(c32 - k * S32);
+    s = lane_shard + rank + 1;
+    if (s >= part.S) s -= part.S;
+    if (s >= part.S) s -= part.S;
+    j0 = ((long long)k * kChunkQuads + within) * 4;
     i0 = part.begin(s) + j0;
     long long rem = part.size(s) - j0;
     cnt = rem >= 4 ? 4 : (rem > 0 ? (int)rem : 0);
@@ -398,7 +403,7 @@ static SignalTable make_sig(const unsigned long long* ptrs, int nranks, int rank
   return t;
 }
 
-static int exch_grid(const QuadWalk& w) { return ew_grid(w.total, 256, 2, 8); }
+static int exch_grid(const QuadWalk& w) { return ew_grid(w.total, 256, 1, 8); }
 
 }  // namespace mpit
 

@@ -162,36 +162,23 @@ umma_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
       if (!mbar_wait(tmem_full, 0)) { if (p.err) *p.err = 13; }
     }
     tc_fence_after();
-    // TMEM gives each lane one row (128 B per 32 columns); storing that way touches 32 lines per warp
-    // instruction.  Transpose each 32x32 block through a swizzled warp-private tile in the (now idle)
-    // pipeline memory so that 8 adjacent lanes write one full 128-byte line.
-    const uint32_t tile = smem_u32(smem) + quad * 4096;
-    const int sub = lane >> 3, ch = lane & 7;
+    // The partial tile is stored n-major, part[split][n][m]: a TMEM lane is one m row, so for each of its
+    // 32 columns the warp's 32 lanes write 32 consecutive m -- one full 128-byte line per store, with no
+    // transposition -- and the reduce kernel reads AND writes (gw[n][m]) along m, coalesced on both sides.
     // rows of chunks this tile does not own hold garbage: write zeros there (one chunk = one warp's 32 rows)
     const bool rows_ok = nkb > 0 && quad < nchunks;
-    float* dst = p.part + ((size_t)split * p.m_pad + m_tile * 128 + quad * 32) * p.N + n_tile0 + 4 * ch;
+    float* dst = p.part + ((size_t)split * p.N + n_tile0) * p.m_pad + m_tile * 128 + quad * 32 + lane;
 #pragma unroll 1
     for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
-      float4 xs[8];
+      float v[32];
       if (rows_ok) {
-        float v[32];
         tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
-#pragma unroll
-        for (int c4 = 0; c4 < 8; ++c4)
-          sts4(tile + (lane * 8 + (c4 ^ (lane & 7))) * 16, v[4 * c4], v[4 * c4 + 1], v[4 * c4 + 2], v[4 * c4 + 3]);
-        __syncwarp();
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int r = i * 4 + sub;
-          xs[i] = lds4(tile + (r * 8 + (ch ^ (r & 7))) * 16);
-        }
-        __syncwarp();
       } else {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) xs[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int c = 0; c < 32; ++c) v[c] = 0.f;
       }
 #pragma unroll
-      for (int i = 0; i < 8; ++i) st4(dst + (size_t)(i * 4 + sub) * p.N + c0, xs[i]);
+      for (int c = 0; c < 32; ++c) dst[(size_t)(c0 + c) * p.m_pad] = v[c];
     }
     tc_fence_before();
   }
@@ -202,35 +189,34 @@ umma_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
   }
 }
 
-// dW[n][m] (packed forward layout, K = ldw) = sum_s part[s][m][n]
+// dW[n][m] (packed forward layout, row pitch ldw) = sum_s part[s][n][m]; threads run along m.
 __global__ void __launch_bounds__(256)
 wgrad_reduce_kernel(const float* __restrict__ part, float* __restrict__ gw, int nsplit, int m_pad, int K, int N,
                     int ldw) {
-  // tile 32(m) x 32(n) through shared memory so that both sides are coalesced
-  __shared__ float t[32][33];
-  int m0 = blockIdx.x * 32, n0 = blockIdx.y * 32;
-  int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 8 rows per pass
-  for (int r = ty; r < 32; r += 8) {
-    int m = m0 + r, n = n0 + tx;
-    float acc = 0.f;
-    if (m < K && n < N)
-      for (int s = 0; s < nsplit; ++s) acc += part[((size_t)s * m_pad + m) * N + n];
-    t[r][tx] = acc;
+  const unsigned e = blockIdx.x * 256u + threadIdx.x;
+  if (e >= (unsigned)K * (unsigned)N) return;
+  const unsigned n = e / (unsigned)K, m = e - n * (unsigned)K;
+  const float* p = part + (size_t)n * m_pad + m;
+  const size_t stride = (size_t)N * m_pad;
+  float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
+  int s = 0;
+  for (; s + 4 <= nsplit; s += 4) {
+    acc0 += p[(size_t)s * stride];
+    acc1 += p[(size_t)(s + 1) * stride];
+    acc2 += p[(size_t)(s + 2) * stride];
+    acc3 += p[(size_t)(s + 3) * stride];
   }
-  __syncthreads();
-  for (int r = ty; r < 32; r += 8) {
-    int n = n0 + r, m = m0 + tx;
-    if (m < K && n < N) gw[(size_t)n * ldw + m] = t[tx][r];
-  }
+  for (; s < nsplit; ++s) acc0 += p[(size_t)s * stride];
+  gw[(size_t)n * ldw + m] = (acc0 + acc1) + (acc2 + acc3);
 }
 
 // Sum the split-K partials of up to 16 segments (layers' weight gradients, and bias-gradient partial rows
 // written by the data-gradient epilogues) in one launch.  An output element is owned by SL = 1..8 threads
 // ("split lanes", chosen per segment from its split count) that each add every SL-th partial with four loads
 // in flight, then combine through shared memory in a fixed order -- a single thread walking 64-144 partials
-// with dependent L2 latencies made this kernel 10 us.  Consecutive threads run along n (coalesced reads of
-// part[s][m][n]).
-struct ReduceSeg { const float* part; float* gw; int nsplit, m_pad, K, N, ldw, first_block, sl; };
+// with dependent L2 latencies made this kernel 10 us.  Partials are n-major (part[s][n][m]) and consecutive
+// threads run along m, so reads and the gw[n][m] writes are both coalesced.
+struct ReduceSeg { const float* part; float* gw; int nsplit, m_pad, K, N, first_block, sl; };
 struct ReduceArgs { ReduceSeg seg[16]; int nseg; };
 
 __global__ void __launch_bounds__(256) multi_wgrad_reduce_kernel(ReduceArgs a) {
@@ -240,16 +226,18 @@ __global__ void __launch_bounds__(256) multi_wgrad_reduce_kernel(ReduceArgs a) {
   int s = 0;
   while (s + 1 < a.nseg && (int)blockIdx.x >= a.seg[s + 1].first_block) ++s;
   const ReduceSeg sg = a.seg[s];
-  const int opb = 256 / sg.sl;                         // outputs per block
-  const int o = threadIdx.x % opb, sl = threadIdx.x / opb;
-  const long long e = (long long)(blockIdx.x - sg.first_block) * opb + o;
-  const bool live = e < (long long)sg.K * sg.N;
+  // sl is a power of two, so outputs-per-block is a shift; all index math in 32 bits (a 64-bit division per
+  // thread cost more than the loads: host checks K*N < 2^31)
+  const int opb_shift = 8 - (31 - __clz(sg.sl));
+  const int opb = 1 << opb_shift;                      // outputs per block
+  const int o = threadIdx.x & (opb - 1), sl = threadIdx.x >> opb_shift;
+  const unsigned e = (unsigned)(blockIdx.x - sg.first_block) * (unsigned)opb + (unsigned)o;
+  const bool live = e < (unsigned)sg.K * (unsigned)sg.N;
   float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
-  int m = 0, n = 0;
   if (live) {
-    m = (int)(e / sg.N); n = (int)(e % sg.N);
-    const float* p = sg.part + (size_t)m * sg.N + n;
-    const size_t stride = (size_t)sg.m_pad * sg.N;
+    const unsigned n = e / (unsigned)sg.K, m = e - n * (unsigned)sg.K;     // m fastest: e is also the gw index
+    const float* p = sg.part + (size_t)n * sg.m_pad + m;
+    const size_t stride = (size_t)sg.N * sg.m_pad;
     int sp = sl;
     for (; sp + 3 * sg.sl < sg.nsplit; sp += 4 * sg.sl) {
       acc0 += p[(size_t)sp * stride];
@@ -266,7 +254,7 @@ __global__ void __launch_bounds__(256) multi_wgrad_reduce_kernel(ReduceArgs a) {
     if (sl == 0)
       for (int k = 1; k < sg.sl; ++k) t += red[k * opb + o];
   }
-  if (live && sl == 0) sg.gw[(size_t)n * sg.ldw + m] = t;
+  if (live && sl == 0) sg.gw[e] = t;
 }
 
 // Column sums of up to 8 [rows][C] matrices in one launch (bias gradients of every layer).
@@ -350,10 +338,13 @@ int mpit_umma_wgrad(const void* tmap_x128, const void* tmap_dz128, const int* ge
   }
 }
 
-// gw[n*ldw + m] = sum_s part[s][m][n] for m < K, n < N.
+// gw[n*ldw + m] = sum_s part[s][n][m] for m < K, n < N.
 int mpit_wgrad_reduce(const float* part, float* gw, int nsplit, int m_pad, int K, int N, int ldw, void* stream) {
-  dim3 grid((K + 31) / 32, (N + 31) / 32);
-  wgrad_reduce_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(part, gw, nsplit, m_pad, K, N, ldw);
+  const long long total = (long long)K * N;
+  if (total <= 0) return 0;
+  if (total >= (1ll << 31)) return MPIT_E_ARG;
+  wgrad_reduce_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(part, gw, nsplit, m_pad, K, N,
+                                                                                         ldw);
   MPIT_LAUNCH_CHECK();
   return 0;
 }
@@ -388,7 +379,7 @@ int mpit_multi_colsum(int nseg, const unsigned long long* srcs, const unsigned l
 }
 
 // Split-K reduction of up to 16 segments in one launch; every array is a HOST array of nseg entries.
-// Segment i: gw_i[n*K_i + m] = sum_{s < nsplit_i} part_i[(s*m_pad_i + m)*N_i + n], m < K_i, n < N_i.
+// Segment i: gw_i[n*K_i + m] = sum_{s < nsplit_i} part_i[(s*N_i + n)*m_pad_i + m], m < K_i, n < N_i.
 // (A bias gradient summed from T tile rows of width G*C is the segment {nsplit=T*G, m_pad=1, K=1, N=C}.)
 int mpit_multi_wgrad_reduce(int nseg, const unsigned long long* parts, const unsigned long long* gws,
                             const int* nsplit, const int* m_pad, const int* K, const int* N, void* stream) {
@@ -400,7 +391,7 @@ int mpit_multi_wgrad_reduce(int nseg, const unsigned long long* parts, const uns
     a.seg[i].part = reinterpret_cast<const float*>(parts[i]);
     a.seg[i].gw = reinterpret_cast<float*>(gws[i]);
     a.seg[i].nsplit = nsplit[i]; a.seg[i].m_pad = m_pad[i]; a.seg[i].K = K[i]; a.seg[i].N = N[i];
-    a.seg[i].ldw = K[i];
+    if ((long long)K[i] * N[i] >= (1ll << 31)) return MPIT_E_ARG;
     a.seg[i].first_block = blocks;
     int sl = 1;
     while (sl < 8 && sl * 4 < nsplit[i]) sl *= 2;      // ~4+ partials per split lane

@@ -178,8 +178,9 @@ int mpit_umma_linear_pull(const void* tmap_a128, const void* tmaps_b, int nranks
 
 /* ---- tcgen05 weight gradients (csrc/kernels/umma_wgrad.cu) ------------------------------------- */
 /* dW = Xcol^T dZ over all output pixels, pixel dimension split over `nsplit` CTAs that each write a
- * partial tile into the scratch workspace `part` (nsplit * m_pad * N floats, m_pad =
- * ceil(total_chunks/4)*128); mpit_wgrad_reduce sums the splits into the packed gradient
+ * partial tile into the scratch workspace `part` (nsplit * N * m_pad floats, laid out
+ * part[split][n][m] with m_pad = ceil(total_chunks/4)*128 the pitch of one n row); mpit_wgrad_reduce sums
+ * the splits into the packed gradient gw[n*ldw + m]
  * (accGradParameters of SpatialConvolution/Linear, asyncsgd/goot.lua:206).
  * geom11 (HOST) = {tw,th,tn,tiles_w,tiles_h,kw_it,cb,total_chunks,num_kb,B,N}. */
 int mpit_umma_wgrad(const void* tmap_x128, const void* tmap_dz128, const int* geom11, float* part,
@@ -204,8 +205,10 @@ int mpit_wgrad_reduce(const float* part, float* gw, int nsplit, int m_pad, int K
 #define MPIT_NOALLOC_SCRATCH_FLOATS (2u * 1024u * 1024u)
 int mpit_umma_wgrad_noalloc(const void* tmap_x128, const void* tmap_dz128, const int* geom11, float* gw, int ldw,
                             const int* crop, int* err, int block_n, int nsplit, void* stream);
-/* mpit_multi_wgrad_reduce: the split-K reduction of up to 8 layers in ONE launch (HOST arrays of
- * nseg entries).  mpit_multi_colsum: bias gradients (column sums) of up to 8 [rows][C] matrices in
+/* mpit_multi_wgrad_reduce: the split-K reduction of up to 16 segments in ONE launch (HOST arrays of
+ * nseg entries): gw_i[n*K_i + m] = sum_s part_i[(s*N_i + n)*m_pad_i + m].  The bias-gradient partial rows
+ * written by mpit_umma_igemm (colpart, T tiles x G*C columns) are the segment {nsplit=T*G, m_pad=1, K=1,
+ * N=C}.  mpit_multi_colsum: bias gradients (column sums) of up to 8 [rows][C] matrices in
  * one launch; srcs/dsts/rows/cols are HOST arrays; C % 4 == 0 and 256 % (C/4) == 0. */
 int mpit_multi_wgrad_reduce(int nseg, const unsigned long long* parts, const unsigned long long* gws,
                             const int* nsplit, const int* m_pad, const int* K, const int* N, void* stream);
