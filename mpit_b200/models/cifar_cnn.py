@@ -326,9 +326,27 @@ class CifarEngine:
         return self.gpk[L.b_off:L.b_off + L.CO]
 
     # -- schedules -----------------------------------------------------------------------------
+    def begin_step(self) -> None:
+        """Optional hook for the optimizers: called right before their step-boundary kernel, it starts the input
+        conversion on the side stream so that it runs beside that kernel (neither needs the other)."""
+        um = self._umma
+        if um is None or not um.two_streams or not um.fork_prep:
+            return
+        main = torch.cuda.current_stream()
+        um._ev_in[0].record(main)
+        um._side.wait_event(um._ev_in[0])
+        with torch.cuda.stream(um._side):
+            self.ops.prep_u8(self.x_u8, self.x0, self.B, IMG, IMG, self.cin)
+            um._ev_in[1].record(um._side)
+        self._prep_forked = True
+
     def forward(self, train: bool = True) -> None:
         ops, B = self.ops, self.B
-        ops.prep_u8(self.x_u8, self.x0, B, IMG, IMG, self.cin)
+        if getattr(self, "_prep_forked", False):
+            torch.cuda.current_stream().wait_event(self._umma._ev_in[1])
+            self._prep_forked = False
+        else:
+            ops.prep_u8(self.x_u8, self.x0, B, IMG, IMG, self.cin)
         if self._umma is not None:
             self._umma.forward(train)
         else:

@@ -180,6 +180,16 @@ class CifarUmmaPlan:
             self.dgrad[i].colpart = cp
             self.bias_parts[i - 1] = (cp, tiles, ncols, eng.layers[i - 1].CO)
 
+        import os
+        self.two_streams = os.environ.get("MPIT_BWD_STREAMS", "2") != "1"
+        # Two more forks exist but are off by default: every fork/join turns a programmatic (PDL) edge into a
+        # full one, and on B200 the two effects cancel (measured, tools/dev/pdl_ab.py, ms/step at batch 128:
+        # PDL on + neither fork 0.1619; PDL on + both 0.1646; PDL off + both 0.1613; PDL off + neither 0.1694).
+        self.fork_prep = os.environ.get("MPIT_FORK_PREP", "0") == "1"        # input conversion beside the boundary kernel
+        self.split_reduce = os.environ.get("MPIT_SPLIT_REDUCE", "0") == "1"  # layers 1..4 reduced beside the last dgrad
+        self._side = torch.cuda.Stream(device=eng.dev)
+        self._ev = [torch.cuda.Event() for _ in range(5)]
+        self._ev_in = [torch.cuda.Event() for _ in range(2)]
         self.wgrad = None
         if wgrad != "ref":
             try:
@@ -195,17 +205,42 @@ class CifarUmmaPlan:
             l.run(self.err, dropout=(train if i == 3 else None))
 
     def backward(self):
+        """Backward sweep.  The data-gradient chain (dgrad 4 -> 3 -> 2 -> 1) is the critical path; the weight
+        gradient of layer i only needs dz[i], so it runs on a side stream next to the chain (most of these
+        kernels occupy a handful of SMs).  The two streams join before the one reduce launch.  Captured into
+        a CUDA graph this becomes two parallel branches."""
         eng, ops, B = self.eng, self.eng.ops, self.eng.B
-        for i in range(4, -1, -1):
-            L = eng.layers[i]
-            x_in = eng.act[i - 1] if i > 0 else eng.x0
-            if self.wgrad is not None:
-                self.wgrad.run(i)
-            else:
+        if self.wgrad is None:
+            for i in range(4, -1, -1):
+                L = eng.layers[i]
+                x_in = eng.act[i - 1] if i > 0 else eng.x0
                 ops.conv_wgrad_ref(L.geom(B), eng.dz[i], x_in, eng.gw(i), crop=eng.crop if i == 0 else None)
                 ops.colsum(eng.dz[i], eng.gb(i), B * L.out_hw * L.out_hw, L.CO)
-            if i > 0:
-                self.dgrad[i].run(self.err)
+                if i > 0:
+                    self.dgrad[i].run(self.err)
+            return
+        main = torch.cuda.current_stream()
+        if not self.two_streams:
+            for i in range(4, -1, -1):
+                self.wgrad.run(i)
+                if i > 0:
+                    self.dgrad[i].run(self.err)
+            self.wgrad.reduce()
+            return
+        side = self._side
+        for i in range(4, 0, -1):
+            self._ev[i].record(main)            # dz[i] is final on the main stream
+            side.wait_event(self._ev[i])
+            with torch.cuda.stream(side):
+                self.wgrad.run(i)
+            self.dgrad[i].run(self.err)
+        if self.split_reduce:
+            with torch.cuda.stream(side):       # layers 1..4 are final on the side stream: reduce them there,
+                self.wgrad.reduce("early")      # beside the last (longest) data gradient
+        self.wgrad.run(0)                       # needs dz[0] from dgrad[1]: stays on the main stream
+        self._ev[0].record(side)
+        main.wait_event(self._ev[0])
+        self.wgrad.reduce("late" if self.split_reduce else "all")
 
     def check(self):
         """Raise if any bounded pipeline wait inside a tcgen05 kernel expired."""

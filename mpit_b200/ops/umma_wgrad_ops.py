@@ -66,20 +66,29 @@ class CifarWgradPlan:
         # split-K scratch workspace shared by all layers
         self.part = torch.empty(off, dtype=torch.float32, device=eng.dev)
         ls = self.launches
-        # segments of the one reduce launch: split-K partials of every layer's weight gradient ...
-        segs = [(self.part.data_ptr() + 4 * l.part_off, l.gw.data_ptr(), l.nsplit, l.m_pad, l.K, l.N) for l in ls]
+        # reduce segments: split-K partials of every layer's weight gradient ...
+        wsegs = {i: (self.part.data_ptr() + 4 * l.part_off, l.gw.data_ptr(), l.nsplit, l.m_pad, l.K, l.N)
+                 for i, l in enumerate(ls)}
         # ... and the bias-gradient partial rows written by the data-gradient epilogues: T tile rows of
         # G*C columns -> {nsplit = T*G, m_pad = 1, K = 1, N = C}
         self.bias_from_epilogue = bias_parts is not None
+        bsegs = {}
         if bias_parts:
             for li, (cp, tiles, ncols, C) in sorted(bias_parts.items()):
                 assert ncols % C == 0
-                segs.append((cp.data_ptr(), eng.gb(li).data_ptr(), tiles * (ncols // C), 1, 1, C))
-        n = len(segs)
-        self._nred = n
-        self._red = ((ctypes.c_ulonglong * n)(*[g[0] for g in segs]), (ctypes.c_ulonglong * n)(*[g[1] for g in segs]),
-                     (ctypes.c_int * n)(*[g[2] for g in segs]), (ctypes.c_int * n)(*[g[3] for g in segs]),
-                     (ctypes.c_int * n)(*[g[4] for g in segs]), (ctypes.c_int * n)(*[g[5] for g in segs]))
+                bsegs[li] = (cp.data_ptr(), eng.gb(li).data_ptr(), tiles * (ncols // C), 1, 1, C)
+
+        def pack(segs):
+            n = len(segs)
+            return (n, (ctypes.c_ulonglong * n)(*[g[0] for g in segs]), (ctypes.c_ulonglong * n)(*[g[1] for g in segs]),
+                    (ctypes.c_int * n)(*[g[2] for g in segs]), (ctypes.c_int * n)(*[g[3] for g in segs]),
+                    (ctypes.c_int * n)(*[g[4] for g in segs]), (ctypes.c_int * n)(*[g[5] for g in segs]))
+
+        # "all": one launch at the end.  "early"/"late": everything that is final once the layer-1 weight gradient
+        # is done (layers 1..4 and the bias rows of the data gradients that ran before it) / the first layer.
+        self._red = {"all": pack(list(wsegs.values()) + list(bsegs.values())),
+                     "early": pack([wsegs[i] for i in range(1, len(ls))] + [bsegs[i] for i in sorted(bsegs) if i >= 1]),
+                     "late": pack([wsegs[0]] + ([bsegs[0]] if 0 in bsegs else []))}
         L = eng.layers
         n = len(ls)
         self._cs = ((ctypes.c_ulonglong * n)(*[dz[i].data_ptr() for i in range(n)]),
@@ -93,13 +102,16 @@ class CifarWgradPlan:
         part = self.part[l.part_off:]
         check(k.mpit_umma_wgrad(l.tmap_x, l.tmap_dz, l.geom, ptr(part), ptr(l.crop), ptr(self.err), l.block_n,
                                 l.nsplit, cur_stream()), "mpit_umma_wgrad")
-        if i == 0:
-            # last layer of the backward sweep: every partial and every dz is final -> one launch sums
-            # the split-K partials of all layers, one more sums every bias gradient
-            r = self._red
-            check(k.mpit_multi_wgrad_reduce(self._nred, r[0], r[1], r[2], r[3], r[4], r[5], cur_stream()),
-                  "mpit_multi_wgrad_reduce")
-            if not self.bias_from_epilogue:
-                n = len(self.launches)
-                check(k.mpit_multi_colsum(n, self._cs[0], self._cs[1], self._cs[2], self._cs[3], cur_stream()),
-                      "mpit_multi_colsum")
+
+    def reduce(self, which: str = "all"):
+        """ONE launch sums split-K partials of weight gradients and the bias-gradient partial rows of the
+        data-gradient epilogues.  ``which``: "all", or "early" (layers 1..4, runs beside the last data gradient)
+        followed by "late" (first layer)."""
+        k = kernels()
+        r = self._red[which]
+        check(k.mpit_multi_wgrad_reduce(r[0], r[1], r[2], r[3], r[4], r[5], r[6], cur_stream()),
+              "mpit_multi_wgrad_reduce")
+        if not self.bias_from_epilogue and which in ("all", "late"):
+            n = len(self.launches)
+            check(k.mpit_multi_colsum(n, self._cs[0], self._cs[1], self._cs[2], self._cs[3], cur_stream()),
+                  "mpit_multi_colsum")

@@ -168,6 +168,7 @@ def test_engine_umma_wgrad_matches_ref_layerwise(B):
     um.gpk.fill_(7.0)
     for i in range(4, -1, -1):
         um._umma.wgrad.run(i)
+    um._umma.wgrad.reduce()
     torch.cuda.synchronize()
     um._umma.check()
     for i in range(5):

@@ -19,6 +19,7 @@ for (oh, ow) in [(5, 6), (5, 7), (2, 1)]:
     dz1 = um.dz[0].view(B, 24, 24, 64)
     dz1[0, oh, ow, 0] = 1.0
     um._umma.wgrad.run(0)
+    um._umma.wgrad.reduce()
     torch.cuda.synchronize()
     gw = um.gw(0).view(64, 5, 32)[0] * 255.0   # [kh][32 floats]
     x0 = um.x0.view(B + 1, 32, 32, 8)[0] * 255.0
