@@ -86,6 +86,23 @@ int mpit_nll_fwd_bwd(const float* logits, const int* labels, float* dlogits, flo
                      int B, int ncls, int ld, float gscale, unsigned long long* rng_inc, int accumulate,
                      float* dbias, void* stream);
 
+/* Fused classifier head (csrc/kernels/head.cu): Linear(K -> ncls) + LogSoftMax + ClassNLLCriterion forward and
+ * their backward down to the pre-activation gradient of the layer below, in ONE launch
+ * (/root/reference/asyncsgd/models/7-layers-cnn.lua:22-25, goot.lua:40,200-206):
+ *   logits[B][ld] = x[B][K] w[ncls][K]^T + bias;  loss_sum (+)= sum NLL;  confusion[y][argmax]++;
+ *   dlogits = gscale * dNLL;  db_cls[ld] = colsum(dlogits);
+ *   dx[B][K] = (dlogits w) * (x > 0 ? in_scale : 0);  db_in[K] = colsum(dx).
+ * dlogits == NULL: forward only.  Limits: ncls <= ld <= 32, K in {64,128,256,512}, else MPIT_E_UNSUPPORTED
+ * (callers fall back to mpit_umma_igemm + mpit_nll_fwd_bwd).  rng_inc as for mpit_nll_fwd_bwd.
+ * scratch: mpit_classifier_head_scratch_floats(K) floats, zero-filled ONCE by the caller; rows are spread over
+ * several CTAs, each leaves partial sums there and the last one to finish adds them in a fixed order (and
+ * re-arms the ticket), so results are bit-reproducible.  Calls sharing a scratch must not overlap. */
+int mpit_classifier_head(const float* x, const float* w, const float* bias, const int* labels, float* logits,
+                         float* dlogits, float* dx, float* loss_sum, int* confusion, float* db_cls, float* db_in,
+                         unsigned long long* rng_inc, float* scratch, int B, int K, int ncls, int ld, float gscale,
+                         float in_scale, int accumulate, void* stream);
+int mpit_classifier_head_scratch_floats(int K);
+
 /* ---- NVLink exchange kernels (csrc/kernels/comm.cu) -------------------------------------- */
 /* `shard_ptrs` is a HOST array of nranks device addresses: entry s is rank s's shard of the
  * centre variable mapped into this process (symmetric heap).  The flat vector of n floats is

@@ -340,7 +340,9 @@ class CifarEngine:
             um._ev_in[1].record(um._side)
         self._prep_forked = True
 
-    def forward(self, train: bool = True) -> None:
+    def forward(self, train: bool = True, classifier: bool = True) -> None:
+        """All layers up to the logits.  ``classifier=False`` (used by :meth:`fwd_bwd` / :meth:`evaluate` when the
+        fused classifier head will follow) stops after the last hidden layer."""
         ops, B = self.ops, self.B
         if getattr(self, "_prep_forked", False):
             torch.cuda.current_stream().wait_event(self._umma._ev_in[1])
@@ -348,7 +350,7 @@ class CifarEngine:
         else:
             ops.prep_u8(self.x_u8, self.x0, B, IMG, IMG, self.cin)
         if self._umma is not None:
-            self._umma.forward(train)
+            self._umma.forward(train, classifier)
         else:
             src = self.x0
             for i, L in enumerate(self.layers):
@@ -357,8 +359,14 @@ class CifarEngine:
                                  pool=L.pool, dropout=(L.dropout and train), rng=self.rng)
                 src = self.act[i]
 
+    def _fused_head(self, train: bool) -> bool:
+        um = self._umma
+        return um is not None and um.head and (not train or um.wgrad is not None)
+
     def loss_and_grad(self, train: bool = True) -> None:
         L5 = self.layers[-1]
+        if self._fused_head(train) and self._umma.head_loss(train):
+            return
         # with the tensor-core plan the classifier's bias gradient is produced here (the other layers' come from
         # the data-gradient epilogues); the reference path column-sums every dz in backward()
         fused_bias = train and self._umma is not None and self._umma.wgrad is not None
@@ -387,13 +395,13 @@ class CifarEngine:
 
     def fwd_bwd(self) -> None:
         """One training forward+backward: fills ``gpk`` and ``loss_sum`` (sum of per-sample NLL)."""
-        self.forward(True)
+        self.forward(True, classifier=not self._fused_head(True))
         self.loss_and_grad(True)
         self.backward()
 
     def evaluate(self) -> None:
         """Forward only (no dropout); accumulates ``loss_sum`` and ``confusion`` (goot.lua:265-322)."""
-        self.forward(False)
+        self.forward(False, classifier=not self._fused_head(False))
         self.loss_and_grad(False)
 
     def logits(self) -> torch.Tensor:

@@ -75,3 +75,23 @@ def nll_fwd_bwd(logits, labels, dlogits, loss_sum, B, ncls, ld, *, gscale, confu
     check(kernels().mpit_nll_fwd_bwd(ptr(logits), ptr(labels), ptr(dlogits), ptr(loss_sum), ptr(confusion),
                                      B, ncls, ld, gscale, ptr(rng_inc), int(accumulate), ptr(dbias), cur_stream()),
           "mpit_nll_fwd_bwd")
+
+
+def classifier_head_scratch(K: int, device) -> "torch.Tensor":
+    """Zero-filled workspace for :func:`classifier_head` (allocate once, reuse for every call)."""
+    import torch
+    return torch.zeros(kernels().mpit_classifier_head_scratch_floats(K), dtype=torch.float32, device=device)
+
+
+def classifier_head(x, w, bias, labels, logits, dlogits, dx, loss_sum, B, K, ncls, ld, *, scratch, gscale, in_scale=1.0,
+                    confusion=None, db_cls=None, db_in=None, rng_inc=None, accumulate=False) -> bool:
+    """Fused Linear(K->ncls) + LogSoftMax + NLL forward/backward (csrc/kernels/head.cu).  Returns False when the
+    shape is outside the kernel's limits (the caller then uses the GEMM + loss kernels)."""
+    code = kernels().mpit_classifier_head(ptr(x), ptr(w), ptr(bias), ptr(labels), ptr(logits), ptr(dlogits), ptr(dx),
+                                          ptr(loss_sum), ptr(confusion), ptr(db_cls), ptr(db_in), ptr(rng_inc),
+                                          ptr(scratch), B, K, ncls, ld, gscale, in_scale, int(accumulate),
+                                          cur_stream())
+    if code == -2:      # MPIT_E_UNSUPPORTED
+        return False
+    check(code, "mpit_classifier_head")
+    return True

@@ -171,8 +171,13 @@ class CifarUmmaPlan:
         # Bias gradients ride on the data-gradient epilogues: dgrad[i] writes dz[i-1], and its per-tile column
         # sums (summed over tiles by the split-K reduce launch) are the bias gradient of layer i-1.  The
         # classifier's bias gradient comes from the loss kernel.  (tiles, columns seen by the kernel, channels)
+        # The classifier (fc2 + log-softmax + NLL and their backward down to dz of fc1) is one CUDA-core kernel
+        # (csrc/kernels/head.cu) when its shape allows: it then also produces gb(4) and gb(3) directly.
+        import os
+        self.head = os.environ.get("MPIT_HEAD", "1") == "1" and f1 in (64, 128, 256, 512) and L5.CO <= 32
+        self._head_scratch = eng.ops.classifier_head_scratch(f1, eng.dev) if self.head else None
         self.bias_parts = {}
-        for i in (4, 3, 2, 1):
+        for i in ((3, 2, 1) if self.head else (4, 3, 2, 1)):
             g = self.dgrad[i].geom            # {nsub,tw,th,tn,tiles_w,tiles_h,...,B at [10],...,N at [13]}
             tiles = -(-(-(-g[10] // g[3]) * g[4] * g[5]) // g[0])
             ncols = g[13]
@@ -180,7 +185,6 @@ class CifarUmmaPlan:
             self.dgrad[i].colpart = cp
             self.bias_parts[i - 1] = (cp, tiles, ncols, eng.layers[i - 1].CO)
 
-        import os
         self.two_streams = os.environ.get("MPIT_BWD_STREAMS", "2") != "1"
         # Two more forks exist but are off by default: every fork/join turns a programmatic (PDL) edge into a
         # full one, and on B200 the two effects cancel (measured, tools/dev/pdl_ab.py, ms/step at batch 128:
@@ -200,9 +204,23 @@ class CifarUmmaPlan:
                     raise
 
     # -- schedules -----------------------------------------------------------------------------
-    def forward(self, train: bool):
-        for i, l in enumerate(self.fwd):
+    def forward(self, train: bool, classifier: bool = True):
+        for i, l in enumerate(self.fwd if classifier else self.fwd[:4]):
             l.run(self.err, dropout=(train if i == 3 else None))
+
+    def head_loss(self, train: bool) -> bool:
+        """fc2 + loss (+ backward to dz[3], gb(4), gb(3) when training) in one launch; False if not applicable."""
+        if not self.head:
+            return False
+        eng = self.eng
+        L4, L5 = eng.layers[3], eng.layers[4]
+        return eng.ops.classifier_head(
+            eng.act[3], eng.w(4), eng.b(4), eng.labels, eng.act[4], eng.dz[4] if train else None,
+            eng.dz[3] if train else None, eng.loss_sum, eng.B, L4.CO, eng.ncls, L5.CO, scratch=self._head_scratch,
+            gscale=1.0 / eng.B,
+            in_scale=2.0 if L4.dropout else 1.0, confusion=eng.confusion,
+            db_cls=eng.gb(4) if train else None, db_in=eng.gb(3) if train else None,
+            rng_inc=eng.rng if train else None)
 
     def backward(self):
         """Backward sweep.  The data-gradient chain (dgrad 4 -> 3 -> 2 -> 1) is the critical path; the weight
@@ -220,10 +238,11 @@ class CifarUmmaPlan:
                     self.dgrad[i].run(self.err)
             return
         main = torch.cuda.current_stream()
+        skip = 4 if self.head else -1      # the head kernel already produced dz[3]
         if not self.two_streams:
             for i in range(4, -1, -1):
                 self.wgrad.run(i)
-                if i > 0:
+                if i > 0 and i != skip:
                     self.dgrad[i].run(self.err)
             self.wgrad.reduce()
             return
@@ -233,7 +252,8 @@ class CifarUmmaPlan:
             side.wait_event(self._ev[i])
             with torch.cuda.stream(side):
                 self.wgrad.run(i)
-            self.dgrad[i].run(self.err)
+            if i != skip:
+                self.dgrad[i].run(self.err)
         if self.split_reduce:
             with torch.cuda.stream(side):       # layers 1..4 are final on the side stream: reduce them there,
                 self.wgrad.reduce("early")      # beside the last (longest) data gradient
