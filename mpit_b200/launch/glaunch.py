@@ -23,12 +23,17 @@ def main(argv=None) -> int:
     ap.add_argument("--mom", type=float, default=0.99)
     ap.add_argument("--kernels", default="umma")
     ap.add_argument("--save", default="results/glaunch")
+    ap.add_argument("--data", default=None, help="directory with the cifar-10-batches-t7 files (default: search, "
+                                                 "else synthetic data)")
+    ap.add_argument("--resume", default=None, help="model-epoch-N.net (or a flat parameter tensor) to start from")
     a = ap.parse_args(argv)
-    from ..workloads.cifar import CifarTrainer, CifarOpts, synthetic_cifar, train_epochs
+    from ..workloads.cifar import CifarTrainer, CifarOpts, cifar_data, load_checkpoint, train_epochs
     opts = CifarOpts(name="sgd", lr=a.lr, mom=a.mom, mb=a.mb, impl=a.kernels, maxepoch=a.epochs, save=a.save)
     print("[client] use gpu", 0)
-    tr = CifarTrainer(opts, torch.device("cuda:0"))
-    hist = train_epochs(tr, synthetic_cifar(a.trsize, seed=1), synthetic_cifar(a.tesize, seed=2))
+    tr = CifarTrainer(opts, torch.device("cuda:0"), theta0=load_checkpoint(a.resume) if a.resume else None)
+    train, test, real = cifar_data(a.trsize, a.tesize, seed=1, root=a.data)
+    print("===> data:", "cifar-10-batches-t7" if real else "synthetic (CIFAR-10 shaped)")
+    hist = train_epochs(tr, train, test)
     print(f"final train loss {hist['train_loss'][-1]:.4f}, test acc {hist['test_acc'][-1]:.4f}, "
           f"{hist['samples_per_s']:.0f} samples/s")
     return 0

@@ -36,6 +36,8 @@ def main(argv=None) -> int:
     ap.add_argument("--tesize", type=int, default=512)
     ap.add_argument("--mb", type=int, default=128)
     ap.add_argument("--save", default="results/mlaunch")
+    ap.add_argument("--data", default=None, help="directory with the cifar-10-batches-t7 files")
+    ap.add_argument("--resume", default=None, help="checkpoint (model-epoch-N.net or flat tensor) to start from")
     a = ap.parse_args(argv)
     lr = a.lr if a.lr is not None else (1e-4 if a.optim == "downpour" else 1e-2)   # mlaunch.lua:50-60
     if a.device == "cuda":
@@ -46,7 +48,7 @@ def main(argv=None) -> int:
 def _gpu(a, lr) -> int:
     import torch.distributed as dist
     from ..parallel.symm import SymmetricHeap
-    from ..workloads.cifar import CifarTrainer, CifarOpts, synthetic_cifar, train_epochs
+    from ..workloads.cifar import CifarTrainer, CifarOpts, cifar_data, load_checkpoint, train_epochs
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -58,10 +60,12 @@ def _gpu(a, lr) -> int:
     opts = CifarOpts(name=a.optim, lr=lr, mom=a.mom, mb=a.mb, su=a.su, mva=0.9 / world, maxepoch=a.epochs,
                      save=a.save, seed=1 + rank, model=a.model)
     print(f"[client] rank {rank} use gpu {local}")
-    tr = CifarTrainer(opts, dev, heap)
+    tr = CifarTrainer(opts, dev, heap, theta0=load_checkpoint(a.resume) if a.resume else None)
     ch = 1 if a.model == "mnist" else 3
-    hist = train_epochs(tr, synthetic_cifar(a.trsize, seed=10 + rank, channels=ch),
-                        synthetic_cifar(a.tesize, seed=2, channels=ch), rank=rank, quiet=rank != 0)
+    train, test, real = cifar_data(a.trsize, a.tesize, seed=10 + rank, channels=ch, root=a.data)
+    if rank == 0:
+        print("===> data:", "cifar-10-batches-t7" if real else "synthetic")
+    hist = train_epochs(tr, train, test, rank=rank, quiet=rank != 0)
     print(f"[rank {rank}] train loss {hist['train_loss'][-1]:.4f} test acc {hist['test_acc'][-1]:.4f} "
           f"{hist['samples_per_s']:.0f} samples/s")
     heap.check_timeout()

@@ -82,15 +82,21 @@ class _Reader:
     def i64(self):
         return struct.unpack("<q", self._read(8))[0]
 
+    def f64(self):
+        return struct.unpack("<d", self._read(8))[0]
+
     def string(self):
         return self._read(self.i32()).decode("latin-1")
+
+    def array(self, n: int, dt: np.dtype) -> np.ndarray:
+        return np.frombuffer(self._read(n * dt.itemsize), dtype=dt).copy()
 
     def obj(self):
         t = self.i32()
         if t == TYPE_NIL:
             return None
         if t == TYPE_NUMBER:
-            v = struct.unpack("<d", self._read(8))[0]
+            v = self.f64()
             return int(v) if v.is_integer() and abs(v) < 2 ** 53 else v
         if t == TYPE_STRING:
             return self.string()
@@ -120,9 +126,7 @@ class _Reader:
     def _torch_payload(self, cls, ref):
         if cls in _STORAGE_DTYPES:
             n = self.i64()
-            dt = _STORAGE_DTYPES[cls]
-            arr = np.frombuffer(self._read(n * dt.itemsize), dtype=dt).copy()
-            return T7Storage(cls, arr)
+            return T7Storage(cls, self.array(n, _STORAGE_DTYPES[cls]))
         if cls in _TENSOR_TO_STORAGE:
             nd = self.i32()
             size = [self.i64() for _ in range(nd)]
@@ -139,6 +143,67 @@ class _Reader:
         return obj
 
 
+class _AsciiReader(_Reader):
+    """``torch.load(file, 'ascii')`` (THDiskFile ascii mode, used by the CIFAR-10 ``*.t7`` batches that
+    /root/reference/asyncsgd/goot.lua:62-69 loads): numbers are decimal tokens separated by blanks with a
+    newline after each write; char/byte data (strings, Byte/CharStorage) is raw bytes followed by a newline."""
+
+    _WS = b" \t\r\n"
+
+    def _token(self) -> bytes:
+        f = self.f
+        c = f.read(1)
+        while c and c in self._WS:
+            c = f.read(1)
+        if not c:
+            raise EOFError("truncated Torch7 ascii file")
+        out = bytearray()
+        while c and c not in self._WS:
+            out += c
+            c = f.read(1)
+        return bytes(out)
+
+    def _eat_newline(self):
+        c = self.f.read(1)
+        if c and c != b"\n":
+            self.f.seek(-1, 1)
+
+    def i32(self):
+        return int(self._token())
+
+    i64 = i32
+
+    def f64(self):
+        return float(self._token())
+
+    def string(self):
+        n = self.i32()
+        b = self._read(n)
+        self._eat_newline()
+        return b.decode("latin-1")
+
+    def array(self, n: int, dt: np.dtype) -> np.ndarray:
+        if n == 0:
+            return np.zeros(0, dtype=dt)
+        if dt.itemsize == 1:                       # raw, like the binary format
+            arr = np.frombuffer(self._read(n), dtype=dt).copy()
+            self._eat_newline()
+            return arr
+        # one line of n blank-separated numbers
+        line = bytearray()
+        while True:
+            chunk = self.f.readline()
+            if not chunk:
+                raise EOFError("truncated Torch7 ascii file")
+            line += chunk
+            vals = line.split()
+            if len(vals) >= n:
+                break
+        if len(vals) != n:
+            raise ValueError("Torch7 ascii storage: element count mismatch")
+        return np.array([float(v) for v in vals], dtype=np.float64).astype(dt)
+
+
 class _Writer:
     def __init__(self, f: BinaryIO):
         self.f = f
@@ -152,10 +217,16 @@ class _Writer:
     def i64(self, v):
         self.f.write(struct.pack("<q", v))
 
+    def f64(self, v):
+        self.f.write(struct.pack("<d", v))
+
     def string(self, s: str):
         b = s.encode("latin-1")
         self.i32(len(b))
         self.f.write(b)
+
+    def array(self, arr: np.ndarray):
+        self.f.write(arr.tobytes())
 
     def _ref(self, o, kind: str = "") -> bool:
         """Write the reference index; True if the object was already written.  ``kind`` separates a
@@ -178,7 +249,7 @@ class _Writer:
             self.i32(1 if o else 0)
         elif isinstance(o, (int, float)):
             self.i32(TYPE_NUMBER)
-            self.f.write(struct.pack("<d", float(o)))
+            self.f64(float(o))
         elif isinstance(o, str):
             self.i32(TYPE_STRING)
             self.string(o)
@@ -216,7 +287,7 @@ class _Writer:
         self.string("V 1")
         self.string(cls)
         self.i64(arr.size)
-        self.f.write(np.ascontiguousarray(arr).astype(_STORAGE_DTYPES[cls], copy=False).tobytes())
+        self.array(np.ascontiguousarray(arr).astype(_STORAGE_DTYPES[cls], copy=False))
 
     def tensor(self, t: torch.Tensor):
         orig = t
@@ -240,21 +311,48 @@ class _Writer:
             self.storage(f"torch.{kind}Storage", tc.numpy().reshape(-1), tc)
 
 
-def load(path_or_file) -> Any:
-    """``torch.load(file)`` (binary format)."""
+class _AsciiWriter(_Writer):
+    def i32(self, v):
+        self.f.write(b"%d\n" % int(v))
+
+    i64 = i32
+
+    def f64(self, v):
+        self.f.write(repr(float(v)).encode() + b"\n")
+
+    def string(self, s: str):
+        b = s.encode("latin-1")
+        self.i32(len(b))
+        self.f.write(b + b"\n")
+
+    def array(self, arr: np.ndarray):
+        if arr.size == 0:
+            return
+        if arr.dtype.itemsize == 1:
+            self.f.write(arr.tobytes() + b"\n")
+        elif arr.dtype.kind == "f":
+            self.f.write(" ".join(repr(float(v)) for v in arr.tolist()).encode() + b"\n")
+        else:
+            self.f.write(" ".join(str(int(v)) for v in arr.tolist()).encode() + b"\n")
+
+
+def load(path_or_file, mode: str = "binary") -> Any:
+    """``torch.load(file [, 'ascii'])``."""
+    R = _AsciiReader if mode == "ascii" else _Reader
     if hasattr(path_or_file, "read"):
-        return _Reader(path_or_file).obj()
+        return R(path_or_file).obj()
     with open(path_or_file, "rb") as f:
-        return _Reader(f).obj()
+        return R(f).obj()
 
 
-def save(path_or_file, obj) -> None:
-    """``torch.save(file, obj)`` (binary format)."""
+def save(path_or_file, obj, mode: str = "binary") -> None:
+    """``torch.save(file, obj [, 'ascii'])``."""
+    W = _AsciiWriter if mode == "ascii" else _Writer
     if hasattr(path_or_file, "write"):
-        _Writer(path_or_file).obj(obj)
+        W(path_or_file).obj(obj)
         return
     with open(path_or_file, "wb") as f:
-        _Writer(f).obj(obj)
+        W(f).obj(obj)
 
 
 def loads(data: bytes) -> Any:

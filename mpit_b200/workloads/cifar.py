@@ -59,6 +59,32 @@ def synthetic_cifar(n: int, seed: int = 0, pinned: bool = True, channels: int = 
     return x, y
 
 
+def cifar_data(trsize: int, tesize: int, seed: int = 0, channels: int = 3, root: Optional[str] = None,
+               pinned: bool = True):
+    """(train_x, train_y), (test_x, test_y), is_real: the Torch7 CIFAR-10 batches the reference loads
+    (goot.lua:62-77) when they can be found (``root`` / $CIFAR10_T7 / ./cifar-10-batches-t7), else synthetic
+    data of the same shape.  Every worker sees the whole set and shuffles with its own seed, like the reference."""
+    from ..data import find_cifar10, load_cifar10
+    if channels == 3 and find_cifar10(root) is not None:
+        (x, y), (tx, ty), _ = load_cifar10(root, trsize, tesize, synthetic_ok=False)
+        if pinned and torch.cuda.is_available():
+            x, y, tx, ty = x.pin_memory(), y.pin_memory(), tx.pin_memory(), ty.pin_memory()
+        return (x, y), (tx, ty), True
+    return (synthetic_cifar(trsize, seed=seed, pinned=pinned, channels=channels),
+            synthetic_cifar(tesize, seed=2, pinned=pinned, channels=channels), False)
+
+
+def load_checkpoint(path: str) -> torch.Tensor:
+    """Flat parameters from a checkpoint written by :func:`train_epochs` (a Torch7 ``nn.Sequential``,
+    goot.lua:246-254) or from a flat-tensor file as BiCNN writes (bicnn.lua:590-594) -- the resume path the
+    reference only has for BiCNN (``-loadmodel``, bicnn.lua:259-261)."""
+    from .. import t7
+    obj = t7.load(path)
+    if isinstance(obj, torch.Tensor):
+        return obj.reshape(-1).float()
+    return t7.cifar_theta_from_t7(obj)
+
+
 class CifarTrainer:
     def __init__(self, opts: CifarOpts, device: Optional[torch.device] = None, heap: Optional[SymmetricHeap] = None,
                  theta0: Optional[torch.Tensor] = None):
