@@ -403,6 +403,32 @@ static SignalTable make_sig(const unsigned long long* ptrs, int nranks, int rank
   return t;
 }
 
+// ---- one-sided window operations (MPI_Put / MPI_Get / MPI_Accumulate, mpifuncs.c:1656,1131,9) ----
+// `remote` is an address inside a peer's symmetric buffer mapped into this process.  Vector (16-byte) accesses
+// when both sides allow it, scalar otherwise (arbitrary displacements are legal in a window).
+enum RmaOp : int { RMA_PUT = 0, RMA_GET = 1, RMA_ACC = 2 };
+
+__global__ void __launch_bounds__(256) peer_rma_kernel(int op, float* remote, float* local, long long n, float scale) {
+  const long long stride = (long long)gridDim.x * blockDim.x, t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool vec = (((uintptr_t)remote | (uintptr_t)local) & 15) == 0;
+  const long long n4 = vec ? n >> 2 : 0;
+  for (long long q = t0; q < n4; q += stride) {
+    if (op == RMA_GET) {
+      st4(local + 4 * q, ld_sys4(remote + 4 * q));
+    } else {
+      float4 v = ld4(local + 4 * q);
+      if (scale != 1.f) { v.x *= scale; v.y *= scale; v.z *= scale; v.w *= scale; }
+      if (op == RMA_PUT) st_sys4(remote + 4 * q, v);
+      else red_add_sys4(remote + 4 * q, v);
+    }
+  }
+  for (long long i = 4 * n4 + t0; i < n; i += stride) {
+    if (op == RMA_GET) local[i] = ld_sys(remote + i);
+    else if (op == RMA_PUT) st_sys(remote + i, local[i] * scale);
+    else red_add_sys(remote + i, local[i] * scale);
+  }
+}
+
 static int exch_grid(const QuadWalk& w) { return ew_grid(w.total, 256, 1, 8); }
 
 }  // namespace mpit
@@ -533,6 +559,14 @@ int mpit_bcast(const unsigned long long* buf_ptrs, unsigned long long buf_mc, co
 int mpit_device_barrier(const unsigned long long* sig_ptrs, int nranks, int rank, void* stream) {
   if (nranks < 1 || nranks > MPIT_MAX_RANKS) return MPIT_E_ARG;
   barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(make_sig(sig_ptrs, nranks, rank));
+  MPIT_LAUNCH_CHECK();
+  return 0;
+}
+
+int mpit_peer_rma(int op, float* remote, float* local, long long n, float scale, void* stream) {
+  if (op < RMA_PUT || op > RMA_ACC || !remote || !local) return MPIT_E_ARG;
+  if (n <= 0) return 0;
+  peer_rma_kernel<<<ew_grid(n, 256, 8), 256, 0, (cudaStream_t)stream>>>(op, remote, local, n, scale);
   MPIT_LAUNCH_CHECK();
   return 0;
 }

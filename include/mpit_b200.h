@@ -141,6 +141,10 @@ int mpit_allreduce(const unsigned long long* in_ptrs, unsigned long long in_mc,
 int mpit_bcast(const unsigned long long* buf_ptrs, unsigned long long buf_mc, const unsigned long long* sig_ptrs,
                int nranks, int rank, int root, long long n, int max_blocks, void* stream);
 int mpit_device_barrier(const unsigned long long* sig_ptrs, int nranks, int rank, void* stream);
+/* One-sided window operation on a peer's symmetric memory (MPI_Put / MPI_Get / MPI_Accumulate(SUM),
+ * /root/reference/mpifuncs.c:1656,1131,9): op 0 remote[i] = scale*local[i], 1 local[i] = remote[i],
+ * 2 remote[i] += scale*local[i] (red.add, fire and forget).  `remote` = peer base + displacement. */
+int mpit_peer_rma(int op, float* remote, float* local, long long n, float scale, void* stream);
 /* Device mailbox (MPI_Send/Recv latency path, /root/reference/test.lua:32-38). A slot is 8 header
  * floats + payload in the receiver's symmetric memory. result3 = {arrived, count, tag}. */
 int mpit_mailbox_put(float* slot_base, const float* payload, unsigned count, unsigned tag, unsigned seq,

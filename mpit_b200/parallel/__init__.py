@@ -2,3 +2,4 @@
 from .symm import SymmetricHeap, SymmBuffer, LocalPeerHeap
 from .center import ShardedCenter, partition
 from .collectives import DeviceCollectives, DeviceMailbox, DeviceRequest
+from .window import DeviceWindow

@@ -219,6 +219,33 @@ def case_pulled_linear(rank, world, dev, heap):
     assert float((y2.cpu() - ref2).norm() / ref2.norm()) < 3e-3
 
 
+def case_window(rank, world, dev, heap):
+    """One-sided ring: every rank Puts into its right neighbour, Accumulates into everybody, fences, checks,
+    then Gets from its left neighbour (MPI_Put/Accumulate/Get/Win_fence over NVLink)."""
+    from mpit_b200.parallel.window import DeviceWindow
+    n = 4096 + 3
+    win = DeviceWindow(heap, n)
+    win.fence()
+    mine = torch.full((n,), float(rank + 1), device=dev)
+    win.put(mine, (rank + 1) % world)
+    win.fence()
+    assert torch.equal(win.local, torch.full((n,), float((rank - 1) % world + 1), device=dev))
+    win.fence()
+    one = torch.ones(n, device=dev)
+    for t in range(world):
+        win.accumulate(one, t, scale=float(rank + 1))
+    win.fence()
+    want = float((rank - 1) % world + 1) + world * (world + 1) / 2
+    assert torch.allclose(win.local, torch.full((n,), want, device=dev)), (float(win.local[0]), want)
+    got = torch.empty(100, device=dev)
+    win.get(got, (rank - 1) % world, target_disp=5, count=100)
+    win.unlock((rank - 1) % world)
+    left = float((rank - 2) % world + 1) + world * (world + 1) / 2
+    assert torch.allclose(got, torch.full((100,), left, device=dev))
+    win.fence()
+    heap.check_timeout()
+
+
 CASES = {k[5:]: v for k, v in globals().items() if k.startswith("case_")}
 
 if __name__ == "__main__":

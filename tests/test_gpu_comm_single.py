@@ -143,3 +143,29 @@ def test_bulk_elastic_and_scaled_push(n, S):
     torch.cuda.synchronize()
     assert torch.allclose(_center_as_flat(cs, n), c0 + ref_d + g0 * 0.5, atol=1e-6)
     assert float(g.abs().sum()) == 0.0
+
+
+def test_device_window_put_get_accumulate_single_gpu():
+    """MPI_Put / MPI_Get / MPI_Accumulate on symmetric memory (mpifuncs.c:1656,1131,9), ranks aliased onto one GPU,
+    odd displacements and lengths (scalar tail path) included.  No fence here: barrier kernels of different ranks
+    must not share one GPU."""
+    from mpit_b200.parallel.window import DeviceWindow
+    S, n = 3, 1000
+    heap = LocalPeerHeap(S, devices=[0] * S)
+    bufs, sigs = heap.alloc(n), heap.signal_pads()
+    wins = [DeviceWindow(None, n, buf=bufs[r], sig=sigs[r]) for r in range(S)]
+    a = torch.randn(257, device="cuda")
+    wins[0].put(a, target_rank=2, target_disp=13)
+    wins[1].accumulate(a, target_rank=2, target_disp=13, scale=0.5)
+    wins[0].unlock(2)
+    want = torch.zeros(n, device="cuda")
+    want[13:13 + 257] = a * 1.5
+    assert torch.allclose(wins[2].local, want)
+    out = torch.empty(100, device="cuda")
+    wins[1].get(out, target_rank=2, target_disp=16, count=100)      # 16-byte aligned: vector path
+    wins[1].flush(2)
+    assert torch.equal(out, wins[2].local[16:116])
+    with pytest.raises(ValueError):
+        wins[0].put(a, target_rank=1, target_disp=n - 10)
+    with pytest.raises(ValueError):
+        wins[0].get(out, target_rank=5)

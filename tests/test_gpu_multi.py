@@ -44,3 +44,10 @@ def test_pull_fused_with_consumer_gemm():
     n = min(torch.cuda.device_count(), 8)
     out = _torchrun(["pulled_linear"], n)
     assert "case pulled_linear: ok" in out
+
+
+def test_one_sided_window():
+    """MPI_Put / Accumulate / Get / Win_fence on the symmetric heap."""
+    n = min(torch.cuda.device_count(), 8)
+    out = _torchrun(["window"], n)
+    assert "case window: ok" in out
