@@ -395,6 +395,8 @@ def Bcast(buf, count: int, dtype: int, root: int, comm: int = COMM_WORLD) -> Non
 
 
 def Reduce(sbuf, rbuf, count: int, dtype: int, op: int, root: int, comm: int = COMM_WORLD) -> None:
+    if extras.is_user_op(op):
+        return extras.reduce_user_op(sbuf, rbuf, count, dtype, op, root, comm, everyone=False)
     s, r = _Buf(sbuf, count, dtype, False), _Buf(rbuf, count, dtype, True)
     _chk(host().mpit_msg_reduce(s.ptr, r.ptr, count, dtype, op, root, comm), "Reduce")
     if r.after and Comm_rank(comm) == root:
@@ -402,6 +404,8 @@ def Reduce(sbuf, rbuf, count: int, dtype: int, op: int, root: int, comm: int = C
 
 
 def Allreduce(sbuf, rbuf, count: int, dtype: int, op: int, comm: int = COMM_WORLD) -> None:
+    if extras.is_user_op(op):
+        return extras.reduce_user_op(sbuf, rbuf, count, dtype, op, 0, comm, everyone=True)
     """MPI_Allreduce (/root/reference/test/testreduceall.lua:28)."""
     s, r = _Buf(sbuf, count, dtype, False), _Buf(rbuf, count, dtype, True)
     _chk(host().mpit_msg_allreduce(s.ptr, r.ptr, count, dtype, op, comm), "Allreduce")
@@ -485,3 +489,10 @@ def deserialize(buf: torch.Tensor):
 
 # coroutine IO lives in mpit_b200.aio; re-exported here because the reference hangs everything on mpiT
 from ..aio import (aio_send, aio_recv, co_execute, co_ping, co_wait, Queue)  # noqa: E402,F401
+
+
+# ---- the wider MPI surface (send modes, persistent requests, vector collectives, groups, user ops, fence
+# windows, error classes ...), composed from the calls above: see msg/extras.py ----
+from . import extras  # noqa: E402
+from .extras import *  # noqa: E402,F401,F403
+from .extras import (PROC_NULL, ROOT, IDENT, CONGRUENT, SIMILAR, UNEQUAL, LXOR, BXOR, GROUP_EMPTY)  # noqa: E402,F401

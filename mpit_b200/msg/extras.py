@@ -1,0 +1,570 @@
+"""The wider MPI surface of the reference's binding, composed from the native primitives.
+
+/root/reference/mpifuncs.c wraps 258 MPI functions; the tree calls 17 of them.  The core of
+``mpit_b200.msg`` implements those natively (C++).  This module adds the rest of the chapters a user of the
+binding could reasonably have reached for -- send modes, persistent requests, Test/Wait-some/any, the vector
+collectives, Exscan/Reduce_scatter, groups and communicator construction, user reduction ops, error classes,
+environment queries, and fence-synchronised one-sided windows -- as thin Python compositions of the native
+point-to-point and collective calls.  MPI-IO, topologies, derived datatypes and dynamic processes stay out of scope
+("wrapped but unused").
+
+Everything here follows the conventions of the core module: results are returned instead of written through
+out-parameters, errors raise :class:`MPIError`.
+"""
+from __future__ import annotations
+
+import socket
+from typing import Callable, Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+# ---- constants (/root/reference/lua-mpi.h:125-231) -------------------------------------------------
+PROC_NULL, ROOT = -2, -3
+MAX_PROCESSOR_NAME, MAX_ERROR_STRING, MAX_OBJECT_NAME = 256, 512, 128
+IDENT, CONGRUENT, SIMILAR, UNEQUAL = 0, 1, 2, 3
+(ERR_BUFFER, ERR_COUNT, ERR_TYPE, ERR_TAG, ERR_COMM, ERR_RANK, ERR_REQUEST, ERR_ROOT, ERR_GROUP, ERR_OP, ERR_TOPOLOGY,
+ ERR_DIMS, ERR_ARG, ERR_UNKNOWN) = range(1, 15)
+ERR_OTHER, ERR_INTERN, ERR_IN_STATUS, ERR_PENDING, ERR_WIN, ERR_RMA_SYNC, ERR_LASTCODE = 16, 17, 18, 19, 45, 50, 92
+LXOR, BXOR = 8, 9                                 # the native layer implements SUM..BOR (0..7)
+OP_NULL, GROUP_NULL, DATATYPE_NULL, ERRHANDLER_NULL, INFO_NULL, WIN_NULL = -1, None, -1, -1, -1, None
+_ERR_NAMES = {0: "MPI_SUCCESS: no errors", 1: "MPI_ERR_BUFFER: invalid buffer pointer", 2: "MPI_ERR_COUNT: invalid count",
+              3: "MPI_ERR_TYPE: invalid datatype", 4: "MPI_ERR_TAG: invalid tag", 5: "MPI_ERR_COMM: invalid communicator",
+              6: "MPI_ERR_RANK: invalid rank", 7: "MPI_ERR_REQUEST: invalid request", 8: "MPI_ERR_ROOT: invalid root",
+              9: "MPI_ERR_GROUP: invalid group", 10: "MPI_ERR_OP: invalid operation", 13: "MPI_ERR_ARG: invalid argument",
+              14: "MPI_ERR_UNKNOWN: unknown error", 15: "MPI_ERR_TRUNCATE: message truncated on receive",
+              16: "MPI_ERR_OTHER: known error not in this list", 17: "MPI_ERR_INTERN: internal error",
+              45: "MPI_ERR_WIN: invalid window", 50: "MPI_ERR_RMA_SYNC: wrong RMA synchronisation"}
+_COLL_TAG = 32100          # tag space of the composed collectives (user tags in the tree are 1..8)
+
+
+def _m():
+    from .. import msg
+    return msg
+
+
+def _flat(buf):
+    """1-D view of a user buffer (torch tensor or numpy array) that aliases its memory."""
+    if isinstance(buf, torch.Tensor):
+        return buf.view(-1) if buf.is_contiguous() else buf.reshape(-1)
+    return np.asarray(buf).reshape(-1)
+
+
+# ---- environment -----------------------------------------------------------------------------------
+def Get_version() -> Tuple[int, int]:
+    """MPI_Get_version: the standard level whose semantics this layer follows for what it implements."""
+    return 3, 1
+
+
+def Get_library_version() -> str:
+    return "mpit_b200 host message layer (TCP, progress thread) -- see csrc/msg/hostcomm.cpp"
+
+
+def Finalized() -> bool:
+    return not _m().Initialized() and getattr(_m(), "_was_finalized", False)
+
+
+def Query_thread() -> int:
+    return _m().THREAD_MULTIPLE       # the native layer is thread-safe (one lock around the matching queues)
+
+
+def Is_thread_main() -> bool:
+    import threading
+    return threading.current_thread() is threading.main_thread()
+
+
+def Error_class(code: int) -> int:
+    return code
+
+
+def Error_string(code: int) -> str:
+    return _ERR_NAMES.get(code, f"error class {code}")
+
+
+def Type_size(dtype: int) -> int:
+    return _m()._DTYPE_SIZE[dtype]
+
+
+def Type_get_extent(dtype: int) -> Tuple[int, int]:
+    return 0, _m()._DTYPE_SIZE[dtype]
+
+
+def Alloc_mem(nbytes: int) -> torch.Tensor:
+    """MPI_Alloc_mem: page-locked host memory when CUDA is present (fast staging for device tensors)."""
+    t = torch.empty(nbytes, dtype=torch.uint8)
+    return t.pin_memory() if torch.cuda.is_available() else t
+
+
+def Free_mem(buf) -> None:
+    del buf
+
+
+def Get_hostname() -> str:
+    return socket.gethostname()
+
+
+# ---- send modes (mpifuncs.c Bsend/Rsend/Ssend and their I-variants) ---------------------------------
+# The native Send returns once the message is handed to the progress thread (buffered semantics), which is a
+# legal implementation of every mode except the synchronous one; Ssend adds the handshake.
+def Bsend(buf, count, dtype, dest, tag, comm=0):
+    _m().Send(buf, count, dtype, dest, tag, comm)
+
+
+Rsend = Bsend
+
+
+def Ssend(buf, count, dtype, dest, tag, comm=0):
+    """Synchronous send: returns only after the receiver has matched the message (0-byte acknowledgement)."""
+    m = _m()
+    m.Send(buf, count, dtype, dest, tag, comm)
+    m.Recv(None, 0, m.BYTE, dest, _COLL_TAG + 90, comm)
+
+
+def Ssend_ack(source, comm=0):
+    """Receiver side of :func:`Ssend` (call after the matching Recv)."""
+    m = _m()
+    m.Send(None, 0, m.BYTE, source, _COLL_TAG + 90, comm)
+
+
+def Ibsend(buf, count, dtype, dest, tag, comm, request, i=0):
+    _m().Isend(buf, count, dtype, dest, tag, comm, request, i)
+
+
+Irsend = Issend = Ibsend
+
+
+# ---- completion of several requests ----------------------------------------------------------------
+def Testany(request, status=None) -> Tuple[int, bool]:
+    """-> (index, flag).  index is UNDEFINED when no active request exists or none has completed."""
+    m = _m()
+    active = [i for i in range(len(request)) if not request.is_null(i)]
+    if not active:
+        return m.UNDEFINED, True
+    for i in active:
+        if m.Test(request, status, i):
+            return i, True
+    return m.UNDEFINED, False
+
+
+def Testsome(request, statuses=None) -> List[int]:
+    """Indices that completed now (empty list: none yet; UNDEFINED semantics -> ``None`` when nothing is active)."""
+    m = _m()
+    active = [i for i in range(len(request)) if not request.is_null(i)]
+    if not active:
+        return None
+    return [i for i in active if m.Test(request, None, i)]
+
+
+def Waitsome(request, statuses=None) -> List[int]:
+    import time
+    while True:
+        done = Testsome(request, statuses)
+        if done is None or done:
+            return done or []
+        time.sleep(0)
+
+
+# ---- persistent requests (Send_init / Recv_init / Start / Startall / Request_free) ------------------
+def _persist(request) -> Dict[int, tuple]:
+    if not hasattr(request, "_persistent"):
+        request._persistent = {}
+    return request._persistent
+
+
+def Send_init(buf, count, dtype, dest, tag, comm, request, i=0):
+    _persist(request)[i] = ("send", buf, count, dtype, dest, tag, comm)
+
+
+Bsend_init = Rsend_init = Ssend_init = Send_init
+
+
+def Recv_init(buf, count, dtype, source, tag, comm, request, i=0):
+    _persist(request)[i] = ("recv", buf, count, dtype, source, tag, comm)
+
+
+def Start(request, i=0):
+    m = _m()
+    kind, buf, count, dtype, peer, tag, comm = _persist(request)[i]
+    (m.Isend if kind == "send" else m.Irecv)(buf, count, dtype, peer, tag, comm, request, i)
+
+
+def Startall(request):
+    for i in sorted(_persist(request)):
+        Start(request, i)
+
+
+def Request_free(request, i=0):
+    _persist(request).pop(i, None)
+    request._arr[i] = _m().REQUEST_NULL
+
+
+# ---- vector collectives ----------------------------------------------------------------------------
+def _p2p_exchange(sends, recvs, comm):
+    """sends/recvs: lists of (peer, flat_buffer, count, dtype).  All posted non-blocking, then waited."""
+    m = _m()
+    req = m.Request(len(sends) + len(recvs))
+    k = 0
+    for peer, b, cnt, dt in recvs:
+        m.Irecv(b, cnt, dt, peer, _COLL_TAG, comm, req, k)
+        k += 1
+    for peer, b, cnt, dt in sends:
+        m.Isend(b, cnt, dt, peer, _COLL_TAG, comm, req, k)
+        k += 1
+    m.Waitall(req)
+
+
+def Gatherv(sbuf, scount, dtype, rbuf, rcounts: Sequence[int], displs: Sequence[int], root, comm=0):
+    m = _m()
+    me, n = m.Comm_rank(comm), m.Comm_size(comm)
+    s = _flat(sbuf)
+    if me != root:
+        m.Send(s[:scount], scount, dtype, root, _COLL_TAG, comm)
+        return
+    r = _flat(rbuf)
+    recvs = [(p, r[displs[p]:displs[p] + rcounts[p]], rcounts[p], dtype) for p in range(n) if p != root]
+    r[displs[root]:displs[root] + rcounts[root]] = s[:rcounts[root]]
+    _p2p_exchange([], recvs, comm)
+
+
+def Scatterv(sbuf, scounts: Sequence[int], displs: Sequence[int], dtype, rbuf, rcount, root, comm=0):
+    m = _m()
+    me, n = m.Comm_rank(comm), m.Comm_size(comm)
+    r = _flat(rbuf)
+    if me != root:
+        m.Recv(r[:rcount], rcount, dtype, root, _COLL_TAG, comm)
+        return
+    s = _flat(sbuf)
+    sends = [(p, s[displs[p]:displs[p] + scounts[p]], scounts[p], dtype) for p in range(n) if p != root]
+    r[:scounts[root]] = s[displs[root]:displs[root] + scounts[root]]
+    _p2p_exchange(sends, [], comm)
+
+
+def Allgatherv(sbuf, scount, dtype, rbuf, rcounts: Sequence[int], displs: Sequence[int], comm=0):
+    m = _m()
+    me, n = m.Comm_rank(comm), m.Comm_size(comm)
+    s, r = _flat(sbuf), _flat(rbuf)
+    r[displs[me]:displs[me] + rcounts[me]] = s[:rcounts[me]]
+    sends = [(p, s[:scount], scount, dtype) for p in range(n) if p != me]
+    recvs = [(p, r[displs[p]:displs[p] + rcounts[p]], rcounts[p], dtype) for p in range(n) if p != me]
+    _p2p_exchange(sends, recvs, comm)
+
+
+def Alltoallv(sbuf, scounts, sdispls, dtype, rbuf, rcounts, rdispls, comm=0):
+    m = _m()
+    me, n = m.Comm_rank(comm), m.Comm_size(comm)
+    s, r = _flat(sbuf), _flat(rbuf)
+    r[rdispls[me]:rdispls[me] + rcounts[me]] = s[sdispls[me]:sdispls[me] + scounts[me]]
+    sends = [(p, s[sdispls[p]:sdispls[p] + scounts[p]], scounts[p], dtype) for p in range(n) if p != me]
+    recvs = [(p, r[rdispls[p]:rdispls[p] + rcounts[p]], rcounts[p], dtype) for p in range(n) if p != me]
+    _p2p_exchange(sends, recvs, comm)
+
+
+def Exscan(sbuf, rbuf, count, dtype, op, comm=0):
+    """Exclusive prefix reduction: rank r gets op(s_0..s_{r-1}); rbuf on rank 0 is left untouched."""
+    m = _m()
+    me, n = m.Comm_rank(comm), m.Comm_size(comm)
+    s = _flat(sbuf)
+    tmp = s.clone() if isinstance(s, torch.Tensor) else s.copy()
+    m.Scan(sbuf, tmp, count, dtype, op, comm)          # inclusive; shift it one rank to the right
+    r = _flat(rbuf)
+    sends = [(me + 1, tmp[:count], count, dtype)] if me + 1 < n else []
+    recvs = [(me - 1, r[:count], count, dtype)] if me > 0 else []
+    _p2p_exchange(sends, recvs, comm)
+
+
+def Reduce_scatter(sbuf, rbuf, rcounts: Sequence[int], dtype, op, comm=0):
+    """General (uneven) reduce-scatter: reduce to rank 0, scatter the pieces."""
+    m = _m()
+    me = m.Comm_rank(comm)
+    total = int(sum(rcounts))
+    s = _flat(sbuf)
+    full = (torch.empty_like(s[:total]) if isinstance(s, torch.Tensor) else np.empty_like(s[:total]))
+    m.Reduce(s[:total], full, total, dtype, op, 0, comm)
+    displs = [int(sum(rcounts[:i])) for i in range(len(rcounts))]
+    Scatterv(full, list(rcounts), displs, dtype, rbuf, rcounts[me], 0, comm)
+
+
+# ---- user reduction operations (Op_create / Op_free) ------------------------------------------------
+_USER_OPS: Dict[int, Tuple[Callable, bool]] = {}
+_USER_OP_BASE = 100
+
+
+def Op_create(fn: Callable, commute: bool = True) -> int:
+    """``fn(invec, inoutvec)`` combines in place into ``inoutvec`` (the MPI_User_function contract)."""
+    h = _USER_OP_BASE + len(_USER_OPS)
+    _USER_OPS[h] = (fn, commute)
+    return h
+
+
+def Op_free(op: int) -> None:
+    if op >= _USER_OP_BASE:
+        _USER_OPS.pop(op, None)
+
+
+def _lxor(invec, inout):
+    inout[:] = ((invec != 0) ^ (inout != 0)).to(inout.dtype) if isinstance(inout, torch.Tensor) else \
+        ((invec != 0) ^ (inout != 0)).astype(inout.dtype)
+
+
+def _bxor(invec, inout):
+    inout ^= invec
+
+
+_USER_OPS[LXOR] = (_lxor, True)      # the two predefined ops the native reducer does not implement
+_USER_OPS[BXOR] = (_bxor, True)
+
+
+def is_user_op(op: int) -> bool:
+    return op in _USER_OPS
+
+
+def reduce_user_op(sbuf, rbuf, count, dtype, op, root, comm, everyone: bool):
+    """Reduce/Allreduce with an Op_create'd operation: gather to the root, fold in rank order, (broadcast)."""
+    m = _m()
+    me, n = m.Comm_rank(comm), m.Comm_size(comm)
+    fn, _ = _USER_OPS[op]
+    s = _flat(sbuf)
+    root_ = 0 if everyone else root
+    gathered = None
+    if me == root_:
+        gathered = torch.empty(n * count, dtype=s.dtype) if isinstance(s, torch.Tensor) else np.empty(n * count, s.dtype)
+    m.Gather(s[:count], count, dtype, gathered, root_, comm)
+    r = _flat(rbuf) if rbuf is not None else None
+    if me == root_:
+        acc = gathered[:count].clone() if isinstance(gathered, torch.Tensor) else gathered[:count].copy()
+        for p in range(1, n):
+            # MPI: inoutvec = invec op inoutvec with invec the lower-ranked operand
+            nxt = gathered[p * count:(p + 1) * count]
+            nxt = nxt.clone() if isinstance(nxt, torch.Tensor) else nxt.copy()
+            fn(acc, nxt)
+            acc = nxt
+        r[:count] = acc
+    if everyone:
+        m.Bcast(r[:count], count, dtype, root_, comm)
+
+
+# ---- groups and communicator construction -----------------------------------------------------------
+class Group:
+    """An ordered set of world ranks (MPI_Group)."""
+
+    def __init__(self, ranks: Sequence[int]):
+        self.ranks = list(ranks)
+
+    def __eq__(self, other):
+        return isinstance(other, Group) and self.ranks == other.ranks
+
+
+GROUP_EMPTY = Group([])
+
+
+def Comm_group(comm=0) -> Group:
+    m = _m()
+    n = m.Comm_size(comm)
+    mine = torch.tensor([m.Comm_rank(m.COMM_WORLD)], dtype=torch.int32)
+    allr = torch.empty(n, dtype=torch.int32)
+    m.Allgather(mine, 1, m.INT, allr, comm)
+    return Group(allr.tolist())
+
+
+def Group_size(g: Group) -> int:
+    return len(g.ranks)
+
+
+def Group_rank(g: Group) -> int:
+    me = _m().Comm_rank(_m().COMM_WORLD)
+    return g.ranks.index(me) if me in g.ranks else _m().UNDEFINED
+
+
+def Group_incl(g: Group, ranks: Sequence[int]) -> Group:
+    return Group([g.ranks[i] for i in ranks])
+
+
+def Group_excl(g: Group, ranks: Sequence[int]) -> Group:
+    drop = set(ranks)
+    return Group([r for i, r in enumerate(g.ranks) if i not in drop])
+
+
+def Group_union(a: Group, b: Group) -> Group:
+    return Group(a.ranks + [r for r in b.ranks if r not in a.ranks])
+
+
+def Group_intersection(a: Group, b: Group) -> Group:
+    return Group([r for r in a.ranks if r in b.ranks])
+
+
+def Group_difference(a: Group, b: Group) -> Group:
+    return Group([r for r in a.ranks if r not in b.ranks])
+
+
+def Group_translate_ranks(a: Group, ranks: Sequence[int], b: Group) -> List[int]:
+    und = _m().UNDEFINED
+    return [b.ranks.index(a.ranks[i]) if a.ranks[i] in b.ranks else und for i in ranks]
+
+
+def Group_compare(a: Group, b: Group) -> int:
+    if a.ranks == b.ranks:
+        return IDENT
+    return SIMILAR if sorted(a.ranks) == sorted(b.ranks) else UNEQUAL
+
+
+def Group_free(g: Group) -> None:
+    g.ranks = []
+
+
+def Comm_create(comm, group: Group) -> int:
+    """Collective over ``comm``: the new communicator holds ``group`` in its order; others get COMM_NULL."""
+    m = _m()
+    me = m.Comm_rank(m.COMM_WORLD)
+    if me in group.ranks:
+        return m.Comm_split(comm, 0, group.ranks.index(me))
+    return m.Comm_split(comm, m.UNDEFINED, 0)
+
+
+def Comm_compare(c1, c2) -> int:
+    if c1 == c2:
+        return IDENT
+    g = Group_compare(Comm_group(c1), Comm_group(c2))
+    return CONGRUENT if g == IDENT else g
+
+
+def Comm_test_inter(comm) -> bool:
+    return False
+
+
+_COMM_NAMES: Dict[int, str] = {0: "MPI_COMM_WORLD", 1: "MPI_COMM_SELF"}
+
+
+def Comm_set_name(comm, name: str) -> None:
+    _COMM_NAMES[comm] = name[:MAX_OBJECT_NAME]
+
+
+def Comm_get_name(comm) -> str:
+    return _COMM_NAMES.get(comm, "")
+
+
+# ---- one-sided communication with fence synchronisation (host memory) -------------------------------
+class Win:
+    """``MPI_Win_create`` over a host tensor.  Put / Get / Accumulate are queued at the origin and performed at the
+    next :func:`Win_fence`, which is when MPI guarantees them complete under active-target synchronisation
+    (/root/reference/mpifuncs.c:2337,1656,1131,9,2367).  Passive target (Win_lock) needs a participant on the target
+    side with two-sided transport; it exists natively on the device path: :class:`mpit_b200.parallel.DeviceWindow`."""
+
+    def __init__(self, base, disp_unit: int, comm: int):
+        self.base = _flat(base)
+        self.disp_unit, self.comm = disp_unit, comm
+        self.ops: List[tuple] = []
+
+
+def Win_create(base, size_bytes: int, disp_unit: int, info=None, comm=0) -> Win:
+    return Win(base, disp_unit, comm)
+
+
+def Put(origin, count, dtype, target_rank, target_disp, win: Win):
+    o = _flat(origin)[:count]
+    win.ops.append(("put", target_rank, target_disp, count, dtype, o.clone() if isinstance(o, torch.Tensor) else o.copy(), None))
+
+
+def Accumulate(origin, count, dtype, target_rank, target_disp, op, win: Win):
+    o = _flat(origin)[:count]
+    win.ops.append(("acc", target_rank, target_disp, count, dtype, o.clone() if isinstance(o, torch.Tensor) else o.copy(), op))
+
+
+def Get(origin, count, dtype, target_rank, target_disp, win: Win):
+    win.ops.append(("get", target_rank, target_disp, count, dtype, _flat(origin), None))
+
+
+def _apply_op(dst, src, op):
+    m = _m()
+    if op == m.SUM:
+        dst += src
+    elif op == m.PROD:
+        dst *= src
+    elif op == m.MAX:
+        dst[:] = torch.maximum(dst, src) if isinstance(dst, torch.Tensor) else np.maximum(dst, src)
+    elif op == m.MIN:
+        dst[:] = torch.minimum(dst, src) if isinstance(dst, torch.Tensor) else np.minimum(dst, src)
+    elif is_user_op(op):
+        fn, _ = _USER_OPS[op]
+        tmp = dst.clone() if isinstance(dst, torch.Tensor) else dst.copy()
+        fn(src, tmp)
+        dst[:] = tmp
+    else:
+        raise _m().MPIError(ERR_OP, "Accumulate")
+
+
+def Win_fence(assertion: int, win: Win) -> None:
+    """Close the access/exposure epoch: exchange the queued operations and apply them at their targets."""
+    m = _m()
+    comm = win.comm
+    me, n = m.Comm_rank(comm), m.Comm_size(comm)
+    # 1. everybody learns how many descriptors it will receive from everybody
+    out_cnt = torch.zeros(n, dtype=torch.int64)
+    for op in win.ops:
+        out_cnt[op[1]] += 1
+    in_cnt = torch.zeros(n, dtype=torch.int64)
+    m.Alltoall(out_cnt, 1, m.LONG, in_cnt, comm)
+    # 2. descriptors {kind, disp, count, dtype, op} then payloads, pairwise and in issue order
+    kinds = {"put": 0, "acc": 1, "get": 2}
+    local = [op for op in win.ops if op[1] == me]
+    req = m.Request(1)
+    for peer in range(n):
+        if peer == me:
+            continue
+        mine = [op for op in win.ops if op[1] == peer]
+        desc = torch.tensor([[kinds[o[0]], o[2], o[3], o[4], -1 if o[6] is None else o[6]] for o in mine],
+                            dtype=torch.int64).reshape(-1)
+        theirs = torch.empty(int(in_cnt[peer]) * 5, dtype=torch.int64)
+        m.Irecv(theirs, theirs.numel(), m.LONG, peer, _COLL_TAG + 1, comm, req)
+        m.Send(desc, desc.numel(), m.LONG, peer, _COLL_TAG + 1, comm)
+        m.Wait(req)
+        def serve_theirs():
+            t = theirs.view(-1, 5).tolist()
+            for kind, disp, cnt, dt, op in t:
+                if kind == 2:
+                    continue
+                tmp = torch.empty(cnt, dtype=win.base.dtype) if isinstance(win.base, torch.Tensor) else np.empty(cnt, win.base.dtype)
+                m.Recv(tmp, cnt, dt, peer, _COLL_TAG + 2, comm)
+                if kind == 0:
+                    win.base[disp:disp + cnt] = tmp
+                else:
+                    _apply_op(win.base[disp:disp + cnt], tmp, op)
+            for kind, disp, cnt, dt, op in t:
+                if kind == 2:
+                    m.Send(win.base[disp:disp + cnt], cnt, dt, peer, _COLL_TAG + 3, comm)
+
+        # puts/accumulates travel eagerly (the native Send returns once the progress thread owns the message), so
+        # both sides can send first; gets are served after the peer's puts, which makes a Get that follows a Put to
+        # the same location inside one epoch well defined here
+        for o in mine:
+            if o[0] != "get":
+                m.Send(o[5], o[3], o[4], peer, _COLL_TAG + 2, comm)
+        serve_theirs()
+        for o in mine:
+            if o[0] == "get":
+                m.Recv(o[5][:o[3]], o[3], o[4], peer, _COLL_TAG + 3, comm)
+    # 3. operations that target myself
+    for kind, _, disp, cnt, dt, data, op in local:
+        if kind == "put":
+            win.base[disp:disp + cnt] = data
+        elif kind == "acc":
+            _apply_op(win.base[disp:disp + cnt], data, op)
+        else:
+            data[:cnt] = win.base[disp:disp + cnt]
+    win.ops = []
+    m.Barrier(comm)
+
+
+def Win_free(win: Win) -> None:
+    win.ops = []
+    win.base = None
+
+
+def Win_lock(lock_type, rank, assertion, win: Win):
+    raise _m().MPIError(ERR_RMA_SYNC, "Win_lock (passive target is provided by mpit_b200.parallel.DeviceWindow; host "
+                                      "windows synchronise with Win_fence)")
+
+
+Win_unlock = Win_lock
+
+
+__all__ = [n for n in dir() if n[0].isupper() and n not in ("Callable", "Dict", "List", "Optional", "Sequence", "Tuple")]

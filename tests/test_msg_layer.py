@@ -75,3 +75,10 @@ def test_ps_single_mode_writer_reader():
 
 def test_ptest_bandwidth():
     _run("ptest", 4)
+
+
+@pytest.mark.parametrize("case,nproc", [("x_vector_collectives", 4), ("x_requests", 3), ("x_groups_ops", 4),
+                                        ("x_window", 3)])
+def test_wider_mpi_surface(case, nproc):
+    """Send modes, persistent requests, vector collectives, groups / user ops, fence windows (msg/extras.py)."""
+    _run(case, nproc)
