@@ -42,3 +42,8 @@ def test_testreduceall_cpu():
 def test_ptest2_stragglers():
     assert launch(4, ["mpit_b200.launch.ptest2", "--ssize", "4096", "--rounds", "2", "--skew-size", "16"], module=True,
                   timeout=120) == 0
+
+
+def test_ring_smoke_script():
+    """/root/reference/test.lua: one float around the ring."""
+    assert launch(3, ["mpit_b200.launch.test"], module=True, timeout=60) == 0
