@@ -75,16 +75,56 @@ class ConfusionMatrix:
         return "\n".join(rows)
 
 
+def _nvtx():
+    """torch.cuda.nvtx when a CUDA runtime is present and tracing is wanted (MPIT_NVTX=1), else None."""
+    if os.environ.get("MPIT_NVTX", "0") != "1":
+        return None
+    try:
+        import torch
+        return torch.cuda.nvtx if torch.cuda.is_available() else None
+    except Exception:       # pragma: no cover
+        return None
+
+
 class Timers(dict):
-    """Accumulating wall-clock buckets (``tm.feval``, ``tm.sync``, ...; goot.lua:24-26, bicnn.lua:17-28)."""
+    """Accumulating wall-clock buckets (``tm.feval``, ``tm.sync``, ...; goot.lua:24-26, bicnn.lua:17-28).
+
+    With ``MPIT_NVTX=1`` every bucket is also an NVTX range, so the same compute / sync / transfer split shows up
+    on an Nsight timeline.  ``device=True`` buckets are timed with CUDA events on the current stream instead of the
+    host clock (resolved lazily by :meth:`resolve`, so that timing never synchronises the step)."""
+
+    def __init__(self, *a, **kw):
+        super().__init__(*a, **kw)
+        self._pending = []
 
     @contextmanager
-    def __call__(self, name: str):
+    def __call__(self, name: str, device: bool = False):
+        nv = _nvtx()
+        if nv is not None:
+            nv.range_push(name)
+        if device:
+            import torch
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
         t0 = time.perf_counter()
         try:
             yield
         finally:
-            self[name] = self.get(name, 0.0) + time.perf_counter() - t0
+            if device:
+                e1.record()
+                self._pending.append((name, e0, e1))
+            else:
+                self[name] = self.get(name, 0.0) + time.perf_counter() - t0
+            if nv is not None:
+                nv.range_pop()
+
+    def resolve(self) -> "Timers":
+        """Fold finished device-timed ranges into their buckets (seconds).  Synchronises on their end events."""
+        for name, e0, e1 in self._pending:
+            e1.synchronize()
+            self[name] = self.get(name, 0.0) + e0.elapsed_time(e1) / 1e3
+        self._pending = []
+        return self
 
 
 def progress(i: int, n: int, every: int = 0, stream=sys.stderr) -> None:

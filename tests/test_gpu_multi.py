@@ -51,3 +51,13 @@ def test_one_sided_window():
     n = min(torch.cuda.device_count(), 8)
     out = _torchrun(["window"], n)
     assert "case window: ok" in out
+
+
+def test_ring_smoke_script_on_device():
+    """/root/reference/test.lua over the NVLink mailbox (one float around the ring of GPUs)."""
+    n = min(torch.cuda.device_count(), 8)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr",
+           "127.0.0.1", "--master-port", "29534", "-m", "mpit_b200.launch.test", "--device", "cuda"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=os.path.dirname(HERE))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "after: rbuf" in r.stdout
