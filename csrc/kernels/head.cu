@@ -56,9 +56,25 @@ __global__ void __launch_bounds__(kHeadWarps * 32) classifier_head_kernel(HeadAr
   if (a.rng_inc && blockIdx.x == 0 && threadIdx.x == 0) a.rng_inc[1] += 1ull;   // dropout step counter lives on the device
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, nw = blockDim.x >> 5;
   const bool train = a.dlogits != nullptr;
-  for (int i = threadIdx.x; i < NC * a.K; i += blockDim.x) ws[i] = i < a.ncls * a.K ? a.w[i] : 0.f;
+  // W is fetched into registers now (16-byte loads; K % 32 == 0 and w is 16-byte aligned) and only parked in shared
+  // memory after the first rows' x loads have been issued, so both global-load latencies overlap
+  constexpr int WV = NC * KPL * 32 / (kHeadWarps * 32 * 4) > 0 ? NC * KPL * 32 / (kHeadWarps * 32 * 4) : 1;
+  float4 wreg[WV];
+#pragma unroll
+  for (int u = 0; u < WV; ++u) {
+    const int i = (u * kHeadWarps * 32 + threadIdx.x) * 4;
+    wreg[u] = (i < a.ncls * a.K) ? ld4(a.w + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  auto park_w = [&]() {
+#pragma unroll
+    for (int u = 0; u < WV; ++u) {
+      const int i = (u * kHeadWarps * 32 + threadIdx.x) * 4;
+      if (i < NC * a.K) *reinterpret_cast<float4*>(ws + i) = wreg[u];
+    }
+    __syncthreads();
+  };
   const float bz = (a.bias && lane < a.ncls) ? a.bias[lane] : 0.f;
-  __syncthreads();
+  bool w_ready = false;
 
   float lsum = 0.f, bsum = 0.f;
   float csum[KPL];
@@ -76,6 +92,7 @@ __global__ void __launch_bounds__(kHeadWarps * 32) classifier_head_kernel(HeadAr
 #pragma unroll
       for (int j = 0; j < KPL; ++j) xv[q][j] = r < a.B ? a.x[(size_t)r * a.K + lane + 32 * j] : 0.f;
     }
+    if (!w_ready) { park_w(); w_ready = true; }            // warp-uniform: r0 depends on the warp only
 #pragma unroll
     for (int q = 0; q < kHeadRows; ++q) {
       const int r = r0 + q * rstride;
@@ -135,6 +152,7 @@ __global__ void __launch_bounds__(kHeadWarps * 32) classifier_head_kernel(HeadAr
       }
     }
   }
+  if (!w_ready) park_w();                                  // warps that had no row still owe their part of W
   // ---- fixed-order reduction: warps of this CTA -> one partial row; last CTA (ticket) -> results ----
   if (lane == 0) lpart[wib] = lsum;
   bpart[wib][lane] = bsum;
@@ -195,6 +213,7 @@ extern "C" int mpit_classifier_head(const float* x, const float* w, const float*
                                     float* db_in, unsigned long long* rng_inc, float* scratch, int B, int K, int ncls,
                                     int ld, float gscale, float in_scale, int accumulate, void* stream) {
   if (!x || !w || !labels || !logits || !loss_sum || !scratch) return MPIT_E_ARG;
+  if ((uintptr_t)w & 15) return MPIT_E_ARG;
   if (B < 1 || ncls < 1 || ncls > 32 || ld < ncls || ld > 32 || K % 32 != 0) return MPIT_E_ARG;
   if ((dx || db_in || db_cls) && !dlogits) return MPIT_E_ARG;
   const int kpl = K / 32;

@@ -119,6 +119,25 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
 
   long long* dbg = p.dbg ? p.dbg + 16 * (blockIdx.y * gridDim.x + blockIdx.x) : nullptr;
   pdl_trigger();   // let the next kernel of the step begin its own set-up now
+  // Everything that depends on the kernel parameters only -- tile origins (integer divisions), each producer's
+  // first pipeline slot and tap -- is computed here, BEFORE the wait on the previous kernel, so that under
+  // programmatic dependent launch it costs nothing (it used to be ~0.4 us between the wait and the first load).
+  int org_n[2], org_h[2], org_w[2];
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    org_n[j] = org_h[j] = org_w[j] = 0;
+    if (j < p.nsub) subtile_origin(p, tile * p.nsub + j, org_n[j], org_h[j], org_w[j]);
+  }
+  const int kProducers = kStages < 5 ? kStages : 5;
+  const int pi = warp == 0 ? 0 : warp - 1;          // warps 0,2,3,4,5 -> 0,1,2,3,4 (warp 1 issues the MMAs)
+  int stage = 0, phase = 0, kh = 0, kw = 0, cblk = 0;
+  auto advance = [&](int by) {
+    stage += by;
+    while (stage >= kStages) { stage -= kStages; phase ^= 1; }
+    cblk += by;
+    while (cblk >= p.cb) { cblk -= p.cb; if (++kw == p.kw_it) { kw = 0; ++kh; } }
+  };
+  if (warp != 1) advance(pi);
   if (dbg && threadIdx.x == 0) dbg[0] = clock64();
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmap_a);
@@ -149,27 +168,22 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
   // Never more producers than stages: a producer that has passed its wait for k-block kb knows k-block
   // kb - kStages is consumed; its next one (kb + NP) needs kb + NP - 2*kStages consumed for the parity test
   // to be unambiguous, which in-order consumption guarantees iff NP <= kStages.
-  const int kProducers = kStages < 5 ? kStages : 5;
-  const int pi = warp == 0 ? 0 : warp - 1;          // warps 0,2,3,4,5 -> 0,1,2,3,4 (warp 1 issues the MMAs)
   if (warp != 1 && pi < kProducers && elect_one()) {
     int n0[2], oh0[2], ow0[2];
-    for (int j = 0; j < p.nsub; ++j) {
-      subtile_origin(p, tile * p.nsub + j, n0[j], oh0[j], ow0[j]);
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      n0[j] = org_n[j]; oh0[j] = org_h[j]; ow0[j] = org_w[j];
       // (in MAXTIME mode `crop` carries per-sentence frame counts for the epilogue, not offsets)
-      if (p.crop && MODE != EPI_MAXTIME && n0[j] < p.B) { oh0[j] += p.crop[2 * n0[j]]; ow0[j] += p.crop[2 * n0[j] + 1]; }
+      if (j < p.nsub && p.crop && MODE != EPI_MAXTIME && n0[j] < p.B) {
+        oh0[j] += p.crop[2 * n0[j]];
+        ow0[j] += p.crop[2 * n0[j] + 1];
+      }
     }
     const int sub_bytes = rows_per_sub * 128;
-    int stage = 0, phase = 0, kh = 0, kw = 0, cblk = 0;
-    auto advance = [&](int by) {
-      stage += by;
-      while (stage >= kStages) { stage -= kStages; phase ^= 1; }
-      cblk += by;
-      while (cblk >= p.cb) { cblk -= p.cb; if (++kw == p.kw_it) { kw = 0; ++kh; } }
-    };
-    advance(pi);
     if (dbg && warp == 0) dbg[8] = clock64();   // producer set-up done
     for (int kb = pi; kb < p.num_kb; kb += kProducers) {
-      if (!mbar_wait(&empty_bar[stage], phase ^ 1)) { if (p.err) *p.err = 1; break; }
+      // the first pass over the ring needs no wait: those slots have never been used
+      if (kb >= kStages && !mbar_wait(&empty_bar[stage], phase ^ 1)) { if (p.err) *p.err = 1; break; }
       if (dbg && kb == 0) dbg[9] = clock64();   // first slot free
       uint8_t* a_dst = smem + stage * L::kStageBytes;
       mbar_expect_tx(&full_bar[stage], L::kStageBytes);
@@ -213,8 +227,7 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
     const int quad = warp & 3;
     const int row = quad * 32 + lane;
     const int j = row / rows_per_sub, rr = row - j * rows_per_sub;
-    int n0, oh0, ow0;
-    subtile_origin(p, tile * p.nsub + j, n0, oh0, ow0);
+    const int n0 = org_n[j], oh0 = org_h[j], ow0 = org_w[j];
     const int w_ = rr % p.tw, h_ = (rr / p.tw) % p.th, nn = rr / (p.tw * p.th);
     const int n = n0 + nn, oh = oh0 + h_, ow = ow0 + w_;
     const bool valid = n < p.B && oh < p.OH && ow < p.OW;

@@ -77,6 +77,15 @@ umma_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
   if (nchunks > 4) nchunks = 4;
 
   pdl_trigger();
+  // parameter-only producer set-up (integer divisions) goes BEFORE the wait on the previous kernel
+  const int pj = warp == 0 ? 0 : warp - 1;     // issuing threads: warps 0,2,3,4 -> 0,1,2,3
+  const int per_kh = p.kw_it * p.cb;
+  const int ch = m_tile * 4 + pj;
+  const int ckh = ch / per_kh, rch = ch - ckh * per_kh;
+  const int ckw = rch / p.cb, cc0 = (rch - ckw * p.cb) * 32;
+  const int per_img = p.tiles_w * p.tiles_h;
+  const int grp0 = kb_lo / per_img, r_img = kb_lo - grp0 * per_img;
+  const int th0 = r_img / p.tiles_w, tw0 = r_img - th0 * p.tiles_w;
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmap_x);
     prefetch_tmap(&tmap_dz);
@@ -97,19 +106,11 @@ umma_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
   // The loads are dealt to four issuing threads -- the elected lanes of warp 0 and of epilogue warps 2,3,4:
   // producer j issues A chunk j and B chunk j of EVERY k-block, producer 0 also posts the expect_tx.  Each
   // producer walks the k-blocks in order, so the empty-barrier parity test stays unambiguous.
-  const int pj = warp == 0 ? 0 : warp - 1;     // warps 0,2,3,4 -> 0,1,2,3
   const bool has_a = pj < nchunks, has_b = pj < BLOCK_N / 32;
   if (warp != 1 && pj < 4 && (has_a || has_b || pj == 0) && elect_one()) {
-    // decode this producer's M chunk once
-    const int per_kh = p.kw_it * p.cb;
-    const int ch = m_tile * 4 + pj;
-    const int ckh = ch / per_kh, rch = ch - ckh * per_kh;
-    const int ckw = rch / p.cb, cc0 = (rch - ckw * p.cb) * 32;
     const uint32_t bytes = (uint32_t)(nchunks * kChunkBytes + L::kBBytes);
-    const int per_img = p.tiles_w * p.tiles_h;
     // k-block -> (image group, tile row, tile column), kept incrementally
-    int grp = kb_lo / per_img, r = kb_lo - grp * per_img;
-    int th_i = r / p.tiles_w, tw_i = r - th_i * p.tiles_w;
+    int grp = grp0, th_i = th0, tw_i = tw0;
     int y0 = 0, x0 = 0;
     if (p.crop && has_a && grp * p.tn < p.B) { y0 = p.crop[2 * grp * p.tn]; x0 = p.crop[2 * grp * p.tn + 1]; }
     int stage = 0, phase = 0;
@@ -122,7 +123,7 @@ umma_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
       if (p.crop && has_a && ngrp != grp && kb + 1 < kb_hi && ngrp * p.tn < p.B) {
         ny0 = p.crop[2 * ngrp * p.tn]; nx0 = p.crop[2 * ngrp * p.tn + 1];
       }
-      if (!mbar_wait(&empty_bar[stage], phase ^ 1)) { if (p.err) *p.err = 11; break; }
+      if (kb - kb_lo >= kWStages && !mbar_wait(&empty_bar[stage], phase ^ 1)) { if (p.err) *p.err = 11; break; }
       uint8_t* a_dst = smem + stage * L::kStageBytes;
       if (pj == 0) mbar_expect_tx(&full_bar[stage], bytes);
       if (has_a)
