@@ -509,11 +509,19 @@ static int launch_igemm(const CUtensorMap* ta, const CUtensorMap* tb, IgemmParam
     attr_done = true;
   }
   dim3 grid(m_tiles, p.N / BLOCK_N);
-  // Pipeline depth: deep (latency hiding) when the grid leaves SMs to spare or k-loops are long;
-  // 4 stages when many short CTAs should co-reside two per SM.
+  // Pipeline depth.  Grids of up to one CTA per SM get the deepest pipeline that fits.  Larger grids are better
+  // served by residency: make the stages small enough that ceil(ctas/148) CTAs (up to 4) share an SM, so the whole
+  // grid is one wave and one CTA's epilogue overlaps another's loads (conv1: 576 short CTAs, 2 stages each).
   int ctas = m_tiles * (p.N / BLOCK_N);
-  int stages = (ctas > 2 * MPIT_NUM_SMS && p.num_kb <= 8) ? 4 : L::kMaxFit;
-  if (stages > p.num_kb) stages = p.num_kb < 2 ? 2 : p.num_kb;
+  int stages = L::kMaxFit;
+  if (ctas > MPIT_NUM_SMS) {
+    int per_sm = (ctas + MPIT_NUM_SMS - 1) / MPIT_NUM_SMS;
+    if (per_sm > 4) per_sm = 4;
+    int fit = ((226 * 1024) / per_sm - 2560) / L::kStageBytes;
+    if (fit < stages) stages = fit;
+  }
+  if (stages > p.num_kb) stages = p.num_kb;
+  if (stages < 2) stages = 2;
   if (stages > L::kMaxFit) stages = L::kMaxFit;
   p.stages = stages;
   MPIT_CUDA_TRY(launch_k(umma_igemm_kernel<BLOCK_N, MODE>, grid, dim3(192), (size_t)L::total(stages), st, *ta, *tb, p));
