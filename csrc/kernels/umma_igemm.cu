@@ -92,6 +92,165 @@ __device__ __forceinline__ void subtile_origin(const IgemmParams& p, int s, int&
   ow0 = tw_i * p.tw;
 }
 
+// Epilogue of one 128-row accumulator tile for the modes that store row-major tiles (STORE / MASK / EXPAND); shared
+// by the streaming kernel below and the resident-input kernel (umma_resident.cu).  Called by the four epilogue
+// warps.  (n, oh, ow, valid) describe the output row of this THREAD (TMEM lane); `tile` indexes the colpart row.
+// `wait_acc`: wait for `tmem_full` (phase 0) after the side inputs have been requested.
+template <int BLOCK_N, int MODE>
+__device__ __forceinline__ void coalesced_epilogue(const IgemmParams& p, uint8_t* smem, const uint32_t tmem_base,
+                                                   uint64_t* tmem_full, const bool wait_acc, const int quad, const int lane,
+                                                   const int row, const int n, const int oh, const int ow, const bool valid,
+                                                   const int n_tile0, const int tile, const unsigned long long seed,
+                                                   const unsigned long long step, const float* bias_s, long long* dbg) {
+  // ---- coalesced epilogue (STORE / MASK / EXPAND) ----
+  // TMEM hands every lane one output ROW (32 columns = 128 B).  Storing (or loading the side inputs) in
+  // that arrangement touches 32 different 128-byte lines per warp instruction -- measured 5.4 us for the
+  // un-pooling epilogue of one 128x64 tile.  So each 32x32 block is transposed through a warp-private,
+  // XOR-swizzled 4 KB tile in (by now idle) pipeline memory: afterwards 8 adjacent lanes cover one
+  // 128-byte row segment and a warp instruction touches 4 full lines.
+  __shared__ long long rowoff_s[128];   // element offset of each tile row's output row, -1 = out of range
+  __shared__ long long rowdst_s[128];   // EXPAND: offset of the 2x2 window's top-left pixel
+  __shared__ __align__(16) float colsum_s[2 * 128];
+  const size_t row_base = (((size_t)n * p.OH + oh) * p.OW + ow) * p.N + n_tile0;
+  rowoff_s[row] = valid ? (long long)row_base : -1;
+  if (MODE == EPI_EXPAND)
+    rowdst_s[row] = (long long)((((size_t)n * (2 * p.OH) + 2 * oh) * (2 * p.OW) + 2 * ow) * p.N + n_tile0);
+  __syncwarp();
+  const int sub = lane >> 3, ch = lane & 7;   // row within a group of 4, 16-byte chunk within the row
+  long long off[8], dst[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    off[i] = rowoff_s[quad * 32 + i * 4 + sub];
+    dst[i] = MODE == EPI_EXPAND ? rowdst_s[quad * 32 + i * 4 + sub] : 0;
+  }
+  // side inputs (stored activation, pool index) are fetched BEFORE the accumulator is waited for
+  float4 ax[8];
+  uint32_t ai[8];
+  auto fetch_side = [&](int c0) {
+    if (MODE == EPI_STORE) return;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      if (off[i] < 0) continue;
+      ax[i] = ld4(p.aux + off[i] + c0 + 4 * ch);
+      if (MODE == EPI_EXPAND) ai[i] = *reinterpret_cast<const uint32_t*>(p.aux_idx + off[i] + c0 + 4 * ch);
+    }
+  };
+  fetch_side(0);
+  // touch the output rows now: the first access of an SM to a page costs ~1 us (translation miss), which
+  // otherwise lands on the critical path between "accumulator ready" and the first store
+  if (off[0] >= 0) {
+    const float* o0 = MODE == EPI_EXPAND ? p.out + (size_t)dst[0] : p.out + (size_t)off[0];
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(o0 + 4 * ch));
+  }
+  if (wait_acc) {
+    if (!mbar_wait(tmem_full, 0)) { if (p.err) *p.err = 3; }
+    if (dbg && threadIdx.x == 64) dbg[5] = clock64();   // accumulator ready
+    tc_fence_after();
+    asm volatile("bar.sync 1, 128;" ::: "memory");      // bias_s written by all four epilogue warps
+  }
+  const uint32_t xpose = smem_u32(smem) + quad * 4096;   // stage 0 is idle: every MMA has completed
+  const size_t up = (size_t)2 * p.OW * p.N;                      // EXPAND: one image row down
+#pragma unroll 1
+  for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+    float v[32];
+    if (c0) fetch_side(c0);
+    tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
+    if (dbg && threadIdx.x == 64 && c0 == 0) dbg[11] = clock64();   // first TMEM read done
+#pragma unroll
+    for (int c4 = 0; c4 < 8; ++c4)
+      sts4(xpose + (lane * 8 + (c4 ^ (lane & 7))) * 16, v[4 * c4], v[4 * c4 + 1], v[4 * c4 + 2], v[4 * c4 + 3]);
+    __syncwarp();
+    float4 xs[8];     // all eight reads first: explicit shared-space loads, nothing for them to alias with
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int r = i * 4 + sub;
+      xs[i] = lds4(xpose + (r * 8 + (ch ^ (r & 7))) * 16);
+    }
+    if (dbg && threadIdx.x == 64 && c0 == 0) dbg[12] = clock64();   // first block transposed
+    const float4 b4 = *reinterpret_cast<const float4*>(&bias_s[c0 + 4 * ch]);
+    float4 csum = make_float4(0.f, 0.f, 0.f, 0.f);   // this lane's 4 columns, summed over its 8 rows
+    uint32_t keep = 0;
+    if (MODE == EPI_STORE && p.dropout) {
+      auto gi = [&](int i) { return (unsigned long long)(((size_t)off[i] + c0 + 4 * ch) >> 2); };
+      keep = keep4_ool(seed, (uint32_t)step, gi(0), gi(1), gi(2), gi(3)) |
+             (keep4_ool(seed, (uint32_t)step, gi(4), gi(5), gi(6), gi(7)) << 16);
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      float4 x = xs[i];
+      if (off[i] < 0) continue;
+      const size_t e0 = (size_t)off[i] + c0 + 4 * ch;
+      if (MODE == EPI_STORE) {
+        x.x += b4.x; x.y += b4.y; x.z += b4.z; x.w += b4.w;
+        if (p.relu == 1) {
+          x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
+        } else if (p.relu == 2) {
+          x = tanh4_ool(x);
+        }
+        if (p.dropout) {
+          const uint32_t kb = keep >> (4 * i);
+          x.x = (kb & 1u) ? x.x * 2.f : 0.f;
+          x.y = (kb & 2u) ? x.y * 2.f : 0.f;
+          x.z = (kb & 4u) ? x.z * 2.f : 0.f;
+          x.w = (kb & 8u) ? x.w * 2.f : 0.f;
+        }
+        st4(p.out + e0, x);
+      } else if (MODE == EPI_MASK) {
+        const float4 h = ax[i];
+        float4 o;
+        if (p.relu == 2) {   // d tanh: g * (1 - h^2)
+          o.x = x.x * (1.f - h.x * h.x) * p.scale;
+          o.y = x.y * (1.f - h.y * h.y) * p.scale;
+          o.z = x.z * (1.f - h.z * h.z) * p.scale;
+          o.w = x.w * (1.f - h.w * h.w) * p.scale;
+        } else {
+          o.x = h.x > 0.f ? x.x * p.scale : 0.f;
+          o.y = h.y > 0.f ? x.y * p.scale : 0.f;
+          o.z = h.z > 0.f ? x.z * p.scale : 0.f;
+          o.w = h.w > 0.f ? x.w * p.scale : 0.f;
+        }
+        st4(p.out + e0, o);
+        csum.x += o.x; csum.y += o.y; csum.z += o.z; csum.w += o.w;
+      } else {  // EPI_EXPAND: un-pool + ReLU mask; tile rows are pooled positions
+        const float4 h = ax[i];
+        const uint32_t bsel = ai[i];   // four arg-max codes (0..3), one byte per column
+        float* d0 = p.out + (size_t)dst[i] + c0 + 4 * ch;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          float4 o;
+          o.x = ((bsel & 0xffu) == (uint32_t)q && h.x > 0.f) ? x.x * p.scale : 0.f;
+          o.y = (((bsel >> 8) & 0xffu) == (uint32_t)q && h.y > 0.f) ? x.y * p.scale : 0.f;
+          o.z = (((bsel >> 16) & 0xffu) == (uint32_t)q && h.z > 0.f) ? x.z * p.scale : 0.f;
+          o.w = ((bsel >> 24) == (uint32_t)q && h.w > 0.f) ? x.w * p.scale : 0.f;
+          st4(d0 + (q >> 1) * up + (q & 1) * p.N, o);
+        }
+        // exactly one of the four window positions receives the gradient (when the unit was active)
+        csum.x += h.x > 0.f ? x.x * p.scale : 0.f;
+        csum.y += h.y > 0.f ? x.y * p.scale : 0.f;
+        csum.z += h.z > 0.f ? x.z * p.scale : 0.f;
+        csum.w += h.w > 0.f ? x.w * p.scale : 0.f;
+      }
+    }
+    if ((MODE == EPI_MASK || MODE == EPI_EXPAND) && p.colpart) {
+      // Bias gradient of the layer below = column sums of what was just written.  Fixed-order reduction:
+      // 8 rows in registers, 4 row groups by shuffle, 4 warps through shared memory -> one partial row per
+      // tile, summed over tiles by the split-K reduce kernel.  No atomics, no zeroing, and the 19 MB
+      // gradient tensor is not read again by a separate column-sum kernel.
+      csum.x += __shfl_xor_sync(0xffffffffu, csum.x, 8);  csum.y += __shfl_xor_sync(0xffffffffu, csum.y, 8);
+      csum.z += __shfl_xor_sync(0xffffffffu, csum.z, 8);  csum.w += __shfl_xor_sync(0xffffffffu, csum.w, 8);
+      csum.x += __shfl_xor_sync(0xffffffffu, csum.x, 16); csum.y += __shfl_xor_sync(0xffffffffu, csum.y, 16);
+      csum.z += __shfl_xor_sync(0xffffffffu, csum.z, 16); csum.w += __shfl_xor_sync(0xffffffffu, csum.w, 16);
+      float* cs = colsum_s + ((c0 >> 5) & 1) * 128;      // double-buffered by iteration parity
+      if (sub == 0) *reinterpret_cast<float4*>(cs + quad * 32 + 4 * ch) = csum;
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (quad == 0)
+        p.colpart[(size_t)tile * p.N + n_tile0 + c0 + lane] = (cs[lane] + cs[32 + lane]) + (cs[64 + lane] + cs[96 + lane]);
+    }
+    if (dbg && threadIdx.x == 64 && c0 == 0) dbg[13] = clock64();   // first iteration's stores issued
+    __syncwarp();
+  }
+}
+
 // Body shared by the plain kernel and the pull-fused kernel.  `tmap_a_p`/`tmap_b_p` point into
 // kernel-parameter space; `b_row0` is the row coordinate of this CTA's B tile inside *its* tensor map
 // (equal to the output column offset unless B lives in a peer's shard).
@@ -301,151 +460,8 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
         }
       }
     } else {
-      // ---- coalesced epilogue (STORE / MASK / EXPAND) ----
-      // TMEM hands every lane one output ROW (32 columns = 128 B).  Storing (or loading the side inputs) in
-      // that arrangement touches 32 different 128-byte lines per warp instruction -- measured 5.4 us for the
-      // un-pooling epilogue of one 128x64 tile.  So each 32x32 block is transposed through a warp-private,
-      // XOR-swizzled 4 KB tile in (by now idle) pipeline memory: afterwards 8 adjacent lanes cover one
-      // 128-byte row segment and a warp instruction touches 4 full lines.
-      __shared__ long long rowoff_s[128];   // element offset of each tile row's output row, -1 = out of range
-      __shared__ long long rowdst_s[128];   // EXPAND: offset of the 2x2 window's top-left pixel
-      __shared__ __align__(16) float colsum_s[2 * 128];
-      const size_t row_base = (((size_t)n * p.OH + oh) * p.OW + ow) * p.N + n_tile0;
-      rowoff_s[row] = valid ? (long long)row_base : -1;
-      if (MODE == EPI_EXPAND)
-        rowdst_s[row] = (long long)((((size_t)n * (2 * p.OH) + 2 * oh) * (2 * p.OW) + 2 * ow) * p.N + n_tile0);
-      __syncwarp();
-      const int sub = lane >> 3, ch = lane & 7;   // row within a group of 4, 16-byte chunk within the row
-      long long off[8], dst[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        off[i] = rowoff_s[quad * 32 + i * 4 + sub];
-        dst[i] = MODE == EPI_EXPAND ? rowdst_s[quad * 32 + i * 4 + sub] : 0;
-      }
-      // side inputs (stored activation, pool index) are fetched BEFORE the accumulator is waited for
-      float4 ax[8];
-      uint32_t ai[8];
-      auto fetch_side = [&](int c0) {
-        if (MODE == EPI_STORE) return;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          if (off[i] < 0) continue;
-          ax[i] = ld4(p.aux + off[i] + c0 + 4 * ch);
-          if (MODE == EPI_EXPAND) ai[i] = *reinterpret_cast<const uint32_t*>(p.aux_idx + off[i] + c0 + 4 * ch);
-        }
-      };
-      fetch_side(0);
-      // touch the output rows now: the first access of an SM to a page costs ~1 us (translation miss), which
-      // otherwise lands on the critical path between "accumulator ready" and the first store
-      if (off[0] >= 0) {
-        const float* o0 = MODE == EPI_EXPAND ? p.out + (size_t)dst[0] : p.out + (size_t)off[0];
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(o0 + 4 * ch));
-      }
-      if (!mbar_wait(tmem_full, 0)) { if (p.err) *p.err = 3; }
-      if (dbg && threadIdx.x == 64) dbg[5] = clock64();   // accumulator ready
-      tc_fence_after();
-      asm volatile("bar.sync 1, 128;" ::: "memory");      // bias_s written by all four epilogue warps
-      const uint32_t xpose = smem_u32(smem) + quad * 4096;   // stage 0 is idle: every MMA has completed
-      const size_t up = (size_t)2 * p.OW * p.N;                      // EXPAND: one image row down
-#pragma unroll 1
-      for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
-        float v[32];
-        if (c0) fetch_side(c0);
-        tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
-        if (dbg && threadIdx.x == 64 && c0 == 0) dbg[11] = clock64();   // first TMEM read done
-#pragma unroll
-        for (int c4 = 0; c4 < 8; ++c4)
-          sts4(xpose + (lane * 8 + (c4 ^ (lane & 7))) * 16, v[4 * c4], v[4 * c4 + 1], v[4 * c4 + 2], v[4 * c4 + 3]);
-        __syncwarp();
-        float4 xs[8];     // all eight reads first: explicit shared-space loads, nothing for them to alias with
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int r = i * 4 + sub;
-          xs[i] = lds4(xpose + (r * 8 + (ch ^ (r & 7))) * 16);
-        }
-        if (dbg && threadIdx.x == 64 && c0 == 0) dbg[12] = clock64();   // first block transposed
-        const float4 b4 = *reinterpret_cast<const float4*>(&bias_s[c0 + 4 * ch]);
-        float4 csum = make_float4(0.f, 0.f, 0.f, 0.f);   // this lane's 4 columns, summed over its 8 rows
-        uint32_t keep = 0;
-        if (MODE == EPI_STORE && p.dropout) {
-          auto gi = [&](int i) { return (unsigned long long)(((size_t)off[i] + c0 + 4 * ch) >> 2); };
-          keep = keep4_ool(seed, (uint32_t)step, gi(0), gi(1), gi(2), gi(3)) |
-                 (keep4_ool(seed, (uint32_t)step, gi(4), gi(5), gi(6), gi(7)) << 16);
-        }
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          float4 x = xs[i];
-          if (off[i] < 0) continue;
-          const size_t e0 = (size_t)off[i] + c0 + 4 * ch;
-          if (MODE == EPI_STORE) {
-            x.x += b4.x; x.y += b4.y; x.z += b4.z; x.w += b4.w;
-            if (p.relu == 1) {
-              x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f);
-            } else if (p.relu == 2) {
-              x = tanh4_ool(x);
-            }
-            if (p.dropout) {
-              const uint32_t kb = keep >> (4 * i);
-              x.x = (kb & 1u) ? x.x * 2.f : 0.f;
-              x.y = (kb & 2u) ? x.y * 2.f : 0.f;
-              x.z = (kb & 4u) ? x.z * 2.f : 0.f;
-              x.w = (kb & 8u) ? x.w * 2.f : 0.f;
-            }
-            st4(p.out + e0, x);
-          } else if (MODE == EPI_MASK) {
-            const float4 h = ax[i];
-            float4 o;
-            if (p.relu == 2) {   // d tanh: g * (1 - h^2)
-              o.x = x.x * (1.f - h.x * h.x) * p.scale;
-              o.y = x.y * (1.f - h.y * h.y) * p.scale;
-              o.z = x.z * (1.f - h.z * h.z) * p.scale;
-              o.w = x.w * (1.f - h.w * h.w) * p.scale;
-            } else {
-              o.x = h.x > 0.f ? x.x * p.scale : 0.f;
-              o.y = h.y > 0.f ? x.y * p.scale : 0.f;
-              o.z = h.z > 0.f ? x.z * p.scale : 0.f;
-              o.w = h.w > 0.f ? x.w * p.scale : 0.f;
-            }
-            st4(p.out + e0, o);
-            csum.x += o.x; csum.y += o.y; csum.z += o.z; csum.w += o.w;
-          } else {  // EPI_EXPAND: un-pool + ReLU mask; tile rows are pooled positions
-            const float4 h = ax[i];
-            const uint32_t bsel = ai[i];   // four arg-max codes (0..3), one byte per column
-            float* d0 = p.out + (size_t)dst[i] + c0 + 4 * ch;
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              float4 o;
-              o.x = ((bsel & 0xffu) == (uint32_t)q && h.x > 0.f) ? x.x * p.scale : 0.f;
-              o.y = (((bsel >> 8) & 0xffu) == (uint32_t)q && h.y > 0.f) ? x.y * p.scale : 0.f;
-              o.z = (((bsel >> 16) & 0xffu) == (uint32_t)q && h.z > 0.f) ? x.z * p.scale : 0.f;
-              o.w = ((bsel >> 24) == (uint32_t)q && h.w > 0.f) ? x.w * p.scale : 0.f;
-              st4(d0 + (q >> 1) * up + (q & 1) * p.N, o);
-            }
-            // exactly one of the four window positions receives the gradient (when the unit was active)
-            csum.x += h.x > 0.f ? x.x * p.scale : 0.f;
-            csum.y += h.y > 0.f ? x.y * p.scale : 0.f;
-            csum.z += h.z > 0.f ? x.z * p.scale : 0.f;
-            csum.w += h.w > 0.f ? x.w * p.scale : 0.f;
-          }
-        }
-        if ((MODE == EPI_MASK || MODE == EPI_EXPAND) && p.colpart) {
-          // Bias gradient of the layer below = column sums of what was just written.  Fixed-order reduction:
-          // 8 rows in registers, 4 row groups by shuffle, 4 warps through shared memory -> one partial row per
-          // tile, summed over tiles by the split-K reduce kernel.  No atomics, no zeroing, and the 19 MB
-          // gradient tensor is not read again by a separate column-sum kernel.
-          csum.x += __shfl_xor_sync(0xffffffffu, csum.x, 8);  csum.y += __shfl_xor_sync(0xffffffffu, csum.y, 8);
-          csum.z += __shfl_xor_sync(0xffffffffu, csum.z, 8);  csum.w += __shfl_xor_sync(0xffffffffu, csum.w, 8);
-          csum.x += __shfl_xor_sync(0xffffffffu, csum.x, 16); csum.y += __shfl_xor_sync(0xffffffffu, csum.y, 16);
-          csum.z += __shfl_xor_sync(0xffffffffu, csum.z, 16); csum.w += __shfl_xor_sync(0xffffffffu, csum.w, 16);
-          float* cs = colsum_s + ((c0 >> 5) & 1) * 128;      // double-buffered by iteration parity
-          if (sub == 0) *reinterpret_cast<float4*>(cs + quad * 32 + 4 * ch) = csum;
-          asm volatile("bar.sync 1, 128;" ::: "memory");
-          if (quad == 0)
-            p.colpart[(size_t)tile * p.N + n_tile0 + c0 + lane] = (cs[lane] + cs[32 + lane]) + (cs[64 + lane] + cs[96 + lane]);
-        }
-        if (dbg && threadIdx.x == 64 && c0 == 0) dbg[13] = clock64();   // first iteration's stores issued
-        __syncwarp();
-      }
+      coalesced_epilogue<BLOCK_N, MODE>(p, smem, tmem_base, tmem_full, true, quad, lane, row, n, oh, ow, valid, n_tile0,
+                                        tile, seed, step, bias_s, dbg);
     }
     tc_fence_before();
     if (dbg && threadIdx.x == 64) dbg[6] = clock64();   // epilogue done
@@ -463,6 +479,131 @@ __global__ void __launch_bounds__(192)
 umma_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                   const IgemmParams p) {
   igemm_body<BLOCK_N, MODE>(&tmap_a, &tmap_b, blockIdx.y * BLOCK_N, p);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Resident-input convolution (forward or data gradient) for layers whose per-image input fits in shared memory.
+//
+// The streaming kernel above fetches, for every kernel tap, the shifted 128-row window of the input again: for the
+// 5x5 data gradient of the second convolution that is 25x the same 32 KB image through L2 -> SM (2.4 MB per CTA),
+// and the kernel ran at the chip's L2 feed limit.  Here one CTA owns one image: its (zero-padded) input is loaded
+// ONCE into shared memory as `cb` channel-chunk planes of RH x RW pixels x 128 B, and the tap shift is applied to
+// the *descriptor*: with q = y*RW + x enumerating output pixels in the padded row pitch, tap (kh,kw) reads plane
+// rows q + shift(kh,kw), shift = (sgn*kh - y_org)*RW + (sgn*kw - x_org), i.e. the A operand of every tap is the same
+// plane at a different start row.  A K-major SWIZZLE_128B operand may start at any 128-byte row of a TMA-written
+// tile (the swizzle is a function of absolute shared-memory address bits; tools/dev/desc_shift_probe.cu).  Only the
+// weights are streamed (BLOCK_N x 32 floats per k-block), and each weight tile feeds all `ntiles` accumulators.
+// Columns x >= OW of the padded pitch are computed and discarded (25 % for RW = 16, OW = 12).
+struct ResidentParams {
+  int RW, RH, x_org, y_org, cb, KH, KW, sgn, ntiles, stages;
+};
+
+template <int BLOCK_N, int MODE>
+__global__ void __launch_bounds__(192)
+umma_resident_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_constant__ CUtensorMap tmap_w,
+                     const IgemmParams p, const ResidentParams r) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int plane_bytes = r.RW * r.RH * 128;
+  constexpr int kBBytes = BLOCK_N * 128;
+  uint8_t* bstage = smem + r.cb * plane_bytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(bstage + r.stages * kBBytes);
+  uint64_t* empty_bar = full_bar + kMaxStages;
+  uint64_t* res_bar = empty_bar + kMaxStages;        // one per channel-chunk plane (<= 8)
+  uint64_t* tmem_full = res_bar + 8;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  __shared__ __align__(16) float bias_s[256];
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n = blockIdx.x;                        // image
+  const int n_tile0 = blockIdx.y * BLOCK_N;
+  const int num_kb = r.KH * r.KW * r.cb;
+  const int kStages = r.stages;
+  const uint32_t tmem_cols = (uint32_t)(r.ntiles * BLOCK_N) <= 32 ? 32 : (r.ntiles * BLOCK_N <= 64 ? 64 :
+                             (r.ntiles * BLOCK_N <= 128 ? 128 : (r.ntiles * BLOCK_N <= 256 ? 256 : 512)));
+  pdl_trigger();
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmap_in);
+    prefetch_tmap(&tmap_w);
+    for (int i = 0; i < kStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    for (int i = 0; i < r.cb; ++i) mbar_init(&res_bar[i], 1);
+    mbar_init(tmem_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, tmem_cols);
+  const int kProducers = kStages < 5 ? kStages : 5;
+  const int pi = warp == 0 ? 0 : warp - 1;
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
+  if (warp >= 2)
+    for (int c = threadIdx.x - 64; c < BLOCK_N; c += 128) bias_s[c] = p.bias ? p.bias[n_tile0 + c] : 0.f;
+
+  if (warp != 1 && pi < kProducers && elect_one()) {
+    if (warp == 0) {       // the resident planes: one box per channel chunk, zero-filled outside the image
+      for (int c = 0; c < r.cb; ++c) {
+        mbar_expect_tx(&res_bar[c], plane_bytes);
+        tma_load_4d(smem + c * plane_bytes, &tmap_in, &res_bar[c], c * 32, r.x_org, r.y_org, n);
+      }
+    }
+    int stage = pi, phase = 0;
+    while (stage >= kStages) { stage -= kStages; phase ^= 1; }
+    for (int kb = pi; kb < num_kb; kb += kProducers) {
+      if (kb >= kStages && !mbar_wait(&empty_bar[stage], phase ^ 1)) { if (p.err) *p.err = 21; break; }
+      mbar_expect_tx(&full_bar[stage], kBBytes);
+      tma_load_2d(bstage + stage * kBBytes, &tmap_w, &full_bar[stage], kb * 32, n_tile0);
+      stage += kProducers;
+      while (stage >= kStages) { stage -= kStages; phase ^= 1; }
+    }
+  }
+  __syncwarp();
+  if (warp == 1) {
+    if (elect_one()) {
+      constexpr uint32_t idesc = make_idesc_tf32(128, BLOCK_N, 0, 0);
+      const uint64_t desc0 = make_smem_desc(smem_u32(smem), 16, 1024);
+      const uint64_t bdesc0 = make_smem_desc(smem_u32(bstage), 16, 1024);
+      int stage = 0, phase = 0, kh = 0, kw = 0, c = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        if (kb < r.cb) {     // first touch of plane c
+          if (!mbar_wait(&res_bar[c], 0)) { if (p.err) *p.err = 22; break; }
+        }
+        if (!mbar_wait(&full_bar[stage], phase)) { if (p.err) *p.err = 23; break; }
+        tc_fence_after();
+        const int shift = (r.sgn * kh - r.y_org) * r.RW + (r.sgn * kw - r.x_org);
+        const uint64_t ad = desc0 + (uint64_t)((c * plane_bytes + shift * 128) >> 4);
+        const uint64_t bd = bdesc0 + (uint64_t)((stage * kBBytes) >> 4);
+        for (int t = 0; t < r.ntiles; ++t) {
+          const uint64_t at = ad + (uint64_t)((t * 128 * 128) >> 4);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            mma_tf32(tmem_base + (uint32_t)(t * BLOCK_N), at + 2 * k, bd + 2 * k, idesc, (kb | k) ? 1u : 0u);
+        }
+        mma_commit(&empty_bar[stage]);
+        if (++stage == kStages) { stage = 0; phase ^= 1; }
+        if (++c == r.cb) { c = 0; if (++kw == r.KW) { kw = 0; ++kh; } }
+      }
+      mma_commit(tmem_full);
+    }
+  } else if (warp >= 2) {
+    const int quad = warp & 3;
+    const int row = quad * 32 + lane;
+    for (int t = 0; t < r.ntiles; ++t) {
+      const int q = t * 128 + row;
+      const int y = q / r.RW, x = q - y * r.RW;
+      const bool valid = n < p.B && y < p.OH && x < p.OW;
+      // plane 0 doubles as the transposition buffer: every MMA has completed once tmem_full fired
+      coalesced_epilogue<BLOCK_N, MODE>(p, smem, tmem_base + (uint32_t)(t * BLOCK_N), tmem_full, t == 0, quad, lane, row, n,
+                                        y, x, valid, n_tile0, n * r.ntiles + t, 0ull, 0ull, bias_s, nullptr);
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, tmem_cols);
+  }
 }
 
 // Parameter pull fused with the GEMM that consumes the weights: the B operand (rows of a Linear /
@@ -606,6 +747,63 @@ int mpit_umma_igemm(const void* tmap_a128, const void* tmap_b128, const int* geo
 #undef MPIT_IGEMM_MODES
     default: return MPIT_E_ARG;
   }
+}
+
+// Resident-input convolution / data gradient: one CTA per image, input planes loaded once, weights streamed.
+// geom15 (HOST) = {RW, RH, x_org, y_org, cb, KH, KW, sgn, ntiles, B, OH, OW, N, mode, relu}; OH/OW are the extents of
+// the GEMM M side (rows q = y*RW + x with y < OH are computed, x >= OW discarded).  tmap_in: 4-D NHWC map with box
+// (32, RW, RH, 1) and zero OOB fill; tmap_w: 2-D [N][K] map with box (32, block_n), k-blocks ordered (kh, kw, chunk).
+// Modes 0 (store), 2 (mask), 3 (un-pool + mask).  Returns MPIT_E_UNSUPPORTED when the planes do not fit.
+int mpit_umma_conv_resident(const void* tmap_in128, const void* tmap_w128, const int* geom15, float scale,
+                            const float* bias, float* out, const float* aux, const unsigned char* aux_idx, int* err,
+                            float* colpart, int block_n, void* stream) {
+  ResidentParams r{};
+  IgemmParams p{};
+  r.RW = geom15[0]; r.RH = geom15[1]; r.x_org = geom15[2]; r.y_org = geom15[3]; r.cb = geom15[4];
+  r.KH = geom15[5]; r.KW = geom15[6]; r.sgn = geom15[7]; r.ntiles = geom15[8];
+  p.B = geom15[9]; p.OH = geom15[10]; p.OW = geom15[11]; p.N = geom15[12]; p.mode = geom15[13]; p.relu = geom15[14];
+  p.scale = scale; p.bias = bias; p.out = out; p.aux = aux; p.aux_idx = aux_idx; p.err = err; p.colpart = colpart;
+  if (r.cb < 1 || r.cb > 8 || r.ntiles < 1 || r.KH < 1 || r.KW < 1 || (r.sgn != 1 && r.sgn != -1) || p.N % block_n != 0)
+    return MPIT_E_ARG;
+  if ((r.RW * r.RH) % 8 != 0 || r.RW > 256 || r.RH > 256) return MPIT_E_ARG;
+  if (r.ntiles * block_n > 512) return MPIT_E_UNSUPPORTED;
+  // every row a tile can touch must lie inside the plane
+  const int max_shift = (r.sgn > 0 ? (r.KH - 1) - r.y_org : -r.y_org) * r.RW + (r.sgn > 0 ? (r.KW - 1) - r.x_org : -r.x_org);
+  const int min_shift = (r.sgn > 0 ? -r.y_org : -(r.KH - 1) - r.y_org) * r.RW + (r.sgn > 0 ? -r.x_org : -(r.KW - 1) - r.x_org);
+  if (min_shift < 0 || r.ntiles * 128 + max_shift > r.RW * r.RH) return MPIT_E_ARG;
+  const int plane_bytes = r.RW * r.RH * 128;
+  const int stage_bytes = block_n * 128;
+  int stages = (220 * 1024 - r.cb * plane_bytes - 1536) / stage_bytes;
+  if (stages > 8) stages = 8;
+  const int num_kb = r.KH * r.KW * r.cb;
+  if (stages > num_kb) stages = num_kb;
+  if (stages < 2) return MPIT_E_UNSUPPORTED;
+  r.stages = stages;
+  const size_t smem = (size_t)r.cb * plane_bytes + (size_t)stages * stage_bytes + 512 + 1024;   // + barriers + align
+  CUtensorMap ti, tw;
+  memcpy(&ti, tmap_in128, sizeof(ti));
+  memcpy(&tw, tmap_w128, sizeof(tw));
+  dim3 grid(p.B, p.N / block_n);
+  cudaStream_t st = (cudaStream_t)stream;
+  auto go = [&](auto kern) -> int {
+    static size_t attr_smem = 0;      // per instantiation: raise the opt-in limit to what this launch needs
+    if (smem > attr_smem) {            // (the kernel's static shared memory counts against the same 227 KB)
+      MPIT_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      attr_smem = smem;
+    }
+    MPIT_CUDA_TRY(launch_k(kern, grid, dim3(192), smem, st, ti, tw, p, r));
+    return 0;
+  };
+  if (block_n == 64) {
+    if (p.mode == EPI_EXPAND) return go(umma_resident_kernel<64, EPI_EXPAND>);
+    if (p.mode == EPI_MASK) return go(umma_resident_kernel<64, EPI_MASK>);
+    if (p.mode == EPI_STORE) return go(umma_resident_kernel<64, EPI_STORE>);
+  } else if (block_n == 32) {
+    if (p.mode == EPI_EXPAND) return go(umma_resident_kernel<32, EPI_EXPAND>);
+    if (p.mode == EPI_MASK) return go(umma_resident_kernel<32, EPI_MASK>);
+    if (p.mode == EPI_STORE) return go(umma_resident_kernel<32, EPI_STORE>);
+  }
+  return MPIT_E_UNSUPPORTED;
 }
 
 // Linear layer whose weight rows live in the NVLink-sharded centre: y = act(x W^T + b), W fetched by

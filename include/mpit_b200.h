@@ -191,6 +191,18 @@ int mpit_umma_igemm(const void* tmap_a128, const void* tmap_b128, const int* geo
                     const float* bias, float* out, unsigned char* idx, const float* aux,
                     const unsigned char* aux_idx, const int* crop, const unsigned long long* rng, int* err,
                     float* colpart, int block_n, void* stream);
+/* Resident-input convolution (forward, sgn=+1) or data gradient (sgn=-1): one CTA per image loads the image's
+ * (zero-padded) input ONCE into shared memory; each kernel tap is the same plane at a shifted descriptor start row,
+ * only the weights are streamed.  For layers whose input per image is a few tens of KB (conv2/conv3 of
+ * /root/reference/asyncsgd/models/7-layers-cnn.lua); mpit_umma_igemm re-fetches the window for every tap.
+ * geom15 (HOST) = {RW, RH, x_org, y_org, cb, KH, KW, sgn, ntiles, B, OH, OW, N, mode, relu}: plane of RH x RW pixels
+ * whose element (0,0) is input pixel (y_org, x_org) (negative = zero padding); output pixels q = y*RW + x, y < OH,
+ * in ntiles tiles of 128 rows; x >= OW is discarded.  tmap_in: 4-D NHWC map, box (32, RW, RH, 1), zero OOB fill;
+ * tmap_w: [N][K] map, box (32, block_n), K ordered (kh, kw, channel chunk).  Modes 0, 2, 3 of mpit_umma_igemm;
+ * colpart has B*ntiles rows.  MPIT_E_UNSUPPORTED when the planes do not fit in shared memory / TMEM. */
+int mpit_umma_conv_resident(const void* tmap_in128, const void* tmap_w128, const int* geom15, float scale,
+                            const float* bias, float* out, const float* aux, const unsigned char* aux_idx, int* err,
+                            float* colpart, int block_n, void* stream);
 /* Parameter pull fused with the GEMM that consumes the weights (/root/reference/asyncsgd/pclient.lua:74-84
  * followed by the model's first Linear): the weight rows stay in the NVLink-sharded centre and the
  * kernel's TMA loads read each tile from its owner's shard. tmaps_b: HOST array of nranks x 128 bytes. */

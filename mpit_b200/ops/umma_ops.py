@@ -56,6 +56,35 @@ class IgemmLaunch:
               "mpit_umma_igemm")
 
 
+@dataclass
+class ResidentLaunch:
+    """mpit_umma_conv_resident: one CTA per image, input planes resident in shared memory, weights streamed."""
+    tmap_in: object
+    tmap_w: object
+    geom: object          # c_int * 15
+    scale: float
+    bias: Optional[torch.Tensor]
+    out: torch.Tensor
+    aux: Optional[torch.Tensor]
+    aux_idx: Optional[torch.Tensor]
+    block_n: int
+    colpart: Optional[torch.Tensor] = None
+
+    def run(self, err: torch.Tensor, dropout: Optional[bool] = None):
+        check(kernels().mpit_umma_conv_resident(self.tmap_in, self.tmap_w, self.geom, self.scale, ptr(self.bias),
+                                                ptr(self.out), ptr(self.aux), ptr(self.aux_idx), ptr(err),
+                                                ptr(self.colpart), self.block_n, cur_stream()),
+              "mpit_umma_conv_resident")
+
+    @property
+    def tiles(self) -> int:
+        return self.geom[9] * self.geom[8]      # B * ntiles rows of colpart
+
+
+def resident_geom(*, RW, RH, x_org, y_org, cb, KH, KW, sgn, ntiles, B, OH, OW, N, mode, relu=0):
+    return (ctypes.c_int * 15)(RW, RH, x_org, y_org, cb, KH, KW, sgn, ntiles, B, OH, OW, N, mode, relu)
+
+
 def igemm_geom(*, nsub, tw, th, tn, tiles_w, tiles_h, kw_it, cb, num_kb, sgn, B, OH, OW, N, mode, relu=0,
                dropout=0):
     assert nsub * tw * th * tn == 128
@@ -171,6 +200,28 @@ class CifarUmmaPlan:
         # Bias gradients ride on the data-gradient epilogues: dgrad[i] writes dz[i-1], and its per-tile column
         # sums (summed over tiles by the split-K reduce launch) are the bias gradient of layer i-1.  The
         # classifier's bias gradient comes from the loss kernel.  (tiles, columns seen by the kernel, channels)
+        # Optional (MPIT_RESIDENT=1): conv2's data gradient with the image's dz resident in shared memory (25 taps = 25
+        # descriptor offsets into the same planes) instead of 25 re-fetched windows.  Correct, and it removes 90 % of
+        # the L2 -> SM traffic, but it is SLOWER on B200 (50.6 us vs 27.8 us, profiles/README.md): one image per CTA in
+        # a 16-pixel padded row pitch computes 256 rows for 144 useful ones, and at TF32 the tensor pipe (64 clk per
+        # 128x64x8 MMA) then needs 27 us where the streaming kernel needs 13.5 us.  The streaming launch is the
+        # default; it also stays available as self.dgrad_stream[1].
+        self.dgrad_stream = dict(self.dgrad)
+        import os as _os
+        RW = 16
+        ntl = -(-(12 * RW) // 128)
+        RH = -(-(ntl * 128 + 4 * RW + 4) // RW)
+        if (RW * RH) % 8:
+            RH += 1
+        plane = RW * RH * 128
+        if (_os.environ.get("MPIT_RESIDENT", "0") == "1" and c1 == 64 and c2 % 32 == 0
+                and (c2 // 32) * plane + 2 * c1 * 128 + 2048 <= 220 * 1024 and ntl * c1 <= 512):
+            self.dgrad[1] = ResidentLaunch(
+                nhwc_tmap(dz[1], B, 8, 8, c2, RW, RH, 1), weight_tmap(wd(1), c1, 25 * c2, c1),
+                resident_geom(RW=RW, RH=RH, x_org=-4, y_org=-4, cb=c2 // 32, KH=5, KW=5, sgn=-1, ntiles=ntl, B=B,
+                              OH=12, OW=12, N=c1, mode=EPI_EXPAND),
+                1.0, None, dz[0], act[0], idx[0], c1)
+
         # The classifier (fc2 + log-softmax + NLL and their backward down to dz of fc1) is one CUDA-core kernel
         # (csrc/kernels/head.cu) when its shape allows: it then also produces gb(4) and gb(3) directly.
         import os
@@ -179,8 +230,11 @@ class CifarUmmaPlan:
         self.bias_parts = {}
         for i in ((3, 2, 1) if self.head else (4, 3, 2, 1)):
             g = self.dgrad[i].geom            # {nsub,tw,th,tn,tiles_w,tiles_h,...,B at [10],...,N at [13]}
-            tiles = -(-(-(-g[10] // g[3]) * g[4] * g[5]) // g[0])
-            ncols = g[13]
+            if isinstance(self.dgrad[i], ResidentLaunch):
+                tiles, ncols = self.dgrad[i].tiles, g[12]
+            else:
+                tiles = -(-(-(-g[10] // g[3]) * g[4] * g[5]) // g[0])
+                ncols = g[13]
             cp = torch.zeros(tiles * ncols, dtype=torch.float32, device=eng.dev)
             self.dgrad[i].colpart = cp
             self.bias_parts[i - 1] = (cp, tiles, ncols, eng.layers[i - 1].CO)

@@ -211,3 +211,32 @@ def test_mnist_cnn_engine_matches_torch_cpu():
         ref_g = flat_from_torch(model, grads=True)
         rel = float((eng.flat_grad().cpu() - ref_g).norm() / ref_g.norm())
         assert rel < (1e-3 if impl == "ref" else 0.15), (impl, rel)
+
+
+def test_resident_input_dgrad_matches_streaming(monkeypatch):
+    """mpit_umma_conv_resident (input planes in shared memory, taps as descriptor row offsets) against the
+    streaming implicit-GEMM data gradient of conv2, same inputs: dz1 and the bias partial sums must agree."""
+    torch.manual_seed(6)
+    B = 16
+    theta = flat_from_torch(TorchCifarCNN()).cuda()
+    images = torch.randint(0, 256, (B, 3, 32, 32), dtype=torch.uint8)
+    labels = torch.randint(0, NUM_CLASSES, (B,), dtype=torch.int32)
+    monkeypatch.setenv("MPIT_RESIDENT", "1")
+    eng = CifarEngine(B, impl="umma", seed=3)
+    from mpit_b200.ops.umma_ops import ResidentLaunch
+    res, stream = eng._umma.dgrad[1], eng._umma.dgrad_stream[1]
+    assert isinstance(res, ResidentLaunch) and not isinstance(stream, ResidentLaunch)
+    eng.load_flat(theta)
+    eng.set_batch(images, labels, random_crop_offsets(B))
+    eng.fwd_bwd()                     # runs the resident kernel in the sweep
+    torch.cuda.synchronize()
+    eng._umma.check()
+    got = eng.dz[0].clone()
+    got_bias = res.colpart.view(res.tiles, -1).sum(0)
+    tiles = -(-(-(-B // 4) * 9) // 2)
+    stream.colpart = torch.zeros(tiles * 64, device="cuda")
+    eng.dz[0].fill_(9.0)
+    stream.run(eng._umma.err)
+    torch.cuda.synchronize()
+    assert _rel_l2(got, eng.dz[0]) < 1e-5, _rel_l2(got, eng.dz[0])
+    assert torch.allclose(got_bias, stream.colpart.view(tiles, 64).sum(0), rtol=1e-3, atol=1e-6)
