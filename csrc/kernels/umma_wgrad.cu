@@ -217,45 +217,71 @@ wgrad_reduce_kernel(const float* __restrict__ part, float* __restrict__ gw, int 
 // in flight, then combine through shared memory in a fixed order -- a single thread walking 64-144 partials
 // with dependent L2 latencies made this kernel 10 us.  Partials are n-major (part[s][n][m]) and consecutive
 // threads run along m, so reads and the gw[n][m] writes are both coalesced.
-struct ReduceSeg { const float* part; float* gw; int nsplit, m_pad, K, N, first_block, sl; };
+struct ReduceSeg { const float* part; float* gw; int nsplit, m_pad, K, N, first_block, sl, vec; };
 struct ReduceArgs { ReduceSeg seg[16]; int nseg; };
 
-__global__ void __launch_bounds__(256) multi_wgrad_reduce_kernel(ReduceArgs a) {
-  __shared__ float red[256];
-  pdl_trigger();
-  pdl_wait();
-  int s = 0;
-  while (s + 1 < a.nseg && (int)blockIdx.x >= a.seg[s + 1].first_block) ++s;
-  const ReduceSeg sg = a.seg[s];
+// V = 4: an output "element" is four consecutive m (16-byte loads and stores; K % 4 == 0, buffers 16-byte
+// aligned -- every weight-gradient segment); V = 1: scalar (bias rows).
+template <int V>
+__device__ __forceinline__ void reduce_segment(const ReduceSeg& sg, float* red, const int block) {
   // sl is a power of two, so outputs-per-block is a shift; all index math in 32 bits (a 64-bit division per
   // thread cost more than the loads: host checks K*N < 2^31)
   const int opb_shift = 8 - (31 - __clz(sg.sl));
   const int opb = 1 << opb_shift;                      // outputs per block
   const int o = threadIdx.x & (opb - 1), sl = threadIdx.x >> opb_shift;
-  const unsigned e = (unsigned)(blockIdx.x - sg.first_block) * (unsigned)opb + (unsigned)o;
-  const bool live = e < (unsigned)sg.K * (unsigned)sg.N;
-  float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
+  const unsigned e = (unsigned)block * (unsigned)opb + (unsigned)o;
+  const unsigned kq = (unsigned)sg.K / V;              // output elements per n row
+  const bool live = e < kq * (unsigned)sg.N;
+  float acc[4][V];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int v = 0; v < V; ++v) acc[i][v] = 0.f;
   if (live) {
-    const unsigned n = e / (unsigned)sg.K, m = e - n * (unsigned)sg.K;     // m fastest: e is also the gw index
+    const unsigned n = e / kq, m = (e - n * kq) * V;   // m fastest: e*V is also the gw index
     const float* p = sg.part + (size_t)n * sg.m_pad + m;
     const size_t stride = (size_t)sg.N * sg.m_pad;
+    auto add = [&](int i, int sp) {
+      if (V == 4) {
+        const float4 t = ld4(p + (size_t)sp * stride);
+        acc[i][0] += t.x; acc[i][V > 1 ? 1 : 0] += t.y; acc[i][V > 2 ? 2 : 0] += t.z; acc[i][V > 3 ? 3 : 0] += t.w;
+      } else {
+        acc[i][0] += p[(size_t)sp * stride];
+      }
+    };
     int sp = sl;
     for (; sp + 3 * sg.sl < sg.nsplit; sp += 4 * sg.sl) {
-      acc0 += p[(size_t)sp * stride];
-      acc1 += p[(size_t)(sp + sg.sl) * stride];
-      acc2 += p[(size_t)(sp + 2 * sg.sl) * stride];
-      acc3 += p[(size_t)(sp + 3 * sg.sl) * stride];
+      add(0, sp); add(1, sp + sg.sl); add(2, sp + 2 * sg.sl); add(3, sp + 3 * sg.sl);
     }
-    for (; sp < sg.nsplit; sp += sg.sl) acc0 += p[(size_t)sp * stride];
+    for (; sp < sg.nsplit; sp += sg.sl) add(0, sp);
   }
-  float t = (acc0 + acc1) + (acc2 + acc3);
+  float t[V];
+#pragma unroll
+  for (int v = 0; v < V; ++v) t[v] = (acc[0][v] + acc[1][v]) + (acc[2][v] + acc[3][v]);
   if (sg.sl > 1) {
-    red[threadIdx.x] = t;
+#pragma unroll
+    for (int v = 0; v < V; ++v) red[v * 256 + threadIdx.x] = t[v];
     __syncthreads();
     if (sl == 0)
-      for (int k = 1; k < sg.sl; ++k) t += red[k * opb + o];
+      for (int k = 1; k < sg.sl; ++k)
+#pragma unroll
+        for (int v = 0; v < V; ++v) t[v] += red[v * 256 + k * opb + o];
   }
-  if (live && sl == 0) sg.gw[e] = t;
+  if (live && sl == 0) {
+    if (V == 4) st4(sg.gw + (size_t)e * 4, make_float4(t[0], t[V > 1 ? 1 : 0], t[V > 2 ? 2 : 0], t[V > 3 ? 3 : 0]));
+    else sg.gw[e] = t[0];
+  }
+}
+
+__global__ void __launch_bounds__(256) multi_wgrad_reduce_kernel(ReduceArgs a) {
+  __shared__ float red[4 * 256];
+  pdl_trigger();
+  pdl_wait();
+  int s = 0;
+  while (s + 1 < a.nseg && (int)blockIdx.x >= a.seg[s + 1].first_block) ++s;
+  const ReduceSeg sg = a.seg[s];
+  if (sg.vec) reduce_segment<4>(sg, red, blockIdx.x - sg.first_block);
+  else reduce_segment<1>(sg, red, blockIdx.x - sg.first_block);
 }
 
 // Column sums of up to 8 [rows][C] matrices in one launch (bias gradients of every layer).
@@ -397,8 +423,10 @@ int mpit_multi_wgrad_reduce(int nseg, const unsigned long long* parts, const uns
     int sl = 1;
     while (sl < 8 && sl * 4 < nsplit[i]) sl *= 2;      // ~4+ partials per split lane
     a.seg[i].sl = sl;
+    const int vec = (K[i] % 4 == 0 && m_pad[i] % 4 == 0 && ((parts[i] | gws[i]) & 15) == 0) ? 1 : 0;
+    a.seg[i].vec = vec;
     const long long opb = 256 / sl;
-    blocks += (int)(((long long)K[i] * N[i] + opb - 1) / opb);
+    blocks += (int)(((long long)K[i] * N[i] / (vec ? 4 : 1) + opb - 1) / opb);
   }
   MPIT_CUDA_TRY(launch_k(multi_wgrad_reduce_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, a));
   return 0;

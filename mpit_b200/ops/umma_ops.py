@@ -142,8 +142,10 @@ class CifarUmmaPlan:
             igemm_geom(nsub=2, tw=8, th=8, tn=1, tiles_w=3, tiles_h=3, kw_it=1, cb=1, num_kb=5, sgn=1, B=B,
                        OH=24, OW=24, N=c1, mode=EPI_POOL, relu=1),
             1.0, eng.b(0), act[0], idx[0], None, None, eng.crop, None, bn))
-        # conv2
-        bn = _pick_block(c2)
+        # conv2: 64-column tiles -> twice the CTAs (128 instead of 64 for c2 = 128).  At TF32 the tensor pipe needs 128
+        # clocks per 128x128x8 MMA, so 64 CTAs were MMA-bound at 13.5 us; MPIT_CONV2_BN overrides for A/B runs.
+        import os as _os2
+        bn = _pick_block(c2, tuple(int(v) for v in _os2.environ.get("MPIT_CONV2_BN", "64,32").split(",")))
         self.fwd.append(IgemmLaunch(
             nhwc_tmap(act[0], B, 12, 12, c1, 8, 8, 1), weight_tmap(w(1), c2, 25 * c1, bn),
             igemm_geom(nsub=2, tw=8, th=8, tn=1, tiles_w=1, tiles_h=1, kw_it=5, cb=c1 // 32, num_kb=25 * c1 // 32,
