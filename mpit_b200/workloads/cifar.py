@@ -40,7 +40,8 @@ class CifarOpts:
     lrp: float = 0.0
     maxepoch: int = 1
     saveep: int = 10
-    seed: int = 1
+    seed: int = 1                 # per-worker: data order, crops, dropout stream
+    init_seed: int = 1            # model initialisation: the same on every worker (goot.lua:29-30 seeds all ranks alike)
     impl: str = "umma"            # kernel path: umma (tcgen05) | ref (fp32 CUDA cores)
     use_graphs: bool = True
     save: str = "results"
@@ -95,7 +96,7 @@ class CifarTrainer:
         layers = mnist_cnn_layers() if opts.model == "mnist" else cifar_layers()
         self.engine = CifarEngine(opts.mb, device=self.dev, impl=opts.impl, seed=opts.seed, layers=layers)
         if theta0 is None:
-            g = torch.Generator().manual_seed(opts.seed)
+            g = torch.Generator().manual_seed(opts.init_seed)
             m = TorchCifarCNN(1, 32, 64, 64, 256) if opts.model == "mnist" else TorchCifarCNN()
             from ..models.cifar_cnn import torch7_reset
             torch7_reset(m, g)
