@@ -130,39 +130,82 @@ class CifarTrainer:
             torch.cuda.synchronize()
             dist.barrier()   # centre seeded before anyone syncs against it
         # pinned landing zone for the per-step loss read-back
-        self._loss_host = torch.zeros(2, dtype=torch.float32).pin_memory()
-        self._loss_dev = torch.zeros(2, dtype=torch.float32, device=self.dev)
-        self._loss_evt = torch.cuda.Event()
-        self._have_loss = False
+        # Pipelined host side of train_step: the loss comes back LAG steps late (so the host never waits for the
+        # step it has just launched) and the inputs of step t travel on a copy stream into a double-buffered device
+        # staging area while step t-1 computes.
+        self.LAG = 2
+        self._loss_host = torch.zeros(self.LAG + 1, 2, dtype=torch.float32).pin_memory()
+        self._loss_dev = torch.zeros(self.LAG + 1, 2, dtype=torch.float32, device=self.dev)
+        self._loss_evt = [torch.cuda.Event() for _ in range(self.LAG + 1)]
+        self._k = 0                                   # steps issued through train_step
+        self._ret = 0                                 # steps whose loss has been handed back
+        e = self.engine
+        self._copy_stream = torch.cuda.Stream(device=self.dev)
+        self._stage = [(torch.empty_like(e.x_u8), torch.empty_like(e.labels), torch.empty_like(e.crop))
+                       for _ in range(2)]
+        self._in_ready = [torch.cuda.Event() for _ in range(2)]     # H2D of the slot has landed
+        self._in_free = [torch.cuda.Event() for _ in range(2)]      # the slot has been consumed by the main stream
         self.tm = {"feval": 0.0, "sync": 0.0}
         self.h2d_bytes = 0
         self.d2h_bytes = 0
 
     # -- one training step ---------------------------------------------------------------------
     def train_step(self, images_u8: torch.Tensor, labels: torch.Tensor, crop: torch.Tensor) -> Optional[float]:
-        """Stage a mini-batch (pinned host tensors), run one optimizer step, and return the mean loss
-        of the *previous* step (its device->host copy has landed by now, so nothing stalls)."""
+        """Stage a mini-batch (pinned host tensors), run one optimizer step, and return the mean loss of the step
+        issued ``LAG`` calls earlier (None for the first calls); :meth:`last_loss` gives the newest one.
+
+        The caller may reuse its host buffers as soon as this returns: the host->device copies run on a copy
+        stream (beside the previous step's kernels) and are waited for here; only the ~2 us device-to-device move
+        into the engine's input buffers sits on the compute stream."""
+        k, lag = self._k, self.LAG
         prev = None
-        if self._have_loss:
-            self._loss_evt.synchronize()
-            prev = float(self._loss_host[0]) / self.opts.mb
-        self.engine.set_batch(images_u8, labels, crop)
+        if k - self._ret >= lag:
+            slot = self._ret % (lag + 1)
+            self._loss_evt[slot].synchronize()
+            prev = float(self._loss_host[slot, 0]) / self.opts.mb
+            self._ret += 1
+        main, cs, b = torch.cuda.current_stream(), self._copy_stream, k & 1
+        sx, sy, sc = self._stage[b]
+        if k >= 2:
+            cs.wait_event(self._in_free[b])
+        with torch.cuda.stream(cs):
+            sx.copy_(images_u8, non_blocking=True)
+            sy.copy_(labels, non_blocking=True)
+            sc.copy_(crop, non_blocking=True)
+            self._in_ready[b].record(cs)
         self.h2d_bytes = images_u8.numel() + labels.numel() * 4 + crop.numel() * 4
+        main.wait_event(self._in_ready[b])
+        self.engine.set_batch(sx, sy, sc)                  # device-to-device, on the compute stream
+        self._in_free[b].record(main)
         self.opt.step()
-        self._loss_dev[:1].copy_(self.engine.loss_sum)     # snapshot: the next step zeroes loss_sum
-        self._loss_host.copy_(self._loss_dev, non_blocking=True)
-        self._loss_evt.record()
-        self.d2h_bytes = self._loss_host.numel() * 4
-        self._have_loss = True
+        slot = k % (lag + 1)
+        # straight from the engine's accumulator: the next step's loss kernel is stream-ordered after this copy
+        self._loss_host[slot, :1].copy_(self.engine.loss_sum, non_blocking=True)
+        self._loss_evt[slot].record()
+        self.d2h_bytes = 4
+        self._k = k + 1
+        self._in_ready[b].synchronize()                    # the caller's host buffers are free again
         return prev
 
     def device_step(self) -> None:
         """One optimizer step on whatever batch is already staged on the device (kernel-only timing)."""
         self.opt.step()
 
+    def drain_losses(self) -> list:
+        """Mean losses of the steps :meth:`train_step` has not handed back yet (waits for them)."""
+        out = []
+        while self._ret < self._k:
+            slot = self._ret % (self.LAG + 1)
+            self._loss_evt[slot].synchronize()
+            out.append(float(self._loss_host[slot, 0]) / self.opts.mb)
+            self._ret += 1
+        return out
+
     def last_loss(self) -> float:
-        self._loss_evt.synchronize()
-        return float(self._loss_host[0]) / self.opts.mb
+        """Mean loss of the most recent step issued through :meth:`train_step` (waits for it)."""
+        slot = (self._k - 1) % (self.LAG + 1)
+        self._loss_evt[slot].synchronize()
+        return float(self._loss_host[slot, 0]) / self.opts.mb
 
     def params(self) -> torch.Tensor:
         return self.opt.params()
@@ -218,7 +261,7 @@ def train_epochs(tr: CifarTrainer, train_xy, test_xy, rank: int = -1, quiet: boo
             if prev is not None:
                 losses.append(prev)
             n_steps += 1
-        losses.append(tr.last_loss())
+        losses.extend(tr.drain_losses())
         conf = tr.engine.confusion.cpu()
         acc = float(conf.diag().sum()) / max(int(conf.sum()), 1)
         elapsed = (time.perf_counter() - t0) / 60
