@@ -188,9 +188,18 @@ colsum_kernel(const float* __restrict__ dz, float* __restrict__ db, long long ro
 // one 128-byte TMA row carries all five kernel columns of the first 5x5 convolution, and every row
 // starts on a 32-byte boundary (needed by the 32-byte-atom swizzle of the weight-gradient kernel).
 __global__ void __launch_bounds__(256)
-prep_u8_kernel(const unsigned char* __restrict__ src, float* __restrict__ dst, int B, int SH, int SW, int cin) {
+prep_u8_kernel(const unsigned char* __restrict__ src, float* __restrict__ dst, int B, int SH, int SW, int cin,
+               const int* __restrict__ labels_src, int* __restrict__ labels_dst, const int* __restrict__ crop_src,
+               int* __restrict__ crop_dst) {
   pdl_trigger();
   pdl_wait();
+  // the batch's labels and crop offsets ride along (one launch stages a whole mini-batch: three separate
+  // device-to-device copies in front of every step cost ~10 us of a 140 us step)
+  {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (labels_src && t < B) labels_dst[t] = labels_src[t];
+    if (crop_src && t < 2 * B) crop_dst[t] = crop_src[t];
+  }
   long long total = (long long)B * SH * SW;
   long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
@@ -359,11 +368,14 @@ int mpit_colsum(const float* dz, float* db, long long rows, int C, void* stream)
   return 0;
 }
 
-int mpit_prep_u8(const unsigned char* src, float* dst, int B, int SH, int SW, int cin, void* stream) {
+int mpit_prep_u8(const unsigned char* src, float* dst, int B, int SH, int SW, int cin, const int* labels_src,
+                 int* labels_dst, const int* crop_src, int* crop_dst, void* stream) {
   if (cin < 1 || cin > 4) return MPIT_E_ARG;
+  if ((labels_src && !labels_dst) || (crop_src && !crop_dst)) return MPIT_E_ARG;
   long long total = (long long)B * SH * SW;
+  if (total < 2 * B) return MPIT_E_ARG;      // the label / crop copy uses the first 2B threads
   MPIT_CUDA_TRY(launch_k(prep_u8_kernel, dim3(ew_grid(total, 256, 1)), dim3(256), 0, (cudaStream_t)stream, src, dst,
-                         B, SH, SW, cin));
+                         B, SH, SW, cin, labels_src, labels_dst, crop_src, crop_dst));
   return 0;
 }
 

@@ -78,7 +78,10 @@ int mpit_conv_wgrad_ref(const int* geom12, const float* dz, const float* x, cons
 int mpit_act_bwd(const float* dout, const float* out, const unsigned char* pool_idx, float* dz, int B, int OH,
                  int OW, int C, int pool, float scale, void* stream);
 int mpit_colsum(const float* dz, float* db, long long rows, int C, void* stream);
-int mpit_prep_u8(const unsigned char* src, float* dst, int B, int SH, int SW, int cin, void* stream);
+/* uint8 NCHW images -> pair-expanded NHWC8 floats in [0,1] (goot.lua:80-81 normalisation).  Optionally copies the
+ * batch's labels [B] and crop offsets [B][2] (device pointers) into the engine's buffers in the same launch. */
+int mpit_prep_u8(const unsigned char* src, float* dst, int B, int SH, int SW, int cin, const int* labels_src,
+                 int* labels_dst, const int* crop_src, int* crop_dst, void* stream);
 /* loss_sum = (accumulate ? loss_sum : 0) + sum of per-sample NLL; dlogits (may be NULL) = gscale * dNLL.
  * dbias (optional, needs dlogits and B <= 4096): dbias[c] = sum over samples of dlogits[.][c], c < ld --
  * the bias gradient of the classifier layer, in a fixed summation order. */

@@ -64,8 +64,10 @@ def colsum(dz, db, rows, C):
     check(kernels().mpit_colsum(ptr(dz), ptr(db), rows, C, cur_stream()), "mpit_colsum")
 
 
-def prep_u8(src, dst, B, SH, SW, cin=3):
-    check(kernels().mpit_prep_u8(ptr(src), ptr(dst), B, SH, SW, cin, cur_stream()), "mpit_prep_u8")
+def prep_u8(src, dst, B, SH, SW, cin=3, labels=None, labels_dst=None, crop=None, crop_dst=None):
+    """uint8 NCHW -> normalised pair-expanded NHWC8; optionally also moves the batch's labels / crop offsets."""
+    check(kernels().mpit_prep_u8(ptr(src), ptr(dst), B, SH, SW, cin, ptr(labels), ptr(labels_dst), ptr(crop),
+                                 ptr(crop_dst), cur_stream()), "mpit_prep_u8")
 
 
 def nll_fwd_bwd(logits, labels, dlogits, loss_sum, B, ncls, ld, *, gscale, confusion=None, rng_inc=None,

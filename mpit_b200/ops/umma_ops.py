@@ -242,14 +242,12 @@ class CifarUmmaPlan:
             self.bias_parts[i - 1] = (cp, tiles, ncols, eng.layers[i - 1].CO)
 
         self.two_streams = os.environ.get("MPIT_BWD_STREAMS", "2") != "1"
-        # Two more forks exist but are off by default: every fork/join turns a programmatic (PDL) edge into a
-        # full one, and on B200 the two effects cancel (measured, tools/dev/pdl_ab.py, ms/step at batch 128:
-        # PDL on + neither fork 0.1619; PDL on + both 0.1646; PDL off + both 0.1613; PDL off + neither 0.1694).
-        self.fork_prep = os.environ.get("MPIT_FORK_PREP", "0") == "1"        # input conversion beside the boundary kernel
-        self.split_reduce = os.environ.get("MPIT_SPLIT_REDUCE", "0") == "1"  # layers 1..4 reduced beside the last dgrad
+        # One more fork exists but is off by default: reducing layers 1..4 on the side stream beside the last data
+        # gradient.  Every fork/join turns a programmatic (PDL) edge into a full one, and on B200 the two effects
+        # cancel (tools/dev/pdl_ab.py, ms/step: PDL on + no fork 0.1619; PDL on + fork 0.1634; PDL off + fork 0.1661).
+        self.split_reduce = os.environ.get("MPIT_SPLIT_REDUCE", "0") == "1"
         self._side = torch.cuda.Stream(device=eng.dev)
         self._ev = [torch.cuda.Event() for _ in range(5)]
-        self._ev_in = [torch.cuda.Event() for _ in range(2)]
         self.wgrad = None
         if wgrad != "ref":
             try:

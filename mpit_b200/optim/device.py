@@ -108,7 +108,6 @@ class DeviceMSGD(_DeviceOptBase):
         do_apply = self.pending_apply
 
         def body():
-            getattr(self.engine, "begin_step", lambda: None)()
             self._boundary(do_apply, True)
             self.engine.fwd_bwd()
 
@@ -164,7 +163,6 @@ class DeviceEAMSGD(_DeviceOptBase):
         has_d_in = do_apply and self.prev_sync
 
         def body():
-            getattr(self.engine, "begin_step", lambda: None)()
             self._boundary(do_apply, True, do_sync, has_d_in)
             self.engine.fwd_bwd()
 
