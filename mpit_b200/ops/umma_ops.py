@@ -193,10 +193,13 @@ class CifarUmmaPlan:
             1.0, None, dz[1], None, act[1], idx[1], None, None, bn)
         # conv2: dz2 [B,8,8,c2] -> d(a1) over 12x12 -> un-pool with idx1, mask -> dz1 [B,24,24,c1]
         bn = _pick_block(c1, (64, 32))
+        # tile shape (MPIT_DGRAD1_TILE = "nsub,tw,th,tn"): rows of a 128-row tile = tn images x th x tw pixels
+        import os as _os3
+        d1 = [int(v) for v in _os3.environ.get("MPIT_DGRAD1_TILE", "1,4,4,8").split(",")]
         self.dgrad[1] = IgemmLaunch(
-            nhwc_tmap(dz[1], B, 8, 8, c2, 4, 4, 4), weight_tmap(wd(1), c1, 25 * c2, bn),
-            igemm_geom(nsub=2, tw=4, th=4, tn=4, tiles_w=3, tiles_h=3, kw_it=5, cb=c2 // 32, num_kb=25 * c2 // 32,
-                       sgn=-1, B=B, OH=12, OW=12, N=c1, mode=EPI_EXPAND),
+            nhwc_tmap(dz[1], B, 8, 8, c2, d1[1], d1[2], d1[3]), weight_tmap(wd(1), c1, 25 * c2, bn),
+            igemm_geom(nsub=d1[0], tw=d1[1], th=d1[2], tn=d1[3], tiles_w=12 // d1[1], tiles_h=12 // d1[2], kw_it=5,
+                       cb=c2 // 32, num_kb=25 * c2 // 32, sgn=-1, B=B, OH=12, OW=12, N=c1, mode=EPI_EXPAND),
             1.0, None, dz[0], None, act[0], idx[0], None, None, bn)
 
         # Bias gradients ride on the data-gradient epilogues: dgrad[i] writes dz[i-1], and its per-tile column
