@@ -62,7 +62,7 @@ int main() {
   cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fp, cudaEnableDefault, &q);
   auto enc = reinterpret_cast<decltype(&cuTensorMapEncodeTiled)>(fp);
   std::vector<float> ha(256 * 32), hb(32 * 32, 0.f);
-  for (int r = 0; r < 256; ++r) for (int c = 0; c < 32; ++c) ha[r * 32 + c] = (float)(r * 32 + c);   // exact in tf32? < 8192: 13 bits ok
+  for (int r = 0; r < 256; ++r) for (int c = 0; c < 32; ++c) ha[r * 32 + c] = (float)((r * 37 + c * 5) % 1021);   // integers < 2^11 are exact in tf32
   for (int i = 0; i < 32; ++i) hb[i * 32 + i] = 1.f;     // B[n][k] = delta
   float *da, *db, *dout;
   cudaMalloc(&da, ha.size() * 4); cudaMalloc(&db, hb.size() * 4); cudaMalloc(&dout, 128 * 32 * 4);
