@@ -140,12 +140,14 @@ gesd_margin_bwd_kernel(const float* __restrict__ y, const int* __restrict__ qi, 
   }
 }
 
-// Backward of Normalize (closed form) -> ReLU -> Max over time: scatters the gradient of sentence s,
-// column c into frame arg[s][c] of the dense dC [S][T][ld] (zeroed by the caller).
+// Backward of Normalize (closed form) -> ReLU -> Max over time.  The gradient of sentence s, column c lands in
+// frame arg[s][c] of the dense dC [S][T][ld]; this kernel writes EVERY frame of its sentence (zeros elsewhere), so
+// the caller does not clear the 100 MB tensor first, and it also leaves the per-sentence gradient in gmax [S][ld]
+// (the temporal convolution's bias gradient is its column sum -- 3 MB instead of a pass over dC).
 //   dx = g/norm - x (x.g)/(normp*norm)  with x = r = relu(max), then masked by r > 0.
 __global__ void __launch_bounds__(256)
 encoder_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ r, const unsigned char* __restrict__ arg,
-                   const float* __restrict__ normp, float* __restrict__ dC, int F, int ld, int T) {
+                   const float* __restrict__ normp, float* __restrict__ dC, float* __restrict__ gmax, int F, int ld, int T) {
   const int s = blockIdx.x;
   __shared__ float red[8];
   float xg = 0.f;
@@ -153,12 +155,20 @@ encoder_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ r, co
   xg = block_sum(xg, red);
   const float np = normp[s], nrm = sqrtf(np);
   const float k1 = 1.f / nrm, k2 = xg / (np * nrm);
-  for (int c = threadIdx.x; c < F; c += blockDim.x) {
-    float x = r[(size_t)s * ld + c];
-    if (x > 0.f) {
-      float g = dy[(size_t)s * ld + c] * k1 - x * k2;
-      dC[((size_t)s * T + arg[(size_t)s * ld + c]) * ld + c] = g;
+  for (int c4 = threadIdx.x * 4; c4 < ld; c4 += blockDim.x * 4) {
+    float g[4];
+    int at[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int c = c4 + j;
+      const float x = c < F ? r[(size_t)s * ld + c] : 0.f;
+      g[j] = x > 0.f ? dy[(size_t)s * ld + c] * k1 - x * k2 : 0.f;
+      at[j] = x > 0.f ? (int)arg[(size_t)s * ld + c] : -1;
     }
+    if (gmax) st4(gmax + (size_t)s * ld + c4, make_float4(g[0], g[1], g[2], g[3]));
+    for (int t = 0; t < T; ++t)
+      st4(dC + ((size_t)s * T + t) * ld + c4, make_float4(at[0] == t ? g[0] : 0.f, at[1] == t ? g[1] : 0.f,
+                                                         at[2] == t ? g[2] : 0.f, at[3] == t ? g[3] : 0.f));
   }
 }
 
@@ -211,10 +221,11 @@ int mpit_gesd_margin_bwd(const float* y, const int* qi, const int* ai, const flo
   return 0;
 }
 
-int mpit_encoder_bwd(const float* dy, const float* r, const unsigned char* arg, const float* normp, float* dC, int S,
-                     int F, int ld, int T, void* stream) {
+int mpit_encoder_bwd(const float* dy, const float* r, const unsigned char* arg, const float* normp, float* dC,
+                     float* gmax, int S, int F, int ld, int T, void* stream) {
   if (S <= 0) return 0;
-  encoder_bwd_kernel<<<S, 256, 0, (cudaStream_t)stream>>>(dy, r, arg, normp, dC, F, ld, T);
+  if (ld & 3) return MPIT_E_ARG;
+  encoder_bwd_kernel<<<S, 256, 0, (cudaStream_t)stream>>>(dy, r, arg, normp, dC, gmax, F, ld, T);
   MPIT_LAUNCH_CHECK();
   return 0;
 }

@@ -267,9 +267,11 @@ int mpit_gesd_pairs(const float* y, const int* qi, const int* ai, float* sim, fl
 /* MarginRankingCriterion (bicnn.lua:121) over triples (pairs 2t, 2t+1) fused with the GESD gradient. */
 int mpit_gesd_margin_bwd(const float* y, const int* qi, const int* ai, const float* sim, const float* stats, float* dy,
                          float* loss_sum, int triples, int F, int ld, float margin, void* stream);
-/* Backward of Normalize (closed form, cf. Normalize.lua:53-69) -> ReLU -> Max: scatter into dense dC[S][T][ld]. */
-int mpit_encoder_bwd(const float* dy, const float* r, const unsigned char* arg, const float* normp, float* dC, int S,
-                     int F, int ld, int T, void* stream);
+/* Backward of Normalize (closed form, cf. Normalize.lua:53-69) -> ReLU -> Max into the dense frame gradient
+ * dC[S][T][ld]: every element is written (zeros off the arg-max frame), no clearing needed.  gmax (optional,
+ * [S][ld]): the per-sentence gradient itself; its column sums are the temporal convolution's bias gradient. */
+int mpit_encoder_bwd(const float* dy, const float* r, const unsigned char* arg, const float* normp, float* dC,
+                     float* gmax, int S, int F, int ld, int T, void* stream);
 
 /* ---- bandwidth-path exchange through the bulk-copy engine (csrc/kernels/comm_bulk.cu) ----------- */
 /* Same semantics as mpit_param_pull / mpit_push_add / mpit_elastic_exchange, moved in 16 KiB

@@ -39,7 +39,12 @@ class BiCnnEngine:
         self.V, self.S, self.L, self.E, self.H, self.F, self.kw, self.margin = vocab, S, L, emb, hidden, filters, kw, margin
         self.dev = torch.device(device)
         dev = self.dev
-        self.Ep, self.Hp, self.Fp = _pad(emb, 32), _pad(hidden, 32), _pad(filters, 64)
+        # Operand paddings.  Wide layers are padded to 128 so that the big GEMMs run on 128-column tiles: with
+        # 32/64-column tiles every n-tile re-fetches the whole A operand (the temporal convolution's data gradient
+        # re-read 8192 x 6016 floats seven times: 187 us; forward 47 times at 64 columns) -- the 14 % extra K / N of
+        # the padding (200 -> 256, 3000 -> 3072) costs far less than that.
+        wide = lambda n: _pad(n, 128) if n >= 128 else _pad(n, 32)
+        self.Ep, self.Hp, self.Fp = _pad(emb, 32), wide(hidden), (_pad(filters, 128) if filters >= 128 else _pad(filters, 64))
         Ep, Hp, Fp = self.Ep, self.Hp, self.Fp
         self.k = kernels()
         # ---- flat <-> packed layout -------------------------------------------------------------
@@ -85,6 +90,7 @@ class BiCnnEngine:
         self.arg = torch.zeros(S * Fp, dtype=torch.uint8, device=dev)
         self.normp = torch.zeros(S, **f32)
         self.dy = torch.zeros(S * Fp, **f32)
+        self.gmax = torch.zeros(S * Fp, **f32)     # per-sentence gradient w.r.t. the max-over-time output
         self.dC = torch.zeros((R + 32) * Fp, **f32)
         self.dZ1 = torch.zeros(R * Hp, **f32)
         self.dEmb = torch.zeros(R * Ep, **f32)
@@ -105,6 +111,9 @@ class BiCnnEngine:
         rows_map = lambda t, C, box_n, sw=1: make_tmap(t.data_ptr(), [C, 1, 1, R], [C * 4, C * 4, C * 4], [32, 1, 1, box_n], sw)
         seq_map = lambda t, C, box_n, sw=1: make_tmap(t.data_ptr(), [C, L, 1, S], [C * 4, L * C * 4, L * C * 4],
                                                       [32, 32, 1, box_n], sw)
+        from ..ops.umma_ops import _pick_block
+        bn_f = _pick_block(Fp, (128, 64))          # temporal convolution forward / weight gradient tiles
+        bn_h = _pick_block(Hp, (128, 64, 32))      # its data gradient (N = hidden)
         # Linear + Tanh
         self.p_lin = IgemmLaunch(
             rows_map(self.emb, Ep, 128), weight_tmap(self._w("W1", Hp * Ep), Hp, Ep, 32),
@@ -113,16 +122,16 @@ class BiCnnEngine:
             1.0, self._w("b1", Hp), self.h, None, None, None, None, None, 32)
         # TemporalConvolution + Max over time + ReLU
         self.p_conv = IgemmLaunch(
-            seq_map(self.h, Hp, 4), weight_tmap(self._w("W2", Fp * kw * Hp), Fp, kw * Hp, 64),
+            seq_map(self.h, Hp, 4), weight_tmap(self._w("W2", Fp * kw * Hp), Fp, kw * Hp, bn_f),
             igemm_geom(nsub=1, tw=32, th=1, tn=4, tiles_w=tw_tiles, tiles_h=1, kw_it=kw, cb=Hp // 32,
                        num_kb=kw * Hp // 32, sgn=1, B=S, OH=1, OW=L, N=Fp, mode=EPI_MAXTIME),
-            1.0, self._w("b2", Fp), self.mx, None, None, None, self.frames, None, 64)
+            1.0, self._w("b2", Fp), self.mx, None, None, None, self.frames, None, bn_f)
         # data gradient of the temporal convolution, tanh' fused: dZ1 = (dC * Wd2) .* (1 - h^2)
         self.p_conv_dgrad = IgemmLaunch(
-            seq_map(self.dC, Fp, 4), weight_tmap(self._w("Wd2", Hp * kw * Fp), Hp, kw * Fp, 32),
+            seq_map(self.dC, Fp, 4), weight_tmap(self._w("Wd2", Hp * kw * Fp), Hp, kw * Fp, bn_h),
             igemm_geom(nsub=1, tw=32, th=1, tn=4, tiles_w=tw_tiles, tiles_h=1, kw_it=kw, cb=Fp // 32,
                        num_kb=kw * Fp // 32, sgn=-1, B=S, OH=1, OW=L, N=Hp, mode=EPI_MASK, relu=2),
-            1.0, None, self.dZ1, None, self.h, None, None, None, 32)
+            1.0, None, self.dZ1, None, self.h, None, None, None, bn_h)
         # data gradient of the Linear layer: dEmb = dZ1 * Wd1
         self.p_lin_dgrad = IgemmLaunch(
             rows_map(self.dZ1, Hp, 128), weight_tmap(self._w("Wd1", Ep * Hp), Ep, Hp, 32),
@@ -134,7 +143,7 @@ class BiCnnEngine:
         ceil = lambda a, b: (a + b - 1) // b
         nkb_c = ceil(S, 2) * tw_tiles
         self.w_conv = dict(tx=seq_map(self.h, Hp, 2, MN_SWIZZLE), tz=seq_map(self.dC, Fp, 2, MN_SWIZZLE),
-                           geom=G(32, 1, 2, tw_tiles, 1, kw, Hp // 32, kw * Hp // 32, nkb_c, S, Fp), block_n=64,
+                           geom=G(32, 1, 2, tw_tiles, 1, kw, Hp // 32, kw * Hp // 32, nkb_c, S, Fp), block_n=bn_f,
                            nsplit=min(4, nkb_c), chunks=kw * Hp // 32, N=Fp, gw=self._g("W2", Fp * kw * Hp))
         nkb_l = ceil(R, 64)
         self.w_lin = dict(tx=rows_map(self.emb, Ep, 64, MN_SWIZZLE), tz=rows_map(self.dZ1, Hp, 64, MN_SWIZZLE),
@@ -204,12 +213,13 @@ class BiCnnEngine:
         self.dy.zero_()
         check(k.mpit_gesd_margin_bwd(ptr(self.y), ptr(qi), ptr(ai), ptr(sim), ptr(stats), ptr(self.dy), ptr(self.loss_sum),
                                      P // 2, self.F, self.Fp, self.margin, st()), "mpit_gesd_margin_bwd")
-        self.dC.zero_()
-        check(k.mpit_encoder_bwd(ptr(self.dy), ptr(self.r), ptr(self.arg), ptr(self.normp), ptr(self.dC), self.S, self.F,
-                                 self.Fp, self.L, st()), "mpit_encoder_bwd")
+        # writes every frame of dC (no clearing of the 100 MB tensor) and the per-sentence gradient gmax
+        check(k.mpit_encoder_bwd(ptr(self.dy), ptr(self.r), ptr(self.arg), ptr(self.normp), ptr(self.dC), ptr(self.gmax),
+                                 self.S, self.F, self.Fp, self.L, st()), "mpit_encoder_bwd")
         R = self.S * self.L
-        # conv bias gradient = column sums of the frame gradient; conv weight gradient on tensor cores
-        colsum(self.dC, self._g("b2", self.Fp), R, self.Fp)
+        # conv bias gradient = column sums of the per-sentence gradient (each (sentence, filter) feeds one frame);
+        # conv weight gradient on tensor cores
+        colsum(self.gmax, self._g("b2", self.Fp), self.S, self.Fp)
         self._wgrad(self.w_conv)
         self.p_conv_dgrad.run(self.err)
         colsum(self.dZ1, self._g("b1", self.Hp), R, self.Hp)

@@ -151,6 +151,55 @@ def lib_nag():
 row("Nesterov apply + look-ahead (3.46M)", lambda: ops.local_step(x, v, g, clr=1e-2, mom_next=0.99, do_apply=True, use_mom=True,
                                                                     do_lookahead=True), lib_nag, "4 torch ops, graph")
 
+# ------------------------------------------------------------------------------------------------ BiCNN
+# one feval-shaped step of the answer-selection model at the reference's dimensions (plaunch.lua:46-53): S sentences
+# of up to 32 tokens = 64 questions, 64 positive and 128 sampled negative answers; encoder forward, GESD + margin
+# loss, full backward into the flat gradient
+from mpit_b200.models.bicnn import BiCNN, gesd, margin_ranking, pad_sentences  # noqa: E402
+from mpit_b200.models.bicnn_engine import BiCnnEngine  # noqa: E402
+
+V, E_, H_, F_, S = 22354, 100, 200, 3000, 256
+torch.manual_seed(1)
+bm = BiCNN(V, E_, H_, F_, 2)
+sents = [torch.randint(0, V, (int(k),)) for k in torch.randint(6, 31, (S,))]
+tokens, lens = pad_sentences(sents)
+q = torch.arange(0, 64).repeat_interleave(2)
+qi = torch.stack([q, q], 1).reshape(-1)[:256].int()            # (q,a+),(q,a-) pairs: 128 triples
+ai = torch.stack([64 + q, 128 + torch.arange(128)], 1).reshape(-1)[:256].int()
+theta = torch.cat([p_.detach().reshape(-1) for p_ in bm.param_list()]).to(dev)
+be = BiCnnEngine(V, S, 32, E_, H_, F_, 2, margin=0.5)
+be.load_flat(theta)
+tk, ln, qd, ad = tokens.to(dev).int(), lens.to(dev).int(), qi.to(dev), ai.to(dev)
+be.set_sentences(tk, ln)
+gflat = torch.zeros_like(theta)
+
+
+def ours_bicnn():
+    be.encode()
+    be.loss_backward(qd, ad, gflat)
+    be.flat_grad(gflat)
+
+
+bmd = bm.to(dev)
+tkl, lnl = tokens.to(dev), lens.to(dev)
+
+
+def lib_bicnn():
+    for p_ in bmd.parameters():
+        p_.grad = None
+    y = bmd.encode(tkl, lnl)
+    sim = gesd(y[qd.long()], y[ad.long()])
+    margin_ranking(sim[0::2], sim[1::2], 0.5).sum().backward()
+
+
+try:
+    o_t = timeit(ours_bicnn, iters=50, warm=5)
+    l_t = timeit(lib_bicnn, iters=50, warm=5)
+    rows.append(("BiCNN step, 256 sentences (fwd+loss+bwd)", o_t, l_t, "torch modules + autograd (cuBLAS TF32), eager both sides"))
+    print(f"BiCNN step: ours {o_t:.1f} us, torch {l_t:.1f} us", flush=True)
+except Exception as ex:      # keep the table even if this optional row fails
+    print("BiCNN row skipped:", repr(ex)[:300], flush=True)
+
 out = sys.argv[1] if len(sys.argv) > 1 else "gpurun_out/kernel_vs_library.md"
 os.makedirs(os.path.dirname(out) or ".", exist_ok=True)
 with open(out, "w") as f:
