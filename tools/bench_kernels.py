@@ -85,9 +85,19 @@ for i in range(3):
     y = F.conv2d(x, c.weight, c.bias)
     gy = torch.randn_like(y)
     if i > 0:
-        lib_d = lambda: torch.ops.aten.convolution_backward(gy, x, c.weight, None, (1, 1), (0, 0), (1, 1), False, (0, 0),
-                                                            1, (True, False, False))
-        row(names[i].split(" +")[0] + " dgrad (+unpool/mask)", lambda: pl.dgrad_stream[i].run(pl.err), lib_d, "cuDNN dgrad only, graph")
+        # the layer below: pre-activation z (2x the spatial size), a = relu(z), x = maxpool(a) with indices
+        zb = torch.randn(B, x.shape[1], 2 * x.shape[2], 2 * x.shape[3], device=dev).contiguous(memory_format=torch.channels_last)
+        ab = F.relu(zb)
+        _, ib = F.max_pool2d(ab, 2, return_indices=True)
+
+        def lib_d():
+            gx = torch.ops.aten.convolution_backward(gy, x, c.weight, None, (1, 1), (0, 0), (1, 1), False, (0, 0), 1,
+                                                     (True, False, False))[0]
+            ga = torch.ops.aten.max_pool2d_with_indices_backward(gx, ab, [2, 2], [2, 2], [0, 0], [1, 1], False, ib)
+            return torch.ops.aten.threshold_backward(ga, ab, 0.0)
+
+        row(names[i].split(" +")[0] + " dgrad + un-pool + ReLU mask", lambda: pl.dgrad_stream[i].run(pl.err), lib_d,
+            "cuDNN dgrad + max_pool backward + threshold backward, graph")
     lib_w = lambda: torch.ops.aten.convolution_backward(gy, x, c.weight, None, (1, 1), (0, 0), (1, 1), False, (0, 0), 1,
                                                         (False, True, False))
 
