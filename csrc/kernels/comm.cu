@@ -165,6 +165,16 @@ __global__ void __launch_bounds__(256) exchange_kernel(ExchArgs a) {
       // EX_ELASTIC / EX_FUSED
       float c[4] = {0.f, 0.f, 0.f, 0.f};
       if (a.do_sync) peer_load4(cptr, cnt, c);  // remote load in flight while we do the local step
+      // operand-copy slots of these four parameters: fetched now, used after the update (the dependent
+      // index -> store chain otherwise starts only once x is final)
+      int wslot[2][4];
+      const bool repack = MODE == EX_FUSED && a.wpk && a.wmap;
+      if (repack) {
+#pragma unroll
+        for (int m = 0; m < 2; ++m)
+#pragma unroll
+          for (int k = 0; k < 4; ++k) wslot[m][k] = (m < a.nmaps && k < cnt) ? a.wmap[(long long)m * a.n + i0 + k] : -1;
+      }
       float x[4], v[4] = {0.f, 0.f, 0.f, 0.f};
       load4(a.x, i0, cnt, x);
       if (a.use_mom) load4(a.v, i0, cnt, v);
@@ -195,7 +205,12 @@ __global__ void __launch_bounds__(256) exchange_kernel(ExchArgs a) {
         }
         store4(a.x, i0, cnt, x);
         if (a.use_mom) store4(a.v, i0, cnt, v);
-        if (a.wpk) {
+        if (repack && a.nmaps <= 2) {
+#pragma unroll
+          for (int m = 0; m < 2; ++m)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) if (wslot[m][k] >= 0) a.wpk[wslot[m][k]] = x[k];
+        } else if (a.wpk) {
 #pragma unroll
           for (int k = 0; k < 4; ++k) if (k < cnt) pack_store(a.wpk, a.wmap, a.nmaps, a.n, i0 + k, x[k]);
         }

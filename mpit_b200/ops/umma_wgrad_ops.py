@@ -2,6 +2,7 @@
 from __future__ import annotations
 
 import ctypes
+import os
 from dataclasses import dataclass
 from typing import Optional
 
@@ -46,7 +47,7 @@ class CifarWgradPlan:
         specs = [
             # tmap_x, tmap_dz, (tw,th,tn,tiles_w,tiles_h,kw_it,cb,total_chunks,num_kb,B,N), crop, block_n, nsplit
             (x0map, nhwc_tmap(dz[0], B, 24, 24, c1, 8, 8, 1), (8, 8, 1, 3, 3, 1, 1, 5, B * 9, B, c1), eng.crop,
-             min(64, pick(c1)), min(64, B * 9)),
+             min(64, pick(c1)), min(int(os.environ.get("MPIT_WGRAD1_NSPLIT", "64")), B * 9)),
             (nhwc_tmap(act[0], B, 12, 12, c1, 8, 8, 1), nhwc_tmap(dz[1], B, 8, 8, c2, 8, 8, 1),
              (8, 8, 1, 1, 1, 5, c1 // 32, 25 * c1 // 32, B, B, c2), None, pick(c2), min(8, B)),
             (nhwc_tmap(act[1], B, 4, 4, c2, 2, 2, 16), nhwc_tmap(dz[2], B, 2, 2, c3, 2, 2, 16),
