@@ -6,6 +6,10 @@ The weight matrix ``W [out, in]`` is row-sharded over the ranks' symmetric memor
 ``out % S == 0``).  ``forward`` launches ONE tcgen05 kernel whose B-operand TMA loads read every weight
 tile from its owner's shard over NVLink while the tensor cores work on earlier tiles; no copy of W is
 ever materialised locally.  The un-fused formulation is ``ShardedCenter.pull`` followed by a GEMM.
+
+Measured (tools/bench_pulled_linear.py): 1.5-3.4x faster than NCCL all_gather + cuBLAS at 2 and 8
+GPUs while the batch is one or two 128-row tiles; every further M-tile fetches its weight tiles again, so for
+M >= 512 the un-fused form wins (cluster multicast across M-tiles is the missing piece).
 """
 from __future__ import annotations
 

@@ -1,0 +1,85 @@
+#!/usr/bin/env python
+"""all-gather -> GEMM as ONE kernel (weights fetched from their owners' shards by the GEMM's own TMA loads) against
+the un-fused formulations, device-timed, max over ranks.
+
+    torchrun --nproc-per-node N tools/bench_pulled_linear.py [out.jsonl]
+"""
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F
+
+from mpit_b200._native import check, cur_stream, kernels, ptr
+from mpit_b200.ops.pulled_linear import PulledLinear
+from mpit_b200.parallel import SymmetricHeap
+
+torch.backends.cuda.matmul.allow_tf32 = True
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dev = torch.device("cuda", local)
+dist.init_process_group("nccl", device_id=dev)
+heap = SymmetricHeap(dev)
+out_path = sys.argv[1] if len(sys.argv) > 1 else None
+rows = []
+
+
+def timed(fn, iters=30, warm=5):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / iters * 1e3], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t)
+
+
+for (M, K, N) in [(128, 1024, 4096), (128, 4096, 4096), (512, 1024, 4096), (128, 256, 2048)]:
+    if N % (64 * world):
+        continue
+    lin = PulledLinear(heap, K, N, M, act=1)
+    rpo = N // world
+    lin.weight_rows().copy_(torch.randn(rpo, K, device=dev) * 0.02)
+    bias = torch.randn(N, device=dev) * 0.1
+    x = torch.randn(M, K, device=dev)
+    lin.forward(x, bias)
+    torch.cuda.synchronize()
+    dist.barrier()
+
+    def fused():
+        check(kernels().mpit_umma_linear_pull(lin._ta, lin._maps, lin.S, lin.rows_per_owner, lin._geom, ptr(bias), ptr(lin.y),
+                                              ptr(lin.err), lin.block_n, cur_stream()), "mpit_umma_linear_pull")
+
+    wfull = torch.empty(N, K, device=dev)
+    wmine = lin.weight_rows()
+
+    def nccl_then_cublas():
+        dist.all_gather_into_tensor(wfull, wmine)
+        return F.relu(F.linear(x, wfull, bias))
+
+    t_f, t_u = timed(fused), timed(nccl_then_cublas)
+    t_g = timed(lambda: F.relu(F.linear(x, wfull, bias)))
+    assert int(lin.err.item()) == 0
+    ref = F.relu(F.linear(x, wfull, bias))
+    rel = float((lin.y.view(lin.M, N)[:M] - ref).norm() / ref.norm())
+    r = {"M": M, "K": K, "N": N, "n_gpus": world, "weight_MB": round(N * K * 4 / 2 ** 20, 1), "fused_us": round(t_f, 1),
+         "nccl_allgather_plus_cublas_us": round(t_u, 1), "cublas_gemm_alone_us": round(t_g, 1), "rel_err_vs_cublas": rel}
+    rows.append(r)
+    if rank == 0:
+        print(json.dumps(r), flush=True)
+heap.check_timeout()
+if rank == 0 and out_path:
+    with open(out_path, "w") as f:
+        for r in rows:
+            f.write(json.dumps(r) + "\n")
+dist.barrier()
+dist.destroy_process_group()
