@@ -18,7 +18,7 @@ import ctypes
 import torch
 
 from .._native import kernels, check, ptr, cur_stream
-from .umma_ops import make_tmap, igemm_geom, EPI_STORE
+from .umma_ops import make_tmap, igemm_geom, weight_tmap, EPI_STORE
 
 
 class PulledLinear:
@@ -44,14 +44,37 @@ class PulledLinear:
         self._geom = igemm_geom(nsub=1, tw=1, th=1, tn=128, tiles_w=1, tiles_h=1, kw_it=1, cb=in_features // 32,
                                 num_kb=in_features // 32, sgn=1, B=self.M, OH=1, OW=1, N=out_features,
                                 mode=EPI_STORE, relu=act)
+        # Un-fused fallback for batches of more than FUSED_MAX_TILES 128-row tiles (every M-tile of the fused kernel
+        # fetches its weight tiles over NVLink again): gather W once with in-kernel peer loads, then a local GEMM.
+        self._wfull = None
+        self._tb_local = None
+
+    FUSED_MAX_TILES = 2
+
+    def _forward_unfused(self, bias):
+        k = kernels()
+        if self._wfull is None:
+            self._wfull = torch.empty(self.N * self.K, device=self.x.device)
+            self._tb_local = weight_tmap(self._wfull, self.N, self.K, self.block_n)
+        n = self.rows_per_owner * self.K
+        for r, p in enumerate(self.shard.ptrs):                       # MPI_Get of every owner's rows (ld.sys over NVLink)
+            check(k.mpit_peer_rma(1, p, self._wfull.data_ptr() + 4 * r * n, n, 1.0, cur_stream()), "mpit_peer_rma")
+        check(k.mpit_umma_igemm(self._ta, self._tb_local, self._geom, 1.0, ptr(bias), ptr(self.y), None, None, None, None,
+                                None, ptr(self.err), None, self.block_n, cur_stream()), "mpit_umma_igemm")
 
     def weight_rows(self) -> torch.Tensor:
         """This rank's rows of W, as a [rows_per_owner, in] view of its symmetric shard."""
         return self.shard.local[:self.rows_per_owner * self.K].view(self.rows_per_owner, self.K)
 
-    def forward(self, x: torch.Tensor, bias: torch.Tensor = None) -> torch.Tensor:
+    def forward(self, x: torch.Tensor, bias: torch.Tensor = None, fused: bool = None) -> torch.Tensor:
+        """``fused=None``: the fused kernel for up to FUSED_MAX_TILES row tiles, gather + GEMM beyond."""
         m = x.shape[0]
         self.x[:m * self.K].copy_(x.reshape(-1))
+        if fused is None:
+            fused = (m + 127) // 128 <= self.FUSED_MAX_TILES
+        if not fused:
+            self._forward_unfused(bias)
+            return self.y.view(self.M, self.N)[:m]
         check(kernels().mpit_umma_linear_pull(self._ta, self._maps, self.S, self.rows_per_owner, self._geom, ptr(bias),
                                               ptr(self.y), ptr(self.err), self.block_n, cur_stream()),
               "mpit_umma_linear_pull")

@@ -217,6 +217,12 @@ def case_pulled_linear(rank, world, dev, heap):
     torch.cuda.synchronize()
     ref2 = torch.relu(x @ (2 * W).t())
     assert float((y2.cpu() - ref2).norm() / ref2.norm()) < 3e-3
+    # the un-fused fallback (gather with in-kernel peer loads, then a local GEMM) gives the same result
+    y3 = lin.forward(x.to(dev), None, fused=False)
+    torch.cuda.synchronize()
+    assert int(lin.err.item()) == 0
+    assert float((y3.cpu() - ref2).norm() / ref2.norm()) < 3e-3
+    sync(dev)
 
 
 def case_window(rank, world, dev, heap):

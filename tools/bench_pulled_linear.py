@@ -67,11 +67,12 @@ for (M, K, N) in [(128, 1024, 4096), (128, 4096, 4096), (512, 1024, 4096), (128,
         return F.relu(F.linear(x, wfull, bias))
 
     t_f, t_u = timed(fused), timed(nccl_then_cublas)
+    t_own = timed(lambda: lin._forward_unfused(bias))
     t_g = timed(lambda: F.relu(F.linear(x, wfull, bias)))
     assert int(lin.err.item()) == 0
     ref = F.relu(F.linear(x, wfull, bias))
     rel = float((lin.y.view(lin.M, N)[:M] - ref).norm() / ref.norm())
-    r = {"M": M, "K": K, "N": N, "n_gpus": world, "weight_MB": round(N * K * 4 / 2 ** 20, 1), "fused_us": round(t_f, 1),
+    r = {"M": M, "K": K, "N": N, "n_gpus": world, "weight_MB": round(N * K * 4 / 2 ** 20, 1), "fused_us": round(t_f, 1), "own_gather_then_gemm_us": round(t_own, 1),
          "nccl_allgather_plus_cublas_us": round(t_u, 1), "cublas_gemm_alone_us": round(t_g, 1), "rel_err_vs_cublas": rel}
     rows.append(r)
     if rank == 0:
