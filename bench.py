@@ -28,33 +28,43 @@ METRIC = "samples/sec (device-timed, max over ranks) CIFAR-10 CNN EAMSGD tau=10"
 
 
 def _clock_sampler(path):
-    q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+    q = ("index,timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
     try:
         f = open(path, "w")
-        return subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "100"],
+        return subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "20"],
                                 stdout=f, stderr=subprocess.DEVNULL), f
     except Exception:
         return None, None
 
 
-def _clock_summary(path, dev_index):
-    sm, mx, reasons = [], 0.0, set()
+def _clock_summary(path, dev_index, t_lo=None, t_hi=None):
+    """Median SM clock and throttle reasons of the samples taken INSIDE the timed region [t_lo, t_hi] (datetime
+    objects; nvidia-smi stamps every sample).  Falls back to all samples if the region was too short to catch one."""
+    import datetime
+    rows = []
     try:
         for line in open(path):
             p = [s.strip() for s in line.split(",")]
-            if len(p) < 9 or not p[0].isdigit() or int(p[0]) != dev_index:
+            if len(p) < 10 or not p[0].isdigit() or int(p[0]) != dev_index:
                 continue
-            sm.append(float(p[1]))
-            mx = max(mx, float(p[2]))
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), p[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
+            try:
+                ts = datetime.datetime.strptime(p[1], "%Y/%m/%d %H:%M:%S.%f")
+            except ValueError:
+                ts = None
+            rows.append((ts, float(p[2]), float(p[3]), p[6:10]))
     except Exception:
         pass
+    inside = [r for r in rows if r[0] is not None and t_lo is not None and t_lo <= r[0] <= t_hi]
+    use = inside or rows
+    sm, mx, reasons = [r[1] for r in use], max([r[2] for r in use], default=0.0), set()
+    for r in use:
+        for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3]):
+            if v.lower().startswith("active"):
+                reasons.add(name)
     return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx or None,
-            "reasons": sorted(reasons), "samples": len(sm)}
+            "reasons": sorted(reasons), "samples": len(sm), "samples_inside_timed_region": len(inside)}
 
 
 def run_reference_arm(args):
@@ -69,7 +79,7 @@ def run_reference_arm(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--steps", type=int, default=2000)
     ap.add_argument("--warmup", type=int, default=30)
     ap.add_argument("--impl", default="mpit", help="mpit (this framework) | reference | torch (library-call baseline)")
     ap.add_argument("--kernels", default=os.environ.get("MPIT_KERNELS", "auto"), help="umma | ref | auto")
@@ -159,6 +169,8 @@ def main():
     sampler, fh = _clock_sampler(clk_path) if rank == 0 else (None, None)
     time.sleep(0.3 if sampler else 0.0)
     barrier()
+    import datetime
+    t_lo = datetime.datetime.now()
     l0 = launches.count
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
@@ -180,6 +192,7 @@ def main():
     last = tr.last_loss()
     barrier()
     e2e_s = time.perf_counter() - t0
+    t_hi = datetime.datetime.now()
     if sampler:
         sampler.terminate()
         fh.close()
@@ -211,7 +224,7 @@ def main():
                     "h2d_bytes_per_step": int(tr.h2d_bytes), "d2h_bytes_per_step": int(tr.d2h_bytes),
                     "timing": "wall clock around CifarTrainer.train_step, max over ranks"},
             "gpu_launches": int(n_launch),
-            "clocks": _clock_summary(clk_path, local_rank),
+            "clocks": _clock_summary(clk_path, local_rank, t_lo, t_hi),
             "loss": {"device_arm_last": round(loss_dev, 4), "e2e_arm_last": round(last, 4)},
             "exchange_bytes_per_sync": 2 * 4 * n_params,
         }
