@@ -832,6 +832,31 @@ int mpit_msg_comm_split(int comm, int color, int key, int* newcomm) {
 
 int mpit_msg_comm_dup(int comm, int* newcomm) { return mpit_msg_comm_split(comm, 0, 0, newcomm); }
 
+// A communicator from an explicit list of world ranks, created WITHOUT communication: every member
+// calls with the same list and the same seed (agreed beforehand, e.g. by the leaders of an
+// inter-communicator handshake).  Callers that are not in the list get COMM_NULL.
+int mpit_msg_comm_from_ranks(const int* world_ranks, int n, int seed, int* newcomm) {
+  if (!g.inited) return MPIT_ERR_OTHER;
+  if (n <= 0) return MPIT_ERR_ARG;
+  Comm nc;
+  for (int i = 0; i < n; ++i) {
+    if (world_ranks[i] < 0 || world_ranks[i] >= g.size) return MPIT_ERR_RANK;
+    if (std::find(nc.ranks.begin(), nc.ranks.end(), world_ranks[i]) != nc.ranks.end()) return MPIT_ERR_ARG;
+    nc.ranks.push_back(world_ranks[i]);
+  }
+  auto me = std::find(nc.ranks.begin(), nc.ranks.end(), g.rank);
+  if (me == nc.ranks.end()) { *newcomm = MPIT_COMM_NULL; return MPIT_SUCCESS; }
+  nc.my = (int)(me - nc.ranks.begin());
+  // wire ids of split communicators carry bit 28; these carry bit 27 and leave bit 28 clear
+  nc.id = (int)(((uint32_t)seed * 2654435761u) & 0x07FFFFFFu) | 0x08000000;
+  std::lock_guard<std::mutex> lk(g.mu);
+  for (auto& kv : g.comms) if (kv.second.id == nc.id) return MPIT_ERR_OTHER;   // seed already in use here
+  int h = g.next_comm++;
+  g.comms[h] = nc;
+  *newcomm = h;
+  return MPIT_SUCCESS;
+}
+
 int mpit_msg_comm_free(int* comm) {
   std::lock_guard<std::mutex> lk(g.mu);
   if (*comm == MPIT_COMM_WORLD || *comm == MPIT_COMM_SELF) return MPIT_ERR_COMM;
@@ -896,6 +921,21 @@ int mpit_msg_test(int* request, int* flag, mpit_status* status) {
     free_req_locked(r->id);
     *request = MPIT_REQUEST_NULL;
     return err;
+  }
+  return MPIT_SUCCESS;
+}
+
+int mpit_msg_request_get_status(int request, int* flag, mpit_status* status) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  if (request == MPIT_REQUEST_NULL) { *flag = 1; return MPIT_SUCCESS; }
+  auto it = g.reqs.find(request);
+  if (it == g.reqs.end()) return MPIT_ERR_REQUEST;
+  Req* r = it->second.get();
+  *flag = r->done ? 1 : 0;
+  if (r->done) {
+    Comm* c = nullptr;
+    for (auto& kv : g.comms) if (kv.second.id == (r->comm & ~(kCollBit | kNbcBit))) { c = &kv.second; break; }
+    fill_status(status, r, c);
   }
   return MPIT_SUCCESS;
 }

@@ -32,6 +32,15 @@ extern "C" {
 #define MPIT_ERR_TRUNCATE 15
 #define MPIT_ERR_OTHER 16
 #define MPIT_ERR_INTERN 17
+/* classes of the MPI-IO chapter (csrc/msg/hostio.cpp) */
+#define MPIT_ERR_ACCESS 20
+#define MPIT_ERR_AMODE 21
+#define MPIT_ERR_FILE_EXISTS 25
+#define MPIT_ERR_FILE 27
+#define MPIT_ERR_IO 32
+#define MPIT_ERR_NO_SPACE 36
+#define MPIT_ERR_NO_SUCH_FILE 37
+#define MPIT_ERR_READ_ONLY 40
 
 /* datatypes (/root/reference/lua-mpi.h:130-151) */
 enum { MPIT_BYTE = 0, MPIT_CHAR = 1, MPIT_SHORT = 2, MPIT_INT = 3, MPIT_LONG = 4, MPIT_FLOAT = 5,
@@ -68,6 +77,9 @@ int mpit_msg_type_size(int dtype, int* size);
 int mpit_msg_comm_rank(int comm, int* rank);
 int mpit_msg_comm_size(int comm, int* size);
 int mpit_msg_comm_dup(int comm, int* newcomm);
+/* Non-collective: a communicator over an explicit world-rank list; all members pass the same list and
+ * seed.  Used for inter-communicator bridges (MPI_Intercomm_create, MPI_Comm_accept / connect). */
+int mpit_msg_comm_from_ranks(const int* world_ranks, int n, int seed, int* newcomm);
 int mpit_msg_comm_split(int comm, int color, int key, int* newcomm);
 int mpit_msg_comm_free(int* comm);
 
@@ -88,6 +100,9 @@ int mpit_msg_waitany(int n, int* requests, int* index, mpit_status* status);
 int mpit_msg_cancel(int* request);
 int mpit_msg_test_cancelled(const mpit_status* status, int* flag);
 int mpit_msg_request_free(int* request);
+/* MPI_Request_get_status: completion flag and status WITHOUT releasing the request
+ * (/root/reference/mpifuncs.c Request_get_status). */
+int mpit_msg_request_get_status(int request, int* flag, mpit_status* status);
 int mpit_msg_get_count(const mpit_status* status, int dtype, long long* count);
 
 /* ---- collectives ------------------------------------------------------------------------------------ */
@@ -107,6 +122,36 @@ int mpit_msg_scan(const void* sbuf, void* rbuf, long long count, int dtype, int 
 /* ---- introspection (tests, tracing) ------------------------------------------------------------------- */
 /* stats8: {msgs_sent, bytes_sent, msgs_recv, bytes_recv, unexpected_now, posted_now, requests_live, 0} */
 int mpit_msg_stats(long long* stats8);
+
+/* ---- derived-datatype engine (csrc/msg/hostio.cpp; /root/reference/mpifuncs.c Pack, Unpack, Type_*) --------
+ * A committed type is `nblk` byte blocks {disp[i], len[i]} in type-map order, replicated every `extent`
+ * bytes.  pack gathers `count` replicas from `base` into the contiguous stream `out`; unpack scatters.
+ * `limit` bounds the stream bytes moved; the number moved is returned. */
+long long mpit_dt_pack(const void* base, long long count, long long extent, int nblk, const long long* disp,
+                       const long long* len, void* out, long long limit);
+long long mpit_dt_unpack(void* base, long long count, long long extent, int nblk, const long long* disp,
+                         const long long* len, const void* in, long long limit);
+
+/* ---- file IO under MPI-IO semantics (csrc/msg/hostio.cpp; /root/reference/mpifuncs.c:557-1080) ------------
+ * amode bits as in MPI (1 RDONLY, 2 RDWR, 4 WRONLY, 8 CREATE, 16 EXCL, 128 APPEND).  Offsets are bytes. */
+int mpit_io_open(const char* path, int amode, int* fd);
+int mpit_io_close(int fd);
+int mpit_io_delete(const char* path);
+int mpit_io_get_size(int fd, long long* size);
+int mpit_io_set_size(int fd, long long size);
+int mpit_io_preallocate(int fd, long long size);
+int mpit_io_sync(int fd);
+int mpit_io_lock(int fd, int mode);   /* 0 unlock, 1 shared, 2 exclusive (atomic mode) */
+int mpit_io_rw(int fd, int write, void* buf, long long nbytes, long long offset, long long* moved);
+/* transfer through a view: tiles of `fextent` bytes starting at `view_disp`, each exposing blocks
+ * {fdisp[i], flen[i]} (`fsize` visible bytes per tile); `pos` counts visible bytes from the view start */
+int mpit_io_view_rw(int fd, int write, void* buf, long long nbytes, long long view_disp, long long fextent,
+                    int nblk, const long long* fdisp, const long long* flen, long long fsize, long long pos,
+                    long long* moved);
+int mpit_io_view_byte_offset(long long view_disp, long long fextent, int nblk, const long long* fdisp,
+                             const long long* flen, long long fsize, long long pos, long long* byte_off);
+/* shared file pointer kept in a side-car file: op 0 fetch-and-add, 1 set, 2 read */
+int mpit_io_shared_pointer(int sidecar_fd, int op, long long value, long long* old);
 
 #ifdef __cplusplus
 }

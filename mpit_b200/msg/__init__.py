@@ -6,8 +6,12 @@ Comm_rank, Comm_size, Send, Recv, Isend, Irecv, Iprobe, Test, Wait, Cancel, Test
 Allreduce, Iallreduce, Request, Status`` and ``FLOAT, LONG, BYTE, SUM, COMM_WORLD``.
 This module provides those, plus ``Bcast, Barrier, Probe, Sendrecv, Reduce, Gather, Allgather,
 Scatter, Alltoall, Scan, Reduce_scatter_block, Waitall, Testall, Waitany, Wtime, Wtick, Comm_dup,
-Comm_split, Comm_free, Get_count, Get_processor_name, Abort, Init_MTF/MTS/MTM``.  MPI-IO, topology
-and derived datatypes (wrapped but never called in the reference) are out of scope.
+Comm_split, Comm_free, Get_count, Get_processor_name, Abort, Init_MTF/MTS/MTM`` natively, and re-exports
+the remaining chapters of the binding from its sibling modules: ``extras`` (send modes, persistent requests,
+vector collectives, groups, user ops, fence windows), ``datatypes`` (derived datatypes, Pack/Unpack),
+``fileio`` (MPI-IO), ``topo`` (cartesian / graph topologies), ``attrs`` (keyvals, error handlers, Info,
+generalized requests), ``rma`` (post/start/complete/wait) and ``dynproc`` (inter-communicators, ports,
+name service).  ``tools/mpi_coverage.py`` checks the result against the reference's 270 spec files.
 
 Buffers are torch tensors or numpy arrays.  Where the reference passes a Torch *Storage* and reads
 ``storage->data`` with no type or bounds check (/root/reference/lua-mpi.h:70-76), this layer checks
@@ -89,6 +93,7 @@ class Request:
         self._arr = (ctypes.c_int * n)(*([REQUEST_NULL] * n))
         self._after: List[Optional[callable]] = [None] * n   # completion hooks (device staging)
         self._keep: List[object] = [None] * n                # buffers that must outlive the transfer
+        self._unroute: List[int] = [0] * n                   # inter-communicator source offset of a receive
 
     def __len__(self):
         return len(self._arr)
@@ -115,6 +120,12 @@ class _Buf:
 
     def __init__(self, obj, count: int, dtype: int, writable: bool):
         self.after = None
+        self.count, self.dtype = count, dtype          # what the native layer is told (bytes for a derived type)
+        if dtype >= datatypes.DERIVED_BASE:
+            stream, self.after = datatypes.stage_for_message(obj, count, dtype, writable)
+            self.ptr, self.keep = ctypes.c_void_p(stream.ctypes.data), (obj, stream)
+            self.count, self.dtype = stream.size, BYTE
+            return
         es = _DTYPE_SIZE[dtype]
         nbytes = count * es
         if obj is None:
@@ -235,12 +246,15 @@ def Get_processor_name() -> str:
 
 
 def Comm_rank(comm: int = COMM_WORLD) -> int:
+    """Rank in ``comm`` (in the LOCAL group of an inter-communicator)."""
+    comm = getattr(comm, "local_comm", comm)
     r = ctypes.c_int(0)
     _chk(host().mpit_msg_comm_rank(comm, ctypes.byref(r)), "Comm_rank")
     return r.value
 
 
 def Comm_size(comm: int = COMM_WORLD) -> int:
+    comm = getattr(comm, "local_comm", comm)
     r = ctypes.c_int(0)
     _chk(host().mpit_msg_comm_size(comm, ctypes.byref(r)), "Comm_size")
     return r.value
@@ -252,8 +266,13 @@ get_size = Comm_size
 
 
 def Comm_dup(comm: int) -> int:
+    """Duplicates the communicator together with its cached attributes (through their copy callbacks) and its
+    topology."""
     r = ctypes.c_int(0)
     _chk(host().mpit_msg_comm_dup(comm, ctypes.byref(r)), "Comm_dup")
+    attrs.copy_attrs("comm", comm, r.value)
+    if comm in topo._TOPO:
+        topo._TOPO[r.value] = dict(topo._TOPO[comm])
     return r.value
 
 
@@ -263,62 +282,92 @@ def Comm_split(comm: int, color: int, key: int) -> int:
     return r.value
 
 
-def Comm_free(comm: int) -> None:
+def Comm_free(comm) -> None:
+    if isinstance(comm, dynproc.Intercomm):
+        dynproc.Comm_disconnect(comm)
+        return
     c = ctypes.c_int(comm)
     _chk(host().mpit_msg_comm_free(ctypes.byref(c)), "Comm_free")
+    attrs.drop_object("comm", comm)
+    topo.forget(comm)
 
 
 # ---- point to point ---------------------------------------------------------------------------------------
+def _unroute(status: Optional["Status"], offset: int) -> None:
+    """Sources reported on an inter-communicator are ranks of the remote group."""
+    if status is not None and offset and status[0].source >= 0:
+        status[0].source -= offset
+
+
 def Send(buf, count: int, dtype: int, dest: int, tag: int, comm: int = COMM_WORLD) -> None:
+    """``dtype`` may be a committed derived datatype (the message travels packed); ``comm`` may be an
+    inter-communicator (``dest`` is then a rank of the remote group)."""
+    comm, dest, _ = dynproc.route(comm, dest)
     b = _Buf(buf, count, dtype, False)
-    _chk(host().mpit_msg_send(b.ptr, count, dtype, dest, tag, comm), "Send")
+    _chk(host().mpit_msg_send(b.ptr, b.count, b.dtype, dest, tag, comm), "Send")
 
 
 def Recv(buf, count: int, dtype: int, source: int, tag: int, comm: int = COMM_WORLD,
          status: Optional[Status] = None) -> None:
+    comm, source, off = dynproc.route(comm, source)
     b = _Buf(buf, count, dtype, True)
-    _chk(host().mpit_msg_recv(b.ptr, count, dtype, source, tag, comm, status._ptr() if status else None), "Recv")
+    _chk(host().mpit_msg_recv(b.ptr, b.count, b.dtype, source, tag, comm, status._ptr() if status else None), "Recv")
+    _unroute(status, off)
     if b.after:
         b.after()
 
 
 def Isend(buf, count: int, dtype: int, dest: int, tag: int, comm: int, request: Request, i: int = 0) -> None:
+    comm, dest, _ = dynproc.route(comm, dest)
     b = _Buf(buf, count, dtype, False)
     request._keep[i] = b.keep
-    _chk(host().mpit_msg_isend(b.ptr, count, dtype, dest, tag, comm, request._ptr(i)), "Isend")
+    _chk(host().mpit_msg_isend(b.ptr, b.count, b.dtype, dest, tag, comm, request._ptr(i)), "Isend")
 
 
 def Irecv(buf, count: int, dtype: int, source: int, tag: int, comm: int, request: Request, i: int = 0) -> None:
+    comm, source, off = dynproc.route(comm, source)
     b = _Buf(buf, count, dtype, True)
     request._keep[i], request._after[i] = b.keep, b.after
-    _chk(host().mpit_msg_irecv(b.ptr, count, dtype, source, tag, comm, request._ptr(i)), "Irecv")
+    request._unroute[i] = off
+    _chk(host().mpit_msg_irecv(b.ptr, b.count, b.dtype, source, tag, comm, request._ptr(i)), "Irecv")
 
 
 def Sendrecv(sbuf, scount, sdtype, dest, stag, rbuf, rcount, rdtype, source, rtag, comm=COMM_WORLD,
              status: Optional[Status] = None) -> None:
+    native, dest, off = dynproc.route(comm, dest)
+    _, source, _ = dynproc.route(comm, source)
     s, r = _Buf(sbuf, scount, sdtype, False), _Buf(rbuf, rcount, rdtype, True)
-    _chk(host().mpit_msg_sendrecv(s.ptr, scount, sdtype, dest, stag, r.ptr, rcount, rdtype, source, rtag, comm,
+    _chk(host().mpit_msg_sendrecv(s.ptr, s.count, s.dtype, dest, stag, r.ptr, r.count, r.dtype, source, rtag, native,
                                   status._ptr() if status else None), "Sendrecv")
+    _unroute(status, off)
     if r.after:
         r.after()
 
 
 def Iprobe(source: int, tag: int, comm: int = COMM_WORLD, status: Optional[Status] = None) -> bool:
+    comm, source, off = dynproc.route(comm, source)
     f = ctypes.c_int(0)
     _chk(host().mpit_msg_iprobe(source, tag, comm, ctypes.byref(f), status._ptr() if status else None), "Iprobe")
+    if f.value:
+        _unroute(status, off)
     return bool(f.value)
 
 
 def Probe(source: int, tag: int, comm: int = COMM_WORLD, status: Optional[Status] = None) -> None:
+    comm, source, off = dynproc.route(comm, source)
     _chk(host().mpit_msg_probe(source, tag, comm, status._ptr() if status else None), "Probe")
+    _unroute(status, off)
 
 
 def Test(request: Request, status: Optional[Status] = None, i: int = 0) -> bool:
     """MPI_Test: True when complete (the handle becomes REQUEST_NULL).  A truncated receive raises."""
+    if isinstance(request, attrs.GeneralizedRequest):
+        return request.test(status)
     st = status or Status()
     f = ctypes.c_int(0)
     code = host().mpit_msg_test(request._ptr(i), ctypes.byref(f), st._ptr())
     if f.value and not st.cancelled:
+        _unroute(st, request._unroute[i])
         request._finish(i)
     elif f.value:
         request._after[i] = request._keep[i] = None
@@ -327,9 +376,14 @@ def Test(request: Request, status: Optional[Status] = None, i: int = 0) -> bool:
 
 
 def Wait(request: Request, status: Optional[Status] = None, i: int = 0) -> None:
+    if isinstance(request, attrs.GeneralizedRequest):
+        return request.wait(status)
     st = status or Status()
+    was_live = not request.is_null(i)
     code = host().mpit_msg_wait(request._ptr(i), st._ptr())
     if not st.cancelled:
+        if was_live:
+            _unroute(st, request._unroute[i])
         request._finish(i)
     else:
         request._after[i] = request._keep[i] = None
@@ -365,6 +419,8 @@ def Waitany(request: Request, status: Optional[Status] = None) -> int:
 
 
 def Cancel(request: Request, i: int = 0) -> None:
+    if isinstance(request, attrs.GeneralizedRequest):
+        return request.cancel()
     _chk(host().mpit_msg_cancel(request._ptr(i)), "Cancel")
 
 
@@ -375,6 +431,9 @@ def Test_cancelled(status: Status) -> bool:
 
 
 def Get_count(status: Status, dtype: int) -> int:
+    """Whole elements of ``dtype`` received (UNDEFINED when the byte count is not a multiple of its size)."""
+    if dtype >= datatypes.DERIVED_BASE:
+        return datatypes.count_from_bytes(int(status[0].count_bytes), dtype)
     c = ctypes.c_longlong(0)
     _chk(host().mpit_msg_get_count(status._ptr(), dtype, ctypes.byref(c)), "Get_count")
     return c.value
@@ -387,9 +446,9 @@ def Barrier(comm: int = COMM_WORLD) -> None:
 
 def Bcast(buf, count: int, dtype: int, root: int, comm: int = COMM_WORLD) -> None:
     b = _Buf(buf, count, dtype, True)
-    if b.after and Comm_rank(comm) == root:   # root's device data must be staged out first
-        b.keep[1].copy_(b.keep[0].view(-1)[:b.keep[1].numel()])
-    _chk(host().mpit_msg_bcast(b.ptr, count, dtype, root, comm), "Bcast")
+    if b.after and Comm_rank(comm) == root and dtype < datatypes.DERIVED_BASE:
+        b.keep[1].copy_(b.keep[0].view(-1)[:b.keep[1].numel()])   # root's device data must be staged out first
+    _chk(host().mpit_msg_bcast(b.ptr, b.count, b.dtype, root, comm), "Bcast")
     if b.after:
         b.after()
 
@@ -495,4 +554,13 @@ from ..aio import (aio_send, aio_recv, co_execute, co_ping, co_wait, Queue)  # n
 # windows, error classes ...), composed from the calls above: see msg/extras.py ----
 from . import extras  # noqa: E402
 from .extras import *  # noqa: E402,F401,F403
+# ---- the remaining chapters: derived datatypes, MPI-IO, topologies, caching / error handlers / Info, PSCW windows,
+# inter-communicators and ports ----
+from . import attrs, datatypes, dynproc, fileio, rma, topo  # noqa: E402
+from .attrs import *  # noqa: E402,F401,F403
+from .datatypes import *  # noqa: E402,F401,F403
+from .dynproc import *  # noqa: E402,F401,F403
+from .fileio import *  # noqa: E402,F401,F403
+from .rma import *  # noqa: E402,F401,F403
+from .topo import *  # noqa: E402,F401,F403
 from .extras import (PROC_NULL, ROOT, IDENT, CONGRUENT, SIMILAR, UNEQUAL, LXOR, BXOR, GROUP_EMPTY)  # noqa: E402,F401

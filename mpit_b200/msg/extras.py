@@ -5,8 +5,9 @@
 binding could reasonably have reached for -- send modes, persistent requests, Test/Wait-some/any, the vector
 collectives, Exscan/Reduce_scatter, groups and communicator construction, user reduction ops, error classes,
 environment queries, and fence-synchronised one-sided windows -- as thin Python compositions of the native
-point-to-point and collective calls.  MPI-IO, topologies, derived datatypes and dynamic processes stay out of scope
-("wrapped but unused").
+point-to-point and collective calls.  The other chapters live beside it: ``datatypes.py`` (derived datatypes),
+``fileio.py`` (MPI-IO), ``topo.py``, ``attrs.py`` (caching, error handlers, Info), ``rma.py`` (post/start/complete/wait)
+and ``dynproc.py`` (inter-communicators, ports).
 
 Everything here follows the conventions of the core module: results are returned instead of written through
 out-parameters, errors raise :class:`MPIError`.
@@ -34,7 +35,21 @@ _ERR_NAMES = {0: "MPI_SUCCESS: no errors", 1: "MPI_ERR_BUFFER: invalid buffer po
               9: "MPI_ERR_GROUP: invalid group", 10: "MPI_ERR_OP: invalid operation", 13: "MPI_ERR_ARG: invalid argument",
               14: "MPI_ERR_UNKNOWN: unknown error", 15: "MPI_ERR_TRUNCATE: message truncated on receive",
               16: "MPI_ERR_OTHER: known error not in this list", 17: "MPI_ERR_INTERN: internal error",
-              45: "MPI_ERR_WIN: invalid window", 50: "MPI_ERR_RMA_SYNC: wrong RMA synchronisation"}
+              45: "MPI_ERR_WIN: invalid window", 50: "MPI_ERR_RMA_SYNC: wrong RMA synchronisation",
+              11: "MPI_ERR_TOPOLOGY: invalid topology", 12: "MPI_ERR_DIMS: invalid dimension argument",
+              20: "MPI_ERR_ACCESS: permission denied", 21: "MPI_ERR_AMODE: invalid access mode",
+              22: "MPI_ERR_BAD_FILE: invalid file name", 23: "MPI_ERR_CONVERSION: data conversion failed",
+              24: "MPI_ERR_DUP_DATAREP: data representation already registered", 25: "MPI_ERR_FILE_EXISTS: file exists",
+              26: "MPI_ERR_FILE_IN_USE: file is open", 27: "MPI_ERR_FILE: invalid file handle",
+              28: "MPI_ERR_INFO: invalid info object", 29: "MPI_ERR_INFO_KEY: invalid info key",
+              30: "MPI_ERR_INFO_VALUE: invalid info value", 31: "MPI_ERR_INFO_NOKEY: no such info key",
+              32: "MPI_ERR_IO: input/output error", 33: "MPI_ERR_NAME: service name not published",
+              35: "MPI_ERR_NOT_SAME: collective arguments differ", 36: "MPI_ERR_NO_SPACE: not enough space",
+              37: "MPI_ERR_NO_SUCH_FILE: file does not exist", 38: "MPI_ERR_PORT: invalid port name",
+              39: "MPI_ERR_QUOTA: quota exceeded", 40: "MPI_ERR_READ_ONLY: read-only file",
+              41: "MPI_ERR_SERVICE: invalid service name", 42: "MPI_ERR_SPAWN: processes cannot be spawned",
+              43: "MPI_ERR_UNSUPPORTED_DATAREP: unsupported data representation",
+              44: "MPI_ERR_UNSUPPORTED_OPERATION: unsupported operation", 48: "MPI_ERR_KEYVAL: invalid keyval"}
 _COLL_TAG = 32100          # tag space of the composed collectives (user tags in the tree are 1..8)
 
 
@@ -74,19 +89,27 @@ def Is_thread_main() -> bool:
 
 
 def Error_class(code: int) -> int:
-    return code
+    """Codes of this layer are their own class; a code from ``Add_error_code`` maps to the class it was added to."""
+    from . import attrs
+    user = attrs.user_error_class(code)
+    return code if user is None else user
 
 
 def Error_string(code: int) -> str:
-    return _ERR_NAMES.get(code, f"error class {code}")
+    from . import attrs
+    user = attrs.user_error_string(code)
+    return user if user is not None else _ERR_NAMES.get(code, f"error class {code}")
 
 
 def Type_size(dtype: int) -> int:
-    return _m()._DTYPE_SIZE[dtype]
+    from . import datatypes
+    return datatypes.Type_size(dtype)
 
 
 def Type_get_extent(dtype: int) -> Tuple[int, int]:
-    return 0, _m()._DTYPE_SIZE[dtype]
+    """-> (lower bound, extent), basic and derived datatypes alike."""
+    from . import datatypes
+    return datatypes.Type_get_extent(dtype)
 
 
 def Alloc_mem(nbytes: int) -> torch.Tensor:
@@ -428,7 +451,8 @@ def Comm_compare(c1, c2) -> int:
 
 
 def Comm_test_inter(comm) -> bool:
-    return False
+    from . import dynproc
+    return isinstance(comm, dynproc.Intercomm)
 
 
 _COMM_NAMES: Dict[int, str] = {0: "MPI_COMM_WORLD", 1: "MPI_COMM_SELF"}
@@ -453,6 +477,9 @@ class Win:
         self.base = _flat(base)
         self.disp_unit, self.comm = disp_unit, comm
         self.ops: List[tuple] = []
+        # Win_create is collective, so the communicator's group can be gathered here once; the post / start /
+        # complete / wait epochs of rma.py need it and are not collective themselves
+        self.group = Comm_group(comm) if _m().Initialized() else Group([0])
 
 
 def Win_create(base, size_bytes: int, disp_unit: int, info=None, comm=0) -> Win:

@@ -230,9 +230,10 @@ def case_collectives():
 CASES = {k[5:]: v for k, v in globals().items() if k.startswith("case_")}
 
 if __name__ == "__main__":
-    from tests import mp_cases_ps, mp_cases_extras
+    from tests import mp_cases_ps, mp_cases_extras, mp_cases_chapters
     CASES.update(mp_cases_ps.CASES)
     CASES.update(mp_cases_extras.CASES)
+    CASES.update(mp_cases_chapters.CASES)
     name = sys.argv[1]
     mpiT.Init()
     try:

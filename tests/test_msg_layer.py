@@ -82,3 +82,12 @@ def test_ptest_bandwidth():
 def test_wider_mpi_surface(case, nproc):
     """Send modes, persistent requests, vector collectives, groups / user ops, fence windows (msg/extras.py)."""
     _run(case, nproc)
+
+
+@pytest.mark.parametrize("case,nproc", [("c_derived_messages", 4), ("c_topology", 6), ("c_file_io", 4),
+                                        ("c_pscw_and_attrs", 4), ("c_intercomm", 4)])
+def test_mpi_chapters_multi_process(case, nproc):
+    """Derived datatypes on the wire, topologies, MPI-IO with views and shared pointers, post/start/complete/wait,
+    attributes across Comm_dup, inter-communicators / ports / Comm_join (msg/datatypes.py, topo.py, fileio.py, rma.py,
+    attrs.py, dynproc.py)."""
+    _run(case, nproc)
