@@ -285,6 +285,17 @@ int mpit_push_add_bulk(const unsigned long long* shard_ptrs, int nranks, int ran
 int mpit_elastic_exchange_bulk(const unsigned long long* shard_ptrs, int nranks, int rank, const float* x, float* d,
                                long long n, float alpha, void* stream);
 
+/* ---- derived-datatype pack / unpack on the device (csrc/kernels/dtpack.cu) ------------------------
+ * Device-side twin of mpit_dt_pack / mpit_dt_unpack (mpit_msg.h): moves `nbytes` between the contiguous
+ * `stream_buf` and replicas, `extent` bytes apart, of a type made of `nblk` blocks.  d_disp[i] = byte
+ * displacement of block i, d_pre[i] = stream offset of block i inside one replica (d_pre[nblk] = size);
+ * both are DEVICE arrays.  `unit` (1,2,4,8,16) must divide every displacement, length, the extent, nbytes
+ * and both base addresses.  to_stream: 1 gather (pack), 0 scatter (unpack).  The reference leaves this
+ * to its CUDA-aware MPI library (/root/reference/lua-mpi.h:70-78). */
+int mpit_dt_move_device(void* strided_base, void* stream_buf, long long nbytes, long long size, long long extent,
+                        int nblk, const long long* d_disp, const long long* d_pre, int unit, int to_stream,
+                        void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -7,7 +7,7 @@ them.  Here a datatype is a *type map* -- for every basic element its byte displ
 bound and extent.  Committing a type flattens the map into maximal contiguous byte blocks; the data movement between
 a strided user buffer and a contiguous stream is then one call into the native engine
 (``mpit_dt_pack`` / ``mpit_dt_unpack``, csrc/msg/hostio.cpp).  CUDA tensors are gathered / scattered on the device
-with one indexed copy over a byte view.
+by ``mpit_dt_move_device`` (csrc/kernels/dtpack.cu), so one contiguous copy crosses PCIe.
 
 A committed handle can be given to ``Send / Recv / Isend / Irecv / Sendrecv / Bcast`` and to the ``File_*``
 routines wherever a basic datatype is accepted: the message travels packed, as bytes.
@@ -464,8 +464,9 @@ def pack_bytes(buf, count: int, dtype: int) -> np.ndarray:
     if isinstance(buf, torch.Tensor) and buf.is_cuda:
         flat = buf.view(-1).view(torch.uint8)
         _check(t, count, flat.numel(), "Pack")
-        idx = torch.from_numpy(_full_index(t, count)).to(buf.device)
-        return flat[idx].cpu().numpy()
+        out = torch.empty(nbytes, dtype=torch.uint8, device=buf.device)
+        _device_move(t, flat, out, nbytes, to_stream=True)
+        return out.cpu().numpy()
     src = _host_bytes(buf, False)
     _check(t, count, src.size, "Pack")
     out = np.empty(nbytes, dtype=np.uint8)
@@ -482,8 +483,8 @@ def unpack_bytes(stream: np.ndarray, buf, count: int, dtype: int, limit: Optiona
     if isinstance(buf, torch.Tensor) and buf.is_cuda:
         flat = buf.view(-1).view(torch.uint8)
         _check(t, count, flat.numel(), "Unpack")
-        idx = torch.from_numpy(_full_index(t, count)[:nbytes]).to(buf.device)
-        flat[idx] = torch.from_numpy(stream).to(buf.device)
+        staged = torch.from_numpy(stream).to(buf.device)
+        _device_move(t, flat, staged, nbytes, to_stream=False)
         return nbytes
     dst = _host_bytes(buf, True)
     _check(t, count, dst.size, "Unpack")
@@ -491,9 +492,29 @@ def unpack_bytes(stream: np.ndarray, buf, count: int, dtype: int, limit: Optiona
     return int(host().mpit_dt_unpack(_cptr(dst), count, t.extent, d.size, _cptr(d), _cptr(n), _cptr(stream), nbytes))
 
 
-def _full_index(t: Datatype, count: int) -> np.ndarray:
-    one = t.byte_index()
-    return (np.arange(count, dtype=np.int64)[:, None] * t.extent + one[None, :]).reshape(-1)
+def _device_move(t: Datatype, strided: torch.Tensor, stream: torch.Tensor, nbytes: int, to_stream: bool) -> None:
+    """Gather / scatter on the GPU (``mpit_dt_move_device``, csrc/kernels/dtpack.cu).  The block tables are uploaded
+    once per datatype and device; the word size is the largest power of two that every address involved is a
+    multiple of."""
+    import math
+    from .._native import kernels, check, ptr, cur_stream
+    if nbytes == 0:
+        return
+    dev = strided.device
+    if not hasattr(t, "_dev_tables"):
+        t._dev_tables = {}
+    if dev not in t._dev_tables:
+        d, n = t.blocks()
+        pre = np.concatenate([[0], np.cumsum(n)]).astype(np.int64)
+        unit = 16
+        for v in (*d.tolist(), *n.tolist(), t.extent):
+            unit = math.gcd(unit, int(v))
+        t._dev_tables[dev] = (torch.from_numpy(d.copy()).to(dev), torch.from_numpy(pre).to(dev), unit, int(d.size))
+    d_disp, d_pre, unit, nblk = t._dev_tables[dev]
+    unit = math.gcd(math.gcd(unit, nbytes), math.gcd(strided.data_ptr() % 16 or 16, stream.data_ptr() % 16 or 16))
+    with torch.cuda.device(dev):
+        check(kernels().mpit_dt_move_device(ptr(strided), ptr(stream), nbytes, t.size, t.extent, nblk, ptr(d_disp),
+                                            ptr(d_pre), unit, int(to_stream), cur_stream()), "mpit_dt_move_device")
 
 
 def Pack_size(incount: int, dtype: int, comm: int = 0) -> int:
