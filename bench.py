@@ -87,6 +87,8 @@ def main():
     ap.add_argument("--tau", type=int, default=10)
     ap.add_argument("--batch", type=int, default=128)
     ap.add_argument("--no-graphs", action="store_true")
+    ap.add_argument("--inline-loader", action="store_true",
+                    help="e2e arm: assemble batches on the Python thread instead of the native loader thread")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_arm(args)
@@ -152,7 +154,18 @@ def main():
         tr.engine.set_batch(dx[j], dy[j], dcrop[j])
         tr.device_step()
 
+    # The e2e arm's batches come from the framework's loader: a native worker thread shuffles the host data set,
+    # copies the samples of a mini-batch into a pinned slot and draws the crop offsets (goot.lua:164,172-184);
+    # train_step then copies that slot host -> device.  --inline-loader assembles the batch on the Python thread
+    # instead (the round-1 arrangement).
+    loader = None
+    if not args.inline_loader:
+        from mpit_b200.data.loader import BatchLoader
+        loader = BatchLoader(hx, hy, B, nslots=4, crop_range=5, seed=7 + rank)
+
     def e2e_step(i):
+        if loader is not None:
+            return tr.train_step(*loader.next())
         lo = (i * B) % n_host
         stage_x.copy_(hx[lo:lo + B])                 # what a loader does: assemble the batch on the host
         stage_y.copy_(hy[lo:lo + B])
@@ -222,7 +235,9 @@ def main():
                        "l2": "kernel-only arm rotates inputs through a 138 MB device-resident set (> 126 MB L2); no explicit flush"},
             "e2e": {"value": round(e2e_value, 1), "unit": "samples/s", "ms_per_step": round(e2e_ms_max / args.steps, 5),
                     "h2d_bytes_per_step": int(tr.h2d_bytes), "d2h_bytes_per_step": int(tr.d2h_bytes),
-                    "timing": "wall clock around CifarTrainer.train_step, max over ranks"},
+                    "timing": "wall clock around BatchLoader.next + CifarTrainer.train_step, max over ranks",
+                    "loader": "inline (Python thread)" if loader is None else "native worker thread, pinned ring",
+                    "host_path": "native stepper" if getattr(tr, "_stepper", None) is not None else "torch streams/events"},
             "gpu_launches": int(n_launch),
             "clocks": _clock_summary(clk_path, local_rank, t_lo, t_hi),
             "loss": {"device_arm_last": round(loss_dev, 4), "e2e_arm_last": round(last, 4)},

@@ -285,6 +285,22 @@ int mpit_push_add_bulk(const unsigned long long* shard_ptrs, int nranks, int ran
 int mpit_elastic_exchange_bulk(const unsigned long long* shard_ptrs, int nranks, int rank, const float* x, float* d,
                                long long n, float alpha, void* stream);
 
+/* ---- host side of an end-to-end training step (csrc/kernels/stepper.cu) ------------------------------
+ * stage(): H2D of one mini-batch (pinned host pointers) on an internal copy stream into the caller's
+ * double-buffered device staging, then mpit_prep_u8 on `main_stream`; hands back the summed loss of the step
+ * issued `lag` steps earlier.  The caller then enqueues its optimizer step on `main_stream` and calls
+ * finish(), which queues the 4-byte loss read-back into the caller's pinned `loss_host_pinned` ([lag+1][2]
+ * floats) and returns once the staged inputs have left the host buffers.  Allocates no device memory.
+ * Counterpart in the reference: the Lua step loop of /root/reference/asyncsgd/goot.lua:172-225. */
+int mpit_stepper_create(void** handle, int lag, void* d_img0, void* d_img1, int* d_lab0, int* d_lab1, int* d_crop0,
+                        int* d_crop1, float* loss_host_pinned, long long img_bytes, int B, int SH, int SW, int cin);
+int mpit_stepper_stage(void* handle, const void* img, const int* labels, const int* crop, float* x0_dst,
+                       int* labels_dst, int* crop_dst, void* main_stream, float* prev_loss_sum, int* have_prev);
+int mpit_stepper_finish(void* handle, const float* loss_dev, void* main_stream);
+int mpit_stepper_loss(void* handle, long long index, float* loss_sum);
+int mpit_stepper_counters(void* handle, long long* issued, long long* returned, int mark_returned);
+int mpit_stepper_destroy(void* handle);
+
 /* ---- derived-datatype pack / unpack on the device (csrc/kernels/dtpack.cu) ------------------------
  * Device-side twin of mpit_dt_pack / mpit_dt_unpack (mpit_msg.h): moves `nbytes` between the contiguous
  * `stream_buf` and replicas, `extent` bytes apart, of a type made of `nblk` blocks.  d_disp[i] = byte

@@ -153,6 +153,19 @@ int mpit_io_view_byte_offset(long long view_disp, long long fextent, int nblk, c
 /* shared file pointer kept in a side-car file: op 0 fetch-and-add, 1 set, 2 read */
 int mpit_io_shared_pointer(int sidecar_fd, int op, long long value, long long* old);
 
+/* ---- background mini-batch assembler (csrc/io/loader.cpp) ---------------------------------------------------
+ * Stands in for the per-sample batch assembly of /root/reference/asyncsgd/goot.lua:164,172-184 (per-epoch
+ * permutation, random crop position per sample), moved to a worker thread.  `images` = n_samples records of
+ * `sample_bytes`, `labels` = n_samples int32; the ring buffers (caller-owned, ideally pinned) hold `nslots`
+ * batches: ring_images [nslots][batch][sample_bytes], ring_labels [nslots][batch], ring_crop [nslots][batch][2]
+ * (y, x in [0, crop_range)).  One consumer thread: next() blocks for a filled slot, release() recycles it. */
+int mpit_loader_create(const unsigned char* images, const int* labels, long long n_samples, long long sample_bytes,
+                       int batch, int nslots, unsigned char* ring_images, int* ring_labels, int* ring_crop,
+                       int crop_range, unsigned long long seed, int shuffle, void** handle);
+int mpit_loader_next(void* handle, int* slot, long long* epoch);
+int mpit_loader_release(void* handle, int slot);
+int mpit_loader_destroy(void* handle);
+
 #ifdef __cplusplus
 }
 #endif

@@ -148,6 +148,63 @@ class CifarTrainer:
         self.tm = {"feval": 0.0, "sync": 0.0}
         self.h2d_bytes = 0
         self.d2h_bytes = 0
+        # The same choreography issued from one C function per half (csrc/kernels/stepper.cu) instead of a dozen
+        # torch stream / event / copy calls: the Python calls cost about as much host time as the device step takes.
+        # MPIT_NATIVE_STEPPER=0 keeps the torch path (same semantics).
+        self._stepper = None
+        if os.environ.get("MPIT_NATIVE_STEPPER", "1") != "0" and self.dev.type == "cuda":
+            import ctypes
+            from .._native import kernels, check, ptr
+            from ..models.cifar_cnn import IMG
+            h = ctypes.c_void_p(0)
+            (x0, y0, c0), (x1, y1, c1) = self._stage
+            with torch.cuda.device(self.dev):
+                check(kernels().mpit_stepper_create(ctypes.byref(h), self.LAG, ptr(x0), ptr(x1), ptr(y0), ptr(y1),
+                                                    ptr(c0), ptr(c1), ptr(self._loss_host), x0.numel(), opts.mb, IMG,
+                                                    IMG, e.cin), "mpit_stepper_create")
+            self._stepper = h
+            self._prev = (ctypes.c_float(0.0), ctypes.c_int(0))
+
+    def __del__(self):
+        if getattr(self, "_stepper", None):
+            try:
+                from .._native import kernels
+                kernels().mpit_stepper_destroy(self._stepper)
+            except Exception:
+                pass
+            self._stepper = None
+
+    def _train_step_native(self, images_u8, labels, crop) -> Optional[float]:
+        import ctypes
+        from .._native import kernels, check, ptr, cur_stream
+        e, lib = self.engine, kernels()
+        assert images_u8.dtype == torch.uint8 and images_u8.is_contiguous() and images_u8.numel() == e.x_u8.numel() \
+            and labels.dtype == torch.int32 and crop.dtype == torch.int32 and labels.numel() == self.opts.mb \
+            and crop.numel() == 2 * self.opts.mb and not images_u8.is_cuda
+        prev, have = self._prev
+        main = cur_stream()
+        check(lib.mpit_stepper_stage(self._stepper, ptr(images_u8), ptr(labels), ptr(crop), ptr(e.x0), ptr(e.labels),
+                                     ptr(e.crop), main, ctypes.byref(prev), ctypes.byref(have)), "mpit_stepper_stage")
+        self.opt.step()
+        rc = lib.mpit_stepper_finish(self._stepper, ptr(e.loss_sum), main)      # no kernel: not a counted launch
+        if rc != 0:
+            raise RuntimeError(f"mpit_stepper_finish failed with code {rc}")
+        self._k += 1
+        self.h2d_bytes = images_u8.numel() + labels.numel() * 4 + crop.numel() * 4
+        self.d2h_bytes = 4
+        if have.value:
+            self._ret += 1
+            return prev.value / self.opts.mb
+        return None
+
+    def _native_loss(self, index: int) -> float:
+        import ctypes
+        from .._native import kernels
+        out = ctypes.c_float(0.0)
+        rc = kernels().mpit_stepper_loss(self._stepper, index, ctypes.byref(out))
+        if rc != 0:
+            raise RuntimeError(f"mpit_stepper_loss({index}) failed with code {rc}")
+        return out.value / self.opts.mb
 
     # -- one training step ---------------------------------------------------------------------
     def train_step(self, images_u8: torch.Tensor, labels: torch.Tensor, crop: torch.Tensor) -> Optional[float]:
@@ -157,6 +214,12 @@ class CifarTrainer:
         The caller may reuse its host buffers as soon as this returns: the host->device copies run on a copy
         stream (beside the previous step's kernels) and are waited for here; only the ~2 us device-to-device move
         into the engine's input buffers sits on the compute stream."""
+        if self._stepper is not None:
+            if not (images_u8.is_cuda or labels.is_cuda or crop.is_cuda):
+                return self._train_step_native(images_u8, labels, crop)
+            if self._k:
+                raise ValueError("train_step: device-resident inputs after host inputs; use one kind per trainer")
+            self.__del__()                       # device-resident inputs: the torch path copies device-to-device
         k, lag = self._k, self.LAG
         prev = None
         if k - self._ret >= lag:
@@ -194,6 +257,14 @@ class CifarTrainer:
     def drain_losses(self) -> list:
         """Mean losses of the steps :meth:`train_step` has not handed back yet (waits for them)."""
         out = []
+        if self._stepper is not None:
+            import ctypes
+            from .._native import kernels
+            out = [self._native_loss(i) for i in range(self._ret, self._k)]
+            a, b = ctypes.c_longlong(0), ctypes.c_longlong(0)
+            kernels().mpit_stepper_counters(self._stepper, ctypes.byref(a), ctypes.byref(b), 1)
+            self._ret = self._k
+            return out
         while self._ret < self._k:
             slot = self._ret % (self.LAG + 1)
             self._loss_evt[slot].synchronize()
@@ -203,6 +274,8 @@ class CifarTrainer:
 
     def last_loss(self) -> float:
         """Mean loss of the most recent step issued through :meth:`train_step` (waits for it)."""
+        if self._stepper is not None:
+            return self._native_loss(-1)
         slot = (self._k - 1) % (self.LAG + 1)
         self._loss_evt[slot].synchronize()
         return float(self._loss_host[slot, 0]) / self.opts.mb

@@ -80,3 +80,38 @@ def test_checkpoint_resume_round_trip(tmp_path):
     q = tmp_path / "flat_model"
     t7.save(str(q), theta)
     assert torch.equal(load_checkpoint(str(q)), theta)
+
+
+def test_native_batch_loader_epochs_crops_and_determinism():
+    """csrc/io/loader.cpp: every sample exactly once per epoch, labels travel with their images, crop offsets in
+    range, same seed -> same stream, sequential order without shuffling."""
+    from mpit_b200.data.loader import BatchLoader
+    n, B = 40, 8
+    x = torch.arange(n, dtype=torch.uint8).view(n, 1, 1, 1).expand(n, 3, 4, 4).contiguous()
+    y = (torch.arange(n, dtype=torch.int32) * 7) % 10
+    ld = BatchLoader(x, y, B, nslots=3, crop_range=5, seed=11)
+    seen, crops = [], []
+    for step in range(10):                                   # two epochs
+        bx, by, bc = ld.next()
+        ids = bx[:, 0, 0, 0].to(torch.int64)
+        assert torch.equal(bx, x[ids]) and torch.equal(by, y[ids])
+        assert int(bc.min()) >= 0 and int(bc.max()) <= 4
+        seen.append(ids.clone())
+        crops.append(bc.clone())
+        assert ld.epoch == step // 5
+    e0, e1 = torch.cat(seen[:5]), torch.cat(seen[5:])
+    assert sorted(e0.tolist()) == list(range(n)) and sorted(e1.tolist()) == list(range(n))
+    assert not torch.equal(e0, e1) and not torch.equal(e0, torch.arange(n))
+    assert len({tuple(c.view(-1).tolist()) for c in crops}) > 1
+    ld2 = BatchLoader(x, y, B, nslots=3, crop_range=5, seed=11)
+    for step in range(10):
+        bx, by, bc = ld2.next()
+        assert torch.equal(bx[:, 0, 0, 0].to(torch.int64), seen[step]) and torch.equal(bc, crops[step])
+    ld.close()
+    ld2.close()
+    seq = BatchLoader(x, y, B, nslots=2, crop_range=0, seed=1, shuffle=False)
+    for step in range(7):                                    # 40 // 8 = 5 batches per epoch, then wraps
+        bx, by, bc = seq.next()
+        lo = (step % 5) * B
+        assert bx[:, 0, 0, 0].tolist() == list(range(lo, lo + B)) and int(bc.abs().sum()) == 0
+    seq.close()

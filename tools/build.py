@@ -80,7 +80,7 @@ def build(verbose: bool = True, jobs: int | None = None) -> dict:
     if shutil.which(NVCC) is None and not Path(NVCC).exists():
         raise RuntimeError("nvcc not found")
     kern_srcs = sorted((CSRC / "kernels").glob("*.cu")) + sorted((CSRC / "symm").glob("*.cu"))
-    host_srcs = sorted((CSRC / "msg").glob("*.cpp"))
+    host_srcs = sorted((CSRC / "msg").glob("*.cpp")) + sorted((CSRC / "io").glob("*.cpp"))
     jobs = jobs or min(8, os.cpu_count() or 4)
     with ThreadPoolExecutor(jobs) as ex:
         kern_objs = list(ex.map(lambda s: _compile(s, verbose), kern_srcs))
