@@ -20,7 +20,7 @@ from typing import Optional
 import torch
 
 from ..models.cifar_cnn import (CifarEngine, TorchCifarCNN, flat_from_torch, random_crop_offsets,
-                                center_crop_offsets, NUM_CLASSES, IMG)
+                                center_crop_offsets, NUM_CLASSES, IMG, CROP)
 from ..optim.device import DeviceMSGD, DeviceEAMSGD, DeviceDownpour, DeviceRule
 from ..parallel.center import ShardedCenter
 from ..parallel.symm import SymmetricHeap
@@ -321,16 +321,27 @@ def train_epochs(tr: CifarTrainer, train_xy, test_xy, rank: int = -1, quiet: boo
     hist = {"train_loss": [], "train_acc": [], "test_acc": [], "test_loss": []}
     t0 = time.perf_counter()
     n_steps = 0
+    # Mini-batches come from the native loader thread (per-epoch permutation, crop offsets, copies into pinned
+    # slots: goot.lua:164,172-184 off the training thread); MPIT_PY_LOADER=1 assembles them here instead.
+    loader = None
+    if os.environ.get("MPIT_PY_LOADER", "0") != "1" and not trx.is_cuda and trx.dtype == torch.uint8 \
+            and try_.dtype == torch.int32 and trsize >= B:
+        from ..data.loader import BatchLoader
+        loader = BatchLoader(trx[:trsize].contiguous(), try_[:trsize].contiguous(), B, nslots=4,
+                             crop_range=IMG - CROP + 1, seed=opts.seed)
     for epoch in range(1, opts.maxepoch + 1):
-        shuffle = torch.randperm(trsize, generator=gen)
+        shuffle = torch.randperm(trsize, generator=gen) if loader is None else None
         tr.engine.confusion.zero_()
         losses = []
         for t in range(0, trsize, B):
-            idx = shuffle[t:t + B]
-            torch.index_select(trx, 0, idx, out=stage_x)
-            torch.index_select(try_, 0, idx, out=stage_y)
-            stage_c.copy_(random_crop_offsets(B, gen))
-            prev = tr.train_step(stage_x, stage_y, stage_c)
+            if loader is not None:
+                prev = tr.train_step(*loader.next())
+            else:
+                idx = shuffle[t:t + B]
+                torch.index_select(trx, 0, idx, out=stage_x)
+                torch.index_select(try_, 0, idx, out=stage_y)
+                stage_c.copy_(random_crop_offsets(B, gen))
+                prev = tr.train_step(stage_x, stage_y, stage_c)
             if prev is not None:
                 losses.append(prev)
             n_steps += 1
@@ -358,4 +369,6 @@ def train_epochs(tr: CifarTrainer, train_xy, test_xy, rank: int = -1, quiet: boo
         print(f"\n===> time to learn 1 sample = {total / max(n_steps * B, 1) * 1000:.5f}ms")
     train_log.close()
     test_log.close()
+    if loader is not None:
+        loader.close()
     return hist
