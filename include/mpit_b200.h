@@ -311,6 +311,11 @@ int mpit_stepper_destroy(void* handle);
 int mpit_dt_move_device(void* strided_base, void* stream_buf, long long nbytes, long long size, long long extent,
                         int nblk, const long long* d_disp, const long long* d_pre, int unit, int to_stream,
                         void* stream);
+/* The same for a REGULAR block list (size/blen blocks of `blen` bytes, block i at d0 + i*bstride: vectors, 2-d
+ * sub-arrays): no tables, four independent words in flight per thread. */
+int mpit_dt_move_device_regular(void* strided_base, void* stream_buf, long long nbytes, long long size,
+                                long long extent, long long d0, long long blen, long long bstride, int unit,
+                                int to_stream, void* stream);
 
 #ifdef __cplusplus
 }

@@ -509,12 +509,23 @@ def _device_move(t: Datatype, strided: torch.Tensor, stream: torch.Tensor, nbyte
         unit = 16
         for v in (*d.tolist(), *n.tolist(), t.extent):
             unit = math.gcd(unit, int(v))
-        t._dev_tables[dev] = (torch.from_numpy(d.copy()).to(dev), torch.from_numpy(pre).to(dev), unit, int(d.size))
-    d_disp, d_pre, unit, nblk = t._dev_tables[dev]
+        regular = None
+        if d.size and np.all(n == n[0]) and (d.size == 1 or np.all(np.diff(d) == d[1] - d[0])):
+            regular = (int(d[0]), int(n[0]), int(d[1] - d[0]) if d.size > 1 else int(n[0]))
+        t._dev_tables[dev] = (torch.from_numpy(d.copy()).to(dev), torch.from_numpy(pre).to(dev), unit, int(d.size),
+                              regular)
+    d_disp, d_pre, unit, nblk, regular = t._dev_tables[dev]
     unit = math.gcd(math.gcd(unit, nbytes), math.gcd(strided.data_ptr() % 16 or 16, stream.data_ptr() % 16 or 16))
     with torch.cuda.device(dev):
-        check(kernels().mpit_dt_move_device(ptr(strided), ptr(stream), nbytes, t.size, t.extent, nblk, ptr(d_disp),
-                                            ptr(d_pre), unit, int(to_stream), cur_stream()), "mpit_dt_move_device")
+        if regular is not None:
+            d0, blen, bstride = regular
+            check(kernels().mpit_dt_move_device_regular(ptr(strided), ptr(stream), nbytes, t.size, t.extent, d0, blen,
+                                                        bstride, unit, int(to_stream), cur_stream()),
+                  "mpit_dt_move_device_regular")
+        else:
+            check(kernels().mpit_dt_move_device(ptr(strided), ptr(stream), nbytes, t.size, t.extent, nblk,
+                                                ptr(d_disp), ptr(d_pre), unit, int(to_stream), cur_stream()),
+                  "mpit_dt_move_device")
 
 
 def Pack_size(incount: int, dtype: int, comm: int = 0) -> int:
