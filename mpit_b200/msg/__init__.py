@@ -454,6 +454,8 @@ def Bcast(buf, count: int, dtype: int, root: int, comm: int = COMM_WORLD) -> Non
 
 
 def Reduce(sbuf, rbuf, count: int, dtype: int, op: int, root: int, comm: int = COMM_WORLD) -> None:
+    if extras.needs_packed_reduce(dtype, op):
+        return extras.reduce_packed(sbuf, rbuf, count, dtype, op, root, comm, everyone=False)
     if extras.is_user_op(op):
         return extras.reduce_user_op(sbuf, rbuf, count, dtype, op, root, comm, everyone=False)
     s, r = _Buf(sbuf, count, dtype, False), _Buf(rbuf, count, dtype, True)
@@ -463,6 +465,8 @@ def Reduce(sbuf, rbuf, count: int, dtype: int, op: int, root: int, comm: int = C
 
 
 def Allreduce(sbuf, rbuf, count: int, dtype: int, op: int, comm: int = COMM_WORLD) -> None:
+    if extras.needs_packed_reduce(dtype, op):
+        return extras.reduce_packed(sbuf, rbuf, count, dtype, op, 0, comm, everyone=True)
     if extras.is_user_op(op):
         return extras.reduce_user_op(sbuf, rbuf, count, dtype, op, 0, comm, everyone=True)
     """MPI_Allreduce (/root/reference/test/testreduceall.lua:28)."""
@@ -563,4 +567,5 @@ from .dynproc import *  # noqa: E402,F401,F403
 from .fileio import *  # noqa: E402,F401,F403
 from .rma import *  # noqa: E402,F401,F403
 from .topo import *  # noqa: E402,F401,F403
-from .extras import (PROC_NULL, ROOT, IDENT, CONGRUENT, SIMILAR, UNEQUAL, LXOR, BXOR, GROUP_EMPTY)  # noqa: E402,F401
+from .extras import (PROC_NULL, ROOT, IDENT, CONGRUENT, SIMILAR, UNEQUAL, LXOR, BXOR, MAXLOC, MINLOC,  # noqa: E402,F401
+                     GROUP_EMPTY)

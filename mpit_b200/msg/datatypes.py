@@ -40,9 +40,13 @@ ERR_TYPE, ERR_ARG, ERR_TRUNCATE, ERR_UNSUPPORTED_DATAREP = 3, 13, 15, 43
 
 # basic types: numpy dtype in memory, and size / dtype in the "external32" representation (big endian,
 # MPI_LONG is four bytes there)
+# (codes 10..12 are the element kinds of the predefined types the native layer has no wire id for:
+# UNSIGNED_SHORT, UNSIGNED_LONG, LONG_DOUBLE -- they travel packed, like derived types)
 _NP = {0: np.uint8, 1: np.int8, 2: np.int16, 3: np.int32, 4: np.int64, 5: np.float32, 6: np.float64, 7: np.uint8,
-       8: np.uint32, 9: np.int64}
-_EXT32 = {0: ">u1", 1: ">i1", 2: ">i2", 3: ">i4", 4: ">i4", 5: ">f4", 6: ">f8", 7: ">u1", 8: ">u4", 9: ">i8"}
+       8: np.uint32, 9: np.int64, 10: np.uint16, 11: np.uint64, 12: np.longdouble}
+_EXT32 = {0: ">u1", 1: ">i1", 2: ">i2", 3: ">i4", 4: ">i4", 5: ">f4", 6: ">f8", 7: ">u1", 8: ">u4", 9: ">i8",
+          10: ">u2", 11: ">u8", 12: ">f16"}
+_NKINDS = len(_NP)
 _BASIC_NAMES = {0: "MPI_BYTE", 1: "MPI_CHAR", 2: "MPI_SHORT", 3: "MPI_INT", 4: "MPI_LONG", 5: "MPI_FLOAT",
                 6: "MPI_DOUBLE", 7: "MPI_UNSIGNED_CHAR", 8: "MPI_UNSIGNED", 9: "MPI_LONG_LONG"}
 
@@ -82,7 +86,7 @@ class Datatype:
         self._byte_index: Optional[np.ndarray] = None
 
     def elem_sizes(self) -> np.ndarray:
-        table = np.array([np.dtype(_NP[k]).itemsize for k in range(10)], dtype=np.int64)
+        table = np.array([np.dtype(_NP[k]).itemsize for k in range(_NKINDS)], dtype=np.int64)
         return table[self.code] if self.code.size else np.zeros(0, np.int64)
 
     def blocks(self) -> Tuple[np.ndarray, np.ndarray]:
@@ -115,7 +119,47 @@ for _k in range(10):
     _t = Datatype([0], [_k])
     _t.committed, _t.name, _t.handle = True, _BASIC_NAMES[_k], _k
     _TYPES[_k] = _t
-_next_handle = [DERIVED_BASE]
+_next_handle = [DERIVED_BASE + 100]        # DERIVED_BASE .. +99 are the predefined types below
+
+
+def _predefine(handle: int, name: str, t: Datatype) -> int:
+    t.committed, t.name, t.handle, t.combiner = True, name, handle, COMBINER_NAMED
+    _TYPES[handle] = t
+    return handle
+
+
+def _pair(value_code: int, name: str, handle: int) -> int:
+    """The {value, int} records MAXLOC / MINLOC reduce over, laid out like the C struct."""
+    vsize = np.dtype(_NP[value_code]).itemsize
+    ioff = (vsize + 3) // 4 * 4
+    return _predefine(handle, name, Datatype([0, ioff], [value_code, 3]))
+
+
+# Predefined types of /root/reference/lua-mpi.h:130-151 that the native layer has no wire id for.  They are handled
+# like committed derived types (packed on the wire, reduced by the generic reducer in extras.reduce_packed).
+UNSIGNED_SHORT = _predefine(DERIVED_BASE + 0, "MPI_UNSIGNED_SHORT", Datatype([0], [10]))
+UNSIGNED_LONG = _predefine(DERIVED_BASE + 1, "MPI_UNSIGNED_LONG", Datatype([0], [11]))
+LONG_DOUBLE = _predefine(DERIVED_BASE + 2, "MPI_LONG_DOUBLE", Datatype([0], [12]))
+PACKED = _predefine(DERIVED_BASE + 3, "MPI_PACKED", Datatype([0], [0]))
+FLOAT_INT = _pair(5, "MPI_FLOAT_INT", DERIVED_BASE + 4)
+DOUBLE_INT = _pair(6, "MPI_DOUBLE_INT", DERIVED_BASE + 5)
+LONG_INT = _pair(4, "MPI_LONG_INT", DERIVED_BASE + 6)
+SHORT_INT = _pair(2, "MPI_SHORT_INT", DERIVED_BASE + 7)
+LONG_DOUBLE_INT = _pair(12, "MPI_LONG_DOUBLE_INT", DERIVED_BASE + 8)
+globals()["2INT"] = TWOINT = _pair(3, "MPI_2INT", DERIVED_BASE + 9)          # mpiT["2INT"] / mpiT.TWOINT
+LONG_LONG_INT = 9                                                            # MPI's other name for LONG_LONG
+# MPI-1 bound markers: zero-size members of Type_create_struct that pin the lower / upper bound
+LB = _predefine(DERIVED_BASE + 10, "MPI_LB", Datatype([], []))
+UB = _predefine(DERIVED_BASE + 11, "MPI_UB", Datatype([], []))
+
+
+def packed_numpy_dtype(dtype: int, records: bool = False) -> np.dtype:
+    """NumPy view of the packed stream of ``dtype``: the scalar dtype when every basic element is of one kind (the
+    stream is then a plain array of them), a record ``(f0, f1, ...)`` per element otherwise."""
+    t = get(dtype)
+    if not records and t.code.size and np.all(t.code == t.code[0]):
+        return np.dtype(_NP[int(t.code[0])])
+    return np.dtype([(f"f{i}", _NP[int(c)]) for i, c in enumerate(t.code)])
 
 
 def is_derived(dtype: int) -> bool:
@@ -216,7 +260,14 @@ def Type_create_indexed_block(blocklength: int, displacements: Sequence[int], ol
 
 def Type_create_struct(blocklengths: Sequence[int], displacements_bytes: Sequence[int], types: Sequence[int]) -> int:
     disp, code, lbs, ubs = [], [], [], []
+    forced_lb = forced_ub = None
     for b, d, t in zip(blocklengths, displacements_bytes, types):
+        if t == LB:
+            forced_lb = d if forced_lb is None else min(forced_lb, d)
+            continue
+        if t == UB:
+            forced_ub = d if forced_ub is None else max(forced_ub, d)
+            continue
         old = get(t)
         off = d + np.arange(b, dtype=np.int64) * old.extent
         dd, cc = _replicate(old, off)
@@ -235,6 +286,10 @@ def Type_create_struct(blocklengths: Sequence[int], displacements_bytes: Sequenc
         lb, ub = min(lbs), max(ubs)
         align = int(t.elem_sizes().max()) if t.disp.size else 1
         t.lb, t.extent = lb, ((ub - lb) + align - 1) // align * align
+    if forced_lb is not None or forced_ub is not None:
+        lb = t.lb if forced_lb is None else forced_lb
+        ub = t.lb + t.extent if forced_ub is None else forced_ub
+        t.lb, t.extent = lb, ub - lb
     return _register(t)
 
 
@@ -330,7 +385,7 @@ def Type_commit(dtype: int) -> int:
 
 def Type_free(dtype: int) -> int:
     """Releases a derived type; returns DATATYPE_NULL (-1).  Basic types cannot be freed."""
-    if not is_derived(dtype):
+    if not is_derived(dtype) or dtype < DERIVED_BASE + 100:
         raise _err(ERR_TYPE, "Type_free of a predefined datatype")
     from . import attrs
     attrs.drop_object("type", dtype)
@@ -556,7 +611,7 @@ def _ext_layout(t: Datatype, count: int):
     code = np.tile(t.code, count)
     nat = t.elem_sizes()
     nat = np.tile(nat, count)
-    ext = np.array([np.dtype(_EXT32[k]).itemsize for k in range(10)], dtype=np.int64)[code]
+    ext = np.array([np.dtype(_EXT32[k]).itemsize for k in range(_NKINDS)], dtype=np.int64)[code]
     return code, nat, np.cumsum(nat) - nat, ext, np.cumsum(ext) - ext
 
 
@@ -568,7 +623,7 @@ def _check_rep(datarep: str):
 def Pack_external_size(datarep: str, incount: int, dtype: int) -> int:
     _check_rep(datarep)
     t = get(dtype)
-    ext = np.array([np.dtype(_EXT32[k]).itemsize for k in range(10)], dtype=np.int64)
+    ext = np.array([np.dtype(_EXT32[k]).itemsize for k in range(_NKINDS)], dtype=np.int64)
     return incount * int(ext[t.code].sum())
 
 
@@ -621,4 +676,4 @@ def stage_for_message(buf, count: int, dtype: int, writable: bool):
 
 
 __all__ = [_n for _n in dir() if _n[0].isupper() and _n not in ("Any", "Callable", "Dict", "List", "Optional", "Sequence",
-                                                                 "Tuple")]
+                                                                 "Tuple")] + ["2INT"]

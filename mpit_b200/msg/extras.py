@@ -28,6 +28,7 @@ IDENT, CONGRUENT, SIMILAR, UNEQUAL = 0, 1, 2, 3
  ERR_DIMS, ERR_ARG, ERR_UNKNOWN) = range(1, 15)
 ERR_OTHER, ERR_INTERN, ERR_IN_STATUS, ERR_PENDING, ERR_WIN, ERR_RMA_SYNC, ERR_LASTCODE = 16, 17, 18, 19, 45, 50, 92
 LXOR, BXOR = 8, 9                                 # the native layer implements SUM..BOR (0..7)
+MAXLOC, MINLOC = 10, 11                           # over the {value, int} pair types (FLOAT_INT, 2INT ...)
 OP_NULL, GROUP_NULL, DATATYPE_NULL, ERRHANDLER_NULL, INFO_NULL, WIN_NULL = -1, None, -1, -1, -1, None
 _ERR_NAMES = {0: "MPI_SUCCESS: no errors", 1: "MPI_ERR_BUFFER: invalid buffer pointer", 2: "MPI_ERR_COUNT: invalid count",
               3: "MPI_ERR_TYPE: invalid datatype", 4: "MPI_ERR_TAG: invalid tag", 5: "MPI_ERR_COMM: invalid communicator",
@@ -364,6 +365,72 @@ def reduce_user_op(sbuf, rbuf, count, dtype, op, root, comm, everyone: bool):
         r[:count] = acc
     if everyone:
         m.Bcast(r[:count], count, dtype, root_, comm)
+
+
+def needs_packed_reduce(dtype: int, op: int) -> bool:
+    from . import datatypes
+    return op in (MAXLOC, MINLOC) or dtype >= datatypes.DERIVED_BASE
+
+
+def _fold(a: np.ndarray, b: np.ndarray, op: int) -> np.ndarray:
+    """``a op b`` with ``a`` the lower-ranked operand; record arrays are the pair types of MAXLOC / MINLOC."""
+    m = _m()
+    if op in (MAXLOC, MINLOC):
+        if a.dtype.names is None or len(a.dtype.names) != 2:
+            raise m.MPIError(ERR_OP, "MAXLOC / MINLOC need a {value, int} pair datatype")
+        v, i = a.dtype.names
+        better = (a[v] > b[v]) if op == MAXLOC else (a[v] < b[v])
+        tie = a[v] == b[v]
+        out = b.copy()
+        take_a = better | (tie & (a[i] < b[i]))
+        out[take_a] = a[take_a]
+        return out
+    if a.dtype.names is not None:
+        raise m.MPIError(ERR_OP, "arithmetic reduction of a record datatype")
+    table = {m.SUM: np.add, m.PROD: np.multiply, m.MAX: np.maximum, m.MIN: np.minimum, m.BAND: np.bitwise_and,
+             m.BOR: np.bitwise_or, BXOR: np.bitwise_xor}
+    if op in table:
+        return table[op](a, b)
+    if op in (m.LAND, m.LOR, LXOR):
+        f = {m.LAND: np.logical_and, m.LOR: np.logical_or, LXOR: np.logical_xor}[op]
+        return f(a != 0, b != 0).astype(a.dtype)
+    raise m.MPIError(ERR_OP, f"reduction op {op}")
+
+
+def reduce_packed(sbuf, rbuf, count, dtype, op, root, comm, everyone: bool):
+    """Reduce / Allreduce for datatypes or operations the native reducer has no code for (UNSIGNED_SHORT,
+    UNSIGNED_LONG, LONG_DOUBLE, the pair types with MAXLOC / MINLOC, contiguous derived types of one element kind):
+    the packed elements are gathered on the root, folded in rank order with NumPy, and broadcast when everyone
+    wants the result."""
+    from . import datatypes
+    m = _m()
+    me, n = m.Comm_rank(comm), m.Comm_size(comm)
+    if is_user_op(op) and op not in (LXOR, BXOR):
+        raise m.MPIError(ERR_OP, "user-defined operations take basic datatypes")
+    el = datatypes.packed_numpy_dtype(dtype, records=op in (MAXLOC, MINLOC))   # MAXLOC sees (value, index) records
+    # argument errors must surface on every rank BEFORE anyone communicates
+    if op in (MAXLOC, MINLOC):
+        if el.names is None or len(el.names) != 2:
+            raise m.MPIError(ERR_OP, "MAXLOC / MINLOC need a {value, int} pair datatype")
+    elif el.names is not None:
+        raise m.MPIError(ERR_OP, "arithmetic reduction of a record datatype")
+    elif op not in (m.SUM, m.PROD, m.MAX, m.MIN, m.BAND, m.BOR, BXOR, m.LAND, m.LOR, LXOR):
+        raise m.MPIError(ERR_OP, f"reduction op {op}")
+    mine = datatypes.pack_bytes(sbuf, count, dtype)
+    root_ = 0 if everyone else root
+    gathered = np.empty(n * mine.size, dtype=np.uint8) if me == root_ else None
+    m.Gather(mine, mine.size, m.BYTE, gathered, root_, comm)
+    result = np.empty(mine.size, dtype=np.uint8)
+    if me == root_:
+        parts = gathered.reshape(n, mine.size)
+        acc = parts[0].view(el).copy()
+        for p in range(1, n):
+            acc = _fold(acc, parts[p].view(el), op)
+        result[:] = acc.view(np.uint8)
+    if everyone:
+        m.Bcast(result, result.size, m.BYTE, root_, comm)
+    if everyone or me == root_:
+        datatypes.unpack_bytes(result, rbuf, count, dtype)
 
 
 # ---- groups and communicator construction -----------------------------------------------------------

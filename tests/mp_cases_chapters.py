@@ -67,6 +67,52 @@ def case_c_derived_messages():
     assert torch.equal(dst, want), (rank, dst, want)
 
 
+def case_c_maxloc_and_wide_types():
+    """MAXLOC / MINLOC over the pair types, reductions of the predefined types without a native wire id, and a
+    contiguous derived type of floats."""
+    rank, size = mpiT.get_rank(), mpiT.get_size()
+    pair = np.dtype([("v", np.float32), ("i", np.int32)])
+    mine = np.zeros(3, dtype=pair)
+    # element 0: value peaks at rank 2; element 1: all equal (tie -> lowest index); element 2: falls with rank
+    mine["v"] = [-abs(rank - 2.0), 5.0, -float(rank)]
+    mine["i"] = rank
+    out = np.zeros(3, dtype=pair)
+    mpiT.Allreduce(mine.view(np.uint8), out.view(np.uint8), 3, mpiT.FLOAT_INT, mpiT.MAXLOC)
+    assert out["v"].tolist() == [0.0, 5.0, 0.0] and out["i"].tolist() == [2, 0, 0], (rank, out)
+    mpiT.Reduce(mine.view(np.uint8), out.view(np.uint8), 3, mpiT.FLOAT_INT, mpiT.MINLOC, 1)
+    if rank == 1:
+        assert out["v"].tolist() == [-2.0, 5.0, -float(size - 1)] and out["i"].tolist() == [0, 0, size - 1], out
+    two = torch.tensor([[rank * 10, rank], [7, rank]], dtype=torch.int32)
+    res = torch.zeros_like(two)
+    mpiT.Allreduce(two, res, 2, getattr(mpiT, "2INT"), mpiT.MAXLOC)
+    assert res.tolist() == [[(size - 1) * 10, size - 1], [7, 0]]
+    us = np.array([rank + 1, 60000], dtype=np.uint16)
+    tot = np.zeros(2, dtype=np.uint16)
+    mpiT.Allreduce(us, tot, 2, mpiT.UNSIGNED_SHORT, mpiT.MAX)
+    assert tot.tolist() == [size, 60000]
+    ul = np.array([2 ** 40 + rank], dtype=np.uint64)
+    s = np.zeros(1, dtype=np.uint64)
+    mpiT.Allreduce(ul, s, 1, mpiT.UNSIGNED_LONG, mpiT.SUM)
+    assert int(s[0]) == size * 2 ** 40 + size * (size - 1) // 2
+    ld = np.array([1.0 + rank], dtype=np.longdouble)
+    p = np.zeros(1, dtype=np.longdouble)
+    mpiT.Allreduce(ld.view(np.uint8), p.view(np.uint8), 1, mpiT.LONG_DOUBLE, mpiT.PROD)
+    want = 1.0
+    for r in range(size):
+        want *= 1.0 + r
+    assert float(p[0]) == want
+    trip = mpiT.Type_commit(mpiT.Type_contiguous(3, mpiT.FLOAT))
+    v = torch.full((6,), float(rank))
+    w = torch.zeros(6)
+    mpiT.Allreduce(v, w, 2, trip, mpiT.SUM)
+    assert w.tolist() == [size * (size - 1) / 2.0] * 6
+    try:
+        mpiT.Allreduce(v, w, 3, mpiT.FLOAT, mpiT.MAXLOC)
+        raise AssertionError("MAXLOC over a scalar type")
+    except mpiT.MPIError as e:
+        assert e.code == mpiT.ERR_OP
+
+
 def case_c_topology():
     """Cartesian grid: coordinates, shifts with and without wrap-around, sub-grids; graph neighbours."""
     rank, size = mpiT.get_rank(), mpiT.get_size()

@@ -139,6 +139,33 @@ def test_datatype_queries_and_errors():
         mpiT.Type_free(mpiT.FLOAT)
 
 
+def test_remaining_predefined_types_and_bound_markers():
+    """lua-mpi.h:130-151 lists 22 datatypes; the twelve without a native wire id are packed types here."""
+    assert mpiT.Type_size(mpiT.UNSIGNED_SHORT) == 2 and mpiT.Type_size(mpiT.UNSIGNED_LONG) == 8
+    assert mpiT.Type_size(mpiT.LONG_DOUBLE) == np.dtype(np.longdouble).itemsize and mpiT.LONG_LONG_INT == mpiT.LONG_LONG
+    assert mpiT.Type_get_extent(mpiT.FLOAT_INT) == (0, 8) and mpiT.Type_get_extent(mpiT.DOUBLE_INT) == (0, 16)
+    assert mpiT.Type_size(mpiT.DOUBLE_INT) == 12 and mpiT.Type_size(mpiT.SHORT_INT) == 6
+    assert mpiT.Type_get_extent(mpiT.SHORT_INT) == (0, 8) and mpiT.Type_get_name(getattr(mpiT, "2INT")) == "MPI_2INT"
+    assert mpiT.Type_get_envelope(mpiT.LONG_INT)[3] == mpiT.COMBINER_NAMED
+    with pytest.raises(mpiT.MPIError):
+        mpiT.Type_free(mpiT.PACKED)
+    # a C array of {double, int} records packs to 12 bytes per record
+    rec = np.zeros(3, dtype=np.dtype([("v", np.float64), ("i", np.int32)], align=True))
+    rec["v"], rec["i"] = [1.5, -2.0, 7.25], [4, 5, 6]
+    stream = _packed(rec.view(np.uint8).reshape(-1), 3, mpiT.DOUBLE_INT)
+    assert stream.size == 36 and stream[:8].view(np.float64)[0] == 1.5 and stream[8:12].view(np.int32)[0] == 4
+    # MPI-1 style bounds: {LB at -4, one float at 0, UB at 12}
+    t = mpiT.Type_commit(mpiT.Type_create_struct([1, 1, 1], [-4, 0, 12], [mpiT.LB, mpiT.FLOAT, mpiT.UB]))
+    assert mpiT.Type_get_extent(t) == (-4, 16) and mpiT.Type_get_true_extent(t) == (0, 4) and mpiT.Type_size(t) == 4
+    us = np.array([1, 65535, 7], dtype=np.uint16)
+    out = np.zeros(3, dtype=np.uint16)
+    mpiT.Unpack(_packed(us, 3, mpiT.UNSIGNED_SHORT), 0, out, 3, mpiT.UNSIGNED_SHORT)
+    assert np.array_equal(out, us)
+    ext = np.zeros(mpiT.Pack_external_size("external32", 3, mpiT.UNSIGNED_SHORT), dtype=np.uint8)
+    mpiT.Pack_external("external32", us, 3, mpiT.UNSIGNED_SHORT, ext, 0)
+    assert ext.tolist() == [0, 1, 255, 255, 0, 7]
+
+
 # ---- Info, attributes, error handlers, misc -----------------------------------------------------------------------
 def test_info_object():
     info = mpiT.Info_create()
