@@ -465,11 +465,12 @@ def Reduce(sbuf, rbuf, count: int, dtype: int, op: int, root: int, comm: int = C
 
 
 def Allreduce(sbuf, rbuf, count: int, dtype: int, op: int, comm: int = COMM_WORLD) -> None:
+    """MPI_Allreduce (/root/reference/test/testreduceall.lua:28).  The ten basic datatypes with SUM..BOR run in the
+    native reducer; user operations, LXOR / BXOR, MAXLOC / MINLOC and the packed datatypes are folded on rank 0."""
     if extras.needs_packed_reduce(dtype, op):
         return extras.reduce_packed(sbuf, rbuf, count, dtype, op, 0, comm, everyone=True)
     if extras.is_user_op(op):
         return extras.reduce_user_op(sbuf, rbuf, count, dtype, op, 0, comm, everyone=True)
-    """MPI_Allreduce (/root/reference/test/testreduceall.lua:28)."""
     s, r = _Buf(sbuf, count, dtype, False), _Buf(rbuf, count, dtype, True)
     _chk(host().mpit_msg_allreduce(s.ptr, r.ptr, count, dtype, op, comm), "Allreduce")
     if r.after:
