@@ -237,7 +237,10 @@ def main():
                     "h2d_bytes_per_step": int(tr.h2d_bytes), "d2h_bytes_per_step": int(tr.d2h_bytes),
                     "timing": "wall clock around BatchLoader.next + CifarTrainer.train_step, max over ranks",
                     "loader": "inline (Python thread)" if loader is None else "native worker thread, pinned ring",
-                    "host_path": "native stepper" if getattr(tr, "_stepper", None) is not None else "torch streams/events"},
+                    "host_path": "native stepper" if getattr(tr, "_stepper", None) is not None else "torch streams/events",
+                    "d2h": "loss of step t stored into host-mapped pinned memory by the input kernel of step t+1 "
+                           "(a copy for the newest step); read by the host every step, LAG=2 steps late"
+                    if getattr(tr, "_stepper", None) is not None else "cudaMemcpyAsync of the loss every step"},
             "gpu_launches": int(n_launch),
             "clocks": _clock_summary(clk_path, local_rank, t_lo, t_hi),
             "loss": {"device_arm_last": round(loss_dev, 4), "e2e_arm_last": round(last, 4)},

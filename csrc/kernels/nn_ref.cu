@@ -190,9 +190,12 @@ colsum_kernel(const float* __restrict__ dz, float* __restrict__ db, long long ro
 __global__ void __launch_bounds__(256)
 prep_u8_kernel(const unsigned char* __restrict__ src, float* __restrict__ dst, int B, int SH, int SW, int cin,
                const int* __restrict__ labels_src, int* __restrict__ labels_dst, const int* __restrict__ crop_src,
-               int* __restrict__ crop_dst) {
+               int* __restrict__ crop_dst, const float* __restrict__ fwd_src, float* fwd_dst, int fwd_n) {
   pdl_trigger();
   pdl_wait();
+  // a few floats forwarded from the previous step (its loss) to wherever the caller points -- in the end-to-end
+  // step that is host-mapped pinned memory, which spares the stream a copy-engine operation per step
+  if (fwd_src && blockIdx.x == 0 && threadIdx.x < fwd_n) fwd_dst[threadIdx.x] = fwd_src[threadIdx.x];
   // the batch's labels and crop offsets ride along (one launch stages a whole mini-batch: three separate
   // device-to-device copies in front of every step cost ~10 us of a 140 us step)
   {
@@ -375,7 +378,21 @@ int mpit_prep_u8(const unsigned char* src, float* dst, int B, int SH, int SW, in
   long long total = (long long)B * SH * SW;
   if (total < 2 * B) return MPIT_E_ARG;      // the label / crop copy uses the first 2B threads
   MPIT_CUDA_TRY(launch_k(prep_u8_kernel, dim3(ew_grid(total, 256, 1)), dim3(256), 0, (cudaStream_t)stream, src, dst,
-                         B, SH, SW, cin, labels_src, labels_dst, crop_src, crop_dst));
+                         B, SH, SW, cin, labels_src, labels_dst, crop_src, crop_dst, (const float*)nullptr,
+                         (float*)nullptr, 0));
+  return 0;
+}
+
+int mpit_prep_u8_fwd(const unsigned char* src, float* dst, int B, int SH, int SW, int cin, const int* labels_src,
+                     int* labels_dst, const int* crop_src, int* crop_dst, const float* fwd_src, float* fwd_dst,
+                     int fwd_n, void* stream) {
+  if (cin < 1 || cin > 4) return MPIT_E_ARG;
+  if ((labels_src && !labels_dst) || (crop_src && !crop_dst) || (fwd_src && !fwd_dst) || fwd_n < 0 || fwd_n > 256)
+    return MPIT_E_ARG;
+  long long total = (long long)B * SH * SW;
+  if (total < 2 * B) return MPIT_E_ARG;
+  MPIT_CUDA_TRY(launch_k(prep_u8_kernel, dim3(ew_grid(total, 256, 1)), dim3(256), 0, (cudaStream_t)stream, src, dst,
+                         B, SH, SW, cin, labels_src, labels_dst, crop_src, crop_dst, fwd_src, fwd_dst, fwd_n));
   return 0;
 }
 

@@ -82,6 +82,12 @@ int mpit_colsum(const float* dz, float* db, long long rows, int C, void* stream)
  * batch's labels [B] and crop offsets [B][2] (device pointers) into the engine's buffers in the same launch. */
 int mpit_prep_u8(const unsigned char* src, float* dst, int B, int SH, int SW, int cin, const int* labels_src,
                  int* labels_dst, const int* crop_src, int* crop_dst, void* stream);
+/* The same launch also forwards fwd_n (<= 256) floats fwd_src -> fwd_dst after the preceding work on the stream has
+ * completed; fwd_dst may be host-mapped pinned memory (the end-to-end step returns the previous step's loss this
+ * way instead of through a copy-engine operation on the compute stream). */
+int mpit_prep_u8_fwd(const unsigned char* src, float* dst, int B, int SH, int SW, int cin, const int* labels_src,
+                     int* labels_dst, const int* crop_src, int* crop_dst, const float* fwd_src, float* fwd_dst,
+                     int fwd_n, void* stream);
 /* loss_sum = (accumulate ? loss_sum : 0) + sum of per-sample NLL; dlogits (may be NULL) = gscale * dNLL.
  * dbias (optional, needs dlogits and B <= 4096): dbias[c] = sum over samples of dlogits[.][c], c < ld --
  * the bias gradient of the classifier layer, in a fixed summation order. */
