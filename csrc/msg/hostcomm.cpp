@@ -17,6 +17,15 @@
 //  * Cancel has real semantics (the reference leaks a posted receive at shutdown,
 //    /root/reference/init.lua:88-90): a receive that is still unmatched or a send that has not begun
 //    to hit the wire is withdrawn and reports cancelled; anything further along completes.
+//  * Large non-blocking sends between processes of one host use a rendezvous with a single copy:
+//    the sender ships a 24-byte descriptor (address, size, request id, pid) instead of the payload,
+//    and the receiver, once a receive has matched, pulls the data straight out of the sender's
+//    address space with process_vm_readv (Linux cross-memory attach) into the user buffer and
+//    acknowledges.  Nothing is buffered for a message nobody has asked for yet -- what the
+//    reference gets from probe-first receives (/root/reference/init.lua:77-90) and MPI libraries
+//    from their intra-node rendezvous protocols.  Whether a peer can read this process is
+//    established at init (same host, same user, ptrace policy); otherwise, and for blocking sends
+//    and small messages, the payload travels through the socket as before.
 //  * Collectives are built on the same transport with a reserved communicator id bit, binomial
 //    trees for bcast/reduce, and a helper thread for the non-blocking all-reduce.
 #include "mpit_msg.h"
@@ -33,7 +42,9 @@
 #include <stdlib.h>
 #include <string.h>
 #include <sys/eventfd.h>
+#include <sys/prctl.h>
 #include <sys/socket.h>
+#include <sys/uio.h>
 #include <time.h>
 #include <unistd.h>
 
@@ -57,7 +68,19 @@ constexpr int kNbcBit = 0x20000000;    // ... and for non-blocking collectives
 struct Frame {
   int32_t tag;
   int32_t comm;
-  int64_t nbytes;
+  int64_t nbytes;             // payload bytes; the two bits below mark control frames
+};
+
+constexpr int64_t kRtsBit = 1LL << 62;   // "ready to send": the body is an RtsDesc, the data stays with the sender
+constexpr int64_t kFinBit = 1LL << 61;   // "finished": tag = the sender's request id, comm = error class
+constexpr int64_t kLenMask = kFinBit - 1;
+constexpr int kCapsComm = 0x7FFFFFF0;    // wire id of the capability exchange at init
+
+struct RtsDesc {
+  uint64_t addr;              // payload address in the sender
+  int64_t size;               // payload bytes
+  int32_t sreq;               // sender's request id (echoed in the FIN frame)
+  int32_t pid;
 };
 
 enum ReqKind { REQ_SEND, REQ_RECV, REQ_COLL };
@@ -78,6 +101,8 @@ struct Req {
   int src_tag = 0;
   size_t got = 0;
   int error = MPIT_SUCCESS;
+  bool rndv = false;          // send: completes on the receiver's FIN, not when the frame has left
+  RtsDesc rts{};
   std::thread worker;         // REQ_COLL
 };
 
@@ -89,6 +114,9 @@ struct Unexpected {
   size_t got = 0;
   bool complete = false;
   Req* claimed = nullptr;     // receive that matched while the payload was still arriving
+  bool is_rts = false;        // rendezvous: no data here, `rts` says where to pull it from
+  RtsDesc rts{};
+  size_t size() const { return is_rts ? (size_t)rts.size : data.size(); }
 };
 
 struct SendItem {
@@ -110,6 +138,9 @@ struct Peer {
   size_t body_got = 0;
   size_t body_len = 0;
   size_t deliver_cap = 0;
+  int ctrl = 0;               // 0 data frame, 1 RTS (body -> rts), 2 FIN
+  RtsDesc rts{};
+  bool reads_me = false;      // the peer can process_vm_readv this process (rendezvous allowed towards it)
 };
 
 struct Comm {
@@ -136,6 +167,8 @@ struct State {
   std::map<int, Comm> comms;   // handle -> comm
   int next_comm = 2;
   long long stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  size_t rndv_min = 256 << 10;   // MPIT_CMA_MIN: smallest Isend that goes through the rendezvous
+  bool cma_enabled = true;       // MPIT_CMA=0 turns the rendezvous off
 };
 
 State g;
@@ -202,13 +235,53 @@ void complete_recv(Req* r, int src, int tag, size_t nbytes) {
   g.stats[3] += (long long)nbytes;
 }
 
+// Pull `n` bytes out of another process of this host.  No lock needed.
+bool cma_read(int pid, uint64_t addr, void* dst, size_t n) {
+  char* out = static_cast<char*>(dst);
+  size_t done = 0;
+  while (done < n) {
+    iovec local{out + done, n - done};
+    iovec remote{reinterpret_cast<void*>(addr + done), n - done};
+    ssize_t k = process_vm_readv(pid, &local, 1, &remote, 1, 0);
+    if (k <= 0) {
+      if (k < 0 && errno == EINTR) continue;
+      return false;
+    }
+    done += (size_t)k;
+  }
+  return true;
+}
+
+void wake();
+
+// Tell the sender of a rendezvous that its buffer has been read (or could not be).  Caller holds g.mu.
+void queue_fin(int dst_world, int sreq, int error) {
+  SendItem it{};
+  it.req = nullptr;
+  it.hdr.tag = sreq; it.hdr.comm = error; it.hdr.nbytes = kFinBit;
+  it.payload = nullptr;
+  g.peers[dst_world].sendq.push_back(it);
+}
+
+// A rendezvous descriptor has matched receive `r`: copy, complete, acknowledge.  Caller holds g.mu (the copy runs
+// under it on the progress thread; irecv_wire releases it around its own copy).
+void deliver_rts(Req* r, int src, int tag, const RtsDesc& d) {
+  size_t n = std::min((size_t)d.size, r->cap);
+  bool ok = cma_read(d.pid, d.addr, r->buf, n);
+  complete_recv(r, src, tag, (size_t)d.size);
+  if (!ok) r->error = MPIT_ERR_OTHER;
+  queue_fin(src, d.sreq, ok ? MPIT_SUCCESS : MPIT_ERR_OTHER);
+}
+
 // A header from `src` has been read: choose where the payload goes.  Caller holds g.mu.
 void route_incoming(Peer& p, int src) {
   p.in_body = true;
   p.body_got = 0;
-  p.body_len = (size_t)p.hdr.nbytes;
   p.rreq = nullptr;
   p.runx = nullptr;
+  p.ctrl = (p.hdr.nbytes & kRtsBit) ? 1 : (p.hdr.nbytes & kFinBit) ? 2 : 0;
+  p.body_len = (size_t)(p.hdr.nbytes & kLenMask);
+  if (p.ctrl) return;         // control frames are interpreted in finish_incoming
   for (auto it = g.posted.begin(); it != g.posted.end(); ++it) {
     Req* r = *it;
     if (match(r->peer, r->tag, r->comm, src, p.hdr.tag, p.hdr.comm)) {
@@ -226,7 +299,32 @@ void route_incoming(Peer& p, int src) {
 }
 
 void finish_incoming(Peer& p, int src) {
-  if (p.rreq) {
+  if (p.ctrl == 2) {                       // FIN: the peer has read the buffer of send request hdr.tag
+    auto it = g.reqs.find(p.hdr.tag);
+    if (it != g.reqs.end() && it->second->rndv && !it->second->done) {
+      Req* r = it->second.get();
+      r->error = p.hdr.comm;
+      r->done = true;
+      g.stats[0]++;
+      g.stats[1] += (long long)r->cap;
+    }
+  } else if (p.ctrl == 1) {                // RTS: match now, or remember the descriptor
+    Req* hit = nullptr;
+    for (auto it = g.posted.begin(); it != g.posted.end(); ++it)
+      if (match((*it)->peer, (*it)->tag, (*it)->comm, src, p.hdr.tag, p.hdr.comm)) {
+        hit = *it;
+        g.posted.erase(it);
+        break;
+      }
+    if (hit) {
+      deliver_rts(hit, src, p.hdr.tag, p.rts);
+    } else {
+      auto u = std::make_unique<Unexpected>();
+      u->src = src; u->tag = p.hdr.tag; u->comm = p.hdr.comm;
+      u->is_rts = true; u->rts = p.rts; u->complete = true; u->got = (size_t)p.rts.size;
+      g.unexpected.push_back(std::move(u));
+    }
+  } else if (p.rreq) {
     complete_recv(p.rreq, src, p.hdr.tag, p.body_len);
   } else if (p.runx) {
     Unexpected* u = p.runx;
@@ -263,7 +361,9 @@ bool pump_recv(int src) {
     char* dst;
     size_t want = p.body_len - p.body_got;
     static thread_local std::vector<char> sink;
-    if (p.rreq) {
+    if (p.ctrl == 1) {
+      dst = reinterpret_cast<char*>(&p.rts) + p.body_got;
+    } else if (p.rreq) {
       if (p.body_got < p.deliver_cap) {
         dst = static_cast<char*>(p.rreq->buf) + p.body_got;
         want = std::min(want, p.deliver_cap - p.body_got);
@@ -287,7 +387,7 @@ bool pump_send(int dst) {
   Peer& p = g.peers[dst];
   while (!p.sendq.empty()) {
     SendItem& it = p.sendq.front();
-    size_t total = sizeof(Frame) + (size_t)it.hdr.nbytes;
+    size_t total = sizeof(Frame) + (size_t)(it.hdr.nbytes & kLenMask);
     while (it.off < total) {
       const char* src;
       size_t n;
@@ -306,9 +406,11 @@ bool pump_send(int dst) {
       if (it.req) it.req->started = true;
       it.off += (size_t)k;
     }
-    if (it.req) { it.req->done = true; }
-    g.stats[0]++;
-    g.stats[1] += it.hdr.nbytes;
+    if (it.req && !it.req->rndv) { it.req->done = true; }
+    if (!(it.hdr.nbytes & (kRtsBit | kFinBit))) {
+      g.stats[0]++;
+      g.stats[1] += it.hdr.nbytes;
+    }
     p.sendq.pop_front();
     g.cv.notify_all();
   }
@@ -384,7 +486,8 @@ void fill_status(mpit_status* st, const Req* r, const Comm* c) {
 }
 
 // ---- core p2p on wire ids (caller holds no lock) ------------------------------------------------
-int isend_wire(const void* buf, size_t nbytes, int dst_world, int tag, int wire_comm, Req** out) {
+int isend_wire(const void* buf, size_t nbytes, int dst_world, int tag, int wire_comm, Req** out,
+               bool may_rendezvous = false) {
   std::unique_lock<std::mutex> lk(g.mu);
   Req* r = new_req(REQ_SEND);
   r->peer = dst_world; r->tag = tag; r->comm = wire_comm;
@@ -417,8 +520,19 @@ int isend_wire(const void* buf, size_t nbytes, int dst_world, int tag, int wire_
     if (g.peers[dst_world].fd < 0) { r->error = MPIT_ERR_OTHER; r->done = true; *out = r; return MPIT_ERR_OTHER; }
     SendItem it{};
     it.req = r;
-    it.hdr.tag = tag; it.hdr.comm = wire_comm; it.hdr.nbytes = (int64_t)nbytes;
-    it.payload = static_cast<const char*>(buf);
+    it.hdr.tag = tag; it.hdr.comm = wire_comm;
+    if (may_rendezvous && g.cma_enabled && g.peers[dst_world].reads_me && nbytes >= g.rndv_min) {
+      r->rndv = true;
+      r->rts.addr = (uint64_t)(uintptr_t)buf;
+      r->rts.size = (int64_t)nbytes;
+      r->rts.sreq = r->id;
+      r->rts.pid = (int32_t)getpid();
+      it.hdr.nbytes = kRtsBit | (int64_t)sizeof(RtsDesc);
+      it.payload = reinterpret_cast<const char*>(&r->rts);
+    } else {
+      it.hdr.nbytes = (int64_t)nbytes;
+      it.payload = static_cast<const char*>(buf);
+    }
     g.peers[dst_world].sendq.push_back(it);
     lk.unlock();
     wake();
@@ -428,12 +542,30 @@ int isend_wire(const void* buf, size_t nbytes, int dst_world, int tag, int wire_
 }
 
 int irecv_wire(void* buf, size_t cap, int src_world, int tag, int wire_comm, Req** out) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::unique_lock<std::mutex> lk(g.mu);
   Req* r = new_req(REQ_RECV);
   r->peer = src_world; r->tag = tag; r->comm = wire_comm; r->buf = buf; r->cap = cap;
   for (auto it = g.unexpected.begin(); it != g.unexpected.end(); ++it) {
     Unexpected* u = it->get();
     if (u->claimed || !match(src_world, tag, wire_comm, u->src, u->tag, u->comm)) continue;
+    if (u->is_rts) {
+      // rendezvous: the data is still in the sender; pull it on this thread, without the lock (the request is in
+      // no list, so nobody else can touch it; it is not done, so it cannot be freed)
+      const RtsDesc d = u->rts;
+      const int src = u->src, utag = u->tag;
+      g.unexpected.erase(it);
+      lk.unlock();
+      bool ok = cma_read(d.pid, d.addr, buf, std::min((size_t)d.size, cap));
+      lk.lock();
+      complete_recv(r, src, utag, (size_t)d.size);
+      if (!ok) r->error = MPIT_ERR_OTHER;
+      queue_fin(src, d.sreq, ok ? MPIT_SUCCESS : MPIT_ERR_OTHER);
+      g.cv.notify_all();
+      lk.unlock();
+      wake();
+      *out = r;
+      return MPIT_SUCCESS;
+    }
     if (u->complete) {
       memcpy(buf, u->data.data(), std::min(cap, u->data.size()));
       complete_recv(r, u->src, u->tag, u->data.size());
@@ -463,6 +595,64 @@ void free_req_locked(int id) {
   g.reqs.erase(it);
 }
 
+int send_wire_blocking(const void* buf, size_t n, int dst_world, int tag, int wire_comm);
+int recv_wire_blocking(void* buf, size_t cap, int src_world, int tag, int wire_comm, size_t* got = nullptr);
+
+// Who can read whose memory?  Every rank tells every other {pid, boot id hash, uid, address and value of a probe
+// word}; a rank that finds a peer on its own host tries process_vm_readv on the probe word and reports the verdict
+// back.  peers[i].reads_me is then "rank i may pull my send buffers".  Runs once at the end of init.
+static volatile uint64_t g_probe_word = 0;
+
+uint64_t boot_id_hash() {
+  uint64_t h = 1469598103934665603ull;
+  FILE* f = fopen("/proc/sys/kernel/random/boot_id", "r");
+  char buf[64] = {0};
+  if (f) { size_t k = fread(buf, 1, sizeof(buf) - 1, f); (void)k; fclose(f); }
+  else if (gethostname(buf, sizeof(buf) - 1) != 0) strcpy(buf, "?");
+  for (char* c = buf; *c; ++c) h = (h ^ (uint64_t)(unsigned char)*c) * 1099511628211ull;
+  // processes in different PID namespaces cannot name each other: fold the namespace in
+  char ns[64] = {0};
+  ssize_t k = readlink("/proc/self/ns/pid", ns, sizeof(ns) - 1);
+  for (ssize_t i = 0; i < k; ++i) h = (h ^ (uint64_t)(unsigned char)ns[i]) * 1099511628211ull;
+  return h;
+}
+
+void exchange_cma_caps() {
+  if (const char* e = getenv("MPIT_CMA")) g.cma_enabled = atoi(e) != 0;
+  if (const char* e = getenv("MPIT_CMA_MIN")) { long long v = atoll(e); if (v > 0) g.rndv_min = (size_t)v; }
+  if (g.size <= 1) return;
+#ifdef PR_SET_PTRACER
+  prctl(PR_SET_PTRACER, PR_SET_PTRACER_ANY, 0, 0, 0);   // Yama scope 1: let sibling ranks attach for reading
+#endif
+  struct Card { uint64_t boot; uint64_t addr; uint64_t value; int32_t pid; int32_t uid; } mine;
+  g_probe_word = 0x6d706954ull * 2654435761ull + (uint64_t)g.rank;
+  mine.boot = boot_id_hash();
+  mine.addr = (uint64_t)(uintptr_t)&g_probe_word;
+  mine.value = g_probe_word;
+  mine.pid = (int32_t)getpid();
+  mine.uid = (int32_t)getuid();
+  for (int p = 0; p < g.size; ++p)
+    if (p != g.rank) send_wire_blocking(&mine, sizeof(mine), p, 0, kCapsComm);
+  std::vector<int32_t> verdict((size_t)g.size, 0);
+  for (int p = 0; p < g.size; ++p) {
+    if (p == g.rank) continue;
+    Card c{};
+    if (recv_wire_blocking(&c, sizeof(c), p, 0, kCapsComm, nullptr) != MPIT_SUCCESS) continue;
+    if (!g.cma_enabled || c.boot != mine.boot || c.uid != mine.uid) continue;
+    uint64_t got = 0;
+    verdict[(size_t)p] = cma_read(c.pid, c.addr, &got, sizeof(got)) && got == c.value ? 1 : 0;
+  }
+  for (int p = 0; p < g.size; ++p)
+    if (p != g.rank) send_wire_blocking(&verdict[(size_t)p], sizeof(int32_t), p, 1, kCapsComm);
+  for (int p = 0; p < g.size; ++p) {
+    if (p == g.rank) continue;
+    int32_t v = 0;
+    if (recv_wire_blocking(&v, sizeof(v), p, 1, kCapsComm, nullptr) != MPIT_SUCCESS) v = 0;
+    std::lock_guard<std::mutex> lk(g.mu);
+    g.peers[(size_t)p].reads_me = v != 0;
+  }
+}
+
 int send_wire_blocking(const void* buf, size_t n, int dst_world, int tag, int wire_comm) {
   Req* r;
   int rc = isend_wire(buf, n, dst_world, tag, wire_comm, &r);
@@ -472,7 +662,7 @@ int send_wire_blocking(const void* buf, size_t n, int dst_world, int tag, int wi
   free_req_locked(r->id);
   return rc;
 }
-int recv_wire_blocking(void* buf, size_t cap, int src_world, int tag, int wire_comm, size_t* got = nullptr) {
+int recv_wire_blocking(void* buf, size_t cap, int src_world, int tag, int wire_comm, size_t* got) {
   Req* r;
   int rc = irecv_wire(buf, cap, src_world, tag, wire_comm, &r);
   if (rc) return rc;
@@ -715,6 +905,8 @@ int mpit_msg_init(int rank, int size, const char* master_addr, int master_port, 
   }
   g.inited = true;
   g.progress = std::thread(progress_loop);
+  lk.unlock();                // the capability exchange uses the message layer itself
+  exchange_cma_caps();
   return MPIT_SUCCESS;
 }
 
@@ -866,7 +1058,8 @@ int mpit_msg_comm_free(int* comm) {
 }
 
 // ---- point to point ------------------------------------------------------------------------------------
-int mpit_msg_isend(const void* buf, long long count, int dtype, int dest, int tag, int comm, int* request) {
+static int isend_checked(const void* buf, long long count, int dtype, int dest, int tag, int comm, int* request,
+                         bool may_rendezvous) {
   size_t es = dtype_size(dtype);
   if (!es) return MPIT_ERR_TYPE;
   if (count < 0) return MPIT_ERR_COUNT;
@@ -881,9 +1074,15 @@ int mpit_msg_isend(const void* buf, long long count, int dtype, int dest, int ta
     wire = c->id;
   }
   Req* r;
-  int rc = isend_wire(buf, (size_t)count * es, world, tag, wire, &r);
+  int rc = isend_wire(buf, (size_t)count * es, world, tag, wire, &r, may_rendezvous);
   *request = r->id;
   return rc;
+}
+
+// Non-blocking sends of large messages to a peer on this host go through the single-copy rendezvous and complete
+// when the receiver has read the buffer; everything else is eager.
+int mpit_msg_isend(const void* buf, long long count, int dtype, int dest, int tag, int comm, int* request) {
+  return isend_checked(buf, count, dtype, dest, tag, comm, request, true);
 }
 
 int mpit_msg_irecv(void* buf, long long count, int dtype, int source, int tag, int comm, int* request) {
@@ -993,9 +1192,11 @@ int mpit_msg_waitany(int n, int* requests, int* index, mpit_status* status) {
   }
 }
 
+// Blocking send: always eager (returns once the payload is in the socket), so that two processes may both send
+// before they receive -- a rendezvous here would turn that legal-if-buffered pattern into a deadlock.
 int mpit_msg_send(const void* buf, long long count, int dtype, int dest, int tag, int comm) {
   int req;
-  int rc = mpit_msg_isend(buf, count, dtype, dest, tag, comm, &req);
+  int rc = isend_checked(buf, count, dtype, dest, tag, comm, &req, false);
   if (rc) return rc;
   return mpit_msg_wait(&req, nullptr);
 }
@@ -1035,7 +1236,7 @@ int mpit_msg_iprobe(int source, int tag, int comm, int* flag, mpit_status* statu
       status->source = it == c->ranks.end() ? u->src : (int)(it - c->ranks.begin());
       status->tag = u->tag;
       status->error = MPIT_SUCCESS;
-      status->count_bytes = (long long)u->data.size();
+      status->count_bytes = (long long)u->size();
       status->cancelled = 0;
     }
     break;

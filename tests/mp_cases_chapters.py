@@ -384,4 +384,84 @@ def case_c_intercomm():
             os.unlink(addr_file)
 
 
+
+
+def case_c_rendezvous():
+    """Large non-blocking sends between processes of one host: single-copy rendezvous (process_vm_readv).  Both
+    arrival orders, wildcards, probe counts, truncation, ordering against small eager messages, cancellation of an
+    unmatched send.  With MPIT_CMA=0 the same body runs over the socket path."""
+    import time
+    rank, size = mpiT.get_rank(), mpiT.get_size()
+    n = 1 << 20                                           # 4 MiB of floats: far above the 256 KiB threshold
+    right, left = (rank + 1) % size, (rank - 1) % size
+    src = torch.arange(n, dtype=torch.float32) + rank * 1e6
+    # 1. receive posted first (descriptor meets a posted receive on the progress thread)
+    dst = torch.zeros(n)
+    req = mpiT.Request(2)
+    mpiT.Irecv(dst, n, mpiT.FLOAT, left, 11, mpiT.COMM_WORLD, req, 0)
+    mpiT.Barrier()
+    mpiT.Isend(src, n, mpiT.FLOAT, right, 11, mpiT.COMM_WORLD, req, 1)
+    st = mpiT.Status()
+    mpiT.Wait(req, st, 0)
+    mpiT.Wait(req, None, 1)
+    assert st.source == left and st.tag == 11 and mpiT.Get_count(st, mpiT.FLOAT) == n
+    assert torch.equal(dst, torch.arange(n, dtype=torch.float32) + left * 1e6)
+    # 2. send first: the message is visible to Iprobe with its full size while the data is still with the sender
+    before = mpiT.stats()["bytes_recv"]
+    mpiT.Isend(src, n, mpiT.FLOAT, right, 12, mpiT.COMM_WORLD, req, 1)
+    while not mpiT.Iprobe(mpiT.ANY_SOURCE, 12, mpiT.COMM_WORLD, st):
+        time.sleep(0.001)
+    assert st.source == left and mpiT.Get_count(st, mpiT.FLOAT) == n
+    if os.environ.get("MPIT_CMA", "1") != "0":
+        assert not mpiT.Test(req, None, 1)                # not complete before the receiver has pulled it
+        assert mpiT.stats()["bytes_recv"] - before < n    # ... and nothing was buffered on this side
+    mpiT.Barrier()                                        # nobody pulls before everybody has looked
+    dst.zero_()
+    mpiT.Recv(dst, n, mpiT.FLOAT, mpiT.ANY_SOURCE, 12, mpiT.COMM_WORLD, st)
+    assert st.source == left and torch.equal(dst, torch.arange(n, dtype=torch.float32) + left * 1e6)
+    mpiT.Wait(req, None, 1)
+    # 3. non-overtaking: small eager, large rendezvous, small eager on one tag arrive in that order
+    a, c = torch.tensor([1.0 + rank]), torch.tensor([3.0 + rank])
+    r3 = mpiT.Request(3)
+    mpiT.Isend(a, 1, mpiT.FLOAT, right, 13, mpiT.COMM_WORLD, r3, 0)
+    mpiT.Isend(src, n, mpiT.FLOAT, right, 13, mpiT.COMM_WORLD, r3, 1)
+    mpiT.Isend(c, 1, mpiT.FLOAT, right, 13, mpiT.COMM_WORLD, r3, 2)
+    x, z = torch.zeros(1), torch.zeros(1)
+    dst.zero_()
+    mpiT.Recv(x, 1, mpiT.FLOAT, left, 13)
+    mpiT.Recv(dst, n, mpiT.FLOAT, left, 13)
+    mpiT.Recv(z, 1, mpiT.FLOAT, left, 13)
+    assert float(x) == 1.0 + left and float(z) == 3.0 + left and float(dst[5]) == 5 + left * 1e6
+    mpiT.Waitall(r3)
+    # 4. truncation: a short receive gets the head of the message and the error
+    mpiT.Isend(src, n, mpiT.FLOAT, right, 14, mpiT.COMM_WORLD, req, 1)
+    small = torch.zeros(100)
+    try:
+        mpiT.Recv(small, 100, mpiT.FLOAT, left, 14, mpiT.COMM_WORLD, st)
+        raise AssertionError("truncation not reported")
+    except mpiT.MPIError as e:
+        assert e.code == mpiT.ERR_TRUNCATE
+    assert torch.equal(small, torch.arange(100, dtype=torch.float32) + left * 1e6)
+    mpiT.Wait(req, None, 1)                               # the sender still completes
+    # 5. Sendrecv of large buffers in both directions at once
+    back = torch.zeros(n)
+    mpiT.Sendrecv(src, n, mpiT.FLOAT, right, 15, back, n, mpiT.FLOAT, left, 15)
+    assert float(back[-1]) == n - 1 + left * 1e6
+    # 6. a large send nobody receives can no longer be withdrawn once announced; it completes when matched
+    mpiT.Barrier()
+    if rank == 0:
+        mpiT.Isend(src, n, mpiT.FLOAT, 1, 16, mpiT.COMM_WORLD, req, 1)
+        time.sleep(0.05)
+        mpiT.Cancel(req, 1)
+        mpiT.Send(None, 0, mpiT.BYTE, 1, 17)             # "now receive it"
+        mpiT.Wait(req, st, 1)
+        assert not mpiT.Test_cancelled(st)
+    elif rank == 1:
+        mpiT.Recv(None, 0, mpiT.BYTE, 0, 17)
+        dst.zero_()
+        mpiT.Recv(dst, n, mpiT.FLOAT, 0, 16)
+        assert float(dst[7]) == 7.0
+    mpiT.Barrier()
+
+
 CASES = {k[5:]: v for k, v in globals().items() if k.startswith("case_")}

@@ -142,6 +142,11 @@ def case_ps_server_adam():
 
         for _ in grads:
             R.adam(opfunc, w, cfg)
+        # Each step queues its push and its pull together, and the server serves them from separate coroutines with no
+        # lock between them ("expect inconsistent read", pserver.lua:81): the pull of step t may or may not contain
+        # gradient t.  Every push has been acknowledged by now, so one more pull is the server's final state.
+        pc.async_recv_param()
+        pc.wait()
         pc.stop()
         p = w0.clone()
         st = R.rule_state("adam", p)

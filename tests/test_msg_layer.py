@@ -92,3 +92,10 @@ def test_mpi_chapters_multi_process(case, nproc):
     attributes across Comm_dup, inter-communicators / ports / Comm_join (msg/datatypes.py, topo.py, fileio.py, rma.py,
     attrs.py, dynproc.py)."""
     _run(case, nproc)
+
+
+@pytest.mark.parametrize("cma", ["1", "0"])
+def test_large_message_rendezvous(cma):
+    """Single-copy rendezvous for large Isends on one host (csrc/msg/hostcomm.cpp) and the socket path it falls back
+    to: same observable behaviour except that the rendezvous buffers nothing at the receiver."""
+    _run("c_rendezvous", 3, env={"MPIT_CMA": cma})
