@@ -83,7 +83,6 @@ class Datatype:
         self.name = ""
         self.handle = -1
         self._blocks: Optional[Tuple[np.ndarray, np.ndarray]] = None
-        self._byte_index: Optional[np.ndarray] = None
 
     def elem_sizes(self) -> np.ndarray:
         table = np.array([np.dtype(_NP[k]).itemsize for k in range(_NKINDS)], dtype=np.int64)
@@ -104,14 +103,6 @@ class Datatype:
                 self._blocks = (np.ascontiguousarray(self.disp[starts]),
                                 np.ascontiguousarray(csum[ends] - csum[starts]))
         return self._blocks
-
-    def byte_index(self) -> np.ndarray:
-        """Byte offsets (relative to the buffer address) of one instance's packed stream."""
-        if self._byte_index is None:
-            d, n = self.blocks()
-            self._byte_index = (np.concatenate([np.arange(a, a + b) for a, b in zip(d, n)])
-                                if d.size else np.zeros(0, np.int64))
-        return self._byte_index
 
 
 _TYPES: Dict[int, Datatype] = {}
