@@ -29,7 +29,7 @@ def main():
     for k in kernels:
         name_m, body = k.split("\n", 1)
         name = subprocess.run(["c++filt", name_m.strip()], capture_output=True, text=True).stdout.strip() or name_m
-        short = re.sub(r"\(.*", "", name).replace("void ", "").replace("mpit::", "")
+        short = re.sub(r"\(.*", "", name.replace("(anonymous namespace)::", "")).replace("void ", "").replace("mpit::", "")
         cnt = Counter()
         for label, pat in KEYS:
             cnt[label] = len(re.findall(pat, body))
