@@ -115,6 +115,13 @@ def _chk(code: int, what: str):
         raise MPIError(code, what)
 
 
+def _intra(comm, what: str):
+    """Collectives take intra-communicators; an inter-communicator has to be merged first (Intercomm_merge)."""
+    if not isinstance(comm, int):
+        raise MPIError(5, f"{what} on an inter-communicator (use Intercomm_merge and call it on the result)")
+    return comm
+
+
 class _Buf:
     """Resolve a user buffer to (host pointer, keep-alive, completion hook)."""
 
@@ -268,6 +275,7 @@ get_size = Comm_size
 def Comm_dup(comm: int) -> int:
     """Duplicates the communicator together with its cached attributes (through their copy callbacks) and its
     topology."""
+    comm = _intra(comm, "Comm_dup")
     r = ctypes.c_int(0)
     _chk(host().mpit_msg_comm_dup(comm, ctypes.byref(r)), "Comm_dup")
     attrs.copy_attrs("comm", comm, r.value)
@@ -277,6 +285,7 @@ def Comm_dup(comm: int) -> int:
 
 
 def Comm_split(comm: int, color: int, key: int) -> int:
+    comm = _intra(comm, "Comm_split")
     r = ctypes.c_int(0)
     _chk(host().mpit_msg_comm_split(comm, color, key, ctypes.byref(r)), "Comm_split")
     return r.value
@@ -441,10 +450,12 @@ def Get_count(status: Status, dtype: int) -> int:
 
 # ---- collectives ----------------------------------------------------------------------------------------------
 def Barrier(comm: int = COMM_WORLD) -> None:
+    comm = _intra(comm, "Barrier")
     _chk(host().mpit_msg_barrier(comm), "Barrier")
 
 
 def Bcast(buf, count: int, dtype: int, root: int, comm: int = COMM_WORLD) -> None:
+    comm = _intra(comm, "Bcast")
     b = _Buf(buf, count, dtype, True)
     if b.after and Comm_rank(comm) == root and dtype < datatypes.DERIVED_BASE:
         b.keep[1].copy_(b.keep[0].view(-1)[:b.keep[1].numel()])   # root's device data must be staged out first
@@ -454,6 +465,7 @@ def Bcast(buf, count: int, dtype: int, root: int, comm: int = COMM_WORLD) -> Non
 
 
 def Reduce(sbuf, rbuf, count: int, dtype: int, op: int, root: int, comm: int = COMM_WORLD) -> None:
+    comm = _intra(comm, "Reduce")
     if extras.needs_packed_reduce(dtype, op):
         return extras.reduce_packed(sbuf, rbuf, count, dtype, op, root, comm, everyone=False)
     if extras.is_user_op(op):
@@ -467,6 +479,7 @@ def Reduce(sbuf, rbuf, count: int, dtype: int, op: int, root: int, comm: int = C
 def Allreduce(sbuf, rbuf, count: int, dtype: int, op: int, comm: int = COMM_WORLD) -> None:
     """MPI_Allreduce (/root/reference/test/testreduceall.lua:28).  The ten basic datatypes with SUM..BOR run in the
     native reducer; user operations, LXOR / BXOR, MAXLOC / MINLOC and the packed datatypes are folded on rank 0."""
+    comm = _intra(comm, "Allreduce")
     if extras.needs_packed_reduce(dtype, op):
         return extras.reduce_packed(sbuf, rbuf, count, dtype, op, 0, comm, everyone=True)
     if extras.is_user_op(op):
@@ -479,12 +492,14 @@ def Allreduce(sbuf, rbuf, count: int, dtype: int, op: int, comm: int = COMM_WORL
 
 def Iallreduce(sbuf, rbuf, count: int, dtype: int, op: int, comm: int, request: Request, i: int = 0) -> None:
     """MPI_Iallreduce (/root/reference/test/testireduceall.lua:32); complete it with Test/Wait."""
+    comm = _intra(comm, "Iallreduce")
     s, r = _Buf(sbuf, count, dtype, False), _Buf(rbuf, count, dtype, True)
     request._keep[i], request._after[i] = (s.keep, r.keep), r.after
     _chk(host().mpit_msg_iallreduce(s.ptr, r.ptr, count, dtype, op, comm, request._ptr(i)), "Iallreduce")
 
 
 def Gather(sbuf, scount: int, dtype: int, rbuf, root: int, comm: int = COMM_WORLD) -> None:
+    comm = _intra(comm, "Gather")
     n = Comm_size(comm)
     s = _Buf(sbuf, scount, dtype, False)
     r = _Buf(rbuf, scount * n, dtype, True) if Comm_rank(comm) == root else _Buf(None, 0, dtype, True)
@@ -494,6 +509,7 @@ def Gather(sbuf, scount: int, dtype: int, rbuf, root: int, comm: int = COMM_WORL
 
 
 def Allgather(sbuf, scount: int, dtype: int, rbuf, comm: int = COMM_WORLD) -> None:
+    comm = _intra(comm, "Allgather")
     s, r = _Buf(sbuf, scount, dtype, False), _Buf(rbuf, scount * Comm_size(comm), dtype, True)
     _chk(host().mpit_msg_allgather(s.ptr, scount, dtype, r.ptr, comm), "Allgather")
     if r.after:
@@ -501,6 +517,7 @@ def Allgather(sbuf, scount: int, dtype: int, rbuf, comm: int = COMM_WORLD) -> No
 
 
 def Scatter(sbuf, count: int, dtype: int, rbuf, root: int, comm: int = COMM_WORLD) -> None:
+    comm = _intra(comm, "Scatter")
     n = Comm_size(comm)
     s = _Buf(sbuf, count * n, dtype, False) if Comm_rank(comm) == root else _Buf(None, 0, dtype, False)
     r = _Buf(rbuf, count, dtype, True)
@@ -510,6 +527,7 @@ def Scatter(sbuf, count: int, dtype: int, rbuf, root: int, comm: int = COMM_WORL
 
 
 def Alltoall(sbuf, count: int, dtype: int, rbuf, comm: int = COMM_WORLD) -> None:
+    comm = _intra(comm, "Alltoall")
     n = Comm_size(comm)
     s, r = _Buf(sbuf, count * n, dtype, False), _Buf(rbuf, count * n, dtype, True)
     _chk(host().mpit_msg_alltoall(s.ptr, count, dtype, r.ptr, comm), "Alltoall")
@@ -518,6 +536,7 @@ def Alltoall(sbuf, count: int, dtype: int, rbuf, comm: int = COMM_WORLD) -> None
 
 
 def Reduce_scatter_block(sbuf, rbuf, count: int, dtype: int, op: int, comm: int = COMM_WORLD) -> None:
+    comm = _intra(comm, "Reduce_scatter_block")
     s, r = _Buf(sbuf, count * Comm_size(comm), dtype, False), _Buf(rbuf, count, dtype, True)
     _chk(host().mpit_msg_reduce_scatter_block(s.ptr, r.ptr, count, dtype, op, comm), "Reduce_scatter_block")
     if r.after:
@@ -525,6 +544,7 @@ def Reduce_scatter_block(sbuf, rbuf, count: int, dtype: int, op: int, comm: int 
 
 
 def Scan(sbuf, rbuf, count: int, dtype: int, op: int, comm: int = COMM_WORLD) -> None:
+    comm = _intra(comm, "Scan")
     s, r = _Buf(sbuf, count, dtype, False), _Buf(rbuf, count, dtype, True)
     _chk(host().mpit_msg_scan(s.ptr, r.ptr, count, dtype, op, comm), "Scan")
     if r.after:
