@@ -73,7 +73,9 @@ struct Frame {
 
 constexpr int64_t kRtsBit = 1LL << 62;   // "ready to send": the body is an RtsDesc, the data stays with the sender
 constexpr int64_t kFinBit = 1LL << 61;   // "finished": tag = the sender's request id, comm = error class
-constexpr int64_t kLenMask = kFinBit - 1;
+constexpr int64_t kCanBit = 1LL << 60;   // "cancel": withdraw the RTS of send request `tag` if it is still unmatched
+constexpr int64_t kLenMask = kCanBit - 1;
+constexpr int kFinCancelled = -1;        // FIN status: the RTS was withdrawn, no data moved
 constexpr int kCapsComm = 0x7FFFFFF0;    // wire id of the capability exchange at init
 
 struct RtsDesc {
@@ -102,6 +104,7 @@ struct Req {
   size_t got = 0;
   int error = MPIT_SUCCESS;
   bool rndv = false;          // send: completes on the receiver's FIN, not when the frame has left
+  bool cancel_sent = false;   // send: a CANCEL frame is chasing the RTS
   RtsDesc rts{};
   std::thread worker;         // REQ_COLL
 };
@@ -279,7 +282,7 @@ void route_incoming(Peer& p, int src) {
   p.body_got = 0;
   p.rreq = nullptr;
   p.runx = nullptr;
-  p.ctrl = (p.hdr.nbytes & kRtsBit) ? 1 : (p.hdr.nbytes & kFinBit) ? 2 : 0;
+  p.ctrl = (p.hdr.nbytes & kRtsBit) ? 1 : (p.hdr.nbytes & kFinBit) ? 2 : (p.hdr.nbytes & kCanBit) ? 3 : 0;
   p.body_len = (size_t)(p.hdr.nbytes & kLenMask);
   if (p.ctrl) return;         // control frames are interpreted in finish_incoming
   for (auto it = g.posted.begin(); it != g.posted.end(); ++it) {
@@ -303,11 +306,24 @@ void finish_incoming(Peer& p, int src) {
     auto it = g.reqs.find(p.hdr.tag);
     if (it != g.reqs.end() && it->second->rndv && !it->second->done) {
       Req* r = it->second.get();
-      r->error = p.hdr.comm;
+      if (p.hdr.comm == kFinCancelled) {
+        r->cancelled = true;
+      } else {
+        r->error = p.hdr.comm;
+        g.stats[0]++;
+        g.stats[1] += (long long)r->cap;
+      }
       r->done = true;
-      g.stats[0]++;
-      g.stats[1] += (long long)r->cap;
     }
+  } else if (p.ctrl == 3) {                // CANCEL: withdraw the descriptor if no receive has taken it yet
+    for (auto it = g.unexpected.begin(); it != g.unexpected.end(); ++it) {
+      Unexpected* u = it->get();
+      if (u->is_rts && u->src == src && u->rts.sreq == p.hdr.tag && !u->claimed) {
+        g.unexpected.erase(it);
+        queue_fin(src, p.hdr.tag, kFinCancelled);
+        break;
+      }
+    }                                      // otherwise it has matched: the ordinary FIN is on its way (or there)
   } else if (p.ctrl == 1) {                // RTS: match now, or remember the descriptor
     Req* hit = nullptr;
     for (auto it = g.posted.begin(); it != g.posted.end(); ++it)
@@ -407,7 +423,7 @@ bool pump_send(int dst) {
       it.off += (size_t)k;
     }
     if (it.req && !it.req->rndv) { it.req->done = true; }
-    if (!(it.hdr.nbytes & (kRtsBit | kFinBit))) {
+    if (!(it.hdr.nbytes & (kRtsBit | kFinBit | kCanBit))) {
       g.stats[0]++;
       g.stats[1] += it.hdr.nbytes;
     }
@@ -1280,6 +1296,16 @@ int mpit_msg_cancel(int* request) {
         g.cv.notify_all();
         break;
       }
+  } else if (r->kind == REQ_SEND && r->rndv && !r->cancel_sent && r->peer != g.rank && g.peers[r->peer].fd >= 0) {
+    // the descriptor is out but the data has not moved: ask the receiver to drop it.  The request then completes
+    // either cancelled (descriptor still unmatched there) or normally (a receive had already taken it).
+    r->cancel_sent = true;
+    SendItem it{};
+    it.req = nullptr;
+    it.hdr.tag = r->id; it.hdr.comm = 0; it.hdr.nbytes = kCanBit;
+    it.payload = nullptr;
+    g.peers[r->peer].sendq.push_back(it);
+    wake();
   }
   return MPIT_SUCCESS;
 }
