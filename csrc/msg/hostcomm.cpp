@@ -1502,7 +1502,9 @@ int mpit_msg_stats(long long* stats8) {
   stats8[4] = (long long)g.unexpected.size();
   stats8[5] = (long long)g.posted.size();
   stats8[6] = (long long)g.reqs.size();
-  stats8[7] = 0;
+  long long rp = 0;
+  for (auto& p : g.peers) rp += p.reads_me ? 1 : 0;
+  stats8[7] = rp;             // peers large Isends reach through the single-copy rendezvous
   return MPIT_SUCCESS;
 }
 

@@ -120,7 +120,8 @@ int mpit_msg_reduce_scatter_block(const void* sbuf, void* rbuf, long long count,
 int mpit_msg_scan(const void* sbuf, void* rbuf, long long count, int dtype, int op, int comm);
 
 /* ---- introspection (tests, tracing) ------------------------------------------------------------------- */
-/* stats8: {msgs_sent, bytes_sent, msgs_recv, bytes_recv, unexpected_now, posted_now, requests_live, 0} */
+/* stats8: {msgs_sent, bytes_sent, msgs_recv, bytes_recv, unexpected_now, posted_now, requests_live,
+ *          rendezvous_peers (peers that may pull this process's large Isends with process_vm_readv)} */
 int mpit_msg_stats(long long* stats8);
 
 /* ---- derived-datatype engine (csrc/msg/hostio.cpp; /root/reference/mpifuncs.c Pack, Unpack, Type_*) --------

@@ -554,7 +554,8 @@ def Scan(sbuf, rbuf, count: int, dtype: int, op: int, comm: int = COMM_WORLD) ->
 def stats() -> dict:
     a = (ctypes.c_longlong * 8)()
     host().mpit_msg_stats(a)
-    keys = ("msgs_sent", "bytes_sent", "msgs_recv", "bytes_recv", "unexpected_now", "posted_now", "requests_live")
+    keys = ("msgs_sent", "bytes_sent", "msgs_recv", "bytes_recv", "unexpected_now", "posted_now", "requests_live",
+            "rendezvous_peers")
     return dict(zip(keys, list(a)))
 
 
