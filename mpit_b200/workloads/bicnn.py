@@ -210,7 +210,7 @@ class BiCNNTrainer:
                 loss = margin_ranking(gesd(qv, m.encode(at[keep], al[keep])), gesd(qv, m.encode(nt, nl)),
                                       opt["margin"]).sum()
                 loss.backward()
-                f = float(loss)
+                f = float(loss.detach())
             g, p = self.gradParameters, self.parameters
             if opt["L1reg"] != 0:                                              # bicnn.lua:398-402
                 f += opt["L1reg"] * float(p.abs().sum())

@@ -115,7 +115,7 @@ def run(opt_in: dict, model: torch.nn.Module, train_xy, test_xy, pclient=None, r
                     loss = torch.nn.functional.nll_loss(out, yb)   # mean over the mini-batch
                     loss.backward()
                     confusion.batch_add(out.detach(), yb)
-                    return float(loss), grad
+                    return float(loss.detach()), grad
 
             _, fx = opti(feval, theta, cfg)
             train_err += fx[0]
