@@ -537,8 +537,9 @@ def Comm_get_name(comm) -> str:
 class Win:
     """``MPI_Win_create`` over a host tensor.  Put / Get / Accumulate are queued at the origin and performed at the
     next :func:`Win_fence`, which is when MPI guarantees them complete under active-target synchronisation
-    (/root/reference/mpifuncs.c:2337,1656,1131,9,2367).  Passive target (Win_lock) needs a participant on the target
-    side with two-sided transport; it exists natively on the device path: :class:`mpit_b200.parallel.DeviceWindow`."""
+    (/root/reference/mpifuncs.c:2337,1656,1131,9,2367).  Inside a passive-target epoch (``Win_lock`` .. ``Win_unlock``,
+    rma.py) they are sent at once to the target's service thread instead.  The device-memory counterpart is
+    :class:`mpit_b200.parallel.DeviceWindow`."""
 
     def __init__(self, base, disp_unit: int, comm: int):
         self.base = _flat(base)
@@ -550,20 +551,33 @@ class Win:
 
 
 def Win_create(base, size_bytes: int, disp_unit: int, info=None, comm=0) -> Win:
-    return Win(base, disp_unit, comm)
+    """Collective.  Also starts the window's passive-target service thread (rma.py)."""
+    from . import rma
+    win = Win(base, disp_unit, comm)
+    rma.start_passive_server(win)
+    return win
 
 
 def Put(origin, count, dtype, target_rank, target_disp, win: Win):
+    from . import rma
     o = _flat(origin)[:count]
+    if rma.passive_op(win, "put", target_rank, target_disp, count, dtype, o, None):
+        return
     win.ops.append(("put", target_rank, target_disp, count, dtype, o.clone() if isinstance(o, torch.Tensor) else o.copy(), None))
 
 
 def Accumulate(origin, count, dtype, target_rank, target_disp, op, win: Win):
+    from . import rma
     o = _flat(origin)[:count]
+    if rma.passive_op(win, "acc", target_rank, target_disp, count, dtype, o, op):
+        return
     win.ops.append(("acc", target_rank, target_disp, count, dtype, o.clone() if isinstance(o, torch.Tensor) else o.copy(), op))
 
 
 def Get(origin, count, dtype, target_rank, target_disp, win: Win):
+    from . import rma
+    if rma.passive_op(win, "get", target_rank, target_disp, count, dtype, _flat(origin), None):
+        return
     win.ops.append(("get", target_rank, target_disp, count, dtype, _flat(origin), None))
 
 
@@ -649,16 +663,9 @@ def Win_fence(assertion: int, win: Win) -> None:
 
 
 def Win_free(win: Win) -> None:
+    """Collective: stops the service thread, drops cached attributes."""
+    from . import attrs, rma
+    rma.stop_passive_server(win)
+    attrs.drop_object("win", win)
     win.ops = []
     win.base = None
-
-
-def Win_lock(lock_type, rank, assertion, win: Win):
-    raise _m().MPIError(ERR_RMA_SYNC, "Win_lock (passive target is provided by mpit_b200.parallel.DeviceWindow; host "
-                                      "windows synchronise with Win_fence)")
-
-
-Win_unlock = Win_lock
-
-
-__all__ = [n for n in dir() if n[0].isupper() and n not in ("Callable", "Dict", "List", "Optional", "Sequence", "Tuple")]

@@ -1,4 +1,4 @@
-"""Generalised active-target synchronisation for host windows: post / start / complete / wait.
+"""Host windows beyond fences: post / start / complete / wait epochs, and passive-target lock / unlock.
 
 /root/reference/mpifuncs.c:2330,2434,2468,2493 wraps ``Win_post``, ``Win_start``, ``Win_complete``, ``Win_wait`` (and
 ``Win_test``, ``Win_get_group``) next to the fence calls ("One-sided 14/14"); the tree calls none
@@ -10,11 +10,21 @@ in the two groups synchronise:
 
 As with fences, ``Put / Get / Accumulate`` are queued at the origin and travel at ``Win_complete``; the target applies
 them in ``Win_wait``, in the order each origin issued them.  Groups hold WORLD ranks (``Comm_group`` /
-``Group_incl``); the window remembers its communicator's group from ``Win_create``.  The device-memory counterpart
-(NVLink ``st`` / ``ld`` / ``red.add`` with flag synchronisation) is ``mpit_b200.parallel.DeviceWindow``.
+``Group_incl``); the window remembers its communicator's group from ``Win_create``.
+
+Passive target (``Win_lock`` / ``Win_unlock``, /root/reference/mpifuncs.c:2424,2485): the target takes no part in the
+epoch, so every window runs a small service thread on a communicator of its own (created in the collective
+``Win_create``).  It grants shared / exclusive locks in arrival order and applies ``Put / Accumulate / Get`` requests of
+the lock holders as they arrive -- inside a lock the operations are sent at once instead of being queued; ``Win_unlock``
+returns when the target has applied everything the origin sent.  The native message layer is thread-safe, which is all
+this needs.
+
+The device-memory counterpart (NVLink ``st`` / ``ld`` / ``red.add`` with flag synchronisation) is
+``mpit_b200.parallel.DeviceWindow``.
 """
 from __future__ import annotations
 
+import threading
 from typing import List
 
 import numpy as np
@@ -139,6 +149,151 @@ def Win_test(win) -> bool:
     if not all(m.Iprobe(o, _TAG_DESC, win.comm) for o in origins):
         return False
     Win_wait(win)
+    return True
+
+
+
+# ---- passive target: lock / unlock served by a thread at the target ------------------------------------------------
+LOCK_EXCLUSIVE, LOCK_SHARED = 234, 235
+_TAG_REQ, _TAG_PAY, _TAG_REPLY = 32220, 32221, 32222
+_K_LOCK, _K_UNLOCK, _K_PUT, _K_ACC, _K_GET, _K_QUIT = range(6)
+
+
+class _PassiveServer(threading.Thread):
+    """Serves one window's passive-target requests.  Requests are 6 x int64 {kind, disp, count, dtype, op, lock type};
+    Put / Accumulate payloads follow on their own tag; grants, Get data and unlock acknowledgements go back on the
+    reply tag.  Requests of one origin arrive in the order it sent them, so an UNLOCK is processed after every
+    operation of that epoch."""
+
+    def __init__(self, win, comm: int):
+        super().__init__(daemon=True, name="mpit-win-server")
+        self.win, self.comm = win, comm
+        self.exclusive = None            # origin holding the exclusive lock
+        self.shared = set()              # origins holding a shared lock
+        self.waiting = []                # (origin, lock type) in arrival order
+
+    def _grantable(self, kind: int) -> bool:
+        if kind == LOCK_EXCLUSIVE:
+            return self.exclusive is None and not self.shared
+        return self.exclusive is None
+
+    def _grant(self, origin: int, kind: int) -> None:
+        m = _m()
+        if kind == LOCK_EXCLUSIVE:
+            self.exclusive = origin
+        else:
+            self.shared.add(origin)
+        m.Send(None, 0, m.BYTE, origin, _TAG_REPLY, self.comm)
+
+    def _drain_waiting(self) -> None:
+        while self.waiting and self._grantable(self.waiting[0][1]):
+            origin, kind = self.waiting.pop(0)
+            self._grant(origin, kind)
+
+    def run(self) -> None:
+        m = _m()
+        ext = m.extras
+        win = self.win
+        hdr = torch.zeros(6, dtype=torch.int64)
+        st = m.Status()
+        while True:
+            m.Recv(hdr, 6, m.LONG, m.ANY_SOURCE, _TAG_REQ, self.comm, st)
+            origin = st.source
+            kind, disp, cnt, dtp, op, ltype = hdr.tolist()
+            if kind == _K_QUIT:
+                return
+            if kind == _K_LOCK:
+                if self._grantable(ltype) and not self.waiting:
+                    self._grant(origin, ltype)
+                else:
+                    self.waiting.append((origin, ltype))
+            elif kind == _K_UNLOCK:
+                if self.exclusive == origin:
+                    self.exclusive = None
+                self.shared.discard(origin)
+                m.Send(None, 0, m.BYTE, origin, _TAG_REPLY, self.comm)
+                self._drain_waiting()
+            elif kind in (_K_PUT, _K_ACC):
+                is_t = isinstance(win.base, torch.Tensor)
+                tmp = torch.empty(cnt, dtype=win.base.dtype) if is_t else np.empty(cnt, win.base.dtype)
+                m.Recv(tmp, cnt, dtp, origin, _TAG_PAY, self.comm)
+                if kind == _K_PUT:
+                    win.base[disp:disp + cnt] = tmp
+                else:
+                    ext._apply_op(win.base[disp:disp + cnt], tmp, op)
+            elif kind == _K_GET:
+                m.Send(win.base[disp:disp + cnt], cnt, dtp, origin, _TAG_REPLY, self.comm)
+
+
+def start_passive_server(win) -> None:
+    """Called from the collective ``Win_create``."""
+    m = _m()
+    if not m.Initialized():
+        win.server = None
+        return
+    win.server_comm = m.Comm_dup(win.comm)
+    win.locked = {}
+    win.server = _PassiveServer(win, win.server_comm)
+    win.server.start()
+
+
+def stop_passive_server(win) -> None:
+    m = _m()
+    srv = getattr(win, "server", None)
+    if srv is None:
+        return
+    if getattr(win, "locked", None):
+        raise _err(ERR_RMA_SYNC, "Win_free with a lock still held")
+    m.Barrier(win.comm)                                      # nobody is still talking to anybody's server
+    quit_ = torch.tensor([_K_QUIT, 0, 0, 0, 0, 0], dtype=torch.int64)
+    m.Send(quit_, 6, m.LONG, m.Comm_rank(win.server_comm), _TAG_REQ, win.server_comm)
+    srv.join()
+    m.Comm_free(win.server_comm)
+    win.server = None
+
+
+def _request(win, target: int, kind: int, disp=0, cnt=0, dtp=0, op=-1, ltype=0) -> None:
+    m = _m()
+    m.Send(torch.tensor([kind, disp, cnt, dtp, op, ltype], dtype=torch.int64), 6, m.LONG, target, _TAG_REQ,
+           win.server_comm)
+
+
+def Win_lock(lock_type: int, rank: int, assertion: int, win) -> None:
+    """Begin a passive-target access epoch at ``rank`` (``LOCK_EXCLUSIVE`` or ``LOCK_SHARED``); returns once granted."""
+    m = _m()
+    if getattr(win, "server", None) is None:
+        raise _err(ERR_RMA_SYNC, "Win_lock: the window has no service thread (created before Init?)")
+    if lock_type not in (LOCK_EXCLUSIVE, LOCK_SHARED):
+        raise _err(13, "Win_lock: lock type")
+    if rank in win.locked:
+        raise _err(ERR_RMA_SYNC, f"Win_lock: rank {rank} is already locked by this process")
+    _request(win, rank, _K_LOCK, ltype=lock_type)
+    m.Recv(None, 0, m.BYTE, rank, _TAG_REPLY, win.server_comm)
+    win.locked[rank] = lock_type
+
+
+def Win_unlock(rank: int, win) -> None:
+    """End the epoch: returns when the target has applied every operation issued since ``Win_lock``."""
+    m = _m()
+    if rank not in getattr(win, "locked", {}):
+        raise _err(ERR_RMA_SYNC, f"Win_unlock: rank {rank} is not locked")
+    _request(win, rank, _K_UNLOCK)
+    m.Recv(None, 0, m.BYTE, rank, _TAG_REPLY, win.server_comm)
+    del win.locked[rank]
+
+
+def passive_op(win, kind: str, target: int, disp: int, count: int, dtype: int, data, op) -> bool:
+    """Issue ``Put / Accumulate / Get`` at once when ``target`` is locked by this process; False = not in a passive
+    epoch (the caller queues the operation for the next fence / complete)."""
+    if target not in getattr(win, "locked", {}):
+        return False
+    m = _m()
+    if kind == "get":
+        _request(win, target, _K_GET, disp, count, dtype)
+        m.Recv(data[:count], count, dtype, target, _TAG_REPLY, win.server_comm)
+        return True
+    _request(win, target, _K_PUT if kind == "put" else _K_ACC, disp, count, dtype, -1 if op is None else op)
+    m.Send(data, count, dtype, target, _TAG_PAY, win.server_comm)
     return True
 
 

@@ -127,7 +127,7 @@ def case_x_groups_ops():
 
 
 def case_x_window():
-    """MPI_Win_create / Put / Accumulate / Get / Win_fence on host memory (active target)."""
+    """MPI_Win_create / Put / Accumulate / Get on host memory: fence epochs, then passive-target lock / unlock."""
     rank, size = mpiT.get_rank(), mpiT.get_size()
     n = 16
     base = torch.zeros(n)
@@ -146,11 +146,38 @@ def case_x_window():
     mpiT.Get(got, 4, mpiT.FLOAT, left, 2, win)
     mpiT.Win_fence(0, win)
     assert torch.equal(got, torch.full((4,), float((left - 1) % size + 1)))
-    try:
-        mpiT.Win_lock(0, 0, 0, win)
-        raise AssertionError("host windows have no passive target")
-    except mpiT.MPIError as e:
-        assert e.code == mpiT.ERR_RMA_SYNC
+    # passive target: rank 0 takes no part.  Every rank does a read-modify-write of element 0 of rank 0's window,
+    # which is only correct if the exclusive lock really excludes the others; then everybody reads under a shared lock
+    base.zero_()
+    mpiT.Barrier()
+    if rank != 0:
+        mpiT.Win_lock(mpiT.LOCK_EXCLUSIVE, 0, 0, win)
+        cur = torch.zeros(1)
+        mpiT.Get(cur, 1, mpiT.FLOAT, 0, 0, win)
+        mpiT.Put(cur + rank + 1, 1, mpiT.FLOAT, 0, 0, win)
+        mpiT.Accumulate(torch.ones(2), 2, mpiT.FLOAT, 0, 4, mpiT.SUM, win)
+        mpiT.Win_unlock(0, win)
+        try:
+            mpiT.Win_unlock(0, win)
+            raise AssertionError("unlock without lock")
+        except mpiT.MPIError as e:
+            assert e.code == mpiT.ERR_RMA_SYNC
+    mpiT.Barrier()                       # every unlock has returned, i.e. every update is applied at rank 0
+    mpiT.Win_lock(mpiT.LOCK_SHARED, 0, 0, win)
+    seen = torch.zeros(6)
+    mpiT.Get(seen, 6, mpiT.FLOAT, 0, 0, win)
+    mpiT.Win_unlock(0, win)
+    assert float(seen[0]) == sum(r + 1 for r in range(1, size)) and seen[4:6].tolist() == [size - 1.0] * 2, seen
+    # locks on two targets at once, operations to each land where they should
+    mpiT.Barrier()
+    mpiT.Win_lock(mpiT.LOCK_SHARED, left, 0, win)
+    mpiT.Win_lock(mpiT.LOCK_SHARED, right, 0, win)
+    mpiT.Accumulate(torch.tensor([100.0]), 1, mpiT.FLOAT, left, 12, mpiT.SUM, win)
+    mpiT.Accumulate(torch.tensor([1.0]), 1, mpiT.FLOAT, right, 12, mpiT.SUM, win)
+    mpiT.Win_unlock(right, win)
+    mpiT.Win_unlock(left, win)
+    mpiT.Barrier()
+    assert float(base[12]) == 101.0, base
     mpiT.Win_free(win)
 
 
