@@ -100,6 +100,30 @@ class ShardedCenter:
                                             int(do_apply), int(use_mom), int(do_lookahead), int(do_sync),
                                             int(has_d_in), cur_stream()), "mpit_eamsgd_fused_step")
 
+    # -- checkpoint of the centre: every owner writes / reads its own shard (utils/sharded_ckpt.py) ---------------
+    def save(self, path: str, barrier=None) -> None:
+        """One Torch7 flat-tensor file holding the whole centre, written in parallel by the shard owners (nothing is
+        gathered; ``t7.load`` / ``-loadmodel`` read it).  ``barrier``: e.g. ``torch.distributed.barrier`` when the host
+        message layer is not initialised.  The reference never saves the centre."""
+        from ..utils.sharded_ckpt import save_flat_sharded
+        off, size = self.parts[self.rank]
+        torch.cuda.synchronize(self.buf.local.device)
+        save_flat_sharded(path, self.buf.local[:size].contiguous(), off, self.n, barrier=barrier, rank=self.rank)
+
+    def load(self, path: str, barrier=None) -> None:
+        """Restore this rank's shard from a checkpoint written by :meth:`save` (or any flat FloatTensor of ``n``
+        elements, e.g. a parameter file the reference wrote)."""
+        from ..utils.sharded_ckpt import load_flat_sharded
+        off, size = self.parts[self.rank]
+        piece = torch.empty(size, dtype=torch.float32)
+        total = load_flat_sharded(path, piece, off, collective=False)
+        if total != self.n:
+            raise ValueError(f"{path} holds {total} elements, the centre has {self.n}")
+        self.buf.local[:size].copy_(piece)
+        torch.cuda.synchronize(self.buf.local.device)
+        if barrier is not None:
+            barrier()
+
     def gather_full(self) -> torch.Tensor:
         """Materialise the whole centre on this rank (tester role, BiCNN/bicnn.lua:580-596)."""
         out = torch.empty(self.n, dtype=torch.float32, device=self.buf.local.device)

@@ -365,6 +365,30 @@ def dumps(obj) -> bytes:
     return b.getvalue()
 
 
+def flat_float_header(n: int) -> bytes:
+    """The bytes that precede the raw data of a 1-d ``torch.FloatTensor`` of ``n`` elements in a Torch7 binary file
+    (tensor header + storage header).  Writing these and then ``n`` little-endian floats gives a file ``torch.load``
+    reads as the flat tensor -- what BiCNN saves and ``-loadmodel`` loads (bicnn.lua:259-261,590-594).  Used by the
+    sharded checkpoint writer, where every rank adds its own slice of the data."""
+    buf = io.BytesIO()
+    w = _Writer(buf)
+    tensor_id, storage_id = object(), object()
+    w.i32(TYPE_TORCH)
+    w._ref(tensor_id)
+    w.string("V 1")
+    w.string("torch.FloatTensor")
+    w.i32(1)
+    w.i64(n)
+    w.i64(1)            # stride
+    w.i64(1)            # storage offset, 1-based
+    w.i32(TYPE_TORCH)
+    w._ref(storage_id, "storage")
+    w.string("V 1")
+    w.string("torch.FloatStorage")
+    w.i64(n)
+    return buf.getvalue()
+
+
 def table_to_list(t: dict) -> list:
     """A 1..n keyed Lua table as a Python list."""
     return [t[i] for i in range(1, len(t) + 1)]

@@ -487,4 +487,38 @@ def case_c_rendezvous():
     mpiT.Barrier()
 
 
+def case_c_sharded_checkpoint():
+    """Every rank writes its shard of a flat vector into one Torch7 file through MPI-IO; the file is what torch.save of
+    the whole tensor would have produced; shards read back in a different partition."""
+    from mpit_b200 import t7
+    from mpit_b200.parallel.center import partition
+    from mpit_b200.utils.sharded_ckpt import load_flat_sharded, save_flat_sharded
+    rank, size = mpiT.get_rank(), mpiT.get_size()
+    n = 351946                                             # the CIFAR CNN's parameter count: uneven shards
+    full = torch.arange(n, dtype=torch.float32) * 0.5
+    off, cnt = partition(n, size)[rank]
+    path = _shared_tmp("centre.t7")
+    save_flat_sharded(path, full[off:off + cnt].contiguous(), off, n)
+    mpiT.Barrier()
+    if rank == 0:
+        whole = t7.load(path)
+        assert whole.dtype == torch.float32 and torch.equal(whole, full)
+        assert open(path, "rb").read() == t7.dumps(full)   # byte for byte the gathered save
+    # read back with the shards rotated by one rank
+    off2, cnt2 = partition(n, size)[(rank + 1) % size]
+    piece = torch.zeros(cnt2)
+    assert load_flat_sharded(path, piece, off2) == n
+    assert torch.equal(piece, full[off2:off2 + cnt2])
+    # a shorter vector over the same path leaves no tail behind
+    mpiT.Barrier()
+    m = 1000
+    o3, c3 = partition(m, size)[rank]
+    save_flat_sharded(path, full[o3:o3 + c3].contiguous(), o3, m)
+    mpiT.Barrier()
+    assert torch.equal(t7.load(path), full[:m])
+    mpiT.Barrier()
+    if rank == 0:
+        os.unlink(path)
+
+
 CASES = {k[5:]: v for k, v in globals().items() if k.startswith("case_")}

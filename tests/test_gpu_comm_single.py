@@ -169,3 +169,22 @@ def test_device_window_put_get_accumulate_single_gpu():
         wins[0].put(a, target_rank=1, target_disp=n - 10)
     with pytest.raises(ValueError):
         wins[0].get(out, target_rank=5)
+
+
+def test_centre_checkpoint_roundtrip(tmp_path):
+    """ShardedCenter.save: every owner writes its (device) shard into one flat Torch7 file; load restores it."""
+    from mpit_b200 import t7
+    n, S = 351946, 3
+    cs = _centers(n, S)
+    theta = torch.randn(n, device="cuda")
+    cs[0].put(theta)
+    torch.cuda.synchronize()
+    path = str(tmp_path / "centre.t7")
+    for c in cs:                                       # the aliased "ranks" take their turns; rank 0 creates the file
+        c.save(path, barrier=lambda: None)
+    assert torch.equal(t7.load(path), theta.cpu())
+    cs[0].put(torch.zeros(n, device="cuda"))
+    torch.cuda.synchronize()
+    for c in cs:
+        c.load(path)
+    assert torch.equal(_center_as_flat(cs, n), theta)
