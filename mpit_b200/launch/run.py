@@ -135,10 +135,20 @@ def main(argv=None) -> int:
                     help="lines of host:slots (BiCNN/hostfiles) or host slots=N")
     ap.add_argument("--rsh", default="ssh -o BatchMode=yes", help="remote shell used for hosts other than this one")
     ap.add_argument("--master-addr", default=None)
+    ap.add_argument("-x", dest="env", action="append", default=[], metavar="NAME[=VALUE]",
+                    help="export an environment variable to every rank (mpirun -x); NAME alone forwards its current value")
+    ap.add_argument("--oversubscribe", action="store_true", help="accepted for mpirun compatibility (always allowed)")
     ap.add_argument("cmd", nargs=argparse.REMAINDER)
     a = ap.parse_args(argv)
     hosts = parse_hostfile(open(a.hostfile).read()) if a.hostfile else None
-    return launch(a.np, a.cmd, timeout=a.timeout, module=a.module, hosts=hosts, rsh=a.rsh, master_addr=a.master_addr)
+    extra = {}
+    for item in a.env:
+        name, eq, value = item.partition("=")
+        extra[name] = value if eq else os.environ.get(name, "")
+    global _FORWARD
+    _FORWARD = _FORWARD + tuple(extra)               # also across the remote shell
+    return launch(a.np, a.cmd, env_extra=extra or None, timeout=a.timeout, module=a.module, hosts=hosts, rsh=a.rsh,
+                  master_addr=a.master_addr)
 
 
 if __name__ == "__main__":

@@ -99,3 +99,14 @@ def test_ring_over_a_hostfile_with_a_remote_shell(tmp_path):
         os.chdir(cwd)
     assert rc == 0
     assert (tmp_path / "hosts_seen").read_text().split() == ["node-b", "node-b"]
+
+
+def test_launcher_exports_environment_like_mpirun_x(tmp_path, monkeypatch):
+    script = tmp_path / "envcheck.py"
+    script.write_text("import os, sys\n"
+                      "ok = os.environ.get('MEGS') == '3' and os.environ.get('FOO_BAR') == 'baz'\n"
+                      "sys.exit(0 if ok else 7)\n")
+    monkeypatch.setenv("FOO_BAR", "baz")
+    assert run.main(["-np", "2", "-x", "MEGS=3", "-x", "FOO_BAR", "--oversubscribe", str(script)]) == 0
+    monkeypatch.delenv("FOO_BAR")
+    assert run.main(["-np", "1", "-x", "MEGS=3", str(script)]) == 7
