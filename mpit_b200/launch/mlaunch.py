@@ -38,6 +38,9 @@ def main(argv=None) -> int:
     ap.add_argument("--save", default="results/mlaunch")
     ap.add_argument("--data", default=None, help="directory with the cifar-10-batches-t7 files")
     ap.add_argument("--resume", default=None, help="checkpoint (model-epoch-N.net or flat tensor) to start from")
+    ap.add_argument("--center-ckpt", default=None,
+                    help="GPU path: file for the centre variable; restored from it when it exists, written to it at the "
+                         "end by the shard owners in parallel (one flat Torch7 tensor, readable with --resume)")
     a = ap.parse_args(argv)
     lr = a.lr if a.lr is not None else (1e-4 if a.optim == "downpour" else 1e-2)   # mlaunch.lua:50-60
     if a.device == "cuda":
@@ -61,11 +64,21 @@ def _gpu(a, lr) -> int:
                      save=a.save, seed=1 + rank, model=a.model)
     print(f"[client] rank {rank} use gpu {local}")
     tr = CifarTrainer(opts, dev, heap, theta0=load_checkpoint(a.resume) if a.resume else None)
+    sync = dist.barrier if world > 1 else None
+    if a.center_ckpt and tr.center is not None and os.path.exists(a.center_ckpt):
+        tr.center.load(a.center_ckpt, barrier=sync)        # the reference has no way to restore the centre
+        if rank == 0:
+            print("===> centre restored from", a.center_ckpt)
     ch = 1 if a.model == "mnist" else 3
     train, test, real = cifar_data(a.trsize, a.tesize, seed=10 + rank, channels=ch, root=a.data)
     if rank == 0:
         print("===> data:", "cifar-10-batches-t7" if real else "synthetic")
     hist = train_epochs(tr, train, test, rank=rank, quiet=rank != 0)
+    if a.center_ckpt and tr.center is not None:
+        torch.cuda.synchronize()
+        if sync:
+            sync()                                         # every worker's last push has landed
+        tr.center.save(a.center_ckpt, barrier=sync)
     print(f"[rank {rank}] train loss {hist['train_loss'][-1]:.4f} test acc {hist['test_acc'][-1]:.4f} "
           f"{hist['samples_per_s']:.0f} samples/s")
     heap.check_timeout()
