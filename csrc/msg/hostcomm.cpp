@@ -633,7 +633,7 @@ void free_req_locked(int id) {
   g.reqs.erase(it);
 }
 
-int send_wire_blocking(const void* buf, size_t n, int dst_world, int tag, int wire_comm);
+int send_wire_blocking(const void* buf, size_t n, int dst_world, int tag, int wire_comm, bool may_rendezvous = false);
 int recv_wire_blocking(void* buf, size_t cap, int src_world, int tag, int wire_comm, size_t* got = nullptr);
 
 // Who can read whose memory?  Every rank tells every other {pid, boot id hash, uid, address and value of a probe
@@ -698,9 +698,11 @@ void exchange_cma_caps() {
   }
 }
 
-int send_wire_blocking(const void* buf, size_t n, int dst_world, int tag, int wire_comm) {
+// may_rendezvous: only where the receiver is certain to post its receive without waiting for anything from this
+// rank (the tree collectives below); a general blocking send must stay eager.
+int send_wire_blocking(const void* buf, size_t n, int dst_world, int tag, int wire_comm, bool may_rendezvous) {
   Req* r;
-  int rc = isend_wire(buf, n, dst_world, tag, wire_comm, &r);
+  int rc = isend_wire(buf, n, dst_world, tag, wire_comm, &r, may_rendezvous);
   if (rc) return rc;
   rc = wait_req(r);
   std::lock_guard<std::mutex> lk(g.mu);
@@ -782,7 +784,7 @@ int coll_bcast(const Group& G, void* buf, size_t nbytes, int root, int tag) {
   while (mask > 0) {
     if (rel + mask < n) {
       int dst = (rel + mask + root) % n;
-      int rc = send_wire_blocking(buf, nbytes, G.ranks[dst], tag, G.wire);
+      int rc = send_wire_blocking(buf, nbytes, G.ranks[dst], tag, G.wire, /*may_rendezvous=*/true);
       if (rc) return rc;
     }
     mask >>= 1;
@@ -801,7 +803,7 @@ int coll_reduce(const Group& G, void* acc, size_t count, int dt, int op, int roo
   while (mask < n) {
     if (rel & mask) {
       int dst = (rel - mask + root) % n;
-      return send_wire_blocking(acc, nbytes, G.ranks[dst], tag, G.wire);
+      return send_wire_blocking(acc, nbytes, G.ranks[dst], tag, G.wire, /*may_rendezvous=*/true);
     }
     int partner = rel + mask;
     if (partner < n) {
