@@ -818,9 +818,48 @@ int coll_reduce(const Group& G, void* acc, size_t count, int dt, int op, int roo
   return MPIT_SUCCESS;
 }
 
+// Large vectors on three or more ranks: ring reduce-scatter followed by a ring all-gather.  Every rank moves
+// 2 (n-1)/n of the vector and reduces 1/n of it per step, all at the same time, where the tree has the root receive,
+// reduce and send the whole vector log2(n) times.  Sends are non-blocking (rendezvous-capable); a step is
+// "post the send to the right, receive from the left, combine, wait for the send".
+int coll_allreduce_ring(const Group& G, void* rbuf, size_t count, int dt, int op, int tag) {
+  const int n = (int)G.ranks.size();
+  const size_t es = dtype_size(dt);
+  const int right = G.ranks[(G.me + 1) % n], left = G.ranks[(G.me - 1 + n) % n];
+  auto lo = [&](int c) { return (size_t)(((unsigned __int128)count * (unsigned)c) / (unsigned)n); };
+  char* base = static_cast<char*>(rbuf);
+  std::vector<char> tmp((lo(1) - lo(0) + 1 + count / n) * es);
+  for (int phase = 0; phase < 2; ++phase) {
+    for (int s = 0; s < n - 1; ++s) {
+      // reduce-scatter: after step s, chunk (me - s - 1) holds s + 2 contributions; all-gather: finished chunks travel on
+      const int send_c = ((G.me - s + (phase ? 1 : 0)) % n + n) % n;
+      const int recv_c = ((G.me - s - 1 + (phase ? 1 : 0)) % n + n) % n;
+      const size_t sn = lo(send_c + 1) - lo(send_c), rn = lo(recv_c + 1) - lo(recv_c);
+      Req* sr;
+      int rc = isend_wire(base + lo(send_c) * es, sn * es, right, tag + phase, G.wire, &sr, /*may_rendezvous=*/true);
+      if (rc) return rc;
+      void* dst = phase ? (void*)(base + lo(recv_c) * es) : (void*)tmp.data();
+      rc = recv_wire_blocking(dst, rn * es, left, tag + phase, G.wire);
+      if (!rc && !phase) rc = reduce_into(base + lo(recv_c) * es, tmp.data(), rn, dt, op);
+      int rc2 = wait_req(sr);
+      {
+        std::lock_guard<std::mutex> lk(g.mu);
+        free_req_locked(sr->id);
+      }
+      if (rc || rc2) return rc ? rc : rc2;
+    }
+  }
+  return MPIT_SUCCESS;
+}
+
 int coll_allreduce(const Group& G, const void* sbuf, void* rbuf, size_t count, int dt, int op, int tag) {
   size_t nbytes = count * dtype_size(dt);
   if (sbuf != rbuf && sbuf) memcpy(rbuf, sbuf, nbytes);
+  static const size_t ring_min = [] { const char* e = getenv("MPIT_RING_MIN"); return e ? (size_t)atoll(e) : (size_t)(1u << 20); }();
+  if (G.ranks.size() >= 3 && nbytes >= ring_min && count >= G.ranks.size()) {
+    if ((op == MPIT_BAND || op == MPIT_BOR) && (dt == MPIT_FLOAT || dt == MPIT_DOUBLE)) return MPIT_ERR_OP;
+    return coll_allreduce_ring(G, rbuf, count, dt, op, tag);
+  }
   int rc = coll_reduce(G, rbuf, count, dt, op, 0, tag);
   if (rc) return rc;
   return coll_bcast(G, rbuf, nbytes, 0, tag + 1);

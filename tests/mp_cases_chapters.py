@@ -521,4 +521,50 @@ def case_c_sharded_checkpoint():
         os.unlink(path)
 
 
+def case_c_ring_allreduce():
+    """Large vectors on >= 3 ranks take the ring reduce-scatter / all-gather path: uneven chunking, several types and
+    operations, in place, and the non-blocking form; a small vector still takes the tree."""
+    rank, size = mpiT.get_rank(), mpiT.get_size()
+    n = 300007                                             # not a multiple of the rank count; 1.2 MB of floats
+    i = torch.arange(n)
+    a = ((i % 97) * (rank + 1)).float()
+    out = torch.zeros(n)
+    mpiT.Allreduce(a, out, n, mpiT.FLOAT, mpiT.SUM)
+    assert torch.equal(out, ((i % 97) * (size * (size + 1) // 2)).float())
+    l = (i + rank * 7).to(torch.int64)
+    lo, hi = torch.zeros(n, dtype=torch.int64), torch.zeros(n, dtype=torch.int64)
+    mpiT.Allreduce(l, hi, n, mpiT.LONG, mpiT.MAX)
+    mpiT.Allreduce(l, lo, n, mpiT.LONG, mpiT.MIN)
+    assert torch.equal(hi, i + (size - 1) * 7) and torch.equal(lo, i)
+    d = torch.full((n,), 1.0 + rank, dtype=torch.float64)
+    mpiT.Allreduce(d, d, n, mpiT.DOUBLE, mpiT.PROD)         # in place
+    want = 1.0
+    for r in range(size):
+        want *= 1.0 + r
+    assert float(d[0]) == want and float(d[-1]) == want and float(d.min()) == float(d.max())
+    bits = torch.full((n,), 1 << rank, dtype=torch.int32)
+    orr = torch.zeros(n, dtype=torch.int32)
+    mpiT.Allreduce(bits, orr, n, mpiT.INT, mpiT.BOR)
+    assert int(orr[0]) == (1 << size) - 1 and int(orr[n // 2]) == (1 << size) - 1
+    req = mpiT.Request(1)
+    out.zero_()
+    mpiT.Iallreduce(a, out, n, mpiT.FLOAT, mpiT.SUM, mpiT.COMM_WORLD, req)
+    mpiT.Wait(req)
+    assert torch.equal(out, ((i % 97) * (size * (size + 1) // 2)).float())
+    # sub-communicator of three out of the ranks, and a small vector (tree path) for contrast
+    sub = mpiT.Comm_split(mpiT.COMM_WORLD, 0 if rank < 3 else 1, rank)
+    if rank < 3:
+        s3 = torch.zeros(n)
+        mpiT.Allreduce(a, s3, n, mpiT.FLOAT, mpiT.SUM, sub)
+        assert torch.equal(s3, ((i % 97) * 6).float())
+    tiny = torch.zeros(5)
+    mpiT.Allreduce(torch.full((5,), float(rank)), tiny, 5, mpiT.FLOAT, mpiT.SUM)
+    assert tiny.tolist() == [size * (size - 1) / 2.0] * 5
+    try:
+        mpiT.Allreduce(a, out, n, mpiT.FLOAT, mpiT.BOR)
+        raise AssertionError("bitwise or of floats")
+    except mpiT.MPIError as e:
+        assert e.code == mpiT.ERR_OP
+
+
 CASES = {k[5:]: v for k, v in globals().items() if k.startswith("case_")}
