@@ -991,6 +991,19 @@ int mpit_msg_init(int rank, int size, const char* master_addr, int master_port, 
   }
   g.inited = true;
   g.progress = std::thread(progress_loop);
+  // a process that exits without Finalize (an uncaught exception in a rank) must keep its exit status: stop the
+  // progress thread before the static destructors find it still joinable and call std::terminate
+  static bool at_exit_registered = false;
+  if (!at_exit_registered) {
+    at_exit_registered = true;
+    std::atexit([] {
+      if (g.progress.joinable()) {
+        g.stop = true;
+        wake();
+        g.progress.join();
+      }
+    });
+  }
   lk.unlock();                // the capability exchange uses the message layer itself
   exchange_cma_caps();
   return MPIT_SUCCESS;
@@ -1478,7 +1491,7 @@ int mpit_msg_gather(const void* sbuf, long long scount, int dtype, void* rbuf, i
     }
     return MPIT_SUCCESS;
   }
-  return send_wire_blocking(sbuf, nb, G.ranks[root], 50, G.wire);
+  return send_wire_blocking(sbuf, nb, G.ranks[root], 50, G.wire, /*may_rendezvous=*/true);   // the root only receives
 }
 
 int mpit_msg_allgather(const void* sbuf, long long scount, int dtype, void* rbuf, int comm) {
@@ -1498,7 +1511,7 @@ int mpit_msg_scatter(const void* sbuf, long long count, int dtype, void* rbuf, i
     for (int i = 0; i < n; ++i) {
       const char* src = static_cast<const char*>(sbuf) + (size_t)i * nb;
       if (i == root) memcpy(rbuf, src, nb);
-      else { int rc = send_wire_blocking(src, nb, G.ranks[i], 60, G.wire); if (rc) return rc; }
+      else { int rc = send_wire_blocking(src, nb, G.ranks[i], 60, G.wire, /*may_rendezvous=*/true); if (rc) return rc; }
     }
     return MPIT_SUCCESS;
   }
@@ -1520,7 +1533,7 @@ int mpit_msg_alltoall(const void* sbuf, long long count, int dtype, void* rbuf, 
   for (int i = 0; i < n; ++i) {
     if (i == G.me) continue;
     Req* r;
-    isend_wire(static_cast<const char*>(sbuf) + (size_t)i * nb, nb, G.ranks[i], 70, G.wire, &r);
+    isend_wire(static_cast<const char*>(sbuf) + (size_t)i * nb, nb, G.ranks[i], 70, G.wire, &r, /*may_rendezvous=*/true);
     ss.push_back(r);
   }
   int rc = MPIT_SUCCESS;
@@ -1562,7 +1575,7 @@ int mpit_msg_scan(const void* sbuf, void* rbuf, long long count, int dtype, int 
     rc = reduce_into(rbuf, mine.data(), (size_t)count, dtype, op);
     if (rc) return rc;
   }
-  if (G.me + 1 < (int)G.ranks.size()) return send_wire_blocking(rbuf, nb, G.ranks[G.me + 1], 80, G.wire);
+  if (G.me + 1 < (int)G.ranks.size()) return send_wire_blocking(rbuf, nb, G.ranks[G.me + 1], 80, G.wire, /*may_rendezvous=*/true);
   return MPIT_SUCCESS;
 }
 

@@ -567,4 +567,33 @@ def case_c_ring_allreduce():
         assert e.code == mpiT.ERR_OP
 
 
+def case_c_big_collectives():
+    """Alltoall / Gather / Scatter / Scan / Allgather with 4 MiB blocks: the sizes at which their sends go through the
+    single-copy rendezvous (and through the socket with MPIT_CMA=0)."""
+    r, n = mpiT.get_rank(), mpiT.get_size()
+    c = 1 << 20   # 4 MB per rank pair
+    idx = torch.arange(n * c)
+    s = (idx % 1000 + (idx // c) * 10000 + r * 100000).float()      # encodes (sender, destination block, position)
+    out = torch.zeros(n * c)
+    mpiT.Alltoall(s, c, mpiT.FLOAT, out)
+    for p in range(n):
+        blk = out[p * c:(p + 1) * c]
+        assert torch.equal(blk, (torch.arange(r * c, (r + 1) * c) % 1000 + r * 10000 + p * 100000).float()), (r, p)
+    g = torch.zeros(n * c) if r == 1 else None
+    mpiT.Gather(s[:c], c, mpiT.FLOAT, g, 1)
+    if r == 1:
+        for p in range(n):
+            assert torch.equal(g[p * c:(p + 1) * c], (torch.arange(c) % 1000 + p * 100000).float())
+    piece = torch.zeros(c)
+    mpiT.Scatter(s if r == 2 else None, c, mpiT.FLOAT, piece, 2)
+    assert torch.equal(piece, (torch.arange(r * c, (r + 1) * c) % 1000 + r * 10000 + 200000).float())
+    sc = torch.zeros(c)
+    mpiT.Scan(torch.full((c,), 1.0 + r), sc, c, mpiT.FLOAT, mpiT.SUM)
+    assert float(sc[9]) == sum(1.0 + q for q in range(r + 1)) and float(sc.min()) == float(sc.max())
+    ag = torch.zeros(n * c)
+    mpiT.Allgather(s[:c], c, mpiT.FLOAT, ag)
+    for p in range(n):
+        assert torch.equal(ag[p * c:(p + 1) * c], (torch.arange(c) % 1000 + p * 100000).float())
+
+
 CASES = {k[5:]: v for k, v in globals().items() if k.startswith("case_")}

@@ -87,7 +87,8 @@ def test_wider_mpi_surface(case, nproc):
 @pytest.mark.parametrize("case,nproc", [("c_derived_messages", 4), ("c_topology", 6), ("c_file_io", 4),
                                         ("c_pscw_and_attrs", 4), ("c_intercomm", 4),
                                         ("c_maxloc_and_wide_types", 4), ("c_sharded_checkpoint", 3),
-                                        ("c_ring_allreduce", 5), ("c_ring_allreduce", 3)])
+                                        ("c_ring_allreduce", 5), ("c_ring_allreduce", 3),
+                                        ("c_big_collectives", 4)])
 def test_mpi_chapters_multi_process(case, nproc):
     """Derived datatypes on the wire, topologies, MPI-IO with views and shared pointers, post/start/complete/wait,
     attributes across Comm_dup, inter-communicators / ports / Comm_join (msg/datatypes.py, topo.py, fileio.py, rma.py,
