@@ -996,7 +996,10 @@ int mpit_msg_init(int rank, int size, const char* master_addr, int master_port, 
   static bool at_exit_registered = false;
   if (!at_exit_registered) {
     at_exit_registered = true;
+    static pid_t owner;
+    owner = getpid();
     std::atexit([] {
+      if (getpid() != owner) return;        // a forked child has no progress thread to join
       if (g.progress.joinable()) {
         g.stop = true;
         wake();
