@@ -594,6 +594,16 @@ def case_c_big_collectives():
     mpiT.Allgather(s[:c], c, mpiT.FLOAT, ag)
     for p in range(n):
         assert torch.equal(ag[p * c:(p + 1) * c], (torch.arange(c) % 1000 + p * 100000).float())
+    # many large non-blocking sends and receives in flight at once (Alltoallv posts them all, then waits)
+    counts = [c // 2 + 1000 * q for q in range(n)]              # what I send to q; I receive c // 2 + 1000 * r from each
+    sd = [sum(counts[:q]) for q in range(n)]
+    mine = c // 2 + 1000 * r
+    sv = torch.cat([torch.full((counts[q],), float(r * 10 + q)) for q in range(n)])
+    rv = torch.zeros(n * mine)
+    mpiT.Alltoallv(sv, counts, sd, mpiT.FLOAT, rv, [mine] * n, [q * mine for q in range(n)])
+    for q in range(n):
+        seg = rv[q * mine:(q + 1) * mine]
+        assert float(seg.min()) == float(seg.max()) == q * 10 + r, (r, q)
 
 
 CASES = {k[5:]: v for k, v in globals().items() if k.startswith("case_")}
