@@ -828,7 +828,7 @@ int coll_allreduce_ring(const Group& G, void* rbuf, size_t count, int dt, int op
   const int right = G.ranks[(G.me + 1) % n], left = G.ranks[(G.me - 1 + n) % n];
   auto lo = [&](int c) { return (size_t)(((unsigned __int128)count * (unsigned)c) / (unsigned)n); };
   char* base = static_cast<char*>(rbuf);
-  std::vector<char> tmp((lo(1) - lo(0) + 1 + count / n) * es);
+  std::vector<char> tmp((count / (size_t)n + 1) * es);     // the largest chunk
   for (int phase = 0; phase < 2; ++phase) {
     for (int s = 0; s < n - 1; ++s) {
       // reduce-scatter: after step s, chunk (me - s - 1) holds s + 2 contributions; all-gather: finished chunks travel on
