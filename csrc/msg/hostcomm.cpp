@@ -739,7 +739,7 @@ void reduce_bits(T* acc, const T* in, size_t n, int op) {
   else if (op == MPIT_BOR) for (size_t i = 0; i < n; ++i) acc[i] = acc[i] | in[i];
   else reduce_typed(acc, in, n, op);
 }
-int reduce_into(void* acc, const void* in, size_t n, int dt, int op) {
+int reduce_span(void* acc, const void* in, size_t n, int dt, int op) {
   if ((op == MPIT_BAND || op == MPIT_BOR) && (dt == MPIT_FLOAT || dt == MPIT_DOUBLE)) return MPIT_ERR_OP;
   switch (dt) {
     case MPIT_BYTE: case MPIT_UNSIGNED_CHAR: reduce_bits((uint8_t*)acc, (const uint8_t*)in, n, op); break;
@@ -752,6 +752,28 @@ int reduce_into(void* acc, const void* in, size_t n, int dt, int op) {
     case MPIT_DOUBLE: reduce_typed((double*)acc, (const double*)in, n, op); break;
     default: return MPIT_ERR_TYPE;
   }
+  return MPIT_SUCCESS;
+}
+
+// acc = acc op in, elementwise.  Vectors of 8 MiB and more are cut over the same number of threads a large
+// rendezvous copy uses (the cores this rank can claim); elementwise, so the result does not depend on the split.
+int reduce_into(void* acc, const void* in, size_t n, int dt, int op) {
+  const size_t es = dtype_size(dt);
+  const int nt = g_cma_threads;
+  if (nt <= 1 || es == 0 || n * es < (8u << 20)) return reduce_span(acc, in, n, dt, op);
+  const size_t per = (n + (size_t)nt - 1) / (size_t)nt;
+  std::vector<std::thread> helpers;
+  std::vector<int> rcs((size_t)nt, MPIT_SUCCESS);
+  for (int t = 1; t < nt; ++t) {
+    const size_t lo = std::min(n, per * (size_t)t), hi = std::min(n, lo + per);
+    if (lo >= hi) break;
+    helpers.emplace_back([=, &rcs] {
+      rcs[(size_t)t] = reduce_span((char*)acc + lo * es, (const char*)in + lo * es, hi - lo, dt, op);
+    });
+  }
+  rcs[0] = reduce_span(acc, in, std::min(n, per), dt, op);
+  for (auto& h : helpers) h.join();
+  for (int rc : rcs) if (rc) return rc;
   return MPIT_SUCCESS;
 }
 
