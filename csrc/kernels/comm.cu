@@ -115,6 +115,7 @@ struct ExchArgs {
   const int* wmap;
   int nmaps;
   long long n;
+  long long map_base;  // pull: elements below map_base have no operand copy; the tables cover [map_base, n)
   float alpha, clr, l2wd, mom_next, scale, l1, l2, clip;
   int do_apply, use_mom, do_lookahead, do_sync, has_d_in, zero_src;
 };
@@ -136,7 +137,9 @@ __global__ void __launch_bounds__(256) exchange_kernel(ExchArgs a) {
       store4(a.src, i0, cnt, c);
       if (a.wpk) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) if (k < cnt) pack_store(a.wpk, a.wmap, a.nmaps, a.n, i0 + k, c[k]);
+        for (int k = 0; k < 4; ++k)
+          if (k < cnt && i0 + k >= a.map_base)
+            pack_store(a.wpk, a.wmap, a.nmaps, a.n - a.map_base, i0 + k - a.map_base, c[k]);
       }
     } else if (MODE == EX_PUT) {
       float r[4];
@@ -220,110 +223,13 @@ __global__ void __launch_bounds__(256) exchange_kernel(ExchArgs a) {
 }
 
 // ---------------------------------------------------------------------------------------
-// All-reduce family.  Buffers are symmetric: tab.peer[r] is rank r's input.
+// Broadcast / barrier over symmetric buffers.  (The all-reduce family lives in allreduce.cu.)
 // ---------------------------------------------------------------------------------------
 struct ArArgs {
-  PeerTable in;       // symmetric input buffers
-  PeerTable out;      // symmetric output buffers (two-shot gathers into every rank's out)
+  PeerTable out;      // symmetric buffers
   SignalTable sig;
-  float* local_out;   // one-shot: private output
-  float* x;           // elastic variant: local params to pull toward the mean
-  long long n;        // elements (multiple of 4 for the vector path; tail handled scalar)
-  float scale;        // 1 for SUM, 1/nranks for AVG
-  float alpha;        // elastic moving rate
+  long long n;
 };
-
-// One-shot: every rank reads all inputs and keeps the whole sum (latency path, small messages).
-__global__ void __launch_bounds__(512) allreduce_oneshot_kernel(ArArgs a) {
-  block_barrier_sys(a.sig, blockIdx.x);  // inputs of every rank are in place
-  long long n4 = a.n >> 2;
-  long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
-    float4 acc;
-    if (a.in.mc) {
-      acc = multimem_ld_reduce_add4(a.in.mc + 4 * i);   // reduction happens inside the NVSwitch
-    } else {
-      float4 r[MPIT_MAX_RANKS];
-#pragma unroll
-      for (int p = 0; p < MPIT_MAX_RANKS; ++p)
-        if (p < a.in.nranks) r[p] = ld_sys4(a.in.peer[p] + 4 * i);   // all loads in flight first
-      acc = r[0];
-#pragma unroll
-      for (int p = 1; p < MPIT_MAX_RANKS; ++p)
-        if (p < a.in.nranks) { acc.x += r[p].x; acc.y += r[p].y; acc.z += r[p].z; acc.w += r[p].w; }
-    }
-    if (a.scale != 1.f) { acc.x *= a.scale; acc.y *= a.scale; acc.z *= a.scale; acc.w *= a.scale; }
-    if (a.x) {
-      // fused elastic pull toward the average: x -= alpha * (x - mean)
-      float4 x = ld4(a.x + 4 * i);
-      x.x = sub_rn(x.x, mul_rn(a.alpha, sub_rn(x.x, acc.x)));
-      x.y = sub_rn(x.y, mul_rn(a.alpha, sub_rn(x.y, acc.y)));
-      x.z = sub_rn(x.z, mul_rn(a.alpha, sub_rn(x.z, acc.z)));
-      x.w = sub_rn(x.w, mul_rn(a.alpha, sub_rn(x.w, acc.w)));
-      st4(a.x + 4 * i, x);
-    }
-    if (a.local_out) st4(a.local_out + 4 * i, acc);
-  }
-  if (blockIdx.x == 0) {
-    for (long long i = (n4 << 2) + threadIdx.x; i < a.n; i += blockDim.x) {
-      float acc = 0.f;
-      for (int p = 0; p < a.in.nranks; ++p) acc += ld_sys(a.in.peer[p] + i);
-      acc *= a.scale;
-      if (a.x) a.x[i] = sub_rn(a.x[i], mul_rn(a.alpha, sub_rn(a.x[i], acc)));
-      if (a.local_out) a.local_out[i] = acc;
-    }
-  }
-  block_barrier_sys(a.sig, blockIdx.x);  // nobody overwrites an input that is still being read
-}
-
-// Two-shot: rank r reduces slice r (reduce-scatter) and writes it into every rank's output
-// (all-gather) -- each byte crosses NVLink once in, once out (bandwidth path, large messages).
-__global__ void __launch_bounds__(512) allreduce_twoshot_kernel(ArArgs a) {
-  block_barrier_sys(a.sig, blockIdx.x);
-  int R = a.in.nranks, me = a.in.rank;
-  long long n4 = a.n >> 2;
-  long long per = (n4 + R - 1) / R;
-  long long lo = per * me, hi = lo + per < n4 ? lo + per : n4;
-  long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
-    float4 acc;
-    if (a.in.mc) {
-      acc = multimem_ld_reduce_add4(a.in.mc + 4 * i);
-    } else {
-      float4 r[MPIT_MAX_RANKS];
-#pragma unroll
-      for (int p = 0; p < MPIT_MAX_RANKS; ++p)
-        if (p < R) r[p] = ld_sys4(a.in.peer[(me + p) % R] + 4 * i);   // stagger peers across ranks
-      acc = r[0];
-#pragma unroll
-      for (int p = 1; p < MPIT_MAX_RANKS; ++p)
-        if (p < R) { acc.x += r[p].x; acc.y += r[p].y; acc.z += r[p].z; acc.w += r[p].w; }
-    }
-    if (a.scale != 1.f) { acc.x *= a.scale; acc.y *= a.scale; acc.z *= a.scale; acc.w *= a.scale; }
-    if (a.out.mc) {
-      multimem_st4(a.out.mc + 4 * i, acc);   // one store, the switch replicates it
-    } else {
-#pragma unroll
-      for (int p = 0; p < MPIT_MAX_RANKS; ++p)
-        if (p < R) st_sys4(a.out.peer[(me + p) % R] + 4 * i, acc);
-    }
-  }
-  if (me == R - 1 && blockIdx.x == 0) {
-    for (long long i = (n4 << 2) + threadIdx.x; i < a.n; i += blockDim.x) {
-      float acc = 0.f;
-      for (int p = 0; p < R; ++p) acc += ld_sys(a.in.peer[p] + i);
-      acc *= a.scale;
-      for (int p = 0; p < R; ++p) st_sys(a.out.peer[p] + i, acc);
-    }
-  }
-  block_barrier_sys(a.sig, blockIdx.x);  // every slice has landed everywhere
-  if (a.x) {
-    // elastic pull toward the mean, reading the gathered result locally
-    const float* mean = a.out.peer[me];
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += stride)
-      a.x[i] = sub_rn(a.x[i], mul_rn(a.alpha, sub_rn(a.x[i], mean[i])));
-  }
-}
 
 // Broadcast (MPI_Bcast, wrapped at /root/reference/mpifuncs.c:145): the root pushes.
 __global__ void __launch_bounds__(512) bcast_kernel(ArArgs a, int root) {
@@ -456,13 +362,13 @@ int mpit_signal_words(void) { return MPIT_SIGNAL_WORDS; }
 int mpit_max_ranks(void) { return MPIT_MAX_RANKS; }
 
 int mpit_param_pull(const unsigned long long* shard_ptrs, int nranks, int rank, float* dst, long long n,
-                    float* wpk, const int* wmap, int nmaps, void* stream) {
+                    float* wpk, const int* wmap, int nmaps, long long map_base, void* stream) {
   if (n <= 0) return 0;
-  if (nranks < 1 || nranks > MPIT_MAX_RANKS) return MPIT_E_ARG;
+  if (nranks < 1 || nranks > MPIT_MAX_RANKS || map_base < 0 || map_base > n) return MPIT_E_ARG;
   ExchArgs a{};
   a.tab = make_table(shard_ptrs, 0, nranks, rank);
   a.walk = QuadWalk::make(n, nranks, rank);
-  a.src = dst; a.wpk = wpk; a.wmap = wmap; a.nmaps = nmaps; a.n = n;
+  a.src = dst; a.wpk = wpk; a.wmap = wmap; a.nmaps = nmaps; a.n = n; a.map_base = map_base;
   exchange_kernel<EX_PULL><<<exch_grid(a.walk), 256, 0, (cudaStream_t)stream>>>(a);
   MPIT_LAUNCH_CHECK();
   return 0;
@@ -532,29 +438,6 @@ static int ar_grid(long long n, int max_blocks) {
   if (need < 1) need = 1;
   if (need > max_blocks) need = max_blocks;
   return (int)need;
-}
-
-int mpit_allreduce(const unsigned long long* in_ptrs, unsigned long long in_mc,
-                   const unsigned long long* out_ptrs, unsigned long long out_mc,
-                   const unsigned long long* sig_ptrs, int nranks, int rank, float* local_out, float* x_elastic,
-                   long long n, float scale, float alpha, int algo, int max_blocks, void* stream) {
-  if (n <= 0) return 0;
-  if (nranks < 1 || nranks > MPIT_MAX_RANKS) return MPIT_E_ARG;
-  if (max_blocks <= 0 || max_blocks > MPIT_BARRIER_BLOCKS) max_blocks = MPIT_BARRIER_BLOCKS;
-  ArArgs a{};
-  a.in = make_table(in_ptrs, in_mc, nranks, rank);
-  a.sig = make_sig(sig_ptrs, nranks, rank);
-  a.local_out = local_out; a.x = x_elastic; a.n = n; a.scale = scale; a.alpha = alpha;
-  int grid = ar_grid(n, max_blocks);
-  if (algo == 0) {
-    allreduce_oneshot_kernel<<<grid, 512, 0, (cudaStream_t)stream>>>(a);
-  } else {
-    if (!out_ptrs) return MPIT_E_ARG;
-    a.out = make_table(out_ptrs, out_mc, nranks, rank);
-    allreduce_twoshot_kernel<<<grid, 512, 0, (cudaStream_t)stream>>>(a);
-  }
-  MPIT_LAUNCH_CHECK();
-  return 0;
 }
 
 int mpit_bcast(const unsigned long long* buf_ptrs, unsigned long long buf_mc, const unsigned long long* sig_ptrs,

@@ -31,6 +31,11 @@ struct SignalTable {
 };
 #define MPIT_SIGNAL_WORDS (MPIT_BARRIER_BLOCKS * MPIT_MAX_RANKS + 64)
 #define MPIT_SIGNAL_ERR_WORD (MPIT_BARRIER_BLOCKS * MPIT_MAX_RANKS)
+// Epoch-based synchronisation of the all-reduce family (allreduce.cu), in the spare words after the error word:
+#define MPIT_SIG_START (MPIT_SIGNAL_ERR_WORD + 8)    // [MPIT_MAX_RANKS] "rank r has started launch e"
+#define MPIT_SIG_DONE (MPIT_SIGNAL_ERR_WORD + 16)    // [MPIT_MAX_RANKS] "rank r has finished launch e"
+#define MPIT_SIG_EPOCH (MPIT_SIGNAL_ERR_WORD + 24)   // launches completed on this pad (local only)
+#define MPIT_SIG_TICKET (MPIT_SIGNAL_ERR_WORD + 25)  // CTAs of the running launch that have finished (local only)
 
 // Reference partition (asyncsgd/pclient.lua:118-128): S contiguous shards of floor(N/S)
 // elements, the last one extended to N.  0-based here (the reference's wire format is 1-based).

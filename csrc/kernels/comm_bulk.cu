@@ -194,11 +194,8 @@ static BulkArgs make_bulk(const unsigned long long* ptrs, int nranks, int rank, 
 template <int MODE>
 static int launch_bulk(const BulkArgs& a, cudaStream_t st) {
   constexpr int smem = (MODE == BULK_ELASTIC ? 3 : 2) * kBulkStages * kBulkBytes + 64;
-  static bool done = false;
-  if (!done) {
-    MPIT_CUDA_TRY(cudaFuncSetAttribute(bulk_exchange_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    done = true;
-  }
+  static unsigned long long done = 0;   // bit per device
+  MPIT_CUDA_TRY(set_smem_limit_per_device(bulk_exchange_kernel<MODE>, smem, done));
   long long total = a.cps * a.part.S;
   int grid = (int)(total < MPIT_NUM_SMS ? total : MPIT_NUM_SMS);
   bulk_exchange_kernel<MODE><<<grid, 256, smem, st>>>(a);

@@ -19,6 +19,21 @@
 
 namespace mpit {
 
+// cudaFuncSetAttribute is per device, not per process: a process that drives several GPUs has to raise the
+// dynamic shared-memory limit on each of them.  One 64-bit mask per kernel instantiation remembers the devices
+// already done (the call itself is idempotent, so a lost race costs one redundant call).
+template <typename K>
+static inline cudaError_t set_smem_limit_per_device(K kernel, int bytes, unsigned long long& done_mask) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (__atomic_load_n(&done_mask, __ATOMIC_ACQUIRE) & bit) return cudaSuccess;
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess) __atomic_fetch_or(&done_mask, bit, __ATOMIC_RELEASE);
+  return e;
+}
+
 // Grid sizing for streaming elementwise kernels: enough CTAs for >= 2 waves on
 // 148 SMs but never more than the work needs.
 static inline int ew_grid(long long n_items, int threads, int items_per_thread = 4, int max_ctas_per_sm = 8) {

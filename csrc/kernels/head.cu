@@ -226,11 +226,8 @@ extern "C" int mpit_classifier_head(const float* x, const float* w, const float*
   if (grid > kHeadMaxCtas) grid = kHeadMaxCtas;
   cudaStream_t st = (cudaStream_t)stream;
   auto go = [&](auto kern) -> int {
-    static bool attr_done = false;    // one per kernel instantiation (generic lambda)
-    if (!attr_done) {
-      MPIT_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-      attr_done = true;
-    }
+    static unsigned long long attr_done = 0;    // one per kernel instantiation (generic lambda); bit per device
+    MPIT_CUDA_TRY(set_smem_limit_per_device(kern, 160 * 1024, attr_done));
     MPIT_CUDA_TRY(launch_k(kern, dim3(grid), dim3(kHeadWarps * 32), smem, st, a));
     return 0;
   };

@@ -643,12 +643,8 @@ template <int BLOCK_N, int MODE>
 static int launch_igemm(const CUtensorMap* ta, const CUtensorMap* tb, IgemmParams p, int m_tiles,
                         cudaStream_t st) {
   using L = SmemLayout<BLOCK_N>;
-  static bool attr_done = false;
-  if (!attr_done) {
-    MPIT_CUDA_TRY(cudaFuncSetAttribute(umma_igemm_kernel<BLOCK_N, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       L::total(L::kMaxFit)));
-    attr_done = true;
-  }
+  static unsigned long long attr_done = 0;   // bit per device
+  MPIT_CUDA_TRY(set_smem_limit_per_device(umma_igemm_kernel<BLOCK_N, MODE>, L::total(L::kMaxFit), attr_done));
   dim3 grid(m_tiles, p.N / BLOCK_N);
   // Pipeline depth.  Grids of up to one CTA per SM get the deepest pipeline that fits.  Larger grids are better
   // served by residency: make the stages small enough that ceil(ctas/148) CTAs (up to 4) share an SM, so the whole
@@ -786,10 +782,12 @@ int mpit_umma_conv_resident(const void* tmap_in128, const void* tmap_w128, const
   dim3 grid(p.B, p.N / block_n);
   cudaStream_t st = (cudaStream_t)stream;
   auto go = [&](auto kern) -> int {
-    static size_t attr_smem = 0;      // per instantiation: raise the opt-in limit to what this launch needs
-    if (smem > attr_smem) {            // (the kernel's static shared memory counts against the same 227 KB)
+    static size_t attr_smem[64] = {0};   // per instantiation and per device: raise the opt-in limit to what this
+    int dev = 0;                          // launch needs (the kernel's static shared memory counts against the same 227 KB)
+    MPIT_CUDA_TRY(cudaGetDevice(&dev));
+    if (smem > attr_smem[dev & 63]) {
       MPIT_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      attr_smem = smem;
+      attr_smem[dev & 63] = smem;
     }
     MPIT_CUDA_TRY(launch_k(kern, grid, dim3(192), smem, st, ti, tw, p, r));
     return 0;

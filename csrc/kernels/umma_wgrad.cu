@@ -324,12 +324,8 @@ template <int BLOCK_N>
 static int launch_wgrad(const CUtensorMap& tx, const CUtensorMap& tz, const WgradParams& p, int m_tiles,
                         int nsplit, cudaStream_t st) {
   using L = WSmem<BLOCK_N>;
-  static bool attr_done = false;
-  if (!attr_done) {
-    MPIT_CUDA_TRY(cudaFuncSetAttribute(umma_wgrad_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       L::kTotal));
-    attr_done = true;
-  }
+  static unsigned long long attr_done = 0;   // bit per device
+  MPIT_CUDA_TRY(set_smem_limit_per_device(umma_wgrad_kernel<BLOCK_N>, L::kTotal, attr_done));
   dim3 grid(m_tiles, p.N / BLOCK_N, nsplit);
   MPIT_CUDA_TRY(launch_k(umma_wgrad_kernel<BLOCK_N>, grid, dim3(192), (size_t)L::kTotal, st, tx, tz, p));
   return 0;

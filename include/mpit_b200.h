@@ -120,9 +120,11 @@ int mpit_classifier_head_scratch_floats(int K);
 int mpit_signal_words(void);
 int mpit_max_ranks(void);
 
-/* Get: dst[i] = centre[i]  (pclient.lua:74-84); optionally also refreshes the packed operand copy. */
+/* Get: dst[i] = centre[i]  (pclient.lua:74-84); optionally also refreshes the packed operand copy.  The index
+ * tables cover the elements [map_base, n) (nmaps tables of n - map_base entries): parameters below map_base,
+ * e.g. an embedding table that is read in flat order, have no operand copy. */
 int mpit_param_pull(const unsigned long long* shard_ptrs, int nranks, int rank, float* dst, long long n,
-                    float* wpk, const int* wmap, int nmaps, void* stream);
+                    float* wpk, const int* wmap, int nmaps, long long map_base, void* stream);
 /* Put: centre[i] = src[i]  (seed, pclient.lua:62-72,131-133; single-mode push). */
 int mpit_param_put(const unsigned long long* shard_ptrs, int nranks, int rank, const float* src, long long n,
                    void* stream);
@@ -140,13 +142,18 @@ int mpit_eamsgd_fused_step(const unsigned long long* shard_ptrs, int nranks, int
                            const float* g, const int* gmap, float* d, float* wpk, const int* wmap,
                            int nmaps, long long n, float alpha, float clr, float l2wd, float mom_next, int do_apply,
                            int use_mom, int do_lookahead, int do_sync, int has_d_in, void* stream);
-/* SUM/AVG all-reduce over symmetric buffers (test/testreduceall.lua:28). algo 0 = one-shot,
- * 1 = two-shot. `in_mc`/`out_mc` are NVLS multicast addresses (0 = use peer loads/stores).
- * x_elastic != NULL fuses x -= alpha*(x - mean). All ranks must call with identical n/max_blocks. */
+/* SUM/AVG all-reduce over symmetric buffers (test/testreduceall.lua:28, asyncsgd/testreduceall.lua:72-77).
+ * algo 0 = one-shot (result in the private `local_out`), 1 = two-shot (result in every rank's `out` buffer).
+ * `in_mc`/`out_mc` are NVLS multicast addresses (0 = use peer loads/stores).  x_elastic != NULL fuses
+ * x -= alpha*(x - mean) into the same kernel; the two-shot form then needs `flag_ptrs`, a symmetric uint32
+ * buffer of mpit_allreduce_flag_words(capacity) words (per-chunk arrival flags).  The signal pad must not be
+ * shared with a collective running concurrently on another stream.  All ranks call with identical n/algo. */
+long long mpit_allreduce_flag_words(long long capacity_floats);
 int mpit_allreduce(const unsigned long long* in_ptrs, unsigned long long in_mc,
                    const unsigned long long* out_ptrs, unsigned long long out_mc,
-                   const unsigned long long* sig_ptrs, int nranks, int rank, float* local_out, float* x_elastic,
-                   long long n, float scale, float alpha, int algo, int max_blocks, void* stream);
+                   const unsigned long long* sig_ptrs, const unsigned long long* flag_ptrs, int nranks, int rank,
+                   float* local_out, float* x_elastic, long long n, float scale, float alpha, int algo,
+                   int max_blocks, void* stream);
 int mpit_bcast(const unsigned long long* buf_ptrs, unsigned long long buf_mc, const unsigned long long* sig_ptrs,
                int nranks, int rank, int root, long long n, int max_blocks, void* stream);
 int mpit_device_barrier(const unsigned long long* sig_ptrs, int nranks, int rank, void* stream);
@@ -160,6 +167,31 @@ int mpit_mailbox_put(float* slot_base, const float* payload, unsigned count, uns
                      void* stream);
 int mpit_mailbox_recv(float* slot_base, float* dst, unsigned max_count, int tag, unsigned seq, int* result3,
                       void* stream);
+
+/* ---- asynchronous parameter server with server-side rules (csrc/kernels/ps_async.cu) ----------------
+ * Device path of BiCNN/pserver.lua:115-205 + BiCNN/optim-{adam,adamax,adagrad,adadelta,rmsprop}.lua: every rank is
+ * a client and the owner of one shard.  Symmetric buffers: `ctl` (mpit_ps_ctl_words() uint32, zeroed), `slots`
+ * ([nranks][cap] floats on every owner), the centre shard `p`.  hyper10 (HOST doubles) =
+ * {a, b, c, d, eps, lr, beta1, beta2, lrd, step_div} (a..eps as in mpit_rule_step's hyper6).
+ * mpit_ps_push: slot_ptrs[s] = address of MY slot inside owner s.  Gradient element i comes from gflat[i], or from
+ * gpk[gmap[i - map_base]] when gmap != NULL and i >= map_base; then gscale, L1/L2/clamp (skipped when *active == 0),
+ * su-step accumulation into acc; do_push = 0 only accumulates.  reg_loss[2] += {l1*|x|_1, l2*|x|^2/2}.
+ * mpit_ps_drain: poll + apply on `stream` (applies whatever has arrived, in arrival order; max_take > 0 limits
+ * the number of gradients per drain).  Neither call waits for a peer except push's bounded flow-control wait. */
+int mpit_ps_ctl_words(void);
+int mpit_ps_counter(const void* ctl_local, int which, unsigned* out);
+int mpit_ps_push(const unsigned long long* slot_ptrs, const unsigned long long* ctl_ptrs, int nranks, int rank,
+                 const float* gflat, const float* gpk, const int* gmap, long long map_base, const float* x, float* acc,
+                 const int* active, float* reg_loss, long long n, float l1, float l2, float clip, float gscale,
+                 int do_push, void* stream);
+int mpit_ps_drain(const unsigned long long* ctl_ptrs, int nranks, int rank, int rule, const double* hyper10, float* p,
+                  float* s0, float* s1, float* s2, const float* slots, long long cap, long long size, int max_take,
+                  void* stream);
+/* Native server thread: keeps draining on a high-priority stream of `dev` every interval_us until stopped. */
+int mpit_ps_server_start(int dev, const unsigned long long* ctl_ptrs, int nranks, int rank, int rule,
+                         const double* hyper10, float* p, float* s0, float* s1, float* s2, const float* slots,
+                         long long cap, long long size, int interval_us, void** out_handle);
+int mpit_ps_server_stop(void* handle, long long* rounds_out);
 
 /* ---- symmetric heap (csrc/symm/symm_heap.cu) --------------------------------------------- */
 /* Takes the place of the reference's CUDA-aware-MPI pointer bridge (/root/reference/lua-mpi.h:70-78).

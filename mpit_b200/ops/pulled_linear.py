@@ -9,7 +9,9 @@ ever materialised locally.  The un-fused formulation is ``ShardedCenter.pull`` f
 
 Measured (tools/bench_pulled_linear.py): 1.5-3.4x faster than NCCL all_gather + cuBLAS at 2 and 8
 GPUs while the batch is one or two 128-row tiles; every further M-tile fetches its weight tiles again, so for
-M >= 512 the un-fused form wins (cluster multicast across M-tiles is the missing piece).
+M >= 512 the un-fused form wins.  The remedy is reuse inside the CTA (one CTA owning several 128-row M-tiles, i.e.
+more TMEM accumulator columns per fetched weight tile) or bringing the shard into local memory first; TMA multicast
+loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's memory hung the GPU.
 """
 from __future__ import annotations
 

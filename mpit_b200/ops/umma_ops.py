@@ -247,7 +247,7 @@ class CifarUmmaPlan:
         self.two_streams = os.environ.get("MPIT_BWD_STREAMS", "2") != "1"
         # One more fork exists but is off by default: reducing layers 1..4 on the side stream beside the last data
         # gradient.  Every fork/join turns a programmatic (PDL) edge into a full one, and on B200 the two effects
-        # cancel (tools/dev/pdl_ab.py, ms/step: PDL on + no fork 0.1619; PDL on + fork 0.1634; PDL off + fork 0.1661).
+        # cancel (A/B, ms/step: PDL on + no fork 0.1619; PDL on + fork 0.1634; PDL off + fork 0.1661).
         self.split_reduce = os.environ.get("MPIT_SPLIT_REDUCE", "0") == "1"
         self._side = torch.cuda.Stream(device=eng.dev)
         self._ev = [torch.cuda.Event() for _ in range(5)]

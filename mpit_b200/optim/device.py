@@ -238,71 +238,63 @@ class DeviceRule(_DeviceOptBase):
 
 class DeviceRuleParallel(_DeviceOptBase):
     """Server-side adaptive rules on the device path (BiCNN/optim-{adam,adamax,adagrad,adadelta,rmsprop}.lua
-    clients + BiCNN/pserver.lua:115-205 server rules).
+    clients + BiCNN/pserver.lua:115-205 server rules), asynchronous like the reference.
 
-    Every GPU is a client *and* the owner of one parameter shard together with that shard's optimizer
-    state (the moments live only with the owner, as on the reference's servers).  A sync step is:
-    each client PUTs its raw (accumulated) gradient into its own staging slot on every owner -- the
-    per-client ``storage.g[crank]`` of pserver.lua:49-58 --, a device barrier, each owner drains the
-    slots **one client at a time in rank order** with the fused rule kernel (pserver.lua:119-198 applies
-    one client's gradient per recvgrad), a second barrier, and every client pulls the fresh parameters
-    (refreshing its tensor-core operand copies in the same kernel).
+    Every GPU is a client *and* the owner of one parameter shard together with that shard's optimizer state (the
+    moments live only with the owner, as on the reference's servers).  A sync step is three kernels and no barrier:
+    ``push`` (gradient prologue, su-step accumulation, stores into this client's staging slot on every owner -- the
+    per-client ``storage.g[crank]`` of pserver.lua:49-58 -- and an arrival ticket per owner), ``drain`` (the owner
+    applies the gradients that have ARRIVED, one client at a time in arrival order, and never waits for the rest) and
+    ``pull`` (fresh parameters + operand copies).  Update counts and step sizes live in device memory, so the whole
+    step is one CUDA graph.  ``server="thread"`` moves the draining to a native host thread with its own stream
+    (the reference's dedicated server process); ``"inline"`` drains once per step on the training stream.
     """
 
     def __init__(self, engine, theta0, rule: str, hyper: dict, center: ShardedCenter, heap, *, su: int = 1,
-                 l1=0.0, l2=0.0, clip=0.0, seed_center: Optional[bool] = None):
-        super().__init__(engine, theta0, False)
-        from ..parallel.center import shard_capacity
-        self.rule, self.hyper, self.center, self.su = rule, dict(hyper), center, su
+                 l1=0.0, l2=0.0, clip=0.0, seed_center: Optional[bool] = None, server: str = "inline",
+                 server_interval_us: int = 20, use_graphs: bool = True):
+        super().__init__(engine, theta0, use_graphs)
+        from ..parallel.ps_device import AsyncDevicePS
+        assert server in ("inline", "thread")
+        self.rule, self.hyper, self.center, self.su, self.server = rule, dict(hyper), center, su, server
         self.l1, self.l2, self.clip = l1, l2, clip
         self.nranks, self.rank = center.nranks, center.rank
-        cap = shard_capacity(self.n, self.nranks)
-        self.cap = cap
-        self.slots = heap.alloc(cap * self.nranks)            # [client][shard element] on every owner
-        self._slot_ptrs = self.slots.offset_ptr_array(4 * cap * self.rank)   # my slot inside each owner
-        self._sig = heap.signal_pad()
-        self._sig_ptrs = self._sig.ptr_array()
-        off, size = center.parts[self.rank]
-        self.shard_size = size
-        z = lambda: torch.zeros(cap, device=self.dev)
-        self.s0, self.s1, self.s2 = z(), z(), z()
-        self.acc = torch.zeros_like(self.x)                     # config.accumulated (optim-adam.lua:27-30)
-        self.g = torch.zeros_like(self.x)
-        self.applied = 0                                        # owner-side update count (adam_t, pversion...)
+        self.ps = AsyncDevicePS(heap, self.n, rule, hyper, center)
+        self.acc = torch.zeros_like(self.x) if su > 1 else None     # config.accumulated (optim-adam.lua:27-30)
         if seed_center if seed_center is not None else center.rank == 0:
             center.put(self.x)
         self.engine.load_flat(self.x)
+        if server == "thread":
+            self.ps.start_server(server_interval_us)
 
-    def _barrier(self):
-        from .._native import kernels, check, cur_stream
-        check(kernels().mpit_device_barrier(self._sig_ptrs, self.nranks, self.rank, cur_stream()), "mpit_device_barrier")
-
-    def step(self) -> None:
-        from .._native import kernels, check, ptr, cur_stream
+    def _sources(self):
         e = self.engine
-        e.fwd_bwd()
-        e.flat_grad(self.g)
-        do_sync = self.t % self.su == 0
-        if self.su > 1:
-            self.acc.add_(self.g)
-            src = self.acc
-        else:
-            src = self.g
+        gmap = getattr(e, "gmap", None)
+        if gmap is None:
+            return dict(gflat=e.gpk, gpk=None, gmap=None, map_base=0)
+        return dict(gflat=getattr(e, "gflat", None), gpk=e.gpk, gmap=gmap, map_base=getattr(e, "map_base", 0))
+
+    def exchange(self, do_sync: bool, active=None, reg_loss=None) -> None:
+        """push [-> drain] -> pull on the current stream (what follows the backward pass of a step)."""
+        e = self.engine
+        self.ps.push(x=self.x, acc=self.acc, active=active, reg_loss=reg_loss, l1=self.l1, l2=self.l2, clip=self.clip,
+                     do_push=do_sync, **self._sources())
         if do_sync:
-            k = kernels()
-            # PUT my gradient into my staging slot on every owner
-            check(k.mpit_param_put(self._slot_ptrs, self.nranks, self.rank, ptr(src), self.n, cur_stream()), "mpit_param_put")
-            self._barrier()
-            # owner: apply the rule once per client, in rank order
-            p = self.center.buf.local
-            for c in range(self.nranks):
-                self.applied += 1
-                h = ops.rule_hyper(self.rule, self.applied, **self.hyper)
-                slot = self.slots.local[c * self.cap:(c + 1) * self.cap]
-                ops.rule_step(self.rule, p[:self.shard_size], slot[:self.shard_size], h, self.s0[:self.shard_size],
-                              self.s1[:self.shard_size], self.s2[:self.shard_size], l1=self.l1, l2=self.l2, clip=self.clip)
-            self._barrier()
-            self.center.pull(self.x, e.wpk, e.wmap)
-            if self.su > 1:
-                self.acc.zero_()
+            if self.server == "inline":
+                self.ps.drain()
+            self.ps.pull(self.x, e.wpk, getattr(e, "wmap", None), getattr(e, "map_base", 0))
+
+    def step(self, fwd_bwd=None) -> None:
+        do_sync = self.t % self.su == 0        # pversion % su == 0, step 0 included (optim-adam.lua:32)
+        run = fwd_bwd if fwd_bwd is not None else self.engine.fwd_bwd
+
+        def body():
+            run()
+            self.exchange(do_sync)
+
+        self.graphs.run(("step", do_sync), body)
         self.t += 1
+
+    def close(self) -> int:
+        """Stops the server thread (if any); returns the number of drains it ran."""
+        return self.ps.stop_server()

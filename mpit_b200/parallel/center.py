@@ -65,14 +65,16 @@ class ShardedCenter:
         check(self.k.mpit_param_put(self._ptrs, self.nranks, self.rank, ptr(src), self.n, cur_stream()),
               "mpit_param_put")
 
-    def pull(self, dst: torch.Tensor, wpk=None, wmap=None) -> None:
-        """dst := centre (pclient.lua:74-84), optionally refreshing the packed operand copy."""
+    def pull(self, dst: torch.Tensor, wpk=None, wmap=None, map_base: int = 0) -> None:
+        """dst := centre (pclient.lua:74-84), optionally refreshing the packed operand copy (``wmap`` covers the
+        elements from ``map_base`` on)."""
         if self.bulk and wpk is None and dst.data_ptr() % 16 == 0:
             check(self.k.mpit_param_pull_bulk(self._ptrs, self.nranks, self.rank, ptr(dst), self.n, cur_stream()),
                   "mpit_param_pull_bulk")
             return
+        nmaps = 0 if wmap is None else max(1, int(wmap.numel()) // (self.n - map_base))
         check(self.k.mpit_param_pull(self._ptrs, self.nranks, self.rank, ptr(dst), self.n, ptr(wpk), ptr(wmap),
-                                     self._nmaps(wmap), cur_stream()), "mpit_param_pull")
+                                     nmaps, map_base, cur_stream()), "mpit_param_pull")
 
     def push_add(self, src: torch.Tensor, params: Optional[torch.Tensor] = None, *, scale=1.0, l1=0.0, l2=0.0,
                  clip=0.0, zero_src=False) -> None:

@@ -49,9 +49,13 @@ class DeviceCollectives:
         self.capacity = capacity
         self.inp: SymmBuffer = heap.alloc(capacity, multicast=multicast)
         self.out: SymmBuffer = heap.alloc(capacity, multicast=multicast)
-        self.sig: SymmBuffer = heap.signal_pad()
+        # a pad of its own: the epoch words of the all-reduce must not be shared with a collective that may run
+        # concurrently on another stream (Iallreduce next to a barrier of the training loop)
+        self.sig: SymmBuffer = heap.alloc(self.k.mpit_signal_words(), dtype=torch.int32)
+        self.flags: SymmBuffer = heap.alloc(int(self.k.mpit_allreduce_flag_words(capacity)), dtype=torch.int32)
         self.nranks, self.rank = self.inp.nranks, self.inp.rank
         self._in_ptrs, self._out_ptrs, self._sig_ptrs = self.inp.ptr_array(), self.out.ptr_array(), self.sig.ptr_array()
+        self._flag_ptrs = self.flags.ptr_array()
         self._side = torch.cuda.Stream()
 
     def allreduce(self, x: Optional[torch.Tensor] = None, n: Optional[int] = None, *, average: bool = False,
@@ -70,9 +74,9 @@ class DeviceCollectives:
         two = algo == "twoshot"
         local_out = None if two else self.out.local
         check(self.k.mpit_allreduce(self._in_ptrs, self.inp.mc_ptr, self._out_ptrs if two else None,
-                                    self.out.mc_ptr if two else 0, self._sig_ptrs, self.nranks, self.rank,
-                                    ptr(local_out), ptr(elastic_x), n, scale, alpha, 1 if two else 0, max_blocks,
-                                    cur_stream()), "mpit_allreduce")
+                                    self.out.mc_ptr if two else 0, self._sig_ptrs, self._flag_ptrs, self.nranks,
+                                    self.rank, ptr(local_out), ptr(elastic_x), n, scale, alpha, 1 if two else 0,
+                                    max_blocks, cur_stream()), "mpit_allreduce")
         return self.out.local[:n]
 
     def iallreduce(self, x: torch.Tensor, **kw) -> DeviceRequest:
@@ -87,6 +91,13 @@ class DeviceCollectives:
         check(self.k.mpit_bcast(self._out_ptrs, self.out.mc_ptr, self._sig_ptrs, self.nranks, self.rank, root, n,
                                 max_blocks, cur_stream()), "mpit_bcast")
         return self.out.local[:n]
+
+    def check_timeout(self) -> None:
+        """Raise if a bounded device-side wait of one of this object's collectives gave up."""
+        from .._native import NativeError
+        err = int(self.sig.local[self.k.mpit_signal_words() - 64].item())
+        if err != 0:
+            raise NativeError("device collective timed out: a peer rank did not launch its kernel")
 
     def barrier(self) -> None:
         check(self.k.mpit_device_barrier(self._sig_ptrs, self.nranks, self.rank, cur_stream()), "mpit_device_barrier")

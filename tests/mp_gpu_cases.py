@@ -65,7 +65,8 @@ def case_center(rank, world, dev, heap):
 
 
 def case_collectives(rank, world, dev, heap):
-    for n, algo in ((6, "oneshot"), (1000, "oneshot"), (1 << 20, "twoshot"), ((1 << 20) + 3, "twoshot"), (4096, "twoshot")):
+    for n, algo in ((6, "oneshot"), (1000, "oneshot"), (1 << 20, "twoshot"), ((1 << 20) + 3, "twoshot"), (4096, "twoshot"),
+                    (351946, "oneshot"), (351946, "twoshot"), ((9 << 20) + 1, "twoshot")):
         coll = DeviceCollectives(heap, n)
         x = torch.full((n,), float(rank + 1), device=dev) + torch.arange(n, device=dev) % 7
         out = coll.allreduce(x, algo=algo)
@@ -77,12 +78,22 @@ def case_collectives(rank, world, dev, heap):
         torch.cuda.synchronize()
         assert torch.allclose(out, want / world, atol=1e-5)
         sync(dev)
-        # fused elastic pull toward the mean
-        xe = x.clone()
-        coll.allreduce(x, algo=algo, average=True, elastic_x=xe, alpha=0.25)
+        # fused elastic pull toward the mean: fresh values, and the output buffer poisoned first so that a tail
+        # pass reading a chunk before its owner wrote it cannot pass on leftovers of the previous call
+        x2 = x * 0.5 + (torch.arange(n, device=dev) % 5) * (rank + 1)
+        coll.out.local.fill_(float("nan"))
+        sync(dev)
+        xe = x2.clone()
+        coll.allreduce(x2, algo=algo, average=True, elastic_x=xe, alpha=0.25)
         torch.cuda.synchronize()
-        mean = want / world
-        assert torch.allclose(xe, x - 0.25 * (x - mean), atol=1e-5), (n, algo)
+        mean2 = want / world * 0.5 + (torch.arange(n, device=dev) % 5) * ((world + 1) / 2)
+        assert torch.allclose(xe, x2 - 0.25 * (x2 - mean2), atol=1e-4), (n, algo, float((xe - (x2 - 0.25 * (x2 - mean2))).abs().max()))
+        sync(dev)
+        # back-to-back launches without a host sync in between (epoch words, buffer reuse)
+        for rep in range(3):
+            out = coll.allreduce(x, algo=algo)
+        torch.cuda.synchronize()
+        assert torch.allclose(out, want), (n, algo, "back to back")
         sync(dev)
         # non-blocking: Test / Wait state machine (test/testireduceall.lua:27-39)
         req = coll.iallreduce(x, algo=algo)
@@ -98,6 +109,7 @@ def case_collectives(rank, world, dev, heap):
         torch.cuda.synchronize()
         assert float(coll.out.local[:n].min()) == root and float(coll.out.local[:n].max()) == root
         sync(dev)
+        coll.check_timeout()
     coll.barrier()
     torch.cuda.synchronize()
     heap.check_timeout()
@@ -142,53 +154,113 @@ def case_eamsgd_train(rank, world, dev, heap):
     assert 0.5 < tr.last_loss() < 5.0
     heap.check_timeout()
 
+PS_HYPER = {
+    "adam": dict(lr=0.01, beta1=0.9, beta2=0.999, epsilon=1e-8, step_div=3),
+    "adagrad": dict(lr=1e-2, lrd=1e-3, epsilon=1e-10),
+    "adadelta": dict(rho=0.9, epsilon=1e-6, lr=1.0),
+    "rmsprop": dict(decay=0.95, lr=1e-3, momentum=0.9, epsilon=1e-4),
+}
+
+
+def _ps_grad(n, r, t):
+    return torch.randn(n, generator=torch.Generator().manual_seed(1000 * r + t)) * 0.1
+
+
 def case_server_rules(rank, world, dev, heap):
-    """Server-side Adam on the device path: owners drain per-client staging slots in rank order; the
-    result must equal the CPU restatement of BiCNN/pserver.lua applied client by client."""
+    """Server-side rules on the asynchronous device path: every owner applies the gradients of a round in the order
+    their arrival tickets were drawn (read back from the device) and must end up, on its shard, exactly where the CPU
+    restatement of BiCNN/pserver.lua:115-205 ends up when fed the same order."""
     from mpit_b200.optim import reference as R
-    from mpit_b200.optim.device import DeviceRuleParallel
+    from mpit_b200.parallel.ps_device import AsyncDevicePS
+    n, rounds = 10007, 4
+    for rule, hyper in PS_HYPER.items():
+        center = ShardedCenter.create(heap, n)
+        ps = AsyncDevicePS(heap, n, rule, hyper, center)
+        theta0 = torch.linspace(-1, 1, n)
+        if rank == 0:
+            center.put(theta0.to(dev))
+        sync(dev)
+        off, sz = center.parts[rank]
+        p = theta0[off:off + sz].clone()
+        st = R.rule_state(rule, p)
+        for t in range(rounds):
+            pushers = list(range(world)) if t != 2 else list(range(0, world, 2))     # round 2: only the even ranks push
+            if rank in pushers:
+                ps.push(gflat=_ps_grad(n, rank, t).to(dev))
+            sync(dev)                      # every gradient of the round has arrived
+            ps.drain()
+            torch.cuda.synchronize()
+            order = ps.ctl.local[64:64 + len(pushers)].tolist()
+            assert sorted(order) == pushers, (order, pushers)
+            for c in order:
+                R.apply_rule(rule, p, _ps_grad(n, c, t)[off:off + sz], st, hyper)
+            sync(dev)
+        got = center.local_shard.cpu()
+        assert torch.allclose(got, p, rtol=1e-6, atol=1e-7), (rule, float((got - p).abs().max()))
+        assert ps.applied == (rounds - 1) * world + len(range(0, world, 2))
+        x = torch.empty(n, device=dev)
+        ps.pull(x)
+        torch.cuda.synchronize()
+        assert torch.equal(x[off:off + sz].cpu(), got)
+        ps.check_timeout()
+        sync(dev)
 
-    class FakeEngine:     # gradient source with the engine interface, deterministic per (rank, step)
-        def __init__(self, n):
-            self.n, self.t = n, 0
-            self.wpk = torch.zeros(n, device=dev)
-            self.wmap = None
-            self.g = torch.zeros(n, device=dev)
 
-        def grad_for(self, r, t):
-            gen = torch.Generator().manual_seed(1000 * r + t)
-            return torch.randn(self.n, generator=gen) * 0.1
-
-        def load_flat(self, x):
-            pass
-
-        def fwd_bwd(self):
-            self.g.copy_(self.grad_for(rank, self.t))
-            self.t += 1
-
-        def flat_grad(self, out):
-            out.copy_(self.g)
-
-    n = 10007
-    hyper = dict(lr=0.01, beta1=0.9, beta2=0.999, epsilon=1e-8, step_div=3)
-    theta0 = torch.linspace(-1, 1, n)
-    eng = FakeEngine(n)
-    center = ShardedCenter.create(heap, n)
-    opt = DeviceRuleParallel(eng, theta0, "adam", hyper, center, heap)
-    sync(dev)
-    steps = 4
-    for _ in range(steps):
-        opt.step()
-    sync(dev)
-    heap.check_timeout()
-    # oracle: one server holding everything, gradients applied client by client each round
-    p = theta0.clone()
-    st = R.rule_state("adam", p)
-    for t in range(steps):
-        for c in range(world):
-            R.apply_rule("adam", p, eng.grad_for(c, t), st, hyper)
-    got = opt.x.cpu()
-    assert torch.allclose(got, p, rtol=1e-5, atol=1e-6), float((got - p).abs().max())
+def case_ps_stress(rank, world, dev, heap):
+    """Skewed ranks on the asynchronous path (the straggler simulation of /root/reference/BiCNN/ptest2.lua:57-70:
+    (rank+1-size/2)^2 busy iterations per round), owners served by their native server threads.  Invariants:
+    every push is applied exactly once on every shard (update count = sum of pushes), nothing is lost or doubled
+    (plain-add rule: centre = theta0 + sum of everything pushed), no wait times out, and the fast ranks are not
+    slowed to the pace of the slowest one."""
+    import time
+    from mpit_b200.parallel.ps_device import AsyncDevicePS
+    n = 3_458_600 if world > 2 else 400_003          # BiCNN-sized vector on the larger boxes
+    rounds = 24
+    skew = (rank + 1 - world / 2) ** 2
+    for rule, hyper in (("add", {}), ("adam", PS_HYPER["adam"])):
+        center = ShardedCenter.create(heap, n)
+        ps = AsyncDevicePS(heap, n, rule, hyper, center)
+        if rank == 0:
+            center.put(torch.zeros(n, device=dev))
+        sync(dev)
+        ps.start_server(interval_us=30)
+        sync(dev)
+        g = torch.full((n,), float(rank + 1) * 2.0 ** -10, device=dev)
+        x = torch.empty(n, device=dev)
+        a = torch.randn(2048, 2048, device=dev)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for t in range(rounds):
+            for _ in range(int(skew) * 4):                 # artificial compute skew
+                a = torch.tanh(a @ a * 1e-3)
+            ps.push(gflat=g)
+            ps.pull(x)
+        torch.cuda.synchronize()
+        mine = time.perf_counter() - t0
+        times = [None] * world
+        dist.all_gather_object(times, mine)
+        sync(dev)
+        # let the server threads finish what is still in the slots, then stop them
+        deadline = time.time() + 20
+        while ps.applied < rounds * world and time.time() < deadline:
+            time.sleep(0.005)
+        drains = ps.stop_server()
+        sync(dev)
+        assert ps.applied == rounds * world, (ps.applied, rounds * world)
+        assert ps.pushes == rounds
+        ps.pull(x)
+        torch.cuda.synchronize()
+        assert torch.isfinite(x).all()
+        if rule == "add":
+            want = rounds * sum(r + 1 for r in range(world)) * 2.0 ** -10      # exact in fp32
+            assert float(x.min()) == want and float(x.max()) == want, (float(x.min()), float(x.max()), want)
+        ps.check_timeout()
+        if rank == 0:
+            print(f"ps_stress {rule}: n={n} rounds={rounds} seconds per rank {[round(t, 4) for t in times]} "
+                  f"server drains on rank 0: {drains}")
+        if world >= 4:
+            assert min(times) < 0.7 * max(times), ("the fastest rank was held back by the slowest", times)
+        sync(dev)
 
 
 def case_pulled_linear(rank, world, dev, heap):

@@ -40,6 +40,12 @@ def test_server_side_rules_on_device_path():
     assert "case server_rules: ok" in out
 
 
+def test_async_parameter_server_under_rank_skew():
+    n = min(torch.cuda.device_count(), 8)
+    out = _torchrun(["ps_stress"], n)
+    assert "case ps_stress: ok" in out
+
+
 def test_pull_fused_with_consumer_gemm():
     n = min(torch.cuda.device_count(), 8)
     out = _torchrun(["pulled_linear"], n)
