@@ -172,6 +172,111 @@ encoder_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ r, co
   }
 }
 
+// ---- device-side mini-batch assembly and negative sampling (bicnn.lua:295-359) ------------------------------
+// The training set, the answer table and the per-sample target lists live on the device; a step only receives
+// the indices of its samples.  Sentence s of the step's [S][Lk] token matrix is: question of sample s (s < B),
+// its positive answer (B <= s < 2B), or candidate negative k of sample b (s = 2B + b*K + k) -- a uniformly drawn
+// answer that is not one of the sample's targets (rejection sampling, bicnn.lua:327-334), keyed by
+// (seed, step, s) through Philox so that graph replays draw fresh candidates.
+struct BatchArgs {
+  const int* q_tok; const int* q_len; const int* a_tok; const int* a_len;   // training set [N][Lk], [N]
+  const int* targets; int tmax;                                           // [N][tmax], -1 padded
+  const int* ans_tok; const int* ans_len; int A;                          // answer table [A][Lk], [A]
+  int Lk, kw;
+  const int* batch; int B, K, S;                                          // sample indices of this step (-1 = none)
+  unsigned long long seed; const unsigned long long* step;
+  int* tokens; int* lens; int* frames; int* row_valid; int* neg_idx;
+};
+
+__global__ void __launch_bounds__(64) bicnn_build_batch_kernel(BatchArgs a) {
+  const int s = blockIdx.x;
+  __shared__ int s_src, s_len;
+  if (threadIdx.x == 0) {
+    int src = -1, len = 0;      // src: row offset into one of the three token tables, encoded below
+    if (s < a.B) {
+      const int idx = a.batch[s];
+      if (idx >= 0) { src = idx; len = a.q_len[idx]; }
+    } else if (s < 2 * a.B) {
+      const int idx = a.batch[s - a.B];
+      if (idx >= 0) { src = idx; len = a.a_len[idx]; }
+    } else if (s < 2 * a.B + a.B * a.K) {
+      const int b = (s - 2 * a.B) / a.K;
+      const int idx = a.batch[b];
+      if (idx >= 0) {
+        const int* tg = a.targets + (size_t)idx * a.tmax;
+        int j = 0;
+        bool found = false;
+        for (unsigned attempt = 0; attempt < 16 && !found; ++attempt) {
+          const uint4 r = Philox::gen(a.seed, *a.step * (unsigned long long)a.S + (unsigned long long)s, attempt);
+          const unsigned rv[4] = {r.x, r.y, r.z, r.w};
+          for (int u = 0; u < 4 && !found; ++u) {
+            j = (int)(rv[u] % (unsigned)a.A);
+            found = true;
+            for (int t = 0; t < a.tmax; ++t) if (tg[t] == j) { found = false; break; }
+          }
+        }
+        a.neg_idx[s - 2 * a.B] = j;
+        src = j;
+        len = a.ans_len[j];
+      }
+    }
+    s_src = src;
+    s_len = len;
+    a.lens[s] = src >= 0 ? len : a.kw;
+    const int fr = len - a.kw + 1;
+    a.frames[s] = (src >= 0 && fr > 0) ? fr : 0;
+  }
+  __syncthreads();
+  const int src = s_src, len = s_len;
+  const int* table = s < a.B ? a.q_tok : (s < 2 * a.B ? a.a_tok : a.ans_tok);
+  for (int l = threadIdx.x; l < a.Lk; l += blockDim.x) {
+    const bool in = src >= 0 && l < len;
+    a.tokens[(size_t)s * a.Lk + l] = in ? table[(size_t)src * a.Lk + l] : 0;
+    a.row_valid[(size_t)s * a.Lk + l] = in ? 1 : 0;
+  }
+}
+
+// First margin violator per sample (bicnn.lua:321-359): sim holds s+ of the B samples followed by the B*K
+// candidate similarities.  Emits the (q,a+),(q,a-) pair list of the backward pass; a sample without a violator
+// (or an empty batch slot) gets the similarity pair (1, 0), which the margin kernel treats as inactive.
+__global__ void __launch_bounds__(128)
+bicnn_select_kernel(const float* __restrict__ sim, const float* __restrict__ stats, const int* __restrict__ batch, int B,
+                    int K, float margin, int* __restrict__ ai2, float* __restrict__ sim2, float* __restrict__ stats2,
+                    int* __restrict__ active, float* __restrict__ counters, unsigned long long* step) {
+  __shared__ int s_any;
+  if (threadIdx.x == 0) s_any = 0;
+  __syncthreads();
+  int mine = 0;
+  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+    int first = -1;
+    if (batch[b] >= 0) {
+      const float sp = sim[b];
+      for (int k = 0; k < K; ++k)
+        if (sp - sim[B + b * K + k] < margin) { first = k; break; }
+    }
+    ai2[2 * b] = B + b;
+    if (first >= 0) {
+      const int p = B + b * K + first;
+      ai2[2 * b + 1] = 2 * B + b * K + first;
+      sim2[2 * b] = sim[b]; sim2[2 * b + 1] = sim[p];
+      stats2[4 * b] = stats[2 * b]; stats2[4 * b + 1] = stats[2 * b + 1];
+      stats2[4 * b + 2] = stats[2 * p]; stats2[4 * b + 3] = stats[2 * p + 1];
+      ++mine;
+    } else {
+      ai2[2 * b + 1] = 2 * B + b * K;
+      sim2[2 * b] = 1.f; sim2[2 * b + 1] = 0.f;
+      stats2[4 * b] = stats2[4 * b + 1] = stats2[4 * b + 2] = stats2[4 * b + 3] = 0.f;
+    }
+  }
+  if (mine) atomicAdd(&s_any, mine);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    *active = s_any > 0 ? 1 : 0;
+    if (counters) { counters[0] += (float)s_any; counters[1] += 1.f; }   // triples trained on, steps
+    *step += 1ull;
+  }
+}
+
 }  // namespace mpit
 
 using namespace mpit;
@@ -226,6 +331,34 @@ int mpit_encoder_bwd(const float* dy, const float* r, const unsigned char* arg, 
   if (S <= 0) return 0;
   if (ld & 3) return MPIT_E_ARG;
   encoder_bwd_kernel<<<S, 256, 0, (cudaStream_t)stream>>>(dy, r, arg, normp, dC, gmax, F, ld, T);
+  MPIT_LAUNCH_CHECK();
+  return 0;
+}
+
+/* Device-side mini-batch assembly with negative sampling; ptrs18 is a HOST array of the 18 device pointers
+ * {q_tok, q_len, a_tok, a_len, targets, ans_tok, ans_len, batch, step, tokens, lens, frames, row_valid, neg_idx}
+ * (14 used, 4 reserved) and dims8 = {tmax, A, Lk, kw, B, K, S, 0}. */
+int mpit_bicnn_build_batch(const unsigned long long* ptrs18, const int* dims8, unsigned long long seed, void* stream) {
+  if (!ptrs18 || !dims8) return MPIT_E_ARG;
+  BatchArgs a{};
+  a.q_tok = (const int*)ptrs18[0]; a.q_len = (const int*)ptrs18[1]; a.a_tok = (const int*)ptrs18[2];
+  a.a_len = (const int*)ptrs18[3]; a.targets = (const int*)ptrs18[4]; a.ans_tok = (const int*)ptrs18[5];
+  a.ans_len = (const int*)ptrs18[6]; a.batch = (const int*)ptrs18[7]; a.step = (const unsigned long long*)ptrs18[8];
+  a.tokens = (int*)ptrs18[9]; a.lens = (int*)ptrs18[10]; a.frames = (int*)ptrs18[11]; a.row_valid = (int*)ptrs18[12];
+  a.neg_idx = (int*)ptrs18[13];
+  a.tmax = dims8[0]; a.A = dims8[1]; a.Lk = dims8[2]; a.kw = dims8[3]; a.B = dims8[4]; a.K = dims8[5]; a.S = dims8[6];
+  a.seed = seed;
+  if (a.A < 1 || a.B < 1 || a.K < 0 || a.S < 2 * a.B + a.B * a.K || a.Lk < 1) return MPIT_E_ARG;
+  bicnn_build_batch_kernel<<<a.S, 64, 0, (cudaStream_t)stream>>>(a);
+  MPIT_LAUNCH_CHECK();
+  return 0;
+}
+
+int mpit_bicnn_select(const float* sim, const float* stats, const int* batch, int B, int K, float margin, int* ai2,
+                      float* sim2, float* stats2, int* active, float* counters, unsigned long long* step, void* stream) {
+  if (B < 1 || K < 1) return MPIT_E_ARG;
+  bicnn_select_kernel<<<1, 128, 0, (cudaStream_t)stream>>>(sim, stats, batch, B, K, margin, ai2, sim2, stats2, active,
+                                                          counters, step);
   MPIT_LAUNCH_CHECK();
   return 0;
 }

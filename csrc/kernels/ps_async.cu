@@ -11,8 +11,8 @@
 //   ps_push   (client)  gradient prologue (packed->flat gather, L1/L2/clamp, su-step accumulation), then
 //                       st.relaxed.sys.v4 of the shard pieces into THIS client's staging slot on every owner;
 //                       the last CTA draws an arrival ticket on each owner (atom.add.sys) and publishes it with
-//                       st.release.sys.  Flow control: before overwriting a slot the kernel waits (bounded, on
-//                       words in its OWN memory) until the owner has acknowledged the previous push.
+//                       st.release.sys.  Flow control: a one-warp kernel in front of it waits (bounded, on words in
+//                       the client's OWN memory) until every owner has acknowledged the previous push.
 //   ps_poll   (owner)   one warp: snapshot of the arrival words, ready slots sorted by arrival ticket, the
 //                       update count and the per-update step sizes (adam bias correction etc.) computed on the
 //                       device -- nothing about a drain depends on host state, so it can sit in a CUDA graph.
@@ -40,16 +40,18 @@ enum PsWord : int {
   PS_DONE = 16,        // [8]  owner side: PS_ARR value of client c already applied (local)
   PS_ACKED = 24,       // [8]  owner side: gradients of client c applied so far (local)
   PS_APPLIED = 32,     //      owner side: total updates applied to this shard (adam_t / pversion)
-  PS_ACK = 40,         // [8]  client side: pushes of mine that owner s has applied (written by s)
-  PS_NPUSH = 48,       //      client side: pushes issued
-  PS_PUSH_TICKET = 49, //      CTA tickets of the running push / apply kernel
-  PS_APPLY_TICKET = 50,
-  PS_ERR = 51,         //      a bounded wait gave up
+  PS_APPLY_TICKET = 50,//      CTA tickets of the running apply kernel
   PS_NTODO = 56,       //      snapshot of the running drain
   PS_TBASE = 57,
   PS_TODO_CLIENT = 64, // [8]
   PS_TODO_ARR = 72,    // [8]
   PS_TODO_STEP = 80,   // [8] float bits
+  // client side, in a 128-byte line of its own (the flow-control wait polls it while the owner side is busy)
+  PS_ACK = 96,         // [8]  pushes of mine that owner s has applied (written by s)
+  PS_NPUSH = 104,      //      pushes issued
+  PS_PUSH_TICKET = 105,//      CTA tickets of the running push kernel
+  PS_ERR = 106,        //      a bounded wait gave up (1 + owner)
+  PS_MAXWAIT = 107,    //      longest flow-control wait of a push so far, in units of 1024 clocks
   PS_WORDS = 128,
 };
 
@@ -109,18 +111,27 @@ struct PsPushArgs {
 
 constexpr long long kPsChunkQuads = 1024;   // 16 KiB runs, dealt round-robin over the owners starting after me
 
+// Flow control, as a kernel of its own in front of the push: one warp waits (bounded, with back-off, on words in
+// this client's OWN memory) until every owner has applied the previous push, i.e. until the staging slots are free.
+// While it waits the rest of the GPU stays available to the owner-side kernels of this very GPU.
+__global__ void __launch_bounds__(32) ps_wait_kernel(uint32_t* mine, int nranks) {
+  const int t = threadIdx.x;
+  if (t < nranks) {
+    const uint32_t want = *reinterpret_cast<volatile uint32_t*>(mine + PS_NPUSH);
+    const long long t0 = clock64();
+    unsigned backoff = 32;
+    while ((int32_t)(ld_acquire_sys_u32(mine + PS_ACK + t) - want) < 0) {
+      if (clock64() - t0 > MPIT_SPIN_TIMEOUT_CYCLES) { atomicExch(mine + PS_ERR, 1u + (uint32_t)t); break; }
+      __nanosleep(backoff);
+      if (backoff < 1024) backoff <<= 1;
+    }
+    atomicMax(mine + PS_MAXWAIT, (uint32_t)((clock64() - t0) >> 10));
+  }
+}
+
 __global__ void __launch_bounds__(256) ps_push_kernel(PsPushArgs a) {
   const int R = a.ctl.nranks, me = a.ctl.rank, t = threadIdx.x;
   uint32_t* mine = a.ctl.peer[me];
-  if (a.do_push && t < R) {
-    // the slot on owner t is free once it has applied every earlier push of mine
-    const uint32_t want = *reinterpret_cast<volatile uint32_t*>(mine + PS_NPUSH);
-    long long t0 = clock64();
-    while ((int32_t)(ld_acquire_sys_u32(mine + PS_ACK + t) - want) < 0) {
-      if (clock64() - t0 > MPIT_SPIN_TIMEOUT_CYCLES) { atomicExch(mine + PS_ERR, 1u); break; }
-    }
-  }
-  __syncthreads();
   const bool act = a.active ? (*a.active != 0) : true;
   float rl1 = 0.f, rl2 = 0.f;
   const long long total = a.cps * R * kPsChunkQuads;
@@ -142,12 +153,12 @@ __global__ void __launch_bounds__(256) ps_push_kernel(PsPushArgs a) {
       if (e >= cnt) break;
       const long long i = i0 + e;
       float v = (a.gmap && i >= a.map_base) ? a.gpk[a.gmap[i - a.map_base]] : a.gflat[i];
-      if (a.gscale != 1.f) v = mul_rn(v, a.gscale);
       if (act && (a.l1 != 0.f || a.l2 != 0.f || a.clip > 0.f)) {
         const float p = (a.l1 != 0.f || a.l2 != 0.f) ? a.x[i] : 0.f;
         v = grad_reg_clip(v, p, a.l1, a.l2, a.clip);
         if (a.reg_loss) { rl1 += fabsf(p); rl2 += p * p; }
       }
+      if (a.gscale != 1.f) v = mul_rn(v, a.gscale);     // e.g. -lr for Downpour (optim-downpour.lua:24)
       if (a.acc) {
         v = add_rn(a.acc[i], v);
         a.acc[i] = a.do_push ? 0.f : v;
@@ -369,11 +380,11 @@ extern "C" {
 int mpit_ps_ctl_words(void) { return PS_WORDS; }
 
 /* counters for tests / monitoring: which = 0 applied updates on my shard, 1 pushes issued by me, 2 error word,
- * 3 arrivals seen on my shard.  `ctl_local` is this rank's control block (DEVICE); the value is copied to *out
+ * 3 arrivals seen on my shard, 4 longest flow-control wait of my pushes (units of 1024 clocks).  `ctl_local` is this rank's control block (DEVICE); the value is copied to *out
  * (HOST) with a synchronous cudaMemcpy. */
 int mpit_ps_counter(const void* ctl_local, int which, unsigned* out) {
-  static const int word[4] = {PS_APPLIED, PS_NPUSH, PS_ERR, PS_ARRIVALS};
-  if (which < 0 || which > 3 || !ctl_local || !out) return MPIT_E_ARG;
+  static const int word[5] = {PS_APPLIED, PS_NPUSH, PS_ERR, PS_ARRIVALS, PS_MAXWAIT};
+  if (which < 0 || which > 4 || !ctl_local || !out) return MPIT_E_ARG;
   MPIT_CUDA_TRY(cudaMemcpy(out, static_cast<const uint32_t*>(ctl_local) + word[which], 4, cudaMemcpyDeviceToHost));
   return 0;
 }
@@ -397,6 +408,10 @@ int mpit_ps_push(const unsigned long long* slot_ptrs, const unsigned long long* 
   a.gflat = gflat; a.gpk = gpk; a.gmap = gmap; a.map_base = map_base; a.x = x; a.acc = acc; a.active = active;
   a.reg_loss = reg_loss; a.n = n; a.l1 = l1; a.l2 = l2; a.clip = clip; a.gscale = gscale; a.do_push = do_push;
   const int grid = ew_grid(a.cps * nranks * kPsChunkQuads, 256, 1, 4);
+  if (do_push) {
+    ps_wait_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(a.ctl.peer[rank], nranks);
+    MPIT_LAUNCH_CHECK();
+  }
   ps_push_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(a);
   MPIT_LAUNCH_CHECK();
   return 0;
@@ -435,7 +450,14 @@ int mpit_ps_server_start(int dev, const unsigned long long* ctl_ptrs, int nranks
       int e = launch_drain(ctl, r, p, s0, s1, s2, slots, cap, size, 0, st);
       if (e != 0 || cudaStreamSynchronize(st) != cudaSuccess) { srv->error = e ? e : 3; break; }
       srv->rounds.fetch_add(1, std::memory_order_relaxed);
-      if (interval_us > 0) std::this_thread::sleep_for(std::chrono::microseconds(interval_us));
+      // pauses below the timer slack of sleep_for (~60 us) are spent polling the clock, like the reference's
+      // servers busy-poll their coroutine queue (co_wait with usec = 0, /root/reference/init.lua:185-192)
+      if (interval_us >= 100) {
+        std::this_thread::sleep_for(std::chrono::microseconds(interval_us));
+      } else if (interval_us > 0) {
+        const auto until = std::chrono::steady_clock::now() + std::chrono::microseconds(interval_us);
+        while (std::chrono::steady_clock::now() < until && !srv->stop.load(std::memory_order_relaxed)) std::this_thread::yield();
+      }
     }
     // a last drain so that nothing pushed before the stop request is left behind
     if (!srv->error.load()) { launch_drain(ctl, r, p, s0, s1, s2, slots, cap, size, 0, st); cudaStreamSynchronize(st); }

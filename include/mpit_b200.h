@@ -174,7 +174,7 @@ int mpit_mailbox_recv(float* slot_base, float* dst, unsigned max_count, int tag,
  * ([nranks][cap] floats on every owner), the centre shard `p`.  hyper10 (HOST doubles) =
  * {a, b, c, d, eps, lr, beta1, beta2, lrd, step_div} (a..eps as in mpit_rule_step's hyper6).
  * mpit_ps_push: slot_ptrs[s] = address of MY slot inside owner s.  Gradient element i comes from gflat[i], or from
- * gpk[gmap[i - map_base]] when gmap != NULL and i >= map_base; then gscale, L1/L2/clamp (skipped when *active == 0),
+ * gpk[gmap[i - map_base]] when gmap != NULL and i >= map_base; then L1/L2/clamp (skipped when *active == 0), gscale,
  * su-step accumulation into acc; do_push = 0 only accumulates.  reg_loss[2] += {l1*|x|_1, l2*|x|^2/2}.
  * mpit_ps_drain: poll + apply on `stream` (applies whatever has arrived, in arrival order; max_take > 0 limits
  * the number of gradients per drain).  Neither call waits for a peer except push's bounded flow-control wait. */
@@ -310,6 +310,19 @@ int mpit_gesd_margin_bwd(const float* y, const int* qi, const int* ai, const flo
  * [S][ld]): the per-sentence gradient itself; its column sums are the temporal convolution's bias gradient. */
 int mpit_encoder_bwd(const float* dy, const float* r, const unsigned char* arg, const float* normp, float* dC,
                      float* gmax, int S, int F, int ld, int T, void* stream);
+
+/* Device-side mini-batch assembly for a BiCNN training step (bicnn.lua:295-359): sentence rows of the question,
+ * the positive answer and K uniformly drawn wrong answers per sample (rejection against the sample's targets,
+ * bicnn.lua:327-334; Philox keyed by seed, *step and the row).  ptrs18 is a HOST array of device pointers
+ * {q_tok, q_len, a_tok, a_len, targets, ans_tok, ans_len, batch, step, tokens, lens, frames, row_valid, neg_idx,
+ * 0, 0, 0, 0}; dims8 (HOST) = {tmax, A, Lk, kw, B, K, S, 0}.  batch[b] < 0 marks an empty slot. */
+int mpit_bicnn_build_batch(const unsigned long long* ptrs18, const int* dims8, unsigned long long seed, void* stream);
+/* First margin violator among the K candidates of every sample (bicnn.lua:351-358) from the similarities of the
+ * B positive pairs followed by the B*K candidate pairs; writes the (q,a+),(q,a-) pair list of the backward pass
+ * (inactive samples get the similarity pair (1,0)), *active = any, counters += {triples, steps}, and advances
+ * *step. */
+int mpit_bicnn_select(const float* sim, const float* stats, const int* batch, int B, int K, float margin, int* ai2,
+                      float* sim2, float* stats2, int* active, float* counters, unsigned long long* step, void* stream);
 
 /* ---- bandwidth-path exchange through the bulk-copy engine (csrc/kernels/comm_bulk.cu) ----------- */
 /* Same semantics as mpit_param_pull / mpit_push_add / mpit_elastic_exchange, moved in 16 KiB

@@ -57,6 +57,7 @@ OPTIONS = [   # (name, default, help) -- plaunch.lua:10-69, same names, same def
     ("maxEvals", 3, "tester iterations before it stops (the reference never stops)"),
     ("synthTrain", 64, "synthetic corpus: training pairs"), ("synthAnswers", 60, "synthetic corpus: answer space"),
     ("synthVocab", 500, "synthetic corpus: vocabulary"),
+    ("psServer", "thread", "device path: thread (native server thread per shard owner) | inline (drain once per step)"),
 ]
 
 
@@ -116,8 +117,62 @@ def assign_roles(rank: int, size: int, opt: dict):
     return role, sranks, cranks, tranks
 
 
+def _corpus(opt: dict, W):
+    if opt["preloadBinary"] or os.path.exists(opt["trainFile"]):
+        return W.parse_corpus(opt)
+    return W.synthetic_corpus(opt["synthVocab"], opt["synthAnswers"], opt["synthTrain"], 20, 10,
+                              opt["embeddingDim"], opt["contConvWidth"], seed=0)
+
+
+def _gpu_main(opt: dict) -> int:
+    """``-type cuda`` under torchrun: one process per B200, no server processes -- every GPU trains and owns one shard
+    of the parameters together with the server-side rule state; gradients, parameters and acknowledgements move over
+    NVLink from inside the kernels (parallel/ps_device.py).  ``-testerlast`` / ``-testerfirst`` turn that rank into
+    the shadow tester of bicnn.lua:576-597 (it only pulls, evaluates and saves, and still serves its shard).
+
+        python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 -m mpit_b200.launch.plaunch \
+            -type cuda -optimization adam -batchSize 4 -epoch 1"""
+    import torch.distributed as dist
+    from ..parallel.symm import SymmetricHeap
+    from ..workloads import bicnn as W
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    barrier = (lambda: (torch.cuda.synchronize(dev), dist.barrier(), torch.cuda.synchronize(dev))) if world > 1 else None
+    if rank == min(1, world - 1):
+        print(opt)
+    torch.manual_seed(rank)
+    random.seed(rank)
+    tester = -1
+    if opt["validMode"] == "additionalTester" and world > 1:
+        tester = 0 if opt["testerfirst"] else (world - 1 if opt["testerlast"] else -1)
+    also_test = opt["validMode"] == "lastClient" and rank == world - 1
+    server = "thread" if (tester >= 0 or opt["psServer"] == "thread") else "inline"
+    heap = SymmetricHeap(dev)
+    tr = W.BiCNNDeviceTrainer(_corpus(opt, W), opt, dev, rank, heap, server=server)
+    if barrier:
+        barrier()                      # the first trainer's parameters are in the shards (pclient.lua:131-133)
+    print(f"Client {rank} ready to run {'testing' if rank == tester else 'training'} (gpu {local}, server {server})")
+    out = W.run_device_trainer(tr, rank == tester, also_test, barrier)
+    if rank != tester:
+        print(f"[rank {rank}] {out['steps']} steps in {out['seconds']:.2f} s, "
+              f"{out['steps'] * opt['batchSize'] / max(out['seconds'], 1e-9):.1f} questions/s, "
+              f"loss {out['loss'][-1] if out['loss'] else float('nan'):.5f}")
+    heap.check_timeout()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
 def main(argv=None) -> int:
     opt = parse(argv)
+    if opt["type"] == "cuda" and "LOCAL_RANK" in os.environ and "MPIT_RANK" not in os.environ:
+        return _gpu_main(opt)
     from .. import msg as mpiT, ps
     from ..workloads import bicnn as W
     torch.set_num_threads(opt["threads"])
@@ -142,11 +197,7 @@ def main(argv=None) -> int:
     if role == "ps":
         ps.pServer(conf).start()
     else:
-        if opt["preloadBinary"] or os.path.exists(opt["trainFile"]):
-            corpus = W.parse_corpus(opt)
-        else:
-            corpus = W.synthetic_corpus(opt["synthVocab"], opt["synthAnswers"], opt["synthTrain"], 20, 10,
-                                        opt["embeddingDim"], opt["contConvWidth"], seed=0)
+        corpus = _corpus(opt, W)
         dev = "cuda" if opt["type"] == "cuda" and torch.cuda.is_available() else "cpu"
         if dev == "cuda":     # B200 path: tcgen05 encoder + fused GESD/margin kernels
             torch.cuda.set_device(rank % torch.cuda.device_count())

@@ -96,6 +96,10 @@ class BiCnnEngine:
         self.dEmb = torch.zeros(R * Ep, **f32)
         self.loss_sum = torch.zeros(1, **f32)
         self.err = torch.zeros(1, dtype=torch.int32, device=dev)
+        # flat-order gradient buffer (its embedding part is what the push of a device optimizer reads; the dense
+        # part arrives packed in gpk and is gathered through gmap from map_base on)
+        self.gflat = torch.zeros(self.n_flat, **f32)
+        self.map_base = self.n_lookup
         self._build_plans()
 
     def _w(self, name, size):
@@ -205,13 +209,22 @@ class BiCnnEngine:
     def loss_backward(self, qi: torch.Tensor, ai: torch.Tensor, grad_flat: torch.Tensor) -> torch.Tensor:
         """``qi/ai`` list pairs as (q,a+),(q,a-) per triple.  Fills the packed dense gradients and adds the
         embedding gradient into ``grad_flat[:n_lookup]`` (which the caller has zeroed); returns loss_sum."""
-        k, st = self.k, cur_stream
         P = qi.numel()
         stats = torch.empty(2 * P, device=self.dev)
         sim = self.gesd(qi, ai, stats)
         self.loss_sum.zero_()
+        return self.backward_from_pairs(qi, ai, sim, stats, grad_flat)
+
+    def backward_from_pairs(self, qi, ai, sim, stats, grad_flat: torch.Tensor, loss_acc: Optional[torch.Tensor] = None):
+        """Backward of the margin loss for pair lists whose similarities are already known (``sim``, ``stats`` from
+        :meth:`gesd` or the device-side violator selection).  The hinge loss is ADDED to ``loss_acc`` (default: the
+        engine's ``loss_sum``)."""
+        k, st = self.k, cur_stream
+        P = qi.numel()
+        if loss_acc is None:
+            loss_acc = self.loss_sum
         self.dy.zero_()
-        check(k.mpit_gesd_margin_bwd(ptr(self.y), ptr(qi), ptr(ai), ptr(sim), ptr(stats), ptr(self.dy), ptr(self.loss_sum),
+        check(k.mpit_gesd_margin_bwd(ptr(self.y), ptr(qi), ptr(ai), ptr(sim), ptr(stats), ptr(self.dy), ptr(loss_acc),
                                      P // 2, self.F, self.Fp, self.margin, st()), "mpit_gesd_margin_bwd")
         # writes every frame of dC (no clearing of the 100 MB tensor) and the per-sentence gradient gmax
         check(k.mpit_encoder_bwd(ptr(self.dy), ptr(self.r), ptr(self.arg), ptr(self.normp), ptr(self.dC), ptr(self.gmax),
@@ -227,7 +240,54 @@ class BiCnnEngine:
         self.p_lin_dgrad.run(self.err)
         check(k.mpit_embedding_scatter_add(ptr(grad_flat), ptr(self.tokens), ptr(self.dEmb), ptr(self.row_valid), R,
                                            self.E, self.E, self.Ep, st()), "mpit_embedding_scatter_add")
-        return self.loss_sum
+        return loss_acc
+
+    # -- device-side training step (no host round trip) -----------------------------------------------------------
+    def attach_dataset(self, q_tok, q_len, a_tok, a_len, targets, ans_tok, ans_len, B: int, K: int, seed: int) -> None:
+        """Device-resident training set for :meth:`train_fwd_bwd`: int32 token matrices padded to ``L`` columns,
+        lengths, per-sample target lists (-1 padded) and the answer table.  ``S`` must be >= B*(2+K)."""
+        assert self.S >= B * (2 + K)
+        i32 = dict(dtype=torch.int32, device=self.dev)
+        self.ds = dict(q_tok=q_tok, q_len=q_len, a_tok=a_tok, a_len=a_len, targets=targets, ans_tok=ans_tok,
+                       ans_len=ans_len)
+        self.B, self.K, self.seed = B, K, seed
+        self.batch = torch.full((B,), -1, **i32)
+        self.step_ctr = torch.zeros(1, dtype=torch.int64, device=self.dev)
+        self.neg_idx = torch.zeros(max(B * K, 1), **i32)
+        P = B * (1 + K)
+        b = torch.arange(B, **i32)
+        self.qi_all = torch.cat([b, b.repeat_interleave(K)]).contiguous()
+        self.ai_all = torch.cat([b + B, 2 * B + torch.arange(B * K, **i32)]).contiguous()
+        self.sim_all = torch.zeros(P, device=self.dev)
+        self.stats_all = torch.zeros(2 * P, device=self.dev)
+        self.qi2 = b.repeat_interleave(2).contiguous()
+        self.ai2 = torch.zeros(2 * B, **i32)
+        self.sim2 = torch.zeros(2 * B, device=self.dev)
+        self.stats2 = torch.zeros(4 * B, device=self.dev)
+        self.active = torch.zeros(1, **i32)
+        self.counters = torch.zeros(4, device=self.dev)      # {triples trained on, steps, -, -}
+        self.loss_acc = torch.zeros(1, device=self.dev)      # running sum of the hinge losses
+        ptrs = [q_tok, q_len, a_tok, a_len, targets, ans_tok, ans_len, self.batch, self.step_ctr, self.tokens, self.lens,
+                self.frames, self.row_valid, self.neg_idx]
+        self._bb_ptrs = (ctypes.c_ulonglong * 18)(*[t.data_ptr() for t in ptrs], 0, 0, 0, 0)
+        self._bb_dims = (ctypes.c_int * 8)(targets.shape[1], ans_tok.shape[0], self.L, self.kw, B, K, self.S, 0)
+
+    def train_fwd_bwd(self) -> None:
+        """One training step's forward + backward for the samples listed in ``self.batch`` (device), everything on the
+        current stream and CUDA-graph capturable: batch assembly with negative sampling, ONE encoder pass over the
+        question, the positive answer and the K candidates of every sample, first-violator selection, and the
+        backward pass of the selected triples (bicnn.lua:279-420).  Gradients: ``gpk`` (dense, packed) and
+        ``gflat[:n_lookup]`` (embedding)."""
+        k, st = self.k, cur_stream
+        check(k.mpit_bicnn_build_batch(self._bb_ptrs, self._bb_dims, self.seed, st()), "mpit_bicnn_build_batch")
+        self.encode()
+        check(k.mpit_gesd_pairs(ptr(self.y), ptr(self.qi_all), ptr(self.ai_all), ptr(self.sim_all), ptr(self.stats_all),
+                                self.qi_all.numel(), self.F, self.Fp, st()), "mpit_gesd_pairs")
+        check(k.mpit_bicnn_select(ptr(self.sim_all), ptr(self.stats_all), ptr(self.batch), self.B, self.K, self.margin,
+                                  ptr(self.ai2), ptr(self.sim2), ptr(self.stats2), ptr(self.active), ptr(self.counters),
+                                  ptr(self.step_ctr), st()), "mpit_bicnn_select")
+        self.gflat[:self.n_lookup].zero_()
+        self.backward_from_pairs(self.qi2, self.ai2, self.sim2, self.stats2, self.gflat, self.loss_acc)
 
     def _wgrad(self, w):
         k = self.k

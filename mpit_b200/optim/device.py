@@ -49,7 +49,9 @@ class _GraphCache:
         torch.cuda.synchronize()
         g = torch.cuda.CUDAGraph()
         before = launches.count
-        with torch.cuda.graph(g):
+        # thread_local: a native server thread (parallel/ps_device.py) may be launching and synchronising on its own
+        # stream while this thread captures; only this thread's calls are checked against the capture
+        with torch.cuda.graph(g, capture_error_mode="thread_local"):
             fn()
         n = launches.count - before
         launches.count = before
@@ -251,13 +253,13 @@ class DeviceRuleParallel(_DeviceOptBase):
     """
 
     def __init__(self, engine, theta0, rule: str, hyper: dict, center: ShardedCenter, heap, *, su: int = 1,
-                 l1=0.0, l2=0.0, clip=0.0, seed_center: Optional[bool] = None, server: str = "inline",
-                 server_interval_us: int = 20, use_graphs: bool = True):
+                 l1=0.0, l2=0.0, clip=0.0, gscale: float = 1.0, seed_center: Optional[bool] = None,
+                 server: str = "inline", server_interval_us: int = 20, use_graphs: bool = True):
         super().__init__(engine, theta0, use_graphs)
         from ..parallel.ps_device import AsyncDevicePS
         assert server in ("inline", "thread")
         self.rule, self.hyper, self.center, self.su, self.server = rule, dict(hyper), center, su, server
-        self.l1, self.l2, self.clip = l1, l2, clip
+        self.l1, self.l2, self.clip, self.gscale = l1, l2, clip, gscale    # gscale = -lr: Downpour's push of -lr*g
         self.nranks, self.rank = center.nranks, center.rank
         self.ps = AsyncDevicePS(heap, self.n, rule, hyper, center)
         self.acc = torch.zeros_like(self.x) if su > 1 else None     # config.accumulated (optim-adam.lua:27-30)
@@ -278,7 +280,7 @@ class DeviceRuleParallel(_DeviceOptBase):
         """push [-> drain] -> pull on the current stream (what follows the backward pass of a step)."""
         e = self.engine
         self.ps.push(x=self.x, acc=self.acc, active=active, reg_loss=reg_loss, l1=self.l1, l2=self.l2, clip=self.clip,
-                     do_push=do_sync, **self._sources())
+                     gscale=self.gscale, do_push=do_sync, **self._sources())
         if do_sync:
             if self.server == "inline":
                 self.ps.drain()

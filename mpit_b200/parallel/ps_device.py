@@ -132,9 +132,16 @@ class AsyncDevicePS:
     def arrivals(self) -> int:
         return self._counter(3)
 
+    @property
+    def max_wait_us(self) -> float:
+        """Longest time a push of mine waited for an owner to free its slot (flow control), at the nominal 1.9 GHz."""
+        return self._counter(4) * 1024 / 1.9e3
+
     def check_timeout(self) -> None:
-        if self._counter(2) != 0:
-            raise NativeError("asynchronous parameter server: a flow-control wait timed out (an owner never drained)")
+        e = self._counter(2)
+        if e != 0:
+            raise NativeError(f"asynchronous parameter server: a push waited more than 2 s for owner {e - 1} to "
+                              f"acknowledge the previous one (that owner never drained)")
 
     def __del__(self):
         try:

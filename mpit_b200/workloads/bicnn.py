@@ -437,3 +437,142 @@ class BiCNNKernelTrainer(BiCNNTrainer):
         print(f"Client {self.rank}: curr time: {time.perf_counter() - self.t_start + self.opt['prevtime']:.2f}, "
               f"Accuracy: {acc:.4f}, best Accuracy: {self.best[name]:.4f} on {name} ")
         return acc
+
+
+def device_rule_for(opt: dict):
+    """Option table -> (rule, hyper, gscale) of the asynchronous device parameter server: the server-side rules of
+    BiCNN/pserver.lua:123-198 ('global' modes) and Downpour's plain add of ``-lr * g`` (optim-downpour.lua:24-54)."""
+    name = opt["optimization"]
+    if name == "downpour":
+        return "add", {}, -float(opt["learningRate"])
+    if name == "rmsprop":
+        if opt["modeRMSProp"] != "global":
+            raise ValueError("device path: rmsprop runs in 'global' mode (the rule lives with the shard)")
+        return "rmsprop", dict(decay=opt["decayRMSProp"], lr=opt["lrRMSProp"], momentum=opt["momentumRMSProp"],
+                               epsilon=opt["epsilonRMSProp"]), 1.0
+    if name in ("adam", "adamax"):
+        h = dict(lr=opt["lrAdam"], beta1=opt["beta1Adam"], beta2=opt["beta2Adam"], epsilon=opt["epsilonAdam"])
+        if name == "adam":
+            h["step_div"] = opt["stepDivAdam"]            # pserver.lua:151-152
+        return name, h, 1.0
+    if name == "adagrad":
+        return "adagrad", dict(lr=opt["lrAdagrad"], lrd=opt["lrDecayAdagrad"], epsilon=opt["epsilonAdagrad"]), 1.0
+    if name == "adadelta":
+        return "adadelta", dict(rho=opt["rhoAdadelta"], lr=opt["lrAdadelta"], epsilon=opt["epsilonAdadelta"]), 1.0
+    raise ValueError(f"device path: optimization {name!r} is not a server-side rule (use -type float)")
+
+
+class BiCNNDeviceTrainer(BiCNNKernelTrainer):
+    """Distributed BiCNN training on the NVLink device path (BASELINE.json config 4): one process per GPU, every GPU
+    a trainer and the owner of one shard of the parameters with the server-side rule state
+    (``optim.DeviceRuleParallel`` over ``parallel.AsyncDevicePS``).
+
+    A training step never returns to the host: the step's sample indices are copied in, and one CUDA graph runs the
+    device-side batch assembly with negative sampling (bicnn.lua:321-334), the encoder over question / positive /
+    candidates, the first-violator selection (:351-358), the backward pass, the client's push (L1 / L2 / clamp of
+    :398-409, ``commperiod`` accumulation), the owner's drain and the parameter pull.  Losses accumulate in device
+    memory and are read when somebody asks (:412-418 prints an average every 2000 evaluations)."""
+
+    def __init__(self, corpus: Corpus, opt: dict, device, rank: int, heap, server: str = "thread",
+                 use_graphs: bool = True):
+        super().__init__(corpus, opt, device, rank)
+        from ..optim.device import DeviceRuleParallel
+        from ..parallel.center import ShardedCenter
+        dev, L = self.dev, self.Lk
+        B, K = opt["batchSize"], opt["maxnegsample"]
+        fit = lambda sents: self._fit(pad_sentences(sents, dev)[0])
+        lens = lambda sents: torch.tensor([int(s.numel()) for s in sents], dtype=torch.int32, device=dev)
+        qs, as_ = [s[1] for s in corpus.train], [s[2] for s in corpus.train]
+        tmax = max(1, max(len(s[0]) for s in corpus.train))
+        targets = torch.full((len(corpus.train), tmax), -1, dtype=torch.int32)
+        for i, s in enumerate(corpus.train):
+            targets[i, :len(s[0])] = torch.tensor(s[0], dtype=torch.int32)
+        self.eng.attach_dataset(fit(qs), lens(qs), fit(as_), lens(as_), targets.to(dev), self._ans_tok32,
+                                self._ans_lens.int().contiguous(), B, K, seed=1000003 * (rank + 1))
+        rule, hyper, gscale = device_rule_for(opt)
+        self.center = ShardedCenter.create(heap, self.parameters.numel())
+        self.optim = DeviceRuleParallel(self.eng, self.parameters, rule, hyper, self.center, heap, su=opt["commperiod"],
+                                        l1=opt["L1reg"], l2=opt["L2reg"], clip=opt["gradClip"], gscale=gscale,
+                                        server=server, use_graphs=use_graphs, seed_center=(rank == 0))
+        self.parameters = self.optim.x                      # the flat vector the step works on
+        self.reg_loss = torch.zeros(2, device=dev)
+        self._batch_host = torch.full((B,), -1, dtype=torch.int32).pin_memory()
+        self.steps = 0
+
+    def train_step(self, batch: List[int]) -> None:
+        """One mini-batch: ``batch`` lists sample indices (at most ``batchSize``)."""
+        o = self.optim
+        self._batch_host.fill_(-1)
+        self._batch_host[:len(batch)] = torch.tensor(batch, dtype=torch.int32)
+        self.eng.batch.copy_(self._batch_host, non_blocking=True)
+        do_sync = o.t % o.su == 0
+
+        def body():
+            self.eng.train_fwd_bwd()
+            o.exchange(do_sync, active=self.eng.active, reg_loss=self.reg_loss)
+
+        o.graphs.run(("bicnn", do_sync), body)
+        o.t += 1
+        self.steps += 1
+
+    def loss_stats(self) -> dict:
+        """Sums since the start (one device->host read): hinge loss, regularisation terms, triples, steps."""
+        c = self.eng.counters.tolist()
+        return {"hinge": float(self.eng.loss_acc.item()), "l1": float(self.reg_loss[0]), "l2": float(self.reg_loss[1]),
+                "triples": int(c[0]), "steps": int(c[1])}
+
+    def pull_params(self) -> torch.Tensor:
+        """Tester role (bicnn.lua:580-596): fetch the current parameters from the shard owners."""
+        self.optim.ps.pull(self.optim.x, self.eng.wpk, self.eng.wmap, self.eng.map_base)
+        torch.cuda.synchronize(self.dev)
+        return self.optim.x
+
+    def close(self) -> int:
+        return self.optim.close()
+
+
+def run_device_trainer(tr: BiCNNDeviceTrainer, is_tester: bool, also_test: bool, barrier=None) -> dict:
+    """bicnn.lua:575-651 on the device path: the tester pulls / evaluates / saves (bounded by ``maxEvals``), trainers
+    run epochs of mini-batches; nobody stops serving its shard before everybody is done."""
+    opt = tr.opt
+    out = {"acc": [], "loss": [], "steps": 0, "seconds": 0.0}
+    t_run = time.perf_counter()
+    if is_tester:
+        for _ in range(opt.get("maxEvals", 3)):
+            t0 = time.perf_counter()
+            tr.pull_params()
+            print(f"Client {tr.rank}: communication time: {time.perf_counter() - t0:.4f} ")
+            out["acc"].append(tr.test3())
+            if opt["outputprefix"] != "none":
+                tr.save(opt["outputprefix"])
+            time.sleep(opt["validSleepTime"])
+    else:
+        n = len(tr.c.train)
+        B = opt["batchSize"]
+        prev = tr.loss_stats()
+        for epoch in range(1, opt["epoch"] + 1):
+            t0 = time.perf_counter()
+            shuffle = torch.randperm(n).tolist()
+            for t in range(0, n, B):
+                tr.train_step(shuffle[t:t + B])
+                if also_test and tr.steps % opt.get("testEvery", 50) == 0:
+                    tr.pull_params()
+                    out["acc"].append(tr.test3())
+            torch.cuda.synchronize(tr.dev)
+            cur = tr.loss_stats()
+            steps = max(1, cur["steps"] - prev["steps"])
+            f = (cur["hinge"] - prev["hinge"] + cur["l1"] - prev["l1"] + cur["l2"] - prev["l2"]) / steps
+            out["loss"].append(f)
+            prev = cur
+            print(f"client {tr.rank}: epoch {epoch} done,  for {time.perf_counter() - t0} seconds , "
+                  f"training loss avg. : {f:.5f} ")
+        out["steps"] = tr.steps
+    out["seconds"] = time.perf_counter() - t_run
+    print("Before Stop !!!!!!!!!!!!!!!!!!!!!!!!!!!!!!!!!!!!!!!")
+    torch.cuda.synchronize(tr.dev)
+    if barrier is not None:
+        barrier()                     # every client's last push is out before any owner stops serving
+    out["drains"] = tr.close()
+    tr.optim.ps.check_timeout()
+    print(tr.rank, "total training time", time.perf_counter() - tr.t_start)
+    return out

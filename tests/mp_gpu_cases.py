@@ -254,10 +254,12 @@ def case_ps_stress(rank, world, dev, heap):
         if rule == "add":
             want = rounds * sum(r + 1 for r in range(world)) * 2.0 ** -10      # exact in fp32
             assert float(x.min()) == want and float(x.max()) == want, (float(x.min()), float(x.max()), want)
-        ps.check_timeout()
+        waits = [None] * world
+        dist.all_gather_object(waits, round(ps.max_wait_us, 1))
         if rank == 0:
             print(f"ps_stress {rule}: n={n} rounds={rounds} seconds per rank {[round(t, 4) for t in times]} "
-                  f"server drains on rank 0: {drains}")
+                  f"server drains on rank 0: {drains}, longest flow-control wait per rank (us): {waits}", flush=True)
+        ps.check_timeout()
         if world >= 4:
             assert min(times) < 0.7 * max(times), ("the fastest rank was held back by the slowest", times)
         sync(dev)
