@@ -126,23 +126,26 @@ class TorchEAMSGD:
         self.t += 1
 
 
-def run(args, rank, world, dev):
+def measure(args, rank, world, dev, blocks: int = 5):
+    """Both arms of the library baseline, timed exactly like the product arm in bench.py: `blocks` back-to-back blocks
+    of `steps` steps each (median block reported); the end-to-end arm takes its batches from the same native loader
+    thread and reads the loss of step t-2 every step, i.e. the same host-side rules as CifarTrainer.train_step."""
+    import statistics
     B = args.batch
     from mpit_b200.workloads.cifar import synthetic_cifar
-    from mpit_b200.models.cifar_cnn import random_crop_offsets
+    from mpit_b200.data.loader import BatchLoader
     tr = TorchEAMSGD(dev, world, rank, B, su=args.tau, mva=0.9 / world, graphs=not args.no_graphs)
     n_host = 64 * B
     hx, hy = synthetic_cifar(n_host, seed=100 + rank)
-    hy = hy.long().pin_memory()
     n_dev = 352
     dx = torch.randint(0, 256, (n_dev, B, 3, 32, 32), dtype=torch.uint8, device=dev)
     dy = torch.randint(0, 10, (n_dev, B), dtype=torch.int64, device=dev)
     dc = torch.randint(0, 5, (n_dev, B, 2), dtype=torch.int64, device=dev)
-    gen = torch.Generator().manual_seed(7 + rank)
-    sx = torch.empty(B, 3, 32, 32, dtype=torch.uint8).pin_memory()
-    sy = torch.empty(B, dtype=torch.int64).pin_memory()
-    sc = torch.empty(B, 2, dtype=torch.int64).pin_memory()
-    loss_host = torch.zeros(1).pin_memory()
+    loader = BatchLoader(hx, hy, B, nslots=4, crop_range=5, seed=7 + rank)
+    LAG = 2
+    loss_host = torch.zeros(LAG + 1).pin_memory()
+    loss_evt = [torch.cuda.Event() for _ in range(LAG + 1)]
+    state = {"k": 0, "last": float("nan")}
 
     def barrier():
         torch.cuda.synchronize()
@@ -156,51 +159,70 @@ def run(args, rank, world, dev):
         tr.step()
 
     def e2e_step(i):
-        lo = (i * B) % n_host
-        sx.copy_(hx[lo:lo + B])
-        sy.copy_(hy[lo:lo + B])
-        sc.copy_(random_crop_offsets(B, gen).long())
-        tr.set_batch(sx, sy, sc)
+        x, y, c = loader.next()                      # pinned slot filled by the loader thread
+        tr.set_batch(x, y, c)                        # host -> device copy of this step's inputs
         tr.step()
-        loss_host.copy_(tr.loss.view(1), non_blocking=False)     # device -> host read of the step's loss
-        return float(loss_host)
+        k = state["k"]
+        slot = k % (LAG + 1)
+        loss_host[slot:slot + 1].copy_(tr.loss.view(1), non_blocking=True)     # device -> host copy of the loss
+        loss_evt[slot].record()
+        state["k"] = k + 1
+        if k >= LAG:                                 # the host reads the loss of step k-LAG every step
+            old = (k - LAG) % (LAG + 1)
+            loss_evt[old].synchronize()
+            state["last"] = float(loss_host[old])
+        return state["last"]
 
     for i in range(max(args.warmup, 3 * args.tau + 3)):
         dev_step(i)
     barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(args.steps):
-        dev_step(i)
-    e1.record()
-    barrier()
-    ms = e0.elapsed_time(e1)
+    dev_ms, e2e_ms = [], []
+    for b in range(blocks):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record()
+        for i in range(args.steps):
+            dev_step(b * args.steps + i)
+        e1.record()
+        barrier()
+        dev_ms.append(e0.elapsed_time(e1))
     for i in range(5):
         e2e_step(i)
-    barrier()
-    t0 = time.perf_counter()
-    for i in range(args.steps):
-        last = e2e_step(i)
-    barrier()
-    e2e_s = time.perf_counter() - t0
-    t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    for b in range(blocks):
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(args.steps):
+            last = e2e_step(i)
+        barrier()
+        e2e_ms.append((time.perf_counter() - t0) * 1e3)
+    t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
     if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)          # per block: the slowest rank
+    dms, ems = statistics.median(t[0].tolist()), statistics.median(t[1].tolist())
+    gb = B * world
+    return {"value": gb * args.steps / (dms / 1e3), "e2e": gb * args.steps / (ems / 1e3), "ms_per_step": dms / args.steps,
+            "e2e_ms_per_step": ems / args.steps, "blocks_ms": [round(v, 4) for v in t[0].tolist()], "loss": last,
+            "h2d_bytes_per_step": int(3 * 32 * 32 * B + 4 * B + 8 * B), "d2h_bytes_per_step": 4}
+
+
+def run(args, rank, world, dev):
+    B = args.batch
+    m = measure(args, rank, world, dev)
     gb = B * world
     if rank == 0:
         print(json.dumps({
             "metric": "samples/sec (device-timed, max over ranks) CIFAR-10 CNN EAMSGD tau=10",
-            "value": round(gb * args.steps / (float(t[0]) / 1e3), 1), "unit": "samples/s", "n_gpus": world,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(float(t[0]) / args.steps, 5),
+            "value": round(m["value"], 1), "unit": "samples/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(m["ms_per_step"], 5),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "tf32 (cuDNN/cuBLAS allow_tf32)",
             "data": "synthetic CIFAR-10-shaped uint8 images, random-init weights", "impl": "torch",
             "config": {"model": "CIFAR-10 7-layer CNN", "global_batch": gb, "per_gpu_batch": B, "optimizer": "eamsgd",
                        "tau": args.tau, "parallelism": f"sync-elastic dp{world} via NCCL all_gather/reduce_scatter",
-                       "cuda_graphs": not args.no_graphs},
-            "e2e": {"value": round(gb * args.steps / (float(t[1]) / 1e3), 1), "unit": "samples/s",
-                    "ms_per_step": round(float(t[1]) / args.steps, 5), "h2d_bytes_per_step": int(sx.numel() + 8 * B + 16 * B),
-                    "d2h_bytes_per_step": 4},
-            "gpu_launches": 0, "loss": round(last, 4)}))
+                       "cuda_graphs": not args.no_graphs, "timing": "median of 5 blocks of `steps` steps"},
+            "e2e": {"value": round(m["e2e"], 1), "unit": "samples/s", "ms_per_step": round(m["e2e_ms_per_step"], 5),
+                    "h2d_bytes_per_step": m["h2d_bytes_per_step"], "d2h_bytes_per_step": 4,
+                    "loader": "native worker thread, pinned ring", "d2h": "loss copied every step, read 2 steps late"},
+            "gpu_launches": 0, "loss": round(m["loss"], 4)}))
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

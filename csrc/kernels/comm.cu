@@ -100,7 +100,7 @@ __device__ __forceinline__ void peer_red4(float* p, int cnt, const float (&r)[4]
   }
 }
 
-enum ExchMode : int { EX_PULL = 0, EX_PUT = 1, EX_PUSH = 2, EX_ELASTIC = 3, EX_FUSED = 4 };
+enum ExchMode : int { EX_PULL = 0, EX_PUT = 1, EX_PUSH = 2, EX_ELASTIC = 3, EX_FUSED = 4, EX_DOWNPOUR = 5 };
 
 struct ExchArgs {
   PeerTable tab;
@@ -163,6 +163,48 @@ __global__ void __launch_bounds__(256) exchange_kernel(ExchArgs a) {
       if (a.zero_src) {
         float z[4] = {0.f, 0.f, 0.f, 0.f};
         store4(a.src, i0, cnt, z);
+      }
+    } else if (MODE == EX_DOWNPOUR) {
+      // Downpour step boundary in one pass (optim-downpour.lua:24-54): g' = -lr (g + l2wd x); acc += g';
+      // sync step: centre += acc on the owner and x = the centre right after that addition (the push followed
+      // by the pull, one NVLink round trip: the accumulate returns the value it found), acc = 0;
+      // otherwise the worker moves on its own, x += g'.  Operand copies refreshed in the same pass.
+      float x[4], acc[4], g[4];
+      load4(a.x, i0, cnt, x);
+      load4(a.src, i0, cnt, acc);
+      if (a.gmap) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) g[k] = k < cnt ? a.g[a.gmap[i0 + k]] : 0.f;
+      } else {
+        load4(a.g, i0, cnt, g);
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        float gk = g[k];
+        if (a.l2wd != 0.f) gk = add_rn(gk, mul_rn(a.l2wd, x[k]));
+        g[k] = mul_rn(gk, a.clr);                 // clr = -lr
+        acc[k] = add_rn(acc[k], g[k]);
+      }
+      if (a.do_sync) {
+        float old[4] = {0.f, 0.f, 0.f, 0.f};
+        if (cnt == 4) {
+          float4 o = atom_add_sys4(cptr, make_float4(acc[0], acc[1], acc[2], acc[3]));
+          old[0] = o.x; old[1] = o.y; old[2] = o.z; old[3] = o.w;
+        } else {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) if (k < cnt) old[k] = atom_add_sys(cptr + k, acc[k]);
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { x[k] = add_rn(old[k], acc[k]); acc[k] = 0.f; }
+      } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) x[k] = add_rn(x[k], g[k]);
+      }
+      store4(a.x, i0, cnt, x);
+      store4(a.src, i0, cnt, acc);
+      if (a.wpk) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) if (k < cnt) pack_store(a.wpk, a.wmap, a.nmaps, a.n, i0 + k, x[k]);
       }
     } else {
       // EX_ELASTIC / EX_FUSED
@@ -429,6 +471,22 @@ int mpit_eamsgd_fused_step(const unsigned long long* shard_ptrs, int nranks, int
   a.do_apply = do_apply; a.use_mom = use_mom; a.do_lookahead = do_lookahead; a.do_sync = do_sync;
   a.has_d_in = has_d_in;
   exchange_kernel<EX_FUSED><<<exch_grid(a.walk), 256, 0, (cudaStream_t)stream>>>(a);
+  MPIT_LAUNCH_CHECK();
+  return 0;
+}
+
+/* Downpour step boundary (optim-downpour.lua:24-54) in one kernel: see EX_DOWNPOUR. */
+int mpit_downpour_fused_step(const unsigned long long* shard_ptrs, int nranks, int rank, float* x, float* acc,
+                             const float* g, const int* gmap, float* wpk, const int* wmap, int nmaps, long long n,
+                             float neg_lr, float l2wd, int do_sync, void* stream) {
+  if (n <= 0) return 0;
+  if (nranks < 1 || nranks > MPIT_MAX_RANKS || !x || !acc || !g) return MPIT_E_ARG;
+  ExchArgs a{};
+  a.tab = make_table(shard_ptrs, 0, nranks, rank);
+  a.walk = QuadWalk::make(n, nranks, rank);
+  a.x = x; a.src = acc; a.g = g; a.gmap = gmap; a.wpk = wpk; a.wmap = wmap; a.nmaps = nmaps; a.n = n;
+  a.clr = neg_lr; a.l2wd = l2wd; a.do_sync = do_sync;
+  exchange_kernel<EX_DOWNPOUR><<<exch_grid(a.walk), 256, 0, (cudaStream_t)stream>>>(a);
   MPIT_LAUNCH_CHECK();
   return 0;
 }

@@ -75,6 +75,21 @@ __device__ __forceinline__ void red_add_sys4(float* p, const float4& v) {
                "f"(v.z), "f"(v.w) : "memory");
 }
 
+// Accumulate that also returns what was there before (MPI_Get_accumulate / Fetch_and_op SUM): one NVLink round trip
+// gives the owner's value including nothing but what arrived before this addition.
+__device__ __forceinline__ float atom_add_sys(float* p, float v) {
+  float old;
+  asm volatile("atom.relaxed.sys.global.add.f32 %0, [%1], %2;" : "=f"(old) : "l"(p), "f"(v) : "memory");
+  return old;
+}
+__device__ __forceinline__ float4 atom_add_sys4(float* p, const float4& v) {
+  float4 old;
+  asm volatile("atom.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4], {%5,%6,%7,%8};"
+               : "=f"(old.x), "=f"(old.y), "=f"(old.z), "=f"(old.w)
+               : "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+  return old;
+}
+
 // ---- NVLS multimem accessors (valid only on a multicast mapping) ---------------------------
 __device__ __forceinline__ float4 multimem_ld_reduce_add4(const float* mc) {
   float4 v;

@@ -154,6 +154,22 @@ int mpit_allreduce(const unsigned long long* in_ptrs, unsigned long long in_mc,
                    const unsigned long long* sig_ptrs, const unsigned long long* flag_ptrs, int nranks, int rank,
                    float* local_out, float* x_elastic, long long n, float scale, float alpha, int algo,
                    int max_blocks, void* stream);
+/* The whole Downpour step boundary in one pass (optim-downpour.lua:24-54): g' = neg_lr (g + l2wd x); acc += g';
+ * do_sync: centre += acc on the owners (accumulate that returns the previous value), x = that value + acc (push
+ * followed by pull), acc = 0; otherwise x += g'.  Refreshes the packed operand copy. */
+int mpit_downpour_fused_step(const unsigned long long* shard_ptrs, int nranks, int rank, float* x, float* acc,
+                             const float* g, const int* gmap, float* wpk, const int* wmap, int nmaps, long long n,
+                             float neg_lr, float l2wd, int do_sync, void* stream);
+/* Boundary of a synchronous-EASGD step in ONE kernel: mean over the ranks of the symmetric input (each rank's
+ * parameters after its local update), x -= alpha (x - mean), then the Nesterov look-ahead of the next step
+ * (v *= mom; x += v when v != NULL) and the refresh of the packed operand copy (wpk / wmap as in mpit_local_step).
+ * The all-reduce/average path of asyncsgd/testreduceall.lua:72-77 fused with the elastic update of
+ * optim-eamsgd.lua:62-70. */
+int mpit_sync_easgd_step(const unsigned long long* in_ptrs, unsigned long long in_mc,
+                         const unsigned long long* out_ptrs, unsigned long long out_mc,
+                         const unsigned long long* sig_ptrs, const unsigned long long* flag_ptrs, int nranks, int rank,
+                         float* x, float* v, float* wpk, const int* wmap, int nmaps, long long n, float alpha, float mom,
+                         int algo, int max_blocks, void* stream);
 int mpit_bcast(const unsigned long long* buf_ptrs, unsigned long long buf_mc, const unsigned long long* sig_ptrs,
                int nranks, int rank, int root, long long n, int max_blocks, void* stream);
 int mpit_device_barrier(const unsigned long long* sig_ptrs, int nranks, int rank, void* stream);

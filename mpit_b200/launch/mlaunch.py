@@ -26,7 +26,7 @@ import torch
 def main(argv=None) -> int:
     ap = argparse.ArgumentParser()
     ap.add_argument("--device", default="cuda" if torch.cuda.is_available() else "cpu")
-    ap.add_argument("--optim", default="eamsgd", choices=["eamsgd", "easgd", "downpour"])
+    ap.add_argument("--optim", default="eamsgd", choices=["eamsgd", "easgd", "downpour", "sync_easgd", "sync_eamsgd"])
     ap.add_argument("--model", default="cifar", choices=["cifar", "mnist"])
     ap.add_argument("--su", type=int, default=2)
     ap.add_argument("--lr", type=float, default=None)

@@ -21,7 +21,8 @@ import sys
 
 import torch
 
-NVLINK_GBS = 770.0   # measured peer-copy bandwidth per direction per GPU (B200_PROFILING.md)
+NVLINK_GBS = 770.0        # measured peer-copy bandwidth per direction per GPU (B200_PROFILING.md)
+NVLINK_LINK_GBS = 900.0   # NVLink 5 link bandwidth per direction per GPU: the roofline denominator of BASELINE.json
 
 
 def _cpu(a) -> int:
@@ -119,6 +120,7 @@ def device_sweep(sizes, iters, warmup, ops, nccl, out_path=None, straggler=0):
             sec = timed(fn)
             row = {"op": op, "bytes": 4 * n, "n_gpus": world, "us": round(sec * 1e6, 2),
                    "link_GBs_per_gpu": round(link_bytes / sec / 1e9, 2),
+                   "frac_of_900": round(link_bytes / sec / 1e9 / NVLINK_LINK_GBS, 4) if world > 1 else None,
                    "frac_of_measured_nvlink": round(link_bytes / sec / 1e9 / NVLINK_GBS, 4) if world > 1 else None,
                    "impl": "mpit"}
             results.append(row)
@@ -129,6 +131,7 @@ def device_sweep(sizes, iters, warmup, ops, nccl, out_path=None, straggler=0):
             sec = timed(lambda: dist.all_reduce(buf))
             row = {"op": "allreduce", "bytes": 4 * n, "n_gpus": world, "us": round(sec * 1e6, 2),
                    "link_GBs_per_gpu": round(4 * n * frac / sec / 1e9, 2),
+                   "frac_of_900": round(4 * n * frac / sec / 1e9 / NVLINK_LINK_GBS, 4),
                    "frac_of_measured_nvlink": round(4 * n * frac / sec / 1e9 / NVLINK_GBS, 4), "impl": "nccl"}
             results.append(row)
             if rank == 0:
@@ -139,6 +142,7 @@ def device_sweep(sizes, iters, warmup, ops, nccl, out_path=None, straggler=0):
             sec = timed(lambda: dist.all_gather_into_tensor(full, shard))
             row = {"op": "pull(all_gather)", "bytes": 4 * n, "n_gpus": world, "us": round(sec * 1e6, 2),
                    "link_GBs_per_gpu": round(4 * n * frac / sec / 1e9, 2),
+                   "frac_of_900": round(4 * n * frac / sec / 1e9 / NVLINK_LINK_GBS, 4),
                    "frac_of_measured_nvlink": round(4 * n * frac / sec / 1e9 / NVLINK_GBS, 4), "impl": "nccl"}
             results.append(row)
             if rank == 0:
@@ -146,10 +150,13 @@ def device_sweep(sizes, iters, warmup, ops, nccl, out_path=None, straggler=0):
             sec = timed(lambda: dist.reduce_scatter_tensor(shard, full))
             row = {"op": "push(reduce_scatter)", "bytes": 4 * n, "n_gpus": world, "us": round(sec * 1e6, 2),
                    "link_GBs_per_gpu": round(4 * n * frac / sec / 1e9, 2),
+                   "frac_of_900": round(4 * n * frac / sec / 1e9 / NVLINK_LINK_GBS, 4),
                    "frac_of_measured_nvlink": round(4 * n * frac / sec / 1e9 / NVLINK_GBS, 4), "impl": "nccl"}
             results.append(row)
             if rank == 0:
                 print(json.dumps(row), flush=True)
+        if coll is not None:
+            coll.check_timeout()
         del center, coll
     heap.check_timeout()
     if out_path and rank == 0:

@@ -180,8 +180,64 @@ class DeviceEAMSGD(_DeviceOptBase):
             self.prev_sync = False
 
 
+class DeviceSyncEASGD(_DeviceOptBase):
+    """Synchronous EASGD / EAMSGD: every ``su`` steps all workers meet, the centre is the mean of their parameters and
+    each worker moves toward it, ``x_i -= alpha (x_i - mean)`` -- the all-reduce/average path of
+    asyncsgd/testreduceall.lua:72-77 (MPI_Allreduce, test/testreduceall.lua:28) used as a training path and fused with
+    the elastic update of optim-eamsgd.lua:62-70.
+
+    A sync step is two kernels: the local update of step t-1 (which also drops the parameters into the symmetric
+    input buffer), then ONE kernel that all-reduces over NVLink (NVLS multimem from three ranks up), applies the
+    elastic update, the Nesterov look-ahead of step t and the operand refresh.  Other steps are the single fused
+    boundary kernel of :class:`DeviceMSGD`.  All ranks must step in lock-step."""
+
+    def __init__(self, engine, theta0, heap, *, lr, mva, su=1, mom=0.0, l2wd=0.0, use_graphs=True):
+        super().__init__(engine, theta0, use_graphs)
+        from ..parallel.collectives import DeviceCollectives
+        assert su > 0 and mva > 0
+        self.lr, self.mva, self.su, self.mom, self.l2wd = lr, mva, su, mom, l2wd
+        self.coll = DeviceCollectives(heap, self.n)
+        self.v = torch.zeros_like(self.x) if mom > 0 else None
+        self.engine.load_flat(self.x)
+
+    def _boundary(self, do_apply: bool, do_lookahead: bool, do_sync: bool) -> None:
+        e = self.engine
+        if do_sync:
+            # apply(t-1); the same pass writes x into the symmetric input buffer (identity "operand copy")
+            ops.local_step(self.x, self.v, e.gpk, e.gmap, None, self.coll.inp.local, None, clr=self.lr, l2wd=self.l2wd,
+                           mom_next=0.0, do_apply=do_apply, use_mom=self.mom > 0, do_lookahead=False)
+            self.coll.sync_easgd_step(self.x, self.v if do_lookahead else None, e.wpk, e.wmap, alpha=self.mva,
+                                      mom=self.mom)
+        else:
+            ops.local_step(self.x, self.v, e.gpk, e.gmap, None, e.wpk, e.wmap, clr=self.lr, l2wd=self.l2wd,
+                           mom_next=self.mom, do_apply=do_apply, use_mom=self.mom > 0, do_lookahead=do_lookahead)
+
+    def step(self) -> None:
+        do_apply = self.pending_apply
+        do_sync = self.t % self.su == 0
+
+        def body():
+            self._boundary(do_apply, True, do_sync)
+            self.engine.fwd_bwd()
+
+        self.graphs.run(("step", do_apply, do_sync), body)
+        self.pending_apply = True
+        self.t += 1
+
+    def finalize(self) -> None:
+        if self.pending_apply:
+            self._boundary(True, False, False)
+            self.pending_apply = False
+
+
 class DeviceDownpour(_DeviceOptBase):
-    """Downpour / hogwild SGD against the sharded centre (asyncsgd/optim-downpour.lua:6-60)."""
+    """Downpour / hogwild SGD against the sharded centre (asyncsgd/optim-downpour.lua:6-60).
+
+    After the backward pass ONE kernel finishes the step: ``g' = -lr (g + l2wd x)``, ``acc += g'``; on a sync step
+    (every ``su``-th, step 0 included) the accumulator goes into the owners' shards with a returning accumulate over
+    NVLink and the worker continues from the value found there plus its own contribution (push followed by pull, one
+    round trip), the accumulator is cleared; on the other steps the worker moves on its own.  The tensor-core operand
+    copies are refreshed in the same pass."""
 
     def __init__(self, engine, theta0, center: ShardedCenter, *, lr, su=1, l2wd=0.0, lrd=0.0,
                  seed_center: Optional[bool] = None, use_graphs=True):
@@ -194,19 +250,23 @@ class DeviceDownpour(_DeviceOptBase):
             center.put(self.x)
         self.engine.load_flat(self.x)
 
+    def boundary(self, do_sync: bool, lr: float) -> None:
+        from .._native import kernels, check, ptr, cur_stream
+        e, c = self.engine, self.center
+        wmap = getattr(e, "wmap", None)
+        nmaps = 0 if wmap is None else max(1, int(wmap.numel()) // self.n)
+        check(kernels().mpit_downpour_fused_step(c._ptrs, c.nranks, c.rank, ptr(self.x), ptr(self.acc), ptr(e.gpk),
+                                                 ptr(getattr(e, "gmap", None)), ptr(e.wpk), ptr(wmap), nmaps, self.n,
+                                                 -lr, self.l2wd, int(do_sync), cur_stream()),
+              "mpit_downpour_fused_step")
+
     def step(self) -> None:
-        e = self.engine
         lr = self.lr / (1 + self.t * self.lrd) if self.lrd != 0 else self.lr
         do_sync = self.t % self.su == 0
 
         def body():
-            e.fwd_bwd()
-            # acc += -lr (g + l2wd x); between syncs also move locally
-            ops.downpour_accum(self.x, self.acc, e.gpk, e.gmap, e.wpk, e.wmap, lr=lr, l2wd=self.l2wd,
-                               move_local=not do_sync)
-            if do_sync:
-                self.center.push_add(self.acc, zero_src=True)   # centre += acc ; acc = 0
-                self.center.pull(self.x, e.wpk, e.wmap)          # x = centre (overwrites), refresh operands
+            self.engine.fwd_bwd()
+            self.boundary(do_sync, lr)
 
         self.graphs.run(("step", do_sync), body)
         self.t += 1

@@ -8,6 +8,7 @@ asyncsgd/testreduceall.lua:76), MPI_Bcast (wrapped only, mpifuncs.c:145), MPI_Se
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Optional
 
 import torch
@@ -73,11 +74,38 @@ class DeviceCollectives:
         scale = 1.0 / self.nranks if average else 1.0
         two = algo == "twoshot"
         local_out = None if two else self.out.local
-        check(self.k.mpit_allreduce(self._in_ptrs, self.inp.mc_ptr, self._out_ptrs if two else None,
-                                    self.out.mc_ptr if two else 0, self._sig_ptrs, self._flag_ptrs, self.nranks,
+        # NVLS (multimem) pays from three ranks up and for the bandwidth algorithm only: measured on B200, 256 MiB
+        # two-shot 624 us with multimem vs 771 us with peer loads on 8 GPUs but 700 vs 445 us on 2, and the 1 MiB
+        # one-shot 105 us with multimem vs 50 us with peer loads on 8 GPUs (profiles/ar_tune_n8_r2_first.jsonl)
+        use_mc = self._use_mc(two)
+        check(self.k.mpit_allreduce(self._in_ptrs, self.inp.mc_ptr if use_mc else 0, self._out_ptrs if two else None,
+                                    self.out.mc_ptr if (two and use_mc) else 0, self._sig_ptrs, self._flag_ptrs, self.nranks,
                                     self.rank, ptr(local_out), ptr(elastic_x), n, scale, alpha, 1 if two else 0,
                                     max_blocks, cur_stream()), "mpit_allreduce")
         return self.out.local[:n]
+
+    def _use_mc(self, two: bool) -> bool:
+        use_mc = two and self.nranks > 2
+        if os.environ.get("MPIT_AR_MC") in ("0", "1"):
+            use_mc = os.environ["MPIT_AR_MC"] == "1"
+        return bool(use_mc and self.inp.mc_ptr != 0 and self.out.mc_ptr != 0)
+
+    def sync_easgd_step(self, x: torch.Tensor, v: Optional[torch.Tensor], wpk, wmap, *, alpha: float, mom: float = 0.0,
+                        algo: Optional[str] = None, max_blocks: int = 0) -> None:
+        """Boundary of a synchronous-EASGD step in one kernel: ``inp.local[:n]`` holds this rank's parameters after
+        its local update (every rank wrote its own); computes the mean over ranks, ``x -= alpha (x - mean)``, the
+        Nesterov look-ahead ``v *= mom; x += v`` (when ``v`` is given) and refreshes the operand copy ``wpk``."""
+        n = x.numel()
+        assert n <= self.capacity
+        if algo is None:
+            algo = "oneshot" if n <= self.ONE_SHOT_MAX else "twoshot"
+        two = algo == "twoshot"
+        mc = self._use_mc(two)
+        nmaps = 0 if wmap is None else max(1, int(wmap.numel()) // n)
+        check(self.k.mpit_sync_easgd_step(self._in_ptrs, self.inp.mc_ptr if mc else 0, self._out_ptrs if two else None,
+                                          self.out.mc_ptr if (two and mc) else 0, self._sig_ptrs, self._flag_ptrs,
+                                          self.nranks, self.rank, ptr(x), ptr(v), ptr(wpk), ptr(wmap), nmaps, n, alpha,
+                                          mom, 1 if two else 0, max_blocks, cur_stream()), "mpit_sync_easgd_step")
 
     def iallreduce(self, x: torch.Tensor, **kw) -> DeviceRequest:
         """MPI_Iallreduce: the same kernel on a side stream; Request = CUDA event."""

@@ -21,7 +21,7 @@ import torch
 
 from ..models.cifar_cnn import (CifarEngine, TorchCifarCNN, flat_from_torch, random_crop_offsets,
                                 center_crop_offsets, NUM_CLASSES, IMG, CROP)
-from ..optim.device import DeviceMSGD, DeviceEAMSGD, DeviceDownpour, DeviceRule
+from ..optim.device import DeviceMSGD, DeviceEAMSGD, DeviceDownpour, DeviceRule, DeviceSyncEASGD
 from ..parallel.center import ShardedCenter
 from ..parallel.symm import SymmetricHeap
 
@@ -29,7 +29,7 @@ from ..parallel.symm import SymmetricHeap
 @dataclass
 class CifarOpts:
     """Mirror of the ``opt`` table of goot.lua:6-21 plus launcher settings (mlaunch.lua:48-67)."""
-    name: str = "eamsgd"          # sgd | downpour | eamsgd | easgd | adam/adamax/adagrad/adadelta/rmsprop-single
+    name: str = "eamsgd"          # sgd | downpour | eamsgd | easgd | sync_easgd | sync_eamsgd | <rule>single
     lr: float = 1e-2
     mom: float = 0.99
     mb: int = 128
@@ -105,6 +105,8 @@ class CifarTrainer:
         self.center: Optional[ShardedCenter] = None
         name = opts.name
         n = theta0.numel()
+        if name in ("sync_easgd", "sync_eamsgd") and heap is None:
+            self.heap = heap = SymmetricHeap(self.dev)
         if name in ("eamsgd", "easgd", "downpour"):
             if heap is None:
                 self.heap = heap = SymmetricHeap(self.dev)
@@ -115,6 +117,11 @@ class CifarTrainer:
             self.opt = DeviceEAMSGD(self.engine, theta0, self.center, lr=opts.lr, mva=mva, su=opts.su,
                                     mom=0.0 if name == "easgd" else opts.mom, l2wd=opts.l2wd, lrd=opts.lrd,
                                     lrp=opts.lrp, use_graphs=opts.use_graphs)
+        elif name in ("sync_easgd", "sync_eamsgd"):
+            mva = opts.mva if opts.mva > 0 else 0.9
+            self.opt = DeviceSyncEASGD(self.engine, theta0, heap, lr=opts.lr, mva=mva, su=opts.su,
+                                       mom=0.0 if name == "sync_easgd" else opts.mom, l2wd=opts.l2wd,
+                                       use_graphs=opts.use_graphs)
         elif name == "downpour":
             self.opt = DeviceDownpour(self.engine, theta0, self.center, lr=opts.lr, su=opts.su, l2wd=opts.l2wd,
                                       lrd=opts.lrd, use_graphs=opts.use_graphs)

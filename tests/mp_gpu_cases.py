@@ -265,6 +265,60 @@ def case_ps_stress(rank, world, dev, heap):
         sync(dev)
 
 
+def case_sync_easgd(rank, world, dev, heap):
+    """Synchronous EASGD/EAMSGD as a training path: local Nesterov steps, and every su-th step ONE kernel that
+    all-reduces the workers' parameters, applies x -= alpha (x - mean), the look-ahead and the operand refresh.
+    Oracle: every rank replays all ranks' trajectories on the CPU (gradients are a fixed function of rank and step)."""
+    from mpit_b200.optim.device import DeviceSyncEASGD
+    for n, mom in ((10007, 0.9), (351946, 0.0)):          # one-shot and two-shot sizes, EAMSGD and EASGD
+        steps, su, lr, alpha = 7, 3, 0.05, 0.4
+        grad = lambda r, t: torch.randn(n, generator=torch.Generator().manual_seed(7000 + 100 * r + t)) * 0.1
+
+        class Eng:
+            def __init__(self):
+                self.wpk = torch.zeros(n, device=dev)
+                self.gpk = torch.zeros(n, device=dev)
+                self.gmap = None
+                self.wmap = None
+                self.t = 0
+
+            def load_flat(self, x):
+                self.wpk.copy_(x)
+
+            def fwd_bwd(self):
+                self.gpk.copy_(grad(rank, self.t))
+                self.t += 1
+
+        theta0 = [torch.linspace(-1, 1, n) * (1 + 0.1 * r) for r in range(world)]
+        eng = Eng()
+        opt = DeviceSyncEASGD(eng, theta0[rank], heap, lr=lr, mva=alpha, su=su, mom=mom, use_graphs=False)
+        sync(dev)
+        f32 = lambda v: torch.tensor(v, dtype=torch.float32)
+        xs = [t.clone() for t in theta0]
+        vs = [torch.zeros(n) for _ in range(world)]
+        for t in range(steps):
+            opt.step()
+            # boundary of step t: apply(t-1) happened at the start of this step; then sync or look-ahead
+            for r in range(world):
+                if t > 0:
+                    d = grad(r, t - 1) * f32(-lr)
+                    xs[r] = xs[r] + d
+                    if mom > 0:
+                        vs[r] = vs[r] + d
+            if t % su == 0:
+                mean = sum(xs) * f32(1.0 / world)
+                xs = [x - (x - mean) * f32(alpha) for x in xs]
+            if mom > 0:
+                for r in range(world):
+                    vs[r] = vs[r] * f32(mom)
+                    xs[r] = xs[r] + vs[r]
+            torch.cuda.synchronize()
+            got = eng.wpk.cpu()              # the operand copy holds the look-ahead point of step t
+            assert torch.allclose(got, xs[rank], rtol=1e-5, atol=1e-6), (n, t, float((got - xs[rank]).abs().max()))
+        opt.coll.check_timeout()
+        sync(dev)
+
+
 def case_pulled_linear(rank, world, dev, heap):
     """Pull fused with the consuming GEMM: weights stay sharded; every rank's GEMM reads them over NVLink."""
     from mpit_b200.ops.pulled_linear import PulledLinear

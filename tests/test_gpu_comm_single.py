@@ -188,3 +188,53 @@ def test_centre_checkpoint_roundtrip(tmp_path):
     for c in cs:
         c.load(path)
     assert torch.equal(_center_as_flat(cs, n), theta)
+
+
+@pytest.mark.parametrize("su,l2wd", [(1, 0.0), (3, 0.0), (2, 1e-3)])
+def test_downpour_fused_boundary_matches_reference_bitwise(su, l2wd):
+    """One worker against a 3-shard centre: the single boundary kernel (accumulate, returning NVLink accumulate,
+    continue from the owner's value) reproduces optim-downpour.lua:24-54 driven through a one-server restatement
+    (push p += g', then pull) bit for bit."""
+    from mpit_b200.optim.device import DeviceDownpour
+    n, S, steps, lr = 10007, 3, 7, 0.05
+    cs = _centers(n, S)
+    grads = [torch.randn(n, generator=torch.Generator().manual_seed(50 + t)) * 0.1 for t in range(steps)]
+
+    class Eng:
+        def __init__(self):
+            self.wpk = torch.zeros(n, device="cuda")
+            self.gpk = torch.zeros(n, device="cuda")
+            self.gmap = None
+            self.wmap = None
+            self.t = 0
+
+        def load_flat(self, x):
+            self.wpk.copy_(x)
+
+        def fwd_bwd(self):
+            self.gpk.copy_(grads[self.t])
+            self.t += 1
+
+    theta0 = torch.linspace(-1, 1, n)
+    opt = DeviceDownpour(Eng(), theta0, cs[1], lr=lr, su=su, l2wd=l2wd, seed_center=True, use_graphs=False)
+    # restatement (reference.py downpour with a server that adds and returns the parameters)
+    w, centre, acc = theta0.clone(), theta0.clone(), torch.zeros(n)
+    f32 = lambda v: torch.tensor(v, dtype=torch.float32)
+    for t in range(steps):
+        opt.step()
+        g = grads[t].clone()
+        if l2wd != 0:
+            g = g + w * f32(l2wd)
+        g = g * f32(-lr)
+        acc = acc + g
+        if t % su == 0:
+            centre = centre + acc
+            w = centre.clone()
+            acc.zero_()
+        else:
+            w = w + g
+    torch.cuda.synchronize()
+    assert torch.equal(opt.x.cpu(), w)
+    assert torch.equal(_center_as_flat(cs, n).cpu(), centre)
+    assert torch.equal(opt.engine.wpk.cpu(), w), "operand copy refreshed in the same pass"
+    assert torch.equal(opt.acc.cpu(), acc)

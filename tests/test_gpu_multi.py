@@ -46,6 +46,12 @@ def test_async_parameter_server_under_rank_skew():
     assert "case ps_stress: ok" in out
 
 
+def test_sync_easgd_allreduce_fused_with_elastic_step():
+    n = min(torch.cuda.device_count(), 8)
+    out = _torchrun(["sync_easgd"], n)
+    assert "case sync_easgd: ok" in out
+
+
 def test_pull_fused_with_consumer_gemm():
     n = min(torch.cuda.device_count(), 8)
     out = _torchrun(["pulled_linear"], n)
