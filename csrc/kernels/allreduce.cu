@@ -334,6 +334,7 @@ static int allreduce_impl(const unsigned long long* in_ptrs, unsigned long long 
     const long long owned = (nchunks + nranks - 1) / nranks;
     const int full = 2 * MPIT_NUM_SMS;
     int cap = max_blocks > 0 ? (max_blocks < full ? max_blocks : full) : (mc ? 32 : (x_elastic ? full * 5 / 8 : full));
+    if (x_elastic && cap > full * 3 / 4) cap = full * 3 / 4;      // the tail needs CTAs of its own
     int nred = (int)(owned < cap ? owned : cap);
     if (nred < 1) nred = 1;
     int grid = nred;

@@ -298,58 +298,6 @@ __global__ void __launch_bounds__(512) bcast_kernel(ArArgs a, int root) {
 
 __global__ void barrier_kernel(SignalTable sig) { block_barrier_sys(sig, blockIdx.x); }
 
-// ---------------------------------------------------------------------------------------
-// Device mailbox: two-sided tagged messages as put + flag (MPI_Send/Recv latency path,
-// /root/reference/test.lua:32-38).  One slot per (src -> dst) pair in the receiver's memory:
-//   header {seq, tag, count, state} then payload.
-// ---------------------------------------------------------------------------------------
-struct MailboxSlot {
-  uint32_t seq;      // written last with release: message number, 0 = empty
-  uint32_t tag;
-  uint32_t count;    // floats
-  uint32_t ack;      // consumer writes seq here when it has copied the payload out
-};
-
-__global__ void __launch_bounds__(256)
-mailbox_put_kernel(float* slot_base, const float* payload, uint32_t count, uint32_t tag, uint32_t seq) {
-  MailboxSlot* hdr = reinterpret_cast<MailboxSlot*>(slot_base);
-  float* body = slot_base + 8;
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
-    st_sys(body + i, payload[i]);
-  __threadfence_system();
-  __syncthreads();
-  // single-CTA launches only (latency path): the last thread publishes
-  if (threadIdx.x == 0 && blockIdx.x == 0) {
-    st_sys(reinterpret_cast<float*>(&hdr->tag), __uint_as_float(tag));
-    st_sys(reinterpret_cast<float*>(&hdr->count), __uint_as_float(count));
-    st_release_sys_u32(&hdr->seq, seq);
-  }
-}
-
-// Copies the payload out if message `seq` with a matching tag has arrived; result[0] = 1 if so,
-// 0 if not yet (MPI_Iprobe + MPI_Recv in one); result[1] = count, result[2] = tag.
-__global__ void __launch_bounds__(256)
-mailbox_recv_kernel(float* slot_base, float* dst, uint32_t max_count, int tag, uint32_t seq, int* result) {
-  MailboxSlot* hdr = reinterpret_cast<MailboxSlot*>(slot_base);
-  __shared__ uint32_t s_ok, s_count;
-  if (threadIdx.x == 0) {
-    uint32_t got = ld_acquire_sys_u32(&hdr->seq);
-    uint32_t t = hdr->tag;
-    bool ok = (got == seq) && (tag < 0 || t == (uint32_t)tag);
-    s_ok = ok ? 1u : 0u;
-    s_count = ok ? (hdr->count < max_count ? hdr->count : max_count) : 0u;
-    result[0] = ok ? 1 : 0;
-    result[1] = (int)hdr->count;
-    result[2] = (int)t;
-  }
-  __syncthreads();
-  if (!s_ok) return;
-  const float* body = slot_base + 8;
-  for (uint32_t i = threadIdx.x; i < s_count; i += blockDim.x) dst[i] = body[i];
-  __syncthreads();
-  if (threadIdx.x == 0) st_release_sys_u32(&hdr->ack, seq);
-}
-
 static PeerTable make_table(const unsigned long long* ptrs, unsigned long long mc, int nranks, int rank) {
   PeerTable t{};
   for (int i = 0; i < MPIT_MAX_RANKS; ++i) t.peer[i] = i < nranks ? reinterpret_cast<float*>(ptrs[i]) : nullptr;
@@ -523,20 +471,6 @@ int mpit_peer_rma(int op, float* remote, float* local, long long n, float scale,
   if (op < RMA_PUT || op > RMA_ACC || !remote || !local) return MPIT_E_ARG;
   if (n <= 0) return 0;
   peer_rma_kernel<<<ew_grid(n, 256, 8), 256, 0, (cudaStream_t)stream>>>(op, remote, local, n, scale);
-  MPIT_LAUNCH_CHECK();
-  return 0;
-}
-
-int mpit_mailbox_put(float* slot_base, const float* payload, unsigned count, unsigned tag, unsigned seq,
-                     void* stream) {
-  mailbox_put_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(slot_base, payload, count, tag, seq);
-  MPIT_LAUNCH_CHECK();
-  return 0;
-}
-
-int mpit_mailbox_recv(float* slot_base, float* dst, unsigned max_count, int tag, unsigned seq, int* result3,
-                      void* stream) {
-  mailbox_recv_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(slot_base, dst, max_count, tag, seq, result3);
   MPIT_LAUNCH_CHECK();
   return 0;
 }

@@ -177,13 +177,6 @@ int mpit_device_barrier(const unsigned long long* sig_ptrs, int nranks, int rank
  * /root/reference/mpifuncs.c:1656,1131,9): op 0 remote[i] = scale*local[i], 1 local[i] = remote[i],
  * 2 remote[i] += scale*local[i] (red.add, fire and forget).  `remote` = peer base + displacement. */
 int mpit_peer_rma(int op, float* remote, float* local, long long n, float scale, void* stream);
-/* Device mailbox (MPI_Send/Recv latency path, /root/reference/test.lua:32-38). A slot is 8 header
- * floats + payload in the receiver's symmetric memory. result3 = {arrived, count, tag}. */
-int mpit_mailbox_put(float* slot_base, const float* payload, unsigned count, unsigned tag, unsigned seq,
-                     void* stream);
-int mpit_mailbox_recv(float* slot_base, float* dst, unsigned max_count, int tag, unsigned seq, int* result3,
-                      void* stream);
-
 /* ---- asynchronous parameter server with server-side rules (csrc/kernels/ps_async.cu) ----------------
  * Device path of BiCNN/pserver.lua:115-205 + BiCNN/optim-{adam,adamax,adagrad,adadelta,rmsprop}.lua: every rank is
  * a client and the owner of one shard.  Symmetric buffers: `ctl` (mpit_ps_ctl_words() uint32, zeroed), `slots`
@@ -208,6 +201,29 @@ int mpit_ps_server_start(int dev, const unsigned long long* ctl_ptrs, int nranks
                          const double* hyper10, float* p, float* s0, float* s1, float* s2, const float* slots,
                          long long cap, long long size, int interval_us, void** out_handle);
 int mpit_ps_server_stop(void* handle, long long* rounds_out);
+
+/* ---- device transport of the message layer (csrc/kernels/mailbox.cu) --------------------------------------
+ * Two-sided tagged messages between GPUs behind mpiT.Send/Recv/Isend/Irecv/Iprobe/Test/Wait/Cancel for CUDA tensors
+ * (/root/reference/lua-mpi.h:70-78 hands the device pointer to MPI; /root/reference/init.lua:41-108 polls
+ * Iprobe/Test).  Payloads move GPU to GPU (eager: into a slot of the receiver's symmetric memory; rendezvous: the
+ * receiver pulls from the sender's tensor through CUDA IPC); 128-byte descriptors live in a POSIX shared-memory
+ * segment registered with CUDA, ring layout [dst][src][K]: the sender's GPU publishes `seq` in stream order, all
+ * probing / matching / cancelling / acknowledging is CPU atomics on the same words.  See mpit_b200/msg/device.py. */
+int mpit_mbx_desc_bytes(void);
+int mpit_shm_map(const char* name, long long bytes, int create, void** host_ptr, void** dev_ptr);
+int mpit_shm_unmap(const char* name, void* host_ptr, long long bytes, int unlink_it);
+int mpit_mbx_copy(void* dst, const void* src, long long nbytes, void* stream);
+int mpit_mbx_publish(void* desc_dev, unsigned seq, void* stream);
+int mpit_mbx_fill(void* desc_host, int tag, long long nbytes, int kind, unsigned long long rv_offset,
+                  const void* ipc64);
+int mpit_mbx_publish_host(void* desc_host, unsigned seq);
+int mpit_mbx_word(const void* desc_host, int which);
+int mpit_mbx_set_done(void* desc_host, unsigned seq);
+int mpit_mbx_cas_state(void* desc_host, unsigned expect, unsigned val);
+int mpit_mbx_scan(const void* ring, int nsrc, int K, const unsigned* base, const unsigned long long* mask,
+                  int want_src, int want_tag, int start_src, int* out5, long long* out_bytes);
+int mpit_mbx_desc_info(const void* desc_host, unsigned long long* rv_offset, void* ipc64);
+int mpit_ipc_export_range(unsigned long long ptr, void* handle64, unsigned long long* offset);
 
 /* ---- symmetric heap (csrc/symm/symm_heap.cu) --------------------------------------------- */
 /* Takes the place of the reference's CUDA-aware-MPI pointer bridge (/root/reference/lua-mpi.h:70-78).

@@ -25,18 +25,29 @@ NVLINK_GBS = 770.0        # measured peer-copy bandwidth per direction per GPU (
 NVLINK_LINK_GBS = 900.0   # NVLink 5 link bandwidth per direction per GPU: the roofline denominator of BASELINE.json
 
 
-def _cpu(a) -> int:
+def _cpu(a, on_gpu: bool = False) -> int:
+    """The reference's ptest over the message layer.  ``on_gpu``: every rank takes a GPU, the device transport of the
+    message layer is enabled and servers and clients keep their vectors in device memory -- the unmodified
+    pServer / pClient protocol (aio_send / aio_recv over Isend / Iprobe / Irecv / Test) then runs GPU to GPU."""
     from .. import msg as mpiT, ps
     mpiT.Init()
     rank, size = mpiT.get_rank(), mpiT.get_size()
     assert size > 0 and size % 2 == 0
     conf = ps.make_conf(rank, size, "halves")
+    dev = "cpu"
+    if on_gpu:
+        from ..msg import device as mdev
+        local = rank % torch.cuda.device_count()
+        torch.cuda.set_device(local)
+        dev = f"cuda:{local}"
+        conf["device"] = dev
+        mdev.enable()
     if rank < size // 2:
         print(f"rank {rank} is server.")
         ps.pServer(conf).start()
     else:
         print(f"rank {rank} is client.")
-        theta, grad = torch.zeros(a.ssize), torch.zeros(a.ssize)
+        theta, grad = torch.zeros(a.ssize, device=dev), torch.zeros(a.ssize, device=dev)
         pc = ps.pClient(conf)
         pc.start(theta, grad)
         t0 = mpiT.Wtime()
@@ -45,9 +56,16 @@ def _cpu(a) -> int:
             pc.async_send_grad()
             pc.wait()
         dt = mpiT.Wtime() - t0
-        print(f"rank {rank} bandwidth(bi-direction) is {2 * a.rounds * a.ssize * 4 / dt / 1024 / 1024:.1f} MBytes/sec")
+        print(f"rank {rank} bandwidth(bi-direction) is {2 * a.rounds * a.ssize * 4 / dt / 1024 / 1024:.1f} MBytes/sec"
+              + (" (device transport)" if on_gpu else ""))
         pc.stop()
         print("pc stopped")
+    if on_gpu:
+        from ..msg import device as mdev
+        st = mdev.transport().stats
+        print(f"rank {rank} device transport: {st}")
+        mpiT.Barrier()
+        mdev.disable()
     mpiT.Finalize()
     return 0
 
@@ -179,9 +197,15 @@ def main(argv=None) -> int:
     ap.add_argument("--ops", default="pull,push,put,elastic,allreduce_oneshot,allreduce_twoshot,allreduce_elastic")
     ap.add_argument("--nccl", action="store_true", help="also time the NCCL formulation")
     ap.add_argument("--out", default=None)
+    ap.add_argument("--protocol", default="kernels", choices=["kernels", "ps"],
+                    help="--device cuda: 'kernels' sweeps the fused exchange kernels, 'ps' runs the reference's "
+                         "pServer/pClient protocol GPU to GPU over the device transport of the message layer "
+                         "(start with python -m mpit_b200.launch.run -np N)")
     a = ap.parse_args(argv)
     if a.device == "cpu":
         return _cpu(a)
+    if a.protocol == "ps":
+        return _cpu(a, on_gpu=True)
     sizes = []
     b = a.min_bytes
     while b <= a.max_bytes:

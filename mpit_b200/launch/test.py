@@ -3,7 +3,7 @@ first, everybody else receives then forwards; the only check there is ``assert(s
 arrives is checked too).
 
     python -m mpit_b200.launch.run -np 2 -m mpit_b200.launch.test                  # host message layer (MPI_Send/Recv)
-    python -m torch.distributed.run --nproc-per-node 2 -m mpit_b200.launch.test --device cuda   # NVLink mailbox
+    python -m mpit_b200.launch.run -np 2 -m mpit_b200.launch.test --device cuda    # same calls, CUDA tensors, NVLink
 """
 from __future__ import annotations
 
@@ -39,34 +39,34 @@ def _cpu() -> int:
 
 
 def _gpu() -> int:
-    import torch.distributed as dist
-    from ..parallel import SymmetricHeap, DeviceMailbox
-    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
+    """The same script on device buffers: ``mpiT.Send`` / ``mpiT.Recv`` of a CUDA tensor go GPU to GPU through the
+    device transport of the message layer (msg/device.py) -- what the reference gets from a CUDA-aware MPI."""
+    from .. import msg as mpiT
+    from ..msg import device as mdev
+    mpiT.Init()
+    rank, world = mpiT.get_rank(), mpiT.get_size()
     assert world > 1, "run with at least two ranks (test.lua:17)"
+    local = int(os.environ.get("LOCAL_RANK", str(rank % max(torch.cuda.device_count(), 1))))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    dist.init_process_group("nccl", device_id=dev)
-    heap = SymmetricHeap(dev)
-    box = DeviceMailbox(heap, 64)
+    mdev.enable()
     src, dest = (rank - 1) % world, (rank + 1) % world
     s, r = torch.full((1,), float(rank), device=dev), torch.full((1,), -1.0, device=dev)
-    dist.barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
+    st = mpiT.Status()
+    mpiT.Barrier()
+    t0 = mpiT.Wtime()
     if rank == 0:
-        box.send(s, dest, tag=0)
-        box.recv(r, src, tag=0)
+        mpiT.Send(s, 1, mpiT.FLOAT, dest, 0, mpiT.COMM_WORLD)
+        mpiT.Recv(r, 1, mpiT.FLOAT, src, 0, mpiT.COMM_WORLD, st)
     else:
-        box.recv(r, src, tag=0)
-        box.send(s, dest, tag=0)
-    e1.record()
-    torch.cuda.synchronize()
-    print(f"[{rank}/{world}] after: rbuf {float(r[0])} from {src} ({e0.elapsed_time(e1) * 1e3:.0f} us on the device)")
+        mpiT.Recv(r, 1, mpiT.FLOAT, src, 0, mpiT.COMM_WORLD, st)
+        mpiT.Send(s, 1, mpiT.FLOAT, dest, 0, mpiT.COMM_WORLD)
+    dt = mpiT.Wtime() - t0
+    print(f"[{rank}/{world}] after: rbuf {float(r[0])} from {st.source} ({dt * 1e6:.0f} us, device transport)")
     assert float(r[0]) == float(src)
-    heap.check_timeout()
-    dist.barrier()
-    dist.destroy_process_group()
+    mpiT.Barrier()
+    mdev.disable()
+    mpiT.Finalize()
     return 0
 
 

@@ -94,6 +94,7 @@ class Request:
         self._after: List[Optional[callable]] = [None] * n   # completion hooks (device staging)
         self._keep: List[object] = [None] * n                # buffers that must outlive the transfer
         self._unroute: List[int] = [0] * n                   # inter-communicator source offset of a receive
+        self._dev: List[object] = [None] * n                 # live request of the device transport (msg/device.py)
 
     def __len__(self):
         return len(self._arr)
@@ -302,6 +303,40 @@ def Comm_free(comm) -> None:
 
 
 # ---- point to point ---------------------------------------------------------------------------------------
+_DEV_LIVE = -2       # Request._arr marker of a live device-transport request
+
+
+def _dev_route(buf, count: int, dtype: int, comm):
+    """The device transport takes a message when it is enabled, the buffer is a CUDA tensor, the datatype is a
+    basic one and the communicator is COMM_WORLD; returns (transport, nbytes) or (None, 0)."""
+    from . import device
+    tr = device.transport()
+    if tr is None or comm != COMM_WORLD or not isinstance(buf, torch.Tensor) or not buf.is_cuda \
+            or dtype >= datatypes.DERIVED_BASE:
+        return None, 0
+    if not buf.is_contiguous():
+        raise ValueError("message buffers must be contiguous")
+    nbytes = count * _DTYPE_SIZE[dtype]
+    if buf.numel() * buf.element_size() < nbytes:
+        raise ValueError(f"buffer holds {buf.numel()} elements, {count} requested")
+    return tr, nbytes
+
+
+def _dev_status(status: Optional["Status"], req) -> None:
+    if status is not None:
+        s = status[0]
+        s.source, s.tag, s.error, s.count_bytes, s.cancelled = req.src, req.rtag, req.error, req.count_bytes, int(req.cancelled)
+
+
+def _dev_finish(request: "Request", i: int, status: Optional["Status"]) -> None:
+    req = request._dev[i]
+    _dev_status(status, req)
+    request._dev[i] = None
+    request._arr[i] = REQUEST_NULL
+    if req.error and not req.cancelled:
+        raise MPIError(req.error, "message truncated: the receive buffer is smaller than the message")
+
+
 def _unroute(status: Optional["Status"], offset: int) -> None:
     """Sources reported on an inter-communicator are ranks of the remote group."""
     if status is not None and offset and status[0].source >= 0:
@@ -312,6 +347,10 @@ def Send(buf, count: int, dtype: int, dest: int, tag: int, comm: int = COMM_WORL
     """``dtype`` may be a committed derived datatype (the message travels packed); ``comm`` may be an
     inter-communicator (``dest`` is then a rank of the remote group)."""
     comm, dest, _ = dynproc.route(comm, dest)
+    tr, nbytes = _dev_route(buf, count, dtype, comm)
+    if tr is not None:
+        tr.wait(tr.isend(buf, nbytes, dest, tag))
+        return
     b = _Buf(buf, count, dtype, False)
     _chk(host().mpit_msg_send(b.ptr, b.count, b.dtype, dest, tag, comm), "Send")
 
@@ -319,6 +358,14 @@ def Send(buf, count: int, dtype: int, dest: int, tag: int, comm: int = COMM_WORL
 def Recv(buf, count: int, dtype: int, source: int, tag: int, comm: int = COMM_WORLD,
          status: Optional[Status] = None) -> None:
     comm, source, off = dynproc.route(comm, source)
+    tr, nbytes = _dev_route(buf, count, dtype, comm)
+    if tr is not None:
+        req = tr.irecv(buf, nbytes, source, tag)
+        tr.wait(req)
+        _dev_status(status, req)
+        if req.error:
+            raise MPIError(req.error, "message truncated: the receive buffer is smaller than the message")
+        return
     b = _Buf(buf, count, dtype, True)
     _chk(host().mpit_msg_recv(b.ptr, b.count, b.dtype, source, tag, comm, status._ptr() if status else None), "Recv")
     _unroute(status, off)
@@ -328,6 +375,11 @@ def Recv(buf, count: int, dtype: int, source: int, tag: int, comm: int = COMM_WO
 
 def Isend(buf, count: int, dtype: int, dest: int, tag: int, comm: int, request: Request, i: int = 0) -> None:
     comm, dest, _ = dynproc.route(comm, dest)
+    tr, nbytes = _dev_route(buf, count, dtype, comm)
+    if tr is not None:
+        request._dev[i], request._keep[i] = tr.isend(buf, nbytes, dest, tag), buf
+        request._arr[i] = _DEV_LIVE
+        return
     b = _Buf(buf, count, dtype, False)
     request._keep[i] = b.keep
     _chk(host().mpit_msg_isend(b.ptr, b.count, b.dtype, dest, tag, comm, request._ptr(i)), "Isend")
@@ -335,6 +387,11 @@ def Isend(buf, count: int, dtype: int, dest: int, tag: int, comm: int, request: 
 
 def Irecv(buf, count: int, dtype: int, source: int, tag: int, comm: int, request: Request, i: int = 0) -> None:
     comm, source, off = dynproc.route(comm, source)
+    tr, nbytes = _dev_route(buf, count, dtype, comm)
+    if tr is not None:
+        request._dev[i], request._keep[i] = tr.irecv(buf, nbytes, source, tag), buf
+        request._arr[i] = _DEV_LIVE
+        return
     b = _Buf(buf, count, dtype, True)
     request._keep[i], request._after[i] = b.keep, b.after
     request._unroute[i] = off
@@ -359,10 +416,26 @@ def Iprobe(source: int, tag: int, comm: int = COMM_WORLD, status: Optional[Statu
     _chk(host().mpit_msg_iprobe(source, tag, comm, ctypes.byref(f), status._ptr() if status else None), "Iprobe")
     if f.value:
         _unroute(status, off)
-    return bool(f.value)
+        return True
+    from . import device
+    tr = device.transport()
+    if tr is not None and comm == COMM_WORLD:
+        # messages that travel GPU to GPU: the probe is a scan of shared descriptor words, no kernel launch
+        flag, src, mtag, nbytes = tr.iprobe(source, tag)
+        if flag and status is not None:
+            s0 = status[0]
+            s0.source, s0.tag, s0.error, s0.count_bytes, s0.cancelled = src, mtag, 0, nbytes, 0
+        return flag
+    return False
 
 
 def Probe(source: int, tag: int, comm: int = COMM_WORLD, status: Optional[Status] = None) -> None:
+    from . import device
+    if device.transport() is not None and comm == COMM_WORLD:
+        import time
+        while not Iprobe(source, tag, comm, status):     # either transport may deliver it
+            time.sleep(0)
+        return
     comm, source, off = dynproc.route(comm, source)
     _chk(host().mpit_msg_probe(source, tag, comm, status._ptr() if status else None), "Probe")
     _unroute(status, off)
@@ -372,6 +445,12 @@ def Test(request: Request, status: Optional[Status] = None, i: int = 0) -> bool:
     """MPI_Test: True when complete (the handle becomes REQUEST_NULL).  A truncated receive raises."""
     if isinstance(request, attrs.GeneralizedRequest):
         return request.test(status)
+    if request._dev[i] is not None:
+        from . import device
+        if not device.transport().test(request._dev[i]):
+            return False
+        _dev_finish(request, i, status)
+        return True
     st = status or Status()
     f = ctypes.c_int(0)
     code = host().mpit_msg_test(request._ptr(i), ctypes.byref(f), st._ptr())
@@ -387,6 +466,11 @@ def Test(request: Request, status: Optional[Status] = None, i: int = 0) -> bool:
 def Wait(request: Request, status: Optional[Status] = None, i: int = 0) -> None:
     if isinstance(request, attrs.GeneralizedRequest):
         return request.wait(status)
+    if request._dev[i] is not None:
+        from . import device
+        device.transport().wait(request._dev[i])
+        _dev_finish(request, i, status)
+        return
     st = status or Status()
     was_live = not request.is_null(i)
     code = host().mpit_msg_wait(request._ptr(i), st._ptr())
@@ -430,6 +514,10 @@ def Waitany(request: Request, status: Optional[Status] = None) -> int:
 def Cancel(request: Request, i: int = 0) -> None:
     if isinstance(request, attrs.GeneralizedRequest):
         return request.cancel()
+    if request._dev[i] is not None:
+        from . import device
+        device.transport().cancel(request._dev[i])
+        return
     _chk(host().mpit_msg_cancel(request._ptr(i)), "Cancel")
 
 
@@ -456,6 +544,10 @@ def Barrier(comm: int = COMM_WORLD) -> None:
 
 def Bcast(buf, count: int, dtype: int, root: int, comm: int = COMM_WORLD) -> None:
     comm = _intra(comm, "Bcast")
+    if dtype == FLOAT and isinstance(buf, torch.Tensor) and buf.is_cuda:
+        from . import device
+        if device.device_bcast(buf, count, root, comm):
+            return
     b = _Buf(buf, count, dtype, True)
     if b.after and Comm_rank(comm) == root and dtype < datatypes.DERIVED_BASE:
         b.keep[1].copy_(b.keep[0].view(-1)[:b.keep[1].numel()])   # root's device data must be staged out first
@@ -480,6 +572,11 @@ def Allreduce(sbuf, rbuf, count: int, dtype: int, op: int, comm: int = COMM_WORL
     """MPI_Allreduce (/root/reference/test/testreduceall.lua:28).  The ten basic datatypes with SUM..BOR run in the
     native reducer; user operations, LXOR / BXOR, MAXLOC / MINLOC and the packed datatypes are folded on rank 0."""
     comm = _intra(comm, "Allreduce")
+    if op == SUM and dtype == FLOAT and isinstance(sbuf, torch.Tensor) and isinstance(rbuf, torch.Tensor) \
+            and sbuf.is_cuda and rbuf.is_cuda:
+        from . import device
+        if device.device_allreduce(sbuf, rbuf, count, comm):      # NVLink / NVLS kernel, no host staging
+            return
     if extras.needs_packed_reduce(dtype, op):
         return extras.reduce_packed(sbuf, rbuf, count, dtype, op, 0, comm, everyone=True)
     if extras.is_user_op(op):

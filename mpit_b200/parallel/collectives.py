@@ -1,6 +1,6 @@
 """Device collectives over the symmetric heap: all-reduce (one-shot / two-shot, NVLS multimem when the
-heap has a multicast mapping), broadcast, barrier, the all-reduce fused with the elastic pull, and the
-device mailbox (two-sided Send/Recv as put + flag).  Kernels: csrc/kernels/comm.cu.
+heap has a multicast mapping), broadcast, barrier and the all-reduce fused with the elastic pull.  (Two-sided Send/Recv on device buffers is the
+device transport of the message layer, ``mpit_b200/msg/device.py``.)  Kernels: csrc/kernels/comm.cu.
 
 Reference call sites: MPI_Allreduce / MPI_Iallreduce (test/testreduceall.lua:28, test/testireduceall.lua:32,
 asyncsgd/testreduceall.lua:76), MPI_Bcast (wrapped only, mpifuncs.c:145), MPI_Send/Recv (test.lua:32-38).
@@ -129,49 +129,3 @@ class DeviceCollectives:
 
     def barrier(self) -> None:
         check(self.k.mpit_device_barrier(self._sig_ptrs, self.nranks, self.rank, cur_stream()), "mpit_device_barrier")
-
-
-class DeviceMailbox:
-    """Two-sided tagged messages between GPUs: one slot per (source -> destination) pair in the
-    receiver's symmetric memory, payload stores followed by a release-flag; probe = acquire-load."""
-
-    HEADER = 8   # floats
-
-    def __init__(self, heap, max_count: int):
-        self.k = kernels()
-        self.max_count = max_count
-        self.slot = self.HEADER + (max_count + 3) // 4 * 4
-        self.buf: SymmBuffer = heap.alloc(self.slot * heap.nranks)
-        self.nranks, self.rank = self.buf.nranks, self.buf.rank
-        self.send_seq = [0] * self.nranks
-        self.recv_seq = [0] * self.nranks
-        self._res = torch.zeros(3, dtype=torch.int32, device=self.buf.local.device)
-
-    def send(self, x: torch.Tensor, dest: int, tag: int) -> None:
-        n = x.numel()
-        assert n <= self.max_count
-        self.send_seq[dest] += 1
-        slot_ptr = self.buf.ptrs[dest] + 4 * self.slot * self.rank      # my slot inside dest's buffer
-        check(self.k.mpit_mailbox_put(ctypes.c_void_p(slot_ptr), ptr(x), n, tag, self.send_seq[dest], cur_stream()),
-              "mpit_mailbox_put")
-
-    def try_recv(self, out: torch.Tensor, source: int, tag: int = -1):
-        """Iprobe+Recv: returns (arrived, count, tag) after a stream sync."""
-        seq = self.recv_seq[source] + 1
-        slot_ptr = self.buf.ptrs[self.rank] + 4 * self.slot * source
-        check(self.k.mpit_mailbox_recv(ctypes.c_void_p(slot_ptr), ptr(out), out.numel(), tag, seq, ptr(self._res),
-                                       cur_stream()), "mpit_mailbox_recv")
-        arrived, count, got_tag = self._res.tolist()
-        if arrived:
-            self.recv_seq[source] = seq
-        return bool(arrived), count, got_tag
-
-    def recv(self, out: torch.Tensor, source: int, tag: int = -1, timeout_s: float = 10.0):
-        import time
-        t0 = time.time()
-        while True:
-            ok, count, got_tag = self.try_recv(out, source, tag)
-            if ok:
-                return count, got_tag
-            if time.time() - t0 > timeout_s:
-                raise TimeoutError("device mailbox receive timed out")

@@ -57,11 +57,24 @@ class SymmBuffer:
         return arr
 
 
+def _mpit_world():
+    """The host message layer as control plane (jobs started with ``python -m mpit_b200.launch.run``, where
+    torch.distributed is not initialised): (rank, size) or None."""
+    try:
+        from .. import msg as mpiT
+        if mpiT.Initialized() and mpiT.get_size() > 1:
+            return mpiT.get_rank(), mpiT.get_size()
+    except Exception:
+        pass
+    return None
+
+
 def _dist_info(group=None):
     import torch.distributed as dist
     if dist.is_available() and dist.is_initialized():
         return dist.get_rank(group), dist.get_world_size(group)
-    return 0, 1
+    w = _mpit_world()
+    return w if w is not None else (0, 1)
 
 
 def _all_gather_obj(obj, group=None):
@@ -69,15 +82,33 @@ def _all_gather_obj(obj, group=None):
     rank, world = _dist_info(group)
     if world == 1:
         return [obj]
-    out = [None] * world
-    dist.all_gather_object(out, obj, group=group)
-    return out
+    if dist.is_available() and dist.is_initialized():
+        out = [None] * world
+        dist.all_gather_object(out, obj, group=group)
+        return out
+    # host message layer: lengths with Allgather, pickles with a padded Allgather
+    import pickle
+    from .. import msg as mpiT
+    blob = pickle.dumps(obj)
+    lens = torch.zeros(world, dtype=torch.int64)
+    mpiT.Allgather(torch.tensor([len(blob)], dtype=torch.int64), 1, mpiT.LONG, lens, mpiT.COMM_WORLD)
+    width = int(lens.max())
+    mine = torch.zeros(width, dtype=torch.uint8)
+    mine[:len(blob)] = torch.frombuffer(bytearray(blob), dtype=torch.uint8)
+    allb = torch.zeros(width * world, dtype=torch.uint8)
+    mpiT.Allgather(mine, width, mpiT.BYTE, allb, mpiT.COMM_WORLD)
+    return [pickle.loads(bytes(allb[r * width:r * width + int(lens[r])].tolist())) for r in range(world)]
 
 
 def _barrier(group=None):
     import torch.distributed as dist
-    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
-        dist.barrier(group=group)
+    if dist.is_available() and dist.is_initialized():
+        if dist.get_world_size(group) > 1:
+            dist.barrier(group=group)
+        return
+    if _mpit_world() is not None:
+        from .. import msg as mpiT
+        mpiT.Barrier(mpiT.COMM_WORLD)
 
 
 class SymmetricHeap:

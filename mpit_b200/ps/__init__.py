@@ -97,11 +97,13 @@ class pServer:
         off, size = int(cinfo[0]), int(cinfo[1])
         if self.offset == -1:
             self.offset, self.size = off, size
-            self.p = torch.zeros(size, dtype=torch.float32)
+            # conf["device"] = "cuda:N": the shard lives on a GPU and the unmodified protocol runs GPU to GPU through
+            # the device transport of the message layer (msg/device.py), like a CudaStorage handed to CUDA-aware MPI
+            self.p = torch.zeros(size, dtype=torch.float32, device=self.conf.get("device", "cpu"))
             self.rule_state = rule_state(self.rule, self.p)   # BiCNN/pserver.lua:50-83
         else:
             assert self.offset == off and self.size == size, "clients disagree on this server's shard"
-        self.g[crank] = torch.zeros(size, dtype=torch.float32)   # one gradient slot per client
+        self.g[crank] = torch.zeros(size, dtype=torch.float32, device=self.conf.get("device", "cpu"))   # one slot per client
         yield signal_DONE
 
     def _sendparam(self, crank):

@@ -12,6 +12,18 @@ from mpit_b200 import msg as mpiT
 from mpit_b200.aio import Queue, IOState, co_execute, co_wait, co_ping, aio_recv, aio_send, signal_INIT, signal_DONE
 
 
+def case_symm_rendezvous():
+    """The symmetric heap's handle exchange over the host message layer (jobs started with launch.run have no
+    torch.distributed): object all-gather and barrier."""
+    from mpit_b200.parallel import symm
+    rank, size = mpiT.get_rank(), mpiT.get_size()
+    assert symm._dist_info() == (rank, size)
+    objs = symm._all_gather_obj({"rank": rank, "blob": b"x" * (10 + 7 * rank), "pid": os.getpid()})
+    assert [o["rank"] for o in objs] == list(range(size))
+    assert all(len(o["blob"]) == 10 + 7 * r for r, o in enumerate(objs))
+    symm._barrier()
+
+
 def case_ring():
     """/root/reference/test.lua:19-38 with an assertion."""
     rank, size = mpiT.get_rank(), mpiT.get_size()

@@ -6,7 +6,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import torch.distributed as dist
 
-from mpit_b200.parallel import SymmetricHeap, ShardedCenter, DeviceCollectives, DeviceMailbox
+from mpit_b200.parallel import SymmetricHeap, ShardedCenter, DeviceCollectives
 from mpit_b200.parallel.center import partition
 
 
@@ -113,24 +113,6 @@ def case_collectives(rank, world, dev, heap):
     coll.barrier()
     torch.cuda.synchronize()
     heap.check_timeout()
-
-
-def case_mailbox(rank, world, dev, heap):
-    """Ring of one float (test.lua:19-38) through the device mailbox, twice to exercise sequencing."""
-    mb = DeviceMailbox(heap, 64)
-    sync(dev)
-    src, dest = (rank - 1) % world, (rank + 1) % world
-    for rnd in range(2):
-        s = torch.full((4,), float(rank * 10 + rnd), device=dev)
-        r = torch.zeros(4, device=dev)
-        if rank == 0:
-            mb.send(s, dest, tag=3)
-            cnt, tag = mb.recv(r, src, tag=3)
-        else:
-            cnt, tag = mb.recv(r, src, tag=3)
-            mb.send(s, dest, tag=3)
-        assert cnt == 4 and tag == 3 and float(r[0]) == src * 10 + rnd, (rank, rnd, r)
-        sync(dev)
 
 
 def case_eamsgd_train(rank, world, dev, heap):
@@ -317,6 +299,140 @@ def case_sync_easgd(rank, world, dev, heap):
             assert torch.allclose(got, xs[rank], rtol=1e-5, atol=1e-6), (n, t, float((got - xs[rank]).abs().max()))
         opt.coll.check_timeout()
         sync(dev)
+
+
+def case_msg_device(rank, world, dev, heap):
+    """The message API on CUDA tensors over the device transport (msg/device.py): the ring of test.lua, tag matching
+    out of order, ANY_SOURCE / ANY_TAG, probe-then-receive, more messages in flight than ring slots, a rendezvous-
+    sized message, zero-byte messages, Cancel of an unmatched send and receive, truncation, aio_send / aio_recv under
+    the coroutine scheduler, and Allreduce / Bcast (ports of the host-layer cases of tests/mp_cases.py)."""
+    from mpit_b200 import msg as mpiT
+    from mpit_b200.msg import device as mdev
+    mpiT.Init()
+    tr = mdev.enable(heap)
+    W = mpiT.COMM_WORLD
+    f = lambda *v: torch.tensor(v, dtype=torch.float32, device=dev)
+    nxt, prv = (rank + 1) % world, (rank - 1) % world
+    # -- ring of one float (test.lua:19-38)
+    sbuf, rbuf = f(float(rank)), torch.zeros(1, device=dev)
+    st = mpiT.Status()
+    if rank == 0:
+        mpiT.Send(sbuf, 1, mpiT.FLOAT, nxt, 0, W)
+        mpiT.Recv(rbuf, 1, mpiT.FLOAT, prv, 0, W, st)
+    else:
+        mpiT.Recv(rbuf, 1, mpiT.FLOAT, prv, 0, W, st)
+        mpiT.Send(sbuf, 1, mpiT.FLOAT, nxt, 0, W)
+    assert float(rbuf) == float(prv) and st.source == prv and st.tag == 0 and st.count_bytes == 4
+    sync(dev)
+    # -- tags out of order + ANY_TAG + probe (rank 0 -> rank 1)
+    if rank == 0:
+        for tag in (5, 6, 7):
+            mpiT.Send(f(tag * 1.0, tag * 2.0), 2, mpiT.FLOAT, 1, tag, W)
+    elif rank == 1:
+        got = torch.zeros(2, device=dev)
+        mpiT.Probe(0, 7, W, st)
+        assert st.tag == 7 and st.count_bytes == 8 and mpiT.Get_count(st, mpiT.FLOAT) == 2
+        mpiT.Recv(got, 2, mpiT.FLOAT, 0, 7, W, st)
+        assert got.tolist() == [7.0, 14.0]
+        mpiT.Recv(got, 2, mpiT.FLOAT, 0, mpiT.ANY_TAG, W, st)          # oldest unconsumed first: tag 5
+        assert st.tag == 5 and got.tolist() == [5.0, 10.0]
+        assert mpiT.Iprobe(0, 6, W, st) and not mpiT.Iprobe(0, 5, W)
+        mpiT.Recv(got, 2, mpiT.FLOAT, 0, 6, W)
+        assert got.tolist() == [6.0, 12.0]
+    sync(dev)
+    # -- ANY_SOURCE: everybody -> rank 0
+    if rank == 0:
+        seen = set()
+        got = torch.zeros(1, device=dev)
+        for _ in range(world - 1):
+            mpiT.Recv(got, 1, mpiT.FLOAT, mpiT.ANY_SOURCE, 11, W, st)
+            assert float(got) == float(st.source) * 3
+            seen.add(st.source)
+        assert seen == set(range(1, world))
+    else:
+        mpiT.Send(f(rank * 3.0), 1, mpiT.FLOAT, 0, 11, W)
+    sync(dev)
+    # -- more eager messages in flight than ring slots (flow control), non-blocking on both sides
+    n_msg = 3 * tr.K + 1
+    reqs = mpiT.Request(n_msg)
+    outs = [torch.zeros(64, device=dev) for _ in range(n_msg)]
+    for i in range(n_msg):
+        mpiT.Irecv(outs[i], 64, mpiT.FLOAT, prv, 20, W, reqs, i)
+    sreq = mpiT.Request(n_msg)
+    srcs = [torch.full((64,), float(rank * 1000 + i), device=dev) for i in range(n_msg)]
+    for i in range(n_msg):
+        mpiT.Isend(srcs[i], 64, mpiT.FLOAT, nxt, 20, W, sreq, i)
+    mpiT.Waitall(reqs)
+    mpiT.Waitall(sreq)
+    for i in range(n_msg):
+        assert float(outs[i][0]) == prv * 1000 + i and float(outs[i][63]) == prv * 1000 + i, i    # in order
+    sync(dev)
+    # -- rendezvous-sized message (pulled by the receiver from the sender's tensor), with an offset into it
+    n_big = (2 << 20) + 3
+    big = torch.arange(n_big + 5, dtype=torch.float32, device=dev) + rank
+    land = torch.zeros(n_big, device=dev)
+    r1, r2 = mpiT.Request(), mpiT.Request()
+    mpiT.Irecv(land, n_big, mpiT.FLOAT, prv, 30, W, r1)
+    mpiT.Isend(big[5:], n_big, mpiT.FLOAT, nxt, 30, W, r2)
+    while not (mpiT.Test(r1) and mpiT.Test(r2)):
+        pass
+    assert torch.equal(land, torch.arange(n_big + 5, dtype=torch.float32, device=dev)[5:] + prv)
+    sync(dev)
+    # -- zero-byte message (descriptor only) and truncation
+    z = torch.zeros(4, device=dev)
+    if rank == 0:
+        mpiT.Send(z, 0, mpiT.FLOAT, 1, 40, W)
+        mpiT.Send(z, 4, mpiT.FLOAT, 1, 41, W)
+    elif rank == 1:
+        mpiT.Recv(z, 0, mpiT.FLOAT, 0, 40, W, st)
+        assert st.count_bytes == 0 and st.tag == 40
+        try:
+            mpiT.Recv(z, 2, mpiT.FLOAT, 0, 41, W, st)
+            raise AssertionError("a truncated receive must raise")
+        except mpiT.MPIError:
+            pass
+    sync(dev)
+    # -- Cancel: a send nobody receives is withdrawn; so is an unmatched receive (init.lua:52-59 / :94-101)
+    if rank == 0:
+        rq = mpiT.Request()
+        mpiT.Isend(f(1.0), 1, mpiT.FLOAT, 1, 99, W, rq)
+        mpiT.Cancel(rq)
+        mpiT.Wait(rq, st)
+        assert mpiT.Test_cancelled(st)
+    rq = mpiT.Request()
+    mpiT.Irecv(z, 1, mpiT.FLOAT, nxt, 98, W, rq)
+    assert not mpiT.Test(rq)
+    mpiT.Cancel(rq)
+    mpiT.Wait(rq, st)
+    assert mpiT.Test_cancelled(st)
+    sync(dev)
+    if rank == 1:
+        assert not mpiT.Iprobe(0, 99, W), "a cancelled message must not be visible"
+    sync(dev)
+    # -- coroutine IO over device buffers (init.lua:41-108): aio_send / aio_recv under co_wait
+    q = mpiT.Queue()
+    a_out = torch.zeros(1000, device=dev)
+    a_in = torch.full((1000,), float(rank + 1), device=dev)
+    q.push(mpiT.co_execute(lambda: mpiT.aio_recv(a_out, 1000, mpiT.FLOAT, prv, 50, W), ()))
+    q.push(mpiT.co_execute(lambda: mpiT.aio_send(a_in, 1000, mpiT.FLOAT, nxt, 50, W), ()))
+    mpiT.co_wait(q)
+    assert float(a_out.min()) == prv + 1 and float(a_out.max()) == prv + 1
+    sync(dev)
+    # -- collectives on CUDA tensors
+    x = torch.full((5000,), float(rank + 1), device=dev)
+    y = torch.zeros(5000, device=dev)
+    mpiT.Allreduce(x, y, 5000, mpiT.FLOAT, mpiT.SUM, W)
+    torch.cuda.synchronize()
+    assert float(y.min()) == world * (world + 1) / 2 and float(y.max()) == world * (world + 1) / 2
+    b = torch.full((300,), float(rank), device=dev)
+    mpiT.Bcast(b, 300, mpiT.FLOAT, world - 1, W)
+    torch.cuda.synchronize()
+    assert float(b.min()) == world - 1 and float(b.max()) == world - 1
+    sync(dev)
+    stats = tr.stats
+    assert stats["eager"] > 0 and stats["rendezvous"] > 0 and (rank > 1 or stats["zero"] + stats["probes"] > 0)
+    mdev.disable()
+    mpiT.Finalize()
 
 
 def case_pulled_linear(rank, world, dev, heap):

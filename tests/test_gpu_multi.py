@@ -1,5 +1,6 @@
 """Multi-GPU tests: one process per GPU under torchrun, exercising the symmetric heap (IPC and VMM /
-multicast), the sharded centre, device collectives, the mailbox and asynchronous EAMSGD."""
+multicast), the sharded centre, device collectives, the device transport of the message layer, the asynchronous
+parameter server and the EAMSGD / sync-EASGD trainers."""
 import os
 import subprocess
 import sys
@@ -22,10 +23,10 @@ def _torchrun(cases, nproc, env=None, timeout=600):
 
 
 @pytest.mark.parametrize("mode", ["ipc", "vmm"])
-def test_center_collectives_mailbox(mode):
+def test_center_and_collectives(mode):
     n = min(torch.cuda.device_count(), 8)
-    out = _torchrun(["center", "collectives", "mailbox"], n, {"MPIT_SYMM_MODE": mode})
-    assert "case mailbox: ok" in out
+    out = _torchrun(["center", "collectives"], n, {"MPIT_SYMM_MODE": mode})
+    assert "case collectives: ok" in out
 
 
 def test_async_eamsgd_training():
@@ -52,6 +53,22 @@ def test_sync_easgd_allreduce_fused_with_elastic_step():
     assert "case sync_easgd: ok" in out
 
 
+def test_message_api_on_device_tensors():
+    n = min(torch.cuda.device_count(), 8)
+    out = _torchrun(["msg_device"], n)
+    assert "case msg_device: ok" in out
+
+
+def test_ps_protocol_gpu_to_gpu_over_device_transport():
+    """The reference's ptest (pServer / pClient, aio_send / aio_recv) with every vector in device memory."""
+    n = min(torch.cuda.device_count(), 8) // 2 * 2
+    cmd = [sys.executable, "-m", "mpit_b200.launch.run", "-np", str(n), "-m", "mpit_b200.launch.ptest", "--device", "cuda",
+           "--protocol", "ps", "--ssize", str(3 * 1024 * 1024 + 5), "--rounds", "5"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=os.path.dirname(HERE))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "(device transport)" in r.stdout and "'rendezvous': 0" not in r.stdout.split("device transport:")[-1]
+
+
 def test_pull_fused_with_consumer_gemm():
     n = min(torch.cuda.device_count(), 8)
     out = _torchrun(["pulled_linear"], n)
@@ -66,7 +83,7 @@ def test_one_sided_window():
 
 
 def test_ring_smoke_script_on_device():
-    """/root/reference/test.lua over the NVLink mailbox (one float around the ring of GPUs)."""
+    """/root/reference/test.lua with CUDA tensors: mpiT.Send / Recv over the device transport (one float around the ring of GPUs)."""
     n = min(torch.cuda.device_count(), 8)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr",
            "127.0.0.1", "--master-port", "29534", "-m", "mpit_b200.launch.test", "--device", "cuda"]

@@ -23,6 +23,10 @@ def test_ring_send_recv(nproc):
     _run("ring", nproc)
 
 
+def test_symmetric_heap_rendezvous_over_host_layer():
+    _run("symm_rendezvous", 3)
+
+
 @pytest.mark.parametrize("nproc", [2, 4])
 def test_allreduce(nproc):
     _run("allreduce", nproc)
