@@ -60,6 +60,21 @@ def synthetic_cifar(n: int, seed: int = 0, pinned: bool = True, channels: int = 
     return x, y
 
 
+def learnable_cifar(n: int, seed: int = 0, pinned: bool = True, channels: int = 3, noise: float = 40.0, proto_seed: int = 1234):
+    """A synthetic set that CAN be learned: every class has its own smooth mean image (8x8 blocks of a random
+    pattern fixed by ``proto_seed``) and a sample is that image plus pixel noise -- for convergence tests, where
+    the uniform-noise set of :func:`synthetic_cifar` has nothing to fit."""
+    gp = torch.Generator().manual_seed(proto_seed)
+    proto = torch.randint(40, 216, (NUM_CLASSES, channels, 4, 4), generator=gp).float()
+    proto = proto.repeat_interleave(IMG // 4, 2).repeat_interleave(IMG // 4, 3)           # [10, C, 32, 32]
+    g = torch.Generator().manual_seed(seed)
+    y = torch.randint(0, NUM_CLASSES, (n,), dtype=torch.int32, generator=g)
+    x = (proto[y.long()] + torch.randn(n, channels, IMG, IMG, generator=g) * noise).clamp_(0, 255).to(torch.uint8)
+    if pinned and torch.cuda.is_available():
+        x, y = x.pin_memory(), y.pin_memory()
+    return x, y
+
+
 def cifar_data(trsize: int, tesize: int, seed: int = 0, channels: int = 3, root: Optional[str] = None,
                pinned: bool = True):
     """(train_x, train_y), (test_x, test_y), is_real: the Torch7 CIFAR-10 batches the reference loads
