@@ -87,7 +87,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=30)
     ap.add_argument("--impl", default="mpit", help="mpit (this framework) | reference | torch (library-call baseline)")
     ap.add_argument("--kernels", default=os.environ.get("MPIT_KERNELS", "auto"), help="umma | ref | auto")
-    ap.add_argument("--optim", default="eamsgd")
+    ap.add_argument("--optim", default="eamsgd", help="eamsgd | easgd | downpour | sync_easgd | sync_eamsgd | sgd")
+    ap.add_argument("--model", default="cifar", choices=["cifar", "mnist"],
+                    help="cifar: the headline 7-layer CNN; mnist: the MNIST-shaped CNN of BASELINE.json config 2")
     ap.add_argument("--tau", type=int, default=10)
     ap.add_argument("--batch", type=int, default=128)
     ap.add_argument("--no-graphs", action="store_true")
@@ -131,7 +133,8 @@ def main():
             kernels = "ref"
     B = args.batch
     opts = CifarOpts(name=args.optim, lr=1e-2, mom=0.99, mb=B, su=args.tau, mva=0.9 / world, impl=kernels,
-                     use_graphs=not args.no_graphs, seed=1 + rank)
+                     use_graphs=not args.no_graphs, seed=1 + rank, model=args.model)
+    CH = 1 if args.model == "mnist" else 3
     heap = SymmetricHeap(dev)
     tr = CifarTrainer(opts, dev, heap)
 
@@ -139,13 +142,13 @@ def main():
     # device-resident set LARGER than the 126 MB L2 for the kernel-only arm so every step's inputs
     # come from HBM.
     n_host = 64 * B
-    hx, hy = synthetic_cifar(n_host, seed=100 + rank)
-    n_dev_batches = 352                      # 352 * 128 * 3072 B = 138 MB > L2
-    dx = torch.randint(0, 256, (n_dev_batches, B, 3, 32, 32), dtype=torch.uint8, device=dev)
+    hx, hy = synthetic_cifar(n_host, seed=100 + rank, channels=CH)
+    n_dev_batches = 352 * 3 // CH            # 352 * 128 * 3072 B = 138 MB > L2
+    dx = torch.randint(0, 256, (n_dev_batches, B, CH, 32, 32), dtype=torch.uint8, device=dev)
     dy = torch.randint(0, 10, (n_dev_batches, B), dtype=torch.int32, device=dev)
     dcrop = torch.randint(0, 5, (n_dev_batches, B, 2), dtype=torch.int32, device=dev)
     gen = torch.Generator().manual_seed(7 + rank)
-    stage_x = torch.empty(B, 3, 32, 32, dtype=torch.uint8).pin_memory()
+    stage_x = torch.empty(B, CH, 32, 32, dtype=torch.uint8).pin_memory()
     stage_y = torch.empty(B, dtype=torch.int32).pin_memory()
     stage_c = torch.empty(B, 2, dtype=torch.int32).pin_memory()
 
@@ -234,7 +237,7 @@ def main():
     # ---- the library-call formulation of the same step (cuDNN / cuBLAS / NCCL through torch), same process, same
     # box, same steps / warm-up / blocks and the same end-to-end rules: the anchor of `vs_baseline` ----
     base = None
-    if not args.no_baseline:
+    if not args.no_baseline and args.model == "cifar" and args.optim in ("eamsgd", "easgd"):
         try:
             del dx, dy, dcrop
             torch.cuda.empty_cache()
@@ -263,13 +266,16 @@ def main():
         elif base:
             detail = base
         out = {
-            "metric": METRIC, "value": round(value, 1), "unit": "samples/s", "n_gpus": world,
+            "metric": METRIC if (args.model, args.optim, args.tau) == ("cifar", "eamsgd", 10) else
+            f"samples/sec (device-timed, max over ranks) {args.model} CNN {args.optim} tau={args.tau}",
+            "value": round(value, 1), "unit": "samples/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_max / args.steps, 5),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": vsb, "vs_baseline_detail": detail,
             "dtype": "tf32 (fp32 storage, fp32 accumulate)" if kernels == "umma" else "fp32",
             "data": "synthetic CIFAR-10-shaped uint8 images, random-init weights",
             "impl": "mpit",
-            "config": {"model": "CIFAR-10 7-layer CNN (asyncsgd/models/7-layers-cnn.lua, 351946 params)",
+            "config": {"model": "CIFAR-10 7-layer CNN (asyncsgd/models/7-layers-cnn.lua, 351946 params)"
+                       if args.model == "cifar" else f"MNIST-shaped CNN 1x32x32, 32/64/64 channels ({n_params} params)",
                        "global_batch": gb, "per_gpu_batch": B, "seq_len": None, "optimizer": args.optim,
                        "tau": args.tau, "lr": 1e-2, "mom": 0.99, "mva": 0.9 / world,
                        "parallelism": f"async-dp{world} + centre sharded over {world} GPU(s)",
@@ -295,6 +301,8 @@ def main():
                          "hbm_gbs_measured": peaks.get("hbm_gbs"), "nvlink_gbs_per_direction": 900.0,
                          "exchange_us_at_nvlink_peak": round(2 * 4 * n_params * (world - 1) / max(world, 1) / 900e9 * 1e6 / 2, 3)},
         }
+        if args.model != "cifar":
+            out["roofline"] = None          # the FLOP count above is the CIFAR network's
         print(json.dumps(out))
     if world > 1:
         dist.barrier()
