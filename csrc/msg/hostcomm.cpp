@@ -455,6 +455,43 @@ bool pump_send(int dst) {
   return true;
 }
 
+// A connection was lost (the peer crashed or left): nothing addressed to or expected from that rank can complete
+// any more.  Called with g.mu held.  Every request tied to the peer finishes with MPIT_ERR_OTHER instead of leaving
+// Wait / Recv / the collectives blocked forever: posted receives naming it as source, sends to it (queued, in flight
+// or waiting for a rendezvous FIN), and the receive it was in the middle of delivering.  ANY_SOURCE receives fail
+// once no peer is left at all.
+void fail_peer_locked(int r) {
+  Peer& p = g.peers[r];
+  if (p.fd >= 0) { ::close(p.fd); p.fd = -1; }
+  bool anyone = false;
+  for (int q = 0; q < g.size; ++q) if (q != g.rank && g.peers[q].fd >= 0) anyone = true;
+  auto fail = [](Req* q) {
+    if (q && !q->done) { q->error = MPIT_ERR_OTHER; q->done = true; }
+  };
+  fail(p.rreq);
+  p.rreq = nullptr;
+  if (p.runx) { fail(p.runx->claimed); p.runx->claimed = nullptr; p.runx = nullptr; }
+  p.in_body = false;
+  p.hdr_got = 0;
+  for (auto& it : p.sendq) fail(it.req);
+  p.sendq.clear();
+  for (auto it = g.posted.begin(); it != g.posted.end();) {
+    Req* q = *it;
+    if (q->peer == r || (q->peer < 0 && !anyone)) { fail(q); it = g.posted.erase(it); }
+    else ++it;
+  }
+  for (auto& kv : g.reqs) {
+    Req* q = kv.second.get();
+    if (q->kind == REQ_SEND && q->peer == r) fail(q);      // includes rendezvous sends waiting for the FIN
+  }
+  for (auto it = g.unexpected.begin(); it != g.unexpected.end();) {
+    Unexpected* u = it->get();
+    if (u->src == r && !u->complete && !u->is_rts) { fail(u->claimed); it = g.unexpected.erase(it); }
+    else ++it;
+  }
+  g.cv.notify_all();
+}
+
 void progress_loop() {
   std::vector<pollfd> pfds;
   while (!g.stop.load()) {
@@ -486,10 +523,10 @@ void progress_loop() {
       if (r == g.rank || g.peers[r].fd < 0) continue;
       short ev = pfds[i++].revents;
       if (ev & (POLLIN | POLLHUP | POLLERR)) {
-        if (!pump_recv(r)) { ::close(g.peers[r].fd); g.peers[r].fd = -1; g.cv.notify_all(); continue; }
+        if (!pump_recv(r)) { fail_peer_locked(r); continue; }
       }
       if (!g.peers[r].sendq.empty()) {
-        if (!pump_send(r)) { ::close(g.peers[r].fd); g.peers[r].fd = -1; g.cv.notify_all(); }
+        if (!pump_send(r)) fail_peer_locked(r);
       }
     }
   }

@@ -24,6 +24,34 @@ def case_symm_rendezvous():
     symm._barrier()
 
 
+def case_peer_death():
+    """A rank that disappears must not leave the others blocked: a receive posted for it, and a send to it that waits
+    for the rendezvous acknowledgement, complete with an error once the connection is gone."""
+    rank = mpiT.get_rank()
+    if rank == 1:
+        time.sleep(0.3)
+        os._exit(0)                       # no Finalize: the sockets just close
+    if rank == 0:
+        buf = torch.zeros(4)
+        t0 = time.time()
+        try:
+            mpiT.Recv(buf, 4, mpiT.FLOAT, 1, 7, mpiT.COMM_WORLD)
+            raise AssertionError("a receive from a dead rank must fail")
+        except mpiT.MPIError:
+            pass
+        assert time.time() - t0 < 20
+        req = mpiT.Request()
+        big = torch.zeros(1 << 20)
+        try:
+            mpiT.Isend(big, big.numel(), mpiT.FLOAT, 1, 8, mpiT.COMM_WORLD, req)
+            mpiT.Wait(req)
+            raise AssertionError("a send to a dead rank must fail")
+        except mpiT.MPIError:
+            pass
+        print("case peer_death: ok", flush=True)
+    os._exit(0)                           # the job cannot run a barrier any more
+
+
 def case_ring():
     """/root/reference/test.lua:19-38 with an assertion."""
     rank, size = mpiT.get_rank(), mpiT.get_size()

@@ -23,6 +23,10 @@ def test_ring_send_recv(nproc):
     _run("ring", nproc)
 
 
+def test_requests_of_a_dead_peer_complete_with_an_error():
+    _run("peer_death", 3, timeout=60)
+
+
 def test_symmetric_heap_rendezvous_over_host_layer():
     _run("symm_rendezvous", 3)
 
