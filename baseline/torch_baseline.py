@@ -23,9 +23,9 @@ from mpit_b200.parallel.center import partition
 
 
 class TorchEAMSGD:
-    def __init__(self, dev, world, rank, B, lr=1e-2, mom=0.99, su=10, mva=0.9, graphs=True):
-        torch.backends.cudnn.allow_tf32 = True
-        torch.backends.cuda.matmul.allow_tf32 = True
+    def __init__(self, dev, world, rank, B, lr=1e-2, mom=0.99, su=10, mva=0.9, graphs=True, tf32=True):
+        torch.backends.cudnn.allow_tf32 = tf32          # False: the libraries' fp32 kernels (the reference's precision)
+        torch.backends.cuda.matmul.allow_tf32 = tf32
         torch.backends.cudnn.benchmark = True
         self.dev, self.world, self.rank, self.B = dev, world, rank, B
         self.lr, self.mom, self.su, self.mva = lr, mom, su, mva
@@ -126,7 +126,7 @@ class TorchEAMSGD:
         self.t += 1
 
 
-def measure(args, rank, world, dev, blocks: int = 5):
+def measure(args, rank, world, dev, blocks: int = 5, tf32: bool = True, e2e: bool = True):
     """Both arms of the library baseline, timed exactly like the product arm in bench.py: `blocks` back-to-back blocks
     of `steps` steps each (median block reported); the end-to-end arm takes its batches from the same native loader
     thread and reads the loss of step t-2 every step, i.e. the same host-side rules as CifarTrainer.train_step."""
@@ -134,7 +134,7 @@ def measure(args, rank, world, dev, blocks: int = 5):
     B = args.batch
     from mpit_b200.workloads.cifar import synthetic_cifar
     from mpit_b200.data.loader import BatchLoader
-    tr = TorchEAMSGD(dev, world, rank, B, su=args.tau, mva=0.9 / world, graphs=not args.no_graphs)
+    tr = TorchEAMSGD(dev, world, rank, B, su=args.tau, mva=0.9 / world, graphs=not args.no_graphs, tf32=tf32)
     n_host = 64 * B
     hx, hy = synthetic_cifar(n_host, seed=100 + rank)
     n_dev = 352
@@ -186,19 +186,23 @@ def measure(args, rank, world, dev, blocks: int = 5):
         e1.record()
         barrier()
         dev_ms.append(e0.elapsed_time(e1))
-    for i in range(5):
+    last = float("nan")
+    for i in range(5 if e2e else 0):
         e2e_step(i)
-    for b in range(blocks):
+    for b in range(blocks if e2e else 0):
         barrier()
         t0 = time.perf_counter()
         for i in range(args.steps):
             last = e2e_step(i)
         barrier()
         e2e_ms.append((time.perf_counter() - t0) * 1e3)
+    if not e2e:
+        e2e_ms = [float("nan")] * blocks
     t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)          # per block: the slowest rank
     dms, ems = statistics.median(t[0].tolist()), statistics.median(t[1].tolist())
+    loader.close()
     gb = B * world
     return {"value": gb * args.steps / (dms / 1e3), "e2e": gb * args.steps / (ems / 1e3), "ms_per_step": dms / args.steps,
             "e2e_ms_per_step": ems / args.steps, "blocks_ms": [round(v, 4) for v in t[0].tolist()], "loss": last,

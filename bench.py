@@ -86,7 +86,7 @@ def main():
     ap.add_argument("--steps", type=int, default=500)
     ap.add_argument("--warmup", type=int, default=30)
     ap.add_argument("--impl", default="mpit", help="mpit (this framework) | reference | torch (library-call baseline)")
-    ap.add_argument("--kernels", default=os.environ.get("MPIT_KERNELS", "auto"), help="umma | ref | auto")
+    ap.add_argument("--kernels", default=os.environ.get("MPIT_KERNELS", "auto"), help="umma | umma3x | ref | auto")
     ap.add_argument("--optim", default="eamsgd", help="eamsgd | easgd | downpour | sync_easgd | sync_eamsgd | sgd")
     ap.add_argument("--model", default="cifar", choices=["cifar", "mnist"],
                     help="cifar: the headline 7-layer CNN; mnist: the MNIST-shaped CNN of BASELINE.json config 2")
@@ -94,6 +94,7 @@ def main():
     ap.add_argument("--batch", type=int, default=128)
     ap.add_argument("--no-graphs", action="store_true")
     ap.add_argument("--blocks", type=int, default=5, help="timed blocks of `steps` steps; the median block is reported")
+    ap.add_argument("--no-fp32-arm", action="store_true", help="skip the 3xTF32 (fp32-accurate) arm")
     ap.add_argument("--no-baseline", action="store_true", help="skip the in-process library-call arm (vs_baseline = null)")
     ap.add_argument("--inline-loader", action="store_true",
                     help="e2e arm: assemble batches on the Python thread instead of the native loader thread")
@@ -246,6 +247,53 @@ def main():
         except Exception as ex:      # the product number must not depend on the baseline arm
             base = {"error": repr(ex)[:200]}
 
+    # ---- the fp32-accurate arm: the same step with 3xTF32 products (the reference computes in fp32), device-timed the
+    # same way, next to the libraries' fp32 kernels (allow_tf32 = False) ----
+    fp32 = None
+    if kernels == "umma" and args.model == "cifar" and not args.no_fp32_arm:
+        try:
+            opts3 = CifarOpts(name=args.optim, lr=1e-2, mom=0.99, mb=B, su=args.tau, mva=0.9 / world, impl="umma3x",
+                              use_graphs=not args.no_graphs, seed=1 + rank)
+            tr3 = CifarTrainer(opts3, dev, heap)
+            dx3 = torch.randint(0, 256, (352, B, 3, 32, 32), dtype=torch.uint8, device=dev)
+            dy3 = torch.randint(0, 10, (352, B), dtype=torch.int32, device=dev)
+            dc3 = torch.randint(0, 5, (352, B, 2), dtype=torch.int32, device=dev)
+
+            def step3(i):
+                j = i % 352
+                tr3.engine.set_batch(dx3[j], dy3[j], dc3[j])
+                tr3.device_step()
+
+            for i in range(max(args.warmup, 3 * args.tau + 3)):
+                step3(i)
+            ms3 = []
+            for b in range(BLOCKS):
+                barrier()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for i in range(args.steps):
+                    step3(b * args.steps + i)
+                e1.record()
+                barrier()
+                ms3.append(e0.elapsed_time(e1))
+            t3 = torch.tensor(ms3, dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(t3, op=dist.ReduceOp.MAX)
+            m3 = statistics.median(t3.tolist())
+            fp32 = {"kernels": "umma3x", "dtype": "fp32-accurate: three tf32 tcgen05.mma per product on operands split "
+                    "in shared memory, fp32 accumulate", "value": round(B * world * args.steps / (m3 / 1e3), 1),
+                    "ms_per_step": round(m3 / args.steps, 5), "loss_last": round(float(tr3.engine.loss_sum.item()) / B, 4)}
+            del tr3, dx3, dy3, dc3
+            torch.cuda.empty_cache()
+            if base and "value" in base:
+                from baseline.torch_baseline import measure as measure_torch
+                b32 = measure_torch(args, rank, world, dev, BLOCKS, tf32=False, e2e=False)
+                fp32["library_fp32_value"] = round(b32["value"], 1)
+                fp32["library_fp32_ms_per_step"] = round(b32["ms_per_step"], 5)
+                fp32["ratio_vs_library_fp32"] = round(fp32["value"] / b32["value"], 3)
+        except Exception as ex:
+            fp32 = {"error": repr(ex)[:200]}
+
     if rank == 0:
         n_params = tr.engine.layout.n_flat
         peaks = {}
@@ -271,7 +319,8 @@ def main():
             "value": round(value, 1), "unit": "samples/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_max / args.steps, 5),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": vsb, "vs_baseline_detail": detail,
-            "dtype": "tf32 (fp32 storage, fp32 accumulate)" if kernels == "umma" else "fp32",
+            "dtype": {"umma": "tf32 (fp32 storage, fp32 accumulate)",
+                      "umma3x": "fp32-accurate 3xTF32 (fp32 storage, three tf32 MMAs per product, fp32 accumulate)"}.get(kernels, "fp32"),
             "data": "synthetic CIFAR-10-shaped uint8 images, random-init weights",
             "impl": "mpit",
             "config": {"model": "CIFAR-10 7-layer CNN (asyncsgd/models/7-layers-cnn.lua, 351946 params)"
@@ -291,6 +340,7 @@ def main():
                     "d2h": "loss of step t stored into host-mapped pinned memory by the input kernel of step t+1 "
                            "(a copy for the newest step); read by the host every step, LAG=2 steps late"
                     if getattr(tr, "_stepper", None) is not None else "cudaMemcpyAsync of the loss every step"},
+            "fp32_accurate": fp32,
             "gpu_launches": int(launches_per_block),
             "clocks": _clock_summary(clk_path, local_rank, t_lo, t_hi),
             "loss": {"device_arm_last": round(loss_dev, 4), "e2e_arm_last": round(last, 4)},

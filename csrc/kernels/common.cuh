@@ -53,6 +53,7 @@ static inline int ew_grid(long long n_items, int threads, int items_per_thread =
 // Rule: a kernel launched through launch_k() must execute pdl_wait() in every thread before its first
 // global-memory access that could alias anything an earlier kernel reads or writes.
 extern int g_pdl_enabled;   // defined in optim.cu; mpit_set_pdl()
+extern int g_x3_mode;       // defined in optim.cu; mpit_set_tf32x3(): 0 plain TF32, 1 / 2 3xTF32 (umma.cuh)
 
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }

@@ -7,6 +7,7 @@
 namespace mpit {
 
 int g_pdl_enabled = 1;
+int g_x3_mode = 0;
 
 // ---------------------------------------------------------------------------------------
 // local_step: [apply(t)] -> [lookahead(t+1)] -> [pack] in one pass.
@@ -185,6 +186,12 @@ extern "C" {
 int mpit_set_pdl(int enabled) {
   int old = g_pdl_enabled;
   if (enabled >= 0) g_pdl_enabled = enabled ? 1 : 0;
+  return old;
+}
+
+int mpit_set_tf32x3(int mode) {
+  int old = g_x3_mode;
+  if (mode >= 0 && mode <= 2) g_x3_mode = mode;
   return old;
 }
 

@@ -66,6 +66,33 @@ __device__ __forceinline__ float4 lds4(uint32_t addr) {
 }
 
 // ---- TMA -------------------------------------------------------------------------------------------
+// ---- 3xTF32 (fp32-accurate products on the TF32 tensor pipe) -----------------------------------------------------
+// kind::tf32 reads fp32 words from shared memory and uses their upper 19 bits.  Splitting an operand tile into
+// hi = the part the tensor core keeps and lo = a - hi (exact in fp32, 13 significant bits at most), and issuing
+//   D += A_lo * B_hi;  D += A_hi * B_lo;  D += A_hi * B_hi      (fp32 accumulation in TMEM)
+// recovers the product to ~2^-21 relative; the dropped lo*lo term is below fp32 rounding.  The split is elementwise,
+// so it is independent of the tile's swizzle and major-ness: `split_tile` is run by the (otherwise idle) epilogue
+// warps on each landed stage, writing the lo tile next to the hi tile.  mode 1: the tensor core truncates, the tile
+// stays as it is and lo = a - trunc(a); mode 2: hi = cvt.rna.tf32(a) is written back in place and lo = a - hi.
+__device__ __forceinline__ float tf32_hi(float a, int mode) {
+  if (mode == 2) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(a));
+    return __uint_as_float(r);
+  }
+  return __uint_as_float(__float_as_uint(a) & 0xffffe000u);
+}
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+// tile_addr / lo_addr: shared-space addresses (16-byte aligned); bytes multiple of 16; tid in [0, nthreads).
+__device__ __forceinline__ void split_tile(uint32_t tile_addr, uint32_t lo_addr, int bytes, int tid, int nthreads, int mode) {
+  for (int off = tid * 16; off < bytes; off += nthreads * 16) {
+    const float4 v = lds4(tile_addr + off);
+    const float hx = tf32_hi(v.x, mode), hy = tf32_hi(v.y, mode), hz = tf32_hi(v.z, mode), hw = tf32_hi(v.w, mode);
+    if (mode == 2) sts4(tile_addr + off, hx, hy, hz, hw);
+    sts4(lo_addr + off, v.x - hx, v.y - hy, v.z - hz, v.w - hw);
+  }
+}
+
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap* m) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(m) : "memory");
 }

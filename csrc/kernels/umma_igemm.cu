@@ -50,6 +50,7 @@ struct IgemmParams {
   int* err;                  // set to 1 when a bounded pipeline wait expires
   float* colpart;            // optional [m_tiles][N]: per-tile column sums of the values written (MASK / EXPAND)
   int stages;                // smem pipeline depth (2..kMaxStages), chosen per launch
+  int x3;                    // 0: plain TF32; 1 / 2: 3xTF32 with the operand split done in shared memory (umma.cuh)
   long long* dbg;            // optional per-CTA timeline (16 clock64 stamps per CTA), null in production
 };
 
@@ -62,7 +63,8 @@ struct SmemLayout {
   static constexpr int kBBytes = BLOCK_N * 128;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kMaxFit = (kSmemBudget / kStageBytes) < kMaxStages ? (kSmemBudget / kStageBytes) : kMaxStages;
-  static constexpr int total(int stages) { return stages * kStageBytes + 256 + 1024; }   // + barriers + align slack
+  // + barriers + align slack; `mul` = 2 in 3xTF32 mode (every stage also holds the lo tiles)
+  static constexpr int total(int stages, int mul = 1) { return stages * kStageBytes * mul + 512 + 1024; }
 };
 
 // Out of line on purpose.  An epilogue runs once per CTA, so its code is fetched cold; with tanh and Philox
@@ -257,7 +259,8 @@ __device__ __forceinline__ void coalesced_epilogue(const IgemmParams& p, uint8_t
 // MODE (the epilogue) is a template parameter: with all five epilogues, 32-column unrolling, tanh and Philox
 // inlined in one body the kernel was ~100 KB of straight-line code that every CTA walks once, and the cold
 // instruction fetches cost more than the math (the "math" phase of a 32-column epilogue measured 1.2 us).
-template <int BLOCK_N, int MODE>
+// X3 (compile time, so that the TF32 kernels carry none of its code): 3xTF32 mode, see umma.cuh.
+template <int BLOCK_N, int MODE, bool X3 = false>
 __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CUtensorMap* tmap_b_p, const int b_row0,
                                            const IgemmParams& p) {
   const CUtensorMap& tmap_a = *tmap_a_p;
@@ -266,9 +269,12 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int kStages = p.stages;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * L::kStageBytes);
+  const int x3 = X3 ? p.x3 : 0;
+  constexpr int stage_bytes = X3 ? 2 * L::kStageBytes : L::kStageBytes;  // [A | B] or [A | B | A_lo | B_lo]
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * stage_bytes);
   uint64_t* empty_bar = full_bar + kMaxStages;
-  uint64_t* tmem_full = empty_bar + kMaxStages;
+  uint64_t* split_bar = empty_bar + kMaxStages;     // 3xTF32: lo tiles of the stage are written (128 arrivals)
+  uint64_t* tmem_full = split_bar + kMaxStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -287,7 +293,9 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
     org_n[j] = org_h[j] = org_w[j] = 0;
     if (j < p.nsub) subtile_origin(p, tile * p.nsub + j, org_n[j], org_h[j], org_w[j]);
   }
-  const int kProducers = kStages < 5 ? kStages : 5;
+  // 3xTF32: the epilogue warps split the landed tiles instead of issuing loads; the MMA side takes three times as
+  // long per k-block, so one issuing thread keeps up
+  const int kProducers = X3 ? 1 : (kStages < 5 ? kStages : 5);
   const int pi = warp == 0 ? 0 : warp - 1;          // warps 0,2,3,4,5 -> 0,1,2,3,4 (warp 1 issues the MMAs)
   int stage = 0, phase = 0, kh = 0, kw = 0, cblk = 0;
   auto advance = [&](int by) {
@@ -301,7 +309,11 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmap_a);
     prefetch_tmap(&tmap_b);
-    for (int i = 0; i < kStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+      if (X3) mbar_init(&split_bar[i], 128);
+    }
     mbar_init(tmem_full, 1);
     fence_barrier_init();
   }
@@ -344,7 +356,7 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
       // the first pass over the ring needs no wait: those slots have never been used
       if (kb >= kStages && !mbar_wait(&empty_bar[stage], phase ^ 1)) { if (p.err) *p.err = 1; break; }
       if (dbg && kb == 0) dbg[9] = clock64();   // first slot free
-      uint8_t* a_dst = smem + stage * L::kStageBytes;
+      uint8_t* a_dst = smem + stage * stage_bytes;
       mbar_expect_tx(&full_bar[stage], L::kStageBytes);
       tma_load_4d(a_dst, &tmap_a, &full_bar[stage], cblk * 32, ow0[0] + p.sgn * kw, oh0[0] + p.sgn * kh, n0[0]);
       if (p.nsub == 2)
@@ -357,6 +369,19 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
     if (dbg && warp == 0) dbg[2] = clock64();   // warp 0's last TMA issued
   }
   __syncwarp();
+  if (X3 && warp >= 2) {
+    // ===== 3xTF32: operand split, warps 2..5 =====
+    const int tid = threadIdx.x - 64;
+    int st = 0, ph = 0;
+    for (int kb = 0; kb < p.num_kb; ++kb) {
+      if (!mbar_wait(&full_bar[st], ph)) { if (p.err) *p.err = 4; break; }
+      const uint32_t base = smem_u32(smem) + st * stage_bytes;
+      split_tile(base, base + L::kStageBytes, L::kStageBytes, tid, 128, x3);
+      fence_proxy_async_smem();            // generic-proxy writes -> visible to the tensor core's async-proxy reads
+      mbar_arrive(&split_bar[st]);
+      if (++st == kStages) { st = 0; ph ^= 1; }
+    }
+  }
   if (warp == 0) {
     // nothing further: warp 0 only issues loads
   } else if (warp == 1) {
@@ -368,14 +393,24 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
       uint64_t ad = desc0;
       int stage = 0, phase = 0;
       for (int kb = 0; kb < p.num_kb; ++kb) {
-        if (!mbar_wait(&full_bar[stage], phase)) { if (p.err) *p.err = 2; break; }
+        if (!mbar_wait(X3 ? &split_bar[stage] : &full_bar[stage], phase)) { if (p.err) *p.err = 2; break; }
         if (dbg && kb == 0) dbg[3] = clock64();   // first operands landed
         tc_fence_after();
         const uint64_t bd = ad + (kABytes >> 4);
+        if (X3) {
+          const uint64_t lo = (uint64_t)(L::kStageBytes >> 4);     // lo tiles sit one [A | B] block further
 #pragma unroll
-        for (int k = 0; k < 4; ++k) mma_tf32(tmem_base, ad + 2 * k, bd + 2 * k, idesc, (kb | k) ? 1u : 0u);
+          for (int k = 0; k < 4; ++k) {
+            mma_tf32(tmem_base, ad + lo + 2 * k, bd + 2 * k, idesc, (kb | k) ? 1u : 0u);     // A_lo * B_hi
+            mma_tf32(tmem_base, ad + 2 * k, bd + lo + 2 * k, idesc, 1u);                     // A_hi * B_lo
+            mma_tf32(tmem_base, ad + 2 * k, bd + 2 * k, idesc, 1u);                          // A_hi * B_hi
+          }
+        } else {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) mma_tf32(tmem_base, ad + 2 * k, bd + 2 * k, idesc, (kb | k) ? 1u : 0u);
+        }
         mma_commit(&empty_bar[stage]);   // frees the smem slot once these MMAs have read it
-        ad += (L::kStageBytes >> 4);
+        ad += (stage_bytes >> 4);
         if (++stage == kStages) { stage = 0; phase ^= 1; ad = desc0; }
       }
       mma_commit(tmem_full);             // accumulator complete
@@ -474,11 +509,11 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap* tmap_a_p, const CU
   if (dbg && threadIdx.x == 0) dbg[7] = clock64();
 }
 
-template <int BLOCK_N, int MODE>
+template <int BLOCK_N, int MODE, bool X3>
 __global__ void __launch_bounds__(192)
 umma_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                   const IgemmParams p) {
-  igemm_body<BLOCK_N, MODE>(&tmap_a, &tmap_b, blockIdx.y * BLOCK_N, p);
+  igemm_body<BLOCK_N, MODE, X3>(&tmap_a, &tmap_b, blockIdx.y * BLOCK_N, p);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -639,30 +674,41 @@ static decltype(&cuTensorMapEncodeTiled) get_encode() {
   return fn;
 }
 
-template <int BLOCK_N, int MODE>
-static int launch_igemm(const CUtensorMap* ta, const CUtensorMap* tb, IgemmParams p, int m_tiles,
-                        cudaStream_t st) {
+template <int BLOCK_N, int MODE, bool X3>
+static int launch_igemm_x(const CUtensorMap* ta, const CUtensorMap* tb, IgemmParams p, int m_tiles,
+                          cudaStream_t st) {
   using L = SmemLayout<BLOCK_N>;
   static unsigned long long attr_done = 0;   // bit per device
-  MPIT_CUDA_TRY(set_smem_limit_per_device(umma_igemm_kernel<BLOCK_N, MODE>, L::total(L::kMaxFit), attr_done));
+  MPIT_CUDA_TRY(set_smem_limit_per_device(umma_igemm_kernel<BLOCK_N, MODE, X3>, L::total(L::kMaxFit), attr_done));
   dim3 grid(m_tiles, p.N / BLOCK_N);
   // Pipeline depth.  Grids of up to one CTA per SM get the deepest pipeline that fits.  Larger grids are better
   // served by residency: make the stages small enough that ceil(ctas/148) CTAs (up to 4) share an SM, so the whole
   // grid is one wave and one CTA's epilogue overlaps another's loads (conv1: 576 short CTAs, 2 stages each).
   int ctas = m_tiles * (p.N / BLOCK_N);
-  int stages = L::kMaxFit;
+  constexpr int mul = X3 ? 2 : 1;               // 3xTF32: every stage also holds the lo tiles
+  const int max_fit = L::kMaxFit / mul;
+  int stages = max_fit;
   if (ctas > MPIT_NUM_SMS) {
     int per_sm = (ctas + MPIT_NUM_SMS - 1) / MPIT_NUM_SMS;
     if (per_sm > 4) per_sm = 4;
-    int fit = ((226 * 1024) / per_sm - 2560) / L::kStageBytes;
+    int fit = ((226 * 1024) / per_sm - 2560) / (L::kStageBytes * mul);
     if (fit < stages) stages = fit;
   }
   if (stages > p.num_kb) stages = p.num_kb;
   if (stages < 2) stages = 2;
-  if (stages > L::kMaxFit) stages = L::kMaxFit;
+  if (stages > max_fit) stages = max_fit;
   p.stages = stages;
-  MPIT_CUDA_TRY(launch_k(umma_igemm_kernel<BLOCK_N, MODE>, grid, dim3(192), (size_t)L::total(stages), st, *ta, *tb, p));
+  MPIT_CUDA_TRY(launch_k(umma_igemm_kernel<BLOCK_N, MODE, X3>, grid, dim3(192), (size_t)L::total(stages, mul), st, *ta, *tb, p));
   return 0;
+}
+
+template <int BLOCK_N, int MODE>
+static int launch_igemm(const CUtensorMap* ta, const CUtensorMap* tb, const IgemmParams& p, int m_tiles, cudaStream_t st) {
+  if (p.x3) {
+    if (MODE == EPI_MAXTIME) return MPIT_E_UNSUPPORTED;      // the sentence-CNN epilogue has no 3xTF32 instantiation
+    return launch_igemm_x<BLOCK_N, MODE == EPI_MAXTIME ? EPI_STORE : MODE, true>(ta, tb, p, m_tiles, st);
+  }
+  return launch_igemm_x<BLOCK_N, MODE, false>(ta, tb, p, m_tiles, st);
 }
 
 }  // namespace mpit
@@ -715,6 +761,7 @@ int mpit_umma_igemm(const void* tmap_a128, const void* tmap_b128, const int* geo
   p.N = geom17[13]; p.mode = geom17[14]; p.relu = geom17[15]; p.dropout = geom17[16];
   p.scale = scale; p.bias = bias; p.out = out; p.idx = idx; p.aux = aux; p.aux_idx = aux_idx;
   p.crop = crop; p.rng = rng; p.err = err; p.colpart = colpart;
+  p.x3 = g_x3_mode;
   if (p.nsub < 1 || p.nsub > 2 || p.nsub * p.tw * p.th * p.tn != 128 || p.num_kb < 1 || p.N % block_n != 0)
     return MPIT_E_ARG;
   if (p.mode == EPI_POOL && (p.tw > 16 || (p.tw & 1) || (p.th & 1))) return MPIT_E_ARG;

@@ -39,6 +39,7 @@ struct WgradParams {
   float* part;               // scratch [split][m_pad][N]
   const int* crop;
   int* err;
+  int x3;                    // 0 plain TF32; 1 / 2: 3xTF32, operands split in shared memory (umma.cuh)
 };
 
 constexpr int kWStages = 3;
@@ -51,9 +52,11 @@ struct WSmem {
   static constexpr int kStageBytes = kWABytes + kBBytes;
   static constexpr int kBarOff = kWStages * kStageBytes;
   static constexpr int kTotal = kBarOff + 256 + 1024;
+  // 3xTF32: a stage is [A | B | A_lo | B_lo]; two stages of BLOCK_N <= 64 fit, BLOCK_N = 128 has room for one only
+  static constexpr int kStages3 = (kBarOff / (2 * kStageBytes)) < 2 ? (kBarOff / (2 * kStageBytes)) : 2;
 };
 
-template <int BLOCK_N>
+template <int BLOCK_N, bool X3 = false>
 __global__ void __launch_bounds__(192)
 umma_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_dz,
                   const WgradParams p) {
@@ -62,8 +65,12 @@ umma_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
   uint64_t* empty_bar = full_bar + kWStages;
-  uint64_t* tmem_full = empty_bar + kWStages;
+  uint64_t* split_bar = empty_bar + kWStages;
+  uint64_t* tmem_full = split_bar + kWStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  const int x3 = X3 ? p.x3 : 0;
+  constexpr int nstages = X3 ? L::kStages3 : kWStages;
+  constexpr int stage_bytes = X3 ? 2 * L::kStageBytes : L::kStageBytes;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m_tile = blockIdx.x;
@@ -78,7 +85,7 @@ umma_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
 
   pdl_trigger();
   // parameter-only producer set-up (integer divisions) goes BEFORE the wait on the previous kernel
-  const int pj = warp == 0 ? 0 : warp - 1;     // issuing threads: warps 0,2,3,4 -> 0,1,2,3
+  const int pj = warp == 0 ? 0 : warp - 1;     // issuing threads: warps 0,2,3,4 -> 0,1,2,3 (3xTF32: warp 0 alone)
   const int per_kh = p.kw_it * p.cb;
   const int ch = m_tile * 4 + pj;
   const int ckh = ch / per_kh, rch = ch - ckh * per_kh;
@@ -89,7 +96,11 @@ umma_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmap_x);
     prefetch_tmap(&tmap_dz);
-    for (int i = 0; i < kWStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    for (int i = 0; i < kWStages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+      if (X3) mbar_init(&split_bar[i], 128);
+    }
     mbar_init(tmem_full, 1);
     fence_barrier_init();
   }
@@ -107,7 +118,33 @@ umma_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
   // producer j issues A chunk j and B chunk j of EVERY k-block, producer 0 also posts the expect_tx.  Each
   // producer walks the k-blocks in order, so the empty-barrier parity test stays unambiguous.
   const bool has_a = pj < nchunks, has_b = pj < BLOCK_N / 32;
-  if (warp != 1 && pj < 4 && (has_a || has_b || pj == 0) && elect_one()) {
+  if (X3) {
+    // 3xTF32: warps 2..5 split the landed tiles, so warp 0 issues every chunk of a k-block itself (the MMA side
+    // needs three times as long per k-block, the feed is not the bound)
+    if (warp == 0 && elect_one()) {
+      const uint32_t bytes = (uint32_t)(nchunks * kChunkBytes + L::kBBytes);
+      int grp = grp0, th_i = th0, tw_i = tw0;
+      int stage = 0, phase = 0;
+      for (int kb = kb_lo; kb < kb_hi; ++kb) {
+        const int n0 = grp * p.tn, oh0 = th_i * p.th, ow0 = tw_i * p.tw;
+        int y0 = 0, x0 = 0;
+        if (p.crop && n0 < p.B) { y0 = p.crop[2 * n0]; x0 = p.crop[2 * n0 + 1]; }
+        if (kb - kb_lo >= nstages && !mbar_wait(&empty_bar[stage], phase ^ 1)) { if (p.err) *p.err = 11; break; }
+        uint8_t* a_dst = smem + stage * stage_bytes;
+        mbar_expect_tx(&full_bar[stage], bytes);
+        for (int j = 0; j < nchunks; ++j) {
+          const int chj = m_tile * 4 + j;
+          const int kh_j = chj / per_kh, rj = chj - kh_j * per_kh;
+          const int kw_j = rj / p.cb, cc_j = (rj - kw_j * p.cb) * 32;
+          tma_load_4d(a_dst + j * kChunkBytes, &tmap_x, &full_bar[stage], cc_j, ow0 + kw_j + x0, oh0 + kh_j + y0, n0);
+        }
+        for (int j = 0; j < BLOCK_N / 32; ++j)
+          tma_load_4d(a_dst + kWABytes + j * kChunkBytes, &tmap_dz, &full_bar[stage], n_tile0 + j * 32, ow0, oh0, n0);
+        if (++stage == nstages) { stage = 0; phase ^= 1; }
+        if (++tw_i == p.tiles_w) { tw_i = 0; if (++th_i == p.tiles_h) { th_i = 0; ++grp; } }
+      }
+    }
+  } else if (warp != 1 && pj < 4 && (has_a || has_b || pj == 0) && elect_one()) {
     const uint32_t bytes = (uint32_t)(nchunks * kChunkBytes + L::kBBytes);
     // k-block -> (image group, tile row, tile column), kept incrementally
     int grp = grp0, th_i = th0, tw_i = tw0;
@@ -135,6 +172,20 @@ umma_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
     }
   }
   __syncwarp();
+  if (X3 && warp >= 2) {
+    // ===== 3xTF32: operand split, warps 2..5 (rows of chunks this tile does not own are never loaded: whatever
+    // they hold only reaches accumulator rows that the epilogue zeroes) =====
+    const int tid = threadIdx.x - 64;
+    int st = 0, ph = 0;
+    for (int i = 0; i < nkb; ++i) {
+      if (!mbar_wait(&full_bar[st], ph)) { if (p.err) *p.err = 14; break; }
+      const uint32_t base = smem_u32(smem) + st * stage_bytes;
+      split_tile(base, base + L::kStageBytes, L::kStageBytes, tid, 128, x3);
+      fence_proxy_async_smem();
+      mbar_arrive(&split_bar[st]);
+      if (++st == nstages) { st = 0; ph ^= 1; }
+    }
+  }
   if (warp == 0) {
     // warp 0 only issues loads
   } else if (warp == 1) {
@@ -145,15 +196,26 @@ umma_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
       uint64_t ad = desc0;
       int stage = 0, phase = 0;
       for (int i = 0; i < nkb; ++i) {
-        if (!mbar_wait(&full_bar[stage], phase)) { if (p.err) *p.err = 12; break; }
+        if (!mbar_wait(X3 ? &split_bar[stage] : &full_bar[stage], phase)) { if (p.err) *p.err = 12; break; }
         tc_fence_after();
         const uint64_t bd = ad + (kWABytes >> 4);
+        if (X3) {
+          const uint64_t lo = (uint64_t)(L::kStageBytes >> 4);
 #pragma unroll
-        for (int ks = 0; ks < 8; ++ks)     // 8 pixels per MMA
-          mma_tf32(tmem_base, ad + ks * (1024 >> 4), bd + ks * (1024 >> 4), idesc, (i | ks) ? 1u : 0u);
+          for (int ks = 0; ks < 8; ++ks) {
+            const uint64_t o = ks * (1024 >> 4);
+            mma_tf32(tmem_base, ad + lo + o, bd + o, idesc, (i | ks) ? 1u : 0u);     // A_lo * B_hi
+            mma_tf32(tmem_base, ad + o, bd + lo + o, idesc, 1u);                     // A_hi * B_lo
+            mma_tf32(tmem_base, ad + o, bd + o, idesc, 1u);                          // A_hi * B_hi
+          }
+        } else {
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)     // 8 pixels per MMA
+            mma_tf32(tmem_base, ad + ks * (1024 >> 4), bd + ks * (1024 >> 4), idesc, (i | ks) ? 1u : 0u);
+        }
         mma_commit(&empty_bar[stage]);
-        ad += (L::kStageBytes >> 4);
-        if (++stage == kWStages) { stage = 0; phase ^= 1; ad = desc0; }
+        ad += (stage_bytes >> 4);
+        if (++stage == nstages) { stage = 0; phase ^= 1; ad = desc0; }
       }
       mma_commit(tmem_full);
     }
@@ -324,10 +386,16 @@ template <int BLOCK_N>
 static int launch_wgrad(const CUtensorMap& tx, const CUtensorMap& tz, const WgradParams& p, int m_tiles,
                         int nsplit, cudaStream_t st) {
   using L = WSmem<BLOCK_N>;
-  static unsigned long long attr_done = 0;   // bit per device
-  MPIT_CUDA_TRY(set_smem_limit_per_device(umma_wgrad_kernel<BLOCK_N>, L::kTotal, attr_done));
   dim3 grid(m_tiles, p.N / BLOCK_N, nsplit);
-  MPIT_CUDA_TRY(launch_k(umma_wgrad_kernel<BLOCK_N>, grid, dim3(192), (size_t)L::kTotal, st, tx, tz, p));
+  if (p.x3) {
+    static unsigned long long attr_done3 = 0;   // bit per device
+    MPIT_CUDA_TRY(set_smem_limit_per_device(umma_wgrad_kernel<BLOCK_N, true>, L::kTotal, attr_done3));
+    MPIT_CUDA_TRY(launch_k(umma_wgrad_kernel<BLOCK_N, true>, grid, dim3(192), (size_t)L::kTotal, st, tx, tz, p));
+    return 0;
+  }
+  static unsigned long long attr_done = 0;   // bit per device
+  MPIT_CUDA_TRY(set_smem_limit_per_device(umma_wgrad_kernel<BLOCK_N, false>, L::kTotal, attr_done));
+  MPIT_CUDA_TRY(launch_k(umma_wgrad_kernel<BLOCK_N, false>, grid, dim3(192), (size_t)L::kTotal, st, tx, tz, p));
   return 0;
 }
 
@@ -349,6 +417,7 @@ int mpit_umma_wgrad(const void* tmap_x128, const void* tmap_dz128, const int* ge
   int m_tiles = (p.total_chunks + 3) / 4;
   p.m_pad = m_tiles * 128;
   p.part = part; p.crop = crop; p.err = err;
+  p.x3 = g_x3_mode;
   CUtensorMap tx, tz;
   memcpy(&tx, tmap_x128, sizeof(tx));
   memcpy(&tz, tmap_dz128, sizeof(tz));
@@ -466,13 +535,13 @@ int noalloc_setup_current_device(float** out) {
     e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
     if (e != cudaSuccess) return (int)e;
     if (!p) return MPIT_E_UNSUPPORTED;
-    e = cudaFuncSetAttribute(mpit::umma_wgrad_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    e = cudaFuncSetAttribute(mpit::umma_wgrad_kernel<32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              mpit::WSmem<32>::kTotal);
     if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(mpit::umma_wgrad_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    e = cudaFuncSetAttribute(mpit::umma_wgrad_kernel<64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              mpit::WSmem<64>::kTotal);
     if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(mpit::umma_wgrad_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    e = cudaFuncSetAttribute(mpit::umma_wgrad_kernel<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              mpit::WSmem<128>::kTotal);
     if (e != cudaSuccess) return (int)e;
     g_noalloc_ptr[dev] = p;

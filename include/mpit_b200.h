@@ -32,6 +32,13 @@ extern "C" {
  * enabled: 1 on, 0 off, <0 query only.  Returns the previous setting.  Takes effect for launches
  * (and graph captures) made after the call.  No reference counterpart. */
 int mpit_set_pdl(int enabled);
+/* Precision of the tensor-core layer kernels launched from now on (mpit_umma_igemm, mpit_umma_wgrad): 0 = TF32
+ * products (default), 1 / 2 = 3xTF32: every operand tile is split in shared memory into the part the tensor core
+ * keeps and the exact remainder and three MMAs are issued per k-step (hi*lo, lo*hi, hi*hi), which gives products
+ * of fp32 accuracy on the TF32 pipe -- the reference computes in fp32 (Torch FloatTensor / CudaTensor SGEMM).
+ * 1 assumes the tensor core truncates its fp32 input, 2 rounds the hi part to nearest explicitly.  Returns the
+ * previous mode; a negative argument only queries. */
+int mpit_set_tf32x3(int mode);
 
 /* ---- optimizer rules (csrc/kernels/optim.cu) ------------------------------------------ */
 

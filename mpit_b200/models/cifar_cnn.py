@@ -21,6 +21,7 @@ captured into a CUDA graph, with:
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass
 from typing import List, Optional
 
@@ -291,7 +292,14 @@ class CifarEngine:
         self.confusion = torch.zeros(self.ncls, self.ncls, dtype=torch.int32, device=dev)
         self.rng = torch.tensor([seed, 0], dtype=torch.int64, device=dev)
         self._umma = None
-        if impl == "umma":
+        # umma3x: the same tcgen05 kernels issuing three MMAs per k-step on operands split in shared memory
+        # (products of fp32 accuracy, the reference's precision; see mpit_set_tf32x3 in include/mpit_b200.h).
+        # The mode is a per-launch property carried by a process-wide setting, so every schedule below sets it first
+        # (captured graphs keep the mode they were captured with).
+        from .._native import kernels as _kernels
+        self.k = _kernels()
+        self.x3 = {"umma": 0, "umma3x": int(os.environ.get("MPIT_X3_MODE", "1"))}.get(impl, 0)
+        if impl in ("umma", "umma3x"):
             from ..ops import umma_ops
             self._umma = umma_ops.CifarUmmaPlan(self)
 
@@ -350,6 +358,7 @@ class CifarEngine:
         layer."""
         ops, B = self.ops, self.B
         if self._umma is not None:
+            self.k.mpit_set_tf32x3(self.x3)
             self._umma.forward(train, classifier)
         else:
             src = self.x0
@@ -377,6 +386,7 @@ class CifarEngine:
     def backward(self) -> None:
         ops, B = self.ops, self.B
         if self._umma is not None:
+            self.k.mpit_set_tf32x3(self.x3)
             self._umma.backward()
             return
         for i in range(len(self.layers) - 1, -1, -1):

@@ -49,7 +49,8 @@ def _run(impl, B=16, train=True, tol=2e-4):
         # TF32 forward flips a few ReLU / max-pool decisions, which moves the gradient by a few
         # per cent in L2 although every kernel is within 1e-3 of fp32 on identical inputs (see the
         # layer-wise tests); the exact-fp32 path has to match tightly.
-        assert float((got_g - ref_g).norm() / ref_g.norm()) < (10 * tol if impl == "ref" else 0.15)
+        limit = {"ref": 10 * tol, "umma3x": 2e-2}.get(impl, 0.15)
+        assert float((got_g - ref_g).norm() / ref_g.norm()) < limit, float((got_g - ref_g).norm() / ref_g.norm())
         # about half of the active units are dropped
         frac = float((a4 > 0).float().mean())
         assert 0.05 < frac < 0.6
@@ -100,6 +101,73 @@ def test_engine_umma_forward_matches_ref_kernels():
     for i in (0, 1):
         same = float((engs["umma"].idx[i] == engs["ref"].idx[i]).float().mean())
         assert same > 0.995, (i, same)
+
+
+def test_engine_3xtf32_train_matches_torch_cpu():
+    """The fp32-accurate tensor-core arm (three TF32 MMAs per product on operands split in shared memory) against the
+    PyTorch CPU fp32 oracle: logits to 2e-4 and the whole gradient to 2e-2 relative L2.  The remaining gradient error is
+    not arithmetic: two fp32 implementations that sum in different orders disagree on the sign of a pre-activation
+    that is within ~1e-6 of zero, and ONE such ReLU decision in a batch of 16 re-routes about 1 % of the gradient (the
+    TF32 arm needs 0.15 here).  The arithmetic itself is checked on identical decisions by the next test."""
+    eng = _run("umma3x", train=True, tol=2e-4)
+    eng._umma.check()
+
+
+def test_engine_3xtf32_backward_on_identical_decisions_is_fp32_accurate():
+    """Backward pass of the 3xTF32 arm fed with the exact-fp32 path's activations, pool indices and loss gradient (so
+    both make the same ReLU / max-pool decisions): every data gradient and the full parameter gradient agree with the
+    fp32 CUDA-core kernels to 1e-4 relative L2; the TF32 arm is two orders of magnitude further away."""
+    torch.manual_seed(0)
+    B = 16
+    theta = flat_from_torch(TorchCifarCNN()).cuda()
+    images = torch.randint(0, 256, (B, 3, 32, 32), dtype=torch.uint8)
+    labels = torch.randint(0, NUM_CLASSES, (B,), dtype=torch.int32)
+    crop = random_crop_offsets(B)
+    engs = {}
+    for impl in ("ref", "umma", "umma3x"):
+        e = CifarEngine(B, impl=impl, seed=7)
+        e.load_flat(theta.clone())
+        e.set_batch(images, labels, crop)
+        e.fwd_bwd()
+        torch.cuda.synchronize()
+        engs[impl] = e
+    ref = engs["ref"]
+    err = {}
+    for impl in ("umma", "umma3x"):
+        e = engs[impl]
+        for i in range(5):
+            e.act[i].copy_(ref.act[i])
+            if e.idx[i] is not None:
+                e.idx[i].copy_(ref.idx[i])
+            e.dz[i].copy_(ref.dz[i])
+        e.gpk.zero_()
+        e.backward()
+        torch.cuda.synchronize()
+        e._umma.check()
+        err[impl] = {"dz": [_rel_l2(e.dz[i], ref.dz[i]) for i in range(3)],
+                     "gw": [_rel_l2(e.gw(i), ref.gw(i)) for i in range(4)]}
+    assert max(err["umma3x"]["dz"]) < 1e-4 and max(err["umma3x"]["gw"]) < 1e-4, err
+    assert max(err["umma3x"]["gw"]) < 0.05 * max(err["umma"]["gw"]), err
+
+
+def test_engine_3xtf32_forward_is_closer_to_fp32_than_tf32():
+    torch.manual_seed(1)
+    B = 16
+    theta = flat_from_torch(TorchCifarCNN()).cuda()
+    images = torch.randint(0, 256, (B, 3, 32, 32), dtype=torch.uint8)
+    labels = torch.randint(0, NUM_CLASSES, (B,), dtype=torch.int32)
+    crop = random_crop_offsets(B)
+    acts = {}
+    for impl in ("ref", "umma", "umma3x"):
+        e = CifarEngine(B, impl=impl, seed=3)
+        e.load_flat(theta.clone())
+        e.set_batch(images, labels, crop)
+        e.forward(False)
+        torch.cuda.synchronize()
+        acts[impl] = [a.clone() for a in e.act]
+    for i in range(5):
+        e1, e3 = _rel_l2(acts["umma"][i], acts["ref"][i]), _rel_l2(acts["umma3x"][i], acts["ref"][i])
+        assert e3 < 2e-5 and e3 < 0.1 * e1, (i, e1, e3)
 
 
 def test_engine_umma_train_matches_torch_cpu():
