@@ -340,6 +340,33 @@ __global__ void __launch_bounds__(256) peer_rma_kernel(int op, float* remote, fl
   }
 }
 
+// Gradient push for a Linear layer whose weight W [N][K] is row-sharded over the owners (ops/pulled_linear.py):
+// W_owner += scale * g on the owner's rows (vector red.add along k) AND on the owner's transposed copy
+// [K][rows_per_owner] that the data-gradient GEMM reads (scalar red.add), so both layouts stay equal without a
+// transpose pass on the owner.  Reference: pclient.lua:49-59 + pserver.lua:91 (p += g on the server).
+__global__ void __launch_bounds__(256)
+pulled_push_kernel(PeerTable wf, PeerTable wd, const float* __restrict__ g, int N, int K, int rpo, float scale) {
+  const long long nq = (long long)N * (K >> 2);
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  // rows are dealt starting at the owner after this rank, like the other exchanges
+  for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < nq; q += stride) {
+    const int kq = K >> 2;
+    int n = (int)(q / kq);
+    const int k4 = (int)(q - (long long)n * kq) * 4;
+    n += (wf.rank + 1) * rpo;
+    if (n >= N) n -= N;
+    const int owner = n / rpo, nl = n - owner * rpo;
+    float4 v = ld4_stream(g + (size_t)n * K + k4);
+    v.x *= scale; v.y *= scale; v.z *= scale; v.w *= scale;
+    red_add_sys4(wf.peer[owner] + (size_t)nl * K + k4, v);
+    float* t = wd.peer[owner] + (size_t)k4 * rpo + nl;
+    red_add_sys(t, v.x);
+    red_add_sys(t + rpo, v.y);
+    red_add_sys(t + 2 * rpo, v.z);
+    red_add_sys(t + 3 * rpo, v.w);
+  }
+}
+
 static int exch_grid(const QuadWalk& w) { return ew_grid(w.total, 256, 1, 8); }
 
 }  // namespace mpit
@@ -435,6 +462,16 @@ int mpit_downpour_fused_step(const unsigned long long* shard_ptrs, int nranks, i
   a.x = x; a.src = acc; a.g = g; a.gmap = gmap; a.wpk = wpk; a.wmap = wmap; a.nmaps = nmaps; a.n = n;
   a.clr = neg_lr; a.l2wd = l2wd; a.do_sync = do_sync;
   exchange_kernel<EX_DOWNPOUR><<<exch_grid(a.walk), 256, 0, (cudaStream_t)stream>>>(a);
+  MPIT_LAUNCH_CHECK();
+  return 0;
+}
+
+int mpit_pulled_linear_push(const unsigned long long* wf_ptrs, const unsigned long long* wd_ptrs, int nranks, int rank,
+                            const float* g, int N, int K, float scale, void* stream) {
+  if (nranks < 1 || nranks > MPIT_MAX_RANKS || !g || N % nranks || K % 4) return MPIT_E_ARG;
+  PeerTable wf = make_table(wf_ptrs, 0, nranks, rank), wd = make_table(wd_ptrs, 0, nranks, rank);
+  pulled_push_kernel<<<ew_grid((long long)N * (K / 4), 256, 2, 4), 256, 0, (cudaStream_t)stream>>>(wf, wd, g, N, K,
+                                                                                                N / nranks, scale);
   MPIT_LAUNCH_CHECK();
   return 0;
 }

@@ -226,8 +226,9 @@ extern "C" int mpit_classifier_head(const float* x, const float* w, const float*
   if (grid > kHeadMaxCtas) grid = kHeadMaxCtas;
   cudaStream_t st = (cudaStream_t)stream;
   auto go = [&](auto kern) -> int {
-    static unsigned long long attr_done = 0;    // one per kernel instantiation (generic lambda); bit per device
-    MPIT_CUDA_TRY(set_smem_limit_per_device(kern, 160 * 1024, attr_done));
+    // set on every launch: a static flag inside a generic lambda turned out to be shared by all of its
+    // instantiations, which left every kernel variant but the first at the default 48 KB limit
+    MPIT_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
     MPIT_CUDA_TRY(launch_k(kern, dim3(grid), dim3(kHeadWarps * 32), smem, st, a));
     return 0;
   };

@@ -660,6 +660,109 @@ umma_igemm_pull_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
   igemm_body<BLOCK_N, EPI_STORE>(&tmap_a, &pm.map[owner], n_tile0 - owner * pm.rows_per_owner, p);
 }
 
+// The same idea as a plain GEMM kernel with reuse inside the CTA: one CTA owns up to MT 128-row M-tiles of the
+// activations (MT accumulators of BLOCK_N TMEM columns each), so every weight tile that crosses NVLink is fetched
+// ONCE per CTA and feeds MT * 4 MMAs -- the single-tile kernel above re-fetches it for every M-tile, which is what
+// made it lose to gather + GEMM from 512 rows up.  (TMA multicast loads here read only this GPU's memory, so sharing
+// a remote tile between CTAs is not an option; reuse across accumulators is.)
+//   BY_K = false (forward, y = act(x W^T + b)): W row-sharded, owner chosen by the output-column tile;
+//   BY_K = true  (data gradient, dx = dy W):   the reduction runs over W's rows, i.e. ACROSS owners; each owner also
+//                keeps its rows transposed ([in][rows_per_owner]), and the owner is chosen by the k-block.
+template <int BLOCK_N, int MT, bool BY_K>
+__global__ void __launch_bounds__(192)
+umma_pulled_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ PeerMaps pm,
+                        const IgemmParams p) {
+  constexpr int kBBytes = BLOCK_N * 128;
+  constexpr int kStage = MT * kABytes + kBBytes;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int kStages = p.stages;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * kStage);
+  uint64_t* empty_bar = full_bar + kMaxStages;
+  uint64_t* tmem_full = empty_bar + kMaxStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  __shared__ __align__(16) float bias_s[256];
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_tile0 = blockIdx.y * BLOCK_N;
+  const int m_tiles = (p.B + 127) / 128;
+  const int mt0 = blockIdx.x * MT;
+  const int mt_here = m_tiles - mt0 < MT ? m_tiles - mt0 : MT;
+  pdl_trigger();
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmap_a);
+    for (int i = 0; i < kStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    mbar_init(tmem_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, MT * BLOCK_N);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
+  if (warp >= 2)
+    for (int c = threadIdx.x - 64; c < BLOCK_N; c += 128) bias_s[c] = p.bias ? p.bias[n_tile0 + c] : 0.f;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      const int owner_n = BY_K ? 0 : n_tile0 / pm.rows_per_owner;
+      int stage = 0, phase = 0;
+      for (int kb = 0; kb < p.num_kb; ++kb) {
+        if (kb >= kStages && !mbar_wait(&empty_bar[stage], phase ^ 1)) { if (p.err) *p.err = 1; break; }
+        uint8_t* dst = smem + stage * kStage;
+        mbar_expect_tx(&full_bar[stage], (uint32_t)(mt_here * kABytes + kBBytes));
+        if (BY_K) {
+          const int owner = (kb * 32) / pm.rows_per_owner;
+          tma_load_2d(dst + MT * kABytes, &pm.map[owner], &full_bar[stage], kb * 32 - owner * pm.rows_per_owner, n_tile0);
+        } else {
+          tma_load_2d(dst + MT * kABytes, &pm.map[owner_n], &full_bar[stage], kb * 32,
+                      n_tile0 - owner_n * pm.rows_per_owner);
+        }
+        for (int mt = 0; mt < mt_here; ++mt)
+          tma_load_4d(dst + mt * kABytes, &tmap_a, &full_bar[stage], kb * 32, 0, 0, (mt0 + mt) * 128);
+        if (++stage == kStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      constexpr uint32_t idesc = make_idesc_tf32(128, BLOCK_N, 0, 0);
+      const uint64_t desc0 = make_smem_desc(smem_u32(smem), 16, 1024);
+      uint64_t ad = desc0;
+      int stage = 0, phase = 0;
+      for (int kb = 0; kb < p.num_kb; ++kb) {
+        if (!mbar_wait(&full_bar[stage], phase)) { if (p.err) *p.err = 2; break; }
+        tc_fence_after();
+        const uint64_t bd = ad + ((MT * kABytes) >> 4);
+        for (int mt = 0; mt < mt_here; ++mt) {
+          const uint64_t am = ad + (uint64_t)((mt * kABytes) >> 4);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            mma_tf32(tmem_base + (uint32_t)(mt * BLOCK_N), am + 2 * k, bd + 2 * k, idesc, (kb | k) ? 1u : 0u);
+        }
+        mma_commit(&empty_bar[stage]);
+        ad += (kStage >> 4);
+        if (++stage == kStages) { stage = 0; phase ^= 1; ad = desc0; }
+      }
+      mma_commit(tmem_full);
+    }
+  } else {
+    const int quad = warp & 3;
+    const int row = quad * 32 + lane;
+    for (int mt = 0; mt < mt_here; ++mt) {
+      const int n = (mt0 + mt) * 128 + row;
+      coalesced_epilogue<BLOCK_N, EPI_STORE>(p, smem, tmem_base + (uint32_t)(mt * BLOCK_N), tmem_full, mt == 0, quad, lane,
+                                             row, n, 0, 0, n < p.B, n_tile0, mt0 + mt, 0ull, 0ull, bias_s, nullptr);
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, MT * BLOCK_N);
+  }
+}
+
 // ---- host side -----------------------------------------------------------------------------------
 static decltype(&cuTensorMapEncodeTiled) get_encode() {
   static decltype(&cuTensorMapEncodeTiled) fn = nullptr;
@@ -709,6 +812,15 @@ static int launch_igemm(const CUtensorMap* ta, const CUtensorMap* tb, const Igem
     return launch_igemm_x<BLOCK_N, MODE == EPI_MAXTIME ? EPI_STORE : MODE, true>(ta, tb, p, m_tiles, st);
   }
   return launch_igemm_x<BLOCK_N, MODE, false>(ta, tb, p, m_tiles, st);
+}
+
+template <int BLOCK_N, int MT, bool BY_K>
+static int launch_pulled(dim3 grid, size_t smem, cudaStream_t st, const CUtensorMap& ta, const PeerMaps& pm,
+                         const IgemmParams& p) {
+  static unsigned long long done = 0;     // bit per device
+  MPIT_CUDA_TRY(set_smem_limit_per_device(umma_pulled_gemm_kernel<BLOCK_N, MT, BY_K>, 208 * 1024, done));
+  MPIT_CUDA_TRY(launch_k(umma_pulled_gemm_kernel<BLOCK_N, MT, BY_K>, grid, dim3(192), smem, st, ta, pm, p));
+  return 0;
 }
 
 }  // namespace mpit
@@ -829,13 +941,9 @@ int mpit_umma_conv_resident(const void* tmap_in128, const void* tmap_w128, const
   dim3 grid(p.B, p.N / block_n);
   cudaStream_t st = (cudaStream_t)stream;
   auto go = [&](auto kern) -> int {
-    static size_t attr_smem[64] = {0};   // per instantiation and per device: raise the opt-in limit to what this
-    int dev = 0;                          // launch needs (the kernel's static shared memory counts against the same 227 KB)
-    MPIT_CUDA_TRY(cudaGetDevice(&dev));
-    if (smem > attr_smem[dev & 63]) {
-      MPIT_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      attr_smem[dev & 63] = smem;
-    }
+    // the opt-in limit is raised on every launch to what it needs (the kernel's static shared memory counts against the
+    // same 227 KB); a static cache in this generic lambda would be shared by all of its instantiations
+    MPIT_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     MPIT_CUDA_TRY(launch_k(kern, grid, dim3(192), smem, st, ti, tw, p, r));
     return 0;
   };
@@ -894,6 +1002,49 @@ int mpit_umma_linear_pull(const void* tmap_a128, const void* tmaps_b, int nranks
   }
   MPIT_LAUNCH_CHECK();
   return 0;
+}
+
+// y[M][N] = act(x[M][K] W^T + b) (by_k = 0) or dx[M][N] = dy[M][K] W (by_k = 1) with W living row-sharded in the owners'
+// symmetric memory; see umma_pulled_gemm_kernel.  `tmap_a128`: 4-D map [K,1,1,Mpad] box [32,1,1,128] over the local
+// activations; `tmaps_b`: HOST array of nranks x 128 bytes, one map per owner (by_k = 0: [rows_per_owner][K] box
+// [32, block_n]; by_k = 1: the transposed shard [N][rows_per_owner] box [32, block_n]).  K is the reduction length,
+// N the number of output columns; mt = M-tiles per CTA (1, 2 or 4; block_n * mt <= 256).
+int mpit_umma_pulled_gemm(const void* tmap_a128, const void* tmaps_b, int nranks, int rows_per_owner, int by_k, int M,
+                          int K, int N, int relu, const float* bias, float* out, int* err, int block_n, int mt,
+                          void* stream) {
+  if (nranks < 1 || nranks > 8 || M < 1 || K % 32 || N % block_n || (block_n != 32 && block_n != 64) ||
+      (mt != 1 && mt != 2 && mt != 4))
+    return MPIT_E_ARG;
+  if (by_k ? (rows_per_owner % 32 != 0 || K != nranks * rows_per_owner)
+           : (rows_per_owner % block_n != 0 || N != nranks * rows_per_owner))
+    return MPIT_E_ARG;
+  IgemmParams p{};
+  p.nsub = 1; p.tw = 1; p.th = 1; p.tn = 128; p.tiles_w = 1; p.tiles_h = 1; p.kw_it = 1; p.cb = K / 32;
+  p.num_kb = K / 32; p.sgn = 1; p.B = M; p.OH = 1; p.OW = 1; p.N = N; p.mode = EPI_STORE; p.relu = relu;
+  p.scale = 1.f; p.bias = bias; p.out = out; p.err = err;
+  CUtensorMap ta;
+  PeerMaps pm;
+  memset(&pm, 0, sizeof(pm));
+  memcpy(&ta, tmap_a128, sizeof(CUtensorMap));
+  for (int i = 0; i < nranks; ++i) memcpy(&pm.map[i], static_cast<const char*>(tmaps_b) + 128 * i, sizeof(CUtensorMap));
+  pm.rows_per_owner = rows_per_owner;
+  const int m_tiles = (M + 127) / 128;
+  dim3 grid((m_tiles + mt - 1) / mt, N / block_n);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int stage_bytes = mt * kABytes + block_n * 128;
+  int stages = (200 * 1024) / stage_bytes;
+  if (stages > kMaxStages) stages = kMaxStages;
+  if (stages > p.num_kb) stages = p.num_kb;
+  if (stages < 2) stages = 2;
+  p.stages = stages;
+  const size_t smem = (size_t)stages * stage_bytes + 512 + 1024;
+#define MPIT_PULLED(BN, MTV)                                                                              \
+  if (block_n == BN && mt == MTV)                                                                         \
+    return by_k ? launch_pulled<BN, MTV, true>(grid, smem, st, ta, pm, p) : launch_pulled<BN, MTV, false>(grid, smem, st, ta, pm, p);
+  MPIT_PULLED(32, 1) MPIT_PULLED(32, 2) MPIT_PULLED(32, 4)
+  MPIT_PULLED(64, 1) MPIT_PULLED(64, 2) MPIT_PULLED(64, 4)
+#undef MPIT_PULLED
+  return MPIT_E_ARG;
 }
 
 }  // extern "C"

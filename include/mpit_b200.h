@@ -167,6 +167,10 @@ int mpit_allreduce(const unsigned long long* in_ptrs, unsigned long long in_mc,
 int mpit_downpour_fused_step(const unsigned long long* shard_ptrs, int nranks, int rank, float* x, float* acc,
                              const float* g, const int* gmap, float* wpk, const int* wmap, int nmaps, long long n,
                              float neg_lr, float l2wd, int do_sync, void* stream);
+/* Gradient push of a row-sharded Linear weight W [N][K] (ops/pulled_linear.py): owner(n)'s rows += scale * g[n][:]
+ * and the same values into its transposed copy [K][N/nranks] (read by the pulled data-gradient GEMM). */
+int mpit_pulled_linear_push(const unsigned long long* wf_ptrs, const unsigned long long* wd_ptrs, int nranks, int rank,
+                            const float* g, int N, int K, float scale, void* stream);
 /* Boundary of a synchronous-EASGD step in ONE kernel: mean over the ranks of the symmetric input (each rank's
  * parameters after its local update), x -= alpha (x - mean), then the Nesterov look-ahead of the next step
  * (v *= mom; x += v when v != NULL) and the refresh of the packed operand copy (wpk / wmap as in mpit_local_step).
@@ -288,6 +292,14 @@ int mpit_umma_conv_resident(const void* tmap_in128, const void* tmap_w128, const
  * kernel's TMA loads read each tile from its owner's shard. tmaps_b: HOST array of nranks x 128 bytes. */
 int mpit_umma_linear_pull(const void* tmap_a128, const void* tmaps_b, int nranks, int rows_per_owner,
                           const int* geom17, const float* bias, float* out, int* err, int block_n, void* stream);
+/* The same fusion with reuse inside the CTA and a backward: y = act(x W^T + b) (by_k = 0) or dx = dy W (by_k = 1),
+ * W row-sharded over the owners' symmetric memory.  One CTA owns mt (1, 2, 4) 128-row M-tiles, so each weight tile
+ * crosses NVLink once per CTA and feeds mt accumulators.  by_k = 1 reads the owners' TRANSPOSED shards
+ * ([out][rows_per_owner]); the reduction then runs across owners, chosen per k-block.  M rows of x / dy, reduction
+ * length K, N output columns; tmap_a128: 4-D map [K,1,1,Mpad] box [32,1,1,128]; tmaps_b: HOST array nranks x 128 B. */
+int mpit_umma_pulled_gemm(const void* tmap_a128, const void* tmaps_b, int nranks, int rows_per_owner, int by_k, int M,
+                          int K, int N, int relu, const float* bias, float* out, int* err, int block_n, int mt,
+                          void* stream);
 
 /* ---- tcgen05 weight gradients (csrc/kernels/umma_wgrad.cu) ------------------------------------- */
 /* dW = Xcol^T dZ over all output pixels, pixel dimension split over `nsplit` CTAs that each write a

@@ -12,7 +12,9 @@ Two paths:
 
       python -m mpit_b200.launch.run -np 4 -m mpit_b200.launch.mlaunch --device cpu
 
-``--model mnist`` runs the MNIST-shaped CNN (BASELINE.json config 2), ``--optim downpour`` its Downpour arm.
+``--model mnist`` runs the MNIST-shaped CNN (BASELINE.json config 2), ``--optim downpour`` its Downpour arm,
+``--optim sync_easgd`` / ``sync_eamsgd`` the synchronous all-reduce trainer; ``--model pulled_mlp`` trains a
+perceptron whose weights are never gathered (pull fused into the GEMMs, workloads/pulled_mlp.py).
 """
 from __future__ import annotations
 
@@ -27,7 +29,7 @@ def main(argv=None) -> int:
     ap = argparse.ArgumentParser()
     ap.add_argument("--device", default="cuda" if torch.cuda.is_available() else "cpu")
     ap.add_argument("--optim", default="eamsgd", choices=["eamsgd", "easgd", "downpour", "sync_easgd", "sync_eamsgd"])
-    ap.add_argument("--model", default="cifar", choices=["cifar", "mnist"])
+    ap.add_argument("--model", default="cifar", choices=["cifar", "mnist", "pulled_mlp"])
     ap.add_argument("--su", type=int, default=2)
     ap.add_argument("--lr", type=float, default=None)
     ap.add_argument("--mom", type=float, default=0.99)
@@ -60,6 +62,17 @@ def _gpu(a, lr) -> int:
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     heap = SymmetricHeap(dev)
+    if a.model == "pulled_mlp":
+        # weights stay sharded: every GEMM pulls its tiles from the owners in-kernel (workloads/pulled_mlp.py)
+        from ..workloads import pulled_mlp
+        sync = (lambda: (torch.cuda.synchronize(dev), dist.barrier(), torch.cuda.synchronize(dev))) if world > 1 else None
+        pulled_mlp.train(heap, batch=a.mb, steps=max(1, a.epochs) * 200, lr=a.lr if a.lr is not None else 0.05,
+                         barrier=sync)
+        heap.check_timeout()
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return 0
     opts = CifarOpts(name=a.optim, lr=lr, mom=a.mom, mb=a.mb, su=a.su, mva=0.9 / world, maxepoch=a.epochs,
                      save=a.save, seed=1 + rank, model=a.model)
     print(f"[client] rank {rank} use gpu {local}")

@@ -1,17 +1,23 @@
 """Linear layer whose weights are pulled from the sharded centre *inside* the GEMM (north-star item:
-"the parameter pull, fused with the first GEMM that consumes the fetched weights").
+"the parameter pull, fused with the first GEMM that consumes the fetched weights"), with its backward.
 
 The weight matrix ``W [out, in]`` is row-sharded over the ranks' symmetric memory (rank s owns rows
 ``[s*out/S, (s+1)*out/S)``, i.e. the reference's contiguous partition of the flat Linear weight when
-``out % S == 0``).  ``forward`` launches ONE tcgen05 kernel whose B-operand TMA loads read every weight
-tile from its owner's shard over NVLink while the tensor cores work on earlier tiles; no copy of W is
-ever materialised locally.  The un-fused formulation is ``ShardedCenter.pull`` followed by a GEMM.
+``out % S == 0``; reference sequence: pull, ``/root/reference/asyncsgd/pclient.lua:74-84``, then the first
+``nn.Linear`` forward of the model, ``asyncsgd/models/7-layers-cnn.lua:20``).
 
-Measured (tools/bench_pulled_linear.py): 1.5-3.4x faster than NCCL all_gather + cuBLAS at 2 and 8
-GPUs while the batch is one or two 128-row tiles; every further M-tile fetches its weight tiles again, so for
-M >= 512 the un-fused form wins.  The remedy is reuse inside the CTA (one CTA owning several 128-row M-tiles, i.e.
-more TMEM accumulator columns per fetched weight tile) or bringing the shard into local memory first; TMA multicast
-loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's memory hung the GPU.
+* ``forward`` launches ONE tcgen05 kernel whose B-operand TMA loads read every weight tile from its owner's shard
+  over NVLink while the tensor cores work on earlier tiles; no copy of W is ever materialised locally.  One CTA owns up
+  to four 128-row M-tiles of the batch (four TMEM accumulators), so a weight tile crosses NVLink once per CTA however
+  large the batch is.  (TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from
+  another GPU's memory hung the GPU -- hence reuse across accumulators instead of sharing a tile between CTAs.)
+* ``backward`` computes ``dx = dy W`` the same way: the reduction now runs over W's rows, i.e. across owners, and each
+  owner keeps its rows a second time transposed (``[in][rows]``) so that the tiles are K-major for the tensor core;
+  the owner of a k-block is chosen per k-block.
+* ``weight_grad`` is the local tcgen05 weight-gradient kernel; ``push`` adds ``scale * dW`` into the owners' rows AND
+  their transposed copies with ``red.add`` over NVLink (``pclient.lua:49-59`` + ``pserver.lua:91``).
+
+Measured (tools/bench_pulled_linear.py): against NCCL all_gather + cuBLAS.
 """
 from __future__ import annotations
 
@@ -22,37 +28,80 @@ import torch
 from .._native import kernels, check, ptr, cur_stream
 from .umma_ops import make_tmap, igemm_geom, weight_tmap, EPI_STORE
 
+MN_SWIZZLE = 2
+
+
+def _tiles_per_cta(m_tiles: int, col_tiles: int) -> int:
+    """M-tiles per CTA: as many as the batch has (up to four) -- every extra tile is a re-use of the weight tiles that
+    crossed NVLink -- but not so many that the grid falls under ~100 CTAs on 148 SMs."""
+    for mt in (4, 2):
+        if m_tiles >= mt and -(-m_tiles // mt) * col_tiles >= 96:
+            return mt
+    return 1
+
 
 class PulledLinear:
     def __init__(self, heap, in_features: int, out_features: int, max_rows: int, act: int = 0):
         S = heap.nranks
         assert in_features % 32 == 0 and out_features % (32 * S) == 0
         self.S, self.K, self.N = S, in_features, out_features
-        self.rows_per_owner = out_features // S
-        self.block_n = 64 if self.rows_per_owner % 64 == 0 else 32
-        self.shard = heap.alloc(self.rows_per_owner * in_features)       # my rows of W (symmetric)
+        self.rank = heap.rank
+        self.rows_per_owner = rpo = out_features // S
+        self.block_n = 64 if rpo % 64 == 0 else 32
+        # output-column tile of the data gradient: 32 columns unless that still leaves plenty of CTAs
+        self.block_k = 64 if (in_features % 64 == 0 and in_features // 64 >= 96) else 32
+        self.shard = heap.alloc(rpo * in_features)                  # my rows of W              [rpo][in]
+        self.shard_t = heap.alloc(rpo * in_features)                # the same rows, transposed [in][rpo]
         self.M = (max_rows + 127) // 128 * 128
         dev = self.shard.local.device
-        self.x = torch.zeros(self.M * in_features, device=dev)
-        self.y = torch.zeros(self.M * out_features, device=dev)
+        f32 = dict(dtype=torch.float32, device=dev)
+        self.x = torch.zeros(self.M * in_features, **f32)
+        self.y = torch.zeros(self.M * out_features, **f32)
+        self.dy = torch.zeros(self.M * out_features, **f32)
+        self.dx = torch.zeros(self.M * in_features, **f32)
+        self.gw = torch.zeros(out_features * in_features, **f32)
         self.err = torch.zeros(1, dtype=torch.int32, device=dev)
         self.act = act
-        maps = (ctypes.c_ubyte * (128 * S))()
-        for r, p in enumerate(self.shard.ptrs):       # one tensor map per owner, over the peer-mapped shard
-            m = make_tmap(p, [in_features, self.rows_per_owner], [in_features * 4], [32, self.block_n])
-            ctypes.memmove(ctypes.addressof(maps) + 128 * r, m, 128)
-        self._maps = maps
-        self._ta = make_tmap(self.x.data_ptr(), [in_features, 1, 1, self.M], [in_features * 4] * 3, [32, 1, 1, 128])
-        self._geom = igemm_geom(nsub=1, tw=1, th=1, tn=128, tiles_w=1, tiles_h=1, kw_it=1, cb=in_features // 32,
-                                num_kb=in_features // 32, sgn=1, B=self.M, OH=1, OW=1, N=out_features,
-                                mode=EPI_STORE, relu=act)
-        # Un-fused fallback for batches of more than FUSED_MAX_TILES 128-row tiles (every M-tile of the fused kernel
-        # fetches its weight tiles over NVLink again): gather W once with in-kernel peer loads, then a local GEMM.
+        K, N, M = in_features, out_features, self.M
+
+        def owner_maps(buf, inner, rows, box_rows):
+            maps = (ctypes.c_ubyte * (128 * S))()
+            for r, p in enumerate(buf.ptrs):          # one tensor map per owner, over the peer-mapped shard
+                m = make_tmap(p, [inner, rows], [inner * 4], [32, box_rows])
+                ctypes.memmove(ctypes.addressof(maps) + 128 * r, m, 128)
+            return maps
+
+        self._maps = owner_maps(self.shard, K, rpo, self.block_n)
+        self._maps_t = owner_maps(self.shard_t, rpo, K, self.block_k)
+        self._ta = make_tmap(self.x.data_ptr(), [K, 1, 1, M], [K * 4] * 3, [32, 1, 1, 128])
+        self._ta_dy = make_tmap(self.dy.data_ptr(), [N, 1, 1, M], [N * 4] * 3, [32, 1, 1, 128])
+        self._geom = igemm_geom(nsub=1, tw=1, th=1, tn=128, tiles_w=1, tiles_h=1, kw_it=1, cb=K // 32,
+                                num_kb=K // 32, sgn=1, B=M, OH=1, OW=1, N=N, mode=EPI_STORE, relu=act)
+        # weight gradient dW[n][k] = sum_m dy[m][n] x[m][k] on the tensor cores (MN-major operands)
+        nkb = M // 64
+        self._wg = dict(tx=make_tmap(self.x.data_ptr(), [K, 1, 1, M], [K * 4] * 3, [32, 1, 1, 64], MN_SWIZZLE),
+                        tz=make_tmap(self.dy.data_ptr(), [N, 1, 1, M], [N * 4] * 3, [32, 1, 1, 64], MN_SWIZZLE),
+                        geom=(ctypes.c_int * 11)(1, 1, 64, 1, 1, 1, K // 32, K // 32, nkb, M, N),
+                        block_n=64 if N % 64 == 0 else 32, nsplit=min(8, nkb), m_pad=-(-(K // 32) // 4) * 128)
+        self._part = torch.empty(self._wg["nsplit"] * self._wg["m_pad"] * N, **f32)
+        # un-fused fallback (gather with in-kernel peer loads, then a local GEMM), kept for comparison
         self._wfull = None
         self._tb_local = None
 
-    FUSED_MAX_TILES = 2
+    # -- weights -------------------------------------------------------------------------------------------------
+    def weight_rows(self) -> torch.Tensor:
+        """This rank's rows of W, as a [rows_per_owner, in] view of its symmetric shard."""
+        return self.shard.local[:self.rows_per_owner * self.K].view(self.rows_per_owner, self.K)
 
+    def weight_rows_t(self) -> torch.Tensor:
+        return self.shard_t.local[:self.rows_per_owner * self.K].view(self.K, self.rows_per_owner)
+
+    def load_rows(self, rows: torch.Tensor) -> None:
+        """Set this rank's rows (both layouts)."""
+        self.weight_rows().copy_(rows)
+        self.weight_rows_t().copy_(rows.t())
+
+    # -- forward ---------------------------------------------------------------------------------------------------
     def _forward_unfused(self, bias):
         k = kernels()
         if self._wfull is None:
@@ -64,20 +113,56 @@ class PulledLinear:
         check(k.mpit_umma_igemm(self._ta, self._tb_local, self._geom, 1.0, ptr(bias), ptr(self.y), None, None, None, None,
                                 None, ptr(self.err), None, self.block_n, cur_stream()), "mpit_umma_igemm")
 
-    def weight_rows(self) -> torch.Tensor:
-        """This rank's rows of W, as a [rows_per_owner, in] view of its symmetric shard."""
-        return self.shard.local[:self.rows_per_owner * self.K].view(self.rows_per_owner, self.K)
-
-    def forward(self, x: torch.Tensor, bias: torch.Tensor = None, fused: bool = None) -> torch.Tensor:
-        """``fused=None``: the fused kernel for up to FUSED_MAX_TILES row tiles, gather + GEMM beyond."""
+    def forward(self, x: torch.Tensor, bias: torch.Tensor = None, fused: bool = True, mt: int = 0) -> torch.Tensor:
+        """``y = act(x W^T + b)``.  ``fused=False`` runs the gather + GEMM formulation; ``mt`` overrides the number of
+        M-tiles per CTA (default: as many as the batch has, up to four)."""
         m = x.shape[0]
+        assert m <= self.M
+        self.m = m
         self.x[:m * self.K].copy_(x.reshape(-1))
-        if fused is None:
-            fused = (m + 127) // 128 <= self.FUSED_MAX_TILES
+        if m < self.M:
+            self.x[m * self.K:].zero_()
         if not fused:
             self._forward_unfused(bias)
             return self.y.view(self.M, self.N)[:m]
-        check(kernels().mpit_umma_linear_pull(self._ta, self._maps, self.S, self.rows_per_owner, self._geom, ptr(bias),
-                                              ptr(self.y), ptr(self.err), self.block_n, cur_stream()),
-              "mpit_umma_linear_pull")
+        mt = mt or _tiles_per_cta((m + 127) // 128, self.N // self.block_n)
+        check(kernels().mpit_umma_pulled_gemm(self._ta, self._maps, self.S, self.rows_per_owner, 0, m, self.K, self.N,
+                                              self.act, ptr(bias), ptr(self.y), ptr(self.err), self.block_n, mt,
+                                              cur_stream()), "mpit_umma_pulled_gemm")
         return self.y.view(self.M, self.N)[:m]
+
+    # -- backward --------------------------------------------------------------------------------------------------
+    def backward(self, dy: torch.Tensor) -> torch.Tensor:
+        """``dx = dy W`` for the batch of the last forward; ``dy`` is the gradient w.r.t. the pre-activation (the caller
+        applies the activation's derivative).  W's transposed shards are read from their owners inside the GEMM."""
+        m = dy.shape[0]
+        assert m == self.m
+        self.dy[:m * self.N].copy_(dy.reshape(-1))
+        if m < self.M:
+            self.dy[m * self.N:].zero_()
+        mt = _tiles_per_cta((m + 127) // 128, self.K // self.block_k)
+        check(kernels().mpit_umma_pulled_gemm(self._ta_dy, self._maps_t, self.S, self.rows_per_owner, 1, m, self.N,
+                                              self.K, 0, None, ptr(self.dx), ptr(self.err), self.block_k, mt,
+                                              cur_stream()), "mpit_umma_pulled_gemm")
+        return self.dx.view(self.M, self.K)[:m]
+
+    def weight_grad(self) -> torch.Tensor:
+        """``dW [out, in]`` of the last forward / backward pair (local: this rank's batch)."""
+        k, w = kernels(), self._wg
+        check(k.mpit_umma_wgrad(w["tx"], w["tz"], w["geom"], ptr(self._part), None, ptr(self.err), w["block_n"],
+                                w["nsplit"], cur_stream()), "mpit_umma_wgrad")
+        check(k.mpit_wgrad_reduce(ptr(self._part), ptr(self.gw), w["nsplit"], w["m_pad"], self.K, self.N, self.K,
+                                  cur_stream()), "mpit_wgrad_reduce")
+        return self.gw.view(self.N, self.K)
+
+    def push(self, scale: float) -> None:
+        """Owners' rows (and transposed copies) ``+= scale * dW``: a plain SGD step is ``push(-lr)``; every rank's
+        contribution accumulates (``p += g`` on the server, pserver.lua:91)."""
+        check(kernels().mpit_pulled_linear_push(self.shard.ptr_array(), self.shard_t.ptr_array(), self.S, self.rank,
+                                                ptr(self.gw), self.N, self.K, scale, cur_stream()),
+              "mpit_pulled_linear_push")
+
+    def check(self) -> None:
+        e = int(self.err.item())
+        if e:
+            raise RuntimeError(f"umma pipeline wait timed out (code {e})")

@@ -436,37 +436,100 @@ def case_msg_device(rank, world, dev, heap):
 
 
 def case_pulled_linear(rank, world, dev, heap):
-    """Pull fused with the consuming GEMM: weights stay sharded; every rank's GEMM reads them over NVLink."""
+    """Pull fused with the consuming GEMM: weights stay sharded; every rank's GEMM reads them over NVLink -- forward with
+    one, two and four M-tiles per CTA, the data gradient (reduction across owners through their transposed shards), the
+    weight gradient and its push, and a few steps of training THROUGH the layer on all ranks at once."""
     from mpit_b200.ops.pulled_linear import PulledLinear
-    K, N, M = 256, 64 * world * 2, 200
-    lin = PulledLinear(heap, K, N, M, act=1)
+    K, N = 256, 64 * world * 2
     gen = torch.Generator().manual_seed(42)
     W = torch.randn(N, K, generator=gen) * 0.05
     b = torch.randn(N, generator=gen) * 0.1
     rpo = N // world
-    lin.weight_rows().copy_(W[rank * rpo:(rank + 1) * rpo])
-    sync(dev)
-    x = torch.randn(M, K, generator=torch.Generator().manual_seed(rank))
-    y = lin.forward(x.to(dev), b.to(dev))
-    torch.cuda.synchronize()
-    assert int(lin.err.item()) == 0
-    ref = torch.relu(x @ W.t() + b)
-    rel = float((y.cpu() - ref).norm() / ref.norm())
-    assert rel < 3e-3, rel
-    sync(dev)
+    for M in (200, 512, 700):
+        lin = PulledLinear(heap, K, N, M, act=1)
+        lin.load_rows(W[rank * rpo:(rank + 1) * rpo].to(dev))
+        sync(dev)
+        x = torch.randn(M, K, generator=torch.Generator().manual_seed(rank))
+        ref = torch.relu(x @ W.t() + b)
+        for mt in (0, 1, 2, 4):
+            y = lin.forward(x.to(dev), b.to(dev), mt=mt)
+            torch.cuda.synchronize()
+            lin.check()
+            rel = float((y.cpu() - ref).norm() / ref.norm())
+            assert rel < 3e-3, (M, mt, rel)
+        # the un-fused formulation (gather with in-kernel peer loads, then a local GEMM) gives the same result
+        y3 = lin.forward(x.to(dev), b.to(dev), fused=False)
+        torch.cuda.synchronize()
+        assert float((y3.cpu() - ref).norm() / ref.norm()) < 3e-3
+        # backward: dx = dy W (W's rows come from all owners), dW = dy^T x
+        y = lin.forward(x.to(dev), b.to(dev))
+        dy = torch.randn(M, N, generator=torch.Generator().manual_seed(100 + rank)) * 0.1
+        dx = lin.backward(dy.to(dev))
+        gw = lin.weight_grad()
+        torch.cuda.synchronize()
+        lin.check()
+        assert float((dx.cpu() - dy @ W).norm() / (dy @ W).norm()) < 3e-3, M
+        assert float((gw.cpu() - dy.t() @ x).norm() / (dy.t() @ x).norm()) < 3e-3, M
+        sync(dev)
+        # push: every rank adds -0.5 * dW into the owners' rows and transposed copies
+        lin.push(-0.5)
+        sync(dev)
+        tot = torch.zeros(N, K)
+        for r in range(world):
+            xr = torch.randn(M, K, generator=torch.Generator().manual_seed(r))
+            dyr = torch.randn(M, N, generator=torch.Generator().manual_seed(100 + r)) * 0.1
+            tot += dyr.t() @ xr
+        want = (W - 0.5 * tot)[rank * rpo:(rank + 1) * rpo]
+        got = lin.weight_rows().cpu()
+        assert float((got - want).norm() / want.norm()) < 3e-3
+        assert torch.allclose(lin.weight_rows_t().cpu(), got.t(), atol=1e-5), "both layouts stay equal"
+        sync(dev)
     # an owner updates its rows; the next forward of every rank sees the new weights without any pull call
-    lin.weight_rows().mul_(2.0)
+    lin.load_rows(lin.weight_rows() * 2.0)
     sync(dev)
+    W2 = torch.cat([r for r in _gather_rows(lin, world, dev)])
     y2 = lin.forward(x.to(dev), None)
     torch.cuda.synchronize()
-    ref2 = torch.relu(x @ (2 * W).t())
+    ref2 = torch.relu(x @ W2.t())
     assert float((y2.cpu() - ref2).norm() / ref2.norm()) < 3e-3
-    # the un-fused fallback (gather with in-kernel peer loads, then a local GEMM) gives the same result
-    y3 = lin.forward(x.to(dev), None, fused=False)
-    torch.cuda.synchronize()
-    assert int(lin.err.item()) == 0
-    assert float((y3.cpu() - ref2).norm() / ref2.norm()) < 3e-3
     sync(dev)
+    # training through the layer: every rank fits y = relu(x Wt^T) on its own data; the shared, sharded W converges
+    Kt, Nt, Mt = 64, 64 * world, 256
+    lin = PulledLinear(heap, Kt, Nt, Mt, act=1)
+    Wt = torch.randn(Nt, Kt, generator=torch.Generator().manual_seed(7)) * 0.3
+    lin.load_rows(torch.zeros(Nt // world, Kt, device=dev) + 0.01)
+    sync(dev)
+    losses = []
+    for step in range(60):
+        xs = torch.randn(Mt, Kt, generator=torch.Generator().manual_seed(1000 * rank + step)).to(dev)
+        tgt = torch.relu(xs @ Wt.t().to(dev))
+        y = lin.forward(xs, None)
+        diff = y - tgt
+        losses.append(float((diff * diff).mean()))
+        dy = diff * (y > 0).float() * (2.0 / (Mt * world))          # d(mean squared error)/d(pre-activation)
+        lin.backward(dy)
+        lin.weight_grad()
+        sync(dev)                        # everybody has read the weights of this step
+        lin.push(-0.2)
+        sync(dev)
+    lin.check()
+    assert losses[-1] < 0.2 * losses[0], (losses[0], losses[-1])
+    heap.check_timeout()
+
+
+def case_pulled_mlp(rank, world, dev, heap):
+    """A model trained through the pull-fused GEMMs on all ranks at once (mlaunch --model pulled_mlp)."""
+    from mpit_b200.workloads import pulled_mlp
+    out = pulled_mlp.train(heap, batch=128, steps=120, lr=0.05, hidden=64 * world * 4, barrier=lambda: sync(dev),
+                           quiet=rank != 0)
+    assert out["loss_last"] < 0.5 * out["loss_first"], out
+    assert out["acc_after"] > max(0.5, out["acc_before"] + 0.3), out
+
+
+def _gather_rows(lin, world, dev):
+    rows = [torch.empty(lin.rows_per_owner, lin.K, device=dev) for _ in range(world)]
+    dist.all_gather(rows, lin.weight_rows().contiguous())
+    return [r.cpu() for r in rows]
 
 
 def case_window(rank, world, dev, heap):

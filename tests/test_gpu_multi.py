@@ -75,6 +75,12 @@ def test_pull_fused_with_consumer_gemm():
     assert "case pulled_linear: ok" in out
 
 
+def test_model_trained_through_pull_fused_gemms():
+    n = min(torch.cuda.device_count(), 8)
+    out = _torchrun(["pulled_mlp"], n)
+    assert "case pulled_mlp: ok" in out
+
+
 def test_one_sided_window():
     """MPI_Put / Accumulate / Get / Win_fence on the symmetric heap."""
     n = min(torch.cuda.device_count(), 8)

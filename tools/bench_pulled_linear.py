@@ -43,19 +43,20 @@ def timed(fn, iters=30, warm=5):
     return float(t)
 
 
-for (M, K, N) in [(128, 1024, 4096), (128, 4096, 4096), (512, 1024, 4096), (128, 256, 2048)]:
+for (M, K, N) in [(128, 1024, 4096), (128, 4096, 4096), (512, 1024, 4096), (1024, 1024, 4096), (128, 256, 2048)]:
     if N % (64 * world):
         continue
     lin = PulledLinear(heap, K, N, M, act=1)
     rpo = N // world
-    lin.weight_rows().copy_(torch.randn(rpo, K, device=dev) * 0.02)
+    lin.load_rows(torch.randn(rpo, K, device=dev) * 0.02)
     bias = torch.randn(N, device=dev) * 0.1
     x = torch.randn(M, K, device=dev)
+    dy = torch.randn(M, N, device=dev) * 0.1
     lin.forward(x, bias)
     torch.cuda.synchronize()
     dist.barrier()
 
-    def fused():
+    def fused_one_tile_per_cta():            # the round-1 kernel: every M-tile fetches its weight tiles again
         check(kernels().mpit_umma_linear_pull(lin._ta, lin._maps, lin.S, lin.rows_per_owner, lin._geom, ptr(bias), ptr(lin.y),
                                               ptr(lin.err), lin.block_n, cur_stream()), "mpit_umma_linear_pull")
 
@@ -66,17 +67,29 @@ for (M, K, N) in [(128, 1024, 4096), (128, 4096, 4096), (512, 1024, 4096), (128,
         dist.all_gather_into_tensor(wfull, wmine)
         return F.relu(F.linear(x, wfull, bias))
 
-    t_f, t_u = timed(fused), timed(nccl_then_cublas)
+    def nccl_then_cublas_bwd():
+        dist.all_gather_into_tensor(wfull, wmine)
+        return dy @ wfull
+
+    t_f = timed(lambda: lin.forward(x, bias))
+    t_1, t_u = timed(fused_one_tile_per_cta), timed(nccl_then_cublas)
     t_own = timed(lambda: lin._forward_unfused(bias))
     t_g = timed(lambda: F.relu(F.linear(x, wfull, bias)))
-    assert int(lin.err.item()) == 0
+    lin.forward(x, bias)
     ref = F.relu(F.linear(x, wfull, bias))
     rel = float((lin.y.view(lin.M, N)[:M] - ref).norm() / ref.norm())
-    r = {"M": M, "K": K, "N": N, "n_gpus": world, "weight_MB": round(N * K * 4 / 2 ** 20, 1), "fused_us": round(t_f, 1), "own_gather_then_gemm_us": round(t_own, 1),
-         "nccl_allgather_plus_cublas_us": round(t_u, 1), "cublas_gemm_alone_us": round(t_g, 1), "rel_err_vs_cublas": rel}
+    t_b, t_bu = timed(lambda: lin.backward(dy)), timed(nccl_then_cublas_bwd)
+    refb = dy @ wfull
+    relb = float((lin.backward(dy) - refb).norm() / refb.norm())
+    assert int(lin.err.item()) == 0
+    r = {"M": M, "K": K, "N": N, "n_gpus": world, "weight_MB": round(N * K * 4 / 2 ** 20, 1), "fused_us": round(t_f, 1),
+         "fused_one_tile_per_cta_us": round(t_1, 1), "own_gather_then_gemm_us": round(t_own, 1),
+         "nccl_allgather_plus_cublas_us": round(t_u, 1), "cublas_gemm_alone_us": round(t_g, 1), "rel_err_vs_cublas": rel,
+         "bwd_fused_us": round(t_b, 1), "bwd_nccl_allgather_plus_cublas_us": round(t_bu, 1), "bwd_rel_err_vs_cublas": relb}
     rows.append(r)
     if rank == 0:
         print(json.dumps(r), flush=True)
+    del lin
 heap.check_timeout()
 if rank == 0 and out_path:
     with open(out_path, "w") as f:
