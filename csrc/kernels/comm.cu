@@ -118,6 +118,7 @@ struct ExchArgs {
   long long map_base;  // pull: elements below map_base have no operand copy; the tables cover [map_base, n)
   float alpha, clr, l2wd, mom_next, scale, l1, l2, clip;
   int do_apply, use_mom, do_lookahead, do_sync, has_d_in, zero_src;
+  int la_in;           // x holds the parameters BEFORE the pending look-ahead and v is already scaled: start from x + v
 };
 
 template <int MODE>
@@ -224,6 +225,13 @@ __global__ void __launch_bounds__(256) exchange_kernel(ExchArgs a) {
       load4(a.x, i0, cnt, x);
       if (a.use_mom) load4(a.v, i0, cnt, v);
       if (MODE == EX_FUSED && a.do_apply) {
+        if (a.la_in && a.use_mom) {
+          // the previous step finished inside the weight-gradient reduction (umma_wgrad.cu), which keeps x at the
+          // parameters proper and folds the look-ahead into the operand copy only: the pending gradient was taken
+          // at x + v (v already scaled)
+#pragma unroll
+          for (int k = 0; k < 4; ++k) x[k] = add_rn(x[k], v[k]);
+        }
         float g[4], din[4] = {0.f, 0.f, 0.f, 0.f};
         if (a.gmap) {
 #pragma unroll
@@ -245,8 +253,14 @@ __global__ void __launch_bounds__(256) exchange_kernel(ExchArgs a) {
       }
       if (MODE == EX_FUSED) {
         if (a.do_lookahead && a.use_mom) {
+          if (a.la_in && !a.do_apply) {
+            // v was scaled when the previous step was finished by the reduction: only re-create the look-ahead point
 #pragma unroll
-          for (int k = 0; k < 4; ++k) nesterov_lookahead_elem(x[k], v[k], a.mom_next);
+            for (int k = 0; k < 4; ++k) x[k] = add_rn(x[k], v[k]);
+          } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) nesterov_lookahead_elem(x[k], v[k], a.mom_next);
+          }
         }
         store4(a.x, i0, cnt, x);
         if (a.use_mom) store4(a.v, i0, cnt, v);
@@ -435,7 +449,7 @@ int mpit_elastic_exchange(const unsigned long long* shard_ptrs, int nranks, int 
 int mpit_eamsgd_fused_step(const unsigned long long* shard_ptrs, int nranks, int rank, float* x, float* v,
                            const float* g, const int* gmap, float* d, float* wpk, const int* wmap,
                            int nmaps, long long n, float alpha, float clr, float l2wd, float mom_next, int do_apply,
-                           int use_mom, int do_lookahead, int do_sync, int has_d_in, void* stream) {
+                           int use_mom, int do_lookahead, int do_sync, int has_d_in, int la_in, void* stream) {
   if (n <= 0) return 0;
   if (nranks < 1 || nranks > MPIT_MAX_RANKS) return MPIT_E_ARG;
   ExchArgs a{};
@@ -444,7 +458,7 @@ int mpit_eamsgd_fused_step(const unsigned long long* shard_ptrs, int nranks, int
   a.x = x; a.v = v; a.g = g; a.gmap = gmap; a.d = d; a.wpk = wpk; a.wmap = wmap; a.nmaps = nmaps; a.n = n;
   a.alpha = alpha; a.clr = clr; a.l2wd = l2wd; a.mom_next = mom_next;
   a.do_apply = do_apply; a.use_mom = use_mom; a.do_lookahead = do_lookahead; a.do_sync = do_sync;
-  a.has_d_in = has_d_in;
+  a.has_d_in = has_d_in; a.la_in = la_in;
   exchange_kernel<EX_FUSED><<<exch_grid(a.walk), 256, 0, (cudaStream_t)stream>>>(a);
   MPIT_LAUNCH_CHECK();
   return 0;

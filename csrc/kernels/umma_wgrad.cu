@@ -20,6 +20,7 @@
 #include "mpit_b200.h"
 #include "common.cuh"
 #include "umma.cuh"
+#include "optim_math.cuh"
 #include <string.h>
 #include <stdio.h>
 #include <mutex>
@@ -280,12 +281,46 @@ wgrad_reduce_kernel(const float* __restrict__ part, float* __restrict__ gw, int 
 // with dependent L2 latencies made this kernel 10 us.  Partials are n-major (part[s][n][m]) and consecutive
 // threads run along m, so reads and the gw[n][m] writes are both coalesced.
 struct ReduceSeg { const float* part; float* gw; int nsplit, m_pad, K, N, first_block, sl, vec; };
-struct ReduceArgs { ReduceSeg seg[16]; int nseg; };
+// Optional optimizer epilogue: the reduction is the last kernel of a step and touches every gradient element exactly
+// once, so on steps without an exchange it can finish the step itself -- Nesterov/EAMSGD apply of THIS step's
+// gradient, the look-ahead of the next step and the refresh of the tensor-core operand copies
+// (asyncsgd/optim-msgd.lua:28-37, optim-eamsgd.lua:37-44,70) -- and the separate boundary kernel of the next step
+// is not launched at all.  The float operations and their order per parameter are those of the boundary kernel
+// (comm.cu EX_FUSED / optim.cu local_step), so trajectories stay bit-identical.  State convention: x is left at the
+// parameters PROPER (after the apply), v already multiplied by the next momentum, and only the operand copy holds the
+// look-ahead point x + v; `la_in` says that this is also the state the step started from.
+struct OptEpi {
+  float* x; float* v; const float* d;
+  const int* pk2flat;        // packed (forward layout) index -> flat parameter index, -1 = padding
+  float* wpk; const int* wmap2;   // operand copies: forward layout has the gradient's index, wmap2[i] = data-gradient slot
+  const float* gpk;          // base of the packed gradient buffer (segment outputs point into it)
+  float clr, l2wd, mom_next;
+  int use_mom, has_d, la_in, enabled;
+};
+struct ReduceArgs { ReduceSeg seg[16]; int nseg; OptEpi opt; };
+
+__device__ __forceinline__ void opt_epilogue_elem(const OptEpi& o, const float* gw_elem, float g) {
+  const int i = o.pk2flat[gw_elem - o.gpk];
+  if (i < 0) return;
+  float x = o.x[i], v = o.use_mom ? o.v[i] : 0.f;
+  if (o.la_in && o.use_mom) x = add_rn(x, v);                        // the point this step's gradient was taken at
+  msgd_apply_elem(x, v, g, o.has_d ? o.d[i] : 0.f, o.clr, o.l2wd, o.use_mom != 0, o.has_d != 0);
+  o.x[i] = x;                                                        // parameters proper
+  float la = x;
+  if (o.use_mom) {
+    v = mul_rn(v, o.mom_next);
+    o.v[i] = v;
+    la = add_rn(x, v);                                               // next step's look-ahead point: operands only
+  }
+  o.wpk[gw_elem - o.gpk] = la;
+  const int s2 = o.wmap2[i];
+  if (s2 >= 0) o.wpk[s2] = la;
+}
 
 // V = 4: an output "element" is four consecutive m (16-byte loads and stores; K % 4 == 0, buffers 16-byte
 // aligned -- every weight-gradient segment); V = 1: scalar (bias rows).
 template <int V>
-__device__ __forceinline__ void reduce_segment(const ReduceSeg& sg, float* red, const int block) {
+__device__ __forceinline__ void reduce_segment(const ReduceSeg& sg, float* red, const int block, const OptEpi& opt) {
   // sl is a power of two, so outputs-per-block is a shift; all index math in 32 bits (a 64-bit division per
   // thread cost more than the loads: host checks K*N < 2^31)
   const int opb_shift = 8 - (31 - __clz(sg.sl));
@@ -332,6 +367,10 @@ __device__ __forceinline__ void reduce_segment(const ReduceSeg& sg, float* red, 
   if (live && sl == 0) {
     if (V == 4) st4(sg.gw + (size_t)e * 4, make_float4(t[0], t[V > 1 ? 1 : 0], t[V > 2 ? 2 : 0], t[V > 3 ? 3 : 0]));
     else sg.gw[e] = t[0];
+    if (opt.enabled) {
+#pragma unroll
+      for (int v = 0; v < V; ++v) opt_epilogue_elem(opt, sg.gw + (size_t)e * V + v, t[v]);
+    }
   }
 }
 
@@ -342,8 +381,8 @@ __global__ void __launch_bounds__(256) multi_wgrad_reduce_kernel(ReduceArgs a) {
   int s = 0;
   while (s + 1 < a.nseg && (int)blockIdx.x >= a.seg[s + 1].first_block) ++s;
   const ReduceSeg sg = a.seg[s];
-  if (sg.vec) reduce_segment<4>(sg, red, blockIdx.x - sg.first_block);
-  else reduce_segment<1>(sg, red, blockIdx.x - sg.first_block);
+  if (sg.vec) reduce_segment<4>(sg, red, blockIdx.x - sg.first_block, a.opt);
+  else reduce_segment<1>(sg, red, blockIdx.x - sg.first_block, a.opt);
 }
 
 // Column sums of up to 8 [rows][C] matrices in one launch (bias gradients of every layer).
@@ -473,11 +512,13 @@ int mpit_multi_colsum(int nseg, const unsigned long long* srcs, const unsigned l
 // Split-K reduction of up to 16 segments in one launch; every array is a HOST array of nseg entries.
 // Segment i: gw_i[n*K_i + m] = sum_{s < nsplit_i} part_i[(s*N_i + n)*m_pad_i + m], m < K_i, n < N_i.
 // (A bias gradient summed from T tile rows of width G*C is the segment {nsplit=T*G, m_pad=1, K=1, N=C}.)
-int mpit_multi_wgrad_reduce(int nseg, const unsigned long long* parts, const unsigned long long* gws,
-                            const int* nsplit, const int* m_pad, const int* K, const int* N, void* stream) {
+static int multi_reduce_impl(int nseg, const unsigned long long* parts, const unsigned long long* gws,
+                             const int* nsplit, const int* m_pad, const int* K, const int* N, const OptEpi* opt,
+                             void* stream) {
   if (nseg < 1 || nseg > 16) return MPIT_E_ARG;
   ReduceArgs a{};
   a.nseg = nseg;
+  if (opt) a.opt = *opt;
   int blocks = 0;
   for (int i = 0; i < nseg; ++i) {
     a.seg[i].part = reinterpret_cast<const float*>(parts[i]);
@@ -495,6 +536,27 @@ int mpit_multi_wgrad_reduce(int nseg, const unsigned long long* parts, const uns
   }
   MPIT_CUDA_TRY(launch_k(multi_wgrad_reduce_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, a));
   return 0;
+}
+
+int mpit_multi_wgrad_reduce(int nseg, const unsigned long long* parts, const unsigned long long* gws,
+                            const int* nsplit, const int* m_pad, const int* K, const int* N, void* stream) {
+  return multi_reduce_impl(nseg, parts, gws, nsplit, m_pad, K, N, nullptr, stream);
+}
+
+/* The same reduction that also FINISHES the training step (see OptEpi): every gradient element it produces is applied
+ * to its parameter (x, v; d subtracted when has_d), the next step's look-ahead is folded into the operand copies
+ * wpk (forward slot = the gradient's own packed index, data-gradient slot = wmap2[flat index]).  Every output segment
+ * must lie inside the packed gradient buffer `gpk`; pk2flat maps a packed index to its flat parameter (-1: none). */
+int mpit_multi_wgrad_reduce_opt(int nseg, const unsigned long long* parts, const unsigned long long* gws,
+                                const int* nsplit, const int* m_pad, const int* K, const int* N, float* x, float* v,
+                                const float* d, const int* pk2flat, float* wpk, const int* wmap2, const float* gpk,
+                                float clr, float l2wd, float mom_next, int use_mom, int has_d, int la_in, void* stream) {
+  if (!x || !pk2flat || !wpk || !wmap2 || !gpk || (use_mom && !v) || (has_d && !d)) return MPIT_E_ARG;
+  OptEpi o{};
+  o.x = x; o.v = v; o.d = d; o.pk2flat = pk2flat; o.wpk = wpk; o.wmap2 = wmap2; o.gpk = gpk;
+  o.clr = clr; o.l2wd = l2wd; o.mom_next = mom_next; o.use_mom = use_mom; o.has_d = has_d; o.la_in = la_in;
+  o.enabled = 1;
+  return multi_reduce_impl(nseg, parts, gws, nsplit, m_pad, K, N, &o, stream);
 }
 
 }  // extern "C"

@@ -144,11 +144,13 @@ int mpit_elastic_exchange(const unsigned long long* shard_ptrs, int nranks, int 
                           long long n, float alpha, void* stream);
 /* The whole EAMSGD step boundary in one pass: apply(t-1) [x -= clr g; v -= clr g; x -= d_in],
  * elastic(t) when do_sync [d = alpha (x - centre); centre += d], lookahead(t) [v *= mom; x += v],
- * and refresh of the packed operand copy (optim-eamsgd.lua:26-47,58-70). */
+ * and refresh of the packed operand copy (optim-eamsgd.lua:26-47,58-70).  la_in: the previous step was finished by
+ * mpit_multi_wgrad_reduce_opt, i.e. x holds the parameters before the pending look-ahead and v is already scaled;
+ * the kernel starts from x + v. */
 int mpit_eamsgd_fused_step(const unsigned long long* shard_ptrs, int nranks, int rank, float* x, float* v,
                            const float* g, const int* gmap, float* d, float* wpk, const int* wmap,
                            int nmaps, long long n, float alpha, float clr, float l2wd, float mom_next, int do_apply,
-                           int use_mom, int do_lookahead, int do_sync, int has_d_in, void* stream);
+                           int use_mom, int do_lookahead, int do_sync, int has_d_in, int la_in, void* stream);
 /* SUM/AVG all-reduce over symmetric buffers (test/testreduceall.lua:28, asyncsgd/testreduceall.lua:72-77).
  * algo 0 = one-shot (result in the private `local_out`), 1 = two-shot (result in every rank's `out` buffer).
  * `in_mc`/`out_mc` are NVLS multicast addresses (0 = use peer loads/stores).  x_elastic != NULL fuses
@@ -337,6 +339,17 @@ int mpit_umma_wgrad_noalloc(const void* tmap_x128, const void* tmap_dz128, const
  * one launch; srcs/dsts/rows/cols are HOST arrays; C % 4 == 0 and 256 % (C/4) == 0. */
 int mpit_multi_wgrad_reduce(int nseg, const unsigned long long* parts, const unsigned long long* gws,
                             const int* nsplit, const int* m_pad, const int* K, const int* N, void* stream);
+/* The reduction as the LAST kernel of a training step that has no exchange: besides summing the partials it applies
+ * every gradient element to its parameter (Nesterov / EAMSGD apply, asyncsgd/optim-msgd.lua:31-37,
+ * optim-eamsgd.lua:37-44,70; d subtracted when has_d), scales v by the next momentum and writes the next step's
+ * look-ahead point x + v into the operand copies -- the boundary kernel of the next step is then not launched.  x is
+ * left at the parameters proper; la_in = the step started from that same state.  Output segments must lie inside the
+ * packed gradient buffer gpk; pk2flat: packed index -> flat parameter index (-1 none); wmap2: flat index -> slot of
+ * the data-gradient operand layout (-1 none). */
+int mpit_multi_wgrad_reduce_opt(int nseg, const unsigned long long* parts, const unsigned long long* gws,
+                                const int* nsplit, const int* m_pad, const int* K, const int* N, float* x, float* v,
+                                const float* d, const int* pk2flat, float* wpk, const int* wmap2, const float* gpk,
+                                float clr, float l2wd, float mom_next, int use_mom, int has_d, int la_in, void* stream);
 int mpit_multi_colsum(int nseg, const unsigned long long* srcs, const unsigned long long* dsts,
                       const long long* rows, const int* cols, void* stream);
 

@@ -40,6 +40,11 @@ def main(argv=None) -> int:
     ap.add_argument("--save", default="results/mlaunch")
     ap.add_argument("--data", default=None, help="directory with the cifar-10-batches-t7 files")
     ap.add_argument("--resume", default=None, help="checkpoint (model-epoch-N.net or flat tensor) to start from")
+    ap.add_argument("--tester-last", action="store_true",
+                    help="GPU path: the last rank does not train; it is the shadow tester of BiCNN/bicnn.lua:576-597 -- it "
+                         "pulls the centre variable from the shard owners, evaluates it and saves it, --max-evals times")
+    ap.add_argument("--max-evals", type=int, default=3)
+    ap.add_argument("--eval-sleep", type=float, default=0.2)
     ap.add_argument("--center-ckpt", default=None,
                     help="GPU path: file for the centre variable; restored from it when it exists, written to it at the "
                          "end by the shard owners in parallel (one flat Torch7 tensor, readable with --resume)")
@@ -73,7 +78,11 @@ def _gpu(a, lr) -> int:
             dist.barrier()
             dist.destroy_process_group()
         return 0
-    opts = CifarOpts(name=a.optim, lr=lr, mom=a.mom, mb=a.mb, su=a.su, mva=0.9 / world, maxepoch=a.epochs,
+    tester = world - 1 if (a.tester_last and world > 1) else -1
+    if tester >= 0 and a.optim.startswith("sync_"):
+        raise SystemExit("--tester-last needs an asynchronous optimizer (a synchronous all-reduce involves every rank)")
+    workers = world - (1 if tester >= 0 else 0)
+    opts = CifarOpts(name=a.optim, lr=lr, mom=a.mom, mb=a.mb, su=a.su, mva=0.9 / workers, maxepoch=a.epochs,
                      save=a.save, seed=1 + rank, model=a.model)
     print(f"[client] rank {rank} use gpu {local}")
     tr = CifarTrainer(opts, dev, heap, theta0=load_checkpoint(a.resume) if a.resume else None)
@@ -86,13 +95,32 @@ def _gpu(a, lr) -> int:
     train, test, real = cifar_data(a.trsize, a.tesize, seed=10 + rank, channels=ch, root=a.data)
     if rank == 0:
         print("===> data:", "cifar-10-batches-t7" if real else "synthetic")
-    hist = train_epochs(tr, train, test, rank=rank, quiet=rank != 0)
+    if rank == tester:
+        # shadow tester: the centre variable -- what EASGD actually returns -- is evaluated while the workers train
+        import time
+        from .. import t7
+        os.makedirs(a.save, exist_ok=True)
+        for k in range(a.max_evals):
+            theta = tr.center.gather_full()                 # one-sided pull of every shard, no worker is interrupted
+            tr.opt.x.copy_(theta)
+            res = tr.test(test[0], test[1])
+            path = os.path.join(a.save, f"centre-eval-{k}.t7")
+            t7.save(path, theta.cpu())                      # flat parameter tensor, as bicnn.lua:590-594 saves it
+            print(f"[tester {rank}] eval {k}: centre test loss {res['loss']:.4f} accuracy {res['acc']:.4f} -> {path}")
+            time.sleep(a.eval_sleep)
+        hist = None
+    else:
+        hist = train_epochs(tr, train, test, rank=rank, quiet=rank != 0)
+    if tester >= 0:
+        torch.cuda.synchronize()
+        sync()                                             # workers done, tester done
     if a.center_ckpt and tr.center is not None:
         torch.cuda.synchronize()
         if sync:
             sync()                                         # every worker's last push has landed
         tr.center.save(a.center_ckpt, barrier=sync)
-    print(f"[rank {rank}] train loss {hist['train_loss'][-1]:.4f} test acc {hist['test_acc'][-1]:.4f} "
+    if hist is not None:
+        print(f"[rank {rank}] train loss {hist['train_loss'][-1]:.4f} test acc {hist['test_acc'][-1]:.4f} "
           f"{hist['samples_per_s']:.0f} samples/s")
     heap.check_timeout()
     if world > 1:

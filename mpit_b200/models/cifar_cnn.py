@@ -270,6 +270,11 @@ class CifarEngine:
         B = batch
         self.wmap = self.layout.wmap2.to(dev)          # [2 * n_flat]: forward + data-gradient tables
         self.gmap = self.wmap[:self.layout.n_flat]     # gradients come back in the forward layout
+        self.wmap_d = self.wmap[self.layout.n_flat:]   # flat index -> slot of the data-gradient operand layout
+        # packed (forward layout) index -> flat index, for the optimizer epilogue of the weight-gradient reduction
+        self.pk2flat = torch.full((self.layout.n_packed,), -1, dtype=torch.int32, device=dev)
+        self.pk2flat[self.gmap.long()] = torch.arange(self.layout.n_flat, dtype=torch.int32, device=dev)
+        self.opt_epi = None                            # set by an optimizer that wants the reduction to finish the step
         self.wpk = torch.zeros(self.layout.n_packed, **f32)
         self.gpk = torch.zeros(self.layout.n_packed, **f32)
         # inputs

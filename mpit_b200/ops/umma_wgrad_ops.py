@@ -87,6 +87,11 @@ class CifarWgradPlan:
 
         # "all": one launch at the end.  "early"/"late": everything that is final once the layer-1 weight gradient
         # is done (layers 1..4 and the bias rows of the data gradients that ran before it) / the first layer.
+        # with the optimizer epilogue every parameter has to pass through the reduction: bias gradients that come from
+        # elsewhere (the classifier head's loss kernel) ride along as one-partial segments that read and rewrite gb
+        extra = [(eng.gb(li).data_ptr(), eng.gb(li).data_ptr(), 1, 1, 1, eng.layers[li].CO)
+                 for li in range(len(ls)) if li not in bsegs]
+        self._red_opt = pack(list(wsegs.values()) + list(bsegs.values()) + extra) if bias_parts else None
         self._red = {"all": pack(list(wsegs.values()) + list(bsegs.values())),
                      "early": pack([wsegs[i] for i in range(1, len(ls))] + [bsegs[i] for i in sorted(bsegs) if i >= 1]),
                      "late": pack([wsegs[0]] + ([bsegs[0]] if 0 in bsegs else []))}
@@ -109,6 +114,15 @@ class CifarWgradPlan:
         data-gradient epilogues.  ``which``: "all", or "early" (layers 1..4, runs beside the last data gradient)
         followed by "late" (first layer)."""
         k = kernels()
+        o = getattr(self.eng, "opt_epi", None)
+        if o is not None and which == "all" and self._red_opt is not None:
+            # the reduction finishes the step: apply + next look-ahead + operand refresh (no boundary kernel next step)
+            e, r = self.eng, self._red_opt
+            check(k.mpit_multi_wgrad_reduce_opt(r[0], r[1], r[2], r[3], r[4], r[5], r[6], ptr(o["x"]), ptr(o["v"]),
+                                                ptr(o["d"]), ptr(e.pk2flat), ptr(e.wpk), ptr(e.wmap_d), ptr(e.gpk),
+                                                o["clr"], o["l2wd"], o["mom_next"], int(o["use_mom"]), int(o["has_d"]),
+                                                int(o["la_in"]), cur_stream()), "mpit_multi_wgrad_reduce_opt")
+            return
         r = self._red[which]
         check(k.mpit_multi_wgrad_reduce(r[0], r[1], r[2], r[3], r[4], r[5], r[6], cur_stream()),
               "mpit_multi_wgrad_reduce")

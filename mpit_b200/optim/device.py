@@ -126,22 +126,41 @@ class DeviceMSGD(_DeviceOptBase):
 class DeviceEAMSGD(_DeviceOptBase):
     """Asynchronous EASGD/EAMSGD against an NVLink-sharded centre (asyncsgd/optim-eamsgd.lua:7-79).
 
-    Per step ONE fused kernel touches the parameters: it applies the previous gradient
-    (``x -= clr g; v -= clr g; x -= d``), on sync steps reads the centre shards from their owners,
-    forms ``d = mva (x - centre)`` and accumulates it into the owners with ``red.add`` (fire and
-    forget: it completes under the following forward/backward), then does the Nesterov look-ahead
-    and refreshes the tensor-core operand copy.
-    """
+    On a sync step ONE fused boundary kernel touches the parameters: it applies the previous gradient
+    (``x -= clr g; v -= clr g; x -= d``), reads the centre shards from their owners, forms
+    ``d = mva (x - centre)`` and accumulates it into the owners with ``red.add`` (fire and forget: it completes under
+    the following forward/backward), then does the Nesterov look-ahead and refreshes the tensor-core operand copy.
+
+    On the other steps nothing has to be exchanged, and the step is finished by the kernel that produces its last
+    gradients anyway: the split-K reduction of the weight gradients applies each gradient element to its parameter,
+    scales the momentum and writes the next look-ahead point into the operand copies (``fuse_reduce``; engines that
+    offer ``opt_epi``; opt-in with ``fuse_reduce=True`` / ``MPIT_FUSE_REDUCE=1`` because it measured 3.6 % SLOWER on
+    B200, see __init__).  With tau = 10 the boundary kernel then runs once in ten steps.  State convention between two
+    such steps: ``x`` = parameters proper, ``v`` already scaled, operand copy = ``x + v`` (``_la_pending``); the float
+    operations per parameter and their order are unchanged, so trajectories are bit-identical either way
+    (tests/test_gpu_train_step.py)."""
 
     def __init__(self, engine, theta0, center: ShardedCenter, *, lr, mva, su=1, mom=0.0, l2wd=0.0, lrd=0.0,
-                 lrp=0.0, seed_center: Optional[bool] = None, use_graphs=True):
+                 lrp=0.0, seed_center: Optional[bool] = None, use_graphs=True, fuse_reduce: Optional[bool] = None):
         super().__init__(engine, theta0, use_graphs and not (lrd != 0 and lrp > 0))
+        import os
         assert su > 0 and mva > 0, "eamsgd needs su > 0 and mva > 0 (optim-eamsgd.lua:50)"
         self.center = center
         self.lr, self.mva, self.su, self.mom, self.l2wd, self.lrd, self.lrp = lr, mva, su, mom, l2wd, lrd, lrp
         self.v = torch.zeros_like(self.x) if mom > 0 else None
         self.d = torch.zeros_like(self.x)
         self.prev_sync = False
+        if fuse_reduce is None:
+            # opt-in: measured on B200 it does NOT pay at this model size -- 0.1353 ms/step fused against 0.1305 with
+            # the boundary kernel (tau = 10, batch 128): the boundary kernel hides under programmatic dependent launch
+            # while the reduction, walking the packed order, pays for scattered x / v accesses on one thread in eight
+            fuse_reduce = os.environ.get("MPIT_FUSE_REDUCE", "0") == "1"
+        plan = getattr(engine, "_umma", None)
+        self.fuse_reduce = bool(fuse_reduce and hasattr(engine, "opt_epi") and plan is not None
+                                and getattr(plan, "wgrad", None) is not None
+                                and getattr(plan.wgrad, "_red_opt", None) is not None and not plan.split_reduce)
+        self._la_pending = False        # x = parameters proper, v scaled, operands at x + v (left by a fused reduction)
+        self._operands_stale = False    # somebody re-packed the operands from x since (params() / test())
         # the first client seeds the servers (pclient.lua:131-133)
         if seed_center if seed_center is not None else center.rank == 0:
             center.put(self.x)
@@ -152,32 +171,53 @@ class DeviceEAMSGD(_DeviceOptBase):
             return self.lr / math.pow(1 + t * self.lrd, self.lrp)
         return self.lr
 
-    def _boundary(self, do_apply, do_lookahead, do_sync, has_d_in):
+    def _boundary(self, do_apply, do_lookahead, do_sync, has_d_in, la_in=False):
         e = self.engine
         self.center.eamsgd_step(self.x, self.v, e.gpk, e.gmap, self.d, e.wpk, e.wmap, alpha=self.mva,
                                 clr=self._clr(self.t - 1), l2wd=self.l2wd, mom_next=self.mom,
                                 do_apply=do_apply, use_mom=self.mom > 0, do_lookahead=do_lookahead,
-                                do_sync=do_sync, has_d_in=has_d_in)
+                                do_sync=do_sync, has_d_in=has_d_in, la_in=la_in)
 
     def step(self) -> None:
         do_apply = self.pending_apply
         do_sync = self.t % self.su == 0
         has_d_in = do_apply and self.prev_sync
+        la_in = self._la_pending
+        # the boundary kernel runs when there is something for it to do: a gradient to apply, an exchange, a first
+        # look-ahead, or operands that were re-packed from x behind our back
+        need_boundary = do_apply or do_sync or not la_in or self._operands_stale
+        fuse = self.fuse_reduce and (self.t + 1) % self.su != 0
+        epi = None
+        if fuse:
+            epi = dict(x=self.x, v=self.v, d=self.d, clr=self._clr(self.t), l2wd=self.l2wd, mom_next=self.mom,
+                       use_mom=self.mom > 0, has_d=do_sync, la_in=la_in and not need_boundary)
 
         def body():
-            self._boundary(do_apply, True, do_sync, has_d_in)
-            self.engine.fwd_bwd()
+            if need_boundary:
+                self._boundary(do_apply, True, do_sync, has_d_in, la_in)
+            self.engine.opt_epi = epi
+            try:
+                self.engine.fwd_bwd()
+            finally:
+                self.engine.opt_epi = None
 
-        self.graphs.run(("step", do_apply, do_sync, has_d_in), body)
-        self.pending_apply = True
-        self.prev_sync = do_sync
+        self.graphs.run(("step", need_boundary, do_apply, do_sync, has_d_in, la_in, fuse), body)
+        self._operands_stale = False
+        if fuse:
+            self.pending_apply, self.prev_sync, self._la_pending = False, False, True
+        else:
+            # without a boundary the state the step started from is still the state: x proper, v scaled
+            self.pending_apply, self.prev_sync, self._la_pending = True, do_sync, la_in and not need_boundary
         self.t += 1
 
     def finalize(self) -> None:
         if self.pending_apply:
-            self._boundary(True, False, False, self.prev_sync)
+            self._boundary(True, False, False, self.prev_sync, self._la_pending)
             self.pending_apply = False
             self.prev_sync = False
+            self._la_pending = False
+        if self._la_pending:
+            self._operands_stale = True     # callers of params() may re-pack the operands from x (test, load_flat)
 
 
 class DeviceSyncEASGD(_DeviceOptBase):

@@ -96,11 +96,11 @@ class ShardedCenter:
                                            cur_stream()), "mpit_elastic_exchange")
 
     def eamsgd_step(self, x, v, g, gmap, d, wpk, wmap, *, alpha, clr, l2wd, mom_next, do_apply, use_mom,
-                    do_lookahead, do_sync, has_d_in) -> None:
+                    do_lookahead, do_sync, has_d_in, la_in=False) -> None:
         check(self.k.mpit_eamsgd_fused_step(self._ptrs, self.nranks, self.rank, ptr(x), ptr(v), ptr(g), ptr(gmap),
                                             ptr(d), ptr(wpk), ptr(wmap), self._nmaps(wmap), self.n, alpha, clr, l2wd, mom_next,
                                             int(do_apply), int(use_mom), int(do_lookahead), int(do_sync),
-                                            int(has_d_in), cur_stream()), "mpit_eamsgd_fused_step")
+                                            int(has_d_in), int(la_in), cur_stream()), "mpit_eamsgd_fused_step")
 
     # -- checkpoint of the centre: every owner writes / reads its own shard (utils/sharded_ckpt.py) ---------------
     def save(self, path: str, barrier=None) -> None:
