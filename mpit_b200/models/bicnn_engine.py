@@ -291,6 +291,7 @@ class BiCnnEngine:
 
     def _wgrad(self, w):
         k = self.k
+        k.mpit_set_tf32x3(0)
         check(k.mpit_umma_wgrad(w["tx"], w["tz"], w["geom"], ptr(self.part), None, ptr(self.err), w["block_n"],
                                 w["nsplit"], cur_stream()), "mpit_umma_wgrad")
         check(k.mpit_wgrad_reduce(ptr(self.part), ptr(w["gw"]), w["nsplit"], w["m_pad"], w["chunks"] * 32, w["N"],

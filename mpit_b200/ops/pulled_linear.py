@@ -110,6 +110,7 @@ class PulledLinear:
         n = self.rows_per_owner * self.K
         for r, p in enumerate(self.shard.ptrs):                       # MPI_Get of every owner's rows (ld.sys over NVLink)
             check(k.mpit_peer_rma(1, p, self._wfull.data_ptr() + 4 * r * n, n, 1.0, cur_stream()), "mpit_peer_rma")
+        k.mpit_set_tf32x3(0)
         check(k.mpit_umma_igemm(self._ta, self._tb_local, self._geom, 1.0, ptr(bias), ptr(self.y), None, None, None, None,
                                 None, ptr(self.err), None, self.block_n, cur_stream()), "mpit_umma_igemm")
 
@@ -149,6 +150,7 @@ class PulledLinear:
     def weight_grad(self) -> torch.Tensor:
         """``dW [out, in]`` of the last forward / backward pair (local: this rank's batch)."""
         k, w = kernels(), self._wg
+        k.mpit_set_tf32x3(0)
         check(k.mpit_umma_wgrad(w["tx"], w["tz"], w["geom"], ptr(self._part), None, ptr(self.err), w["block_n"],
                                 w["nsplit"], cur_stream()), "mpit_umma_wgrad")
         check(k.mpit_wgrad_reduce(ptr(self._part), ptr(self.gw), w["nsplit"], w["m_pad"], self.K, self.N, self.K,

@@ -44,8 +44,10 @@ class IgemmLaunch:
     block_n: int
     dropout_slot: int = 16
     colpart: Optional[torch.Tensor] = None    # [m_tiles][N] per-tile column sums (modes MASK / EXPAND)
+    x3: int = 0                               # 0 TF32 products, 1 / 2 fp32-accurate 3xTF32 (mpit_set_tf32x3)
 
     def run(self, err: torch.Tensor, dropout: Optional[bool] = None):
+        kernels().mpit_set_tf32x3(self.x3)    # the mode is process-wide: every launch states the one it wants
         g = self.geom
         if dropout is not None:
             g = (ctypes.c_int * 17)(*self.geom)
@@ -244,6 +246,9 @@ class CifarUmmaPlan:
             self.dgrad[i].colpart = cp
             self.bias_parts[i - 1] = (cp, tiles, ncols, eng.layers[i - 1].CO)
 
+        for l in list(self.fwd) + list(self.dgrad.values()) + list(self.dgrad_stream.values()):
+            if isinstance(l, IgemmLaunch):
+                l.x3 = getattr(eng, "x3", 0)
         self.two_streams = os.environ.get("MPIT_BWD_STREAMS", "2") != "1"
         # One more fork exists but is off by default: reducing layers 1..4 on the side stream beside the last data
         # gradient.  Every fork/join turns a programmatic (PDL) edge into a full one, and on B200 the two effects

@@ -105,6 +105,7 @@ class CifarWgradPlan:
     def run(self, i: int):
         l = self.launches[i]
         k = kernels()
+        k.mpit_set_tf32x3(getattr(self.eng, "x3", 0))
         part = self.part[l.part_off:]
         check(k.mpit_umma_wgrad(l.tmap_x, l.tmap_dz, l.geom, ptr(part), ptr(l.crop), ptr(self.err), l.block_n,
                                 l.nsplit, cur_stream()), "mpit_umma_wgrad")
