@@ -42,7 +42,9 @@ class DeviceCollectives:
     ``inp``/``out`` are symmetric buffers of ``capacity`` floats; the caller writes its contribution
     into ``inp.local`` (or passes a tensor to copy in) and reads the result from ``out.local``."""
 
-    ONE_SHOT_MAX = 256 * 1024   # floats (1 MiB): below this the latency path wins
+    ONE_SHOT_MAX = 256 * 1024   # floats (1 MiB): below this the latency path wins on 2 ranks
+    ONE_SHOT_MAX_NVLS = 16 * 1024   # from 3 ranks up the multimem two-shot is as fast at 64 KiB and faster beyond
+                                    # (8 GPUs: 256 KiB 39.6 vs 102 us, 1 MiB 43.8 vs 52.6 us; profiles/ev_r2/n8/sweep.jsonl)
 
     def __init__(self, heap, capacity: int, multicast: bool = True):
         self.heap = heap
@@ -70,7 +72,7 @@ class DeviceCollectives:
             self.inp.local[:n].copy_(x.reshape(-1))
         assert n is not None and n <= self.capacity
         if algo is None:
-            algo = "oneshot" if n <= self.ONE_SHOT_MAX else "twoshot"
+            algo = "oneshot" if n <= self._one_shot_max() else "twoshot"
         scale = 1.0 / self.nranks if average else 1.0
         two = algo == "twoshot"
         local_out = None if two else self.out.local
@@ -83,6 +85,9 @@ class DeviceCollectives:
                                     self.rank, ptr(local_out), ptr(elastic_x), n, scale, alpha, 1 if two else 0,
                                     max_blocks, cur_stream()), "mpit_allreduce")
         return self.out.local[:n]
+
+    def _one_shot_max(self) -> int:
+        return self.ONE_SHOT_MAX_NVLS if (self.nranks > 2 and self.inp.mc_ptr != 0) else self.ONE_SHOT_MAX
 
     def _use_mc(self, two: bool) -> bool:
         use_mc = two and self.nranks > 2
@@ -98,7 +103,7 @@ class DeviceCollectives:
         n = x.numel()
         assert n <= self.capacity
         if algo is None:
-            algo = "oneshot" if n <= self.ONE_SHOT_MAX else "twoshot"
+            algo = "oneshot" if n <= self._one_shot_max() else "twoshot"
         two = algo == "twoshot"
         mc = self._use_mc(two)
         nmaps = 0 if wmap is None else max(1, int(wmap.numel()) // n)
