@@ -76,6 +76,11 @@ static inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 blo
 
 __device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
 __device__ __forceinline__ void st4(float* p, const float4& v) { *reinterpret_cast<float4*>(p) = v; }
+// 16-byte float add into this GPU's memory, no return value (one L2 atomic unit operation per quad)
+__device__ __forceinline__ void red_add4(float* p, const float4& v) {
+  asm volatile("red.relaxed.gpu.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
 
 // Streaming (read-once) 128-bit load that does not allocate in L1.
 __device__ __forceinline__ float4 ld4_stream(const float* p) {

@@ -51,6 +51,7 @@ struct IgemmParams {
   float* colpart;            // optional [m_tiles][N]: per-tile column sums of the values written (MASK / EXPAND)
   int stages;                // smem pipeline depth (2..kMaxStages), chosen per launch
   int x3;                    // 0: plain TF32; 1 / 2: 3xTF32 with the operand split done in shared memory (umma.cuh)
+  int sb, kb_split, accum;   // pulled GEMM only: depth of the weight ring, k-blocks per split-K slice, red.add epilogue
   long long* dbg;            // optional per-CTA timeline (16 clock64 stamps per CTA), null in production
 };
 
@@ -98,7 +99,7 @@ __device__ __forceinline__ void subtile_origin(const IgemmParams& p, int s, int&
 // by the streaming kernel below and the resident-input kernel (umma_resident.cu).  Called by the four epilogue
 // warps.  (n, oh, ow, valid) describe the output row of this THREAD (TMEM lane); `tile` indexes the colpart row.
 // `wait_acc`: wait for `tmem_full` (phase 0) after the side inputs have been requested.
-template <int BLOCK_N, int MODE>
+template <int BLOCK_N, int MODE, bool ACCUM = false>
 __device__ __forceinline__ void coalesced_epilogue(const IgemmParams& p, uint8_t* smem, const uint32_t tmem_base,
                                                    uint64_t* tmem_full, const bool wait_acc, const int quad, const int lane,
                                                    const int row, const int n, const int oh, const int ow, const bool valid,
@@ -196,7 +197,8 @@ __device__ __forceinline__ void coalesced_epilogue(const IgemmParams& p, uint8_t
           x.z = (kb & 4u) ? x.z * 2.f : 0.f;
           x.w = (kb & 8u) ? x.w * 2.f : 0.f;
         }
-        st4(p.out + e0, x);
+        if (ACCUM && p.accum) red_add4(p.out + e0, x);   // split-K slice: partial tile into the zeroed output
+        else st4(p.out + e0, x);
       } else if (MODE == EPI_MASK) {
         const float4 h = ax[i];
         float4 o;
@@ -668,18 +670,32 @@ umma_igemm_pull_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
 //   BY_K = false (forward, y = act(x W^T + b)): W row-sharded, owner chosen by the output-column tile;
 //   BY_K = true  (data gradient, dx = dy W):   the reduction runs over W's rows, i.e. ACROSS owners; each owner also
 //                keeps its rows transposed ([in][rows_per_owner]), and the owner is chosen by the k-block.
+// Two rings instead of one: the local activation tiles (MT x 16 KB per k-block, L2 latency) and the remote weight
+// tiles (4 / 8 KB per k-block, NVLink latency) have very different latency x size products.  With one ring of
+// [A | B] stages only two stages fit at MT = 4, i.e. two weight tiles in flight per CTA, and every k-block then
+// waited a whole NVLink round trip.  The B ring is `p.sb` slots deep (up to 16) and runs `sb - stages` k-blocks
+// ahead of the A ring, issued by the same thread: slot B(j + sb - stages) and slot A(j) are both released by the
+// MMAs of k-block j - stages, so running ahead costs no extra waiting.
+// gridDim.z > 1 (data gradient only): split-K -- slice z reduces k-blocks [z * kb_split, (z+1) * kb_split) and the
+// epilogue adds its partial tile into the (zeroed) output with red.add.v4.f32, which gives the few-output-tile,
+// long-reduction shape of dx = dy W enough CTAs.
+constexpr int kMaxBStages = 16;
+
 template <int BLOCK_N, int MT, bool BY_K>
 __global__ void __launch_bounds__(192)
 umma_pulled_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ PeerMaps pm,
                         const IgemmParams p) {
   constexpr int kBBytes = BLOCK_N * 128;
-  constexpr int kStage = MT * kABytes + kBBytes;
+  constexpr int kAStage = MT * kABytes;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  const int kStages = p.stages;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * kStage);
-  uint64_t* empty_bar = full_bar + kMaxStages;
-  uint64_t* tmem_full = empty_bar + kMaxStages;
+  const int SA = p.stages, SB = p.sb;
+  uint8_t* smem_b = smem + SA * kAStage;
+  uint64_t* full_a = reinterpret_cast<uint64_t*>(smem_b + SB * kBBytes);
+  uint64_t* empty_a = full_a + kMaxStages;
+  uint64_t* full_b = empty_a + kMaxStages;
+  uint64_t* empty_b = full_b + kMaxBStages;
+  uint64_t* tmem_full = empty_b + kMaxBStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
   __shared__ __align__(16) float bias_s[256];
 
@@ -688,10 +704,13 @@ umma_pulled_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
   const int m_tiles = (p.B + 127) / 128;
   const int mt0 = blockIdx.x * MT;
   const int mt_here = m_tiles - mt0 < MT ? m_tiles - mt0 : MT;
+  const int kb0 = BY_K ? (int)blockIdx.z * p.kb_split : 0;          // this CTA's slice of the reduction
+  const int nkb = BY_K ? (p.num_kb - kb0 < p.kb_split ? p.num_kb - kb0 : p.kb_split) : p.num_kb;
   pdl_trigger();
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmap_a);
-    for (int i = 0; i < kStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    for (int i = 0; i < SA; ++i) { mbar_init(&full_a[i], 1); mbar_init(&empty_a[i], 1); }
+    for (int i = 0; i < SB; ++i) { mbar_init(&full_b[i], 1); mbar_init(&empty_b[i], 1); }
     mbar_init(tmem_full, 1);
     fence_barrier_init();
   }
@@ -702,47 +721,62 @@ umma_pulled_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();
   if (warp >= 2)
-    for (int c = threadIdx.x - 64; c < BLOCK_N; c += 128) bias_s[c] = p.bias ? p.bias[n_tile0 + c] : 0.f;
+    for (int c = threadIdx.x - 64; c < BLOCK_N; c += 128)
+      bias_s[c] = (p.bias && (!BY_K || blockIdx.z == 0)) ? p.bias[n_tile0 + c] : 0.f;
 
   if (warp == 0) {
     if (elect_one()) {
       const int owner_n = BY_K ? 0 : n_tile0 / pm.rows_per_owner;
-      int stage = 0, phase = 0;
-      for (int kb = 0; kb < p.num_kb; ++kb) {
-        if (kb >= kStages && !mbar_wait(&empty_bar[stage], phase ^ 1)) { if (p.err) *p.err = 1; break; }
-        uint8_t* dst = smem + stage * kStage;
-        mbar_expect_tx(&full_bar[stage], (uint32_t)(mt_here * kABytes + kBBytes));
+      int as = 0, aph = 0, bs = 0, bph = 0, jb = 0;
+      bool ok = true;
+      auto issue_b = [&]() {   // weight tile of local k-block jb, from its owner's shard
+        if (jb >= SB && !mbar_wait(&empty_b[bs], bph ^ 1)) { ok = false; return; }
+        mbar_expect_tx(&full_b[bs], (uint32_t)kBBytes);
+        const int kb = kb0 + jb;
         if (BY_K) {
           const int owner = (kb * 32) / pm.rows_per_owner;
-          tma_load_2d(dst + MT * kABytes, &pm.map[owner], &full_bar[stage], kb * 32 - owner * pm.rows_per_owner, n_tile0);
+          tma_load_2d(smem_b + bs * kBBytes, &pm.map[owner], &full_b[bs], kb * 32 - owner * pm.rows_per_owner, n_tile0);
         } else {
-          tma_load_2d(dst + MT * kABytes, &pm.map[owner_n], &full_bar[stage], kb * 32,
-                      n_tile0 - owner_n * pm.rows_per_owner);
+          tma_load_2d(smem_b + bs * kBBytes, &pm.map[owner_n], &full_b[bs], kb * 32, n_tile0 - owner_n * pm.rows_per_owner);
         }
+        ++jb;
+        if (++bs == SB) { bs = 0; bph ^= 1; }
+      };
+      const int ahead = SB - SA;
+      while (jb < ahead && jb < nkb) issue_b();          // never waits: jb < SB
+      for (int j = 0; j < nkb && ok; ++j) {
+        if (jb < nkb) issue_b();
+        if (!ok) break;
+        if (j >= SA && !mbar_wait(&empty_a[as], aph ^ 1)) { ok = false; break; }
+        uint8_t* dst = smem + as * kAStage;
+        mbar_expect_tx(&full_a[as], (uint32_t)(mt_here * kABytes));
         for (int mt = 0; mt < mt_here; ++mt)
-          tma_load_4d(dst + mt * kABytes, &tmap_a, &full_bar[stage], kb * 32, 0, 0, (mt0 + mt) * 128);
-        if (++stage == kStages) { stage = 0; phase ^= 1; }
+          tma_load_4d(dst + mt * kABytes, &tmap_a, &full_a[as], (kb0 + j) * 32, 0, 0, (mt0 + mt) * 128);
+        if (++as == SA) { as = 0; aph ^= 1; }
       }
+      if (!ok && p.err) *p.err = 1;
     }
   } else if (warp == 1) {
     if (elect_one()) {
       constexpr uint32_t idesc = make_idesc_tf32(128, BLOCK_N, 0, 0);
-      const uint64_t desc0 = make_smem_desc(smem_u32(smem), 16, 1024);
-      uint64_t ad = desc0;
-      int stage = 0, phase = 0;
-      for (int kb = 0; kb < p.num_kb; ++kb) {
-        if (!mbar_wait(&full_bar[stage], phase)) { if (p.err) *p.err = 2; break; }
+      const uint64_t desc_a0 = make_smem_desc(smem_u32(smem), 16, 1024);
+      const uint64_t desc_b0 = make_smem_desc(smem_u32(smem_b), 16, 1024);
+      int as = 0, aph = 0, bs = 0, bph = 0;
+      for (int j = 0; j < nkb; ++j) {
+        if (!mbar_wait(&full_b[bs], bph) || !mbar_wait(&full_a[as], aph)) { if (p.err) *p.err = 2; break; }
         tc_fence_after();
-        const uint64_t bd = ad + ((MT * kABytes) >> 4);
+        const uint64_t ad = desc_a0 + (uint64_t)((as * kAStage) >> 4);
+        const uint64_t bd = desc_b0 + (uint64_t)((bs * kBBytes) >> 4);
         for (int mt = 0; mt < mt_here; ++mt) {
           const uint64_t am = ad + (uint64_t)((mt * kABytes) >> 4);
 #pragma unroll
           for (int k = 0; k < 4; ++k)
-            mma_tf32(tmem_base + (uint32_t)(mt * BLOCK_N), am + 2 * k, bd + 2 * k, idesc, (kb | k) ? 1u : 0u);
+            mma_tf32(tmem_base + (uint32_t)(mt * BLOCK_N), am + 2 * k, bd + 2 * k, idesc, (j | k) ? 1u : 0u);
         }
-        mma_commit(&empty_bar[stage]);
-        ad += (kStage >> 4);
-        if (++stage == kStages) { stage = 0; phase ^= 1; ad = desc0; }
+        mma_commit(&empty_a[as]);
+        mma_commit(&empty_b[bs]);
+        if (++as == SA) { as = 0; aph ^= 1; }
+        if (++bs == SB) { bs = 0; bph ^= 1; }
       }
       mma_commit(tmem_full);
     }
@@ -751,8 +785,9 @@ umma_pulled_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
     const int row = quad * 32 + lane;
     for (int mt = 0; mt < mt_here; ++mt) {
       const int n = (mt0 + mt) * 128 + row;
-      coalesced_epilogue<BLOCK_N, EPI_STORE>(p, smem, tmem_base + (uint32_t)(mt * BLOCK_N), tmem_full, mt == 0, quad, lane,
-                                             row, n, 0, 0, n < p.B, n_tile0, mt0 + mt, 0ull, 0ull, bias_s, nullptr);
+      coalesced_epilogue<BLOCK_N, EPI_STORE, BY_K>(p, smem, tmem_base + (uint32_t)(mt * BLOCK_N), tmem_full, mt == 0, quad,
+                                                   lane, row, n, 0, 0, n < p.B, n_tile0, mt0 + mt, 0ull, 0ull, bias_s,
+                                                   nullptr);
     }
     tc_fence_before();
   }
@@ -818,7 +853,7 @@ template <int BLOCK_N, int MT, bool BY_K>
 static int launch_pulled(dim3 grid, size_t smem, cudaStream_t st, const CUtensorMap& ta, const PeerMaps& pm,
                          const IgemmParams& p) {
   static unsigned long long done = 0;     // bit per device
-  MPIT_CUDA_TRY(set_smem_limit_per_device(umma_pulled_gemm_kernel<BLOCK_N, MT, BY_K>, 208 * 1024, done));
+  MPIT_CUDA_TRY(set_smem_limit_per_device(umma_pulled_gemm_kernel<BLOCK_N, MT, BY_K>, 220 * 1024, done));
   MPIT_CUDA_TRY(launch_k(umma_pulled_gemm_kernel<BLOCK_N, MT, BY_K>, grid, dim3(192), smem, st, ta, pm, p));
   return 0;
 }
@@ -1008,20 +1043,25 @@ int mpit_umma_linear_pull(const void* tmap_a128, const void* tmaps_b, int nranks
 // symmetric memory; see umma_pulled_gemm_kernel.  `tmap_a128`: 4-D map [K,1,1,Mpad] box [32,1,1,128] over the local
 // activations; `tmaps_b`: HOST array of nranks x 128 bytes, one map per owner (by_k = 0: [rows_per_owner][K] box
 // [32, block_n]; by_k = 1: the transposed shard [N][rows_per_owner] box [32, block_n]).  K is the reduction length,
-// N the number of output columns; mt = M-tiles per CTA (1, 2 or 4; block_n * mt <= 256).
+// N the number of output columns; mt = M-tiles per CTA (1, 2 or 4; block_n * mt <= 256).  ksplit > 1 (by_k = 1, no
+// bias, no activation, K / 32 divisible by ksplit): split-K over ksplit CTAs per output tile; `out` is zeroed on the
+// stream first and the slices add into it.
 int mpit_umma_pulled_gemm(const void* tmap_a128, const void* tmaps_b, int nranks, int rows_per_owner, int by_k, int M,
                           int K, int N, int relu, const float* bias, float* out, int* err, int block_n, int mt,
-                          void* stream) {
+                          int ksplit, void* stream) {
   if (nranks < 1 || nranks > 8 || M < 1 || K % 32 || N % block_n || (block_n != 32 && block_n != 64) ||
-      (mt != 1 && mt != 2 && mt != 4))
+      (mt != 1 && mt != 2 && mt != 4) || ksplit < 1)
     return MPIT_E_ARG;
   if (by_k ? (rows_per_owner % 32 != 0 || K != nranks * rows_per_owner)
            : (rows_per_owner % block_n != 0 || N != nranks * rows_per_owner))
     return MPIT_E_ARG;
+  if (ksplit > 1 && (!by_k || relu || bias || (K / 32) % ksplit)) return MPIT_E_ARG;
   IgemmParams p{};
   p.nsub = 1; p.tw = 1; p.th = 1; p.tn = 128; p.tiles_w = 1; p.tiles_h = 1; p.kw_it = 1; p.cb = K / 32;
   p.num_kb = K / 32; p.sgn = 1; p.B = M; p.OH = 1; p.OW = 1; p.N = N; p.mode = EPI_STORE; p.relu = relu;
   p.scale = 1.f; p.bias = bias; p.out = out; p.err = err;
+  p.kb_split = p.num_kb / ksplit;
+  p.accum = ksplit > 1;
   CUtensorMap ta;
   PeerMaps pm;
   memset(&pm, 0, sizeof(pm));
@@ -1029,15 +1069,21 @@ int mpit_umma_pulled_gemm(const void* tmap_a128, const void* tmaps_b, int nranks
   for (int i = 0; i < nranks; ++i) memcpy(&pm.map[i], static_cast<const char*>(tmaps_b) + 128 * i, sizeof(CUtensorMap));
   pm.rows_per_owner = rows_per_owner;
   const int m_tiles = (M + 127) / 128;
-  dim3 grid((m_tiles + mt - 1) / mt, N / block_n);
+  dim3 grid((m_tiles + mt - 1) / mt, N / block_n, ksplit);
   cudaStream_t st = (cudaStream_t)stream;
-  const int stage_bytes = mt * kABytes + block_n * 128;
-  int stages = (200 * 1024) / stage_bytes;
-  if (stages > kMaxStages) stages = kMaxStages;
-  if (stages > p.num_kb) stages = p.num_kb;
-  if (stages < 2) stages = 2;
-  p.stages = stages;
-  const size_t smem = (size_t)stages * stage_bytes + 512 + 1024;
+  // ring depths: the activation ring as shallow as keeps the tensor core fed from L2 (4 / 3 / 2 stages of
+  // mt x 16 KB), everything else of ~216 KB for weight tiles in flight over NVLink
+  const int a_stage = mt * kABytes, b_tile = block_n * 128;
+  int sa = mt == 1 ? 4 : (mt == 2 ? 3 : 2);
+  if (sa > p.kb_split) sa = p.kb_split;
+  int sb = (216 * 1024 - sa * a_stage) / b_tile;
+  if (sb > kMaxBStages) sb = kMaxBStages;
+  if (sb > p.kb_split) sb = p.kb_split;
+  if (sb < sa) sb = sa;
+  p.stages = sa;
+  p.sb = sb;
+  const size_t smem = (size_t)sa * a_stage + (size_t)sb * b_tile + 512 + 1024;
+  if (ksplit > 1) MPIT_CUDA_TRY(cudaMemsetAsync(out, 0, (size_t)M * N * sizeof(float), st));
 #define MPIT_PULLED(BN, MTV)                                                                              \
   if (block_n == BN && mt == MTV)                                                                         \
     return by_k ? launch_pulled<BN, MTV, true>(grid, smem, st, ta, pm, p) : launch_pulled<BN, MTV, false>(grid, smem, st, ta, pm, p);

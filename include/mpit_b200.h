@@ -298,10 +298,13 @@ int mpit_umma_linear_pull(const void* tmap_a128, const void* tmaps_b, int nranks
  * W row-sharded over the owners' symmetric memory.  One CTA owns mt (1, 2, 4) 128-row M-tiles, so each weight tile
  * crosses NVLink once per CTA and feeds mt accumulators.  by_k = 1 reads the owners' TRANSPOSED shards
  * ([out][rows_per_owner]); the reduction then runs across owners, chosen per k-block.  M rows of x / dy, reduction
- * length K, N output columns; tmap_a128: 4-D map [K,1,1,Mpad] box [32,1,1,128]; tmaps_b: HOST array nranks x 128 B. */
+ * length K, N output columns; tmap_a128: 4-D map [K,1,1,Mpad] box [32,1,1,128]; tmaps_b: HOST array nranks x 128 B.
+ * Weight tiles travel in their own ring (up to 16 tiles in flight per CTA), ahead of the activation ring.
+ * ksplit > 1 (by_k = 1 only, no bias / activation, K / 32 divisible by ksplit): split-K; `out` is zeroed on the
+ * stream and the ksplit slices of an output tile add into it (red.add.v4.f32; summation order not fixed). */
 int mpit_umma_pulled_gemm(const void* tmap_a128, const void* tmaps_b, int nranks, int rows_per_owner, int by_k, int M,
                           int K, int N, int relu, const float* bias, float* out, int* err, int block_n, int mt,
-                          void* stream);
+                          int ksplit, void* stream);
 
 /* ---- tcgen05 weight gradients (csrc/kernels/umma_wgrad.cu) ------------------------------------- */
 /* dW = Xcol^T dZ over all output pixels, pixel dimension split over `nsplit` CTAs that each write a

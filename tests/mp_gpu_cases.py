@@ -469,6 +469,11 @@ def case_pulled_linear(rank, world, dev, heap):
         torch.cuda.synchronize()
         lin.check()
         assert float((dx.cpu() - dy @ W).norm() / (dy @ W).norm()) < 3e-3, M
+        for mt, ks in ((1, 1), (2, 2), (4, 4), (1, 4 * world)):      # M-tiles per CTA x split-K slices
+            dxs = lin.backward(dy.to(dev), mt=mt, ksplit=ks)
+            torch.cuda.synchronize()
+            lin.check()
+            assert float((dxs.cpu() - dy @ W).norm() / (dy @ W).norm()) < 3e-3, (M, mt, ks)
         assert float((gw.cpu() - dy.t() @ x).norm() / (dy.t() @ x).norm()) < 3e-3, M
         sync(dev)
         # push: every rank adds -0.5 * dW into the owners' rows and transposed copies

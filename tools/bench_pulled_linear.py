@@ -56,8 +56,10 @@ for (M, K, N) in [(128, 1024, 4096), (128, 4096, 4096), (512, 1024, 4096), (1024
     torch.cuda.synchronize()
     dist.barrier()
 
+    _, ta_x = lin._operand(x, K, lin.x)
+
     def fused_one_tile_per_cta():            # the round-1 kernel: every M-tile fetches its weight tiles again
-        check(kernels().mpit_umma_linear_pull(lin._ta, lin._maps, lin.S, lin.rows_per_owner, lin._geom, ptr(bias), ptr(lin.y),
+        check(kernels().mpit_umma_linear_pull(ta_x, lin._maps, lin.S, lin.rows_per_owner, lin._geom, ptr(bias), ptr(lin.y),
                                               ptr(lin.err), lin.block_n, cur_stream()), "mpit_umma_linear_pull")
 
     wfull = torch.empty(N, K, device=dev)
@@ -71,21 +73,29 @@ for (M, K, N) in [(128, 1024, 4096), (128, 4096, 4096), (512, 1024, 4096), (1024
         dist.all_gather_into_tensor(wfull, wmine)
         return dy @ wfull
 
+    timed(lambda: lin.forward(x, bias), iters=10)          # clocks up before the first number that is kept
     t_f = timed(lambda: lin.forward(x, bias))
     t_1, t_u = timed(fused_one_tile_per_cta), timed(nccl_then_cublas)
-    t_own = timed(lambda: lin._forward_unfused(bias))
+    t_own = timed(lambda: lin._forward_unfused(ta_x, bias))
     t_g = timed(lambda: F.relu(F.linear(x, wfull, bias)))
     lin.forward(x, bias)
     ref = F.relu(F.linear(x, wfull, bias))
     rel = float((lin.y.view(lin.M, N)[:M] - ref).norm() / ref.norm())
     t_b, t_bu = timed(lambda: lin.backward(dy)), timed(nccl_then_cublas_bwd)
+    # tiling sweeps (what the defaults were picked from): forward by M-tiles per CTA, backward by (M-tiles, split-K)
+    m_tiles = (M + 127) // 128
+    by_mt = {mt: round(timed(lambda mt=mt: lin.forward(x, bias, mt=mt), iters=20, warm=3), 1)
+             for mt in (1, 2, 4) if mt == 1 or m_tiles >= mt}
+    by_split = {f"{mt}x{ks}": round(timed(lambda mt=mt, ks=ks: lin.backward(dy, mt=mt, ksplit=ks), iters=20, warm=3), 1)
+                for mt in (1, 4) if mt == 1 or m_tiles >= mt for ks in (1, 4, 8)}
     refb = dy @ wfull
     relb = float((lin.backward(dy) - refb).norm() / refb.norm())
     assert int(lin.err.item()) == 0
     r = {"M": M, "K": K, "N": N, "n_gpus": world, "weight_MB": round(N * K * 4 / 2 ** 20, 1), "fused_us": round(t_f, 1),
          "fused_one_tile_per_cta_us": round(t_1, 1), "own_gather_then_gemm_us": round(t_own, 1),
          "nccl_allgather_plus_cublas_us": round(t_u, 1), "cublas_gemm_alone_us": round(t_g, 1), "rel_err_vs_cublas": rel,
-         "bwd_fused_us": round(t_b, 1), "bwd_nccl_allgather_plus_cublas_us": round(t_bu, 1), "bwd_rel_err_vs_cublas": relb}
+         "bwd_fused_us": round(t_b, 1), "bwd_nccl_allgather_plus_cublas_us": round(t_bu, 1), "bwd_rel_err_vs_cublas": relb,
+         "fwd_us_by_mtiles_per_cta": by_mt, "bwd_us_by_mtiles_x_splitk": by_split}
     rows.append(r)
     if rank == 0:
         print(json.dumps(r), flush=True)
