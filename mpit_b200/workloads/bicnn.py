@@ -496,15 +496,30 @@ class BiCNNDeviceTrainer(BiCNNKernelTrainer):
                                         server=server, use_graphs=use_graphs, seed_center=(rank == 0))
         self.parameters = self.optim.x                      # the flat vector the step works on
         self.reg_loss = torch.zeros(2, device=dev)
-        self._batch_host = torch.full((B,), -1, dtype=torch.int32).pin_memory()
+        # The step's sample indices reach the device by an asynchronous copy from pinned memory, and with the step in a
+        # CUDA graph the host runs many steps ahead of the GPU: every step in flight needs its own pinned slot (one
+        # buffer refilled per step would be read by the copy engine AFTER later steps had overwritten it).
+        self._batch_ring = [torch.full((B,), -1, dtype=torch.int32).pin_memory() for _ in range(32)]
+        self._batch_copied = [torch.cuda.Event() for _ in self._batch_ring]
+        self._staged = 0
         self.steps = 0
+
+    def _stage_batch(self, batch: List[int]) -> None:
+        """Sample indices of the next step -> ``eng.batch`` (stream-ordered copy from this step's pinned slot)."""
+        slot = self._staged % len(self._batch_ring)
+        if self._staged >= len(self._batch_ring):
+            self._batch_copied[slot].synchronize()          # only blocks when the GPU is a whole ring behind
+        h = self._batch_ring[slot]
+        h.fill_(-1)
+        h[:len(batch)] = torch.tensor(batch, dtype=torch.int32)
+        self.eng.batch.copy_(h, non_blocking=True)
+        self._batch_copied[slot].record()
+        self._staged += 1
 
     def train_step(self, batch: List[int]) -> None:
         """One mini-batch: ``batch`` lists sample indices (at most ``batchSize``)."""
         o = self.optim
-        self._batch_host.fill_(-1)
-        self._batch_host[:len(batch)] = torch.tensor(batch, dtype=torch.int32)
-        self.eng.batch.copy_(self._batch_host, non_blocking=True)
+        self._stage_batch(batch)
         do_sync = o.t % o.su == 0
 
         def body():

@@ -33,9 +33,7 @@ def test_device_batch_assembly_selection_and_gradient():
     eng = tr.eng
     B, K = opt["batchSize"], opt["maxnegsample"]
     batch = [5, 17, 2]                                  # one empty slot
-    tr._batch_host.fill_(-1)
-    tr._batch_host[:3] = torch.tensor(batch, dtype=torch.int32)
-    eng.batch.copy_(tr._batch_host)
+    tr._stage_batch(batch)
     eng.train_fwd_bwd()
     torch.cuda.synchronize()
     eng.check()
@@ -90,6 +88,24 @@ def test_device_batch_assembly_selection_and_gradient():
     eng.train_fwd_bwd()
     torch.cuda.synchronize()
     assert not torch.equal(eng.neg_idx.cpu().view(B, K)[:3], negs[:3])
+    tr.close()
+
+
+def test_every_step_in_flight_keeps_its_own_batch():
+    """The host runs ahead of the GPU (the step is a graph launch): the sample indices of step t must still be the ones
+    the device sees at step t.  The GPU is held busy while 48 steps' indices are staged; a device-side log records
+    what each step would have read."""
+    W, corpus, opt, tr = _make([])
+    B = opt["batchSize"]
+    log = torch.full((48, B), -7, dtype=torch.int32, device="cuda")
+    torch.cuda._sleep(int(3e8))                                   # ~0.15 s of GPU time in front of everything
+    for i in range(48):
+        tr._stage_batch([i, i + 1][:B])
+        log[i].copy_(tr.eng.batch)
+    torch.cuda.synchronize()
+    got = log.cpu()
+    for i in range(48):
+        assert got[i].tolist()[:2] == [i, i + 1][:B] and all(int(v) == -1 for v in got[i][2:]), (i, got[i].tolist())
     tr.close()
 
 
