@@ -673,8 +673,9 @@ umma_igemm_pull_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
 // Two rings instead of one: the local activation tiles (MT x 16 KB per k-block, L2 latency) and the remote weight
 // tiles (4 / 8 KB per k-block, NVLink latency) have very different latency x size products.  With one ring of
 // [A | B] stages only two stages fit at MT = 4, i.e. two weight tiles in flight per CTA, and every k-block then
-// waited a whole NVLink round trip.  The B ring is `p.sb` slots deep (up to 16) and is filled by its own thread, so
-// it runs up to `sb` k-blocks ahead of the MMAs whatever the A ring is doing.
+// waited a whole NVLink round trip.  The B ring is `p.sb` slots deep (up to 16) and runs `sb - stages` k-blocks
+// ahead of the A ring, issued by the same thread: slot B(j + sb - stages) and slot A(j) are both released by the
+// MMAs of k-block j - stages, so running ahead costs no extra waiting.
 // gridDim.z > 1 (data gradient only): split-K -- slice z reduces k-blocks [z * kb_split, (z+1) * kb_split) and the
 // epilogue adds its partial tile into the (zeroed) output with red.add.v4.f32, which gives the few-output-tile,
 // long-reduction shape of dx = dy W enough CTAs.
@@ -723,28 +724,37 @@ umma_pulled_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
     for (int c = threadIdx.x - 64; c < BLOCK_N; c += 128)
       bias_s[c] = (p.bias && (!BY_K || blockIdx.z == 0)) ? p.bias[n_tile0 + c] : 0.f;
 
-  // Producers.  One thread issuing a k-block's B load and MT A loads is a dependent chain of ~200 clocks per load (wait,
-  // expect_tx, coordinates, issue) -- longer than the MMAs of the k-block; ncu showed the feed at 35 B/clk/SM.  So the
-  // loads are dealt out as in the convolution kernels: warp 0's elected lane streams the weight tiles (its ring is free
-  // running, bounded only by its depth), the elected lanes of the four epilogue warps -- idle until the accumulators are
-  // complete -- issue activation tile 0..3 of EVERY k-block, producer 0 also posting the stage's expect_tx.  Each producer
-  // walks the k-blocks in order, so its empty-barrier parity test stays unambiguous.
   if (warp == 0) {
     if (elect_one()) {
       const int owner_n = BY_K ? 0 : n_tile0 / pm.rows_per_owner;
-      int bs = 0, bph = 0;
-      for (int j = 0; j < nkb; ++j) {
-        if (j >= SB && !mbar_wait(&empty_b[bs], bph ^ 1)) { if (p.err) *p.err = 1; break; }
+      int as = 0, aph = 0, bs = 0, bph = 0, jb = 0;
+      bool ok = true;
+      auto issue_b = [&]() {   // weight tile of local k-block jb, from its owner's shard
+        if (jb >= SB && !mbar_wait(&empty_b[bs], bph ^ 1)) { ok = false; return; }
         mbar_expect_tx(&full_b[bs], (uint32_t)kBBytes);
-        const int kb = kb0 + j;
+        const int kb = kb0 + jb;
         if (BY_K) {
           const int owner = (kb * 32) / pm.rows_per_owner;
           tma_load_2d(smem_b + bs * kBBytes, &pm.map[owner], &full_b[bs], kb * 32 - owner * pm.rows_per_owner, n_tile0);
         } else {
           tma_load_2d(smem_b + bs * kBBytes, &pm.map[owner_n], &full_b[bs], kb * 32, n_tile0 - owner_n * pm.rows_per_owner);
         }
+        ++jb;
         if (++bs == SB) { bs = 0; bph ^= 1; }
+      };
+      const int ahead = SB - SA;
+      while (jb < ahead && jb < nkb) issue_b();          // never waits: jb < SB
+      for (int j = 0; j < nkb && ok; ++j) {
+        if (jb < nkb) issue_b();
+        if (!ok) break;
+        if (j >= SA && !mbar_wait(&empty_a[as], aph ^ 1)) { ok = false; break; }
+        uint8_t* dst = smem + as * kAStage;
+        mbar_expect_tx(&full_a[as], (uint32_t)(mt_here * kABytes));
+        for (int mt = 0; mt < mt_here; ++mt)
+          tma_load_4d(dst + mt * kABytes, &tmap_a, &full_a[as], (kb0 + j) * 32, 0, 0, (mt0 + mt) * 128);
+        if (++as == SA) { as = 0; aph ^= 1; }
       }
+      if (!ok && p.err) *p.err = 1;
     }
   } else if (warp == 1) {
     if (elect_one()) {
@@ -771,17 +781,6 @@ umma_pulled_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid
       mma_commit(tmem_full);
     }
   } else {
-    const int pj = warp - 2;
-    if (pj < mt_here && elect_one()) {
-      int as = 0, aph = 0;
-      for (int j = 0; j < nkb; ++j) {
-        if (j >= SA && !mbar_wait(&empty_a[as], aph ^ 1)) { if (p.err) *p.err = 4; break; }
-        if (pj == 0) mbar_expect_tx(&full_a[as], (uint32_t)(mt_here * kABytes));
-        tma_load_4d(smem + as * kAStage + pj * kABytes, &tmap_a, &full_a[as], (kb0 + j) * 32, 0, 0, (mt0 + pj) * 128);
-        if (++as == SA) { as = 0; aph ^= 1; }
-      }
-    }
-    __syncwarp();
     const int quad = warp & 3;
     const int row = quad * 32 + lane;
     for (int mt = 0; mt < mt_here; ++mt) {
