@@ -92,10 +92,14 @@ def test_three_paths_learn_the_same_thing():
     print("smoothed loss curves:", {k: [round(x, 3) for x in v] for k, v in sm.items()}, "accuracy:", acc)
     # the curves stay together: the paths differ in their dropout streams (and, for TF32, in rounding), which shifts
     # the steep part of the descent by a few steps -- hence a tolerance that is relative to the loss level
-    # Compared over the descent (windows in which the fp32 torch model is still above 0.15): once a path has converged
-    # its loss is dominated by rare SGD spikes of its own dropout stream.
-    descent = [i for i, b in enumerate(sm["torch"]) if b > 0.15 and all(x > 0.15 for x in sm["torch"][:i])]
+    # Compared over the descent (windows in which the fp32 torch model is still above 0.5): below that a path's loss is
+    # dominated by rare SGD spikes of its own dropout stream, which land in different windows on different paths (seen:
+    # 0.44 against 0.16 in one window, 0.14 against 0.42 in the next).  After the descent the paths are compared on
+    # the level they settle at (median of the late windows), not window by window.
+    descent = [i for i, b in enumerate(sm["torch"]) if b > 0.5 and all(x > 0.5 for x in sm["torch"][:i])]
     assert len(descent) >= 6, sm["torch"]
+    late = {k: sorted(v[-6:])[2] for k, v in sm.items()}
+    assert max(late.values()) < 0.3, late
     for k in ("umma", "umma3x", "ref"):
         for i in descent:
             a, b = sm[k][i], sm["torch"][i]
