@@ -10,8 +10,6 @@ The reference's own build (Lua/Torch7 + MPI) cannot be installed on this image (
 from __future__ import annotations
 
 import json
-import os
-import sys
 import time
 
 import torch

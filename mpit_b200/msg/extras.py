@@ -15,7 +15,7 @@ out-parameters, errors raise :class:`MPIError`.
 from __future__ import annotations
 
 import socket
-from typing import Callable, Dict, List, Optional, Sequence, Tuple
+from typing import Callable, Dict, List, Sequence, Tuple
 
 import numpy as np
 import torch

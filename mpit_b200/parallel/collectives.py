@@ -7,7 +7,6 @@ asyncsgd/testreduceall.lua:76), MPI_Bcast (wrapped only, mpifuncs.c:145), MPI_Se
 """
 from __future__ import annotations
 
-import ctypes
 import os
 from typing import Optional
 

@@ -327,7 +327,7 @@ def train_epochs(tr: CifarTrainer, train_xy, test_xy, rank: int = -1, quiet: boo
     ``train.log``/``test.log`` rows, a Torch7 ``model-epoch-N.net`` every ``saveep`` epochs (a loadable
     ``nn.Sequential``, goot.lua:246-254), test after every epoch, timing summary (goot.lua:330-337)."""
     from .. import t7
-    from ..utils import Logger, ConfusionMatrix
+    from ..utils import Logger
     opts = tr.opts
     B = opts.mb
     (trx, try_), (tex, tey) = train_xy, test_xy
