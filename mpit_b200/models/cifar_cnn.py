@@ -322,7 +322,8 @@ class CifarEngine:
         """Stage one mini-batch: ONE launch converts the uint8 images into the network's input layout
         (/255, pair-expanded NHWC8) and moves labels and crop offsets into the engine's buffers.  Device tensors
         are read in place (no staging copies: three small device-to-device copies in front of every step cost
-        ~10 us of a 140 us step); host tensors are first copied (asynchronously when pinned).  The conversion is
+        ~10 us of a 140 us step); host tensors are first copied (asynchronously when pinned -- the caller must then
+        leave them alone until the stream has passed this point; ``CifarTrainer.train_step`` does that bookkeeping).  The conversion is
         NOT part of the captured step graph, so ``forward`` / ``fwd_bwd`` / ``evaluate`` always use the batch
         staged by the latest ``set_batch``."""
         if not images_u8.is_cuda:

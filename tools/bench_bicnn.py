@@ -176,11 +176,11 @@ def main():
         nparams = tr.parameters.numel()
     else:
         tr = TorchPS(corpus, opt, dev, rank, world)
-        pinned = torch.zeros(B, dtype=torch.int64).pin_memory()
 
         def step(b):
-            pinned.copy_(torch.tensor(b))
-            tr.step(pinned.to(dev, non_blocking=True))
+            # a pinned block of its own per step (torch's pinned allocator recycles a block only after the copy that
+            # reads it has run): the host may run ahead of the GPU
+            tr.step(torch.tensor(b).pin_memory().to(dev, non_blocking=True))
         read_loss = lambda: float(tr.loss.item())
         nparams = tr.n
     barrier()
