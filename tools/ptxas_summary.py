@@ -28,7 +28,7 @@ out = ["# ptxas -v per kernel (sm_100a, final build)", "",
        f"{len(rows)} kernels, {sum(1 for r in rows if r[4])} of them with spill stores (8-48 bytes in the once-per-CTA epilogue code of some "
        "`umma_igemm_kernel` instantiations, in the index arithmetic of `ps_push_kernel` / `rule_kernel<5>` and in the 4-way unrolled "
        "peer-load all-reduce; 580 bytes in `classifier_head_kernel<16, 16>`, the 512-input instantiation that neither model uses -- "
-       "the CIFAR head is `<8, 16>`).  No kernel spills inside a tensor-core main loop.", "",
+       "the CIFAR head is `<8, 16>`).  Where a reload does sit in a main loop (three `LDL` after the four `UTCHMMA` of a k-block in `umma_igemm_kernel<32, 0>`) it is executed by the one issuing thread, once per k-block of several hundred clocks.", "",
        "| source | kernel | registers | stack B | spill stores B | spill loads B | static smem B |", "|---|---|---:|---:|---:|---:|---:|"]
 out += [f"| `{s}` | `{d}` | {regs} | {stack} | {sst} | {sld} | {smem} |" for s, d, regs, stack, sst, sld, smem in rows]
 (ROOT / "profiles" / "ptxas_summary.md").write_text("\n".join(out) + "\n")
